@@ -1,0 +1,329 @@
+// oracle/_ref driver: a C interface over the UNMODIFIED reference sensor models
+// (TEST INFRASTRUCTURE -- not part of the product; only tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline / --impl reference legs may load the library built from it).
+//
+// The reference sources are compiled where they lie under /root/reference by
+// oracle/Makefile; this file only adds the loop a caller of the reference writes itself
+// (/root/reference/bin/usgscsm_cam_test.cc:294-309): one csm::RasterGM virtual call per
+// point, optionally under OpenMP over points (the calls are const and re-entrant,
+// SURVEY.md §5).  Per point it records the result, achievedPrecision and a status word
+// rebuilt from the csm::WarningList / thrown csm::Error, using the same bit layout as
+// include/usgscsm_b200.h.
+// Everything the model headers pull in is included first, so that the access hack below
+// touches the four model class definitions only.
+#include <any>
+#include <sstream>
+#include <nlohmann/json.hpp>
+#include <RasterGM.h>
+#include <CorrelationModel.h>
+#include <SettableEllipsoid.h>
+#include "Utilities.h"
+#include "Distortion.h"
+#include "EigenUtilities.h"
+#include "VariantMap.h"
+#include "ale/Orientations.h"
+#include "ale/States.h"
+#define private public  // oracle only: read m_projTransCoeffs & friends for the tests
+#define protected public
+#include "UsgsAstroFrameSensorModel.h"
+#include "UsgsAstroLsSensorModel.h"
+#include "UsgsAstroPushFrameSensorModel.h"
+#include "UsgsAstroSarSensorModel.h"
+#undef private
+#undef protected
+#include "UsgsAstroPlugin.h"
+#include "Utilities.h"
+#include "Distortion.h"
+#include "EigenUtilities.h"
+
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <string>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+enum : uint32_t {
+  ST_NO_INTERSECTION = 1u << 0,
+  ST_PRECISION_NOT_MET = 1u << 1,
+  ST_ERROR_ALGORITHM = 1u << 5,
+  ST_ERROR_UNKNOWN = 1u << 6,
+  ST_NONFINITE = 1u << 7,
+  ST_OUT_OF_IMAGE = 1u << 8,
+  ST_ERROR_OTHER = 1u << 9,
+};
+
+struct RefModel {
+  std::unique_ptr<csm::Model> model;
+  csm::RasterGM *gm = nullptr;
+  std::string state;
+};
+
+thread_local std::string g_lastError;
+
+uint32_t bitsFromWarnings(const csm::WarningList &w) {
+  uint32_t s = 0;
+  for (const csm::Warning &x : w) {
+    if (x.getWarning() == csm::Warning::NO_INTERSECTION) s |= ST_NO_INTERSECTION;
+    if (x.getWarning() == csm::Warning::PRECISION_NOT_MET) s |= ST_PRECISION_NOT_MET;
+  }
+  return s;
+}
+
+uint32_t bitsFromError(const csm::Error &e) {
+  if (e.getError() == csm::Error::ALGORITHM) return ST_ERROR_ALGORITHM;
+  if (e.getError() == csm::Error::UNKNOWN_ERROR) return ST_ERROR_UNKNOWN;
+  return ST_ERROR_OTHER;
+}
+
+int pickThreads(int threads) {
+#ifdef _OPENMP
+  return threads > 0 ? threads : omp_get_max_threads();
+#else
+  (void)threads;
+  return 1;
+#endif
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *ref_last_error() { return g_lastError.c_str(); }
+
+int ref_max_threads() { return pickThreads(0); }
+
+// Build a model through the reference plugin from a model-state string
+// ("<MODEL_NAME>\n{json}" or bare JSON; /root/reference/src/UsgsAstroPlugin.cpp:535-555).
+void *ref_model_from_state(const char *state, size_t len) {
+  try {
+    UsgsAstroPlugin plugin;
+    std::string s(state, len);
+    csm::Model *m = plugin.constructModelFromState(s, nullptr);
+    auto *rm = new RefModel;
+    rm->model.reset(m);
+    rm->gm = dynamic_cast<csm::RasterGM *>(m);
+    if (!rm->gm) {
+      delete rm;
+      g_lastError = "model is not a csm::RasterGM";
+      return nullptr;
+    }
+    return rm;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return nullptr;
+  }
+}
+
+void ref_model_free(void *h) { delete static_cast<RefModel *>(h); }
+
+// getModelState() of the live model; returns the length, copies up to cap bytes.
+size_t ref_model_state(void *h, char *out, size_t cap) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  rm->state = rm->model->getModelState();
+  if (out && cap) {
+    size_t n = rm->state.size() < cap ? rm->state.size() : cap;
+    std::memcpy(out, rm->state.data(), n);
+  }
+  return rm->state.size();
+}
+
+// Host-derived quantities of a line-scan model that are inputs to the per-point math
+// (SURVEY.md §3.1): out[0..3] = gsd, flyingHeight, halfSwath, halfTime; out[4] =
+// useApproxInitTrans; out[5..18] = projTransCoeffs; out[19..21] = reference point.
+int ref_ls_derived(void *h, double *out) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  auto *ls = dynamic_cast<UsgsAstroLsSensorModel *>(rm->model.get());
+  if (!ls) return -1;
+  out[0] = ls->m_gsd;
+  out[1] = ls->m_flyingHeight;
+  out[2] = ls->m_halfSwath;
+  out[3] = ls->m_halfTime;
+  out[4] = ls->m_useApproxInitTrans ? 1.0 : 0.0;
+  for (int i = 0; i < 14; i++)
+    out[5 + i] = i < (int)ls->m_projTransCoeffs.size() ? ls->m_projTransCoeffs[i] : 0.0;
+  out[19] = ls->m_referencePointXyz.x;
+  out[20] = ls->m_referencePointXyz.y;
+  out[21] = ls->m_referencePointXyz.z;
+  return 0;
+}
+
+// Override the line-scan projective seed (so oracle and kernel can be fed identical
+// host-fitted coefficients; the fit is an INPUT to the hot path).
+int ref_ls_set_projective(void *h, int use, const double *coeffs14) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  auto *ls = dynamic_cast<UsgsAstroLsSensorModel *>(rm->model.get());
+  if (!ls) return -1;
+  ls->m_useApproxInitTrans = use != 0;
+  if (coeffs14) ls->m_projTransCoeffs.assign(coeffs14, coeffs14 + 14);
+  return 0;
+}
+
+// Set an adjustable parameter through the CSM API (GeometricModel::setParameterValue).
+int ref_set_parameter(void *h, int index, double value) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  try {
+    rm->gm->setParameterValue(index, value);
+    return 0;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return -1;
+  }
+}
+
+int ref_image_size(void *h, int *lines, int *samps) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  csm::ImageVector v = rm->gm->getImageSize();
+  *lines = (int)v.line;
+  *samps = (int)v.samp;
+  return 0;
+}
+
+// groundToImage over n points.  SoA inputs; outputs nullable except line/samp.
+int ref_ground_to_image(void *h, long n, const double *x, const double *y, const double *z,
+                        double prec, double *line, double *samp, double *achieved,
+                        uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const auto range = gm->getValidImageRange();
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    csm::ImageCoord ip(std::nan(""), std::nan(""));
+    try {
+      csm::WarningList warn;
+      ip = gm->groundToImage(csm::EcefCoord(x[i], y[i], z[i]), prec, &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+    }
+    if (!(std::isfinite(ip.line) && std::isfinite(ip.samp))) st |= ST_NONFINITE;
+    if (!(ip.line >= range.first.line && ip.line <= range.second.line &&
+          ip.samp >= range.first.samp && ip.samp <= range.second.samp))
+      st |= ST_OUT_OF_IMAGE;
+    line[i] = ip.line;
+    samp[i] = ip.samp;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
+// imageToGround over n points; `height` has n entries (height_stride 1) or 1 (stride 0).
+int ref_image_to_ground(void *h, long n, const double *line, const double *samp,
+                        const double *height, int height_stride, double prec, double *x,
+                        double *y, double *z, double *achieved, uint32_t *status,
+                        int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    csm::EcefCoord gp(std::nan(""), std::nan(""), std::nan(""));
+    try {
+      csm::WarningList warn;
+      gp = gm->imageToGround(csm::ImageCoord(line[i], samp[i]),
+                             height[height_stride ? i : 0], prec, &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+    }
+    if (!(std::isfinite(gp.x) && std::isfinite(gp.y) && std::isfinite(gp.z))) st |= ST_NONFINITE;
+    x[i] = gp.x;
+    y[i] = gp.y;
+    z[i] = gp.z;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
+// ---- L1 math entry points, for replaying the reference's known-answer tests ---------
+// (/root/reference/tests/UtilitiesTests.cpp, DistortionTests.cpp, EigenUtilitiesTests.cpp)
+
+int ref_lagrange(int numTime, const double *values, double startTime, double delTime,
+                 double time, int vectorLength, int order, double *out) {
+  try {
+    lagrangeInterp(numTime, values, startTime, delTime, time, vectorLength, order, out);
+    return 0;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return -1;
+  }
+}
+
+int ref_remove_distortion(double dx, double dy, double *ux, double *uy, const double *coeffs,
+                          int ncoeffs, double focal, int type, double tolerance) {
+  try {
+    std::vector<double> c(coeffs, coeffs + ncoeffs);
+    removeDistortion(dx, dy, *ux, *uy, c, focal, (DistortionType)type, tolerance);
+    return 0;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return -1;
+  }
+}
+
+int ref_apply_distortion(double ux, double uy, double *dx, double *dy, const double *coeffs,
+                         int ncoeffs, double focal, int type, double desiredPrecision,
+                         double tolerance) {
+  try {
+    std::vector<double> c(coeffs, coeffs + ncoeffs);
+    applyDistortion(ux, uy, *dx, *dy, c, focal, (DistortionType)type, desiredPrecision,
+                    tolerance);
+    return 0;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return -1;
+  }
+}
+
+double ref_ellipsoid_elevation(double x, double y, double z, double a, double b, double prec,
+                               double *achieved) {
+  return computeEllipsoidElevation(x, y, z, a, b, prec, achieved);
+}
+
+void ref_rotation_from_quaternion(const double *q, double *m9) {
+  double qq[4] = {q[0], q[1], q[2], q[3]};
+  calculateRotationMatrixFromQuaternions(qq, m9);
+}
+
+void ref_rotation_from_euler(const double *e, double *m9) {
+  double ee[3] = {e[0], e[1], e[2]};
+  calculateRotationMatrixFromEuler(ee, m9);
+}
+
+int ref_projective_fit(int npts, const double *line, const double *samp, const double *x,
+                       const double *y, const double *z, double *coeffs14) {
+  try {
+    std::vector<csm::ImageCoord> ip;
+    std::vector<csm::EcefCoord> gp;
+    for (int i = 0; i < npts; i++) {
+      ip.push_back(csm::ImageCoord(line[i], samp[i]));
+      gp.push_back(csm::EcefCoord(x[i], y[i], z[i]));
+    }
+    std::vector<double> u;
+    usgscsm::computeBestFitProjectiveTransform(ip, gp, u);
+    for (int i = 0; i < 14; i++) coeffs14[i] = u[i];
+    return 0;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return -1;
+  }
+}
+
+}  // extern "C"
