@@ -1,0 +1,162 @@
+/* usgscsm_b200.h -- C-ABI of the B200-native batched sensor-model engine.
+ *
+ * This is the drop-in boundary for the ONE data-parallel hot path of DOI-USGS/usgscsm:
+ * per-point csm::RasterGM::groundToImage / imageToGround of the USGS Astro line-scan,
+ * push-frame, frame and SAR sensor models, evaluated for whole batches of points by
+ * hand-written sm_100a CUDA kernels (one thread per point, FP64).
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * reference repository root).  Plain pointers and sizes only: no C++ or torch types.
+ *
+ * Conventions
+ *   - all functions return 0 on success or a negative USGSCSM_B200_E* code; the message of
+ *     the last failure on the calling thread is returned by usgscsm_b200_last_error();
+ *   - per-point failures never fail the call: they are reported in the `status` words
+ *     (bit-field below), which restate the reference's csm::Warning list and thrown
+ *     csm::Error of the scalar call for that point;
+ *   - the library has NO CPU implementation of the per-point math.  If no CUDA device is
+ *     usable every compute entry point fails with USGSCSM_B200_ENODEVICE.
+ */
+#ifndef USGSCSM_B200_H_
+#define USGSCSM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define USGSCSM_B200_ABI_VERSION 1
+
+/* ---- error codes (function return values) ------------------------------------------ */
+#define USGSCSM_B200_OK 0
+#define USGSCSM_B200_EINVAL -1    /* bad argument                                        */
+#define USGSCSM_B200_ESTATE -2    /* model state could not be parsed / is inconsistent   */
+#define USGSCSM_B200_ENODEVICE -3 /* no usable CUDA device                               */
+#define USGSCSM_B200_ECUDA -4     /* a CUDA runtime call failed                          */
+#define USGSCSM_B200_EUNSUPPORTED -5
+
+/* ---- model kinds: csm model names of src/UsgsAstroPlugin.cpp:62-69 ------------------ */
+#define USGSCSM_B200_MODEL_LINE_SCANNER 1 /* USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL */
+#define USGSCSM_B200_MODEL_PUSH_FRAME 2   /* USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL   */
+#define USGSCSM_B200_MODEL_FRAME 3        /* USGS_ASTRO_FRAME_SENSOR_MODEL        */
+#define USGSCSM_B200_MODEL_SAR 4          /* USGS_ASTRO_SAR_SENSOR_MODEL          */
+
+/* ---- per-point status bits ----------------------------------------------------------
+ * Bits 0,1 restate csm::Warning::WarningType entries pushed by the scalar call
+ * (csm/Warning.h:39-47); bits 5,6,9 restate the csm::Error the scalar call would have
+ * thrown (csm/Error.h:40-48) -- the outputs of such a point are NaN; bits 7,8 are derived
+ * the way a caller of the reference derives them; bits 2-4 are diagnostics only this
+ * engine can see (the reference does not report them). */
+#define USGSCSM_B200_ST_NO_INTERSECTION (1u << 0)   /* Warning::NO_INTERSECTION (LS:2433-2441)   */
+#define USGSCSM_B200_ST_PRECISION_NOT_MET (1u << 1) /* Warning::PRECISION_NOT_MET (LS:882-887)   */
+#define USGSCSM_B200_ST_ITERATION_CAP (1u << 2)     /* root search hit its iteration cap         */
+#define USGSCSM_B200_ST_SEARCH_STALL (1u << 3)      /* secant stopped on equal residuals         */
+#define USGSCSM_B200_ST_DISTORTION_NOT_CONVERGED (1u << 4)
+#define USGSCSM_B200_ST_ERROR_ALGORITHM (1u << 5)   /* Error::ALGORITHM  (Distortion.cpp:357-365) */
+#define USGSCSM_B200_ST_ERROR_UNKNOWN (1u << 6)     /* Error::UNKNOWN_ERROR (SAR:569-575)        */
+#define USGSCSM_B200_ST_NONFINITE (1u << 7)         /* an output coordinate is NaN/Inf           */
+#define USGSCSM_B200_ST_OUT_OF_IMAGE (1u << 8)      /* g2i result outside getValidImageRange()   */
+#define USGSCSM_B200_ST_ERROR_OTHER (1u << 9)
+/* the bits the reference itself makes observable (compared bit-exactly in the tests) */
+#define USGSCSM_B200_ST_REFERENCE_MASK \
+  (USGSCSM_B200_ST_NO_INTERSECTION | USGSCSM_B200_ST_PRECISION_NOT_MET | \
+   USGSCSM_B200_ST_ERROR_ALGORITHM | USGSCSM_B200_ST_ERROR_UNKNOWN |     \
+   USGSCSM_B200_ST_NONFINITE | USGSCSM_B200_ST_OUT_OF_IMAGE | USGSCSM_B200_ST_ERROR_OTHER)
+
+typedef struct usgscsm_b200_model usgscsm_b200_model;
+
+/* ---- library ------------------------------------------------------------------------ */
+int usgscsm_b200_abi_version(void);
+const char *usgscsm_b200_last_error(void);
+/* Number of CUDA devices the engine can use (0 when there is none). */
+int usgscsm_b200_device_count(void);
+
+/* ---- model construction ---------------------------------------------------------------
+ * Replaces UsgsAstroPlugin::constructModelFromState (src/UsgsAstroPlugin.cpp:535-555) +
+ * <Model>::populateModel (LS: src/UsgsAstroLsSensorModel.cpp:141-293): `state` is a model
+ * state string as written by getModelState() -- "<MODEL_NAME>\n{json}", bare JSON, or the
+ * body of a GXP .sup file (non-printable bytes are treated as newlines and the text is cut
+ * to the outermost braces, src/Utilities.cpp:2489-2500).  The packed device state is
+ * uploaded to CUDA device `device`.  Derived quantities the reference computes at load time
+ * with its own per-point calls (updateState LS:649-735, createProjectiveApproximation
+ * LS:2745-2803) are computed here by running the batch kernels on those points. */
+int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
+                                  usgscsm_b200_model **out);
+/* csm::Model destructor. */
+void usgscsm_b200_model_free(usgscsm_b200_model *m);
+/* USGSCSM_B200_MODEL_* */
+int usgscsm_b200_model_kind(const usgscsm_b200_model *m);
+int usgscsm_b200_model_device(const usgscsm_b200_model *m);
+/* csm::RasterGM::getImageSize (LS:1845-1852). */
+int usgscsm_b200_model_image_size(const usgscsm_b200_model *m, int *lines, int *samps);
+/* csm::GeometricModel::getNumParameters / getParameterValue / setParameterValue
+ * (LS:1585-1620).  Setting a parameter re-packs the device state. */
+int usgscsm_b200_model_num_parameters(const usgscsm_b200_model *m);
+int usgscsm_b200_model_get_parameter(const usgscsm_b200_model *m, int index, double *value);
+int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double value);
+/* Host-derived inputs of the line-scan per-point math:
+ * out[0..3] = gsd, flyingHeight, halfSwath, halfTime; out[4] = useApproxInitTrans;
+ * out[5..18] = the 14 projective-seed coefficients (LS:2688-2736); out[19..21] = reference
+ * point.  Only meaningful for the line-scan model. */
+int usgscsm_b200_model_ls_derived(const usgscsm_b200_model *m, double *out22);
+/* Override the projective seed (m_useApproxInitTrans, m_projTransCoeffs). */
+int usgscsm_b200_model_ls_set_projective(usgscsm_b200_model *m, int use,
+                                         const double *coeffs14);
+
+/* ---- per-point math, batched ------------------------------------------------------------
+ * groundToImage: replaces csm::RasterGM::groundToImage(const EcefCoord&, double
+ * desiredPrecision, double* achievedPrecision, WarningList*) (csm/RasterGM.h;
+ * LS:757-890, PF:715-778, FR:137-232, SAR:541-593) called once per point.
+ *   x,y,z     body-fixed ground coordinates, metres, n each (SoA)
+ *   prec      desiredPrecision (reference default 0.001)
+ *   line,samp outputs, n each
+ *   achieved  nullable; the value the scalar call writes to *achievedPrecision
+ *   status    nullable; USGSCSM_B200_ST_* bits
+ * The plain flavour takes HOST pointers and performs the host<->device copies itself
+ * (chunked and overlapped with the kernels); the _dev flavour takes DEVICE pointers on
+ * the model's device and enqueues on `stream` (a cudaStream_t; NULL = default stream)
+ * without synchronising. */
+int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double *x,
+                                 const double *y, const double *z, double prec, double *line,
+                                 double *samp, double *achieved, uint32_t *status);
+int usgscsm_b200_ground_to_image_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+                                     const double *y, const double *z, double prec,
+                                     double *line, double *samp, double *achieved,
+                                     uint32_t *status, void *stream);
+
+/* imageToGround: replaces csm::RasterGM::imageToGround(const ImageCoord&, double height,
+ * double desiredPrecision, double* achievedPrecision, WarningList*) (LS:980-1009,
+ * PF:842-870, FR:280-372, SAR:775-861).
+ *   height         heights above the ellipsoid, metres; n entries when height_stride = 1,
+ *                  one entry when height_stride = 0 */
+int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double *line,
+                                 const double *samp, const double *height, int height_stride,
+                                 double prec, double *x, double *y, double *z, double *achieved,
+                                 uint32_t *status);
+int usgscsm_b200_image_to_ground_dev(usgscsm_b200_model *m, int64_t n, const double *line,
+                                     const double *samp, const double *height,
+                                     int height_stride, double prec, double *x, double *y,
+                                     double *z, double *achieved, uint32_t *status,
+                                     void *stream);
+
+/* Dense-grid imageToGround: the double loop of bin/usgscsm_cam_test.cc:294-309 (and of an
+ * orthorectifier) with the pixel coordinates generated in the kernel.  Point k =
+ * r * n_samps + c is pixel (line0 + r * dline, samp0 + c * dsamp), r < n_lines,
+ * c < n_samps; `height` as above, indexed by k.  Device pointers. */
+int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, double samp0,
+                                          double dline, double dsamp, int64_t n_lines,
+                                          int64_t n_samps, const double *height,
+                                          int height_stride, double prec, double *x, double *y,
+                                          double *z, double *achieved, uint32_t *status,
+                                          void *stream);
+
+/* Number of kernels this library has launched on the calling process so far (all models,
+ * all streams).  bench.py reports the difference over its timed region as gpu_launches. */
+int64_t usgscsm_b200_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* USGSCSM_B200_H_ */

@@ -1,0 +1,43 @@
+// kernels.h -- host-side declarations of the kernel launchers (one .cu per sensor model).
+#ifndef USGSCSM_B200_KERNELS_H_
+#define USGSCSM_B200_KERNELS_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "sensor_state.h"
+
+namespace ub200 {
+
+// Tables up to this size are staged into shared memory by every block (keeps >= 4 blocks
+// of 256 threads resident per SM: 4 x 48 KB < 227 KB); larger tables (e.g. the 1.28 MB
+// HiRISE quaternion table) are read through L1/L2, where neighbouring threads -- which
+// need neighbouring times -- hit the same lines.
+constexpr size_t kMaxStagedTableBytes = 48 * 1024;
+// Persistent grid: resident blocks per SM the launchers size the grid for.
+constexpr int kBlocksPerSm = 4;
+
+struct LaunchShape {
+  int blocks;
+  int threads;
+};
+
+// Dense pixel grid: point k = r * nSamps + c  ->  (line0 + r * dline, samp0 + c * dsamp).
+struct GridSpec {
+  double line0, samp0, dline, dsamp;
+  long nSamps;
+};
+
+void countLaunch();
+
+cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const double *x,
+                                  const double *y, const double *z, double prec, double *line,
+                                  double *samp, double *achieved, uint32_t *status,
+                                  cudaStream_t stream);
+cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const double *line,
+                                  const double *samp, const GridSpec *grid, const double *height,
+                                  int heightStride, double prec, double *x, double *y, double *z,
+                                  double *achieved, uint32_t *status, cudaStream_t stream);
+
+}  // namespace ub200
+#endif

@@ -1,0 +1,244 @@
+// ls_common.cuh -- exterior orientation and ray geometry shared by the line-scan and
+// push-frame kernels (the reference's two models are near copies of each other:
+// src/UsgsAstroLsSensorModel.cpp and src/UsgsAstroPushFrameSensorModel.cpp).
+#ifndef USGSCSM_B200_LS_COMMON_CUH_
+#define USGSCSM_B200_LS_COMMON_CUH_
+
+#include "device_math.cuh"
+
+namespace ub200 {
+
+// Where the kernels read the ephemeris / attitude tables from: the device pointers of the
+// packed state, or a copy the block staged into shared memory.
+struct OrientationTables {
+  const double *positions;
+  const double *velocities;
+  const double *quaternions;
+};
+
+// Bytes of shared memory needed to stage the tables of S (velocities only when the
+// adjusted-position path can run).
+__host__ __device__ inline size_t orientationTableBytes(const LsState &S, bool needVelocity) {
+  size_t n = (size_t)S.positions.numNodes * 3 + (size_t)S.quaternions.numNodes * 4;
+  if (needVelocity) n += (size_t)S.velocities.numNodes * 3;
+  return n * sizeof(double);
+}
+
+// Cooperative copy of the tables into `smem`; returns the staged pointers.  All threads
+// of the block must call it; ends with __syncthreads().
+__device__ inline OrientationTables stageOrientationTables(const LsState &S, bool needVelocity,
+                                                           double *smem) {
+  OrientationTables t;
+  const int np = S.positions.numNodes * 3;
+  const int nq = S.quaternions.numNodes * 4;
+  double *sp = smem;
+  double *sq = sp + np;
+  double *sv = sq + nq;
+  for (int i = threadIdx.x; i < np; i += blockDim.x) sp[i] = __ldg(S.positions.values + i);
+  for (int i = threadIdx.x; i < nq; i += blockDim.x) sq[i] = __ldg(S.quaternions.values + i);
+  if (needVelocity) {
+    const int nv = S.velocities.numNodes * 3;
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) sv[i] = __ldg(S.velocities.values + i);
+  }
+  __syncthreads();
+  t.positions = sp;
+  t.quaternions = sq;
+  t.velocities = needVelocity ? sv : S.velocities.values;
+  return t;
+}
+
+// getValue(i, adj) with adj == _no_adjustment (LS:757-772 passes 16 zeros): the host packs
+// m_currentParameterValue[i] + 0.0.
+UB_DEV double param(const LsState &S, int i) { return S.params[i]; }
+
+// LS::getImageTime LS:1543-1568: std::upper_bound over m_intTimeLines, step back one.
+UB_DEV double lsImageTime(const LsState &S, double lineFull) {
+  if (S.numIntTimes == 1) {
+    return S.intStart0 + S.intTime0 * (lineFull - S.intLine0 + 0.5);
+  }
+  // std::upper_bound: first element with lineFull < element
+  int first = 0;
+  int len = S.numIntTimes;
+  while (len > 0) {
+    int half = len >> 1;
+    int mid = first + half;
+    if (lineFull < S.intTimeLines[mid]) {
+      len = half;
+    } else {
+      first = mid + 1;
+      len = len - half - 1;
+    }
+  }
+  int idx = first;
+  if (idx != 0) --idx;
+  return S.intTimeStartTimes[idx] + S.intTimes[idx] * (lineFull - S.intTimeLines[idx] + 0.5);
+}
+
+// LS::getAdjSensorPosVel LS:2484-2589 / PF:1955-2034.
+//   ALWAYS_VEL = false: line-scan semantics (calc_vel == false at every hot-path call site:
+//                position only unless some parameter is non-zero);
+//   ALWAYS_VEL = true:  push-frame semantics (no shortcut).
+template <bool ALWAYS_VEL>
+UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double time,
+                            double pos[3], double vel[3]) {
+  LagrangeWeights w;
+  lagrangeWeights(S.positions.numNodes, S.positions.t0, S.positions.dt, time,
+                  S.positions.maxOrder, w);
+  double sensPosNom[3];
+  lagrangeApply<3>(T.positions, w, sensPosNom);
+  if (!ALWAYS_VEL && !S.hasAdj) {
+    pos[0] = sensPosNom[0];
+    pos[1] = sensPosNom[1];
+    pos[2] = sensPosNom[2];
+    vel[0] = 0.0;
+    vel[1] = 0.0;
+    vel[2] = 0.0;
+    return;
+  }
+  // Same grid, same time, same order => the same weights (the reference recomputes them).
+  double sensVelNom[3];
+  lagrangeApply<3>(T.velocities, w, sensVelNom);
+
+  double radialUnitVec[3];
+  double radMag = sqrt(sensPosNom[0] * sensPosNom[0] + sensPosNom[1] * sensPosNom[1] +
+                       sensPosNom[2] * sensPosNom[2]);
+  for (int i = 0; i < 3; i++) radialUnitVec[i] = sensPosNom[i] / radMag;
+  double crossTrackUnitVec[3];
+  crossTrackUnitVec[0] = sensPosNom[1] * sensVelNom[2] - sensPosNom[2] * sensVelNom[1];
+  crossTrackUnitVec[1] = sensPosNom[2] * sensVelNom[0] - sensPosNom[0] * sensVelNom[2];
+  crossTrackUnitVec[2] = sensPosNom[0] * sensVelNom[1] - sensPosNom[1] * sensVelNom[0];
+  double crossMag = sqrt(crossTrackUnitVec[0] * crossTrackUnitVec[0] +
+                         crossTrackUnitVec[1] * crossTrackUnitVec[1] +
+                         crossTrackUnitVec[2] * crossTrackUnitVec[2]);
+  for (int i = 0; i < 3; i++) crossTrackUnitVec[i] /= crossMag;
+  double inTrackUnitVec[3];
+  inTrackUnitVec[0] =
+      crossTrackUnitVec[1] * radialUnitVec[2] - crossTrackUnitVec[2] * radialUnitVec[1];
+  inTrackUnitVec[1] =
+      crossTrackUnitVec[2] * radialUnitVec[0] - crossTrackUnitVec[0] * radialUnitVec[2];
+  inTrackUnitVec[2] =
+      crossTrackUnitVec[0] * radialUnitVec[1] - crossTrackUnitVec[1] * radialUnitVec[0];
+  double ecfFromIcr[9];
+  ecfFromIcr[0] = inTrackUnitVec[0];
+  ecfFromIcr[1] = crossTrackUnitVec[0];
+  ecfFromIcr[2] = radialUnitVec[0];
+  ecfFromIcr[3] = inTrackUnitVec[1];
+  ecfFromIcr[4] = crossTrackUnitVec[1];
+  ecfFromIcr[5] = radialUnitVec[1];
+  ecfFromIcr[6] = inTrackUnitVec[2];
+  ecfFromIcr[7] = crossTrackUnitVec[2];
+  ecfFromIcr[8] = radialUnitVec[2];
+
+  double aTime = time - S.positions.t0;
+  double dvi = param(S, 3) / S.halfTime;
+  double dvc = param(S, 4) / S.halfTime;
+  double dvr = param(S, 5) / S.halfTime;
+  vel[0] = sensVelNom[0] + ecfFromIcr[0] * dvi + ecfFromIcr[1] * dvc + ecfFromIcr[2] * dvr;
+  vel[1] = sensVelNom[1] + ecfFromIcr[3] * dvi + ecfFromIcr[4] * dvc + ecfFromIcr[5] * dvr;
+  vel[2] = sensVelNom[2] + ecfFromIcr[6] * dvi + ecfFromIcr[7] * dvc + ecfFromIcr[8] * dvr;
+  double di = param(S, 0) + dvi * aTime;
+  double dc = param(S, 1) + dvc * aTime;
+  double dr = param(S, 2) + dvr * aTime;
+  pos[0] = sensPosNom[0] + ecfFromIcr[0] * di + ecfFromIcr[1] * dc + ecfFromIcr[2] * dr;
+  pos[1] = sensPosNom[1] + ecfFromIcr[3] * di + ecfFromIcr[4] * dc + ecfFromIcr[5] * dr;
+  pos[2] = sensPosNom[2] + ecfFromIcr[6] * di + ecfFromIcr[7] * dc + ecfFromIcr[8] * dr;
+}
+
+// LS::getQuaternions LS:2140-2153 + calculateRotationMatrixFromQuaternions U:78-95.
+UB_DEV void cameraToBodyMatrix(const LsState &S, const OrientationTables &T, double time,
+                               double m[9]) {
+  double q[4];
+  lagrangeInterp<4>(S.quaternions, T.quaternions, time, q);
+  rotationFromQuaternion(q, m);
+}
+
+// LS::calculateAttitudeCorrection LS:2162-2187.  Only called when S.hasAttAdj: with
+// parameters 6..14 all zero the Euler angles are exactly 0 and the matrix is the identity
+// up to the sign of its zeros, so applying it returns its argument unchanged.
+UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9]) {
+  double aTime = time - S.quaternions.t0;
+  double euler[3];
+  double nTime = aTime / S.halfTime;
+  double nTime2 = nTime * nTime;
+  euler[0] = (param(S, 6) + param(S, 9) * nTime + param(S, 12) * nTime2) / S.flyingHeight;
+  euler[1] = (param(S, 7) + param(S, 10) * nTime + param(S, 13) * nTime2) / S.flyingHeight;
+  euler[2] = (param(S, 8) + param(S, 11) * nTime + param(S, 14) * nTime2) / S.halfSwath;
+  rotationFromEuler(euler, attCorr);
+}
+
+// LS::computeDetectorView LS:2603-2675 (PF:2038-2110 is the same with the push-frame
+// position routine): ground point -> undistorted focal-plane coordinates at `time`.
+template <bool ALWAYS_VEL>
+UB_DEV void detectorView(const LsState &S, const OrientationTables &T, double time, double gx,
+                         double gy, double gz, double &focalX, double &focalY) {
+  double pos[3], vel[3];
+  adjSensorPosVel<ALWAYS_VEL>(S, T, time, pos, vel);
+  double bodyLook[3] = {gx - pos[0], gy - pos[1], gz - pos[2]};
+  double bodyToCamera[9];
+  cameraToBodyMatrix(S, T, time, bodyToCamera);
+  double cameraLook[3];
+  matTVec(bodyToCamera, bodyLook, cameraLook);
+  double adjustedLook[3];
+  if (S.hasAttAdj) {
+    double attCorr[9];
+    attitudeCorrection(S, time, attCorr);
+    matTVec(attCorr, cameraLook, adjustedLook);
+  } else {
+    adjustedLook[0] = cameraLook[0];
+    adjustedLook[1] = cameraLook[1];
+    adjustedLook[2] = cameraLook[2];
+  }
+  double lookScale = (S.fp.focalLength + param(S, 15)) / adjustedLook[2];
+  focalX = adjustedLook[0] * lookScale;
+  focalY = adjustedLook[1] * lookScale;
+}
+
+// Camera-frame look vector -> body-fixed look (second half of losToEcf, LS:2268-2300).
+UB_DEV void cameraLookToBody(const LsState &S, const OrientationTables &T, double time,
+                             const double cameraLook[3], double bodyLook[3]) {
+  double corrected[3];
+  if (S.hasAttAdj) {
+    double attCorr[9];
+    attitudeCorrection(S, time, attCorr);
+    matVec(attCorr, cameraLook, corrected);
+  } else {
+    corrected[0] = cameraLook[0];
+    corrected[1] = cameraLook[1];
+    corrected[2] = cameraLook[2];
+  }
+  double cameraToBody[9];
+  cameraToBodyMatrix(S, T, time, cameraToBody);
+  matVec(cameraToBody, corrected, bodyLook);
+}
+
+// LS::losEllipsoidIntersect LS:2398-2465 (PF:1883-1950 identical): root with the smaller
+// magnitude; negative discriminant clamped with NO_INTERSECTION; achieved precision from
+// computeEllipsoidElevation.
+UB_DEV void lsEllipsoidIntersect(const Ellipsoid &ell, double height, const double c[3],
+                                 const double l[3], double desired_precision, double &x,
+                                 double &y, double &z, double &achieved, uint32_t &status) {
+  double ap = ell.majorAxis + height;
+  double bp = ell.minorAxis + height;
+  double k = ap * ap / (bp * bp);
+  double at = l[0] * l[0] + l[1] * l[1] + k * l[2] * l[2];
+  double bt = 2.0 * (l[0] * c[0] + l[1] * c[1] + k * l[2] * c[2]);
+  double ct = c[0] * c[0] + c[1] * c[1] + k * c[2] * c[2] - ap * ap;
+  double quadTerm = bt * bt - 4.0 * at * ct;
+  if (0.0 > quadTerm) {
+    quadTerm = 0.0;
+    status |= USGSCSM_B200_ST_NO_INTERSECTION;
+  }
+  double sTerm = sqrt(quadTerm);
+  double scale = (-bt - sTerm);
+  double scale1 = (-bt + sTerm);
+  if (fabs(scale1) < fabs(scale)) scale = scale1;
+  scale /= (2.0 * at);
+  x = c[0] + scale * l[0];
+  y = c[1] + scale * l[1];
+  z = c[2] + scale * l[2];
+  double h = ellipsoidElevation(x, y, z, ell, desired_precision);
+  achieved = fabs(height - h);
+}
+
+}  // namespace ub200
+#endif

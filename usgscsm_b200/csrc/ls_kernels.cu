@@ -1,0 +1,306 @@
+// ls_kernels.cu -- line-scan groundToImage / imageToGround, one thread per point, FP64.
+//
+// Replaces the per-point calls UsgsAstroLsSensorModel::groundToImage
+// (src/UsgsAstroLsSensorModel.cpp:757-890) and ::imageToGround (:980-1009).
+//
+// Layout: SoA double arrays in HBM, read/written once with streaming cache hints (a warp
+// touches 32 consecutive doubles per array = two full 128-byte lines); the packed model
+// state is a __grid_constant__ kernel parameter (constant bank); the ephemeris and
+// attitude tables are staged once per block into shared memory when they fit, and the
+// grid is persistent (a multiple of the SM count, grid-stride over points) so that the
+// staging cost is paid once per resident block, not once per 256 points.
+#include "kernels.h"
+#include "ls_common.cuh"
+
+namespace ub200 {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// ---- groundToImage ---------------------------------------------------------------------
+// LS::computeProjectiveApproximation LS:2688-2736
+UB_DEV void projectiveSeed(const LsState &S, double x, double y, double z, double &line,
+                           double &samp) {
+  if (S.useApproxInitTrans) {
+    const double *u = S.projCoeffs;
+    double line_den = 1 + u[4] * x + u[5] * y + u[6] * z;
+    double samp_den = 1 + u[11] * x + u[12] * y + u[13] * z;
+    if (line_den == 0.0 || isnan(line_den) || isinf(line_den) || samp_den == 0.0 ||
+        isnan(samp_den) || isinf(samp_den)) {
+      line = S.nLines / 2.0;
+      samp = S.nSamples / 2.0;
+      return;
+    }
+    line = (u[0] + u[1] * x + u[2] * y + u[3] * z) / line_den;
+    samp = (u[7] + u[8] * x + u[9] * y + u[10] * z) / samp_den;
+    double numRows = S.nLines;
+    double numCols = S.nSamples;
+    if (line < 0.0) line = 0.0;
+    if (line > numRows) line = numRows;
+    if (samp < 0.0) samp = 0.0;
+    if (samp > numCols) samp = numCols;
+  } else {
+    line = S.nLines / 2.0;
+    samp = S.nSamples / 2.0;
+  }
+}
+
+// One point of LS::groundToImage(groundPt, adj = 0, desiredPrecision, ...) LS:795-890.
+//
+// The reference evaluates calcDetectorLineErr (LS:3209-3231) at t = 0, t = 0.1 and at
+// every secant iterate, then evaluates computeDetectorView once more at approxPt.line + t1.
+// That last call sees exactly the time of the last residual evaluation (same sum
+// approxPt.line + t1, same getImageTime), so its focal-plane point IS the one already
+// computed; only applyDistortion is repeated, now with the caller's desiredPrecision
+// instead of the default 1e-6 (hazard 3 in SURVEY.md §9).  The loop below therefore has a
+// single inlined copy of the detector view and runs it 2 + k times.
+template <bool ALWAYS_VEL>
+UB_DEV void lsGroundToImagePoint(const LsState &S, const OrientationTables &T, double gx,
+                                 double gy, double gz, double desiredPrecision, double &outLine,
+                                 double &outSamp, double &achieved, uint32_t &status) {
+  double approxLine, approxSamp;
+  projectiveSeed(S, gx, gy, gz, approxLine, approxSamp);
+
+  const FocalPlane &fp = S.fp;
+  int count = 0;
+  double t0 = 0.0, lineErr0 = 0.0;
+  double t1 = 0.0, lineErr1;
+  double focalX, focalY;
+  uint32_t distStatus;
+  int stage = 0;  // 0: residual at t = 0; 1: residual at t1 (0.1, then secant iterates)
+  for (;;) {
+    double timei = lsImageTime(S, approxLine + t1);
+    detectorView<ALWAYS_VEL>(S, T, timei, gx, gy, gz, focalX, focalY);
+    double distortedFocalX, distortedFocalY;
+    distStatus = 0;
+    applyDistortion(focalX, focalY, distortedFocalX, distortedFocalY, fp, 1.0E-6, distStatus);
+    double detectorLine = fp.iTransL[0] + fp.iTransL[1] * distortedFocalX +
+                          fp.iTransL[2] * distortedFocalY + fp.detectorLineOrigin -
+                          fp.startingDetectorLine;
+    detectorLine /= fp.detectorLineSumming;
+    if (stage == 0) {
+      lineErr0 = detectorLine;
+      t1 = 0.1;
+      stage = 1;
+      continue;
+    }
+    lineErr1 = detectorLine;
+    // while (std::abs(lineErr1) > desiredPrecision && ++count < 15) { if (==) break; ... }
+    if (!(fabs(lineErr1) > desiredPrecision)) break;
+    if (!(++count < 15)) {
+      status |= USGSCSM_B200_ST_ITERATION_CAP;
+      break;
+    }
+    if (lineErr1 == lineErr0) {
+      status |= USGSCSM_B200_ST_SEARCH_STALL;
+      break;
+    }
+    double t2 = t1 - lineErr1 * (t1 - t0) / (lineErr1 - lineErr0);
+    t0 = t1;
+    lineErr0 = lineErr1;
+    t1 = t2;
+  }
+
+  approxLine += t1;
+  // Final projection: same focal-plane point, distortion at the caller's precision.
+  double distortedFocalX, distortedFocalY;
+  distStatus = 0;
+  applyDistortion(focalX, focalY, distortedFocalX, distortedFocalY, fp, desiredPrecision,
+                  distStatus);
+  status |= distStatus;
+  double detectorLine =
+      fp.iTransL[0] + fp.iTransL[1] * distortedFocalX + fp.iTransL[2] * distortedFocalY;
+  double detectorSample =
+      fp.iTransS[0] + fp.iTransS[1] * distortedFocalX + fp.iTransS[2] * distortedFocalY;
+  double finalUpdate =
+      (detectorLine + fp.detectorLineOrigin - fp.startingDetectorLine) / fp.detectorLineSumming;
+  outLine = approxLine + finalUpdate;
+  outSamp = (detectorSample + fp.detectorSampleOrigin - fp.startingDetectorSample) /
+            fp.detectorSampleSumming;
+  achieved = finalUpdate;
+  if ((desiredPrecision > 0.0) && (fabs(finalUpdate) > desiredPrecision))
+    status |= USGSCSM_B200_ST_PRECISION_NOT_MET;
+}
+
+UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamples) {
+  uint32_t st = 0;
+  if (!(isfinite(line) && isfinite(samp))) st |= USGSCSM_B200_ST_NONFINITE;
+  // getValidImageRange LS:1862-1869: (0,0) .. (nLines, nSamples), inclusive
+  if (!(line >= 0.0 && line <= (double)nLines && samp >= 0.0 && samp <= (double)nSamples))
+    st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+  return st;
+}
+
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
+                          const double *__restrict__ y, const double *__restrict__ z, double prec,
+                          double *__restrict__ line, double *__restrict__ samp,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ double smem[];
+  OrientationTables T;
+  if (STAGE) {
+    T = stageOrientationTables(S, S.hasAdj != 0, smem);
+  } else {
+    T.positions = S.positions.values;
+    T.velocities = S.velocities.values;
+    T.quaternions = S.quaternions.values;
+  }
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
+    double l, s, a;
+    uint32_t st = 0;
+    lsGroundToImagePoint<false>(S, T, gx, gy, gz, prec, l, s, a, st);
+    st |= imageRangeStatus(l, s, S.nLines, S.nSamples);
+    __stcs(line + i, l);
+    __stcs(samp + i, s);
+    if (achieved) __stcs(achieved + i, a);
+    if (status) __stcs(status + i, st);
+  }
+}
+
+// ---- imageToGround -----------------------------------------------------------------------
+// One point of LS::imageToGround LS:980-1009 = losToEcf LS:2209-2305 + losEllipsoidIntersect.
+UB_DEV void lsImageToGroundPoint(const LsState &S, const OrientationTables &T, double line,
+                                 double sample, double height, double desiredPrecision,
+                                 double &x, double &y, double &z, double &achieved,
+                                 uint32_t &status) {
+  double time = lsImageTime(S, line);
+  double pos[3], vel[3];
+  adjSensorPosVel<false>(S, T, time, pos, vel);
+  // The detector is one row: the focal-plane affine is fed line = 0.0 (LS:2242-2246).
+  double distortedFocalPlaneX, distortedFocalPlaneY;
+  distortedFocalPlaneCoordinates(0.0, sample, S.fp, distortedFocalPlaneX, distortedFocalPlaneY);
+  double undistortedFocalPlaneX, undistortedFocalPlaneY;
+  removeDistortion(distortedFocalPlaneX, distortedFocalPlaneY, undistortedFocalPlaneX,
+                   undistortedFocalPlaneY, S.fp, 1.0E-6, status);
+  double cameraLook[3];
+  cameraLookVector(undistortedFocalPlaneX, undistortedFocalPlaneY, S.fp.zDirection,
+                   S.fp.focalLength * (1 - param(S, 15) / S.halfSwath), cameraLook);
+  double bodyLook[3];
+  cameraLookToBody(S, T, time, cameraLook, bodyLook);
+  lsEllipsoidIntersect(S.ell, height, pos, bodyLook, desiredPrecision, x, y, z, achieved, status);
+  if ((desiredPrecision > 0.0) && (achieved > desiredPrecision))
+    status |= USGSCSM_B200_ST_PRECISION_NOT_MET;
+  if (status & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+    // the scalar call throws before producing anything
+    status = USGSCSM_B200_ST_ERROR_ALGORITHM;
+    x = y = z = achieved = nan("");
+  }
+  if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
+}
+
+// GRID = true: pixel coordinates generated from the point index (dense grid);
+// GRID = false: explicit (line, samp) arrays.
+template <bool STAGE, bool GRID>
+__global__ void __launch_bounds__(kThreads)
+    lsImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                          const double *__restrict__ samp, GridSpec g,
+                          const double *__restrict__ height, int heightStride, double prec,
+                          double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ double smem[];
+  OrientationTables T;
+  if (STAGE) {
+    T = stageOrientationTables(S, S.hasAdj != 0, smem);
+  } else {
+    T.positions = S.positions.values;
+    T.velocities = S.velocities.values;
+    T.quaternions = S.quaternions.values;
+  }
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l, s;
+    if (GRID) {
+      long r = i / g.nSamps;
+      long c = i - r * g.nSamps;
+      l = g.line0 + (double)r * g.dline;
+      s = g.samp0 + (double)c * g.dsamp;
+    } else {
+      l = __ldcs(line + i);
+      s = __ldcs(samp + i);
+    }
+    double h = heightStride ? __ldcs(height + i) : __ldg(height);
+    double px, py, pz, a;
+    uint32_t st = 0;
+    lsImageToGroundPoint(S, T, l, s, h, prec, px, py, pz, a, st);
+    __stcs(x + i, px);
+    __stcs(y + i, py);
+    __stcs(z + i, pz);
+    if (achieved) __stcs(achieved + i, a);
+    if (status) __stcs(status + i, st);
+  }
+}
+
+}  // namespace
+
+// ---- launchers ---------------------------------------------------------------------------
+static LaunchShape shapeFor(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage,
+                            int blocksPerSm) {
+  size_t bytes = orientationTableBytes(S, S.hasAdj != 0);
+  stage = bytes <= kMaxStagedTableBytes;
+  smemBytes = stage ? bytes : 0;
+  LaunchShape sh;
+  sh.threads = kThreads;
+  long blocksNeeded = (n + kThreads - 1) / kThreads;
+  long persistent = (long)smCount * blocksPerSm;
+  sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
+  if (sh.blocks < 1) sh.blocks = 1;
+  return sh;
+}
+
+cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const double *x,
+                                  const double *y, const double *z, double prec, double *line,
+                                  double *samp, double *achieved, uint32_t *status,
+                                  cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kBlocksPerSm);
+  if (stage) {
+    if (smemBytes > 48 * 1024)
+      cudaFuncSetAttribute(lsGroundToImageKernel<true>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    lsGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
+        S, n, x, y, z, prec, line, samp, achieved, status);
+  } else {
+    lsGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
+        S, n, x, y, z, prec, line, samp, achieved, status);
+  }
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const double *line,
+                                  const double *samp, const GridSpec *grid, const double *height,
+                                  int heightStride, double prec, double *x, double *y, double *z,
+                                  double *achieved, uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kBlocksPerSm);
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+#define UB_LAUNCH_I2G(STAGE, GRID)                                                           \
+  do {                                                                                       \
+    if (smemBytes > 48 * 1024)                                                               \
+      cudaFuncSetAttribute(lsImageToGroundKernel<STAGE, GRID>,                               \
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);     \
+    lsImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(        \
+        S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status);         \
+  } while (0)
+  if (stage && grid)
+    UB_LAUNCH_I2G(true, true);
+  else if (stage)
+    UB_LAUNCH_I2G(true, false);
+  else if (grid)
+    UB_LAUNCH_I2G(false, true);
+  else
+    UB_LAUNCH_I2G(false, false);
+#undef UB_LAUNCH_I2G
+  countLaunch();
+  return cudaGetLastError();
+}
+
+}  // namespace ub200

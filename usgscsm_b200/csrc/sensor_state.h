@@ -1,0 +1,150 @@
+// sensor_state.h -- packed, device-ready model states (plain PODs shared by host and kernels).
+//
+// A packed state is the subset of a sensor model's members that the per-point math
+// reads (SURVEY.md §8b "Packed device state"): scalars by value, tables as device
+// pointers.  The struct is passed to the kernels as a __grid_constant__ parameter, so its
+// scalars live in the constant bank and FP64 instructions read them as immediate
+// operands; the tables live in HBM/L2 and are staged into shared memory by the kernels
+// when they fit.
+//
+// Reference members mirrored here:
+//   line-scan  include/usgscsm/UsgsAstroLsSensorModel.h:77-131,983-989
+//   push-frame include/usgscsm/UsgsAstroPushFrameSensorModel.h (framelet fields)
+//   frame      include/usgscsm/UsgsAstroFrameSensorModel.h
+//   SAR        include/usgscsm/UsgsAstroSarSensorModel.h
+#ifndef USGSCSM_B200_SENSOR_STATE_H_
+#define USGSCSM_B200_SENSOR_STATE_H_
+
+#include <stdint.h>
+
+namespace ub200 {
+
+// include/usgscsm/Distortion.h:10-11 (same numeric values: they are what m_distortionType
+// holds in a serialised model state).
+enum DistortionKind : int {
+  DIST_RADIAL = 0,
+  DIST_TRANSVERSE = 1,
+  DIST_KAGUYALISM = 2,
+  DIST_DAWNFC = 3,
+  DIST_LROLROCNAC = 4,
+  DIST_CAHVOR = 5,
+  DIST_LUNARORBITER = 6,
+  DIST_RADTAN = 7,
+  DIST_KPLOSHADOWCAM = 8,
+};
+
+constexpr int kMaxDistCoeffs = 20;
+
+// Focal-plane <-> detector affine, shared by all optical models.
+struct FocalPlane {
+  double iTransS[3];
+  double iTransL[3];
+  double detectorSampleOrigin;
+  double detectorLineOrigin;
+  double detectorSampleSumming;
+  double detectorLineSumming;
+  double startingDetectorSample;
+  double startingDetectorLine;
+  double focalLength;
+  double zDirection;  // LS/PF only
+  int distortionType;
+  int numDistCoeffs;
+  double distCoeffs[kMaxDistCoeffs];
+  // Inverse of the 2x2 part of (iTransL, iTransS), evaluated once on the host with the
+  // exact expressions of computeDistortedFocalPlaneCoordinates (src/Utilities.cpp:143-147;
+  // IEEE division is deterministic, so this equals the per-call value bit for bit).
+  double p11, p12, p21, p22;
+};
+
+// Ellipsoid constants of computeEllipsoidElevation (src/Utilities.cpp:825-826), evaluated
+// once on the host with the same expressions.
+struct Ellipsoid {
+  double majorAxis;
+  double minorAxis;
+  double eccSqr;  // 1.0 - b * b / a / a
+  double ep2;     // 1.0 - eccSqr
+};
+
+// Uniformly sampled table of `vlen`-vectors for lagrangeInterp (src/Utilities.cpp:409-513).
+struct UniformTable {
+  const double *values;  // device pointer, numNodes * vlen doubles
+  int numNodes;
+  int maxOrder;  // i_order passed by the model (8, or 4: LS:2142-2145, LS:2494-2495)
+  double t0;
+  double dt;
+};
+
+// Line-scan and push-frame models share the time-dependent exterior orientation.
+struct LsState {
+  FocalPlane fp;
+  int nLines;
+  int nSamples;
+  int numIntTimes;        // m_intTimeLines.size()
+  int useApproxInitTrans; // LS:2688-2736
+  int hasAdj;             // any m_currentParameterValue[i] != 0 (LS:2505-2509)
+  int hasAttAdj;          // any of parameters 6..14 != 0 (Euler angles not identically 0)
+  Ellipsoid ell;
+  double gsd;
+  double flyingHeight;
+  double halfSwath;
+  double halfTime;
+  double projCoeffs[14];
+  double params[16];
+  // first line-rate segment inline (every fixture has exactly one)
+  double intLine0, intStart0, intTime0;
+  const double *intTimeLines;      // device, numIntTimes
+  const double *intTimeStartTimes; // device
+  const double *intTimes;          // device
+  UniformTable positions;          // vlen 3
+  UniformTable velocities;         // vlen 3 (same grid as positions)
+  UniformTable quaternions;        // vlen 4
+  // push-frame only (PF:715-778, PF:1258-1276, PF:1726-1824)
+  int frameletHeight;        // m_reducedFrameletHeight  (push-frame: m_frameletHeight)
+  int nReducedLines;         // unused by the reference's g2i but kept for symmetry
+  int numLinesOverlap;
+  int frameletsFlipped;
+  int frameletsOrderReversed;
+  int pad0;
+  double startingEphemerisTime;
+  double centerEphemerisTime;
+  double exposureDuration;
+  double interframeDelay;
+};
+
+// Frame model (FR:137-372, FR:2250-2385).
+struct FrameState {
+  FocalPlane fp;  // zDirection unused
+  int nLines;
+  int nSamples;
+  int numJitterCoeffs; // m_lineJitter.size() (== m_sampleJitter.size()); 0 = no jitter
+  int numLineTimes;
+  Ellipsoid ell;
+  double params[7];    // x,y,z, q0..q3 (m_currentParameterValue)
+  double ccdCenter[2]; // line, sample
+  const double *lineJitter;   // device
+  const double *sampleJitter; // device
+  const double *lineTimes;    // device
+};
+
+// SAR model (SAR:541-861, SAR:1196-1300, SAR:1936-1972).
+struct SarState {
+  int nLines;
+  int nSamples;
+  int lookDirection; // 0 = LEFT, 1 = RIGHT (include/usgscsm/UsgsAstroSarSensorModel.h)
+  int numScaleTimes; // m_scaleConversionTimes.size()
+  Ellipsoid ell;
+  double exposureDuration;
+  double scaledPixelWidth;
+  double wavelength;
+  double startingEphemerisTime;
+  double centerEphemerisTime;
+  double endingEphemerisTime;
+  double params[6];
+  UniformTable positions;  // vlen 3
+  UniformTable velocities; // vlen 3
+  const double *scaleConversionCoefficients; // device, 4 per time
+  const double *scaleConversionTimes;        // device
+};
+
+}  // namespace ub200
+#endif
