@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py -- line-scan groundToImage / imageToGround throughput on B200 (BASELINE.json metric).
+
+Workload (config C2 of BASELINE.json): a synthetic orbital NAC-style line-scan image
+(lroLrocNac distortion), 5064 samples x 52224 lines per GPU, dense grid orthorectification:
+imageToGround of every pixel centre at a synthetic-DEM height, then groundToImage of every
+resulting ground point.  A "step" is one groundToImage pass over the whole grid (264.5 M
+points per GPU); imageToGround is timed beside it and reported under "image_to_ground".
+At N > 1 the image is N times taller and every rank takes one row band (weak scaling, no
+data-path collective).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          # this engine
+  python bench.py --impl reference [...]                        # the reference's CPU code
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mpoints/s groundToImage & imageToGround (line-scan) at 1/2/4/8 B200 vs host CPU"
+N_SAMPLES = 5064
+N_LINES_PER_GPU = 52224
+PREC = 0.001
+# algorithmic HBM bytes per point: x,y,z in; line,samp + status out
+G2I_BYTES_PER_POINT = 24 + 16 + 4
+# dense-grid imageToGround: height in; x,y,z + status out
+I2G_BYTES_PER_POINT = 8 + 24 + 4
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--lines", type=int, default=N_LINES_PER_GPU,
+                    help="lines per GPU (default: the full C2 image)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([c.strip() for c in ln.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(self.NAMES, r[2:]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload_state(n_gpus, lines_per_gpu):
+    from usgscsm_b200 import synth
+    return synth.linescan_state(n_lines=lines_per_gpu * n_gpus, n_samples=N_SAMPLES, seed=20261104)
+
+
+def peak_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def sample_pixels(n_lines_total, target_points):
+    """Bounded sample of the dense grid: every k-th line, all samples (pixel centres)."""
+    import numpy as np
+    lines_wanted = max(1, min(n_lines_total, int(target_points // N_SAMPLES)))
+    k = max(1, n_lines_total // lines_wanted)
+    rows = np.arange(0, n_lines_total, k, dtype=np.float64)[:lines_wanted] + 0.5
+    line = np.repeat(rows, N_SAMPLES)
+    samp = np.tile(np.arange(N_SAMPLES, dtype=np.float64) + 0.5, rows.size)
+    return line, samp, "every %d-th line of the grid, all %d samples: %d points" % (k, N_SAMPLES, line.size)
+
+
+def cpu_reference_rate(state, n_lines_total, seconds, direction="g2i", proj=None):
+    """Reference CPU code (oracle/_ref, OpenMP over points, all host threads) on a bounded
+    sample sized for about `seconds` of work.  Returns (Mpoints/s, cores, kind, sample, fn)
+    where fn() re-times one pass over the sample."""
+    import numpy as np
+    from oracle import ref
+    from usgscsm_b200 import synth
+    rm = ref.RefModel(state)
+    if proj is not None:
+        rm.ls_set_projective(True, proj)
+    cores = ref.max_threads()
+
+    def run(line, samp):
+        h = synth.synthetic_dem(line, samp)
+        x, y, z, _, _ = rm.image_to_ground(line, samp, h, PREC, threads=0)
+        if direction == "i2g":
+            t = time.perf_counter()
+            rm.image_to_ground(line, samp, h, PREC, threads=0)
+            return time.perf_counter() - t, None
+        t = time.perf_counter()
+        rm.ground_to_image(x, y, z, PREC, threads=0)
+        return time.perf_counter() - t, (x, y, z)
+
+    line, samp, _ = sample_pixels(n_lines_total, 40 * N_SAMPLES)
+    dt, _ = run(line, samp)
+    rate = line.size / dt
+    line, samp, desc = sample_pixels(n_lines_total, rate * seconds)
+    dt, pts = run(line, samp)
+
+    def again():
+        t = time.perf_counter()
+        if direction == "i2g":
+            rm.image_to_ground(line, samp, synth.synthetic_dem(line, samp), PREC, threads=0)
+        else:
+            rm.ground_to_image(pts[0], pts[1], pts[2], PREC, threads=0)
+        return time.perf_counter() - t, line.size
+
+    return line.size / dt / 1e6, cores, "reference", desc, again
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ref
+    if not ref.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libusgscsm_ref.so not built"}))
+        return
+    state = workload_state(args.gpus, args.lines)
+    n_lines_total = args.lines * args.gpus
+    # each step is one pass over a sample sized for ~4 s of host work
+    _, cores, kind, desc, again = cpu_reference_rate(state, n_lines_total, 4.0)
+    for _ in range(args.warmup):
+        again()
+    t_total, n_total = 0.0, 0
+    for _ in range(args.steps):
+        dt, n = again()
+        t_total += dt
+        n_total += n
+    value = n_total / t_total / 1e6
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mpoints/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": "Mpoints/s", "cores": cores, "kind": kind,
+                         "sample": desc + " per step, groundToImage"},
+        "e2e": {"value": value, "unit": "Mpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_config(args):
+    return {"workload": "C2 orbital line-scan (lroLrocNac distortion) %dx%d dense grid per GPU, "
+                        "imageToGround at synthetic-DEM heights then groundToImage; value = "
+                        "groundToImage" % (N_SAMPLES, args.lines),
+            "points_per_gpu": N_SAMPLES * args.lines, "desired_precision": PREC,
+            "sharding": "row bands, one per GPU" if args.gpus > 1 else "single GPU",
+            "l2": "inputs (6.3 GB per GPU) larger than L2; no flush needed"}
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import _capi, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the engine has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    lines = args.lines
+    n = lines * N_SAMPLES
+    state = workload_state(world, lines)
+    model = ub.UsgsAstroPlugin(device=local).constructModelFromState(state)
+    line0 = rank * lines + 0.5  # this rank's row band
+
+    # synthetic DEM heights for the band, built band by band on the device
+    h = torch.empty(n, dtype=torch.float64, device=dev)
+    cols = torch.arange(N_SAMPLES, device=dev, dtype=torch.float64) + 0.5
+    cterm = torch.cos(2 * np.pi * cols / 1024.0)
+    for r0 in range(0, lines, 4096):
+        r1 = min(lines, r0 + 4096)
+        rows = torch.arange(r0, r1, device=dev, dtype=torch.float64) + line0
+        h[r0 * N_SAMPLES:r1 * N_SAMPLES] = (500.0 * torch.sin(2 * np.pi * rows / 4096.0)[:, None] * cterm[None, :]).reshape(-1)
+
+    x, y, z = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
+    st_g = torch.empty(n, dtype=torch.int32, device=dev)
+    out_line, out_samp = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(2))
+    st_i = torch.empty(n, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    h_lib = model._h
+
+    def i2g():
+        _capi.check(_capi.lib.usgscsm_b200_image_to_ground_grid_dev(
+            h_lib, line0, 0.5, 1.0, 1.0, lines, N_SAMPLES, h.data_ptr(), 1, PREC, x.data_ptr(),
+            y.data_ptr(), z.data_ptr(), None, st_g.data_ptr(), stream))
+
+    def g2i():
+        _capi.check(_capi.lib.usgscsm_b200_ground_to_image_dev(
+            h_lib, n, x.data_ptr(), y.data_ptr(), z.data_ptr(), PREC, out_line.data_ptr(),
+            out_samp.data_ptr(), None, st_i.data_ptr(), stream))
+
+    def timed(fn, steps):
+        """K launches bracketed by barrier + synchronize; per-launch CUDA events on the
+        launching stream.  Returns (total ms max over ranks, mean per-launch ms on this rank)."""
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+              for _ in range(steps)]
+        barrier()
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for a, b in ev:
+            a.record()
+            fn()
+            b.record()
+        t1.record()
+        torch.cuda.synchronize()
+        total = t0.elapsed_time(t1)
+        per = sum(a.elapsed_time(b) for a, b in ev) / steps
+        barrier()
+        return max_over_ranks(total), per
+
+    i2g()
+    torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        g2i()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = _capi.lib.usgscsm_b200_kernel_launches()
+    total_ms, kern_ms = timed(g2i, args.steps)
+    launches = _capi.lib.usgscsm_b200_kernel_launches() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    value = world * n * args.steps / (total_ms * 1e-3) / 1e6
+
+    # correctness of what was just timed: the round trip must close and no flag may be set
+    err = max(float((out_line.view(lines, N_SAMPLES) - (torch.arange(lines, device=dev, dtype=torch.float64) + line0)[:, None]).abs().max()),
+              float((out_samp.view(lines, N_SAMPLES) - cols[None, :]).abs().max()))
+    flags = int((st_i != 0).sum().item()) + int((st_g != 0).sum().item())
+
+    # imageToGround beside it
+    for _ in range(args.warmup):
+        i2g()
+    i2g_total_ms, i2g_kern_ms = timed(i2g, args.steps)
+    i2g_value = world * n * args.steps / (i2g_total_ms * 1e-3) / 1e6
+
+    peak, peak_src = peak_hbm()
+    achieved = G2I_BYTES_PER_POINT * n / (kern_ms * 1e-3) / 1e9
+    result = {
+        "metric": METRIC, "value": value, "unit": "Mpoints/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(args), "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "kernel": "lsGroundToImageKernel", "kernel_ms": kern_ms,
+                     "bytes_per_point": G2I_BYTES_PER_POINT,
+                     "note": "FP64-pipe bound, not HBM bound: see DESIGN.md"},
+        "image_to_ground": {"value": i2g_value, "unit": "Mpoints/s", "ms_per_step": i2g_total_ms / args.steps,
+                            "kernel_ms": i2g_kern_ms,
+                            "hbm_gbs": I2G_BYTES_PER_POINT * n / (i2g_kern_ms * 1e-3) / 1e9},
+        "check": {"round_trip_max_px": err, "points_with_flags": flags},
+    }
+
+    if not args.no_e2e:
+        result["e2e"] = e2e(args, model, x, y, z, n, world, barrier, max_over_ranks)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import ref
+        if ref.available():
+            v, cores, kind, desc, _ = cpu_reference_rate(state, lines, 15.0, proj=model.lsDerived()[5:19])
+            result["cpu_baseline"] = {"value": v, "unit": "Mpoints/s", "cores": cores, "kind": kind,
+                                      "sample": desc + ", groundToImage, OpenMP over points"}
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def e2e(args, model, x, y, z, n, world, barrier, max_over_ranks):
+    """Same metric through the host-pointer C-ABI call: pinned host arrays in, pinned host
+    arrays out, host<->device copies inside the timed region."""
+    import torch
+    from usgscsm_b200 import _capi
+    hx, hy, hz = (t.cpu().pin_memory() for t in (x, y, z))
+    hl = torch.empty(n, dtype=torch.float64).pin_memory()
+    hs = torch.empty(n, dtype=torch.float64).pin_memory()
+    hst = torch.empty(n, dtype=torch.int32).pin_memory()
+
+    def call():
+        _capi.check(_capi.lib.usgscsm_b200_ground_to_image(
+            model._h, n, hx.data_ptr(), hy.data_ptr(), hz.data_ptr(), PREC, hl.data_ptr(),
+            hs.data_ptr(), None, hst.data_ptr()))
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        call()
+    barrier()
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        call()
+    torch.cuda.synchronize()
+    dt = max_over_ranks(time.perf_counter() - t)
+    barrier()
+    return {"value": world * n * args.steps / dt / 1e6, "unit": "Mpoints/s",
+            "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 20 * n,
+            "ms_per_step": 1e3 * dt / args.steps,
+            "api": "usgscsm_b200_ground_to_image (host pointers, pinned)"}
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

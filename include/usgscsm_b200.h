@@ -29,6 +29,13 @@ extern "C" {
 
 #define USGSCSM_B200_ABI_VERSION 1
 
+/* every entry point below is exported from libusgscsm_b200.so */
+#if defined(__GNUC__)
+#define USGSCSM_B200_API __attribute__((visibility("default")))
+#else
+#define USGSCSM_B200_API
+#endif
+
 /* ---- error codes (function return values) ------------------------------------------ */
 #define USGSCSM_B200_OK 0
 #define USGSCSM_B200_EINVAL -1    /* bad argument                                        */
@@ -68,10 +75,10 @@ extern "C" {
 typedef struct usgscsm_b200_model usgscsm_b200_model;
 
 /* ---- library ------------------------------------------------------------------------ */
-int usgscsm_b200_abi_version(void);
-const char *usgscsm_b200_last_error(void);
+USGSCSM_B200_API int usgscsm_b200_abi_version(void);
+USGSCSM_B200_API const char *usgscsm_b200_last_error(void);
 /* Number of CUDA devices the engine can use (0 when there is none). */
-int usgscsm_b200_device_count(void);
+USGSCSM_B200_API int usgscsm_b200_device_count(void);
 
 /* ---- model construction ---------------------------------------------------------------
  * Replaces UsgsAstroPlugin::constructModelFromState (src/UsgsAstroPlugin.cpp:535-555) +
@@ -82,27 +89,27 @@ int usgscsm_b200_device_count(void);
  * uploaded to CUDA device `device`.  Derived quantities the reference computes at load time
  * with its own per-point calls (updateState LS:649-735, createProjectiveApproximation
  * LS:2745-2803) are computed here by running the batch kernels on those points. */
-int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
+USGSCSM_B200_API int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
                                   usgscsm_b200_model **out);
 /* csm::Model destructor. */
-void usgscsm_b200_model_free(usgscsm_b200_model *m);
+USGSCSM_B200_API void usgscsm_b200_model_free(usgscsm_b200_model *m);
 /* USGSCSM_B200_MODEL_* */
-int usgscsm_b200_model_kind(const usgscsm_b200_model *m);
-int usgscsm_b200_model_device(const usgscsm_b200_model *m);
+USGSCSM_B200_API int usgscsm_b200_model_kind(const usgscsm_b200_model *m);
+USGSCSM_B200_API int usgscsm_b200_model_device(const usgscsm_b200_model *m);
 /* csm::RasterGM::getImageSize (LS:1845-1852). */
-int usgscsm_b200_model_image_size(const usgscsm_b200_model *m, int *lines, int *samps);
+USGSCSM_B200_API int usgscsm_b200_model_image_size(const usgscsm_b200_model *m, int *lines, int *samps);
 /* csm::GeometricModel::getNumParameters / getParameterValue / setParameterValue
  * (LS:1585-1620).  Setting a parameter re-packs the device state. */
-int usgscsm_b200_model_num_parameters(const usgscsm_b200_model *m);
-int usgscsm_b200_model_get_parameter(const usgscsm_b200_model *m, int index, double *value);
-int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double value);
+USGSCSM_B200_API int usgscsm_b200_model_num_parameters(const usgscsm_b200_model *m);
+USGSCSM_B200_API int usgscsm_b200_model_get_parameter(const usgscsm_b200_model *m, int index, double *value);
+USGSCSM_B200_API int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double value);
 /* Host-derived inputs of the line-scan per-point math:
  * out[0..3] = gsd, flyingHeight, halfSwath, halfTime; out[4] = useApproxInitTrans;
  * out[5..18] = the 14 projective-seed coefficients (LS:2688-2736); out[19..21] = reference
  * point.  Only meaningful for the line-scan model. */
-int usgscsm_b200_model_ls_derived(const usgscsm_b200_model *m, double *out22);
+USGSCSM_B200_API int usgscsm_b200_model_ls_derived(const usgscsm_b200_model *m, double *out22);
 /* Override the projective seed (m_useApproxInitTrans, m_projTransCoeffs). */
-int usgscsm_b200_model_ls_set_projective(usgscsm_b200_model *m, int use,
+USGSCSM_B200_API int usgscsm_b200_model_ls_set_projective(usgscsm_b200_model *m, int use,
                                          const double *coeffs14);
 
 /* ---- per-point math, batched ------------------------------------------------------------
@@ -118,10 +125,10 @@ int usgscsm_b200_model_ls_set_projective(usgscsm_b200_model *m, int use,
  * (chunked and overlapped with the kernels); the _dev flavour takes DEVICE pointers on
  * the model's device and enqueues on `stream` (a cudaStream_t; NULL = default stream)
  * without synchronising. */
-int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double *x,
+USGSCSM_B200_API int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double *x,
                                  const double *y, const double *z, double prec, double *line,
                                  double *samp, double *achieved, uint32_t *status);
-int usgscsm_b200_ground_to_image_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_dev(usgscsm_b200_model *m, int64_t n, const double *x,
                                      const double *y, const double *z, double prec,
                                      double *line, double *samp, double *achieved,
                                      uint32_t *status, void *stream);
@@ -131,11 +138,11 @@ int usgscsm_b200_ground_to_image_dev(usgscsm_b200_model *m, int64_t n, const dou
  * PF:842-870, FR:280-372, SAR:775-861).
  *   height         heights above the ellipsoid, metres; n entries when height_stride = 1,
  *                  one entry when height_stride = 0 */
-int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double *line,
+USGSCSM_B200_API int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double *line,
                                  const double *samp, const double *height, int height_stride,
                                  double prec, double *x, double *y, double *z, double *achieved,
                                  uint32_t *status);
-int usgscsm_b200_image_to_ground_dev(usgscsm_b200_model *m, int64_t n, const double *line,
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_dev(usgscsm_b200_model *m, int64_t n, const double *line,
                                      const double *samp, const double *height,
                                      int height_stride, double prec, double *x, double *y,
                                      double *z, double *achieved, uint32_t *status,
@@ -145,7 +152,7 @@ int usgscsm_b200_image_to_ground_dev(usgscsm_b200_model *m, int64_t n, const dou
  * orthorectifier) with the pixel coordinates generated in the kernel.  Point k =
  * r * n_samps + c is pixel (line0 + r * dline, samp0 + c * dsamp), r < n_lines,
  * c < n_samps; `height` as above, indexed by k.  Device pointers. */
-int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, double samp0,
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, double samp0,
                                           double dline, double dsamp, int64_t n_lines,
                                           int64_t n_samps, const double *height,
                                           int height_stride, double prec, double *x, double *y,
@@ -154,7 +161,7 @@ int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, d
 
 /* Number of kernels this library has launched on the calling process so far (all models,
  * all streams).  bench.py reports the difference over its timed region as gpu_launches. */
-int64_t usgscsm_b200_kernel_launches(void);
+USGSCSM_B200_API int64_t usgscsm_b200_kernel_launches(void);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,136 @@
+"""ctypes bridge to oracle/_ref/libusgscsm_ref.so -- TEST INFRASTRUCTURE, not the product.
+
+The library is the UNMODIFIED reference sensor-model code compiled by oracle/Makefile from
+/root/reference (plus ALE/PROJ/Eigen shims and the C driver oracle/ref_driver.cpp).  Only
+tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module; nothing under usgscsm_b200/ does.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libusgscsm_ref.so")
+
+_dp = C.c_void_p
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError("oracle/_ref/libusgscsm_ref.so is missing: run `make -C oracle ref` "
+                               "in the build container (needs /root/reference)")
+        L = C.CDLL(LIB_PATH)
+        L.ref_last_error.restype = C.c_char_p
+        L.ref_max_threads.restype = C.c_int
+        L.ref_model_from_state.restype = C.c_void_p
+        L.ref_model_from_state.argtypes = [C.c_char_p, C.c_size_t]
+        L.ref_model_free.argtypes = [C.c_void_p]
+        L.ref_model_state.restype = C.c_size_t
+        L.ref_model_state.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
+        L.ref_ls_derived.argtypes = [C.c_void_p, _dp]
+        L.ref_ls_set_projective.argtypes = [C.c_void_p, C.c_int, _dp]
+        L.ref_set_parameter.argtypes = [C.c_void_p, C.c_int, C.c_double]
+        L.ref_image_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.ref_ground_to_image.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, C.c_double, _dp,
+                                          _dp, _dp, _dp, C.c_int]
+        L.ref_image_to_ground.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, C.c_int,
+                                          C.c_double, _dp, _dp, _dp, _dp, _dp, C.c_int]
+        L.ref_lagrange.argtypes = [C.c_int, _dp, C.c_double, C.c_double, C.c_double, C.c_int,
+                                   C.c_int, _dp]
+        L.ref_remove_distortion.argtypes = [C.c_double, C.c_double, _dp, _dp, _dp, C.c_int,
+                                            C.c_double, C.c_int, C.c_double]
+        L.ref_apply_distortion.argtypes = [C.c_double, C.c_double, _dp, _dp, _dp, C.c_int,
+                                           C.c_double, C.c_int, C.c_double, C.c_double]
+        L.ref_ellipsoid_elevation.restype = C.c_double
+        L.ref_ellipsoid_elevation.argtypes = [C.c_double] * 6 + [_dp]
+        L.ref_rotation_from_quaternion.argtypes = [_dp, _dp]
+        L.ref_rotation_from_euler.argtypes = [_dp, _dp]
+        L.ref_projective_fit.argtypes = [C.c_int, _dp, _dp, _dp, _dp, _dp, _dp]
+        _lib = L
+    return _lib
+
+
+def _a(x, n=None):
+    x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1)
+    if n is not None and x.size != n:
+        raise ValueError("length mismatch")
+    return x
+
+
+class RefModel(object):
+    """A reference csm::RasterGM built by the reference plugin from a model-state string."""
+
+    def __init__(self, state):
+        raw = state if isinstance(state, bytes) else state.encode("utf-8")
+        self._L = lib()
+        self._h = self._L.ref_model_from_state(raw, len(raw))
+        if not self._h:
+            raise RuntimeError("reference could not build the model: " +
+                               self._L.ref_last_error().decode("utf-8", "replace"))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._L.ref_model_free(self._h)
+            self._h = None
+
+    def state(self):
+        n = self._L.ref_model_state(self._h, None, 0)
+        buf = C.create_string_buffer(n)
+        self._L.ref_model_state(self._h, buf, n)
+        return buf.raw.decode("utf-8")
+
+    def image_size(self):
+        l, s = C.c_int(), C.c_int()
+        self._L.ref_image_size(self._h, C.byref(l), C.byref(s))
+        return l.value, s.value
+
+    def ls_derived(self):
+        out = np.zeros(22)
+        if self._L.ref_ls_derived(self._h, out.ctypes.data) != 0:
+            raise RuntimeError("not a line-scan model")
+        return out
+
+    def ls_set_projective(self, use, coeffs14=None):
+        c = None if coeffs14 is None else _a(coeffs14, 14)
+        self._L.ref_ls_set_projective(self._h, int(bool(use)), None if c is None else c.ctypes.data)
+
+    def set_parameter(self, index, value):
+        if self._L.ref_set_parameter(self._h, index, float(value)) != 0:
+            raise RuntimeError(self._L.ref_last_error().decode())
+
+    def ground_to_image(self, x, y, z, prec=0.001, threads=1):
+        x = _a(x)
+        n = x.size
+        y, z = _a(y, n), _a(z, n)
+        line, samp, ach = np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_ground_to_image(self._h, n, x.ctypes.data, y.ctypes.data, z.ctypes.data, prec,
+                                    line.ctypes.data, samp.ctypes.data, ach.ctypes.data,
+                                    st.ctypes.data, threads)
+        return line, samp, ach, st
+
+    def image_to_ground(self, line, samp, height, prec=0.001, threads=1):
+        line = _a(line)
+        n = line.size
+        samp = _a(samp, n)
+        height = _a(height)
+        stride = 0 if (height.size == 1 and n != 1) else 1
+        x, y, z, ach = np.empty(n), np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_image_to_ground(self._h, n, line.ctypes.data, samp.ctypes.data,
+                                    height.ctypes.data, stride, prec, x.ctypes.data,
+                                    y.ctypes.data, z.ctypes.data, ach.ctypes.data,
+                                    st.ctypes.data, threads)
+        return x, y, z, ach, st
+
+
+def max_threads():
+    return lib().ref_max_threads()

@@ -1,0 +1,93 @@
+"""ctypes binding of the C-ABI in include/usgscsm_b200.h (libusgscsm_b200.so).
+
+The library is the product: there is no Python or CPU implementation of the per-point
+math behind it.  Importing this module fails loudly when the shared library has not been
+built (``python -c "import __graft_entry__ as g; g.build()"`` or ``make -C usgscsm_b200``).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libusgscsm_b200.so")
+
+OK = 0
+EINVAL, ESTATE, ENODEVICE, ECUDA, EUNSUPPORTED = -1, -2, -3, -4, -5
+
+MODEL_LINE_SCANNER, MODEL_PUSH_FRAME, MODEL_FRAME, MODEL_SAR = 1, 2, 3, 4
+
+ST_NO_INTERSECTION = 1 << 0
+ST_PRECISION_NOT_MET = 1 << 1
+ST_ITERATION_CAP = 1 << 2
+ST_SEARCH_STALL = 1 << 3
+ST_DISTORTION_NOT_CONVERGED = 1 << 4
+ST_ERROR_ALGORITHM = 1 << 5
+ST_ERROR_UNKNOWN = 1 << 6
+ST_NONFINITE = 1 << 7
+ST_OUT_OF_IMAGE = 1 << 8
+ST_ERROR_OTHER = 1 << 9
+ST_REFERENCE_MASK = (ST_NO_INTERSECTION | ST_PRECISION_NOT_MET | ST_ERROR_ALGORITHM |
+                     ST_ERROR_UNKNOWN | ST_NONFINITE | ST_OUT_OF_IMAGE | ST_ERROR_OTHER)
+
+_dp = C.c_void_p  # double* / uint32_t* / stream, passed as raw addresses
+_h = C.c_void_p   # usgscsm_b200_model*
+
+# name -> (restype, argtypes); the order follows include/usgscsm_b200.h
+SIGNATURES = {
+    "usgscsm_b200_abi_version": (C.c_int, []),
+    "usgscsm_b200_last_error": (C.c_char_p, []),
+    "usgscsm_b200_device_count": (C.c_int, []),
+    "usgscsm_b200_model_from_state": (C.c_int, [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_h)]),
+    "usgscsm_b200_model_free": (None, [_h]),
+    "usgscsm_b200_model_kind": (C.c_int, [_h]),
+    "usgscsm_b200_model_device": (C.c_int, [_h]),
+    "usgscsm_b200_model_image_size": (C.c_int, [_h, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "usgscsm_b200_model_num_parameters": (C.c_int, [_h]),
+    "usgscsm_b200_model_get_parameter": (C.c_int, [_h, C.c_int, C.POINTER(C.c_double)]),
+    "usgscsm_b200_model_set_parameter": (C.c_int, [_h, C.c_int, C.c_double]),
+    "usgscsm_b200_model_ls_derived": (C.c_int, [_h, C.POINTER(C.c_double)]),
+    "usgscsm_b200_model_ls_set_projective": (C.c_int, [_h, C.c_int, C.POINTER(C.c_double)]),
+    "usgscsm_b200_ground_to_image": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_dev": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_dev": (
+        C.c_int,
+        [_h, C.c_int64, _dp, _dp, _dp, C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_grid_dev": (
+        C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
+                  C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_kernel_launches": (C.c_int64, []),
+}
+
+
+class EngineError(RuntimeError):
+    """A C-ABI call returned a negative USGSCSM_B200_E* code."""
+
+    def __init__(self, code, message):
+        super().__init__("usgscsm_b200 error %d: %s" % (code, message))
+        self.code = code
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "usgscsm_b200: %s is missing -- build the CUDA library first (there is no CPU "
+            "fallback): python -c 'import __graft_entry__ as g; g.build()'" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export it
+        fn.restype = res
+        fn.argtypes = args
+    if lib.usgscsm_b200_abi_version() != 1:
+        raise ImportError("usgscsm_b200: ABI version mismatch")
+    return lib
+
+
+lib = _load()
+
+
+def check(code):
+    if code != OK:
+        raise EngineError(code, lib.usgscsm_b200_last_error().decode("utf-8", "replace"))

@@ -1,0 +1,374 @@
+// capi.cu -- the C-ABI of include/usgscsm_b200.h over the kernel launchers.
+//
+// There is no CPU implementation of the per-point math behind these entry points: every
+// compute call ends in a kernel launch or fails with a negative error code.
+#include <atomic>
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "../../include/usgscsm_b200.h"
+#include "model.h"
+#include "state_reader.h"
+
+namespace ub200 {
+
+static std::atomic<int64_t> g_launches{0};
+void countLaunch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static thread_local std::string g_lastError;
+
+// ---- Model ------------------------------------------------------------------------------
+Model::~Model() {
+  cudaSetDevice(device);
+  for (DeviceBuffer &b : owned) cudaFree(b.ptr);
+  for (PipelineSlot &s : slots) {
+    for (double *p : s.in) cudaFree(p);
+    for (double *p : s.out) cudaFree(p);
+    cudaFree(s.status);
+    if (s.done) cudaEventDestroy(s.done);
+    if (s.stream) cudaStreamDestroy(s.stream);
+  }
+}
+
+const double *Model::upload(const std::vector<double> &v) {
+  DeviceBuffer b;
+  b.bytes = (v.empty() ? 1 : v.size()) * sizeof(double);
+  UB_CUDA(cudaMalloc(&b.ptr, b.bytes));
+  owned.push_back(b);
+  if (!v.empty()) UB_CUDA(cudaMemcpy(b.ptr, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return static_cast<const double *>(b.ptr);
+}
+
+void Model::ensureSlot(int s, long points) {
+  PipelineSlot &p = slots[s];
+  if (!p.stream) UB_CUDA(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
+  if (!p.done) UB_CUDA(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
+  if (p.capacity >= points) return;
+  for (double *&q : p.in) {
+    cudaFree(q);
+    q = nullptr;
+    UB_CUDA(cudaMalloc(&q, points * sizeof(double)));
+  }
+  for (double *&q : p.out) {
+    cudaFree(q);
+    q = nullptr;
+    UB_CUDA(cudaMalloc(&q, points * sizeof(double)));
+  }
+  cudaFree(p.status);
+  p.status = nullptr;
+  UB_CUDA(cudaMalloc(&p.status, points * sizeof(uint32_t)));
+  p.capacity = points;
+}
+
+// ---- error plumbing ---------------------------------------------------------------------
+template <class F>
+static int guarded(F &&f) {
+  try {
+    return f();
+  } catch (const CudaError &e) {
+    g_lastError = e.what();
+    return USGSCSM_B200_ECUDA;
+  } catch (const StateError &e) {
+    g_lastError = e.what();
+    return USGSCSM_B200_ESTATE;
+  } catch (const std::invalid_argument &e) {
+    g_lastError = e.what();
+    return USGSCSM_B200_EINVAL;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return USGSCSM_B200_ESTATE;
+  }
+}
+
+static int fail(int code, const char *msg) {
+  g_lastError = msg;
+  return code;
+}
+
+static int deviceCount() {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// Dispatch of the two per-point operations on the model kind (device pointers).
+static cudaError_t launchGroundToImage(Model &m, long n, const double *x, const double *y,
+                                       const double *z, double prec, double *line, double *samp,
+                                       double *achieved, uint32_t *status, cudaStream_t stream) {
+  switch (m.kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+      return launchLsGroundToImage(m.ls, m.smCount, n, x, y, z, prec, line, samp, achieved,
+                                   status, stream);
+    default:
+      return cudaErrorNotSupported;
+  }
+}
+
+static cudaError_t launchImageToGround(Model &m, long n, const double *line, const double *samp,
+                                       const GridSpec *grid, const double *height,
+                                       int heightStride, double prec, double *x, double *y,
+                                       double *z, double *achieved, uint32_t *status,
+                                       cudaStream_t stream) {
+  switch (m.kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+      return launchLsImageToGround(m.ls, m.smCount, n, line, samp, grid, height, heightStride,
+                                   prec, x, y, z, achieved, status, stream);
+    default:
+      return cudaErrorNotSupported;
+  }
+}
+
+}  // namespace ub200
+
+using namespace ub200;
+
+extern "C" {
+
+int usgscsm_b200_abi_version(void) { return USGSCSM_B200_ABI_VERSION; }
+const char *usgscsm_b200_last_error(void) { return g_lastError.c_str(); }
+int usgscsm_b200_device_count(void) { return deviceCount(); }
+int64_t usgscsm_b200_kernel_launches(void) { return g_launches.load(); }
+
+// getModelNameFromModelState (src/UsgsAstroPlugin.cpp:176-218): the JSON key "m_modelName".
+int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
+                                  usgscsm_b200_model **out) {
+  if (!state || !out) return fail(USGSCSM_B200_EINVAL, "null argument");
+  *out = nullptr;
+  if (device < 0 || device >= deviceCount())
+    return fail(USGSCSM_B200_ENODEVICE, "no usable CUDA device with that index");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(device));
+    std::string text = stateJsonText(state, len);
+    json::Value root = json::parse(text);
+    StateReader st(root);
+    std::unique_ptr<usgscsm_b200_model> m(new usgscsm_b200_model);
+    m->device = device;
+    cudaDeviceProp prop;
+    UB_CUDA(cudaGetDeviceProperties(&prop, device));
+    m->smCount = prop.multiProcessorCount;
+    m->modelName = st.getString("m_modelName");
+    if (m->modelName == "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL") {
+      m->kind = USGSCSM_B200_MODEL_LINE_SCANNER;
+      loadLineScanner(*m, st);
+    } else {
+      g_lastError = "unsupported model name: " + m->modelName;
+      return USGSCSM_B200_EUNSUPPORTED;
+    }
+    UB_CUDA(cudaDeviceSynchronize());
+    *out = m.release();
+    return USGSCSM_B200_OK;
+  });
+}
+
+void usgscsm_b200_model_free(usgscsm_b200_model *m) { delete m; }
+
+int usgscsm_b200_model_kind(const usgscsm_b200_model *m) { return m ? m->kind : 0; }
+int usgscsm_b200_model_device(const usgscsm_b200_model *m) { return m ? m->device : -1; }
+
+int usgscsm_b200_model_image_size(const usgscsm_b200_model *m, int *lines, int *samps) {
+  if (!m || !lines || !samps) return fail(USGSCSM_B200_EINVAL, "null argument");
+  switch (m->kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+    case USGSCSM_B200_MODEL_PUSH_FRAME:
+      *lines = m->ls.nLines;
+      *samps = m->ls.nSamples;
+      break;
+    case USGSCSM_B200_MODEL_FRAME:
+      *lines = m->fr.nLines;
+      *samps = m->fr.nSamples;
+      break;
+    default:
+      *lines = m->sar.nLines;
+      *samps = m->sar.nSamples;
+      break;
+  }
+  return USGSCSM_B200_OK;
+}
+
+int usgscsm_b200_model_num_parameters(const usgscsm_b200_model *m) {
+  return m ? (int)m->params.size() : 0;
+}
+
+int usgscsm_b200_model_get_parameter(const usgscsm_b200_model *m, int index, double *value) {
+  if (!m || !value) return fail(USGSCSM_B200_EINVAL, "null argument");
+  if (index < 0 || index >= (int)m->params.size())
+    return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
+  *value = m->params[index];
+  return USGSCSM_B200_OK;
+}
+
+int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double value) {
+  if (!m) return fail(USGSCSM_B200_EINVAL, "null argument");
+  if (index < 0 || index >= (int)m->params.size())
+    return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
+  m->params[index] = value;
+  if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER) repackLineScanner(*m);
+  return USGSCSM_B200_OK;
+}
+
+int usgscsm_b200_model_ls_derived(const usgscsm_b200_model *m, double *out) {
+  if (!m || !out) return fail(USGSCSM_B200_EINVAL, "null argument");
+  if (m->kind != USGSCSM_B200_MODEL_LINE_SCANNER)
+    return fail(USGSCSM_B200_EINVAL, "not a line-scan model");
+  out[0] = m->ls.gsd;
+  out[1] = m->ls.flyingHeight;
+  out[2] = m->ls.halfSwath;
+  out[3] = m->ls.halfTime;
+  out[4] = m->ls.useApproxInitTrans ? 1.0 : 0.0;
+  for (int i = 0; i < 14; i++) out[5 + i] = m->ls.projCoeffs[i];
+  for (int i = 0; i < 3; i++) out[19 + i] = m->referencePoint[i];
+  return USGSCSM_B200_OK;
+}
+
+int usgscsm_b200_model_ls_set_projective(usgscsm_b200_model *m, int use, const double *coeffs14) {
+  if (!m) return fail(USGSCSM_B200_EINVAL, "null argument");
+  if (m->kind != USGSCSM_B200_MODEL_LINE_SCANNER)
+    return fail(USGSCSM_B200_EINVAL, "not a line-scan model");
+  m->ls.useApproxInitTrans = use != 0;
+  if (coeffs14) std::memcpy(m->ls.projCoeffs, coeffs14, 14 * sizeof(double));
+  return USGSCSM_B200_OK;
+}
+
+// ---- device-pointer flavours ----------------------------------------------------------------
+int usgscsm_b200_ground_to_image_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+                                     const double *y, const double *z, double prec, double *line,
+                                     double *samp, double *achieved, uint32_t *status,
+                                     void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!x || !y || !z || !line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    UB_CUDA(launchGroundToImage(*m, (long)n, x, y, z, prec, line, samp, achieved, status,
+                                static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_ground_dev(usgscsm_b200_model *m, int64_t n, const double *line,
+                                     const double *samp, const double *height, int height_stride,
+                                     double prec, double *x, double *y, double *z,
+                                     double *achieved, uint32_t *status, void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp || !height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    UB_CUDA(launchImageToGround(*m, (long)n, line, samp, nullptr, height, height_stride ? 1 : 0,
+                                prec, x, y, z, achieved, status,
+                                static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, double samp0,
+                                          double dline, double dsamp, int64_t n_lines,
+                                          int64_t n_samps, const double *height,
+                                          int height_stride, double prec, double *x, double *y,
+                                          double *z, double *achieved, uint32_t *status,
+                                          void *stream) {
+  if (!m || n_lines < 0 || n_samps < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n_lines == 0 || n_samps == 0) return USGSCSM_B200_OK;
+  if (!height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    GridSpec g{line0, samp0, dline, dsamp, (long)n_samps};
+    UB_CUDA(launchImageToGround(*m, (long)(n_lines * n_samps), nullptr, nullptr, &g, height,
+                                height_stride ? 1 : 0, prec, x, y, z, achieved, status,
+                                static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
+// ---- host-pointer flavours ------------------------------------------------------------------
+// Chunked three-slot pipeline: while chunk c runs its kernel, chunk c+1 is copied in and
+// chunk c-1 is copied out, each slot on its own stream.  Copies are truly asynchronous when
+// the caller's arrays are page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory);
+// with pageable arrays the runtime stages them and the calls still complete correctly.
+int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double *x,
+                                 const double *y, const double *z, double prec, double *line,
+                                 double *samp, double *achieved, uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!x || !y || !z || !line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % kPipelineSlots);
+      m->ensureSlot(si, chunk);
+      PipelineSlot &s = m->slots[si];
+      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      UB_CUDA(cudaMemcpyAsync(s.in[0], x + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(s.in[1], y + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(s.in[2], z + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launchGroundToImage(*m, cnt, s.in[0], s.in[1], s.in[2], prec, s.out[0], s.out[1],
+                                  achieved ? s.out[2] : nullptr, status ? s.status : nullptr,
+                                  s.stream));
+      UB_CUDA(cudaMemcpyAsync(line + off, s.out[0], b, cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaMemcpyAsync(samp + off, s.out[1], b, cudaMemcpyDeviceToHost, s.stream));
+      if (achieved)
+        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < kPipelineSlots && si < c; si++)
+      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double *line,
+                                 const double *samp, const double *height, int height_stride,
+                                 double prec, double *x, double *y, double *z, double *achieved,
+                                 uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp || !height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % kPipelineSlots);
+      m->ensureSlot(si, chunk);
+      PipelineSlot &s = m->slots[si];
+      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      UB_CUDA(cudaMemcpyAsync(s.in[0], line + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(s.in[1], samp + off, b, cudaMemcpyHostToDevice, s.stream));
+      if (height_stride)
+        UB_CUDA(cudaMemcpyAsync(s.in[2], height + off, b, cudaMemcpyHostToDevice, s.stream));
+      else
+        UB_CUDA(cudaMemcpyAsync(s.in[2], height, sizeof(double), cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launchImageToGround(*m, cnt, s.in[0], s.in[1], nullptr, s.in[2],
+                                  height_stride ? 1 : 0, prec, s.out[0], s.out[1], s.out[2],
+                                  achieved ? s.out[3] : nullptr, status ? s.status : nullptr,
+                                  s.stream));
+      UB_CUDA(cudaMemcpyAsync(x + off, s.out[0], b, cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaMemcpyAsync(y + off, s.out[1], b, cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaMemcpyAsync(z + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
+      if (achieved)
+        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[3], b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < kPipelineSlots && si < c; si++)
+      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+}  // extern "C"

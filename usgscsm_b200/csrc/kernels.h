@@ -39,5 +39,10 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream);
 
+cudaError_t launchLsSensorPosition(const LsState &S, int n, const double *line, double *xyz,
+                                   cudaStream_t stream);
+cudaError_t launchEllipsoidElevation(const Ellipsoid &ell, int n, const double *xyz, double prec,
+                                     double *h, cudaStream_t stream);
+
 }  // namespace ub200
 #endif

@@ -234,6 +234,35 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// ---- model set-up helpers -------------------------------------------------------------------
+// The reference derives a few per-model inputs of the hot path at load time with its own
+// per-point routines (updateState LS:649-735, createProjectiveApproximation LS:2745-2803).
+// The engine has no CPU copy of that math, so the loader runs these two small kernels.
+
+// getSensorPosition(ImageCoord) LS:1580-1611: getAdjSensorPosVel with calc_vel = true.
+__global__ void lsSensorPositionKernel(const __grid_constant__ LsState S, int n,
+                                       const double *__restrict__ line, double *__restrict__ xyz) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  OrientationTables T;
+  T.positions = S.positions.values;
+  T.velocities = S.velocities.values;
+  T.quaternions = S.quaternions.values;
+  double pos[3], vel[3];
+  adjSensorPosVel<true>(S, T, lsImageTime(S, line[i]), pos, vel);
+  xyz[3 * i + 0] = pos[0];
+  xyz[3 * i + 1] = pos[1];
+  xyz[3 * i + 2] = pos[2];
+}
+
+// computeEllipsoidElevation U:819-868 for n points (xyz interleaved).
+__global__ void ellipsoidElevationKernel(Ellipsoid ell, int n, const double *__restrict__ xyz,
+                                         double prec, double *__restrict__ h) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  h[i] = ellipsoidElevation(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], ell, prec);
+}
+
 }  // namespace
 
 // ---- launchers ---------------------------------------------------------------------------
@@ -299,6 +328,22 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
   else
     UB_LAUNCH_I2G(false, false);
 #undef UB_LAUNCH_I2G
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchLsSensorPosition(const LsState &S, int n, const double *line, double *xyz,
+                                   cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  lsSensorPositionKernel<<<(n + 63) / 64, 64, 0, stream>>>(S, n, line, xyz);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchEllipsoidElevation(const Ellipsoid &ell, int n, const double *xyz, double prec,
+                                     double *h, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  ellipsoidElevationKernel<<<(n + 63) / 64, 64, 0, stream>>>(ell, n, xyz, prec, h);
   countLaunch();
   return cudaGetLastError();
 }

@@ -1,0 +1,102 @@
+// model.h -- host-side model object behind the C-ABI handle (usgscsm_b200_model).
+//
+// Mirrors what a reference model object owns on the hot path: the members read by
+// groundToImage / imageToGround (host copies, for re-packing after setParameterValue)
+// and, new here, the packed device state + device tables + streams/staging buffers.
+#ifndef USGSCSM_B200_MODEL_H_
+#define USGSCSM_B200_MODEL_H_
+
+#include <cuda_runtime.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "sensor_state.h"
+
+namespace ub200 {
+
+struct CudaError : std::runtime_error {
+  explicit CudaError(const std::string &what) : std::runtime_error(what) {}
+};
+struct StateError : std::runtime_error {
+  explicit StateError(const std::string &what) : std::runtime_error(what) {}
+};
+
+#define UB_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t e_ = (expr);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      throw ::ub200::CudaError(std::string(#expr) + ": " + cudaGetErrorString(e_));       \
+  } while (0)
+
+// Device allocation owned by a model.
+struct DeviceBuffer {
+  void *ptr = nullptr;
+  size_t bytes = 0;
+};
+
+// One slot of the chunked host-pointer pipeline: device scratch for one chunk + a stream.
+struct PipelineSlot {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;
+  double *in[3] = {nullptr, nullptr, nullptr};   // x,y,z  or line,samp,height
+  double *out[4] = {nullptr, nullptr, nullptr, nullptr};  // up to x,y,z,achieved
+  uint32_t *status = nullptr;
+  long capacity = 0;  // points
+};
+
+constexpr int kPipelineSlots = 3;
+constexpr long kPipelineChunk = 1L << 22;  // 4 Mi points per chunk (~200 MB of I/O)
+
+struct Model {
+  int kind = 0;
+  int device = 0;
+  int smCount = 0;
+  std::string modelName;
+
+  // ---- host copies of the members the per-point math reads ---------------------------
+  // line-scan / push-frame
+  LsState ls{};  // scalars valid on host; pointer members hold DEVICE addresses
+  std::vector<double> intTimeLines, intTimeStartTimes, intTimes;
+  std::vector<double> positions, velocities, quaternions;
+  double referencePoint[3] = {0, 0, 0};
+  int platformFlag = 1;
+  int numQuaternionDoubles = 0;  // m_numQuaternions (counts doubles, LS:2145)
+  // frame
+  FrameState fr{};
+  std::vector<double> lineJitter, sampleJitter, lineTimes;
+  // SAR
+  SarState sar{};
+  std::vector<double> scaleCoeffs, scaleTimes;
+
+  std::vector<double> params;  // m_currentParameterValue (raw, without the +0.0)
+
+  // ---- device side ---------------------------------------------------------------------
+  std::vector<DeviceBuffer> owned;
+  PipelineSlot slots[kPipelineSlots];
+
+  ~Model();
+  const double *upload(const std::vector<double> &v);
+  void ensureSlot(int s, long points);
+};
+
+// model_ls.cu
+void loadLineScanner(Model &m, const class StateReader &st);
+void repackLineScanner(Model &m);  // after a parameter / projective-seed change
+void loadPushFrame(Model &m, const class StateReader &st);
+
+// projective_fit.cpp
+// Least-squares fit of the 14-coefficient 3D->2D projective map (the reference's
+// usgscsm::computeBestFitProjectiveTransform, src/EigenUtilities.cpp:14-66).
+void fitProjectiveTransform(int numPts, const double *line, const double *samp,
+                            const double *x, const double *y, const double *z,
+                            double coeffs[14]);
+
+}  // namespace ub200
+
+// The opaque C handle is the Model itself.
+struct usgscsm_b200_model : ub200::Model {};
+
+#endif

@@ -1,0 +1,326 @@
+"""Host-side mirror of the reference's plugin / sensor-model interface for the hot path.
+
+Names, argument meaning and error behaviour follow the reference:
+
+* ``UsgsAstroPlugin``  -- src/UsgsAstroPlugin.cpp (constructModelFromState :535-555,
+  getModelNameFromModelState :176-218, canModelBeConstructedFromState :229-250);
+* ``RasterGM.groundToImage / imageToGround`` -- csm/RasterGM.h, one point per call, warnings
+  appended to an optional list, hard failures raised as ``Error`` (csm/Error.h:40-48);
+* new here: ``groundToImageBatch / imageToGroundBatch / imageToGroundGrid`` -- whole arrays per
+  call through the C-ABI (include/usgscsm_b200.h) into the sm_100a kernels.
+
+Every call, scalar or batched, runs on the GPU; there is no CPU path.
+"""
+import collections
+import ctypes as C
+import json
+
+import numpy as np
+
+from . import _capi
+from ._capi import lib, check
+
+ImageCoord = collections.namedtuple("ImageCoord", "line samp")
+EcefCoord = collections.namedtuple("EcefCoord", "x y z")
+
+
+class Warning(object):  # csm/Warning.h:39-47
+    UNKNOWN_WARNING, DATA_NOT_AVAILABLE, PRECISION_NOT_MET, NEGATIVE_PRECISION, \
+        IMAGE_COORD_OUT_OF_BOUNDS, IMAGE_ID_TOO_LONG, NO_INTERSECTION, DEPRECATED_FUNCTION = range(1, 9)
+
+    def __init__(self, warning, message, function):
+        self.warning, self.message, self.function = warning, message, function
+
+    def getWarning(self):
+        return self.warning
+
+    def getMessage(self):
+        return self.message
+
+    def getFunction(self):
+        return self.function
+
+
+class Error(Exception):  # csm/Error.h:40-48
+    ALGORITHM, BOUNDS, FILE_READ, FILE_WRITE, ILLEGAL_MATH_OPERATION, INDEX_OUT_OF_RANGE, \
+        INVALID_SENSOR_MODEL_STATE, INVALID_USE, ISD_NOT_SUPPORTED, MEMORY, \
+        SENSOR_MODEL_NOT_CONSTRUCTIBLE, SENSOR_MODEL_NOT_SUPPORTED, STRING_TOO_LONG, \
+        UNKNOWN_ERROR, UNSUPPORTED_FUNCTION, UNKNOWN_SUPPORT_DATA = range(1, 17)
+
+    def __init__(self, error, message, function):
+        super().__init__(message)
+        self.error, self.message, self.function = error, message, function
+
+    def getError(self):
+        return self.error
+
+
+_MODEL_NAMES = {
+    "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL": _capi.MODEL_LINE_SCANNER,
+    "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL": _capi.MODEL_PUSH_FRAME,
+    "USGS_ASTRO_FRAME_SENSOR_MODEL": _capi.MODEL_FRAME,
+    "USGS_ASTRO_SAR_SENSOR_MODEL": _capi.MODEL_SAR,
+}
+
+
+def _is_torch(a):
+    return hasattr(a, "data_ptr") and hasattr(a, "is_cuda")
+
+
+def _host(a, n=None):
+    a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1)
+    if n is not None and a.size != n:
+        raise ValueError("array length mismatch")
+    return a
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if _is_torch(a):
+        return a.data_ptr()
+    return a.ctypes.data
+
+
+class RasterGM(object):
+    """A sensor model living on one GPU (csm::RasterGM of the reference)."""
+
+    def __init__(self, handle, state):
+        self._h = handle
+        self._state = state
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.usgscsm_b200_model_free(h)
+
+    # ---- csm::Model / GeometricModel subset --------------------------------------------
+    def getModelName(self):
+        kind = lib.usgscsm_b200_model_kind(self._h)
+        return [k for k, v in _MODEL_NAMES.items() if v == kind][0]
+
+    def getModelState(self):
+        return self._state
+
+    def getImageSize(self):
+        l, s = C.c_int(), C.c_int()
+        check(lib.usgscsm_b200_model_image_size(self._h, C.byref(l), C.byref(s)))
+        return ImageCoord(l.value, s.value)
+
+    def getValidImageRange(self):
+        sz = self.getImageSize()
+        return ImageCoord(0.0, 0.0), ImageCoord(float(sz.line), float(sz.samp))
+
+    def getNumParameters(self):
+        return lib.usgscsm_b200_model_num_parameters(self._h)
+
+    def getParameterValue(self, index):
+        v = C.c_double()
+        check(lib.usgscsm_b200_model_get_parameter(self._h, index, C.byref(v)))
+        return v.value
+
+    def setParameterValue(self, index, value):
+        check(lib.usgscsm_b200_model_set_parameter(self._h, index, float(value)))
+
+    @property
+    def device(self):
+        return lib.usgscsm_b200_model_device(self._h)
+
+    def lsDerived(self):
+        out = (C.c_double * 22)()
+        check(lib.usgscsm_b200_model_ls_derived(self._h, out))
+        return np.array(out[:], dtype=np.float64)
+
+    def lsSetProjective(self, use, coeffs14=None):
+        c = None
+        if coeffs14 is not None:
+            c = (C.c_double * 14)(*[float(v) for v in coeffs14])
+        check(lib.usgscsm_b200_model_ls_set_projective(self._h, int(bool(use)), c))
+
+    # ---- batched per-point math ---------------------------------------------------------
+    def groundToImageBatch(self, x, y, z, desiredPrecision=0.001, achieved=True, status=True,
+                           stream=None):
+        """groundToImage for arrays.  numpy in -> numpy out (host flavour, copies included);
+        torch CUDA tensors in -> torch CUDA tensors out (device flavour, enqueued on `stream`
+        or torch's current stream, not synchronised).  Returns (line, samp, achieved, status)."""
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            line, samp = torch.empty_like(x), torch.empty_like(x)
+            ach = torch.empty_like(x) if achieved else None
+            st = torch.empty(n, dtype=torch.int32, device=x.device) if status else None
+            if stream is None:
+                stream = torch.cuda.current_stream(x.device).cuda_stream
+            check(lib.usgscsm_b200_ground_to_image_dev(
+                self._h, n, _ptr(x), _ptr(y), _ptr(z), desiredPrecision, _ptr(line), _ptr(samp),
+                _ptr(ach), _ptr(st), stream))
+            return line, samp, ach, st
+        x = _host(x)
+        n = x.size
+        y, z = _host(y, n), _host(z, n)
+        line, samp = np.empty(n), np.empty(n)
+        ach = np.empty(n) if achieved else None
+        st = np.empty(n, dtype=np.uint32) if status else None
+        check(lib.usgscsm_b200_ground_to_image(self._h, n, _ptr(x), _ptr(y), _ptr(z),
+                                               desiredPrecision, _ptr(line), _ptr(samp),
+                                               _ptr(ach), _ptr(st)))
+        return line, samp, ach, st
+
+    def imageToGroundBatch(self, line, samp, height, desiredPrecision=0.001, achieved=True,
+                           status=True, stream=None):
+        """imageToGround for arrays; `height` is a scalar or an array of the same length.
+        Returns (x, y, z, achieved, status)."""
+        if _is_torch(line):
+            import torch
+            n = line.numel()
+            if not _is_torch(height):
+                height = torch.full((1,), float(height), dtype=torch.float64, device=line.device)
+            stride = 0 if height.numel() == 1 else 1
+            x, y, z = torch.empty_like(line), torch.empty_like(line), torch.empty_like(line)
+            ach = torch.empty_like(line) if achieved else None
+            st = torch.empty(n, dtype=torch.int32, device=line.device) if status else None
+            if stream is None:
+                stream = torch.cuda.current_stream(line.device).cuda_stream
+            check(lib.usgscsm_b200_image_to_ground_dev(
+                self._h, n, _ptr(line), _ptr(samp), _ptr(height), stride, desiredPrecision,
+                _ptr(x), _ptr(y), _ptr(z), _ptr(ach), _ptr(st), stream))
+            return x, y, z, ach, st
+        line = _host(line)
+        n = line.size
+        samp = _host(samp, n)
+        height = _host(height)
+        if height.size not in (1, n):
+            raise ValueError("height must be a scalar or match line/samp")
+        stride = 0 if height.size == 1 and n != 1 else 1
+        x, y, z = np.empty(n), np.empty(n), np.empty(n)
+        ach = np.empty(n) if achieved else None
+        st = np.empty(n, dtype=np.uint32) if status else None
+        check(lib.usgscsm_b200_image_to_ground(self._h, n, _ptr(line), _ptr(samp), _ptr(height),
+                                               stride, desiredPrecision, _ptr(x), _ptr(y),
+                                               _ptr(z), _ptr(ach), _ptr(st)))
+        return x, y, z, ach, st
+
+    def imageToGroundGrid(self, line0, samp0, dline, dsamp, n_lines, n_samps, height,
+                          desiredPrecision=0.001, achieved=False, status=True, out=None,
+                          stream=None):
+        """Dense-grid imageToGround (bin/usgscsm_cam_test.cc:294-309) with pixel coordinates
+        generated in the kernel.  `height`: torch CUDA tensor with 1 or n_lines*n_samps
+        entries.  Returns torch CUDA tensors (x, y, z, achieved, status)."""
+        import torch
+        n = int(n_lines) * int(n_samps)
+        dev = height.device
+        stride = 0 if height.numel() == 1 else 1
+        if out is None:
+            x, y, z = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
+            ach = torch.empty(n, dtype=torch.float64, device=dev) if achieved else None
+            st = torch.empty(n, dtype=torch.int32, device=dev) if status else None
+        else:
+            x, y, z, ach, st = out
+        if stream is None:
+            stream = torch.cuda.current_stream(dev).cuda_stream
+        check(lib.usgscsm_b200_image_to_ground_grid_dev(
+            self._h, float(line0), float(samp0), float(dline), float(dsamp), int(n_lines),
+            int(n_samps), _ptr(height), stride, desiredPrecision, _ptr(x), _ptr(y), _ptr(z),
+            _ptr(ach), _ptr(st), stream))
+        return x, y, z, ach, st
+
+    # ---- csm::RasterGM per-point API (a batch of one) ---------------------------------------
+    @staticmethod
+    def _raise_or_warn(st, warnings, function):
+        if st & _capi.ST_ERROR_ALGORITHM:
+            raise Error(Error.ALGORITHM, "Unable to apply transform.", function)
+        if st & _capi.ST_ERROR_UNKNOWN:
+            raise Error(Error.UNKNOWN_ERROR, "Could not calculate the image coordinate.", function)
+        if st & _capi.ST_ERROR_OTHER:
+            raise Error(Error.UNKNOWN_ERROR, "per-point failure", function)
+        if warnings is not None:
+            if st & _capi.ST_NO_INTERSECTION:
+                warnings.append(Warning(Warning.NO_INTERSECTION, "No Intersection", function))
+            if st & _capi.ST_PRECISION_NOT_MET:
+                warnings.append(Warning(Warning.PRECISION_NOT_MET,
+                                        "Desired precision not achieved.", function))
+
+    def groundToImage(self, groundPt, desiredPrecision=0.001, achievedPrecision=None,
+                      warnings=None):
+        """csm::RasterGM::groundToImage.  `achievedPrecision`: optional list, receives one
+        value; `warnings`: optional list, receives Warning objects."""
+        l, s, a, st = self.groundToImageBatch([groundPt[0]], [groundPt[1]], [groundPt[2]],
+                                              desiredPrecision)
+        self._raise_or_warn(int(st[0]), warnings, "groundToImage")
+        if achievedPrecision is not None:
+            achievedPrecision.append(float(a[0]))
+        return ImageCoord(float(l[0]), float(s[0]))
+
+    def imageToGround(self, imagePt, height, desiredPrecision=0.001, achievedPrecision=None,
+                      warnings=None):
+        """csm::RasterGM::imageToGround."""
+        x, y, z, a, st = self.imageToGroundBatch([imagePt[0]], [imagePt[1]], [height],
+                                                 desiredPrecision)
+        self._raise_or_warn(int(st[0]), warnings, "imageToGround")
+        if achievedPrecision is not None:
+            achievedPrecision.append(float(a[0]))
+        return EcefCoord(float(x[0]), float(y[0]), float(z[0]))
+
+
+class UsgsAstroPlugin(object):
+    """src/UsgsAstroPlugin.cpp: the factory; models are built from model-state strings."""
+
+    _PLUGIN_NAME = "UsgsAstroPluginCSM"
+    _MANUFACTURER_NAME = "UsgsAstrogeology"
+    _RELEASE_DATE = "20190222"
+
+    def __init__(self, device=0):
+        self.device = device
+
+    def getPluginName(self):
+        return self._PLUGIN_NAME
+
+    def getManufacturer(self):
+        return self._MANUFACTURER_NAME
+
+    def getReleaseDate(self):
+        return self._RELEASE_DATE
+
+    def getNumModels(self):
+        return len(_MODEL_NAMES)
+
+    def getModelName(self, index):
+        return list(_MODEL_NAMES)[index]
+
+    @staticmethod
+    def _state_bytes(state):
+        return state if isinstance(state, bytes) else state.encode("utf-8")
+
+    def getModelNameFromModelState(self, modelState):
+        """UsgsAstroPlugin.cpp:176-218: JSON key m_modelName (after stateAsJson)."""
+        raw = self._state_bytes(modelState)
+        text = bytes(c if 32 <= c < 127 else 10 for c in raw).decode("ascii")
+        a, b = text.find("{"), text.rfind("}")
+        try:
+            name = json.loads(text[max(a, 0):b + 1])["m_modelName"]
+        except Exception:
+            raise Error(Error.INVALID_SENSOR_MODEL_STATE, "No 'm_modelName' key in the model state object.",
+                        "UsgsAstroPlugin::getModelNameFromModelState")
+        if name not in _MODEL_NAMES:
+            raise Error(Error.SENSOR_MODEL_NOT_SUPPORTED, "Sensor model not supported.",
+                        "UsgsAstroPlugin::getModelNameFromModelState")
+        return name
+
+    def canModelBeConstructedFromState(self, modelName, modelState, warnings=None):
+        try:
+            return self.getModelNameFromModelState(modelState) == modelName
+        except Error:
+            return False
+
+    def constructModelFromState(self, modelState, warnings=None, device=None):
+        raw = self._state_bytes(modelState)
+        h = C.c_void_p()
+        code = lib.usgscsm_b200_model_from_state(raw, len(raw), self.device if device is None else device,
+                                                 C.byref(h))
+        if code in (_capi.ESTATE, _capi.EUNSUPPORTED):
+            raise Error(Error.SENSOR_MODEL_NOT_CONSTRUCTIBLE if code == _capi.ESTATE
+                        else Error.SENSOR_MODEL_NOT_SUPPORTED,
+                        lib.usgscsm_b200_last_error().decode("utf-8", "replace"),
+                        "UsgsAstroPlugin::constructModelFromState")
+        check(code)
+        return RasterGM(h, modelState if isinstance(modelState, str) else raw.decode("latin-1"))

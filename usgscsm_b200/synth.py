@@ -1,0 +1,185 @@
+"""Synthetic model states for the hot-path workloads (no ISD / ALE involved).
+
+A model state is what ``getModelState()`` of the reference writes: ``<MODEL_NAME>\\n{json}``
+with the keys of ``UsgsAstroLsSensorModel::getModelMap`` (src/UsgsAstroLsSensorModel.cpp:345-474).
+The orbit recipe follows jupyter_notebooks/OrbitalLsGeneration.ipynb of the reference
+(circular orbit, nadir pointing), plus a small attitude wobble so that the 8-point Lagrange
+interpolation of the quaternion table is exercised; LRO-NAC-like camera constants follow
+tests/data/toughLroNacLineScan.json.
+
+Every float array starts with a float literal: the reference types a JSON array by its
+first element (src/Utilities.cpp:2760-2768).
+"""
+import json
+import math
+
+import numpy as np
+
+RADIAL, TRANSVERSE, KAGUYALISM, DAWNFC, LROLROCNAC, CAHVOR, LUNARORBITER, RADTAN, KPLOSHADOWCAM = range(9)
+
+MOON_RADIUS = 1737400.0
+
+
+def _rot(axis, a):
+    c, s = math.cos(a), math.sin(a)
+    if axis == 0:
+        return np.array([[1, 0, 0], [0, c, -s], [0, s, c]], dtype=np.float64)
+    if axis == 1:
+        return np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]], dtype=np.float64)
+    return np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]], dtype=np.float64)
+
+
+def _quat_xyzw(m):
+    """Rotation matrix -> unit quaternion (x, y, z, w), the storage order of m_quaternions."""
+    t = m[0, 0] + m[1, 1] + m[2, 2]
+    if t > 0:
+        s = math.sqrt(t + 1.0) * 2
+        w, x, y, z = 0.25 * s, (m[2, 1] - m[1, 2]) / s, (m[0, 2] - m[2, 0]) / s, (m[1, 0] - m[0, 1]) / s
+    elif m[0, 0] > m[1, 1] and m[0, 0] > m[2, 2]:
+        s = math.sqrt(1.0 + m[0, 0] - m[1, 1] - m[2, 2]) * 2
+        w, x, y, z = (m[2, 1] - m[1, 2]) / s, 0.25 * s, (m[0, 1] + m[1, 0]) / s, (m[0, 2] + m[2, 0]) / s
+    elif m[1, 1] > m[2, 2]:
+        s = math.sqrt(1.0 + m[1, 1] - m[0, 0] - m[2, 2]) * 2
+        w, x, y, z = (m[0, 2] - m[2, 0]) / s, (m[0, 1] + m[1, 0]) / s, 0.25 * s, (m[1, 2] + m[2, 1]) / s
+    else:
+        s = math.sqrt(1.0 + m[2, 2] - m[0, 0] - m[1, 1]) * 2
+        w, x, y, z = (m[1, 0] - m[0, 1]) / s, (m[0, 2] + m[2, 0]) / s, (m[1, 2] + m[2, 1]) / s, 0.25 * s
+    return np.array([x, y, z, w], dtype=np.float64)
+
+
+def synthetic_dem(line, samp, amplitude=500.0):
+    """h = A sin(2 pi l / 4096) cos(2 pi s / 1024) metres."""
+    return amplitude * np.sin(2 * np.pi * line / 4096.0) * np.cos(2 * np.pi * samp / 1024.0)
+
+
+def linescan_state(n_lines=52224, n_samples=5064, focal_length=699.62, pixel_pitch_inv=142.857,
+                   altitude=50000.0, major_axis=MOON_RADIUS, minor_axis=MOON_RADIUS,
+                   distortion_type=LROLROCNAC, dist_coeffs=(1.81e-5,), seed=20261104,
+                   wobble=1e-5, wobble_hz=3.0, dt_ephem=1.0, dt_quat=0.05, line_time=None,
+                   params=None, platform_flag=1, n_time_segments=1, gm=4.9028e12,
+                   summing=1, starting_sample=0.0, derived=None, as_dict=False):
+    """A line-scan model state on a circular, tilted polar orbit with nadir pointing.
+
+    `line_time` defaults to the value giving square ground pixels.  `n_time_segments` > 1
+    splits the image into segments with slightly different line rates (exercises the
+    upper_bound of getImageTime, LS:1543-1568).  `derived` = None leaves gsd/flyingHeight at
+    their defaults so the model computes them itself (LS:283-285).
+    """
+    rng = np.random.default_rng(seed)
+    r_orbit = major_axis + altitude
+    v = math.sqrt(gm / r_orbit)
+    omega = v / r_orbit
+    ground_speed = omega * major_axis
+    gsd_cross = altitude / (focal_length * pixel_pitch_inv) * summing
+    if line_time is None:
+        line_time = gsd_cross / ground_speed
+
+    # line -> time segments (m_intTimeLines is 0.5-based as written by the reference's ISD path)
+    seg_lines, seg_starts, seg_times = [], [], []
+    t = 0.0
+    per = n_lines // n_time_segments
+    for k in range(n_time_segments):
+        l0 = k * per
+        rate = line_time * (1.0 + 0.01 * k)
+        seg_lines.append(l0 + 0.5)
+        seg_starts.append(t)
+        seg_times.append(rate)
+        nl = (n_lines - l0) if k == n_time_segments - 1 else per
+        t += rate * nl
+    total = t
+    seg_starts = [s - total / 2.0 for s in seg_starts]  # time is relative to the image centre
+    t_begin, t_end = -total / 2.0, total / 2.0
+
+    tilt = _rot(2, 0.3 + 0.1 * rng.random()) @ _rot(0, 0.2 + 0.1 * rng.random())
+    phase0 = 0.4 + rng.random()
+
+    def frame(tt):
+        th = phase0 + omega * tt
+        radial = tilt @ np.array([math.cos(th), 0.0, math.sin(th)])
+        intrack = tilt @ np.array([-math.sin(th), 0.0, math.cos(th)])
+        cross = np.cross(radial, intrack)
+        return radial, intrack, cross
+
+    n_pos = int(math.ceil((t_end - t_begin) / dt_ephem)) + 1 + 8
+    t0_ephem = t_begin - 4 * dt_ephem
+    pos = np.empty((n_pos, 3))
+    vel = np.empty((n_pos, 3))
+    for i in range(n_pos):
+        radial, intrack, _ = frame(t0_ephem + i * dt_ephem)
+        pos[i] = r_orbit * radial
+        vel[i] = v * intrack
+
+    n_quat = int(math.ceil((t_end - t_begin) / dt_quat)) + 1 + 8
+    t0_quat = t_begin - 4 * dt_quat
+    ph = rng.random(3) * 2 * math.pi
+    quat = np.empty((n_quat, 4))
+    for i in range(n_quat):
+        tt = t0_quat + i * dt_quat
+        radial, intrack, cross = frame(tt)
+        nominal = np.column_stack([intrack, cross, radial])  # camera x, y, z axes in body frame
+        w = [wobble * math.sin(2 * math.pi * wobble_hz * (1 + 0.13 * k) * tt + ph[k]) for k in range(3)]
+        q = _quat_xyzw(nominal @ _rot(0, w[0]) @ _rot(1, w[1]) @ _rot(2, w[2]))
+        if i and float(np.dot(q, quat[i - 1])) < 0:
+            q = -q
+        quat[i] = q
+
+    p = [0.0] * 16 if params is None else [float(x) for x in params]
+    d = derived or {}
+    state = {
+        "m_modelName": "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL",
+        "m_imageIdentifier": "synthetic_ls_%d" % seed,
+        "m_sensorName": "SYNTHETIC_NAC",
+        "m_nLines": int(n_lines),
+        "m_nSamples": int(n_samples),
+        "m_platformFlag": int(platform_flag),
+        "m_intTimeLines": [float(x) for x in seg_lines],
+        "m_intTimeStartTimes": [float(x) for x in seg_starts],
+        "m_intTimes": [float(x) for x in seg_times],
+        "m_startingEphemerisTime": float(t_begin),
+        "m_centerEphemerisTime": 0.0,
+        "m_detectorSampleSumming": int(summing),
+        "m_detectorLineSumming": int(summing),
+        "m_startingDetectorSample": float(starting_sample),
+        "m_startingDetectorLine": 0.0,
+        "m_ikCode": -85600,
+        "m_focalLength": float(focal_length),
+        "m_zDirection": 1.0,
+        "m_distortionType": int(distortion_type),
+        "m_opticalDistCoeffs": [float(x) for x in dist_coeffs],
+        "m_iTransS": [0.0, 0.0, float(pixel_pitch_inv)],
+        "m_iTransL": [0.0, float(pixel_pitch_inv), 0.0],
+        "m_detectorSampleOrigin": float(n_samples * summing / 2.0 - 0.5),
+        "m_detectorLineOrigin": 0.0,
+        "m_majorAxis": float(major_axis),
+        "m_minorAxis": float(minor_axis),
+        "m_platformIdentifier": "SYNTH",
+        "m_sensorIdentifier": "SYNTH_NAC",
+        "m_minElevation": -1000.0,
+        "m_maxElevation": 1000.0,
+        "m_dtEphem": float(dt_ephem),
+        "m_t0Ephem": float(t0_ephem),
+        "m_dtQuat": float(dt_quat),
+        "m_t0Quat": float(t0_quat),
+        "m_numPositions": int(3 * n_pos),
+        "m_numQuaternions": int(4 * n_quat),
+        "m_referencePointXyz": [0.0, 0.0, 0.0],
+        "m_gsd": float(d.get("gsd", 1.0)),
+        "m_flyingHeight": float(d.get("flyingHeight", 1000.0)),
+        "m_halfSwath": float(d.get("halfSwath", 1000.0)),
+        "m_halfTime": float(d.get("halfTime", 10.0)),
+        "m_positions": [float(x) for x in pos.reshape(-1)],
+        "m_velocities": [float(x) for x in vel.reshape(-1)],
+        "m_quaternions": [float(x) for x in quat.reshape(-1)],
+        "m_currentParameterValue": p,
+        "m_covariance": [0.0] * 256,
+        "m_sunPosition": [1.5e11, 0.0, 0.0],
+        "m_sunVelocity": [0.0, 0.0, 0.0],
+    }
+    if as_dict:
+        return state
+    return state_string(state)
+
+
+def state_string(state):
+    """``<MODEL_NAME>\\n{json}`` as getModelState() writes it (LS:476-483)."""
+    return state["m_modelName"] + "\n" + json.dumps(state)
