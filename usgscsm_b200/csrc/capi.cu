@@ -103,6 +103,9 @@ static cudaError_t launchGroundToImage(Model &m, long n, const double *x, const 
     case USGSCSM_B200_MODEL_LINE_SCANNER:
       return launchLsGroundToImage(m.ls, m.smCount, n, x, y, z, prec, line, samp, achieved,
                                    status, stream);
+    case USGSCSM_B200_MODEL_PUSH_FRAME:
+      return launchPfGroundToImage(m.ls, m.smCount, n, x, y, z, prec, line, samp, achieved,
+                                   status, stream);
     default:
       return cudaErrorNotSupported;
   }
@@ -116,6 +119,9 @@ static cudaError_t launchImageToGround(Model &m, long n, const double *line, con
   switch (m.kind) {
     case USGSCSM_B200_MODEL_LINE_SCANNER:
       return launchLsImageToGround(m.ls, m.smCount, n, line, samp, grid, height, heightStride,
+                                   prec, x, y, z, achieved, status, stream);
+    case USGSCSM_B200_MODEL_PUSH_FRAME:
+      return launchPfImageToGround(m.ls, m.smCount, n, line, samp, grid, height, heightStride,
                                    prec, x, y, z, achieved, status, stream);
     default:
       return cudaErrorNotSupported;
@@ -154,6 +160,9 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     if (m->modelName == "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL") {
       m->kind = USGSCSM_B200_MODEL_LINE_SCANNER;
       loadLineScanner(*m, st);
+    } else if (m->modelName == "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL") {
+      m->kind = USGSCSM_B200_MODEL_PUSH_FRAME;
+      loadPushFrame(*m, st);
     } else {
       g_lastError = "unsupported model name: " + m->modelName;
       return USGSCSM_B200_EUNSUPPORTED;
@@ -173,8 +182,11 @@ int usgscsm_b200_model_image_size(const usgscsm_b200_model *m, int *lines, int *
   if (!m || !lines || !samps) return fail(USGSCSM_B200_EINVAL, "null argument");
   switch (m->kind) {
     case USGSCSM_B200_MODEL_LINE_SCANNER:
-    case USGSCSM_B200_MODEL_PUSH_FRAME:
       *lines = m->ls.nLines;
+      *samps = m->ls.nSamples;
+      break;
+    case USGSCSM_B200_MODEL_PUSH_FRAME:  // getImageSize PF:1447-1449
+      *lines = m->ls.nReducedLines;
       *samps = m->ls.nSamples;
       break;
     case USGSCSM_B200_MODEL_FRAME:
@@ -206,8 +218,12 @@ int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double va
   if (index < 0 || index >= (int)m->params.size())
     return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
   m->params[index] = value;
-  if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER) repackLineScanner(*m);
-  return USGSCSM_B200_OK;
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER) repackLineScanner(*m);
+    if (m->kind == USGSCSM_B200_MODEL_PUSH_FRAME) repackPushFrame(*m);
+    return USGSCSM_B200_OK;
+  });
 }
 
 int usgscsm_b200_model_ls_derived(const usgscsm_b200_model *m, double *out) {

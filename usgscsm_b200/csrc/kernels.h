@@ -39,6 +39,19 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream);
 
+// push-frame (pf_kernels.cu)
+cudaError_t launchPfFrameletOrientations(const LsState &S, double *out, cudaStream_t stream);
+cudaError_t launchPfSensorPosition(const LsState &S, double time, double *xyz,
+                                   cudaStream_t stream);
+cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const double *x,
+                                  const double *y, const double *z, double prec, double *line,
+                                  double *samp, double *achieved, uint32_t *status,
+                                  cudaStream_t stream);
+cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const double *line,
+                                  const double *samp, const GridSpec *grid, const double *height,
+                                  int heightStride, double prec, double *x, double *y, double *z,
+                                  double *achieved, uint32_t *status, cudaStream_t stream);
+
 cudaError_t launchLsSensorPosition(const LsState &S, int n, const double *line, double *xyz,
                                    cudaStream_t stream);
 cudaError_t launchEllipsoidElevation(const Ellipsoid &ell, int n, const double *xyz, double prec,

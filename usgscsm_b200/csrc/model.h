@@ -75,6 +75,7 @@ struct Model {
 
   // ---- device side ---------------------------------------------------------------------
   std::vector<DeviceBuffer> owned;
+  double *frameletOrient = nullptr;  // push-frame: device table behind ls.frameletOrient
   PipelineSlot slots[kPipelineSlots];
 
   ~Model();
@@ -85,7 +86,13 @@ struct Model {
 // model_ls.cu
 void loadLineScanner(Model &m, const class StateReader &st);
 void repackLineScanner(Model &m);  // after a parameter / projective-seed change
+// model_pf.cu
 void loadPushFrame(Model &m, const class StateReader &st);
+void repackPushFrame(Model &m);  // after a parameter change: params + framelet orientations
+// shared readers (model_ls.cu)
+void readFocalPlane(FocalPlane &fp, const class StateReader &st, bool lineScanTypes);
+void readEllipsoid(Ellipsoid &e, const class StateReader &st);
+void readOrientation(Model &m, const class StateReader &st);
 
 // projective_fit.cpp
 // Least-squares fit of the 14-coefficient 3D->2D projective map (the reference's

@@ -137,14 +137,21 @@ void checkDistortionCoeffs(int type, size_t n) {
 
 }  // namespace
 
-void readFocalPlane(FocalPlane &fp, const StateReader &st, bool hasZDirection) {
-  fp.detectorSampleSumming = st.getInt("m_detectorSampleSumming");
-  fp.detectorLineSumming = st.getInt("m_detectorLineSumming");
+// lineScanTypes: the line-scan model reads the summing factors and m_zDirection as int
+// (LS:170-190: a double in the state is truncated); push-frame reads all three as double
+// (PF:166-191).
+void readFocalPlane(FocalPlane &fp, const StateReader &st, bool lineScanTypes) {
+  if (lineScanTypes) {
+    fp.detectorSampleSumming = st.getInt("m_detectorSampleSumming");
+    fp.detectorLineSumming = st.getInt("m_detectorLineSumming");
+  } else {
+    fp.detectorSampleSumming = st.getDouble("m_detectorSampleSumming");
+    fp.detectorLineSumming = st.getDouble("m_detectorLineSumming");
+  }
   fp.startingDetectorSample = st.getDouble("m_startingDetectorSample");
   fp.startingDetectorLine = st.getDouble("m_startingDetectorLine");
   fp.focalLength = st.getDouble("m_focalLength");
-  // LS:184-190: read as int first (a double value is truncated by VariantMap::get<int>)
-  fp.zDirection = hasZDirection ? (double)st.getInt("m_zDirection") : 1.0;
+  fp.zDirection = lineScanTypes ? (double)st.getInt("m_zDirection") : st.getDouble("m_zDirection");
   fp.distortionType = st.getInt("m_distortionType");
   std::vector<double> coeffs = st.getVecDouble("m_opticalDistCoeffs");
   checkDistortionCoeffs(fp.distortionType, coeffs.size());

@@ -1,0 +1,417 @@
+// pf_kernels.cu -- push-frame groundToImage / imageToGround, one thread per point, FP64.
+//
+// Replaces UsgsAstroPushFrameSensorModel::groundToImage
+// (src/UsgsAstroPushFrameSensorModel.cpp:715-778, with calcFrameDistance :2496-2521) and
+// ::imageToGround (:842-870, losToEcf :1726-1824, losEllipsoidIntersect :1883-1950).
+//
+// B200-first restructuring (bit-identical to the per-point code): a push-frame image has
+// ONE exposure time per framelet (getImageTime, PF:1258-1276), so everything the reference
+// recomputes per point and per secant step from the time alone -- two Lagrange-8
+// interpolations of the ephemeris, the in-track / cross-track / radial frame, the
+// Lagrange-8 quaternion, its rotation matrix and the attitude correction -- takes at most
+// numFramelets + 2 distinct values.  A set-up kernel evaluates them once per model with the
+// same device functions (same arithmetic, same rounding => same bits); the per-point
+// kernels read the 12 (or 21) doubles of their framelet from a copy staged in shared
+// memory.  A framelet number outside the table (imageToGround of a line far outside the
+// image) falls back to the in-thread evaluation.
+#include "kernels.h"
+#include "ls_common.cuh"
+
+namespace ub200 {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// The time framelet number of getImageTime (PF:1258-1276) for an image line.
+UB_DEV int pfTimeFramelet(const LsState &S, double line) {
+  int frameletNumber = truncToInt(line / S.summedFrameletHeight);
+  if (S.frameletsOrderReversed) frameletNumber = S.numFramelets - frameletNumber - 1;
+  return frameletNumber;
+}
+
+UB_DEV double pfFrameletTime(const LsState &S, int frameletNumber) {
+  double time = S.startingEphemerisTime + 0.5 * S.exposureDuration +
+                frameletNumber * S.interframeDelay;
+  time -= S.centerEphemerisTime;
+  return time;
+}
+
+struct Orientation {
+  double pos[3];
+  double camToBody[9];
+  double attCorr[9];  // valid only when S.hasAttAdj
+};
+
+// getAdjSensorPosVel PF:1955-2034 + getQuaternions PF:1679-1692 +
+// calculateRotationMatrixFromQuaternions + calculateAttitudeCorrection at one time.
+UB_DEV void computeOrientation(const LsState &S, const OrientationTables &T, double time,
+                               Orientation &o) {
+  double vel[3];
+  adjSensorPosVel<true>(S, T, time, o.pos, vel);
+  cameraToBodyMatrix(S, T, time, o.camToBody);
+  if (S.hasAttAdj) attitudeCorrection(S, time, o.attCorr);
+}
+
+// Where the per-framelet orientations are read from.
+struct OrientCache {
+  const double *entries;  // entry k + 1 <-> time framelet number k; null = no cache
+  int stride;             // doubles per entry in `entries`
+};
+
+UB_DEV void orientationAt(const LsState &S, const OrientationTables &T, const OrientCache &C,
+                          int frameletNumber, Orientation &o) {
+  if (C.entries && frameletNumber >= -1 && frameletNumber <= S.numFramelets) {
+    const double *e = C.entries + (long)(frameletNumber + 1) * C.stride;
+#pragma unroll
+    for (int i = 0; i < 3; i++) o.pos[i] = e[i];
+#pragma unroll
+    for (int i = 0; i < 9; i++) o.camToBody[i] = e[3 + i];
+    if (S.hasAttAdj) {
+#pragma unroll
+      for (int i = 0; i < 9; i++) o.attCorr[i] = e[12 + i];
+    }
+  } else {
+    computeOrientation(S, T, pfFrameletTime(S, frameletNumber), o);
+  }
+}
+
+// Second half of computeDetectorView PF:2038-2110 given the exterior orientation.
+UB_DEV void viewFromOrientation(const LsState &S, const Orientation &o, double gx, double gy,
+                                double gz, double &focalX, double &focalY) {
+  double bodyLook[3] = {gx - o.pos[0], gy - o.pos[1], gz - o.pos[2]};
+  double cameraLook[3];
+  matTVec(o.camToBody, bodyLook, cameraLook);
+  double adjustedLook[3];
+  if (S.hasAttAdj) {
+    matTVec(o.attCorr, cameraLook, adjustedLook);
+  } else {  // Euler angles identically 0: the correction is the identity
+    adjustedLook[0] = cameraLook[0];
+    adjustedLook[1] = cameraLook[1];
+    adjustedLook[2] = cameraLook[2];
+  }
+  double lookScale = (S.fp.focalLength + param(S, 15)) / adjustedLook[2];
+  focalX = adjustedLook[0] * lookScale;
+  focalY = adjustedLook[1] * lookScale;
+}
+
+// Stage the framelet orientations into shared memory (12 doubles per entry, or all 21 when
+// the attitude correction is live).  All threads of the block call it.
+__device__ inline OrientCache stageOrientCache(const LsState &S, double *smem, bool stage) {
+  OrientCache c;
+  if (!S.frameletOrient) {
+    c.entries = nullptr;
+    c.stride = 0;
+    return c;
+  }
+  if (!stage) {
+    c.entries = S.frameletOrient;
+    c.stride = kFrameletOrientDoubles;
+    return c;
+  }
+  const int stride = S.hasAttAdj ? kFrameletOrientDoubles : 12;
+  const int entries = S.numFramelets + 2;
+  for (int i = threadIdx.x; i < entries * stride; i += blockDim.x) {
+    int e = i / stride, j = i - e * stride;
+    smem[i] = __ldg(S.frameletOrient + (long)e * kFrameletOrientDoubles + j);
+  }
+  __syncthreads();
+  c.entries = smem;
+  c.stride = stride;
+  return c;
+}
+
+__host__ __device__ inline size_t orientCacheBytes(const LsState &S) {
+  return (size_t)(S.numFramelets + 2) * (S.hasAttAdj ? kFrameletOrientDoubles : 12) *
+         sizeof(double);
+}
+
+__global__ void pfFrameletOrientKernel(const __grid_constant__ LsState S, double *out) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;  // entry index; time framelet number k - 1
+  if (k >= S.numFramelets + 2) return;
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  Orientation o;
+#pragma unroll
+  for (int i = 0; i < 9; i++) o.attCorr[i] = 0.0;
+  computeOrientation(S, T, pfFrameletTime(S, k - 1), o);
+  double *e = out + (long)k * kFrameletOrientDoubles;
+  for (int i = 0; i < 3; i++) e[i] = o.pos[i];
+  for (int i = 0; i < 9; i++) e[3 + i] = o.camToBody[i];
+  for (int i = 0; i < 9; i++) e[12 + i] = o.attCorr[i];
+}
+
+// ---- groundToImage -------------------------------------------------------------------------
+UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
+                                 const OrientCache &C, double gx, double gy, double gz,
+                                 double desiredPrecision, double &outLine, double &outSamp,
+                                 double &achieved, uint32_t &status) {
+  const FocalPlane &fp = S.fp;
+  const int summedFrameletHeight = S.summedFrameletHeight;
+  const int numFramelets = S.numFramelets;
+
+  int startFramelet = 0;
+  double startDistance = 0.0;
+  int endFramelet = 0;
+  double endDistance = 0.0;
+  double focalX = 0.0, focalY = 0.0;
+  int viewFramelet = 0;  // time framelet number focalX/focalY were evaluated at
+  int count = 0;
+  // Evaluation order of the reference: calcFrameDistance(0), calcFrameDistance(n - 1), then
+  // one per secant step.  stage 0/1 are the two seeds.
+  int stage = 0;
+  for (;;) {
+    // calcFrameDistance PF:2496-2521 at endFramelet
+    double centerLine = (endFramelet + 0.5) * summedFrameletHeight;
+    viewFramelet = pfTimeFramelet(S, centerLine);
+    Orientation o;
+    orientationAt(S, T, C, viewFramelet, o);
+    viewFromOrientation(S, o, gx, gy, gz, focalX, focalY);
+    double detectorLine = fp.iTransL[0] + fp.iTransL[1] * focalX + fp.iTransL[2] * focalY +
+                          fp.detectorLineOrigin - fp.startingDetectorLine;
+    detectorLine /= fp.detectorLineSumming;
+    detectorLine -= S.halfOverlap;
+    double distance = detectorLine - summedFrameletHeight / 2.0;
+    if (stage == 0) {
+      startFramelet = 0;
+      startDistance = distance;
+      endFramelet = numFramelets - 1;
+      stage = 1;
+      continue;
+    }
+    endDistance = distance;
+    // while (startFramelet != endFramelet && startDistance != endDistance && count++ < 20)
+    if (!(startFramelet != endFramelet)) break;
+    if (!(startDistance != endDistance)) {
+      status |= USGSCSM_B200_ST_SEARCH_STALL;
+      break;
+    }
+    if (!(count++ < 20)) {
+      status |= USGSCSM_B200_ST_ITERATION_CAP;
+      break;
+    }
+    double offset = endDistance * (endFramelet - startFramelet) / (endDistance - startDistance);
+    startFramelet = endFramelet;
+    startDistance = endDistance;
+    endFramelet = truncToInt(round(endFramelet - offset));
+    endFramelet = max(0, min(numFramelets, endFramelet));
+  }
+
+  // getImageTime(ImageCoord(0.5 + summedFrameletHeight * endFramelet, 0.0)) + computeDetectorView:
+  // the same framelet time as the last distance evaluation, hence the same focal-plane point.
+  int finalFramelet = pfTimeFramelet(S, 0.5 + summedFrameletHeight * endFramelet);
+  if (finalFramelet != viewFramelet) {
+    Orientation o;
+    orientationAt(S, T, C, finalFramelet, o);
+    viewFromOrientation(S, o, gx, gy, gz, focalX, focalY);
+  }
+  double distortedFocalX, distortedFocalY;
+  applyDistortion(focalX, focalY, distortedFocalX, distortedFocalY, fp, desiredPrecision, status);
+  double detectorLine =
+      fp.iTransL[0] + fp.iTransL[1] * distortedFocalX + fp.iTransL[2] * distortedFocalY;
+  double detectorSample =
+      fp.iTransS[0] + fp.iTransS[1] * distortedFocalX + fp.iTransS[2] * distortedFocalY;
+  double line = (detectorLine + fp.detectorLineOrigin - fp.startingDetectorLine) /
+                fp.detectorLineSumming;
+  line += endFramelet * summedFrameletHeight;
+  line -= S.halfOverlap;
+  outLine = line;
+  outSamp = (detectorSample + fp.detectorSampleOrigin - fp.startingDetectorSample) /
+            fp.detectorSampleSumming;
+  achieved = desiredPrecision;  // PF:769-771
+}
+
+UB_DEV uint32_t pfImageRangeStatus(double line, double samp, const LsState &S) {
+  uint32_t st = 0;
+  if (!(isfinite(line) && isfinite(samp))) st |= USGSCSM_B200_ST_NONFINITE;
+  // getValidImageRange PF:1465-1472: (0,0) .. (nReducedLines, nSamples)
+  if (!(line >= 0.0 && line <= (double)S.nReducedLines && samp >= 0.0 &&
+        samp <= (double)S.nSamples))
+    st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+  return st;
+}
+
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    pfGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
+                          const double *__restrict__ y, const double *__restrict__ z, double prec,
+                          double *__restrict__ line, double *__restrict__ samp,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ double smem[];
+  OrientCache C = stageOrientCache(S, smem, STAGE);
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
+    double l, s, a;
+    uint32_t st = 0;
+    pfGroundToImagePoint(S, T, C, gx, gy, gz, prec, l, s, a, st);
+    st |= pfImageRangeStatus(l, s, S);
+    __stcs(line + i, l);
+    __stcs(samp + i, s);
+    if (achieved) __stcs(achieved + i, a);
+    if (status) __stcs(status + i, st);
+  }
+}
+
+// ---- imageToGround -------------------------------------------------------------------------
+UB_DEV void pfImageToGroundPoint(const LsState &S, const OrientationTables &T,
+                                 const OrientCache &C, double line, double sample, double height,
+                                 double desiredPrecision, double &x, double &y, double &z,
+                                 double &achieved, uint32_t &status) {
+  int frameletNumber = pfTimeFramelet(S, line);
+  Orientation o;
+  orientationAt(S, T, C, frameletNumber, o);
+
+  // line within the framelet, PF:1757-1764
+  double frameletLine = fmod(line, (double)S.summedFrameletHeight);
+  if (S.frameletsFlipped) frameletLine = S.summedFrameletHeight - frameletLine;
+  frameletLine += S.halfOverlap;
+
+  double distortedFocalPlaneX, distortedFocalPlaneY;
+  distortedFocalPlaneCoordinates(frameletLine, sample, S.fp, distortedFocalPlaneX,
+                                 distortedFocalPlaneY);
+  double undistortedFocalPlaneX, undistortedFocalPlaneY;
+  removeDistortion(distortedFocalPlaneX, distortedFocalPlaneY, undistortedFocalPlaneX,
+                   undistortedFocalPlaneY, S.fp, 1.0E-6, status);
+  double cameraLook[3];
+  cameraLookVector(undistortedFocalPlaneX, undistortedFocalPlaneY, S.fp.zDirection,
+                   S.fp.focalLength * (1 - param(S, 15) / S.halfSwath), cameraLook);
+  double corrected[3];
+  if (S.hasAttAdj) {
+    matVec(o.attCorr, cameraLook, corrected);
+  } else {
+    corrected[0] = cameraLook[0];
+    corrected[1] = cameraLook[1];
+    corrected[2] = cameraLook[2];
+  }
+  double bodyLook[3];
+  matVec(o.camToBody, corrected, bodyLook);
+  lsEllipsoidIntersect(S.ell, height, o.pos, bodyLook, desiredPrecision, x, y, z, achieved,
+                       status);
+  if ((desiredPrecision > 0.0) && (achieved > desiredPrecision))
+    status |= USGSCSM_B200_ST_PRECISION_NOT_MET;
+  if (status & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+    status = USGSCSM_B200_ST_ERROR_ALGORITHM;
+    x = y = z = achieved = nan("");
+  }
+  if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
+}
+
+template <bool STAGE, bool GRID>
+__global__ void __launch_bounds__(kThreads)
+    pfImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                          const double *__restrict__ samp, GridSpec g,
+                          const double *__restrict__ height, int heightStride, double prec,
+                          double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ double smem[];
+  OrientCache C = stageOrientCache(S, smem, STAGE);
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l, s;
+    if (GRID) {
+      long r = i / g.nSamps;
+      long c = i - r * g.nSamps;
+      l = g.line0 + (double)r * g.dline;
+      s = g.samp0 + (double)c * g.dsamp;
+    } else {
+      l = __ldcs(line + i);
+      s = __ldcs(samp + i);
+    }
+    double h = heightStride ? __ldcs(height + i) : __ldg(height);
+    double px, py, pz, a;
+    uint32_t st = 0;
+    pfImageToGroundPoint(S, T, C, l, s, h, prec, px, py, pz, a, st);
+    __stcs(x + i, px);
+    __stcs(y + i, py);
+    __stcs(z + i, pz);
+    if (achieved) __stcs(achieved + i, a);
+    if (status) __stcs(status + i, st);
+  }
+}
+
+// getSensorPosition(double time) PF:1290-1303: getAdjSensorPosVel at `time`.
+__global__ void pfSensorPositionKernel(const __grid_constant__ LsState S, double time,
+                                       double *__restrict__ xyz) {
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  double pos[3], vel[3];
+  adjSensorPosVel<true>(S, T, time, pos, vel);
+  xyz[0] = pos[0];
+  xyz[1] = pos[1];
+  xyz[2] = pos[2];
+}
+
+LaunchShape pfShape(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
+  size_t bytes = S.frameletOrient ? orientCacheBytes(S) : 0;
+  stage = bytes > 0 && bytes <= kMaxStagedTableBytes;
+  smemBytes = stage ? bytes : 0;
+  LaunchShape sh;
+  sh.threads = kThreads;
+  long blocksNeeded = (n + kThreads - 1) / kThreads;
+  long persistent = (long)smCount * kBlocksPerSm;
+  sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
+  if (sh.blocks < 1) sh.blocks = 1;
+  return sh;
+}
+
+}  // namespace
+
+cudaError_t launchPfFrameletOrientations(const LsState &S, double *out, cudaStream_t stream) {
+  int n = S.numFramelets + 2;
+  pfFrameletOrientKernel<<<(n + 63) / 64, 64, 0, stream>>>(S, out);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchPfSensorPosition(const LsState &S, double time, double *xyz,
+                                   cudaStream_t stream) {
+  pfSensorPositionKernel<<<1, 1, 0, stream>>>(S, time, xyz);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const double *x,
+                                  const double *y, const double *z, double prec, double *line,
+                                  double *samp, double *achieved, uint32_t *status,
+                                  cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  if (stage)
+    pfGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
+        S, n, x, y, z, prec, line, samp, achieved, status);
+  else
+    pfGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
+        S, n, x, y, z, prec, line, samp, achieved, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const double *line,
+                                  const double *samp, const GridSpec *grid, const double *height,
+                                  int heightStride, double prec, double *x, double *y, double *z,
+                                  double *achieved, uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+#define UB_LAUNCH_PF(STAGE, GRID)                                                         \
+  pfImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(       \
+      S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status)
+  if (stage && grid)
+    UB_LAUNCH_PF(true, true);
+  else if (stage)
+    UB_LAUNCH_PF(true, false);
+  else if (grid)
+    UB_LAUNCH_PF(false, true);
+  else
+    UB_LAUNCH_PF(false, false);
+#undef UB_LAUNCH_PF
+  countLaunch();
+  return cudaGetLastError();
+}
+
+}  // namespace ub200

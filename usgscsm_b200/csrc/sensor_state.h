@@ -99,17 +99,25 @@ struct LsState {
   UniformTable velocities;         // vlen 3 (same grid as positions)
   UniformTable quaternions;        // vlen 4
   // push-frame only (PF:715-778, PF:1258-1276, PF:1726-1824)
-  int frameletHeight;        // m_reducedFrameletHeight  (push-frame: m_frameletHeight)
-  int nReducedLines;         // unused by the reference's g2i but kept for symmetry
-  int numLinesOverlap;
+  int nReducedLines;          // m_nReducedLines (the push-frame image height)
+  int summedFrameletHeight;   // int(m_reducedFrameletHeight / m_detectorLineSumming), PF:721
+  int numFramelets;           // m_nReducedLines / summedFrameletHeight (integer division)
+  int halfOverlap;            // m_numLinesOverlap / 2 (integer division), PF:764
   int frameletsFlipped;
   int frameletsOrderReversed;
-  int pad0;
   double startingEphemerisTime;
   double centerEphemerisTime;
   double exposureDuration;
   double interframeDelay;
+  // Exterior orientation per framelet time.  A push-frame image has one exposure time per
+  // framelet (PF:1258-1276), so the adjusted sensor position, the camera-to-body matrix
+  // and the attitude correction take only numFramelets + 2 distinct values (time framelet
+  // numbers -1 .. numFramelets).  A set-up kernel evaluates them once with the per-point
+  // device functions; entry k + 1 holds pos[3], camToBody[9], attCorr[9] (kFrameletOrientDoubles).
+  const double *frameletOrient;  // device, (numFramelets + 2) * kFrameletOrientDoubles; may be null
 };
+
+constexpr int kFrameletOrientDoubles = 21;
 
 // Frame model (FR:137-372, FR:2250-2385).
 struct FrameState {

@@ -180,6 +180,126 @@ def linescan_state(n_lines=52224, n_samples=5064, focal_length=699.62, pixel_pit
     return state_string(state)
 
 
+def _orbit_tables(t_begin, t_end, dt_ephem, dt_quat, r_orbit, gm, rng, wobble, wobble_hz, pad=4):
+    """Positions/velocities every dt_ephem and camera-to-body quaternions (x,y,z,w) every
+    dt_quat over [t_begin, t_end] padded by `pad` nodes: circular tilted orbit, nadir pointing
+    (camera x = in-track, y = cross-track, z = radial) plus a small attitude wobble."""
+    v = math.sqrt(gm / r_orbit)
+    omega = v / r_orbit
+    tilt = _rot(2, 0.3 + 0.1 * rng.random()) @ _rot(0, 0.2 + 0.1 * rng.random())
+    phase0 = 0.4 + rng.random()
+
+    def frame(tt):
+        th = phase0 + omega * tt
+        radial = tilt @ np.array([math.cos(th), 0.0, math.sin(th)])
+        intrack = tilt @ np.array([-math.sin(th), 0.0, math.cos(th)])
+        return radial, intrack, np.cross(radial, intrack)
+
+    n_pos = int(math.ceil((t_end - t_begin) / dt_ephem)) + 1 + 2 * pad
+    t0_ephem = t_begin - pad * dt_ephem
+    pos, vel = np.empty((n_pos, 3)), np.empty((n_pos, 3))
+    for i in range(n_pos):
+        radial, intrack, _ = frame(t0_ephem + i * dt_ephem)
+        pos[i], vel[i] = r_orbit * radial, v * intrack
+    n_quat = int(math.ceil((t_end - t_begin) / dt_quat)) + 1 + 2 * pad
+    t0_quat = t_begin - pad * dt_quat
+    ph = rng.random(3) * 2 * math.pi
+    quat = np.empty((n_quat, 4))
+    for i in range(n_quat):
+        tt = t0_quat + i * dt_quat
+        radial, intrack, cross = frame(tt)
+        nominal = np.column_stack([intrack, cross, radial])
+        w = [wobble * math.sin(2 * math.pi * wobble_hz * (1 + 0.13 * k) * tt + ph[k]) for k in range(3)]
+        q = _quat_xyzw(nominal @ _rot(0, w[0]) @ _rot(1, w[1]) @ _rot(2, w[2]))
+        if i and float(np.dot(q, quat[i - 1])) < 0:
+            q = -q
+        quat[i] = q
+    return dict(pos=pos, vel=vel, quat=quat, t0_ephem=t0_ephem, t0_quat=t0_quat, omega=omega, v=v)
+
+
+def pushframe_state(n_framelets=256, framelet_height=16, n_samples=4096, overlap=2,
+                    focal_length=6.0, pixel_pitch_inv=640.0, altitude=50000.0,
+                    major_axis=MOON_RADIUS, minor_axis=MOON_RADIUS, distortion_type=RADIAL,
+                    dist_coeffs=(-0.0113109, -1.44463e-4, -4.88754e-6), seed=3, wobble=1e-5,
+                    wobble_hz=0.5, dt_ephem=1.0, dt_quat=0.25, exposure=0.039, params=None,
+                    platform_flag=1, gm=4.9028e12, summing=1.0, flipped=False, reversed_order=False,
+                    line_sign=-1.0, derived=None, as_dict=False):
+    """A push-frame model state (keys of UsgsAstroPushFrameSensorModel::getModelMap, PF:332-466;
+    shape of config C3 / tests/data/lroWacPushFrame.json): `n_framelets` framelets of
+    `framelet_height` reduced lines each (the detector framelet has `overlap` more lines),
+    one exposure per framelet, interframe delay chosen so consecutive framelets tile the ground."""
+    rng = np.random.default_rng(seed)
+    r_orbit = major_axis + altitude
+    v = math.sqrt(gm / r_orbit)
+    ground_speed = v / r_orbit * major_axis
+    gsd = altitude / (focal_length * pixel_pitch_inv) * summing
+    delay = framelet_height * gsd / ground_speed
+    total = n_framelets * delay
+    t_begin = -total / 2.0
+    orb = _orbit_tables(t_begin, t_begin + total, dt_ephem, dt_quat, r_orbit, gm, rng, wobble, wobble_hz)
+    p = [0.0] * 16 if params is None else [float(x) for x in params]
+    d = derived or {}
+    full_height = int(framelet_height * summing) + overlap
+    state = {
+        "m_modelName": "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL",
+        "m_imageIdentifier": "synthetic_pf_%d" % seed,
+        "m_sensorName": "SYNTHETIC_WAC",
+        "m_nLines": int(n_framelets * (framelet_height + overlap)),
+        "m_nSamples": int(n_samples),
+        "m_platformFlag": int(platform_flag),
+        "m_exposureDuration": float(exposure),
+        "m_interframeDelay": float(delay),
+        "m_frameletHeight": int(full_height),
+        "m_frameletsFlipped": bool(flipped),
+        "m_frameletsOrderReversed": bool(reversed_order),
+        "m_startingEphemerisTime": float(t_begin),
+        "m_centerEphemerisTime": 0.0,
+        "m_detectorSampleSumming": float(summing),
+        "m_detectorLineSumming": float(summing),
+        "m_startingDetectorSample": 0.0,
+        "m_startingDetectorLine": 0.0,
+        "m_ikCode": -85621,
+        "m_focalLength": float(focal_length),
+        "m_zDirection": 1.0,
+        "m_distortionType": int(distortion_type),
+        "m_opticalDistCoeffs": [float(x) for x in dist_coeffs],
+        "m_iTransS": [0.0, 0.0, float(pixel_pitch_inv)],
+        "m_iTransL": [0.0, float(line_sign * pixel_pitch_inv), 0.0],
+        "m_detectorSampleOrigin": float(n_samples * summing / 2.0),
+        "m_detectorLineOrigin": float(full_height / 2.0),
+        "m_majorAxis": float(major_axis),
+        "m_minorAxis": float(minor_axis),
+        "m_platformIdentifier": "SYNTH",
+        "m_sensorIdentifier": "SYNTH_WAC",
+        "m_minElevation": -1000.0,
+        "m_maxElevation": 1000.0,
+        "m_dtEphem": float(dt_ephem),
+        "m_t0Ephem": float(orb["t0_ephem"]),
+        "m_dtQuat": float(dt_quat),
+        "m_t0Quat": float(orb["t0_quat"]),
+        "m_numPositions": int(orb["pos"].size),
+        "m_numQuaternions": int(orb["quat"].size),
+        "m_referencePointXyz": [0.0, 0.0, 0.0],
+        "m_gsd": float(d.get("gsd", 1.0)),
+        "m_flyingHeight": float(d.get("flyingHeight", 1000.0)),
+        "m_halfSwath": float(d.get("halfSwath", 1000.0)),
+        "m_halfTime": float(d.get("halfTime", 10.0)),
+        "m_positions": [float(x) for x in orb["pos"].reshape(-1)],
+        "m_velocities": [float(x) for x in orb["vel"].reshape(-1)],
+        "m_quaternions": [float(x) for x in orb["quat"].reshape(-1)],
+        "m_currentParameterValue": p,
+        "m_covariance": [0.0] * 256,
+        "m_sunPosition": [1.5e11, 0.0, 0.0],
+        "m_sunVelocity": [0.0, 0.0, 0.0],
+        "m_numLinesOverlap": int(overlap),
+        "m_reducedframeletHeight": int(framelet_height * summing),
+        "m_nReducedLines": int(n_framelets * framelet_height),
+    }
+    if as_dict:
+        return state
+    return state_string(state)
+
+
 def state_string(state):
     """``<MODEL_NAME>\\n{json}`` as getModelState() writes it (LS:476-483)."""
     return state["m_modelName"] + "\n" + json.dumps(state)
