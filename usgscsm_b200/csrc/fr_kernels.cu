@@ -1,0 +1,214 @@
+// fr_kernels.cu -- framing-camera groundToImage / imageToGround, one thread per point, FP64.
+//
+// Replaces UsgsAstroFrameSensorModel::groundToImage (src/UsgsAstroFrameSensorModel.cpp:137-232)
+// and ::imageToGround (:280-372) with losEllipsoidIntersect (:2288-2345) and the
+// rolling-shutter jitter polynomial removeJitter / addJitter (src/Utilities.cpp:182-282).
+//
+// A frame has one exposure: position and attitude are model constants, so the two rotation
+// matrices are evaluated once on the host (sensor_state.h) and the per-point work is ~100
+// flop against 44-52 B of HBM traffic: this is the one HBM-bound kernel pair of the engine
+// (SURVEY.md §8d).  I/O is SoA, coalesced, streaming.
+#include "kernels.h"
+#include "device_math.cuh"
+
+namespace ub200 {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// removeJitter U:182-213.  Coefficients are in descending power, no constant term.
+UB_DEV void removeJitter(const FrameState &S, double line, double sample, double &dejitteredLine,
+                         double &dejitteredSample) {
+  double lineJitter = 0;
+  double sampleJitter = 0;
+  int idx = max(min(truncToInt(round(line)), S.numLineTimes), 1) - 1;
+  double time = __ldg(S.lineTimes + idx);
+  for (int n = 0; n < S.numJitterCoeffs; n++) {
+    double timeTerm = pow(time, (double)(S.numJitterCoeffs - n));
+    lineJitter += __ldg(S.lineJitter + n) * timeTerm;
+    sampleJitter += __ldg(S.sampleJitter + n) * timeTerm;
+  }
+  dejitteredLine = line - lineJitter;
+  dejitteredSample = sample - sampleJitter;
+}
+
+// addJitter U:244-282
+UB_DEV void addJitter(const FrameState &S, double line, double sample, double tolerance,
+                      int maxIts, double &jitteredLine, double &jitteredSample) {
+  int iteration = 0;
+  double dejitteredLine = line - 1;
+  double dejitteredSample = sample - 1;
+  double currentLine = line;
+  double currentSample = sample;
+  while (iteration < maxIts) {
+    removeJitter(S, currentLine, currentSample, dejitteredLine, dejitteredSample);
+    if (fabs(dejitteredLine - line) < tolerance && fabs(dejitteredSample - sample) < tolerance)
+      break;
+    currentLine = line + currentLine - dejitteredLine;
+    currentSample = sample + currentSample - dejitteredSample;
+    iteration++;
+  }
+  jitteredLine = currentLine;
+  jitteredSample = currentSample;
+}
+
+UB_DEV void frGroundToImagePoint(const FrameState &S, double x, double y, double z,
+                                 double desiredPrecision, double &outLine, double &outSamp,
+                                 uint32_t &status) {
+  const double *m = S.mRaw;  // m[r][c] = m[3 * r + c]
+  double xo = x - S.params[0];
+  double yo = y - S.params[1];
+  double zo = z - S.params[2];
+  double f = S.fp.focalLength;
+  double denom = m[2] * xo + m[5] * yo + m[8] * zo;
+  double undistortedx = (f * (m[0] * xo + m[3] * yo + m[6] * zo) / denom);
+  double undistortedy = (f * (m[1] * xo + m[4] * yo + m[7] * zo) / denom);
+  double distortedX, distortedY;
+  applyDistortion(undistortedx, undistortedy, distortedX, distortedY, S.fp, 1.0E-6, status);
+  double line, sample;
+  computePixel(distortedX, distortedY, S.fp, line, sample);
+  if (S.numLineTimes) {
+    double jitteredLine, jitteredSample;
+    addJitter(S, line, sample, desiredPrecision, 20, jitteredLine, jitteredSample);
+    line = jitteredLine;
+    sample = jitteredSample;
+  }
+  outLine = line;
+  outSamp = sample;
+}
+
+UB_DEV void frImageToGroundPoint(const FrameState &S, double line, double sample, double height,
+                                 double &x, double &y, double &z, uint32_t &status) {
+  const double *m = S.mNorm;
+  if (S.numLineTimes) {
+    double dejitteredLine, dejitteredSample;
+    removeJitter(S, line, sample, dejitteredLine, dejitteredSample);
+    line = dejitteredLine;
+    sample = dejitteredSample;
+  }
+  double x_camera, y_camera;
+  distortedFocalPlaneCoordinates(line, sample, S.fp, x_camera, y_camera);
+  double undistortedX, undistortedY;
+  removeDistortion(x_camera, y_camera, undistortedX, undistortedY, S.fp, 1.0E-6, status);
+  const double f = S.fp.focalLength;
+  double xl = m[0] * undistortedX + m[1] * undistortedY - m[2] * -f;
+  double yl = m[3] * undistortedX + m[4] * undistortedY - m[5] * -f;
+  double zl = m[6] * undistortedX + m[7] * undistortedY - m[8] * -f;
+  double xc = S.params[0], yc = S.params[1], zc = S.params[2];
+
+  // losEllipsoidIntersect FR:2288-2345: always the (-bt - sqrt) root
+  double ap = S.ell.majorAxis + height;
+  double bp = S.ell.minorAxis + height;
+  double k = ap * ap / (bp * bp);
+  double at = xl * xl + yl * yl + k * zl * zl;
+  double bt = 2.0 * (xl * xc + yl * yc + k * zl * zc);
+  double ct = xc * xc + yc * yc + k * zc * zc - ap * ap;
+  double quadTerm = bt * bt - 4.0 * at * ct;
+  if (0.0 > quadTerm) {
+    quadTerm = 0.0;
+    status |= USGSCSM_B200_ST_NO_INTERSECTION;
+  }
+  double scale = (-bt - sqrt(quadTerm)) / (2.0 * at);
+  x = xc + scale * xl;
+  y = yc + scale * yl;
+  z = zc + scale * zl;
+  if (status & USGSCSM_B200_ST_ERROR_ALGORITHM) {  // removeDistortion threw (D:357-365)
+    status = USGSCSM_B200_ST_ERROR_ALGORITHM;
+    x = y = z = nan("");
+  }
+  if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
+}
+
+__global__ void __launch_bounds__(kThreads)
+    frGroundToImageKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ x,
+                          const double *__restrict__ y, const double *__restrict__ z, double prec,
+                          double *__restrict__ line, double *__restrict__ samp,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
+    double l, s;
+    uint32_t st = 0;
+    frGroundToImagePoint(S, gx, gy, gz, prec, l, s, st);
+    if (!(isfinite(l) && isfinite(s))) st |= USGSCSM_B200_ST_NONFINITE;
+    // getValidImageRange FR:600-608: (startingDetectorLine, startingDetectorSample) .. (nLines, nSamples)
+    if (!(l >= S.fp.startingDetectorLine && l <= (double)S.nLines &&
+          s >= S.fp.startingDetectorSample && s <= (double)S.nSamples))
+      st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+    __stcs(line + i, l);
+    __stcs(samp + i, s);
+    if (achieved) __stcs(achieved + i, nan(""));  // the frame model never writes achievedPrecision
+    if (status) __stcs(status + i, st);
+  }
+}
+
+template <bool GRID>
+__global__ void __launch_bounds__(kThreads)
+    frImageToGroundKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ line,
+                          const double *__restrict__ samp, GridSpec g,
+                          const double *__restrict__ height, int heightStride,
+                          double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l, s;
+    if (GRID) {
+      long r = i / g.nSamps;
+      long c = i - r * g.nSamps;
+      l = g.line0 + (double)r * g.dline;
+      s = g.samp0 + (double)c * g.dsamp;
+    } else {
+      l = __ldcs(line + i);
+      s = __ldcs(samp + i);
+    }
+    double h = heightStride ? __ldcs(height + i) : __ldg(height);
+    double px, py, pz;
+    uint32_t st = 0;
+    frImageToGroundPoint(S, l, s, h, px, py, pz, st);
+    __stcs(x + i, px);
+    __stcs(y + i, py);
+    __stcs(z + i, pz);
+    if (achieved) __stcs(achieved + i, nan(""));
+    if (status) __stcs(status + i, st);
+  }
+}
+
+int frBlocks(long n, int smCount) {
+  long blocksNeeded = (n + kThreads - 1) / kThreads;
+  long persistent = (long)smCount * 8;  // light kernels: 8 resident blocks of 256 per SM
+  long b = blocksNeeded < persistent ? blocksNeeded : persistent;
+  return (int)(b < 1 ? 1 : b);
+}
+
+}  // namespace
+
+cudaError_t launchFrGroundToImage(const FrameState &S, int smCount, long n, const double *x,
+                                  const double *y, const double *z, double prec, double *line,
+                                  double *samp, double *achieved, uint32_t *status,
+                                  cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  frGroundToImageKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, prec, line,
+                                                                      samp, achieved, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, const double *line,
+                                  const double *samp, const GridSpec *grid, const double *height,
+                                  int heightStride, double prec, double *x, double *y, double *z,
+                                  double *achieved, uint32_t *status, cudaStream_t stream) {
+  (void)prec;  // the frame model's imageToGround is closed form: desiredPrecision is unused
+  if (n <= 0) return cudaSuccess;
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+  if (grid)
+    frImageToGroundKernel<true><<<frBlocks(n, smCount), kThreads, 0, stream>>>(
+        S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
+  else
+    frImageToGroundKernel<false><<<frBlocks(n, smCount), kThreads, 0, stream>>>(
+        S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+}  // namespace ub200

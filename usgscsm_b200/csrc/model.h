@@ -89,6 +89,9 @@ void repackLineScanner(Model &m);  // after a parameter / projective-seed change
 // model_pf.cu
 void loadPushFrame(Model &m, const class StateReader &st);
 void repackPushFrame(Model &m);  // after a parameter change: params + framelet orientations
+// model_fr.cu
+void loadFrame(Model &m, const class StateReader &st);
+void repackFrame(Model &m);
 // shared readers (model_ls.cu)
 void readFocalPlane(FocalPlane &fp, const class StateReader &st, bool lineScanTypes);
 void readEllipsoid(Ellipsoid &e, const class StateReader &st);

@@ -116,6 +116,8 @@ void createProjectiveApproximationLs(Model &m) {
   S.useApproxInitTrans = 1;
 }
 
+}  // namespace
+
 void checkDistortionCoeffs(int type, size_t n) {
   // Size checks the reference makes per call (src/Distortion.cpp:120-127, 261-269,
   // 342-350, 408-416) are made once here, so that the kernels never see a short array.
@@ -135,7 +137,6 @@ void checkDistortionCoeffs(int type, size_t n) {
   if (n > (size_t)kMaxDistCoeffs) throw StateError("m_opticalDistCoeffs has more than 20 entries");
 }
 
-}  // namespace
 
 // lineScanTypes: the line-scan model reads the summing factors and m_zDirection as int
 // (LS:170-190: a double in the state is truncated); push-frame reads all three as double

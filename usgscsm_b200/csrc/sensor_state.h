@@ -119,19 +119,22 @@ struct LsState {
 
 constexpr int kFrameletOrientDoubles = 21;
 
-// Frame model (FR:137-372, FR:2250-2385).
+// Frame model (FR:137-372, FR:2242-2385).
 struct FrameState {
-  FocalPlane fp;  // zDirection unused
+  FocalPlane fp;  // detector origins = m_ccdCenter[1] (sample), m_ccdCenter[0] (line); zDirection unused
   int nLines;
   int nSamples;
-  int numJitterCoeffs; // m_lineJitter.size() (== m_sampleJitter.size()); 0 = no jitter
-  int numLineTimes;
+  int numJitterCoeffs;  // m_lineJitter.size() (== m_sampleJitter.size())
+  int numLineTimes;     // m_lineTimes.size(); 0 = no rolling-shutter jitter correction
   Ellipsoid ell;
-  double params[7];    // x,y,z, q0..q3 (m_currentParameterValue)
-  double ccdCenter[2]; // line, sample
-  const double *lineJitter;   // device
-  const double *sampleJitter; // device
-  const double *lineTimes;    // device
+  double params[7];  // x, y, z, qx, qy, qz, qw (m_currentParameterValue + 0.0)
+  // Camera-to-body matrices, evaluated once on the host with the reference's expressions
+  // (IEEE arithmetic without contraction on both sides, hence the same bits):
+  double mNorm[9];  // calcRotationMatrix(m) FR:2242-2265: quaternion normalised (imageToGround)
+  double mRaw[9];   // calcRotationMatrix(m, adj) FR:2267-2286: NOT normalised (groundToImage)
+  const double *lineJitter;    // device
+  const double *sampleJitter;  // device
+  const double *lineTimes;     // device
 };
 
 // SAR model (SAR:541-861, SAR:1196-1300, SAR:1936-1972).

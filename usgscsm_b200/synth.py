@@ -300,6 +300,75 @@ def pushframe_state(n_framelets=256, framelet_height=16, n_samples=4096, overlap
     return state_string(state)
 
 
+def frame_state(n_lines=4096, n_samples=4096, focal_length=100.0, pixel_pitch_inv=100.0,
+                altitude=50000.0, major_axis=MOON_RADIUS, minor_axis=MOON_RADIUS,
+                distortion_type=RADIAL, dist_coeffs=(1e-4, -2e-7, 3e-10), seed=5, off_nadir=0.05,
+                summing=1, starting_sample=0.0, starting_line=0.0, jitter=None, params_delta=None,
+                unnormalised=1.0, as_dict=False):
+    """A framing-camera model state (keys of UsgsAstroFrameSensorModel::getModelState,
+    FR:1242-1288): one exposure from `altitude` above a random sub-spacecraft point, boresight
+    (camera +z) tilted `off_nadir` rad from nadir.  `jitter` = (line_coeffs, sample_coeffs,
+    line_time_step) adds the rolling-shutter polynomial of tests/data/jitterFramer-style states;
+    `unnormalised` scales the stored quaternion (imageToGround normalises it, groundToImage
+    does not: FR:2242-2286)."""
+    rng = np.random.default_rng(seed)
+    tilt = _rot(2, rng.random() * 6.0) @ _rot(0, rng.random() * 3.0)
+    radial = tilt @ np.array([1.0, 0.0, 0.0])
+    intrack = tilt @ np.array([0.0, 0.0, 1.0])
+    zc = -radial
+    yc = np.cross(zc, intrack)
+    nominal = np.column_stack([intrack, yc, zc]) @ _rot(0, off_nadir) @ _rot(1, -0.7 * off_nadir) @ _rot(2, 0.3)
+    q = _quat_xyzw(nominal) * unnormalised
+    # geodetic-ish: put the camera above the ellipsoid along `radial`
+    surf = 1.0 / math.sqrt((radial[0] ** 2 + radial[1] ** 2) / major_axis ** 2 + radial[2] ** 2 / minor_axis ** 2)
+    pos = radial * (surf + altitude)
+    p = [float(v) for v in pos] + [float(v) for v in q]
+    if params_delta is not None:
+        p = [a + float(b) for a, b in zip(p, params_delta)]
+    state = {
+        "m_modelName": "USGS_ASTRO_FRAME_SENSOR_MODEL",
+        "m_majorAxis": float(major_axis),
+        "m_minorAxis": float(minor_axis),
+        "m_focalLength": float(focal_length),
+        "m_startingDetectorSample": float(starting_sample),
+        "m_startingDetectorLine": float(starting_line),
+        "m_detectorSampleSumming": int(summing),
+        "m_detectorLineSumming": int(summing),
+        "m_focalLengthEpsilon": 1.0,
+        "m_nLines": int(n_lines),
+        "m_nSamples": int(n_samples),
+        "m_ephemerisTime": 1000.0,
+        "m_currentParameterValue": p,
+        "m_ccdCenter": [float(n_lines * summing / 2.0), float(n_samples * summing / 2.0)],
+        "m_spacecraftVelocity": [0.0, 1600.0, 0.0],
+        "m_sunPosition": [1.5e11, 0.0, 0.0],
+        "m_distortionType": int(distortion_type),
+        "m_opticalDistCoeffs": [float(x) for x in dist_coeffs],
+        "m_transX": [0.0, 1.0 / pixel_pitch_inv, 0.0],
+        "m_transY": [0.0, 0.0, 1.0 / pixel_pitch_inv],
+        "m_iTransS": [0.0, float(pixel_pitch_inv), 0.0],
+        "m_iTransL": [0.0, 0.0, float(pixel_pitch_inv)],
+        "m_imageIdentifier": "synthetic_frame_%d" % seed,
+        "m_platformName": "SYNTH",
+        "m_sensorName": "SYNTH_FRAMER",
+        "m_collectionIdentifier": "",
+        "m_currentParameterCovariance": [0.0] * 49,
+        "m_minElevation": -1000.0,
+        "m_maxElevation": 1000.0,
+        "m_originalHalfLines": float(n_lines / 2.0),
+        "m_originalHalfSamples": float(n_samples / 2.0),
+        "m_pixelPitch": 1.0 / pixel_pitch_inv,
+    }
+    if jitter is not None:
+        lj, sj, step = jitter
+        state["m_lineJitter"] = [float(v) for v in lj]
+        state["m_sampleJitter"] = [float(v) for v in sj]
+        state["m_lineTimes"] = [float(step * (i - n_lines / 2.0)) + 1e-9 for i in range(n_lines)]
+    if as_dict:
+        return state
+    return state_string(state)
+
+
 def state_string(state):
     """``<MODEL_NAME>\\n{json}`` as getModelState() writes it (LS:476-483)."""
     return state["m_modelName"] + "\n" + json.dumps(state)
