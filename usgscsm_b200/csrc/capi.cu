@@ -109,6 +109,9 @@ static cudaError_t launchGroundToImage(Model &m, long n, const double *x, const 
     case USGSCSM_B200_MODEL_FRAME:
       return launchFrGroundToImage(m.fr, m.smCount, n, x, y, z, prec, line, samp, achieved,
                                    status, stream);
+    case USGSCSM_B200_MODEL_SAR:
+      return launchSarGroundToImage(m.sar, m.smCount, n, x, y, z, prec, line, samp, achieved,
+                                    status, stream);
     default:
       return cudaErrorNotSupported;
   }
@@ -129,6 +132,9 @@ static cudaError_t launchImageToGround(Model &m, long n, const double *line, con
     case USGSCSM_B200_MODEL_FRAME:
       return launchFrImageToGround(m.fr, m.smCount, n, line, samp, grid, height, heightStride,
                                    prec, x, y, z, achieved, status, stream);
+    case USGSCSM_B200_MODEL_SAR:
+      return launchSarImageToGround(m.sar, m.smCount, n, line, samp, grid, height, heightStride,
+                                    prec, x, y, z, achieved, status, stream);
     default:
       return cudaErrorNotSupported;
   }
@@ -172,6 +178,9 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     } else if (m->modelName == "USGS_ASTRO_FRAME_SENSOR_MODEL") {
       m->kind = USGSCSM_B200_MODEL_FRAME;
       loadFrame(*m, st);
+    } else if (m->modelName == "USGS_ASTRO_SAR_SENSOR_MODEL") {
+      m->kind = USGSCSM_B200_MODEL_SAR;
+      loadSar(*m, st);
     } else {
       g_lastError = "unsupported model name: " + m->modelName;
       return USGSCSM_B200_EUNSUPPORTED;
@@ -232,6 +241,7 @@ int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double va
     if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER) repackLineScanner(*m);
     if (m->kind == USGSCSM_B200_MODEL_PUSH_FRAME) repackPushFrame(*m);
     if (m->kind == USGSCSM_B200_MODEL_FRAME) repackFrame(*m);
+    if (m->kind == USGSCSM_B200_MODEL_SAR) repackSar(*m);
     return USGSCSM_B200_OK;
   });
 }

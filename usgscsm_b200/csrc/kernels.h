@@ -62,6 +62,16 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream);
 
+// SAR (sar_kernels.cu)
+cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double prec, double *line,
+                                   double *samp, double *achieved, uint32_t *status,
+                                   cudaStream_t stream);
+cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const double *line,
+                                   const double *samp, const GridSpec *grid, const double *height,
+                                   int heightStride, double prec, double *x, double *y, double *z,
+                                   double *achieved, uint32_t *status, cudaStream_t stream);
+
 cudaError_t launchLsSensorPosition(const LsState &S, int n, const double *line, double *xyz,
                                    cudaStream_t stream);
 cudaError_t launchEllipsoidElevation(const Ellipsoid &ell, int n, const double *xyz, double prec,

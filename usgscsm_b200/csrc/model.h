@@ -92,6 +92,9 @@ void repackPushFrame(Model &m);  // after a parameter change: params + framelet 
 // model_fr.cu
 void loadFrame(Model &m, const class StateReader &st);
 void repackFrame(Model &m);
+// model_sar.cu
+void loadSar(Model &m, const class StateReader &st);
+void repackSar(Model &m);
 // shared readers (model_ls.cu)
 void readFocalPlane(FocalPlane &fp, const class StateReader &st, bool lineScanTypes);
 void readEllipsoid(Ellipsoid &e, const class StateReader &st);

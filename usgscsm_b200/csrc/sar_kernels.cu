@@ -1,0 +1,454 @@
+// sar_kernels.cu -- SAR groundToImage / imageToGround, one thread per point, FP64.
+//
+// Replaces UsgsAstroSarSensorModel::groundToImage (src/UsgsAstroSarSensorModel.cpp:541-593:
+// zero-Doppler time by brentRoot src/Utilities.cpp:545-622 over dopplerShift SAR:595-632,
+// slantRange SAR:634-656, slantRangeToGroundRange SAR:658-686 with polynomialRoot
+// U:771-791 over the time-interpolated range polynomial getRangeCoefficients SAR:1936-1972)
+// and ::imageToGround (SAR:775-861).  Exceptions of the scalar code (no Doppler bracket,
+// Newton failure) become USGSCSM_B200_ST_ERROR_UNKNOWN with NaN outputs (SAR:569-575).
+//
+// The ephemeris tables (positions, velocities: ~1200 nodes each for an orbital SAR image)
+// and the range-coefficient table are staged once per persistent block into shared memory.
+#include "kernels.h"
+#include "device_math.cuh"
+
+namespace ub200 {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr size_t kSarMaxStagedBytes = 100 * 1024;  // 2 resident blocks per SM
+
+struct SarTables {
+  const double *positions;
+  const double *velocities;
+  const double *scale;
+};
+
+__host__ __device__ inline size_t sarTableBytes(const SarState &S) {
+  return ((size_t)S.positions.numNodes * 3 + (size_t)S.velocities.numNodes * 3 +
+          (size_t)S.scale.numNodes * 4) *
+         sizeof(double);
+}
+
+__device__ inline SarTables stageSarTables(const SarState &S, double *smem, bool stage) {
+  SarTables t{S.positions.values, S.velocities.values, S.scale.values};
+  if (!stage) return t;
+  const int np = S.positions.numNodes * 3, nv = S.velocities.numNodes * 3,
+            ns = S.scale.numNodes * 4;
+  double *sp = smem, *sv = sp + np, *ss = sv + nv;
+  for (int i = threadIdx.x; i < np; i += blockDim.x) sp[i] = __ldg(S.positions.values + i);
+  for (int i = threadIdx.x; i < nv; i += blockDim.x) sv[i] = __ldg(S.velocities.values + i);
+  for (int i = threadIdx.x; i < ns; i += blockDim.x) ss[i] = __ldg(S.scale.values + i);
+  __syncthreads();
+  t.positions = sp;
+  t.velocities = sv;
+  t.scale = ss;
+  return t;
+}
+
+// getAdjustedSensorPosition SAR:1196-1218 and getAdjustedSensorVelocity SAR:1266-1288 with
+// adj = m_noAdjustments.  Both tables share t0 / dt; when they also have the same node
+// count the Lagrange weights are identical and evaluated once.
+UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double pos[3],
+                      double vel[3]) {
+  LagrangeWeights w;
+  bool haveW = false;
+  if (S.positions.numNodes > 1) {
+    lagrangeWeights(S.positions.numNodes, S.positions.t0, S.positions.dt, time, 8, w);
+    haveW = true;
+    double p[3];
+    lagrangeApply<3>(T.positions, w, p);
+    pos[0] = p[0] + S.params[0];
+    pos[1] = p[1] + S.params[1];
+    pos[2] = p[2] + S.params[2];
+  } else {
+    pos[0] = T.positions[0] + S.params[0];
+    pos[1] = T.positions[1] + S.params[1];
+    pos[2] = T.positions[2] + S.params[2];
+  }
+  if (S.velocities.numNodes > 1) {
+    if (!haveW || S.velocities.numNodes != S.positions.numNodes)
+      lagrangeWeights(S.velocities.numNodes, S.velocities.t0, S.velocities.dt, time, 8, w);
+    double v[3];
+    lagrangeApply<3>(T.velocities, w, v);
+    vel[0] = v[0] + S.params[3];
+    vel[1] = v[1] + S.params[4];
+    vel[2] = v[2] + S.params[5];
+  } else {
+    vel[0] = T.velocities[0] + S.params[3];
+    vel[1] = T.velocities[1] + S.params[4];
+    vel[2] = T.velocities[2] + S.params[5];
+  }
+}
+
+// The Doppler-shift function of dopplerShift SAR:603-617; also returns the slant range.
+UB_DEV double sarDoppler(const SarState &S, const SarTables &T, double time, double gx, double gy,
+                         double gz, double &slantRange) {
+  double pos[3], vel[3];
+  sarPosVel(S, T, time, pos, vel);
+  double lx = pos[0] - gx, ly = pos[1] - gy, lz = pos[2] - gz;
+  slantRange = sqrt(lx * lx + ly * ly + lz * lz);
+  return -2.0 * (lx * vel[0] + ly * vel[1] + lz * vel[2]) / (slantRange * S.wavelength);
+}
+
+// getRangeCoefficients SAR:1936-1972
+UB_DEV void sarRangeCoefficients(const SarState &S, const SarTables &T, double time, double c[4]) {
+  if (S.scale.numNodes > 1) {
+    LagrangeWeights w;
+    lagrangeWeights(S.scale.numNodes, S.scale.t0, S.scale.dt, time, 8, w);
+    lagrangeApply<4>(T.scale, w, c);
+  } else {
+    c[0] = T.scale[0];
+    c[1] = T.scale[1];
+    c[2] = T.scale[2];
+    c[3] = T.scale[3];
+  }
+}
+
+// evaluatePolynomial / evaluatePolynomialDerivative U:696-727 for 4 coefficients
+UB_DEV double poly3(const double c[4], double x) {
+  double value = c[3];
+  value *= x;
+  value += c[2];
+  value *= x;
+  value += c[1];
+  value *= x;
+  value += c[0];
+  return value;
+}
+UB_DEV double poly3Derivative(const double c[4], double x) {
+  double value = 3 * c[3];
+  value *= x;
+  value += 2 * c[2];
+  value *= x;
+  value += 1 * c[1];
+  return value;
+}
+
+// Brent's method state (brentRoot U:545-622) and the choice of the next abscissa.
+struct Brent {
+  double counterPoint, currentPoint, counterFunc, currentFunc;
+  double previousPoint, previousFunc, evenOlderPoint;
+  bool bisected;
+};
+
+UB_DEV double brentNextPoint(Brent &b, double epsilon) {
+  double nextPoint;
+  if (b.counterFunc != b.previousFunc && b.counterFunc != b.currentFunc &&
+      b.currentFunc != b.previousFunc) {
+    nextPoint = (b.counterPoint * b.currentFunc * b.previousFunc) /
+                ((b.counterFunc - b.currentFunc) * (b.counterFunc - b.previousFunc));
+    nextPoint += (b.currentPoint * b.counterFunc * b.previousFunc) /
+                 ((b.currentFunc - b.counterFunc) * (b.currentFunc - b.previousFunc));
+    nextPoint += (b.previousPoint * b.currentFunc * b.counterFunc) /
+                 ((b.previousFunc - b.counterFunc) * (b.previousFunc - b.currentFunc));
+  } else {
+    nextPoint = b.currentPoint -
+                b.currentFunc * (b.currentPoint - b.counterPoint) / (b.currentFunc - b.counterFunc);
+  }
+  if (((b.currentPoint - nextPoint) * (nextPoint - (3 * b.counterPoint + b.currentPoint) / 4) < 0) ||
+      (b.bisected &&
+       fabs(nextPoint - b.currentPoint) >= fabs(b.currentPoint - b.previousPoint) / 2) ||
+      (!b.bisected &&
+       fabs(nextPoint - b.currentPoint) >= fabs(b.previousPoint - b.evenOlderPoint) / 2) ||
+      (b.bisected && fabs(b.currentPoint - b.previousPoint) < epsilon) ||
+      (!b.bisected && fabs(b.previousPoint - b.evenOlderPoint) < epsilon)) {
+    nextPoint = (b.currentPoint + b.counterPoint) / 2;
+    b.bisected = true;
+  } else {
+    b.bisected = false;
+  }
+  b.evenOlderPoint = b.previousPoint;
+  b.previousPoint = b.currentPoint;
+  b.previousFunc = b.currentFunc;
+  return nextPoint;
+}
+
+// One point of SAR::groundToImage SAR:541-593.
+UB_DEV void sarGroundToImagePoint(const SarState &S, const SarTables &T, double gx, double gy,
+                                  double gz, double desiredPrecision, double &outLine,
+                                  double &outSamp, uint32_t &status) {
+  const double timeTolerance = S.exposureDuration * desiredPrecision / 2.0;
+  const double timePadding = S.exposureDuration * S.nLines * 0.25;
+  const double lowerBound = S.startingEphemerisTime - timePadding;
+  const double upperBound = S.endingEphemerisTime + timePadding;
+
+  // brentRoot with a single inlined copy of the function: stage 0 evaluates the lower
+  // bound, stage 1 the upper bound, stage 2 the iterates.
+  Brent b;
+  b.counterPoint = lowerBound;
+  b.currentPoint = upperBound;
+  b.counterFunc = 0.0;
+  b.currentFunc = 0.0;
+  b.previousPoint = b.previousFunc = b.evenOlderPoint = 0.0;
+  b.bisected = true;
+  int stage = 0, iteration = 0;
+  double t = lowerBound, slant = 0.0;
+  bool failed = false;
+  for (;;) {
+    double f = sarDoppler(S, T, t, gx, gy, gz, slant);
+    if (stage == 0) {
+      b.counterFunc = f;
+      t = upperBound;
+      stage = 1;
+      continue;
+    }
+    if (stage == 1) {
+      b.currentFunc = f;
+      if (b.counterFunc * b.currentFunc > 0.0) {  // throws std::invalid_argument
+        failed = true;
+        break;
+      }
+      if (fabs(b.counterFunc) < fabs(b.currentFunc)) {
+        double tp = b.counterPoint;
+        b.counterPoint = b.currentPoint;
+        b.currentPoint = tp;
+        double tf = b.counterFunc;
+        b.counterFunc = b.currentFunc;
+        b.currentFunc = tf;
+      }
+      b.previousPoint = b.counterPoint;
+      b.previousFunc = b.counterFunc;
+      b.evenOlderPoint = b.previousPoint;
+      b.bisected = true;
+      stage = 2;
+      t = brentNextPoint(b, timeTolerance);
+      continue;
+    }
+    // stage 2: f = nextFunc at nextPoint = t
+    if (f == 0) break;
+    if (b.counterFunc * f < 0) {
+      b.currentPoint = t;
+      b.currentFunc = f;
+    } else {
+      b.counterPoint = t;
+      b.counterFunc = f;
+    }
+    if (!(++iteration < 30)) {
+      status |= USGSCSM_B200_ST_ITERATION_CAP;
+      break;
+    }
+    if (!(fabs(b.counterPoint - b.currentPoint) > timeTolerance)) break;
+    t = brentNextPoint(b, timeTolerance);
+  }
+
+  if (!failed) {
+    // time = t (the last abscissa evaluated); slantRange(groundPt, time) SAR:634-656 is the
+    // norm already computed by that evaluation.
+    double time = t;
+    double c[4];
+    sarRangeCoefficients(S, T, time, c);
+    double guess = 0.5 * S.nSamples * S.scaledPixelWidth;
+    const double groundTolerance = S.scaledPixelWidth * desiredPrecision / 2.0;
+    c[0] -= slant;
+    // polynomialRoot U:771-791, maxIterations = 30
+    double root = guess;
+    double polyValue = poly3(c, root);
+    bool converged = false;
+    for (int it = 0; it < 31; it++) {
+      if (fabs(polyValue) < groundTolerance) {
+        converged = true;
+        break;
+      }
+      double polyDeriv = poly3Derivative(c, root);
+      if (fabs(polyDeriv) < 1e-15) break;  // throws
+      root -= polyValue / polyDeriv;
+      polyValue = poly3(c, root);
+    }
+    if (converged) {
+      outLine = (time - S.startingEphemerisTime) / S.exposureDuration + 0.5;
+      outSamp = root / S.scaledPixelWidth + 0.5;
+      return;
+    }
+  }
+  status |= USGSCSM_B200_ST_ERROR_UNKNOWN;
+  outLine = nan("");
+  outSamp = nan("");
+}
+
+// One point of SAR::imageToGround SAR:775-861.
+UB_DEV void sarImageToGroundPoint(const SarState &S, const SarTables &T, double line, double samp,
+                                  double height, double desiredPrecision, double &x, double &y,
+                                  double &z, double &achieved, uint32_t &status) {
+  double time = S.startingEphemerisTime + (line - 0.5) * S.exposureDuration;
+  double groundRange = (samp - 0.5) * S.scaledPixelWidth;
+  double c[4];
+  sarRangeCoefficients(S, T, time, c);
+  double slantRange = poly3(c, groundRange);
+
+  double pos[3], vel[3];
+  sarPosVel(S, T, time, pos, vel);
+  double positionMag = sqrt(pos[0] * pos[0] + pos[1] * pos[1] + pos[2] * pos[2]);
+  // vHat = normalized(velocity) = 1.0 / norm * vec  (U:899-901, 972-974)
+  double s = 1.0 / sqrt(vel[0] * vel[0] + vel[1] * vel[1] + vel[2] * vel[2]);
+  double vHat[3] = {s * vel[0], s * vel[1], s * vel[2]};
+  // tHat = normalized(rejection(position, vHat))
+  double pr = (pos[0] * vHat[0] + pos[1] * vHat[1] + pos[2] * vHat[2]) /
+              (vHat[0] * vHat[0] + vHat[1] * vHat[1] + vHat[2] * vHat[2]);
+  double rej[3] = {pos[0] - pr * vHat[0], pos[1] - pr * vHat[1], pos[2] - pr * vHat[2]};
+  s = 1.0 / sqrt(rej[0] * rej[0] + rej[1] * rej[1] + rej[2] * rej[2]);
+  double tHat[3] = {s * rej[0], s * rej[1], s * rej[2]};
+  double uHat[3] = {vHat[1] * tHat[2] - vHat[2] * tHat[1], vHat[2] * tHat[0] - vHat[0] * tHat[2],
+                    vHat[0] * tHat[1] - vHat[1] * tHat[0]};
+  double nadirComp = pos[0] * tHat[0] + pos[1] * tHat[1] + pos[2] * tHat[2];
+
+  double pointRadius = S.ell.majorAxis + height;
+  double pointHeight = 0.0;
+  double gvx = 0.0, gvy = 0.0, gvz = 0.0;
+  for (int it = 0; it < 10; it++) {
+    double radiusSqr = pointRadius * pointRadius;
+    double alpha =
+        (radiusSqr - slantRange * slantRange - positionMag * positionMag) / (2 * nadirComp);
+    double beta = sqrt(slantRange * slantRange - alpha * alpha);
+    if (S.lookDirection == 0) beta *= -1;
+    gvx = alpha * tHat[0] + beta * uHat[0] + pos[0];
+    gvy = alpha * tHat[1] + beta * uHat[1] + pos[1];
+    gvz = alpha * tHat[2] + beta * uHat[2] + pos[2];
+    pointHeight = ellipsoidElevation(gvx, gvy, gvz, S.ell, 0.001);
+    pointRadius -= (pointHeight - height);
+    if (fabs(pointHeight - height) <= desiredPrecision) break;
+  }
+  achieved = fabs(pointHeight - height);
+  x = gvx;
+  y = gvy;
+  z = gvz;
+  if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
+}
+
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    sarGroundToImageKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z, double prec,
+                           double *__restrict__ line, double *__restrict__ samp,
+                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ double smem[];
+  SarTables T = stageSarTables(S, smem, STAGE);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
+    double l, s;
+    uint32_t st = 0;
+    sarGroundToImagePoint(S, T, gx, gy, gz, prec, l, s, st);
+    if (!(isfinite(l) && isfinite(s))) st |= USGSCSM_B200_ST_NONFINITE;
+    // getValidImageRange SAR:1066-1072: (0,0) .. (nLines, nSamples)
+    if (!(l >= 0.0 && l <= 0.0 + S.nLines && s >= 0.0 && s <= 0.0 + S.nSamples))
+      st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+    __stcs(line + i, l);
+    __stcs(samp + i, s);
+    if (achieved) __stcs(achieved + i, nan(""));  // SAR groundToImage never writes achievedPrecision
+    if (status) __stcs(status + i, st);
+  }
+}
+
+template <bool STAGE, bool GRID>
+__global__ void __launch_bounds__(kThreads)
+    sarImageToGroundKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ line,
+                           const double *__restrict__ samp, GridSpec g,
+                           const double *__restrict__ height, int heightStride, double prec,
+                           double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ double smem[];
+  SarTables T = stageSarTables(S, smem, STAGE);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l, s;
+    if (GRID) {
+      long r = i / g.nSamps;
+      long c = i - r * g.nSamps;
+      l = g.line0 + (double)r * g.dline;
+      s = g.samp0 + (double)c * g.dsamp;
+    } else {
+      l = __ldcs(line + i);
+      s = __ldcs(samp + i);
+    }
+    double h = heightStride ? __ldcs(height + i) : __ldg(height);
+    double px, py, pz, a;
+    uint32_t st = 0;
+    sarImageToGroundPoint(S, T, l, s, h, prec, px, py, pz, a, st);
+    __stcs(x + i, px);
+    __stcs(y + i, py);
+    __stcs(z + i, pz);
+    if (achieved) __stcs(achieved + i, a);
+    if (status) __stcs(status + i, st);
+  }
+}
+
+LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
+  size_t bytes = sarTableBytes(S);
+  stage = bytes <= kSarMaxStagedBytes;
+  smemBytes = stage ? bytes : 0;
+  int perSm = kBlocksPerSm;
+  if (stage && smemBytes > 0) {
+    size_t fit = (size_t)(220 * 1024) / (smemBytes + 1024);
+    if (fit < (size_t)perSm) perSm = (int)(fit < 1 ? 1 : fit);
+  }
+  LaunchShape sh;
+  sh.threads = kThreads;
+  long blocksNeeded = (n + kThreads - 1) / kThreads;
+  long persistent = (long)smCount * perSm;
+  sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
+  if (sh.blocks < 1) sh.blocks = 1;
+  return sh;
+}
+
+template <class K>
+cudaError_t allowSmem(K kernel, size_t bytes) {
+  if (bytes > 48 * 1024)
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  return cudaSuccess;
+}
+
+}  // namespace
+
+cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double prec, double *line,
+                                   double *samp, double *achieved, uint32_t *status,
+                                   cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
+  if (stage) {
+    cudaError_t e = allowSmem(sarGroundToImageKernel<true>, smemBytes);
+    if (e != cudaSuccess) return e;
+    sarGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
+        S, n, x, y, z, prec, line, samp, achieved, status);
+  } else {
+    sarGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
+        S, n, x, y, z, prec, line, samp, achieved, status);
+  }
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const double *line,
+                                   const double *samp, const GridSpec *grid, const double *height,
+                                   int heightStride, double prec, double *x, double *y, double *z,
+                                   double *achieved, uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+#define UB_LAUNCH_SAR(STAGE, GRID)                                                          \
+  do {                                                                                      \
+    cudaError_t e = allowSmem(sarImageToGroundKernel<STAGE, GRID>, smemBytes);              \
+    if (e != cudaSuccess) return e;                                                         \
+    sarImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(      \
+        S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status);        \
+  } while (0)
+  if (stage && grid)
+    UB_LAUNCH_SAR(true, true);
+  else if (stage)
+    UB_LAUNCH_SAR(true, false);
+  else if (grid)
+    UB_LAUNCH_SAR(false, true);
+  else
+    UB_LAUNCH_SAR(false, false);
+#undef UB_LAUNCH_SAR
+  countLaunch();
+  return cudaGetLastError();
+}
+
+}  // namespace ub200

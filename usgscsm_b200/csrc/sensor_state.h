@@ -141,20 +141,22 @@ struct FrameState {
 struct SarState {
   int nLines;
   int nSamples;
-  int lookDirection; // 0 = LEFT, 1 = RIGHT (include/usgscsm/UsgsAstroSarSensorModel.h)
-  int numScaleTimes; // m_scaleConversionTimes.size()
+  int lookDirection;  // 0 = LEFT, 1 = RIGHT (include/usgscsm/UsgsAstroSarSensorModel.h)
+  int pad0;
   Ellipsoid ell;
   double exposureDuration;
   double scaledPixelWidth;
   double wavelength;
   double startingEphemerisTime;
-  double centerEphemerisTime;
   double endingEphemerisTime;
-  double params[6];
-  UniformTable positions;  // vlen 3
-  UniformTable velocities; // vlen 3
-  const double *scaleConversionCoefficients; // device, 4 per time
-  const double *scaleConversionTimes;        // device
+  double params[6];  // position and velocity offsets (m_currentParameterValue + 0.0)
+  // positions.numNodes = m_positions.size() / 3, velocities.numNodes = m_velocities.size() / 3
+  // (SAR:1199, 1269): a table with a single node is used as a constant.
+  UniformTable positions;   // vlen 3, order 8
+  UniformTable velocities;  // vlen 3, order 8, same t0 / dt
+  // m_scaleConversionCoefficients, 4 per node; t0 = m_scaleConversionTimes[0],
+  // dt = (m_scaleConversionTimes.back() - t0) / numNodes  (sic: /N, SAR:1944-1945)
+  UniformTable scale;       // vlen 4, order 8
 };
 
 }  // namespace ub200

@@ -369,6 +369,71 @@ def frame_state(n_lines=4096, n_samples=4096, focal_length=100.0, pixel_pitch_in
     return state_string(state)
 
 
+def sar_state(n_lines=64576, n_samples=2367, exposure=0.004704421474, pixel_width=7.5,
+              wavelength=0.12596322416750805, altitude=50000.0, near_slant=79942.38,
+              major_axis=MOON_RADIUS, minor_axis=MOON_RADIUS, look="right", n_scale_sets=20,
+              dt_ephem=0.25, seed=4, t_start=325441417.4304223, params=None, gm=4.9028e12,
+              single_node=False, as_dict=False):
+    """A SAR model state shaped like tests/data/orbitalSar.json after the reference's ISD load
+    (keys of UsgsAstroSarSensorModel::getModelState, SAR:396-438): circular orbit, `n_scale_sets`
+    cubic ground-range -> slant-range polynomials (slowly varying in time) fitted to the
+    spherical geometry, absolute ephemeris times."""
+    rng = np.random.default_rng(seed)
+    r_orbit = major_axis + altitude
+    total = n_lines * exposure
+    t_end = t_start + total
+    orb = _orbit_tables(t_start, t_end, dt_ephem, 10.0, r_orbit, gm, rng, 0.0, 1.0, pad=6)
+    # cubic slant(ground range) for a sphere of radius major_axis seen from r_orbit
+    R, r = major_axis, r_orbit
+    th0 = math.acos((R * R + r * r - near_slant ** 2) / (2 * R * r))
+    g = np.linspace(0.0, n_samples * pixel_width, 400)
+    slant = np.sqrt(R * R + r * r - 2 * R * r * np.cos(th0 + g / R))
+    base = np.polyfit(g, slant, 3)[::-1]
+    times = t_start + total * np.arange(n_scale_sets) / max(n_scale_sets - 1, 1)
+    coeffs = []
+    for k in range(n_scale_sets):
+        f = 1.0 + 2e-4 * math.sin(0.7 * k)
+        coeffs += [float(base[0] * (1.0 + 1e-8 * k)), float(base[1] * f), float(base[2] / f), float(base[3])]
+    pos, vel = orb["pos"], orb["vel"]
+    if single_node:
+        pos, vel = pos[len(pos) // 2: len(pos) // 2 + 1], vel[len(vel) // 2: len(vel) // 2 + 1]
+    p = [0.0] * 6 if params is None else [float(x) for x in params]
+    state = {
+        "m_modelName": "USGS_ASTRO_SAR_SENSOR_MODEL",
+        "m_imageIdentifier": "synthetic_sar_%d" % seed,
+        "m_sensorName": "SYNTH_MINI_RF",
+        "m_platformIdentifier": "SYNTH",
+        "m_sensorIdentifier": "SYNTH_MINI_RF",
+        "m_nLines": int(n_lines),
+        "m_nSamples": int(n_samples),
+        "m_exposureDuration": float(exposure),
+        "m_scaledPixelWidth": float(pixel_width),
+        "m_lookDirection": look,
+        "m_wavelength": float(wavelength),
+        "m_startingEphemerisTime": float(t_start),
+        "m_centerEphemerisTime": float(t_start + total / 2.0),
+        "m_endingEphemerisTime": float(t_end),
+        "m_majorAxis": float(major_axis),
+        "m_minorAxis": float(minor_axis),
+        "m_minElevation": -1000.0,
+        "m_maxElevation": 1000.0,
+        "m_dtEphem": float(dt_ephem),
+        "m_t0Ephem": float(orb["t0_ephem"]),
+        "m_scaleConversionCoefficients": coeffs,
+        "m_scaleConversionTimes": [float(t) for t in times],
+        "m_positions": [float(x) for x in pos.reshape(-1)],
+        "m_velocities": [float(x) for x in vel.reshape(-1)],
+        "m_currentParameterValue": p,
+        "m_referencePointXyz": [1.0, 0.0, 0.0],
+        "m_covariance": [0.0] * 36,
+        "m_sunPosition": [1.5e11, 0.0, 0.0],
+        "m_sunVelocity": [0.0, 0.0, 0.0],
+    }
+    if as_dict:
+        return state
+    return state_string(state)
+
+
 def state_string(state):
     """``<MODEL_NAME>\\n{json}`` as getModelState() writes it (LS:476-483)."""
     return state["m_modelName"] + "\n" + json.dumps(state)
