@@ -159,6 +159,31 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m
                                           double *z, double *achieved, uint32_t *status,
                                           void *stream);
 
+/* ---- building blocks of the per-point math, batched -------------------------------------
+ * The reference exposes these as free functions and tests them directly
+ * (tests/DistortionTests.cpp, tests/UtilitiesTests.cpp); exporting the device versions lets
+ * the same known-answer vectors be replayed on the GPU.  HOST pointers, n entries each.
+ *
+ * applyDistortion / removeDistortion: include/usgscsm/Distortion.h:20-31
+ * (src/Distortion.cpp:441-775, 208-424).  `type` is the DistortionType value
+ * (include/usgscsm/Distortion.h:10-11), `coeffs` the opticalDistCoeffs (ncoeffs <= 20).
+ * status: ST_ERROR_ALGORITHM where the reference throws, ST_DISTORTION_NOT_CONVERGED. */
+USGSCSM_B200_API int usgscsm_b200_apply_distortion(int device, int type, const double *coeffs, int ncoeffs,
+                                  double focal_length, double desired_precision, int64_t n,
+                                  const double *ux, const double *uy, double *dx, double *dy,
+                                  uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_remove_distortion(int device, int type, const double *coeffs, int ncoeffs,
+                                   double focal_length, double tolerance, int64_t n,
+                                   const double *dx, const double *dy, double *ux, double *uy,
+                                   uint32_t *status);
+/* lagrangeInterp (include/usgscsm/Utilities.h; src/Utilities.cpp:409-513) of a uniformly
+ * sampled table of `vector_length`-vectors (1..4) at n times; out is n * vector_length.
+ * Fails with USGSCSM_B200_EINVAL where the reference throws INDEX_OUT_OF_RANGE
+ * (num_time < 2). */
+USGSCSM_B200_API int usgscsm_b200_lagrange_interp(int device, int num_time, const double *values,
+                                 double start_time, double del_time, int vector_length, int order,
+                                 int64_t n, const double *times, double *out);
+
 /* Number of kernels this library has launched on the calling process so far (all models,
  * all streams).  bench.py reports the difference over its timed region as gpu_launches. */
 USGSCSM_B200_API int64_t usgscsm_b200_kernel_launches(void);

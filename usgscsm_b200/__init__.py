@@ -6,4 +6,4 @@ of the reference's plugin interface; it has no CPU implementation of the math.
 """
 from . import _capi, synth  # noqa: F401  (_capi raises ImportError when the .so is missing)
 from .plugin import (EcefCoord, Error, ImageCoord, RasterGM, UsgsAstroPlugin,  # noqa: F401
-                     Warning)
+                     Warning, applyDistortion, lagrangeInterp, removeDistortion)

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <vector>
 
 #include "../../include/usgscsm_b200.h"
 #include "model.h"
@@ -142,6 +143,9 @@ static cudaError_t launchImageToGround(Model &m, long n, const double *line, con
 
 }  // namespace ub200
 
+namespace ub200 {
+void checkDistortionCoeffs(int type, size_t n);  // model_ls.cu
+}
 using namespace ub200;
 
 extern "C" {
@@ -403,6 +407,101 @@ int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double 
     }
     for (int si = 0; si < kPipelineSlots && si < c; si++)
       UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+}  // extern "C"
+
+// ---- building blocks ------------------------------------------------------------------------
+namespace {
+struct DevArrays {  // a few device arrays freed on scope exit
+  std::vector<void *> ptrs;
+  ~DevArrays() {
+    for (void *p : ptrs) cudaFree(p);
+  }
+  template <class T>
+  T *alloc(size_t count) {
+    void *p = nullptr;
+    UB_CUDA(cudaMalloc(&p, (count ? count : 1) * sizeof(T)));
+    ptrs.push_back(p);
+    return static_cast<T *>(p);
+  }
+  template <class T>
+  T *upload(const T *host, size_t count) {
+    T *d = alloc<T>(count);
+    if (count) UB_CUDA(cudaMemcpy(d, host, count * sizeof(T), cudaMemcpyHostToDevice));
+    return d;
+  }
+};
+
+int distortionCall(bool apply, int device, int type, const double *coeffs, int ncoeffs,
+                   double focal, double precision, int64_t n, const double *inX,
+                   const double *inY, double *outX, double *outY, uint32_t *status) {
+  if (n < 0 || ncoeffs < 0 || (ncoeffs && !coeffs)) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!inX || !inY || !outX || !outY) return fail(USGSCSM_B200_EINVAL, "null array");
+  if (device < 0 || device >= deviceCount())
+    return fail(USGSCSM_B200_ENODEVICE, "no usable CUDA device with that index");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(device));
+    checkDistortionCoeffs(type, (size_t)ncoeffs);
+    FocalPlane fp{};
+    fp.distortionType = type;
+    fp.numDistCoeffs = ncoeffs;
+    for (int i = 0; i < ncoeffs; i++) fp.distCoeffs[i] = coeffs[i];
+    fp.focalLength = focal;
+    DevArrays d;
+    const double *dx = d.upload(inX, (size_t)n), *dy = d.upload(inY, (size_t)n);
+    double *ox = d.alloc<double>((size_t)n), *oy = d.alloc<double>((size_t)n);
+    uint32_t *st = status ? d.alloc<uint32_t>((size_t)n) : nullptr;
+    UB_CUDA(launchDistortion(apply, fp, precision, (long)n, dx, dy, ox, oy, st, nullptr));
+    UB_CUDA(cudaMemcpy(outX, ox, n * sizeof(double), cudaMemcpyDeviceToHost));
+    UB_CUDA(cudaMemcpy(outY, oy, n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (status) UB_CUDA(cudaMemcpy(status, st, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    return USGSCSM_B200_OK;
+  });
+}
+}  // namespace
+
+extern "C" {
+
+int usgscsm_b200_apply_distortion(int device, int type, const double *coeffs, int ncoeffs,
+                                  double focal_length, double desired_precision, int64_t n,
+                                  const double *ux, const double *uy, double *dx, double *dy,
+                                  uint32_t *status) {
+  return distortionCall(true, device, type, coeffs, ncoeffs, focal_length, desired_precision, n,
+                        ux, uy, dx, dy, status);
+}
+
+int usgscsm_b200_remove_distortion(int device, int type, const double *coeffs, int ncoeffs,
+                                   double focal_length, double tolerance, int64_t n,
+                                   const double *dx, const double *dy, double *ux, double *uy,
+                                   uint32_t *status) {
+  return distortionCall(false, device, type, coeffs, ncoeffs, focal_length, tolerance, n, dx, dy,
+                        ux, uy, status);
+}
+
+int usgscsm_b200_lagrange_interp(int device, int num_time, const double *values, double start_time,
+                                 double del_time, int vector_length, int order, int64_t n,
+                                 const double *times, double *out) {
+  if (n < 0 || !values || vector_length < 1 || vector_length > 4)
+    return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (num_time < 2)  // U:414-419 throws csm::Error(INDEX_OUT_OF_RANGE)
+    return fail(USGSCSM_B200_EINVAL, "Not enough data to interpolate");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!times || !out) return fail(USGSCSM_B200_EINVAL, "null array");
+  if (device < 0 || device >= deviceCount())
+    return fail(USGSCSM_B200_ENODEVICE, "no usable CUDA device with that index");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(device));
+    DevArrays d;
+    UniformTable tab{d.upload(values, (size_t)num_time * vector_length), num_time, order,
+                     start_time, del_time};
+    const double *dt = d.upload(times, (size_t)n);
+    double *dout = d.alloc<double>((size_t)n * vector_length);
+    UB_CUDA(launchLagrange(tab, vector_length, (long)n, dt, dout, nullptr));
+    UB_CUDA(cudaMemcpy(out, dout, n * vector_length * sizeof(double), cudaMemcpyDeviceToHost));
     return USGSCSM_B200_OK;
   });
 }

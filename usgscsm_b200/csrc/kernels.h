@@ -72,6 +72,13 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
                                    int heightStride, double prec, double *x, double *y, double *z,
                                    double *achieved, uint32_t *status, cudaStream_t stream);
 
+// building blocks (blocks_kernels.cu)
+cudaError_t launchDistortion(bool apply, const FocalPlane &fp, double precision, long n,
+                             const double *inX, const double *inY, double *outX, double *outY,
+                             uint32_t *status, cudaStream_t stream);
+cudaError_t launchLagrange(const UniformTable &tab, int vlen, long n, const double *times,
+                           double *out, cudaStream_t stream);
+
 cudaError_t launchLsSensorPosition(const LsState &S, int n, const double *line, double *xyz,
                                    cudaStream_t stream);
 cudaError_t launchEllipsoidElevation(const Ellipsoid &ell, int n, const double *xyz, double prec,

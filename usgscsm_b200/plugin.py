@@ -324,3 +324,46 @@ class UsgsAstroPlugin(object):
                         "UsgsAstroPlugin::constructModelFromState")
         check(code)
         return RasterGM(h, modelState if isinstance(modelState, str) else raw.decode("latin-1"))
+
+
+# ---- building blocks (include/usgscsm/Distortion.h, Utilities.h of the reference) ------------
+def applyDistortion(ux, uy, opticalDistCoeffs, focalLength, distortionType,
+                    desiredPrecision=1.0e-6, device=0):
+    """applyDistortion (src/Distortion.cpp:441-775) for arrays -> (dx, dy, status)."""
+    ux = _host(ux)
+    uy = _host(uy, ux.size)
+    c = _host(opticalDistCoeffs)
+    dx, dy = np.empty(ux.size), np.empty(ux.size)
+    st = np.empty(ux.size, dtype=np.uint32)
+    check(lib.usgscsm_b200_apply_distortion(device, int(distortionType), _ptr(c), c.size,
+                                            float(focalLength), float(desiredPrecision), ux.size,
+                                            _ptr(ux), _ptr(uy), _ptr(dx), _ptr(dy), _ptr(st)))
+    return dx, dy, st
+
+
+def removeDistortion(dx, dy, opticalDistCoeffs, focalLength, distortionType, tolerance=1.0e-6,
+                     device=0):
+    """removeDistortion (src/Distortion.cpp:208-424) for arrays -> (ux, uy, status)."""
+    dx = _host(dx)
+    dy = _host(dy, dx.size)
+    c = _host(opticalDistCoeffs)
+    ux, uy = np.empty(dx.size), np.empty(dx.size)
+    st = np.empty(dx.size, dtype=np.uint32)
+    check(lib.usgscsm_b200_remove_distortion(device, int(distortionType), _ptr(c), c.size,
+                                             float(focalLength), float(tolerance), dx.size,
+                                             _ptr(dx), _ptr(dy), _ptr(ux), _ptr(uy), _ptr(st)))
+    return ux, uy, st
+
+
+def lagrangeInterp(numTime, valueArray, startTime, delTime, times, vectorLength, order, device=0):
+    """lagrangeInterp (src/Utilities.cpp:409-513) at an array of times -> (n, vectorLength)."""
+    v = _host(valueArray)
+    t = _host(times)
+    out = np.empty(t.size * int(vectorLength))
+    code = lib.usgscsm_b200_lagrange_interp(device, int(numTime), _ptr(v), float(startTime),
+                                            float(delTime), int(vectorLength), int(order), t.size,
+                                            _ptr(t), _ptr(out))
+    if code == _capi.EINVAL and numTime < 2:
+        raise Error(Error.INDEX_OUT_OF_RANGE, "Not enough data to interpolate", "lagrangeInterp")
+    check(code)
+    return out.reshape(t.size, int(vectorLength))
