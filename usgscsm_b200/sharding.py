@@ -1,0 +1,89 @@
+"""Row-band sharding of whole-image batches across the GPUs of one box.
+
+Points are independent and the packed model state is a few KB to MB, so the hot path
+shards with NO exchange step: every rank (one process per GPU, torch.distributed) builds
+the model on its own device from the same state string and processes a contiguous band of
+image rows -- rows map monotonically to time (getImageTime), so a band touches a
+contiguous window of the ephemeris tables.  Unordered point lists are split into equal
+contiguous chunks.  The only collective is the optional final gather of the outputs.
+"""
+import torch
+import torch.distributed as dist
+
+
+def row_bands(n_lines, world_size):
+    """[(first_line, n_lines_in_band)] for every rank: contiguous, covering, sizes differ by
+    at most one line (the first n_lines % world_size ranks get the extra line)."""
+    if world_size < 1 or n_lines < 0:
+        raise ValueError("bad world size / line count")
+    base, extra = divmod(int(n_lines), int(world_size))
+    bands, start = [], 0
+    for r in range(world_size):
+        cnt = base + (1 if r < extra else 0)
+        bands.append((start, cnt))
+        start += cnt
+    return bands
+
+
+def band_for_rank(n_lines, rank, world_size):
+    return row_bands(n_lines, world_size)[rank]
+
+
+def chunk_for_rank(n_points, rank, world_size):
+    """(offset, count) of this rank's contiguous chunk of an n_points list."""
+    return row_bands(n_points, world_size)[rank]
+
+
+def images_for_rank(n_images, rank, world_size):
+    """Whole-image distribution for many small images (config C5): image i goes to rank
+    i % world_size."""
+    return list(range(rank, n_images, world_size))
+
+
+def gather_bands(local, n_lines, row_len, group=None):
+    """All-gather of row-band shards into the full (n_lines * row_len) array on every rank.
+    `local` holds this rank's band, row-major.  Bands may differ by one line, so shards are
+    padded to the longest band for the collective (NCCL on GPUs, gloo on CPU)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return local.reshape(-1).clone()
+    bands = row_bands(n_lines, world)
+    longest = max(c for _, c in bands) * row_len
+    rank = dist.get_rank(group)
+    if local.numel() != bands[rank][1] * row_len:
+        raise ValueError("local shard does not match this rank's band")
+    padded = torch.zeros(longest, dtype=local.dtype, device=local.device)
+    padded[:local.numel()] = local.reshape(-1)
+    parts = [torch.empty_like(padded) for _ in range(world)]
+    dist.all_gather(parts, padded, group=group)
+    return torch.cat([p[:c * row_len] for p, (_, c) in zip(parts, bands)])
+
+
+class ShardedImage(object):
+    """One image, one band per rank.  Construct on every rank with the same model state."""
+
+    def __init__(self, model_state, local_device=None, group=None):
+        import usgscsm_b200 as ub
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if local_device is None:
+            local_device = self.rank % max(torch.cuda.device_count(), 1)
+        self.model = ub.UsgsAstroPlugin(device=local_device).constructModelFromState(model_state)
+        size = self.model.getImageSize()
+        self.n_lines, self.n_samples = int(size.line), int(size.samp)
+        self.first_line, self.band_lines = band_for_rank(self.n_lines, self.rank, self.world)
+
+    def image_to_ground_band(self, height, desiredPrecision=0.001, line_offset=0.5, samp_offset=0.5):
+        """Dense-grid imageToGround of this rank's band (pixel centres); `height`: CUDA tensor
+        with 1 or band_lines * n_samples entries.  Outputs stay sharded on this rank's GPU."""
+        return self.model.imageToGroundGrid(self.first_line + line_offset, samp_offset, 1.0, 1.0,
+                                            self.band_lines, self.n_samples, height,
+                                            desiredPrecision)
+
+    def ground_to_image_chunk(self, x, y, z, desiredPrecision=0.001):
+        """groundToImage of this rank's chunk of ground points (CUDA tensors)."""
+        return self.model.groundToImageBatch(x, y, z, desiredPrecision)
+
+    def gather(self, local):
+        return gather_bands(local, self.n_lines, self.n_samples, self.group)
