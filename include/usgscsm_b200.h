@@ -184,6 +184,14 @@ USGSCSM_B200_API int usgscsm_b200_lagrange_interp(int device, int num_time, cons
                                  double start_time, double del_time, int vector_length, int order,
                                  int64_t n, const double *times, double *out);
 
+/* Self-test of the engine's division: the kernels replace a / b by divideBy(a, b, r) with a
+ * hoisted reciprocal (usgscsm_b200/csrc/device_math.cuh), which must equal the IEEE quotient
+ * bit for bit.  Compares the two on `pairs` pseudo-random operand pairs (all exponents,
+ * subnormals, infinities, NaNs, and the constant divisors the kernels use) on the GPU and
+ * returns the number of differing results (0 expected). */
+USGSCSM_B200_API int usgscsm_b200_selftest_division(int device, int64_t pairs, uint64_t seed,
+                                   uint64_t *mismatches);
+
 /* Number of kernels this library has launched on the calling process so far (all models,
  * all streams).  bench.py reports the difference over its timed region as gpu_launches. */
 USGSCSM_B200_API int64_t usgscsm_b200_kernel_launches(void);

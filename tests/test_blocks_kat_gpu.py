@@ -105,3 +105,14 @@ def test_lagrange_bit_exact_vs_reference(ref):
         for i, t in enumerate(times):
             assert L.ref_lagrange(n, vals.ctypes.data, t0, dt, float(t), vlen, order, out.ctypes.data) == 0
             assert np.array_equal(out, got[i], equal_nan=True), (n, vlen, order, t)
+
+
+def test_division_with_hoisted_reciprocal_is_ieee_division():
+    """The kernels' divideBy(a, b, refinedReciprocal(b)) against a / b on 2 * 10^9 operand pairs
+    (all exponents, subnormals, inf/NaN, the constant divisors): zero differing bit patterns."""
+    import ctypes as C
+    from usgscsm_b200 import _capi
+    bad = C.c_uint64(123)
+    for seed in (1, 20261104):
+        _capi.check(_capi.lib.usgscsm_b200_selftest_division(0, 1_000_000_000, seed, C.byref(bad)))
+        assert bad.value == 0

@@ -67,6 +67,7 @@ SIGNATURES = {
     "usgscsm_b200_lagrange_interp": (
         C.c_int, [C.c_int, C.c_int, _dp, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int64, _dp,
                   _dp]),
+    "usgscsm_b200_selftest_division": (C.c_int, [C.c_int, C.c_int64, C.c_uint64, C.POINTER(C.c_uint64)]),
     "usgscsm_b200_kernel_launches": (C.c_int64, []),
 }
 

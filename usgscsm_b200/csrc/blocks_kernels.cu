@@ -30,14 +30,52 @@ __global__ void distortionKernel(const __grid_constant__ FocalPlane fp, double p
 }
 
 template <int VLEN>
-__global__ void lagrangeKernel(UniformTable tab, long n, const double *__restrict__ times,
+__global__ void lagrangeKernel(UniformTable tab, LagrangeDivisors lag, long n, const double *__restrict__ times,
                                double *__restrict__ out) {
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     double v[VLEN];
-    lagrangeInterp<VLEN>(tab, tab.values, times[i], v);
+    lagrangeInterp<VLEN>(tab, lag, tab.values, times[i], v);
     for (int j = 0; j < VLEN; j++) out[i * VLEN + j] = v[j];
   }
+}
+
+// r[i] = refinedReciprocal(b[i]); a divisor the fast path can never accept (zero, subnormal,
+// huge, non-finite) gets NaN, which sends every division by it to the slow path.
+__global__ void reciprocalKernel(int n, const double *__restrict__ b, double *__restrict__ r) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) r[i] = refinedReciprocal(b[i]);
+}
+
+// divideBy(a, b, refinedReciprocal(b)) against a / b on pseudo-random operands over the
+// whole exponent range (every 16th pair has extreme exponents).  Counts bit mismatches.
+__device__ inline unsigned long long mix64(unsigned long long z) {
+  z += 0x9e3779b97f4a7c15ull;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return z ^ (z >> 31);
+}
+__global__ void divisionSelfTestKernel(unsigned long long seed, long perThread,
+                                       unsigned long long *mismatches) {
+  unsigned long long s = seed + ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * 0x632be59bd9b4e019ull;
+  unsigned long long bad = 0;
+  const double fixed[8] = {5040.0, 720.0, 240.0, 144.0, 120.0, 24.0, 12.0, 6.0};
+  for (long k = 0; k < perThread; k++) {
+    unsigned long long ra = mix64(s += 1), rb = mix64(s += 1);
+    double a, b;
+    if ((k & 15) == 0) {  // raw bit patterns: every exponent, subnormals, inf, NaN
+      a = __longlong_as_double((long long)ra);
+      b = __longlong_as_double((long long)rb);
+    } else {  // moderate exponents (+-2^40), full random mantissas
+      a = __longlong_as_double((long long)((ra & 0x800fffffffffffffull) | ((0x3d7ull + (ra >> 52) % 80) << 52)));
+      b = __longlong_as_double((long long)((rb & 0x800fffffffffffffull) | ((0x3d7ull + (rb >> 52) % 80) << 52)));
+      if ((k & 15) == 1) b = fixed[rb & 7];
+    }
+    double want = a / b;
+    double got = divideBy(a, b, refinedReciprocal(b));
+    if (__double_as_longlong(want) != __double_as_longlong(got) && !(want != want && got != got)) bad++;
+  }
+  if (bad) atomicAdd(mismatches, bad);
 }
 
 int gridFor(long n) {
@@ -59,16 +97,30 @@ cudaError_t launchDistortion(bool apply, const FocalPlane &fp, double precision,
   return cudaGetLastError();
 }
 
-cudaError_t launchLagrange(const UniformTable &tab, int vlen, long n, const double *times,
+cudaError_t launchLagrange(const UniformTable &tab, const LagrangeDivisors &lag, int vlen, long n, const double *times,
                            double *out, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   switch (vlen) {
-    case 1: lagrangeKernel<1><<<gridFor(n), 128, 0, stream>>>(tab, n, times, out); break;
-    case 2: lagrangeKernel<2><<<gridFor(n), 128, 0, stream>>>(tab, n, times, out); break;
-    case 3: lagrangeKernel<3><<<gridFor(n), 128, 0, stream>>>(tab, n, times, out); break;
-    case 4: lagrangeKernel<4><<<gridFor(n), 128, 0, stream>>>(tab, n, times, out); break;
+    case 1: lagrangeKernel<1><<<gridFor(n), 128, 0, stream>>>(tab, lag, n, times, out); break;
+    case 2: lagrangeKernel<2><<<gridFor(n), 128, 0, stream>>>(tab, lag, n, times, out); break;
+    case 3: lagrangeKernel<3><<<gridFor(n), 128, 0, stream>>>(tab, lag, n, times, out); break;
+    case 4: lagrangeKernel<4><<<gridFor(n), 128, 0, stream>>>(tab, lag, n, times, out); break;
     default: return cudaErrorInvalidValue;
   }
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchReciprocals(int n, const double *b, double *r, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  reciprocalKernel<<<(n + 63) / 64, 64, 0, stream>>>(n, b, r);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchDivisionSelfTest(unsigned long long seed, int blocks, long perThread,
+                                   unsigned long long *mismatches, cudaStream_t stream) {
+  divisionSelfTestKernel<<<blocks, 256, 0, stream>>>(seed, perThread, mismatches);
   countLaunch();
   return cudaGetLastError();
 }

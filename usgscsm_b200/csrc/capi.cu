@@ -451,6 +451,7 @@ int distortionCall(bool apply, int device, int type, const double *coeffs, int n
     fp.numDistCoeffs = ncoeffs;
     for (int i = 0; i < ncoeffs; i++) fp.distCoeffs[i] = coeffs[i];
     fp.focalLength = focal;
+    fp.detectorLineSumming = fp.detectorSampleSumming = 1.0;
     DevArrays d;
     const double *dx = d.upload(inX, (size_t)n), *dy = d.upload(inY, (size_t)n);
     double *ox = d.alloc<double>((size_t)n), *oy = d.alloc<double>((size_t)n);
@@ -497,11 +498,35 @@ int usgscsm_b200_lagrange_interp(int device, int num_time, const double *values,
     UB_CUDA(cudaSetDevice(device));
     DevArrays d;
     UniformTable tab{d.upload(values, (size_t)num_time * vector_length), num_time, order,
-                     start_time, del_time};
+                     start_time, del_time, 0.0};
+    fillTableSteps({&tab});
+    LagrangeDivisors lag;
+    std::vector<Divisor *> ds;
+    appendLagrangeDivisors(lag, ds);
+    fillDivisors(ds);
     const double *dt = d.upload(times, (size_t)n);
     double *dout = d.alloc<double>((size_t)n * vector_length);
-    UB_CUDA(launchLagrange(tab, vector_length, (long)n, dt, dout, nullptr));
+    UB_CUDA(launchLagrange(tab, lag, vector_length, (long)n, dt, dout, nullptr));
     UB_CUDA(cudaMemcpy(out, dout, n * vector_length * sizeof(double), cudaMemcpyDeviceToHost));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_selftest_division(int device, int64_t pairs, uint64_t seed, uint64_t *mismatches) {
+  if (!mismatches || pairs < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (device < 0 || device >= deviceCount())
+    return fail(USGSCSM_B200_ENODEVICE, "no usable CUDA device with that index");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(device));
+    DevArrays d;
+    unsigned long long *dm = d.alloc<unsigned long long>(1);
+    UB_CUDA(cudaMemset(dm, 0, sizeof(unsigned long long)));
+    const int blocks = 148 * 8;
+    long perThread = (long)((pairs + (int64_t)blocks * 256 - 1) / ((int64_t)blocks * 256));
+    UB_CUDA(launchDivisionSelfTest((unsigned long long)seed, blocks, perThread, dm, nullptr));
+    unsigned long long h = 0;
+    UB_CUDA(cudaMemcpy(&h, dm, sizeof(h), cudaMemcpyDeviceToHost));
+    *mismatches = h;
     return USGSCSM_B200_OK;
   });
 }

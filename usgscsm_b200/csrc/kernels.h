@@ -76,8 +76,11 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
 cudaError_t launchDistortion(bool apply, const FocalPlane &fp, double precision, long n,
                              const double *inX, const double *inY, double *outX, double *outY,
                              uint32_t *status, cudaStream_t stream);
-cudaError_t launchLagrange(const UniformTable &tab, int vlen, long n, const double *times,
-                           double *out, cudaStream_t stream);
+cudaError_t launchLagrange(const UniformTable &tab, const LagrangeDivisors &lag, int vlen, long n,
+                           const double *times, double *out, cudaStream_t stream);
+cudaError_t launchReciprocals(int n, const double *b, double *r, cudaStream_t stream);
+cudaError_t launchDivisionSelfTest(unsigned long long seed, int blocks, long perThread,
+                                   unsigned long long *mismatches, cudaStream_t stream);
 
 cudaError_t launchLsSensorPosition(const LsState &S, int n, const double *line, double *xyz,
                                    cudaStream_t stream);

@@ -82,8 +82,7 @@ template <bool ALWAYS_VEL>
 UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double time,
                             double pos[3], double vel[3]) {
   LagrangeWeights w;
-  lagrangeWeights(S.positions.numNodes, S.positions.t0, S.positions.dt, time,
-                  S.positions.maxOrder, w);
+  lagrangeWeights(S.positions, S.lag, time, w);
   double sensPosNom[3];
   lagrangeApply<3>(T.positions, w, sensPosNom);
   if (!ALWAYS_VEL && !S.hasAdj) {
@@ -102,7 +101,8 @@ UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double
   double radialUnitVec[3];
   double radMag = sqrt(sensPosNom[0] * sensPosNom[0] + sensPosNom[1] * sensPosNom[1] +
                        sensPosNom[2] * sensPosNom[2]);
-  for (int i = 0; i < 3; i++) radialUnitVec[i] = sensPosNom[i] / radMag;
+  double rRadMag = refinedReciprocal(radMag);
+  for (int i = 0; i < 3; i++) radialUnitVec[i] = divideBy(sensPosNom[i], radMag, rRadMag);
   double crossTrackUnitVec[3];
   crossTrackUnitVec[0] = sensPosNom[1] * sensVelNom[2] - sensPosNom[2] * sensVelNom[1];
   crossTrackUnitVec[1] = sensPosNom[2] * sensVelNom[0] - sensPosNom[0] * sensVelNom[2];
@@ -110,7 +110,9 @@ UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double
   double crossMag = sqrt(crossTrackUnitVec[0] * crossTrackUnitVec[0] +
                          crossTrackUnitVec[1] * crossTrackUnitVec[1] +
                          crossTrackUnitVec[2] * crossTrackUnitVec[2]);
-  for (int i = 0; i < 3; i++) crossTrackUnitVec[i] /= crossMag;
+  double rCrossMag = refinedReciprocal(crossMag);
+  for (int i = 0; i < 3; i++)
+    crossTrackUnitVec[i] = divideBy(crossTrackUnitVec[i], crossMag, rCrossMag);
   double inTrackUnitVec[3];
   inTrackUnitVec[0] =
       crossTrackUnitVec[1] * radialUnitVec[2] - crossTrackUnitVec[2] * radialUnitVec[1];
@@ -148,7 +150,7 @@ UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double
 UB_DEV void cameraToBodyMatrix(const LsState &S, const OrientationTables &T, double time,
                                double m[9]) {
   double q[4];
-  lagrangeInterp<4>(S.quaternions, T.quaternions, time, q);
+  lagrangeInterp<4>(S.quaternions, S.lag, T.quaternions, time, q);
   rotationFromQuaternion(q, m);
 }
 

@@ -9,6 +9,8 @@
 // attitude tables are staged once per block into shared memory when they fit, and the
 // grid is persistent (a multiple of the SM count, grid-stride over points) so that the
 // staging cost is paid once per resident block, not once per 256 points.
+#include <cstdlib>
+
 #include "kernels.h"
 #include "ls_common.cuh"
 
@@ -16,7 +18,8 @@ namespace ub200 {
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 256;         // __launch_bounds__ cap
+constexpr int kDefaultThreads = 256;  // block size used unless overridden
 
 // ---- groundToImage ---------------------------------------------------------------------
 // LS::computeProjectiveApproximation LS:2688-2736
@@ -78,7 +81,7 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const OrientationTables &T, d
     double detectorLine = fp.iTransL[0] + fp.iTransL[1] * distortedFocalX +
                           fp.iTransL[2] * distortedFocalY + fp.detectorLineOrigin -
                           fp.startingDetectorLine;
-    detectorLine /= fp.detectorLineSumming;
+    detectorLine = divideBy(detectorLine, fp.lineSumming);
     if (stage == 0) {
       lineErr0 = detectorLine;
       t1 = 0.1;
@@ -114,10 +117,10 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const OrientationTables &T, d
   double detectorSample =
       fp.iTransS[0] + fp.iTransS[1] * distortedFocalX + fp.iTransS[2] * distortedFocalY;
   double finalUpdate =
-      (detectorLine + fp.detectorLineOrigin - fp.startingDetectorLine) / fp.detectorLineSumming;
+      divideBy(detectorLine + fp.detectorLineOrigin - fp.startingDetectorLine, fp.lineSumming);
   outLine = approxLine + finalUpdate;
-  outSamp = (detectorSample + fp.detectorSampleOrigin - fp.startingDetectorSample) /
-            fp.detectorSampleSumming;
+  outSamp = divideBy(detectorSample + fp.detectorSampleOrigin - fp.startingDetectorSample,
+                     fp.sampleSumming);
   achieved = finalUpdate;
   if ((desiredPrecision > 0.0) && (fabs(finalUpdate) > desiredPrecision))
     status |= USGSCSM_B200_ST_PRECISION_NOT_MET;
@@ -266,14 +269,28 @@ __global__ void ellipsoidElevationKernel(Ellipsoid ell, int n, const double *__r
 }  // namespace
 
 // ---- launchers ---------------------------------------------------------------------------
+// Launch shape: persistent grid of smCount x blocksPerSm blocks.  The two tuning knobs can
+// be overridden from the environment for experiments (USGSCSM_B200_LS_THREADS,
+// USGSCSM_B200_LS_BLOCKS_PER_SM); the defaults are the measured best on B200.
+static int envInt(const char *name, int def) {
+  const char *v = getenv(name);
+  if (!v || !*v) return def;
+  int x = atoi(v);
+  return x > 0 ? x : def;
+}
+
 static LaunchShape shapeFor(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage,
                             int blocksPerSm) {
+  static const int threads = envInt("USGSCSM_B200_LS_THREADS", kDefaultThreads);
+  static const int perSm = envInt("USGSCSM_B200_LS_BLOCKS_PER_SM", 0);
   size_t bytes = orientationTableBytes(S, S.hasAdj != 0);
   stage = bytes <= kMaxStagedTableBytes;
   smemBytes = stage ? bytes : 0;
   LaunchShape sh;
-  sh.threads = kThreads;
-  long blocksNeeded = (n + kThreads - 1) / kThreads;
+  sh.threads = threads > kThreads ? kThreads : threads;
+  if (perSm > 0) blocksPerSm = perSm;
+  else blocksPerSm = blocksPerSm * kThreads / sh.threads;
+  long blocksNeeded = (n + sh.threads - 1) / sh.threads;
   long persistent = (long)smCount * blocksPerSm;
   sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
   if (sh.blocks < 1) sh.blocks = 1;

@@ -89,6 +89,10 @@ void repackLineScanner(Model &m);  // after a parameter / projective-seed change
 // model_pf.cu
 void loadPushFrame(Model &m, const class StateReader &st);
 void repackPushFrame(Model &m);  // after a parameter change: params + framelet orientations
+// divisors.cu: reciprocals of constant divisors, evaluated on the device
+void fillDivisors(const std::vector<Divisor *> &divisors);
+void appendLagrangeDivisors(LagrangeDivisors &L, std::vector<Divisor *> &out);
+void fillTableSteps(const std::vector<UniformTable *> &tables);
 // model_fr.cu
 void loadFrame(Model &m, const class StateReader &st);
 void repackFrame(Model &m);

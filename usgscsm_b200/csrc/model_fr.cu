@@ -86,6 +86,9 @@ void loadFrame(Model &m, const StateReader &st) {
   fp.p12 = -fp.iTransS[1] / determinant;
   fp.p21 = -fp.iTransL[2] / determinant;
   fp.p22 = fp.iTransL[1] / determinant;
+  fp.lineSumming.b = fp.detectorLineSumming;
+  fp.sampleSumming.b = fp.detectorSampleSumming;
+  fillDivisors({&fp.lineSumming, &fp.sampleSumming});
 
   m.lineJitter = st.getVecDouble("m_lineJitter", {});
   m.sampleJitter = st.getVecDouble("m_sampleJitter", {});

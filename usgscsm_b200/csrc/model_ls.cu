@@ -168,6 +168,9 @@ void readFocalPlane(FocalPlane &fp, const StateReader &st, bool lineScanTypes) {
   fp.detectorSampleOrigin = st.getDouble("m_detectorSampleOrigin");
   fp.detectorLineOrigin = st.getDouble("m_detectorLineOrigin");
   fillFocalPlaneInverse(fp);
+  fp.lineSumming.b = fp.detectorLineSumming;
+  fp.sampleSumming.b = fp.detectorSampleSumming;
+  fillDivisors({&fp.lineSumming, &fp.sampleSumming});
 }
 
 void readEllipsoid(Ellipsoid &e, const StateReader &st) {
@@ -209,6 +212,10 @@ void readOrientation(Model &m, const StateReader &st) {
   S.velocities = UniformTable{m.upload(m.velocities), numPositions / 3, nOrder, t0Ephem, dtEphem};
   S.quaternions =
       UniformTable{m.upload(m.quaternions), m.numQuaternionDoubles / 4, nOrderQuat, t0Quat, dtQuat};
+  fillTableSteps({&S.positions, &S.velocities, &S.quaternions});
+  std::vector<Divisor *> ds;
+  appendLagrangeDivisors(S.lag, ds);
+  fillDivisors(ds);
 }
 
 void repackLineScanner(Model &m) {

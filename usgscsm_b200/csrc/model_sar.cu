@@ -50,6 +50,14 @@ void loadSar(Model &m, const StateReader &st) {
   const int numSets = (int)(m.scaleCoeffs.size() / 4);
   const double dtScale = (m.scaleTimes.back() - m.scaleTimes[0]) / (m.scaleCoeffs.size() / 4);
   S.scale = UniformTable{m.upload(m.scaleCoeffs), numSets, 8, m.scaleTimes[0], dtScale};
+  fillTableSteps({&S.positions, &S.velocities, &S.scale});
+  std::vector<Divisor *> ds;
+  appendLagrangeDivisors(S.lag, ds);
+  S.exposure.b = S.exposureDuration;
+  S.pixelWidth.b = S.scaledPixelWidth;
+  ds.push_back(&S.exposure);
+  ds.push_back(&S.pixelWidth);
+  fillDivisors(ds);
   repackSar(m);
 }
 

@@ -168,7 +168,7 @@ UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
     viewFromOrientation(S, o, gx, gy, gz, focalX, focalY);
     double detectorLine = fp.iTransL[0] + fp.iTransL[1] * focalX + fp.iTransL[2] * focalY +
                           fp.detectorLineOrigin - fp.startingDetectorLine;
-    detectorLine /= fp.detectorLineSumming;
+    detectorLine = divideBy(detectorLine, fp.lineSumming);
     detectorLine -= S.halfOverlap;
     double distance = detectorLine - summedFrameletHeight / 2.0;
     if (stage == 0) {
@@ -210,13 +210,13 @@ UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
       fp.iTransL[0] + fp.iTransL[1] * distortedFocalX + fp.iTransL[2] * distortedFocalY;
   double detectorSample =
       fp.iTransS[0] + fp.iTransS[1] * distortedFocalX + fp.iTransS[2] * distortedFocalY;
-  double line = (detectorLine + fp.detectorLineOrigin - fp.startingDetectorLine) /
-                fp.detectorLineSumming;
+  double line =
+      divideBy(detectorLine + fp.detectorLineOrigin - fp.startingDetectorLine, fp.lineSumming);
   line += endFramelet * summedFrameletHeight;
   line -= S.halfOverlap;
   outLine = line;
-  outSamp = (detectorSample + fp.detectorSampleOrigin - fp.startingDetectorSample) /
-            fp.detectorSampleSumming;
+  outSamp = divideBy(detectorSample + fp.detectorSampleOrigin - fp.startingDetectorSample,
+                     fp.sampleSumming);
   achieved = desiredPrecision;  // PF:769-771
 }
 

@@ -55,7 +55,7 @@ UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double
   LagrangeWeights w;
   bool haveW = false;
   if (S.positions.numNodes > 1) {
-    lagrangeWeights(S.positions.numNodes, S.positions.t0, S.positions.dt, time, 8, w);
+    lagrangeWeights(S.positions, S.lag, time, w);
     haveW = true;
     double p[3];
     lagrangeApply<3>(T.positions, w, p);
@@ -69,7 +69,7 @@ UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double
   }
   if (S.velocities.numNodes > 1) {
     if (!haveW || S.velocities.numNodes != S.positions.numNodes)
-      lagrangeWeights(S.velocities.numNodes, S.velocities.t0, S.velocities.dt, time, 8, w);
+      lagrangeWeights(S.velocities, S.lag, time, w);
     double v[3];
     lagrangeApply<3>(T.velocities, w, v);
     vel[0] = v[0] + S.params[3];
@@ -96,7 +96,7 @@ UB_DEV double sarDoppler(const SarState &S, const SarTables &T, double time, dou
 UB_DEV void sarRangeCoefficients(const SarState &S, const SarTables &T, double time, double c[4]) {
   if (S.scale.numNodes > 1) {
     LagrangeWeights w;
-    lagrangeWeights(S.scale.numNodes, S.scale.t0, S.scale.dt, time, 8, w);
+    lagrangeWeights(S.scale, S.lag, time, w);
     lagrangeApply<4>(T.scale, w, c);
   } else {
     c[0] = T.scale[0];
@@ -257,8 +257,8 @@ UB_DEV void sarGroundToImagePoint(const SarState &S, const SarTables &T, double 
       polyValue = poly3(c, root);
     }
     if (converged) {
-      outLine = (time - S.startingEphemerisTime) / S.exposureDuration + 0.5;
-      outSamp = root / S.scaledPixelWidth + 0.5;
+      outLine = divideBy(time - S.startingEphemerisTime, S.exposure) + 0.5;
+      outSamp = divideBy(root, S.pixelWidth) + 0.5;
       return;
     }
   }

@@ -35,6 +35,21 @@ enum DistortionKind : int {
 
 constexpr int kMaxDistCoeffs = 20;
 
+// A divisor that is constant for a launch, with the reciprocal the compiler's own IEEE
+// division would derive from it (device_math.cuh, refinedReciprocal), evaluated once per
+// model by a set-up kernel.  divideBy(a, d) == a / d.b bit for bit, at 3 FP64 operations.
+struct Divisor {
+  double b;
+  double r;
+};
+
+// The factorial constants of the Lagrange weights (src/Utilities.cpp:455-505).
+struct LagrangeDivisors {
+  Divisor d5040, d720, d240, d144;  // order 8
+  Divisor d120, d24, d12;           // order 6
+  Divisor d6;                       // order 4 (the other order-4 divisor, 2.0, is a * 0.5)
+};
+
 // Focal-plane <-> detector affine, shared by all optical models.
 struct FocalPlane {
   double iTransS[3];
@@ -54,6 +69,8 @@ struct FocalPlane {
   // exact expressions of computeDistortedFocalPlaneCoordinates (src/Utilities.cpp:143-147;
   // IEEE division is deterministic, so this equals the per-call value bit for bit).
   double p11, p12, p21, p22;
+  Divisor lineSumming;    // detectorLineSumming
+  Divisor sampleSumming;  // detectorSampleSumming
 };
 
 // Ellipsoid constants of computeEllipsoidElevation (src/Utilities.cpp:825-826), evaluated
@@ -72,11 +89,13 @@ struct UniformTable {
   int maxOrder;  // i_order passed by the model (8, or 4: LS:2142-2145, LS:2494-2495)
   double t0;
   double dt;
+  double rdt;  // refinedReciprocal(dt)
 };
 
 // Line-scan and push-frame models share the time-dependent exterior orientation.
 struct LsState {
   FocalPlane fp;
+  LagrangeDivisors lag;
   int nLines;
   int nSamples;
   int numIntTimes;        // m_intTimeLines.size()
@@ -157,6 +176,9 @@ struct SarState {
   // m_scaleConversionCoefficients, 4 per node; t0 = m_scaleConversionTimes[0],
   // dt = (m_scaleConversionTimes.back() - t0) / numNodes  (sic: /N, SAR:1944-1945)
   UniformTable scale;       // vlen 4, order 8
+  LagrangeDivisors lag;
+  Divisor exposure;    // exposureDuration
+  Divisor pixelWidth;  // scaledPixelWidth
 };
 
 }  // namespace ub200
