@@ -19,6 +19,7 @@ namespace ub200 {
 namespace {
 
 constexpr int kThreads = 256;         // __launch_bounds__ cap
+constexpr int kDefaultMinBlocks = 4;
 constexpr int kDefaultThreads = 256;  // block size used unless overridden
 
 // ---- groundToImage ---------------------------------------------------------------------
@@ -135,8 +136,10 @@ UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamp
   return st;
 }
 
-template <bool STAGE>
-__global__ void __launch_bounds__(kThreads)
+// MINB = resident blocks of 256 threads per SM the register allocation is held to
+// (2: 96+ registers, 3: 80, 4: 64).
+template <bool STAGE, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
     lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
@@ -304,17 +307,26 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   if (n <= 0) return cudaSuccess;
   size_t smemBytes;
   bool stage;
-  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kBlocksPerSm);
+  static const int minb = envInt("USGSCSM_B200_LS_MINB", kDefaultMinBlocks);
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, minb);
+#define UB_LAUNCH_G2I(STAGE, MINB)                                                            \
+  do {                                                                                        \
+    if (smemBytes > 48 * 1024)                                                                \
+      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, MINB>,                                \
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
+    lsGroundToImageKernel<STAGE, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(         \
+        S, n, x, y, z, prec, line, samp, achieved, status);                                   \
+  } while (0)
   if (stage) {
-    if (smemBytes > 48 * 1024)
-      cudaFuncSetAttribute(lsGroundToImageKernel<true>,
-                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-    lsGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status);
+    if (minb >= 4) UB_LAUNCH_G2I(true, 4);
+    else if (minb == 3) UB_LAUNCH_G2I(true, 3);
+    else UB_LAUNCH_G2I(true, 2);
   } else {
-    lsGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status);
+    if (minb >= 4) UB_LAUNCH_G2I(false, 4);
+    else if (minb == 3) UB_LAUNCH_G2I(false, 3);
+    else UB_LAUNCH_G2I(false, 2);
   }
+#undef UB_LAUNCH_G2I
   countLaunch();
   return cudaGetLastError();
 }
