@@ -172,6 +172,15 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     cudaDeviceProp prop;
     UB_CUDA(cudaGetDeviceProperties(&prop, device));
     m->smCount = prop.multiProcessorCount;
+    {
+      // Stream-ordered scratch (dense-grid row / column tables) comes from the device's default
+      // memory pool; keep freed blocks cached instead of returning them to the driver at every
+      // synchronisation (the default threshold of 0 makes each cudaMallocAsync a driver call).
+      cudaMemPool_t pool;
+      UB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+      uint64_t threshold = ~0ull;
+      UB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+    }
     m->modelName = st.getString("m_modelName");
     if (m->modelName == "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL") {
       m->kind = USGSCSM_B200_MODEL_LINE_SCANNER;

@@ -198,6 +198,99 @@ UB_DEV void lsImageToGroundPoint(const LsState &S, const OrientationTables &T, d
   if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
 }
 
+// ---- dense-grid imageToGround with row / column tables -------------------------------------
+// On a dense grid everything the reference recomputes per pixel from the LINE alone (image
+// time, Lagrange position, Lagrange quaternion, rotation matrix, attitude correction) is
+// shared by a whole image row, and everything it recomputes from the SAMPLE alone (focal
+// plane affine, distortion removal, unit look vector) by a whole column.  A set-up kernel
+// evaluates both once per row / column with the per-point device functions (same arithmetic
+// => same bits); the per-pixel kernel is left with the two rotations, the ellipsoid
+// intersection and the elevation iteration.
+constexpr int kRowDoubles = 21;  // pos[3], camToBody[9], attCorr[9]
+constexpr int kColDoubles = 4;   // cameraLook[3], status bits of removeDistortion
+
+__global__ void lsGridTablesKernel(const __grid_constant__ LsState S, GridSpec g, long nRows,
+                                   long nCols, double *__restrict__ rowTab,
+                                   double *__restrict__ colTab) {
+  long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  if (k < nRows) {
+    double line = g.line0 + (double)k * g.dline;
+    double time = lsImageTime(S, line);
+    double pos[3], vel[3], m[9], a[9];
+    adjSensorPosVel<false>(S, T, time, pos, vel);
+    cameraToBodyMatrix(S, T, time, m);
+    for (int i = 0; i < 9; i++) a[i] = 0.0;
+    if (S.hasAttAdj) attitudeCorrection(S, time, a);
+    double *e = rowTab + k * kRowDoubles;
+    for (int i = 0; i < 3; i++) e[i] = pos[i];
+    for (int i = 0; i < 9; i++) e[3 + i] = m[i];
+    for (int i = 0; i < 9; i++) e[12 + i] = a[i];
+  } else if (k < nRows + nCols) {
+    long c = k - nRows;
+    double sample = g.samp0 + (double)c * g.dsamp;
+    uint32_t st = 0;
+    double dx, dy, ux, uy, look[3];
+    distortedFocalPlaneCoordinates(0.0, sample, S.fp, dx, dy);
+    removeDistortion(dx, dy, ux, uy, S.fp, 1.0E-6, st);
+    cameraLookVector(ux, uy, S.fp.zDirection, S.fp.focalLength * (1 - param(S, 15) / S.halfSwath),
+                     look);
+    double *e = colTab + c * kColDoubles;
+    e[0] = look[0];
+    e[1] = look[1];
+    e[2] = look[2];
+    e[3] = (double)st;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 3)
+    lsImageToGroundGridKernel(const __grid_constant__ LsState S, long n, long nSamps,
+                              const double *__restrict__ rowTab, const double *__restrict__ colTab,
+                              const double *__restrict__ height, int heightStride, double prec,
+                              double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                              double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    long r = i / nSamps;
+    long c = i - r * nSamps;
+    const double *re = rowTab + r * kRowDoubles;
+    const double *ce = colTab + c * kColDoubles;
+    double h = heightStride ? __ldcs(height + i) : __ldg(height);
+    double cameraLook[3] = {__ldg(ce), __ldg(ce + 1), __ldg(ce + 2)};
+    uint32_t st = (uint32_t)__ldg(ce + 3);
+    double pos[3] = {__ldg(re), __ldg(re + 1), __ldg(re + 2)};
+    double m[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) m[k] = __ldg(re + 3 + k);
+    double corrected[3];
+    if (S.hasAttAdj) {
+      double a[9];
+#pragma unroll
+      for (int k = 0; k < 9; k++) a[k] = __ldg(re + 12 + k);
+      matVec(a, cameraLook, corrected);
+    } else {
+      corrected[0] = cameraLook[0];
+      corrected[1] = cameraLook[1];
+      corrected[2] = cameraLook[2];
+    }
+    double bodyLook[3];
+    matVec(m, corrected, bodyLook);
+    double px, py, pz, ach;
+    lsEllipsoidIntersect(S.ell, h, pos, bodyLook, prec, px, py, pz, ach, st);
+    if ((prec > 0.0) && (ach > prec)) st |= USGSCSM_B200_ST_PRECISION_NOT_MET;
+    if (st & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+      st = USGSCSM_B200_ST_ERROR_ALGORITHM;
+      px = py = pz = ach = nan("");
+    }
+    if (!finite3(px, py, pz)) st |= USGSCSM_B200_ST_NONFINITE;
+    __stcs(x + i, px);
+    __stcs(y + i, py);
+    __stcs(z + i, pz);
+    if (achieved) __stcs(achieved + i, ach);
+    if (status) __stcs(status + i, st);
+  }
+}
+
 // GRID = true: pixel coordinates generated from the point index (dense grid);
 // GRID = false: explicit (line, samp) arrays.
 template <bool STAGE, bool GRID>
@@ -336,6 +429,27 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
+  static const int useTables = envInt("USGSCSM_B200_LS_GRID_TABLES", 1);
+  if (grid && grid->nSamps > 0 && n % grid->nSamps == 0 && useTables == 1) {
+    // row / column tables in stream-ordered scratch, then the per-pixel kernel
+    const long nCols = grid->nSamps, nRows = n / nCols;
+    double *scratch = nullptr;
+    cudaError_t e = cudaMallocAsync(&scratch, (nRows * kRowDoubles + nCols * kColDoubles) * sizeof(double), stream);
+    if (e != cudaSuccess) return e;
+    double *rowTab = scratch, *colTab = scratch + nRows * kRowDoubles;
+    long items = nRows + nCols;
+    lsGridTablesKernel<<<(unsigned)((items + 127) / 128), 128, 0, stream>>>(S, *grid, nRows, nCols, rowTab, colTab);
+    countLaunch();
+    long blocksNeeded = (n + kThreads - 1) / kThreads;
+    long persistent = (long)smCount * 3;
+    int blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
+    lsImageToGroundGridKernel<<<blocks, kThreads, 0, stream>>>(S, n, nCols, rowTab, colTab, height, heightStride,
+                                                              prec, x, y, z, achieved, status);
+    countLaunch();
+    e = cudaGetLastError();
+    cudaError_t e2 = cudaFreeAsync(scratch, stream);
+    return e != cudaSuccess ? e : e2;
+  }
   size_t smemBytes;
   bool stage;
   LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kBlocksPerSm);
