@@ -31,6 +31,10 @@ PREC = 0.001
 G2I_BYTES_PER_POINT = 24 + 16 + 4
 # dense-grid imageToGround: height in; x,y,z + status out
 I2G_BYTES_PER_POINT = 8 + 24 + 4
+# algorithmic FP64 flops (SURVEY.md §8d counting convention): per evaluation of the detector
+# view on the no-adjustment path with LRO-NAC distortion, and per point outside the loop
+FLOPS_PER_EVALUATION = 450.0
+FLOPS_FIXED = 40.0
 
 
 def parse_args():
@@ -43,6 +47,8 @@ def parse_args():
                     help="lines per GPU (default: the full C2 image)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-others", action="store_true",
+                    help="skip the push-frame / frame / SAR side measurements (configs C3, C4)")
     return ap.parse_args()
 
 
@@ -295,7 +301,10 @@ def run_b200(args):
     # correctness of what was just timed: the round trip must close and no flag may be set
     err = max(float((out_line.view(lines, N_SAMPLES) - (torch.arange(lines, device=dev, dtype=torch.float64) + line0)[:, None]).abs().max()),
               float((out_samp.view(lines, N_SAMPLES) - cols[None, :]).abs().max()))
-    flags = int((st_i != 0).sum().item()) + int((st_g != 0).sum().item())
+    ev_mask = _capi.ST_EVALS_MASK
+    flags = int(((st_i & ~ev_mask) != 0).sum().item()) + int(((st_g & ~ev_mask) != 0).sum().item())
+    # evaluations of the detector view per point, counted by the kernel itself (status bits 16-23)
+    mean_evals = float(((st_i >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean().item())
 
     # imageToGround beside it
     for _ in range(args.warmup):
@@ -305,6 +314,15 @@ def run_b200(args):
 
     peak, peak_src = peak_hbm()
     achieved = G2I_BYTES_PER_POINT * n / (kern_ms * 1e-3) / 1e9
+    # FP64 roofline: algorithmic flops per point = 450 per detector-view
+    # evaluation x measured evaluations + 40; peak = 64 FP64 FMA lanes per SM x 2 flop x SMs x
+    # the SM clock sampled under load (ncu: sm__sass_thread_inst_executed_op_dfma_pred_on
+    # peak_sustained = 64 per SM per cycle).
+    props = torch.cuda.get_device_properties(dev)
+    sm_mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0
+    fp64_peak_tflops = 64 * 2 * props.multi_processor_count * sm_mhz * 1e6 / 1e12
+    flops_per_point = FLOPS_PER_EVALUATION * mean_evals + FLOPS_FIXED
+    fp64_achieved = flops_per_point * n / (kern_ms * 1e-3) / 1e12
     result = {
         "metric": METRIC, "value": value, "unit": "Mpoints/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
@@ -315,7 +333,16 @@ def run_b200(args):
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "kernel": "lsGroundToImageKernel", "kernel_ms": kern_ms,
                      "bytes_per_point": G2I_BYTES_PER_POINT,
-                     "note": "FP64-pipe bound, not HBM bound: see DESIGN.md"},
+                     "note": "the kernel is FP64-pipe bound, not HBM bound (DESIGN.md §4): fp64 "
+                             "below is the roofline that binds",
+                     "fp64": {"bound": "fp64", "achieved": fp64_achieved, "peak": fp64_peak_tflops,
+                              "unit": "TFLOP/s", "frac": fp64_achieved / fp64_peak_tflops,
+                              "flops_per_point": flops_per_point,
+                              "evaluations_per_point": mean_evals,
+                              "peak_source": "64 DFMA lanes/SM/clk x 2 x %d SMs x %.0f MHz (FMA "
+                                             "counted as 2; the reference's arithmetic has no "
+                                             "FMAs, so 0.5 is the ceiling for identical "
+                                             "rounding)" % (props.multi_processor_count, sm_mhz)}},
         "image_to_ground": {"value": i2g_value, "unit": "Mpoints/s", "ms_per_step": i2g_total_ms / args.steps,
                             "kernel_ms": i2g_kern_ms,
                             "hbm_gbs": I2G_BYTES_PER_POINT * n / (i2g_kern_ms * 1e-3) / 1e9},
@@ -330,10 +357,68 @@ def run_b200(args):
             v, cores, kind, desc, _ = cpu_reference_rate(state, lines, 15.0, proj=model.lsDerived()[5:19])
             result["cpu_baseline"] = {"value": v, "unit": "Mpoints/s", "cores": cores, "kind": kind,
                                       "sample": desc + ", groundToImage, OpenMP over points"}
+    if rank == 0 and world == 1 and not args.no_others:
+        result["other_models"] = other_models(dev)
     if rank == 0:
         print(json.dumps(result))
     if world > 1:
         dist.destroy_process_group()
+
+
+def other_models(dev):
+    """Side measurements (not the headline): dense-grid imageToGround at synthetic-DEM heights
+    then groundToImage of the result for the push-frame and frame models (config C3,
+    4096 x 4096) and the SAR model (config C4 shape, 64576 x 2367 = 152.9 M points), device
+    resident, CUDA events, mean of 3 launches after 1 warm-up."""
+    import numpy as np
+    import torch
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import _capi, synth
+    out = {}
+    cases = [
+        ("pushframe_radial_4096x4096", synth.pushframe_state(n_framelets=256, framelet_height=16, n_samples=4096)),
+        ("frame_radial_4096x4096", synth.frame_state(n_lines=4096, n_samples=4096)),
+        ("frame_transverse_4096x4096", synth.frame_state(
+            n_lines=4096, n_samples=4096, distortion_type=synth.TRANSVERSE,
+            dist_coeffs=(0.0, 1.0, 0.0, 1e-6, 2e-6, -1e-6, 1e-8, 0.0, 2e-8, 0.0,
+                         0.0, 0.0, 1.0, -1e-6, 1e-6, 2e-6, 0.0, 1e-8, 0.0, -2e-8))),
+        ("sar_orbital_64576x2367", synth.sar_state()),
+    ]
+    for name, state in cases:
+        gm = ub.UsgsAstroPlugin(device=dev.index or 0).constructModelFromState(state)
+        sz = gm.getImageSize()
+        nl, ns = int(sz.line), int(sz.samp)
+        n = nl * ns
+        rows = torch.arange(nl, device=dev, dtype=torch.float64) + 0.5
+        cols = torch.arange(ns, device=dev, dtype=torch.float64) + 0.5
+        h = (500.0 * torch.sin(2 * np.pi * rows / 4096.0)[:, None] *
+             torch.cos(2 * np.pi * cols / 1024.0)[None, :]).reshape(-1).contiguous()
+        res = {}
+
+        def timed(fn):
+            fn()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(3):
+                r = fn()
+            b.record()
+            torch.cuda.synchronize()
+            return r, a.elapsed_time(b) / 3.0
+
+        (x, y, z, _, st), ms = timed(lambda: gm.imageToGroundGrid(0.5, 0.5, 1.0, 1.0, nl, ns, h, PREC))
+        res["image_to_ground_mpts"] = n / ms / 1e3
+        (l, s, _, st2), ms2 = timed(lambda: gm.groundToImageBatch(x, y, z, PREC, achieved=False))
+        res["ground_to_image_mpts"] = n / ms2 / 1e3
+        res["points"] = n
+        res["round_trip_max_line_px"] = float((l.view(nl, ns) - rows[:, None]).abs().max())
+        res["round_trip_max_samp_px"] = float((s.view(nl, ns) - cols[None, :]).abs().max())
+        res["points_with_flags"] = int(((st & ~_capi.ST_EVALS_MASK) != 0).sum()) + int(((st2 & ~_capi.ST_EVALS_MASK) != 0).sum())
+        res["evaluations_per_point"] = float(((st2 >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean())
+        out[name] = res
+        del gm, x, y, z, l, s, st, st2, h
+        torch.cuda.empty_cache()
+    return out
 
 
 def e2e(args, model, x, y, z, n, world, barrier, max_over_ranks):

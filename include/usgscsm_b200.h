@@ -66,6 +66,12 @@ extern "C" {
 #define USGSCSM_B200_ST_NONFINITE (1u << 7)         /* an output coordinate is NaN/Inf           */
 #define USGSCSM_B200_ST_OUT_OF_IMAGE (1u << 8)      /* g2i result outside getValidImageRange()   */
 #define USGSCSM_B200_ST_ERROR_OTHER (1u << 9)
+/* Bits 16-23 (diagnostic): how many times the root search of groundToImage evaluated its
+ * function for this point (line-scan: detector views of the secant search; push-frame: frame
+ * distances; SAR: Doppler evaluations of Brent's method).  bench.py derives the algorithmic
+ * flop count of a pass from it. */
+#define USGSCSM_B200_ST_EVALS_SHIFT 16
+#define USGSCSM_B200_ST_EVALS_MASK (0xffu << USGSCSM_B200_ST_EVALS_SHIFT)
 /* the bits the reference itself makes observable (compared bit-exactly in the tests) */
 #define USGSCSM_B200_ST_REFERENCE_MASK \
   (USGSCSM_B200_ST_NO_INTERSECTION | USGSCSM_B200_ST_PRECISION_NOT_MET | \

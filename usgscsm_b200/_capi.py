@@ -25,6 +25,8 @@ ST_ERROR_UNKNOWN = 1 << 6
 ST_NONFINITE = 1 << 7
 ST_OUT_OF_IMAGE = 1 << 8
 ST_ERROR_OTHER = 1 << 9
+ST_EVALS_SHIFT = 16
+ST_EVALS_MASK = 0xff << 16
 ST_REFERENCE_MASK = (ST_NO_INTERSECTION | ST_PRECISION_NOT_MET | ST_ERROR_ALGORITHM |
                      ST_ERROR_UNKNOWN | ST_NONFINITE | ST_OUT_OF_IMAGE | ST_ERROR_OTHER)
 

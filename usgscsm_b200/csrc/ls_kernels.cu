@@ -73,7 +73,9 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const OrientationTables &T, d
   double focalX, focalY;
   uint32_t distStatus;
   int stage = 0;  // 0: residual at t = 0; 1: residual at t1 (0.1, then secant iterates)
+  uint32_t evals = 0;
   for (;;) {
+    evals++;
     double timei = lsImageTime(S, approxLine + t1);
     detectorView<ALWAYS_VEL>(S, T, timei, gx, gy, gz, focalX, focalY);
     double distortedFocalX, distortedFocalY;
@@ -106,6 +108,7 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const OrientationTables &T, d
     t1 = t2;
   }
 
+  status |= evals << USGSCSM_B200_ST_EVALS_SHIFT;
   approxLine += t1;
   // Final projection: same focal-plane point, distortion at the caller's precision.
   double distortedFocalX, distortedFocalY;

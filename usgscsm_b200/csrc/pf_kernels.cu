@@ -159,7 +159,9 @@ UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
   // Evaluation order of the reference: calcFrameDistance(0), calcFrameDistance(n - 1), then
   // one per secant step.  stage 0/1 are the two seeds.
   int stage = 0;
+  uint32_t evals = 0;
   for (;;) {
+    evals++;
     // calcFrameDistance PF:2496-2521 at endFramelet
     double centerLine = (endFramelet + 0.5) * summedFrameletHeight;
     viewFramelet = pfTimeFramelet(S, centerLine);
@@ -198,6 +200,7 @@ UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
 
   // getImageTime(ImageCoord(0.5 + summedFrameletHeight * endFramelet, 0.0)) + computeDetectorView:
   // the same framelet time as the last distance evaluation, hence the same focal-plane point.
+  status |= evals << USGSCSM_B200_ST_EVALS_SHIFT;
   int finalFramelet = pfTimeFramelet(S, 0.5 + summedFrameletHeight * endFramelet);
   if (finalFramelet != viewFramelet) {
     Orientation o;

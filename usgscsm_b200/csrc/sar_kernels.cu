@@ -186,7 +186,9 @@ UB_DEV void sarGroundToImagePoint(const SarState &S, const SarTables &T, double 
   int stage = 0, iteration = 0;
   double t = lowerBound, slant = 0.0;
   bool failed = false;
+  uint32_t evals = 0;
   for (;;) {
+    evals++;
     double f = sarDoppler(S, T, t, gx, gy, gz, slant);
     if (stage == 0) {
       b.counterFunc = f;
@@ -233,6 +235,7 @@ UB_DEV void sarGroundToImagePoint(const SarState &S, const SarTables &T, double 
     t = brentNextPoint(b, timeTolerance);
   }
 
+  status |= evals << USGSCSM_B200_ST_EVALS_SHIFT;
   if (!failed) {
     // time = t (the last abscissa evaluated); slantRange(groundPt, time) SAR:634-656 is the
     // norm already computed by that evaluation.
