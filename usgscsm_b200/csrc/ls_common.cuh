@@ -8,42 +8,65 @@
 
 namespace ub200 {
 
-// Where the kernels read the ephemeris / attitude tables from: the device pointers of the
-// packed state, or a copy the block staged into shared memory.
+// Where the kernels read the ephemeris / attitude tables from: the device arrays of the
+// packed state (rows of 3 / 4 doubles), or a copy the block staged into shared memory as
+// rows of 4 doubles on 16-byte boundaries (128-bit loads).
 struct OrientationTables {
+  static constexpr bool kPadded = false;
+  const double *positions;
+  const double *velocities;
+  const double *quaternions;
+};
+struct StagedTables {
+  static constexpr bool kPadded = true;
   const double *positions;
   const double *velocities;
   const double *quaternions;
 };
 
+template <int VLEN, class TAB>
+UB_DEV void tableApply(const TAB &, const double *table, const LagrangeWeights &w,
+                       double out[VLEN]) {
+  if (TAB::kPadded)
+    lagrangeApplyPadded<VLEN>(table, w, out);
+  else
+    lagrangeApply<VLEN>(table, w, out);
+}
+
 // Bytes of shared memory needed to stage the tables of S (velocities only when the
 // adjusted-position path can run).
 __host__ __device__ inline size_t orientationTableBytes(const LsState &S, bool needVelocity) {
-  size_t n = (size_t)S.positions.numNodes * 3 + (size_t)S.quaternions.numNodes * 4;
-  if (needVelocity) n += (size_t)S.velocities.numNodes * 3;
+  size_t n = (size_t)S.positions.numNodes * 4 + (size_t)S.quaternions.numNodes * 4;
+  if (needVelocity) n += (size_t)S.velocities.numNodes * 4;
   return n * sizeof(double);
 }
 
-// Cooperative copy of the tables into `smem`; returns the staged pointers.  All threads
-// of the block must call it; ends with __syncthreads().
-__device__ inline OrientationTables stageOrientationTables(const LsState &S, bool needVelocity,
-                                                           double *smem) {
-  OrientationTables t;
-  const int np = S.positions.numNodes * 3;
+// Cooperative copy of the tables into `smem` (16-byte aligned); returns the staged pointers.
+// All threads of the block must call it; ends with __syncthreads().
+__device__ inline StagedTables stageOrientationTables(const LsState &S, bool needVelocity,
+                                                      double *smem) {
+  StagedTables t;
+  const int np = S.positions.numNodes;
   const int nq = S.quaternions.numNodes * 4;
   double *sp = smem;
-  double *sq = sp + np;
+  double *sq = sp + 4 * np;
   double *sv = sq + nq;
-  for (int i = threadIdx.x; i < np; i += blockDim.x) sp[i] = __ldg(S.positions.values + i);
+  for (int i = threadIdx.x; i < 4 * np; i += blockDim.x) {
+    int node = i >> 2, j = i & 3;
+    sp[i] = j < 3 ? __ldg(S.positions.values + 3 * node + j) : 0.0;
+  }
   for (int i = threadIdx.x; i < nq; i += blockDim.x) sq[i] = __ldg(S.quaternions.values + i);
   if (needVelocity) {
-    const int nv = S.velocities.numNodes * 3;
-    for (int i = threadIdx.x; i < nv; i += blockDim.x) sv[i] = __ldg(S.velocities.values + i);
+    const int nv = S.velocities.numNodes;
+    for (int i = threadIdx.x; i < 4 * nv; i += blockDim.x) {
+      int node = i >> 2, j = i & 3;
+      sv[i] = j < 3 ? __ldg(S.velocities.values + 3 * node + j) : 0.0;
+    }
   }
   __syncthreads();
   t.positions = sp;
   t.quaternions = sq;
-  t.velocities = needVelocity ? sv : S.velocities.values;
+  t.velocities = sv;  // only read when needVelocity (S.hasAdj)
   return t;
 }
 
@@ -78,13 +101,13 @@ UB_DEV double lsImageTime(const LsState &S, double lineFull) {
 //   ALWAYS_VEL = false: line-scan semantics (calc_vel == false at every hot-path call site:
 //                position only unless some parameter is non-zero);
 //   ALWAYS_VEL = true:  push-frame semantics (no shortcut).
-template <bool ALWAYS_VEL>
-UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double time,
+template <bool ALWAYS_VEL, class TAB>
+UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
                             double pos[3], double vel[3]) {
   LagrangeWeights w;
   lagrangeWeights(S.positions, S.lag, time, w);
   double sensPosNom[3];
-  lagrangeApply<3>(T.positions, w, sensPosNom);
+  tableApply<3>(T, T.positions, w, sensPosNom);
   if (!ALWAYS_VEL && !S.hasAdj) {
     pos[0] = sensPosNom[0];
     pos[1] = sensPosNom[1];
@@ -96,7 +119,7 @@ UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double
   }
   // Same grid, same time, same order => the same weights (the reference recomputes them).
   double sensVelNom[3];
-  lagrangeApply<3>(T.velocities, w, sensVelNom);
+  tableApply<3>(T, T.velocities, w, sensVelNom);
 
   double radialUnitVec[3];
   double radMag = sqrt(sensPosNom[0] * sensPosNom[0] + sensPosNom[1] * sensPosNom[1] +
@@ -147,10 +170,12 @@ UB_DEV void adjSensorPosVel(const LsState &S, const OrientationTables &T, double
 }
 
 // LS::getQuaternions LS:2140-2153 + calculateRotationMatrixFromQuaternions U:78-95.
-UB_DEV void cameraToBodyMatrix(const LsState &S, const OrientationTables &T, double time,
-                               double m[9]) {
+template <class TAB>
+UB_DEV void cameraToBodyMatrix(const LsState &S, const TAB &T, double time, double m[9]) {
   double q[4];
-  lagrangeInterp<4>(S.quaternions, S.lag, T.quaternions, time, q);
+  LagrangeWeights w;
+  lagrangeWeights(S.quaternions, S.lag, time, w);
+  tableApply<4>(T, T.quaternions, w, q);
   rotationFromQuaternion(q, m);
 }
 
@@ -170,8 +195,8 @@ UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9])
 
 // LS::computeDetectorView LS:2603-2675 (PF:2038-2110 is the same with the push-frame
 // position routine): ground point -> undistorted focal-plane coordinates at `time`.
-template <bool ALWAYS_VEL>
-UB_DEV void detectorView(const LsState &S, const OrientationTables &T, double time, double gx,
+template <bool ALWAYS_VEL, class TAB>
+UB_DEV void detectorView(const LsState &S, const TAB &T, double time, double gx,
                          double gy, double gz, double &focalX, double &focalY) {
   double pos[3], vel[3];
   adjSensorPosVel<ALWAYS_VEL>(S, T, time, pos, vel);
@@ -196,7 +221,8 @@ UB_DEV void detectorView(const LsState &S, const OrientationTables &T, double ti
 }
 
 // Camera-frame look vector -> body-fixed look (second half of losToEcf, LS:2268-2300).
-UB_DEV void cameraLookToBody(const LsState &S, const OrientationTables &T, double time,
+template <class TAB>
+UB_DEV void cameraLookToBody(const LsState &S, const TAB &T, double time,
                              const double cameraLook[3], double bodyLook[3]) {
   double corrected[3];
   if (S.hasAttAdj) {

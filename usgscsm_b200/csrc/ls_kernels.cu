@@ -59,8 +59,8 @@ UB_DEV void projectiveSeed(const LsState &S, double x, double y, double z, doubl
 // computed; only applyDistortion is repeated, now with the caller's desiredPrecision
 // instead of the default 1e-6 (hazard 3 in SURVEY.md §9).  The loop below therefore has a
 // single inlined copy of the detector view and runs it 2 + k times.
-template <bool ALWAYS_VEL>
-UB_DEV void lsGroundToImagePoint(const LsState &S, const OrientationTables &T, double gx,
+template <bool ALWAYS_VEL, class TAB>
+UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
                                  double gy, double gz, double desiredPrecision, double &outLine,
                                  double &outSamp, double &achieved, uint32_t &status) {
   double approxLine, approxSamp;
@@ -139,23 +139,11 @@ UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamp
   return st;
 }
 
-// MINB = resident blocks of 256 threads per SM the register allocation is held to
-// (2: 96+ registers, 3: 80, 4: 64).
-template <bool STAGE, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB)
-    lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
-                          const double *__restrict__ y, const double *__restrict__ z, double prec,
-                          double *__restrict__ line, double *__restrict__ samp,
-                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
-  extern __shared__ double smem[];
-  OrientationTables T;
-  if (STAGE) {
-    T = stageOrientationTables(S, S.hasAdj != 0, smem);
-  } else {
-    T.positions = S.positions.values;
-    T.velocities = S.velocities.values;
-    T.quaternions = S.quaternions.values;
-  }
+template <class TAB>
+UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const double *__restrict__ x,
+                                const double *__restrict__ y, const double *__restrict__ z,
+                                double prec, double *__restrict__ line, double *__restrict__ samp,
+                                double *__restrict__ achieved, uint32_t *__restrict__ status) {
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
@@ -170,9 +158,28 @@ __global__ void __launch_bounds__(kThreads, MINB)
   }
 }
 
+// MINB = resident blocks of 256 threads per SM the register allocation is held to
+// (2: 96+ registers, 3: 80, 4: 64).
+template <bool STAGE, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
+    lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
+                          const double *__restrict__ y, const double *__restrict__ z, double prec,
+                          double *__restrict__ line, double *__restrict__ samp,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ __align__(16) double smem[];
+  if (STAGE) {
+    StagedTables T = stageOrientationTables(S, S.hasAdj != 0, smem);
+    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status);
+  } else {
+    OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status);
+  }
+}
+
 // ---- imageToGround -----------------------------------------------------------------------
 // One point of LS::imageToGround LS:980-1009 = losToEcf LS:2209-2305 + losEllipsoidIntersect.
-UB_DEV void lsImageToGroundPoint(const LsState &S, const OrientationTables &T, double line,
+template <class TAB>
+UB_DEV void lsImageToGroundPoint(const LsState &S, const TAB &T, double line,
                                  double sample, double height, double desiredPrecision,
                                  double &x, double &y, double &z, double &achieved,
                                  uint32_t &status) {
@@ -294,24 +301,12 @@ __global__ void __launch_bounds__(kThreads, 3)
   }
 }
 
-// GRID = true: pixel coordinates generated from the point index (dense grid);
-// GRID = false: explicit (line, samp) arrays.
-template <bool STAGE, bool GRID>
-__global__ void __launch_bounds__(kThreads)
-    lsImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
-                          const double *__restrict__ samp, GridSpec g,
-                          const double *__restrict__ height, int heightStride, double prec,
-                          double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
-                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
-  extern __shared__ double smem[];
-  OrientationTables T;
-  if (STAGE) {
-    T = stageOrientationTables(S, S.hasAdj != 0, smem);
-  } else {
-    T.positions = S.positions.values;
-    T.velocities = S.velocities.values;
-    T.quaternions = S.quaternions.values;
-  }
+template <bool GRID, class TAB>
+UB_DEV void lsImageToGroundLoop(const LsState &S, const TAB &T, long n, const double *__restrict__ line,
+                                const double *__restrict__ samp, const GridSpec &g,
+                                const double *__restrict__ height, int heightStride, double prec,
+                                double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                                double *__restrict__ achieved, uint32_t *__restrict__ status) {
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     double l, s;
@@ -336,6 +331,27 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// GRID = true: pixel coordinates generated from the point index (dense grid);
+// GRID = false: explicit (line, samp) arrays.
+template <bool STAGE, bool GRID>
+__global__ void __launch_bounds__(kThreads)
+    lsImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                          const double *__restrict__ samp, GridSpec g,
+                          const double *__restrict__ height, int heightStride, double prec,
+                          double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
+                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  extern __shared__ __align__(16) double smem[];
+  if (STAGE) {
+    StagedTables T = stageOrientationTables(S, S.hasAdj != 0, smem);
+    lsImageToGroundLoop<GRID>(S, T, n, line, samp, g, height, heightStride, prec, x, y, z, achieved,
+                              status);
+  } else {
+    OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+    lsImageToGroundLoop<GRID>(S, T, n, line, samp, g, height, heightStride, prec, x, y, z, achieved,
+                              status);
+  }
+}
+
 // ---- model set-up helpers -------------------------------------------------------------------
 // The reference derives a few per-model inputs of the hot path at load time with its own
 // per-point routines (updateState LS:649-735, createProjectiveApproximation LS:2745-2803).
@@ -346,10 +362,7 @@ __global__ void lsSensorPositionKernel(const __grid_constant__ LsState S, int n,
                                        const double *__restrict__ line, double *__restrict__ xyz) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  OrientationTables T;
-  T.positions = S.positions.values;
-  T.velocities = S.velocities.values;
-  T.quaternions = S.quaternions.values;
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   double pos[3], vel[3];
   adjSensorPosVel<true>(S, T, lsImageTime(S, line[i]), pos, vel);
   xyz[3 * i + 0] = pos[0];
