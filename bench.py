@@ -313,6 +313,7 @@ def run_b200(args):
     i2g_value = world * n * args.steps / (i2g_total_ms * 1e-3) / 1e6
 
     peak, peak_src = peak_hbm()
+    traffic, traffic_src = ncu_traffic(n)
     achieved = G2I_BYTES_PER_POINT * n / (kern_ms * 1e-3) / 1e9
     # FP64 roofline: algorithmic flops per point = 450 per detector-view
     # evaluation x measured evaluations + 40; peak = 64 FP64 FMA lanes per SM x 2 flop x SMs x
@@ -330,7 +331,8 @@ def run_b200(args):
         "data": "synthetic", "config": workload_config(args), "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch",
+                     "traffic_source": traffic_src, "peak_source": peak_src,
                      "kernel": "lsGroundToImageKernel", "kernel_ms": kern_ms,
                      "bytes_per_point": G2I_BYTES_PER_POINT,
                      "note": "the kernel is FP64-pipe bound, not HBM bound (DESIGN.md §4): fp64 "
@@ -365,11 +367,25 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def ncu_traffic(n):
+    """DRAM bytes of one lsGroundToImageKernel launch from the committed ncu --set full capture
+    (profiles/ncu_g2i.json: dram__bytes_read.sum + dram__bytes_write.sum and the points of the
+    captured launch), scaled to this launch's points.  None if the summary is absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_g2i.json")
+    try:
+        with open(path) as f:
+            p = json.load(f)
+        per_point = (p["dram_bytes_read"] + p["dram_bytes_write"]) / p["points"]
+        return per_point * n / 1e9, "profiles/ncu_g2i.json (%s)" % p.get("capture", "ncu --set full")
+    except (OSError, KeyError, ValueError):
+        return None, None
+
+
 def other_models(dev):
     """Side measurements (not the headline): dense-grid imageToGround at synthetic-DEM heights
     then groundToImage of the result for the push-frame and frame models (config C3,
     4096 x 4096) and the SAR model (config C4 shape, 64576 x 2367 = 152.9 M points), device
-    resident, CUDA events, mean of 3 launches after 1 warm-up."""
+    resident, outputs preallocated, CUDA events per launch, median of 5 after 2 warm-ups."""
     import numpy as np
     import torch
     import usgscsm_b200 as ub
@@ -397,18 +413,25 @@ def other_models(dev):
 
         def timed(fn):
             fn()
+            fn()
             torch.cuda.synchronize()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            for _ in range(3):
+            ms = []
+            for _ in range(5):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
                 r = fn()
-            b.record()
-            torch.cuda.synchronize()
-            return r, a.elapsed_time(b) / 3.0
+                b.record()
+                torch.cuda.synchronize()
+                ms.append(a.elapsed_time(b))
+            return r, sorted(ms)[len(ms) // 2]
 
-        (x, y, z, _, st), ms = timed(lambda: gm.imageToGroundGrid(0.5, 0.5, 1.0, 1.0, nl, ns, h, PREC))
+        o1 = tuple(torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3)) + (
+            None, torch.empty(n, dtype=torch.int32, device=dev))
+        o2 = tuple(torch.empty(n, dtype=torch.float64, device=dev) for _ in range(2)) + (
+            None, torch.empty(n, dtype=torch.int32, device=dev))
+        (x, y, z, _, st), ms = timed(lambda: gm.imageToGroundGrid(0.5, 0.5, 1.0, 1.0, nl, ns, h, PREC, out=o1))
         res["image_to_ground_mpts"] = n / ms / 1e3
-        (l, s, _, st2), ms2 = timed(lambda: gm.groundToImageBatch(x, y, z, PREC, achieved=False))
+        (l, s, _, st2), ms2 = timed(lambda: gm.groundToImageBatch(x, y, z, PREC, achieved=False, out=o2))
         res["ground_to_image_mpts"] = n / ms2 / 1e3
         res["points"] = n
         res["round_trip_max_line_px"] = float((l.view(nl, ns) - rows[:, None]).abs().max())
@@ -416,7 +439,7 @@ def other_models(dev):
         res["points_with_flags"] = int(((st & ~_capi.ST_EVALS_MASK) != 0).sum()) + int(((st2 & ~_capi.ST_EVALS_MASK) != 0).sum())
         res["evaluations_per_point"] = float(((st2 >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean())
         out[name] = res
-        del gm, x, y, z, l, s, st, st2, h
+        del gm, x, y, z, l, s, st, st2, h, o1, o2
         torch.cuda.empty_cache()
     return out
 

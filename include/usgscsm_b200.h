@@ -97,6 +97,12 @@ USGSCSM_B200_API int usgscsm_b200_device_count(void);
  * LS:2745-2803) are computed here by running the batch kernels on those points. */
 USGSCSM_B200_API int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
                                   usgscsm_b200_model **out);
+/* UsgsAstroPlugin::getModelNameFromModelState (src/UsgsAstroPlugin.cpp:176-218): the value of
+ * the "m_modelName" key, written NUL-terminated into name[cap].  Host only (no device needed).
+ * USGSCSM_B200_ESTATE: no such key / unparsable; USGSCSM_B200_EUNSUPPORTED: not one of the
+ * four model names above. */
+USGSCSM_B200_API int usgscsm_b200_model_name_from_state(const char *state, size_t len, char *name,
+                                       size_t cap);
 /* csm::Model destructor. */
 USGSCSM_B200_API void usgscsm_b200_model_free(usgscsm_b200_model *m);
 /* USGSCSM_B200_MODEL_* */
@@ -153,6 +159,17 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_dev(usgscsm_b200_model *m, int
                                      int height_stride, double prec, double *x, double *y,
                                      double *z, double *achieved, uint32_t *status,
                                      void *stream);
+
+/* AoS flavours of the two host-pointer calls, for callers that hold arrays of the CSM value
+ * types (csm/csm.h:212-308): xyz = n csm::EcefCoord {x,y,z} (3n doubles), line_samp =
+ * n csm::ImageCoord {line,samp} (2n doubles).  Split / joined on the device. */
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_aos(usgscsm_b200_model *m, int64_t n, const double *xyz,
+                                     double prec, double *line_samp, double *achieved,
+                                     uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n,
+                                     const double *line_samp, const double *height,
+                                     int height_stride, double prec, double *xyz,
+                                     double *achieved, uint32_t *status);
 
 /* Dense-grid imageToGround: the double loop of bin/usgscsm_cam_test.cc:294-309 (and of an
  * orthorectifier) with the pixel coordinates generated in the kernel.  Point k =

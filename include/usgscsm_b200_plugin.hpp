@@ -1,0 +1,351 @@
+// usgscsm_b200_plugin.hpp -- C++ host side of the engine, above the C-ABI (usgscsm_b200.h).
+//
+// Header-only mirror of the reference's plugin / sensor-model interface for the hot path:
+// same names, argument meaning, defaults and error behaviour as
+//   * UsgsAstroPlugin                 (include/usgscsm/UsgsAstroPlugin.h:42-72,
+//                                      src/UsgsAstroPlugin.cpp:62-69, 158-250, 535-555),
+//   * csm::RasterGM::groundToImage / imageToGround (csm/RasterGM.h; LS:757-890, 980-1009),
+//   * csm value types ImageCoord / ImageVector / EcefCoord (csm/csm.h:212-445),
+//     csm::Warning (csm/Warning.h:39-47) and csm::Error (csm/Error.h:40-48),
+// plus the batched array entry points the reference does not have (groundToImageBatch,
+// imageToGroundBatch, imageToGroundGrid).  Every call, scalar or batched, ends in a kernel
+// launch through libusgscsm_b200.so: there is no CPU implementation behind this header, and
+// with no CUDA device constructModelFromState throws csm::Error(SENSOR_MODEL_NOT_CONSTRUCTIBLE).
+//
+// The value types are declared here (namespace usgscsm_b200::csm) with the memory layout of
+// the CSM API's, so arrays of ::csm::EcefCoord / ::csm::ImageCoord can be handed to the AoS
+// batch calls with a reinterpret_cast.
+#ifndef USGSCSM_B200_PLUGIN_HPP_
+#define USGSCSM_B200_PLUGIN_HPP_
+
+#include <cstddef>
+#include <cstdint>
+#include <exception>
+#include <list>
+#include <string>
+#include <vector>
+
+#include "usgscsm_b200.h"
+
+namespace usgscsm_b200 {
+namespace csm {
+
+struct ImageCoord {  // csm/csm.h:212-226
+  double line, samp;
+  ImageCoord() : line(0.0), samp(0.0) {}
+  ImageCoord(double aLine, double aSamp) : line(aLine), samp(aSamp) {}
+};
+struct ImageVector {  // csm/csm.h:258-272
+  double line, samp;
+  ImageVector() : line(0.0), samp(0.0) {}
+  ImageVector(double aLine, double aSamp) : line(aLine), samp(aSamp) {}
+};
+struct EcefCoord {  // csm/csm.h:292-308
+  double x, y, z;
+  EcefCoord() : x(0.0), y(0.0), z(0.0) {}
+  EcefCoord(double aX, double aY, double aZ) : x(aX), y(aY), z(aZ) {}
+};
+
+class Warning {  // csm/Warning.h:36-89
+ public:
+  enum WarningType {
+    UNKNOWN_WARNING = 1,
+    DATA_NOT_AVAILABLE,
+    PRECISION_NOT_MET,
+    NEGATIVE_PRECISION,
+    IMAGE_COORD_OUT_OF_BOUNDS,
+    IMAGE_ID_TOO_LONG,
+    NO_INTERSECTION,
+    DEPRECATED_FUNCTION
+  };
+  Warning() : theWarning(UNKNOWN_WARNING) {}
+  Warning(const WarningType &aWarningType, const std::string &aMessage,
+          const std::string &aFunction)
+      : theWarning(aWarningType), theMessage(aMessage), theFunction(aFunction) {}
+  WarningType getWarning() const { return theWarning; }
+  const std::string &getMessage() const { return theMessage; }
+  const std::string &getFunction() const { return theFunction; }
+
+ private:
+  WarningType theWarning;
+  std::string theMessage, theFunction;
+};
+typedef std::list<Warning> WarningList;
+
+class Error : public std::exception {  // csm/Error.h:37-100
+ public:
+  enum ErrorType {
+    ALGORITHM = 1,
+    BOUNDS,
+    FILE_READ,
+    FILE_WRITE,
+    ILLEGAL_MATH_OPERATION,
+    INDEX_OUT_OF_RANGE,
+    INVALID_SENSOR_MODEL_STATE,
+    INVALID_USE,
+    ISD_NOT_SUPPORTED,
+    MEMORY,
+    SENSOR_MODEL_NOT_CONSTRUCTIBLE,
+    SENSOR_MODEL_NOT_SUPPORTED,
+    STRING_TOO_LONG,
+    UNKNOWN_ERROR,
+    UNSUPPORTED_FUNCTION,
+    UNKNOWN_SUPPORT_DATA
+  };
+  Error() : theError(UNKNOWN_ERROR) {}
+  Error(const ErrorType &aErrorType, const std::string &aMessage, const std::string &aFunction)
+      : theError(aErrorType), theMessage(aMessage), theFunction(aFunction) {}
+  virtual ~Error() throw() {}
+  ErrorType getError() const { return theError; }
+  const std::string &getMessage() const { return theMessage; }
+  const std::string &getFunction() const { return theFunction; }
+  virtual const char *what() const throw() { return theMessage.c_str(); }
+
+ private:
+  ErrorType theError;
+  std::string theMessage, theFunction;
+};
+
+}  // namespace csm
+
+// A sensor model living on one GPU: the hot-path subset of csm::RasterGM.
+class RasterGM {
+ public:
+  RasterGM(usgscsm_b200_model *handle, const std::string &state) : m_h(handle), m_state(state) {}
+  ~RasterGM() { usgscsm_b200_model_free(m_h); }  // csm::Model::~Model; the caller owns the model
+
+  // ---- csm::Model / GeometricModel subset ------------------------------------------------
+  std::string getModelName() const {
+    switch (usgscsm_b200_model_kind(m_h)) {
+      case USGSCSM_B200_MODEL_LINE_SCANNER: return "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL";
+      case USGSCSM_B200_MODEL_PUSH_FRAME: return "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL";
+      case USGSCSM_B200_MODEL_FRAME: return "USGS_ASTRO_FRAME_SENSOR_MODEL";
+      default: return "USGS_ASTRO_SAR_SENSOR_MODEL";
+    }
+  }
+  std::string getModelState() const { return m_state; }
+  csm::ImageVector getImageSize() const {  // LS:1845-1852
+    int l = 0, s = 0;
+    check(usgscsm_b200_model_image_size(m_h, &l, &s), "getImageSize");
+    return csm::ImageVector(l, s);
+  }
+  std::pair<csm::ImageCoord, csm::ImageCoord> getValidImageRange() const {  // LS:1862-1869
+    csm::ImageVector sz = getImageSize();
+    return std::make_pair(csm::ImageCoord(0.0, 0.0), csm::ImageCoord(sz.line, sz.samp));
+  }
+  int getNumParameters() const { return usgscsm_b200_model_num_parameters(m_h); }
+  double getParameterValue(int index) const {
+    double v = 0.0;
+    if (usgscsm_b200_model_get_parameter(m_h, index, &v) != 0)
+      throw csm::Error(csm::Error::INDEX_OUT_OF_RANGE, usgscsm_b200_last_error(),
+                       "getParameterValue");
+    return v;
+  }
+  void setParameterValue(int index, double value) {
+    if (usgscsm_b200_model_set_parameter(m_h, index, value) != 0)
+      throw csm::Error(csm::Error::INDEX_OUT_OF_RANGE, usgscsm_b200_last_error(),
+                       "setParameterValue");
+  }
+  int device() const { return usgscsm_b200_model_device(m_h); }
+  usgscsm_b200_model *handle() const { return m_h; }
+
+  // ---- csm::RasterGM per-point API (a batch of one; pays one kernel launch) ---------------
+  csm::ImageCoord groundToImage(const csm::EcefCoord &groundPt, double desiredPrecision = 0.001,
+                                double *achievedPrecision = NULL,
+                                csm::WarningList *warnings = NULL) const {
+    double l = 0, s = 0, a = 0;
+    uint32_t st = 0;
+    check(usgscsm_b200_ground_to_image(m_h, 1, &groundPt.x, &groundPt.y, &groundPt.z,
+                                       desiredPrecision, &l, &s, &a, &st),
+          "groundToImage");
+    raiseOrWarn(st, warnings, "groundToImage");
+    if (achievedPrecision) *achievedPrecision = a;
+    return csm::ImageCoord(l, s);
+  }
+  csm::EcefCoord imageToGround(const csm::ImageCoord &imagePt, double height,
+                               double desiredPrecision = 0.001, double *achievedPrecision = NULL,
+                               csm::WarningList *warnings = NULL) const {
+    double x = 0, y = 0, z = 0, a = 0;
+    uint32_t st = 0;
+    check(usgscsm_b200_image_to_ground(m_h, 1, &imagePt.line, &imagePt.samp, &height, 1,
+                                       desiredPrecision, &x, &y, &z, &a, &st),
+          "imageToGround");
+    raiseOrWarn(st, warnings, "imageToGround");
+    if (achievedPrecision) *achievedPrecision = a;
+    return csm::EcefCoord(x, y, z);
+  }
+
+  // ---- batched entry points: SoA host arrays (H2D/D2H inside) ------------------------------
+  // status[i] carries the warnings / errors the scalar call would have raised for point i
+  // (USGSCSM_B200_ST_*); no exception is thrown for a per-point failure.
+  void groundToImageBatch(size_t n, const double *x, const double *y, const double *z,
+                          double desiredPrecision, double *line, double *samp,
+                          double *achievedPrecision = NULL, uint32_t *status = NULL) const {
+    check(usgscsm_b200_ground_to_image(m_h, (int64_t)n, x, y, z, desiredPrecision, line, samp,
+                                       achievedPrecision, status),
+          "groundToImageBatch");
+  }
+  void imageToGroundBatch(size_t n, const double *line, const double *samp, const double *height,
+                          bool perPointHeight, double desiredPrecision, double *x, double *y,
+                          double *z, double *achievedPrecision = NULL,
+                          uint32_t *status = NULL) const {
+    check(usgscsm_b200_image_to_ground(m_h, (int64_t)n, line, samp, height, perPointHeight ? 1 : 0,
+                                       desiredPrecision, x, y, z, achievedPrecision, status),
+          "imageToGroundBatch");
+  }
+  // AoS flavours over the CSM value types (csm/csm.h:212-308).
+  void groundToImageBatch(const std::vector<csm::EcefCoord> &groundPts, double desiredPrecision,
+                          std::vector<csm::ImageCoord> &imagePts,
+                          std::vector<double> *achievedPrecision = NULL,
+                          std::vector<uint32_t> *status = NULL) const {
+    const size_t n = groundPts.size();
+    imagePts.resize(n);
+    if (achievedPrecision) achievedPrecision->resize(n);
+    if (status) status->resize(n);
+    check(usgscsm_b200_ground_to_image_aos(
+              m_h, (int64_t)n, n ? &groundPts[0].x : NULL, desiredPrecision,
+              n ? &imagePts[0].line : NULL, achievedPrecision && n ? &(*achievedPrecision)[0] : NULL,
+              status && n ? &(*status)[0] : NULL),
+          "groundToImageBatch");
+  }
+  void imageToGroundBatch(const std::vector<csm::ImageCoord> &imagePts,
+                          const std::vector<double> &heights, double desiredPrecision,
+                          std::vector<csm::EcefCoord> &groundPts,
+                          std::vector<double> *achievedPrecision = NULL,
+                          std::vector<uint32_t> *status = NULL) const {
+    const size_t n = imagePts.size();
+    if (heights.size() != n && heights.size() != 1)
+      throw csm::Error(csm::Error::BOUNDS, "heights must hold 1 or n entries", "imageToGroundBatch");
+    groundPts.resize(n);
+    if (achievedPrecision) achievedPrecision->resize(n);
+    if (status) status->resize(n);
+    check(usgscsm_b200_image_to_ground_aos(
+              m_h, (int64_t)n, n ? &imagePts[0].line : NULL, &heights[0], heights.size() == n ? 1 : 0,
+              desiredPrecision, n ? &groundPts[0].x : NULL,
+              achievedPrecision && n ? &(*achievedPrecision)[0] : NULL,
+              status && n ? &(*status)[0] : NULL),
+          "imageToGroundBatch");
+  }
+
+  // ---- device-pointer flavours (enqueue on `stream`, no synchronisation) --------------------
+  void groundToImageDevice(size_t n, const double *x, const double *y, const double *z,
+                           double desiredPrecision, double *line, double *samp,
+                           double *achievedPrecision, uint32_t *status, void *stream) const {
+    check(usgscsm_b200_ground_to_image_dev(m_h, (int64_t)n, x, y, z, desiredPrecision, line, samp,
+                                           achievedPrecision, status, stream),
+          "groundToImageDevice");
+  }
+  void imageToGroundDevice(size_t n, const double *line, const double *samp, const double *height,
+                           bool perPointHeight, double desiredPrecision, double *x, double *y,
+                           double *z, double *achievedPrecision, uint32_t *status,
+                           void *stream) const {
+    check(usgscsm_b200_image_to_ground_dev(m_h, (int64_t)n, line, samp, height,
+                                           perPointHeight ? 1 : 0, desiredPrecision, x, y, z,
+                                           achievedPrecision, status, stream),
+          "imageToGroundDevice");
+  }
+  // The pixel double loop of bin/usgscsm_cam_test.cc:294-309 with the coordinates generated
+  // in the kernel; point k = r * nSamps + c is pixel (line0 + r*dline, samp0 + c*dsamp).
+  void imageToGroundGridDevice(double line0, double samp0, double dline, double dsamp,
+                               size_t nLines, size_t nSamps, const double *height,
+                               bool perPointHeight, double desiredPrecision, double *x, double *y,
+                               double *z, double *achievedPrecision, uint32_t *status,
+                               void *stream) const {
+    check(usgscsm_b200_image_to_ground_grid_dev(m_h, line0, samp0, dline, dsamp, (int64_t)nLines,
+                                                (int64_t)nSamps, height, perPointHeight ? 1 : 0,
+                                                desiredPrecision, x, y, z, achievedPrecision,
+                                                status, stream),
+          "imageToGroundGridDevice");
+  }
+
+  // Status word of one point -> what the scalar reference call does: throw csm::Error for
+  // the error bits (Distortion.cpp:357-365, SAR:569-575), append csm::Warning otherwise.
+  static void raiseOrWarn(uint32_t st, csm::WarningList *warnings, const char *function) {
+    if (st & USGSCSM_B200_ST_ERROR_ALGORITHM)
+      throw csm::Error(csm::Error::ALGORITHM, "Unable to apply transform.", function);
+    if (st & USGSCSM_B200_ST_ERROR_UNKNOWN)
+      throw csm::Error(csm::Error::UNKNOWN_ERROR, "Could not calculate the image coordinate.",
+                       function);
+    if (st & USGSCSM_B200_ST_ERROR_OTHER)
+      throw csm::Error(csm::Error::UNKNOWN_ERROR, "per-point failure", function);
+    if (!warnings) return;
+    if (st & USGSCSM_B200_ST_NO_INTERSECTION)
+      warnings->push_back(csm::Warning(csm::Warning::NO_INTERSECTION, "No Intersection", function));
+    if (st & USGSCSM_B200_ST_PRECISION_NOT_MET)
+      warnings->push_back(csm::Warning(csm::Warning::PRECISION_NOT_MET,
+                                       "Desired precision not achieved.", function));
+  }
+
+ private:
+  RasterGM(const RasterGM &);
+  RasterGM &operator=(const RasterGM &);
+  static void check(int code, const char *function) {
+    if (code == USGSCSM_B200_OK) return;
+    throw csm::Error(code == USGSCSM_B200_EINVAL ? csm::Error::BOUNDS : csm::Error::UNKNOWN_ERROR,
+                     usgscsm_b200_last_error(), function);
+  }
+  usgscsm_b200_model *m_h;
+  std::string m_state;
+};
+
+// src/UsgsAstroPlugin.cpp: the factory.  Models are built from model-state strings
+// (constructModelFromISD needs ALE and is outside the hot path).
+class UsgsAstroPlugin {
+ public:
+  explicit UsgsAstroPlugin(int device = 0) : m_device(device) {}
+  std::string getPluginName() const { return "UsgsAstroPluginCSM"; }       // :62
+  std::string getManufacturer() const { return "UsgsAstrogeology"; }       // :63
+  std::string getReleaseDate() const { return "20190222"; }                // :64
+  size_t getNumModels() const { return 4; }  // the projected wrapper (PROJ) is out of scope
+  std::string getModelName(size_t modelIndex) const {                      // :158-170
+    static const char *names[4] = {
+        "USGS_ASTRO_FRAME_SENSOR_MODEL", "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL",
+        "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL", "USGS_ASTRO_SAR_SENSOR_MODEL"};
+    if (modelIndex >= 4)
+      throw csm::Error(csm::Error::INDEX_OUT_OF_RANGE, "Model index out of range.",
+                       "UsgsAstroPlugin::getModelName");
+    return names[modelIndex];
+  }
+  // :176-218 -- the JSON key "m_modelName" of the state (after stateAsJson U:2489-2500).
+  std::string getModelNameFromModelState(const std::string &modelState,
+                                         csm::WarningList * = NULL) const {
+    char name[128];
+    int code = usgscsm_b200_model_name_from_state(modelState.data(), modelState.size(), name,
+                                                  sizeof(name));
+    if (code == USGSCSM_B200_EUNSUPPORTED)
+      throw csm::Error(csm::Error::SENSOR_MODEL_NOT_SUPPORTED, "Sensor model not supported.",
+                       "UsgsAstroPlugin::getModelNameFromModelState");
+    if (code != USGSCSM_B200_OK)
+      throw csm::Error(csm::Error::INVALID_SENSOR_MODEL_STATE,
+                       "No 'm_modelName' key in the model state object.",
+                       "UsgsAstroPlugin::getModelNameFromModelState");
+    return name;
+  }
+  bool canModelBeConstructedFromState(const std::string &modelName, const std::string &modelState,
+                                      csm::WarningList * = NULL) const {  // :229-250
+    try {
+      return getModelNameFromModelState(modelState) == modelName;
+    } catch (const csm::Error &) {
+      return false;
+    }
+  }
+  // :535-555.  Returns a raw heap pointer the caller owns and deletes (csm/Plugin.h:186-205).
+  RasterGM *constructModelFromState(const std::string &modelState,
+                                    csm::WarningList * = NULL) const {
+    usgscsm_b200_model *h = NULL;
+    int code = usgscsm_b200_model_from_state(modelState.data(), modelState.size(), m_device, &h);
+    if (code == USGSCSM_B200_EUNSUPPORTED)
+      throw csm::Error(csm::Error::SENSOR_MODEL_NOT_SUPPORTED, usgscsm_b200_last_error(),
+                       "UsgsAstroPlugin::constructModelFromState");
+    if (code != USGSCSM_B200_OK)
+      throw csm::Error(csm::Error::SENSOR_MODEL_NOT_CONSTRUCTIBLE, usgscsm_b200_last_error(),
+                       "UsgsAstroPlugin::constructModelFromState");
+    return new RasterGM(h, modelState);
+  }
+
+ private:
+  int m_device;
+};
+
+}  // namespace usgscsm_b200
+#endif  // USGSCSM_B200_PLUGIN_HPP_

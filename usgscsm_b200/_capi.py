@@ -39,6 +39,7 @@ SIGNATURES = {
     "usgscsm_b200_last_error": (C.c_char_p, []),
     "usgscsm_b200_device_count": (C.c_int, []),
     "usgscsm_b200_model_from_state": (C.c_int, [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_h)]),
+    "usgscsm_b200_model_name_from_state": (C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]),
     "usgscsm_b200_model_free": (None, [_h]),
     "usgscsm_b200_model_kind": (C.c_int, [_h]),
     "usgscsm_b200_model_device": (C.c_int, [_h]),
@@ -57,6 +58,10 @@ SIGNATURES = {
     "usgscsm_b200_image_to_ground_dev": (
         C.c_int,
         [_h, C.c_int64, _dp, _dp, _dp, C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_aos": (
+        C.c_int, [_h, C.c_int64, _dp, C.c_double, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_aos": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, C.c_int, C.c_double, _dp, _dp, _dp]),
     "usgscsm_b200_image_to_ground_grid_dev": (
         C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
                   C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),

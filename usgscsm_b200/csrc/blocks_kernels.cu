@@ -40,6 +40,30 @@ __global__ void lagrangeKernel(UniformTable tab, LagrangeDivisors lag, long n, c
   }
 }
 
+// AoS <-> SoA for the csm value types (csm::EcefCoord = 3 doubles, csm::ImageCoord = 2,
+// csm/csm.h:212-308): arrays of structs are copied to the device as they are and split /
+// joined there, so the per-point kernels always see coalesced SoA arrays.
+template <int NC>
+__global__ void aosSplitKernel(long n, const double *__restrict__ aos, double *__restrict__ c0,
+                               double *__restrict__ c1, double *__restrict__ c2) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    c0[i] = aos[i * NC];
+    c1[i] = aos[i * NC + 1];
+    if (NC == 3) c2[i] = aos[i * NC + 2];
+  }
+}
+template <int NC>
+__global__ void aosJoinKernel(long n, const double *__restrict__ c0, const double *__restrict__ c1,
+                              const double *__restrict__ c2, double *__restrict__ aos) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    aos[i * NC] = c0[i];
+    aos[i * NC + 1] = c1[i];
+    if (NC == 3) aos[i * NC + 2] = c2[i];
+  }
+}
+
 // r[i] = refinedReciprocal(b[i]); a divisor the fast path can never accept (zero, subnormal,
 // huge, non-finite) gets NaN, which sends every division by it to the slow path.
 __global__ void reciprocalKernel(int n, const double *__restrict__ b, double *__restrict__ r) {
@@ -121,6 +145,30 @@ cudaError_t launchReciprocals(int n, const double *b, double *r, cudaStream_t st
 cudaError_t launchDivisionSelfTest(unsigned long long seed, int blocks, long perThread,
                                    unsigned long long *mismatches, cudaStream_t stream) {
   divisionSelfTestKernel<<<blocks, 256, 0, stream>>>(seed, perThread, mismatches);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchAosSplit(int ncomp, long n, const double *aos, double *c0, double *c1,
+                           double *c2, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  if (ncomp == 3)
+    aosSplitKernel<3><<<blocks, 256, 0, stream>>>(n, aos, c0, c1, c2);
+  else
+    aosSplitKernel<2><<<blocks, 256, 0, stream>>>(n, aos, c0, c1, c2);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchAosJoin(int ncomp, long n, const double *c0, const double *c1, const double *c2,
+                          double *aos, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  if (ncomp == 3)
+    aosJoinKernel<3><<<blocks, 256, 0, stream>>>(n, c0, c1, c2, aos);
+  else
+    aosJoinKernel<2><<<blocks, 256, 0, stream>>>(n, c0, c1, c2, aos);
   countLaunch();
   return cudaGetLastError();
 }

@@ -3,6 +3,7 @@
 // There is no CPU implementation of the per-point math behind these entry points: every
 // compute call ends in a kernel launch or fails with a negative error code.
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -11,6 +12,7 @@
 #include "../../include/usgscsm_b200.h"
 #include "model.h"
 #include "state_reader.h"
+#include "work_queue.cuh"
 
 namespace ub200 {
 
@@ -18,6 +20,16 @@ static std::atomic<int64_t> g_launches{0};
 void countLaunch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 static thread_local std::string g_lastError;
+
+int grabSize() {
+  static const int grab = [] {
+    const char *v = getenv("USGSCSM_B200_GRAB");
+    int g = v && *v ? atoi(v) : kDefaultGrab;
+    if (g < 32) g = 32;
+    return (g + 31) / 32 * 32;
+  }();
+  return grab;
+}
 
 // ---- Model ------------------------------------------------------------------------------
 Model::~Model() {
@@ -27,6 +39,7 @@ Model::~Model() {
     for (double *p : s.in) cudaFree(p);
     for (double *p : s.out) cudaFree(p);
     cudaFree(s.status);
+    cudaFree(s.aos);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
   }
@@ -60,6 +73,15 @@ void Model::ensureSlot(int s, long points) {
   p.status = nullptr;
   UB_CUDA(cudaMalloc(&p.status, points * sizeof(uint32_t)));
   p.capacity = points;
+}
+
+void Model::ensureAos(int s, long points) {
+  PipelineSlot &p = slots[s];
+  if (p.aosCapacity >= points) return;
+  cudaFree(p.aos);
+  p.aos = nullptr;
+  UB_CUDA(cudaMalloc(&p.aos, points * 3 * sizeof(double)));
+  p.aosCapacity = points;
 }
 
 // ---- error plumbing ---------------------------------------------------------------------
@@ -200,6 +222,26 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     }
     UB_CUDA(cudaDeviceSynchronize());
     *out = m.release();
+    return USGSCSM_B200_OK;
+  });
+}
+
+// getModelNameFromModelState (src/UsgsAstroPlugin.cpp:176-218).  Host only: no device needed.
+int usgscsm_b200_model_name_from_state(const char *state, size_t len, char *name, size_t cap) {
+  if (!state || !name || cap == 0) return fail(USGSCSM_B200_EINVAL, "null argument");
+  name[0] = 0;
+  return guarded([&]() -> int {
+    std::string text = stateJsonText(state, len);
+    json::Value root = json::parse(text);
+    StateReader st(root);
+    std::string n = st.getString("m_modelName");
+    if (n != "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL" && n != "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL" &&
+        n != "USGS_ASTRO_FRAME_SENSOR_MODEL" && n != "USGS_ASTRO_SAR_SENSOR_MODEL") {
+      g_lastError = "unsupported model name: " + n;
+      return USGSCSM_B200_EUNSUPPORTED;
+    }
+    if (n.size() + 1 > cap) return fail(USGSCSM_B200_EINVAL, "name buffer too small");
+    std::memcpy(name, n.c_str(), n.size() + 1);
     return USGSCSM_B200_OK;
   });
 }
@@ -407,6 +449,90 @@ int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double 
       UB_CUDA(cudaMemcpyAsync(x + off, s.out[0], b, cudaMemcpyDeviceToHost, s.stream));
       UB_CUDA(cudaMemcpyAsync(y + off, s.out[1], b, cudaMemcpyDeviceToHost, s.stream));
       UB_CUDA(cudaMemcpyAsync(z + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
+      if (achieved)
+        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[3], b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < kPipelineSlots && si < c; si++)
+      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+// ---- AoS flavours (arrays of csm::EcefCoord / csm::ImageCoord, csm/csm.h:212-308) -----------
+// Same three-slot pipeline; a chunk is copied as it lies, split into SoA on the device, run
+// through the same kernels, joined and copied back.
+int usgscsm_b200_ground_to_image_aos(usgscsm_b200_model *m, int64_t n, const double *xyz,
+                                     double prec, double *line_samp, double *achieved,
+                                     uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!xyz || !line_samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % kPipelineSlots);
+      m->ensureSlot(si, chunk);
+      m->ensureAos(si, chunk);
+      PipelineSlot &s = m->slots[si];
+      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      UB_CUDA(cudaMemcpyAsync(s.aos, xyz + 3 * off, 3 * b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launchAosSplit(3, cnt, s.aos, s.in[0], s.in[1], s.in[2], s.stream));
+      UB_CUDA(launchGroundToImage(*m, cnt, s.in[0], s.in[1], s.in[2], prec, s.out[0], s.out[1],
+                                  achieved ? s.out[2] : nullptr, status ? s.status : nullptr,
+                                  s.stream));
+      UB_CUDA(launchAosJoin(2, cnt, s.out[0], s.out[1], nullptr, s.aos, s.stream));
+      UB_CUDA(cudaMemcpyAsync(line_samp + 2 * off, s.aos, 2 * b, cudaMemcpyDeviceToHost, s.stream));
+      if (achieved)
+        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < kPipelineSlots && si < c; si++)
+      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n, const double *line_samp,
+                                     const double *height, int height_stride, double prec,
+                                     double *xyz, double *achieved, uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line_samp || !height || !xyz) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % kPipelineSlots);
+      m->ensureSlot(si, chunk);
+      m->ensureAos(si, chunk);
+      PipelineSlot &s = m->slots[si];
+      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      UB_CUDA(cudaMemcpyAsync(s.aos, line_samp + 2 * off, 2 * b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launchAosSplit(2, cnt, s.aos, s.in[0], s.in[1], nullptr, s.stream));
+      if (height_stride)
+        UB_CUDA(cudaMemcpyAsync(s.in[2], height + off, b, cudaMemcpyHostToDevice, s.stream));
+      else
+        UB_CUDA(cudaMemcpyAsync(s.in[2], height, sizeof(double), cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launchImageToGround(*m, cnt, s.in[0], s.in[1], nullptr, s.in[2],
+                                  height_stride ? 1 : 0, prec, s.out[0], s.out[1], s.out[2],
+                                  achieved ? s.out[3] : nullptr, status ? s.status : nullptr,
+                                  s.stream));
+      UB_CUDA(launchAosJoin(3, cnt, s.out[0], s.out[1], s.out[2], s.aos, s.stream));
+      UB_CUDA(cudaMemcpyAsync(xyz + 3 * off, s.aos, 3 * b, cudaMemcpyDeviceToHost, s.stream));
       if (achieved)
         UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[3], b, cudaMemcpyDeviceToHost, s.stream));
       if (status)

@@ -78,6 +78,10 @@ cudaError_t launchDistortion(bool apply, const FocalPlane &fp, double precision,
                              uint32_t *status, cudaStream_t stream);
 cudaError_t launchLagrange(const UniformTable &tab, const LagrangeDivisors &lag, int vlen, long n,
                            const double *times, double *out, cudaStream_t stream);
+cudaError_t launchAosSplit(int ncomp, long n, const double *aos, double *c0, double *c1,
+                           double *c2, cudaStream_t stream);
+cudaError_t launchAosJoin(int ncomp, long n, const double *c0, const double *c1, const double *c2,
+                          double *aos, cudaStream_t stream);
 cudaError_t launchReciprocals(int n, const double *b, double *r, cudaStream_t stream);
 cudaError_t launchDivisionSelfTest(unsigned long long seed, int blocks, long perThread,
                                    unsigned long long *mismatches, cudaStream_t stream);

@@ -13,6 +13,7 @@
 
 #include "kernels.h"
 #include "ls_common.cuh"
+#include "work_queue.cuh"
 
 namespace ub200 {
 
@@ -143,9 +144,9 @@ template <class TAB>
 UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const double *__restrict__ x,
                                 const double *__restrict__ y, const double *__restrict__ z,
                                 double prec, double *__restrict__ line, double *__restrict__ samp,
-                                double *__restrict__ achieved, uint32_t *__restrict__ status) {
-  const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+                                double *__restrict__ achieved, uint32_t *__restrict__ status,
+                                unsigned long long *__restrict__ next, int grab) {
+  forEachPointDynamic(n, next, grab, [&](long i) {
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s, a;
     uint32_t st = 0;
@@ -155,7 +156,7 @@ UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const do
     __stcs(samp + i, s);
     if (achieved) __stcs(achieved + i, a);
     if (status) __stcs(status + i, st);
-  }
+  });
 }
 
 // MINB = resident blocks of 256 threads per SM the register allocation is held to
@@ -165,14 +166,15 @@ __global__ void __launch_bounds__(kThreads, MINB)
     lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
-                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+                          double *__restrict__ achieved, uint32_t *__restrict__ status,
+                          unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
   if (STAGE) {
     StagedTables T = stageOrientationTables(S, S.hasAdj != 0, smem);
-    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status);
+    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
   } else {
     OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
-    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status);
+    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
   }
 }
 
@@ -418,13 +420,20 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   bool stage;
   static const int minb = envInt("USGSCSM_B200_LS_MINB", kDefaultMinBlocks);
   LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, minb);
+  // work counter of this launch: stream-ordered scratch, so that launches in flight on
+  // different streams never share one
+  const int grab = grabSize();
+  WorkCounter wc;
+  cudaError_t e = wc.acquire(stream);
+  if (e != cudaSuccess) return e;
+  unsigned long long *next = wc.ptr;
 #define UB_LAUNCH_G2I(STAGE, MINB)                                                            \
   do {                                                                                        \
     if (smemBytes > 48 * 1024)                                                                \
       cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, MINB>,                                \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
     lsGroundToImageKernel<STAGE, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(         \
-        S, n, x, y, z, prec, line, samp, achieved, status);                                   \
+        S, n, x, y, z, prec, line, samp, achieved, status, next, grab);                       \
   } while (0)
   if (stage) {
     if (minb >= 4) UB_LAUNCH_G2I(true, 4);
@@ -437,7 +446,7 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   }
 #undef UB_LAUNCH_G2I
   countLaunch();
-  return cudaGetLastError();
+  return wc.release();
 }
 
 cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const double *line,

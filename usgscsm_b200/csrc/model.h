@@ -45,6 +45,8 @@ struct PipelineSlot {
   double *out[4] = {nullptr, nullptr, nullptr, nullptr};  // up to x,y,z,achieved
   uint32_t *status = nullptr;
   long capacity = 0;  // points
+  double *aos = nullptr;  // AoS flavours: 3 doubles per point, input then output of a chunk
+  long aosCapacity = 0;
 };
 
 constexpr int kPipelineSlots = 3;
@@ -81,6 +83,7 @@ struct Model {
   ~Model();
   const double *upload(const std::vector<double> &v);
   void ensureSlot(int s, long points);
+  void ensureAos(int s, long points);
 };
 
 // model_ls.cu

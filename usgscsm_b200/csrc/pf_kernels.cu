@@ -16,6 +16,7 @@
 // image) falls back to the in-thread evaluation.
 #include "kernels.h"
 #include "ls_common.cuh"
+#include "work_queue.cuh"
 
 namespace ub200 {
 
@@ -238,12 +239,12 @@ __global__ void __launch_bounds__(kThreads)
     pfGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
-                          double *__restrict__ achieved, uint32_t *__restrict__ status) {
+                          double *__restrict__ achieved, uint32_t *__restrict__ status,
+                          unsigned long long *__restrict__ next, int grab) {
   extern __shared__ double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
-  const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  forEachPointDynamic(n, next, grab, [&](long i) {
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s, a;
     uint32_t st = 0;
@@ -253,7 +254,7 @@ __global__ void __launch_bounds__(kThreads)
     __stcs(samp + i, s);
     if (achieved) __stcs(achieved + i, a);
     if (status) __stcs(status + i, st);
-  }
+  });
 }
 
 // ---- imageToGround -------------------------------------------------------------------------
@@ -382,14 +383,17 @@ cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const d
   size_t smemBytes;
   bool stage;
   LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  WorkCounter wc;
+  cudaError_t e = wc.acquire(stream);
+  if (e != cudaSuccess) return e;
   if (stage)
     pfGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status);
+        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
   else
     pfGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status);
+        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
   countLaunch();
-  return cudaGetLastError();
+  return wc.release();
 }
 
 cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const double *line,

@@ -11,6 +11,7 @@
 // and the range-coefficient table are staged once per persistent block into shared memory.
 #include "kernels.h"
 #include "device_math.cuh"
+#include "work_queue.cuh"
 
 namespace ub200 {
 
@@ -324,11 +325,11 @@ __global__ void __launch_bounds__(kThreads)
     sarGroundToImageKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z, double prec,
                            double *__restrict__ line, double *__restrict__ samp,
-                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
+                           double *__restrict__ achieved, uint32_t *__restrict__ status,
+                           unsigned long long *__restrict__ next, int grab) {
   extern __shared__ double smem[];
   SarTables T = stageSarTables(S, smem, STAGE);
-  const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  forEachPointDynamic(n, next, grab, [&](long i) {
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s;
     uint32_t st = 0;
@@ -341,7 +342,7 @@ __global__ void __launch_bounds__(kThreads)
     __stcs(samp + i, s);
     if (achieved) __stcs(achieved + i, nan(""));  // SAR groundToImage never writes achievedPrecision
     if (status) __stcs(status + i, st);
-  }
+  });
 }
 
 template <bool STAGE, bool GRID>
@@ -415,14 +416,19 @@ cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const
   if (stage) {
     cudaError_t e = allowSmem(sarGroundToImageKernel<true>, smemBytes);
     if (e != cudaSuccess) return e;
+  }
+  WorkCounter wc;
+  cudaError_t e = wc.acquire(stream);
+  if (e != cudaSuccess) return e;
+  if (stage) {
     sarGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status);
+        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
   } else {
     sarGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status);
+        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
   }
   countLaunch();
-  return cudaGetLastError();
+  return wc.release();
 }
 
 cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const double *line,

@@ -139,16 +139,19 @@ class RasterGM(object):
 
     # ---- batched per-point math ---------------------------------------------------------
     def groundToImageBatch(self, x, y, z, desiredPrecision=0.001, achieved=True, status=True,
-                           stream=None):
+                           stream=None, out=None):
         """groundToImage for arrays.  numpy in -> numpy out (host flavour, copies included);
         torch CUDA tensors in -> torch CUDA tensors out (device flavour, enqueued on `stream`
         or torch's current stream, not synchronised).  Returns (line, samp, achieved, status)."""
         if _is_torch(x):
             import torch
             n = x.numel()
-            line, samp = torch.empty_like(x), torch.empty_like(x)
-            ach = torch.empty_like(x) if achieved else None
-            st = torch.empty(n, dtype=torch.int32, device=x.device) if status else None
+            if out is not None:
+                line, samp, ach, st = out
+            else:
+                line, samp = torch.empty_like(x), torch.empty_like(x)
+                ach = torch.empty_like(x) if achieved else None
+                st = torch.empty(n, dtype=torch.int32, device=x.device) if status else None
             if stream is None:
                 stream = torch.cuda.current_stream(x.device).cuda_stream
             check(lib.usgscsm_b200_ground_to_image_dev(
