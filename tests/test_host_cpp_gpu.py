@@ -87,7 +87,7 @@ def test_aos_entry_points_equal_soa(kind):
         gm._h, n, ls.ctypes.data, h.ctypes.data, 1, 0.001, xyz.ctypes.data, ach.ctypes.data, st.ctypes.data))
     x, y, z, a, s = gm.imageToGroundBatch(ls[:, 0].copy(), ls[:, 1].copy(), h)
     assert np.array_equal(xyz[:, 0], x) and np.array_equal(xyz[:, 1], y) and np.array_equal(xyz[:, 2], z)
-    assert np.array_equal(ach, a) and np.array_equal(st, s)
+    assert np.array_equal(ach, a, equal_nan=True) and np.array_equal(st, s)
     back = np.empty((n, 2))
     _capi.check(_capi.lib.usgscsm_b200_ground_to_image_aos(
         gm._h, n, xyz.ctypes.data, 0.001, back.ctypes.data, ach.ctypes.data, st.ctypes.data))
