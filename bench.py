@@ -122,7 +122,7 @@ def sample_pixels(n_lines_total, target_points):
     return line, samp, "every %d-th line of the grid, all %d samples: %d points" % (k, N_SAMPLES, line.size)
 
 
-def cpu_reference_rate(state, n_lines_total, seconds, direction="g2i", proj=None):
+def cpu_reference_rate(state, n_lines_total, seconds, direction="g2i", proj=None, cores=None):
     """Reference CPU code (oracle/_ref, OpenMP over points, all host threads) on a bounded
     sample sized for about `seconds` of work.  Returns (Mpoints/s, cores, kind, sample, fn)
     where fn() re-times one pass over the sample."""
@@ -132,17 +132,19 @@ def cpu_reference_rate(state, n_lines_total, seconds, direction="g2i", proj=None
     rm = ref.RefModel(state)
     if proj is not None:
         rm.ls_set_projective(True, proj)
-    cores = ref.max_threads()
+    # every host core this process may run on -- not OMP_NUM_THREADS, which torchrun sets to 1
+    if cores is None:
+        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
 
     def run(line, samp):
         h = synth.synthetic_dem(line, samp)
-        x, y, z, _, _ = rm.image_to_ground(line, samp, h, PREC, threads=0)
+        x, y, z, _, _ = rm.image_to_ground(line, samp, h, PREC, threads=cores)
         if direction == "i2g":
             t = time.perf_counter()
-            rm.image_to_ground(line, samp, h, PREC, threads=0)
+            rm.image_to_ground(line, samp, h, PREC, threads=cores)
             return time.perf_counter() - t, None
         t = time.perf_counter()
-        rm.ground_to_image(x, y, z, PREC, threads=0)
+        rm.ground_to_image(x, y, z, PREC, threads=cores)
         return time.perf_counter() - t, (x, y, z)
 
     line, samp, _ = sample_pixels(n_lines_total, 40 * N_SAMPLES)
@@ -154,9 +156,9 @@ def cpu_reference_rate(state, n_lines_total, seconds, direction="g2i", proj=None
     def again():
         t = time.perf_counter()
         if direction == "i2g":
-            rm.image_to_ground(line, samp, synth.synthetic_dem(line, samp), PREC, threads=0)
+            rm.image_to_ground(line, samp, synth.synthetic_dem(line, samp), PREC, threads=cores)
         else:
-            rm.ground_to_image(pts[0], pts[1], pts[2], PREC, threads=0)
+            rm.ground_to_image(pts[0], pts[1], pts[2], PREC, threads=cores)
         return time.perf_counter() - t, line.size
 
     return line.size / dt / 1e6, cores, "reference", desc, again
@@ -219,6 +221,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # stdout carries ONE JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it
+        if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -351,6 +356,33 @@ def run_b200(args):
         "check": {"round_trip_max_px": err, "points_with_flags": flags},
     }
 
+    # second column: desiredPrecision 1e-8, what the reference's own CLI test
+    # uses (tests/CMakeLists.txt:30) -- more secant iterations per point
+    def g2i_tight():
+        _capi.check(_capi.lib.usgscsm_b200_ground_to_image_dev(
+            h_lib, n, x.data_ptr(), y.data_ptr(), z.data_ptr(), 1e-8, out_line.data_ptr(),
+            out_samp.data_ptr(), None, st_i.data_ptr(), stream))
+    g2i_tight()
+    tight_total_ms, tight_kern_ms = timed(g2i_tight, args.steps)
+    result["ground_to_image_prec_1e-8"] = {
+        "value": world * n * args.steps / (tight_total_ms * 1e-3) / 1e6, "unit": "Mpoints/s",
+        "kernel_ms": tight_kern_ms,
+        "evaluations_per_point": float(((st_i >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean().item())}
+
+    # imageToGround from explicit (line, samp) arrays (not the dense-grid tables): 52 B/pt
+    ex_line = (torch.arange(lines, device=dev, dtype=torch.float64) + line0).repeat_interleave(N_SAMPLES)
+    ex_samp = cols.repeat(lines)
+    def i2g_explicit():
+        _capi.check(_capi.lib.usgscsm_b200_image_to_ground_dev(
+            h_lib, n, ex_line.data_ptr(), ex_samp.data_ptr(), h.data_ptr(), 1, PREC,
+            out_line.data_ptr(), out_samp.data_ptr(), ex_line.data_ptr(), None, st_i.data_ptr(), stream))
+    i2g_explicit()
+    ex_total_ms, ex_kern_ms = timed(i2g_explicit, max(1, args.steps // 2))
+    result["image_to_ground_explicit"] = {
+        "value": world * n * max(1, args.steps // 2) / (ex_total_ms * 1e-3) / 1e6,
+        "unit": "Mpoints/s", "kernel_ms": ex_kern_ms}
+    del ex_line, ex_samp
+
     if not args.no_e2e:
         result["e2e"] = e2e(args, model, x, y, z, n, world, barrier, max_over_ranks)
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -359,6 +391,8 @@ def run_b200(args):
             v, cores, kind, desc, _ = cpu_reference_rate(state, lines, 15.0, proj=model.lsDerived()[5:19])
             result["cpu_baseline"] = {"value": v, "unit": "Mpoints/s", "cores": cores, "kind": kind,
                                       "sample": desc + ", groundToImage, OpenMP over points"}
+            v1, _, _, desc1, _ = cpu_reference_rate(state, lines, 4.0, proj=model.lsDerived()[5:19], cores=1)
+            result["cpu_baseline"]["single_thread"] = {"value": v1, "sample": desc1}
     if rank == 0 and world == 1 and not args.no_others:
         result["other_models"] = other_models(dev)
     if rank == 0:

@@ -171,6 +171,20 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int
                                      int height_stride, double prec, double *xyz,
                                      double *achieved, uint32_t *status);
 
+/* Several GPUs from one process (row-band / chunk sharding, no exchange step): models[g] are
+ * the SAME model state loaded on n_models different devices; contiguous chunk g of the host
+ * arrays (sizes differ by at most one point) is processed on models[g], all concurrently.
+ * For a dense grid stored row-major, contiguous chunks are contiguous row bands. */
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_multi(usgscsm_b200_model *const *models, int n_models,
+                                       int64_t n, const double *x, const double *y,
+                                       const double *z, double prec, double *line, double *samp,
+                                       double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_multi(usgscsm_b200_model *const *models, int n_models,
+                                       int64_t n, const double *line, const double *samp,
+                                       const double *height, int height_stride, double prec,
+                                       double *x, double *y, double *z, double *achieved,
+                                       uint32_t *status);
+
 /* Dense-grid imageToGround: the double loop of bin/usgscsm_cam_test.cc:294-309 (and of an
  * orthorectifier) with the pixel coordinates generated in the kernel.  Point k =
  * r * n_samps + c is pixel (line0 + r * dline, samp0 + c * dsamp), r < n_lines,

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/usgscsm_b200.h"
@@ -20,6 +21,20 @@ static std::atomic<int64_t> g_launches{0};
 void countLaunch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 static thread_local std::string g_lastError;
+
+static long envLong(const char *name, long def, long lo, long hi) {
+  const char *v = getenv(name);
+  long x = v && *v ? atol(v) : def;
+  return x < lo ? lo : (x > hi ? hi : x);
+}
+int pipelineSlots() {
+  static const int n = (int)envLong("USGSCSM_B200_PIPELINE_SLOTS", kDefaultPipelineSlots, 1, kMaxPipelineSlots);
+  return n;
+}
+long pipelineChunk() {
+  static const long n = envLong("USGSCSM_B200_PIPELINE_CHUNK", kDefaultPipelineChunk, 1024, 1L << 28);
+  return n;
+}
 
 int grabSize() {
   static const int grab = [] {
@@ -388,7 +403,8 @@ int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double 
   if (!x || !y || !z || !line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
-    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    const int kPipelineSlots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
     long c = 0;
     for (long off = 0; off < n; off += chunk, c++) {
       const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
@@ -427,7 +443,8 @@ int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double 
   if (!line || !samp || !height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
-    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    const int kPipelineSlots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
     long c = 0;
     for (long off = 0; off < n; off += chunk, c++) {
       const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
@@ -473,7 +490,8 @@ int usgscsm_b200_ground_to_image_aos(usgscsm_b200_model *m, int64_t n, const dou
   if (!xyz || !line_samp) return fail(USGSCSM_B200_EINVAL, "null array");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
-    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    const int kPipelineSlots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
     long c = 0;
     for (long off = 0; off < n; off += chunk, c++) {
       const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
@@ -511,7 +529,8 @@ int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n, const dou
   if (!line_samp || !height || !xyz) return fail(USGSCSM_B200_EINVAL, "null array");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
-    const long chunk = n < kPipelineChunk ? (long)n : kPipelineChunk;
+    const int kPipelineSlots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
     long c = 0;
     for (long off = 0; off < n; off += chunk, c++) {
       const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
@@ -543,6 +562,77 @@ int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n, const dou
     for (int si = 0; si < kPipelineSlots && si < c; si++)
       UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
     return USGSCSM_B200_OK;
+  });
+}
+
+// ---- several GPUs from one process -----------------------------------------------------------
+// Points are independent and the packed state is tiny, so a batch shards with no exchange
+// step: contiguous chunk g of the arrays goes to models[g] (the same state
+// loaded on different devices; sizes differ by at most one point), one host thread per model,
+// each running the chunked host-pointer pipeline on its own device.
+}  // extern "C"
+
+static void splitChunk(int64_t n, int parts, int g, int64_t &off, int64_t &cnt) {
+  const int64_t base = n / parts, extra = n % parts;
+  off = base * g + (g < extra ? g : extra);
+  cnt = base + (g < extra ? 1 : 0);
+}
+
+template <class F>
+static int runOnModels(usgscsm_b200_model *const *models, int n_models, int64_t n, F &&call) {
+  if (!models || n_models < 1 || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  for (int g = 0; g < n_models; g++) {
+    if (!models[g]) return fail(USGSCSM_B200_EINVAL, "null model");
+    for (int k = 0; k < g; k++)
+      if (models[k] == models[g]) return fail(USGSCSM_B200_EINVAL, "a model is listed twice");
+  }
+  std::vector<int> codes((size_t)n_models, USGSCSM_B200_OK);
+  std::vector<std::string> messages((size_t)n_models);
+  std::vector<std::thread> workers;
+  for (int g = 0; g < n_models; g++) {
+    workers.emplace_back([&, g]() {
+      int64_t off, cnt;
+      splitChunk(n, n_models, g, off, cnt);
+      codes[g] = call(models[g], off, cnt);
+      if (codes[g] != USGSCSM_B200_OK) messages[g] = g_lastError;  // the worker's own copy
+    });
+  }
+  for (std::thread &t : workers) t.join();
+  for (int g = 0; g < n_models; g++)
+    if (codes[g] != USGSCSM_B200_OK) {
+      g_lastError = "model " + std::to_string(g) + ": " + messages[g];
+      return codes[g];
+    }
+  return USGSCSM_B200_OK;
+}
+
+extern "C" {
+
+int usgscsm_b200_ground_to_image_multi(usgscsm_b200_model *const *models, int n_models, int64_t n,
+                                       const double *x, const double *y, const double *z,
+                                       double prec, double *line, double *samp, double *achieved,
+                                       uint32_t *status) {
+  if (n > 0 && (!x || !y || !z || !line || !samp)) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runOnModels(models, n_models, n, [&](usgscsm_b200_model *m, int64_t off, int64_t cnt) {
+    return usgscsm_b200_ground_to_image(m, cnt, x + off, y + off, z + off, prec, line + off,
+                                        samp + off, achieved ? achieved + off : nullptr,
+                                        status ? status + off : nullptr);
+  });
+}
+
+int usgscsm_b200_image_to_ground_multi(usgscsm_b200_model *const *models, int n_models, int64_t n,
+                                       const double *line, const double *samp,
+                                       const double *height, int height_stride, double prec,
+                                       double *x, double *y, double *z, double *achieved,
+                                       uint32_t *status) {
+  if (n > 0 && (!line || !samp || !height || !x || !y || !z))
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return runOnModels(models, n_models, n, [&](usgscsm_b200_model *m, int64_t off, int64_t cnt) {
+    return usgscsm_b200_image_to_ground(m, cnt, line + off, samp + off,
+                                        height_stride ? height + off : height, height_stride,
+                                        prec, x + off, y + off, z + off,
+                                        achieved ? achieved + off : nullptr,
+                                        status ? status + off : nullptr);
   });
 }
 

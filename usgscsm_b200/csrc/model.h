@@ -49,8 +49,12 @@ struct PipelineSlot {
   long aosCapacity = 0;
 };
 
-constexpr int kPipelineSlots = 3;
-constexpr long kPipelineChunk = 1L << 22;  // 4 Mi points per chunk (~200 MB of I/O)
+constexpr int kMaxPipelineSlots = 8;
+constexpr int kDefaultPipelineSlots = 3;
+constexpr long kDefaultPipelineChunk = 1L << 22;  // 4 Mi points per chunk (~200 MB of I/O)
+// USGSCSM_B200_PIPELINE_SLOTS / USGSCSM_B200_PIPELINE_CHUNK override the defaults (capi.cu)
+int pipelineSlots();
+long pipelineChunk();
 
 struct Model {
   int kind = 0;
@@ -78,7 +82,7 @@ struct Model {
   // ---- device side ---------------------------------------------------------------------
   std::vector<DeviceBuffer> owned;
   double *frameletOrient = nullptr;  // push-frame: device table behind ls.frameletOrient
-  PipelineSlot slots[kPipelineSlots];
+  PipelineSlot slots[kMaxPipelineSlots];
 
   ~Model();
   const double *upload(const std::vector<double> &v);
