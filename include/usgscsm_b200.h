@@ -115,6 +115,12 @@ USGSCSM_B200_API int usgscsm_b200_model_image_size(const usgscsm_b200_model *m, 
 USGSCSM_B200_API int usgscsm_b200_model_num_parameters(const usgscsm_b200_model *m);
 USGSCSM_B200_API int usgscsm_b200_model_get_parameter(const usgscsm_b200_model *m, int index, double *value);
 USGSCSM_B200_API int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double value);
+/* csm::SettableEllipsoid::setEllipsoid / getEllipsoid (LS:2116-2119, PF:1663-1666, FR:2235-2240,
+ * SAR:1884-1887): replaces the two radii; as in the reference nothing else is re-derived. */
+USGSCSM_B200_API int usgscsm_b200_model_set_ellipsoid(usgscsm_b200_model *m, double semi_major,
+                                     double semi_minor);
+USGSCSM_B200_API int usgscsm_b200_model_get_ellipsoid(const usgscsm_b200_model *m, double *semi_major,
+                                     double *semi_minor);
 /* Host-derived inputs of the line-scan per-point math:
  * out[0..3] = gsd, flyingHeight, halfSwath, halfTime; out[4] = useApproxInitTrans;
  * out[5..18] = the 14 projective-seed coefficients (LS:2688-2736); out[19..21] = reference
@@ -170,6 +176,39 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int
                                      const double *line_samp, const double *height,
                                      int height_stride, double prec, double *xyz,
                                      double *achieved, uint32_t *status);
+
+/* imageToRemoteImagingLocus: replaces csm::RasterGM::imageToRemoteImagingLocus(const ImageCoord&,
+ * double desiredPrecision, double* achievedPrecision, WarningList*) (LS:1254-1282, PF:1060-1082,
+ * FR:488-543, SAR:1009-1030) called once per pixel -- the call ray-tracing callers (DEM
+ * intersection) make.  Outputs SoA: locus point (px,py,pz) and direction (dx,dy,dz) of
+ * csm::EcefLocus (csm/csm.h:420-445).  Line-scan / push-frame: point = sensor position,
+ * direction = the look vector as the reference returns it; frame: point = parameters 0..2,
+ * unit direction; SAR: point = imageToGround at height 0, unit direction from the sensor.
+ * achieved (nullable): 0 for the optical models, the imageToGround value for SAR. */
+USGSCSM_B200_API int usgscsm_b200_image_to_remote_imaging_locus(usgscsm_b200_model *m, int64_t n,
+                                               const double *line, const double *samp,
+                                               double prec, double *px, double *py, double *pz,
+                                               double *dx, double *dy, double *dz,
+                                               double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_to_remote_imaging_locus_dev(usgscsm_b200_model *m, int64_t n,
+                                                   const double *line, const double *samp,
+                                                   double prec, double *px, double *py,
+                                                   double *pz, double *dx, double *dy, double *dz,
+                                                   double *achieved, uint32_t *status,
+                                                   void *stream);
+
+/* computeGroundPartials: replaces csm::RasterGM::computeGroundPartials(const EcefCoord&)
+ * (LS:1299-1325, PF:1091-1116, FR:955-1003, SAR:1384-1406), four groundToImage searches per
+ * point fused in one kernel.  partials: 6 doubles per point, [dLine/dX, dLine/dY, dLine/dZ,
+ * dSamp/dX, dSamp/dY, dSamp/dZ] (the std::vector the scalar call returns).  status: only the
+ * ERROR bits and NONFINITE (the scalar call has no warning list); a point whose scalar call
+ * would have thrown gets NaN partials. */
+USGSCSM_B200_API int usgscsm_b200_ground_partials(usgscsm_b200_model *m, int64_t n, const double *x,
+                                 const double *y, const double *z, double *partials,
+                                 uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_ground_partials_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+                                     const double *y, const double *z, double *partials,
+                                     uint32_t *status, void *stream);
 
 /* Several GPUs from one process (row-band / chunk sharding, no exchange step): models[g] are
  * the SAME model state loaded on n_models different devices; contiguous chunk g of the host

@@ -40,10 +40,23 @@ struct ImageVector {  // csm/csm.h:258-272
   ImageVector() : line(0.0), samp(0.0) {}
   ImageVector(double aLine, double aSamp) : line(aLine), samp(aSamp) {}
 };
+struct EcefVector {  // csm/csm.h:360-376
+  double x, y, z;
+  EcefVector() : x(0.0), y(0.0), z(0.0) {}
+  EcefVector(double aX, double aY, double aZ) : x(aX), y(aY), z(aZ) {}
+};
 struct EcefCoord {  // csm/csm.h:292-308
   double x, y, z;
   EcefCoord() : x(0.0), y(0.0), z(0.0) {}
   EcefCoord(double aX, double aY, double aZ) : x(aX), y(aY), z(aZ) {}
+};
+
+struct EcefLocus {  // csm/csm.h:420-445
+  EcefCoord point;
+  EcefVector direction;
+  EcefLocus() {}
+  EcefLocus(double ptX, double ptY, double ptZ, double dirX, double dirY, double dirZ)
+      : point(ptX, ptY, ptZ), direction(dirX, dirY, dirZ) {}
 };
 
 class Warning {  // csm/Warning.h:36-89
@@ -173,6 +186,53 @@ class RasterGM {
     raiseOrWarn(st, warnings, "imageToGround");
     if (achievedPrecision) *achievedPrecision = a;
     return csm::EcefCoord(x, y, z);
+  }
+
+  // LS:1254-1282, PF:1060-1082, FR:488-543, SAR:1009-1030
+  csm::EcefLocus imageToRemoteImagingLocus(const csm::ImageCoord &imagePt,
+                                           double desiredPrecision = 0.001,
+                                           double *achievedPrecision = NULL,
+                                           csm::WarningList *warnings = NULL) const {
+    double o[7] = {0, 0, 0, 0, 0, 0, 0};
+    uint32_t st = 0;
+    check(usgscsm_b200_image_to_remote_imaging_locus(m_h, 1, &imagePt.line, &imagePt.samp,
+                                                     desiredPrecision, o, o + 1, o + 2, o + 3,
+                                                     o + 4, o + 5, o + 6, &st),
+          "imageToRemoteImagingLocus");
+    raiseOrWarn(st, warnings, "imageToRemoteImagingLocus");
+    if (achievedPrecision) *achievedPrecision = o[6];
+    return csm::EcefLocus(o[0], o[1], o[2], o[3], o[4], o[5]);
+  }
+  // LS:1299-1325, PF:1091-1116, FR:955-1003, SAR:1384-1406
+  std::vector<double> computeGroundPartials(const csm::EcefCoord &groundPt) const {
+    std::vector<double> p(6, 0.0);
+    uint32_t st = 0;
+    check(usgscsm_b200_ground_partials(m_h, 1, &groundPt.x, &groundPt.y, &groundPt.z, &p[0], &st),
+          "computeGroundPartials");
+    raiseOrWarn(st, NULL, "computeGroundPartials");
+    return p;
+  }
+  // csm::SettableEllipsoid (LS:2116-2119)
+  void setEllipsoid(double semiMajorRadius, double semiMinorRadius) {
+    check(usgscsm_b200_model_set_ellipsoid(m_h, semiMajorRadius, semiMinorRadius), "setEllipsoid");
+  }
+
+  // whole arrays: loci (SoA: point px,py,pz and direction dx,dy,dz) and ground partials
+  // (6 doubles per point, the layout of the vector the scalar call returns)
+  void imageToRemoteImagingLocusBatch(size_t n, const double *line, const double *samp,
+                                      double desiredPrecision, double *px, double *py, double *pz,
+                                      double *dx, double *dy, double *dz,
+                                      double *achievedPrecision = NULL,
+                                      uint32_t *status = NULL) const {
+    check(usgscsm_b200_image_to_remote_imaging_locus(m_h, (int64_t)n, line, samp, desiredPrecision,
+                                                     px, py, pz, dx, dy, dz, achievedPrecision,
+                                                     status),
+          "imageToRemoteImagingLocusBatch");
+  }
+  void computeGroundPartialsBatch(size_t n, const double *x, const double *y, const double *z,
+                                  double *partials6n, uint32_t *status = NULL) const {
+    check(usgscsm_b200_ground_partials(m_h, (int64_t)n, x, y, z, partials6n, status),
+          "computeGroundPartialsBatch");
   }
 
   // ---- batched entry points: SoA host arrays (H2D/D2H inside) ------------------------------

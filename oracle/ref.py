@@ -43,6 +43,9 @@ def lib():
                                           _dp, _dp, _dp, C.c_int]
         L.ref_image_to_ground.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, C.c_int,
                                           C.c_double, _dp, _dp, _dp, _dp, _dp, C.c_int]
+        L.ref_remote_locus.argtypes = [C.c_void_p, C.c_long, _dp, _dp, C.c_double] + [_dp] * 8 + [C.c_int]
+        L.ref_ground_partials.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, _dp, C.c_int]
+        L.ref_set_ellipsoid.argtypes = [C.c_void_p, C.c_double, C.c_double]
         L.ref_lagrange.argtypes = [C.c_int, _dp, C.c_double, C.c_double, C.c_double, C.c_int,
                                    C.c_int, _dp]
         L.ref_remove_distortion.argtypes = [C.c_double, C.c_double, _dp, _dp, _dp, C.c_int,
@@ -130,6 +133,33 @@ class RefModel(object):
                                     y.ctypes.data, z.ctypes.data, ach.ctypes.data,
                                     st.ctypes.data, threads)
         return x, y, z, ach, st
+
+
+    def remote_locus(self, line, samp, prec=0.001, threads=1):
+        """imageToRemoteImagingLocus per pixel -> (px, py, pz, dx, dy, dz, achieved, status)."""
+        line = _a(line)
+        n = line.size
+        samp = _a(samp, n)
+        out = [np.empty(n) for _ in range(7)]
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_remote_locus(self._h, n, line.ctypes.data, samp.ctypes.data, prec,
+                                 *[o.ctypes.data for o in out], st.ctypes.data, threads)
+        return tuple(out) + (st,)
+
+    def ground_partials(self, x, y, z, threads=1):
+        """computeGroundPartials per point -> ((n, 6) partials, status)."""
+        x = _a(x)
+        n = x.size
+        y, z = _a(y, n), _a(z, n)
+        p = np.empty((n, 6))
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_ground_partials(self._h, n, x.ctypes.data, y.ctypes.data, z.ctypes.data,
+                                    p.ctypes.data, st.ctypes.data, threads)
+        return p, st
+
+    def set_ellipsoid(self, a, b):
+        if self._L.ref_set_ellipsoid(self._h, float(a), float(b)) != 0:
+            raise RuntimeError("model is not a csm::SettableEllipsoid")
 
 
 def max_threads():

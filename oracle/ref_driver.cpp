@@ -252,6 +252,89 @@ int ref_image_to_ground(void *h, long n, const double *line, const double *samp,
   return 0;
 }
 
+// imageToRemoteImagingLocus over n pixels (csm::RasterGM virtual; LS:1254-1282 etc.).
+int ref_remote_locus(void *h, long n, const double *line, const double *samp, double prec,
+                     double *px, double *py, double *pz, double *dx, double *dy, double *dz,
+                     double *achieved, uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    const double q = std::nan("");
+    csm::EcefLocus loc(q, q, q, q, q, q);
+    try {
+      csm::WarningList warn;
+      loc = gm->imageToRemoteImagingLocus(csm::ImageCoord(line[i], samp[i]), prec, &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+    }
+    if (!(std::isfinite(loc.point.x) && std::isfinite(loc.point.y) && std::isfinite(loc.point.z) &&
+          std::isfinite(loc.direction.x) && std::isfinite(loc.direction.y) &&
+          std::isfinite(loc.direction.z)))
+      st |= ST_NONFINITE;
+    px[i] = loc.point.x;
+    py[i] = loc.point.y;
+    pz[i] = loc.point.z;
+    dx[i] = loc.direction.x;
+    dy[i] = loc.direction.y;
+    dz[i] = loc.direction.z;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
+// computeGroundPartials over n points; partials = 6 doubles per point (LS:1299-1325 etc.).
+int ref_ground_partials(void *h, long n, const double *x, const double *y, const double *z,
+                        double *partials, uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    std::vector<double> p(6, std::nan(""));
+    try {
+      p = gm->computeGroundPartials(csm::EcefCoord(x[i], y[i], z[i]));
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+      p.assign(6, std::nan(""));
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+      p.assign(6, std::nan(""));
+    }
+    bool finite = true;
+    for (int k = 0; k < 6; k++) {
+      partials[6 * i + k] = p[k];
+      finite = finite && std::isfinite(p[k]);
+    }
+    if (!finite) st |= ST_NONFINITE;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
+// csm::SettableEllipsoid::setEllipsoid (LS:2116-2119 etc.).
+int ref_set_ellipsoid(void *h, double a, double b) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  csm::Model *m = rm->model.get();
+  const csm::Ellipsoid e(a, b);
+  if (auto *ls = dynamic_cast<UsgsAstroLsSensorModel *>(m)) ls->setEllipsoid(e);
+  else if (auto *pf = dynamic_cast<UsgsAstroPushFrameSensorModel *>(m)) pf->setEllipsoid(e);
+  else if (auto *fr = dynamic_cast<UsgsAstroFrameSensorModel *>(m)) fr->setEllipsoid(e);
+  else if (auto *sar = dynamic_cast<UsgsAstroSarSensorModel *>(m)) sar->setEllipsoid(e);
+  else return -1;
+  return 0;
+}
+
 // ---- L1 math entry points, for replaying the reference's known-answer tests ---------
 // (/root/reference/tests/UtilitiesTests.cpp, DistortionTests.cpp, EigenUtilitiesTests.cpp)
 

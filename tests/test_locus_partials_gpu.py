@@ -1,0 +1,113 @@
+"""Parity of the batched imageToRemoteImagingLocus, computeGroundPartials and setEllipsoid with
+the reference's per-point calls (LS:1254-1325, PF:1060-1116, FR:488-543 / 955-1003,
+SAR:1009-1030 / 1384-1406; setEllipsoid LS:2116-2119), all four sensor models."""
+import numpy as np
+import pytest
+
+from parity_util import M_TOL, PX_TOL, check_g2i, check_i2g, models, pixels
+
+pytestmark = pytest.mark.gpu
+
+
+def _cases():
+    from usgscsm_b200 import synth
+    return {
+        "linescan": synth.linescan_state(n_lines=2048, n_samples=512, seed=31),
+        "linescan_adjusted": synth.linescan_state(n_lines=1024, n_samples=512, seed=32,
+                                                  params=(3.0, 0, 0, 0, -0.01, 0, 0, 0.3, 0, 0, 0, 0, 0, 0, 0, 0.05)),
+        "pushframe": synth.pushframe_state(n_framelets=32, framelet_height=16, n_samples=512),
+        "frame": synth.frame_state(n_lines=1024, n_samples=1024),
+        "frame_transverse": synth.frame_state(distortion_type=1, dist_coeffs=(
+            0.0, 1.0, 0.0, 1e-6, 2e-6, -1e-6, 1e-8, 0.0, 2e-8, 0.0,
+            0.0, 0.0, 1.0, -1e-6, 1e-6, 2e-6, 0.0, 1e-8, 0.0, -2e-8)),
+        "sar": synth.sar_state(),
+    }
+
+
+def _pair(ref, kind):
+    state = _cases()[kind]
+    gm, rm = models(ref, state)
+    if kind.startswith("linescan"):
+        rm.ls_set_projective(True, gm.lsDerived()[5:19])
+    return gm, rm
+
+
+KINDS = ["linescan", "linescan_adjusted", "pushframe", "frame", "frame_transverse", "sar"]
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_remote_imaging_locus(ref, kind):
+    gm, rm = _pair(ref, kind)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(12)
+    line, samp = pixels(rng, 20000, nl, ns)
+    # a few pixels outside the image: the reference extrapolates, so must the kernel
+    line[:50] -= 30.0
+    samp[50:100] += ns
+    got = gm.imageToRemoteImagingLocusBatch(line, samp, 1e-5)
+    exp = rm.remote_locus(line, samp, 1e-5)
+    from usgscsm_b200 import _capi
+    assert np.array_equal(got[7] & _capi.ST_REFERENCE_MASK, exp[7])
+    ok = (exp[7] & _capi.ST_NONFINITE) == 0
+    for k in range(3):   # locus point, metres
+        assert np.abs(got[k][ok] - exp[k][ok]).max() <= M_TOL
+    for k in range(3, 6):  # direction (unit-scale)
+        assert np.abs(got[k][ok] - exp[k][ok]).max() <= 1e-12
+    fa = np.isfinite(exp[6])
+    assert np.array_equal(np.isfinite(got[6]), fa)
+    assert np.abs(got[6][fa] - exp[6][fa]).max(initial=0.0) <= M_TOL
+    # device-pointer flavour gives the same bits as the host flavour
+    import torch
+    tl, ts = torch.as_tensor(line, device="cuda"), torch.as_tensor(samp, device="cuda")
+    dev = gm.imageToRemoteImagingLocusBatch(tl, ts, 1e-5)
+    torch.cuda.synchronize()
+    for k in range(7):
+        assert np.array_equal(dev[k].cpu().numpy(), got[k], equal_nan=True)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_ground_partials(ref, kind):
+    from usgscsm_b200 import _capi, synth
+    gm, rm = _pair(ref, kind)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(13)
+    n = 3000 if kind == "sar" else 12000
+    line, samp = pixels(rng, n, nl, ns)
+    x, y, z, _, _ = gm.imageToGroundBatch(line, samp, synth.synthetic_dem(line, samp))
+    # some hopeless points too (far side of the body, NaN)
+    x[:20] *= -1.0
+    y[:20] *= -1.0
+    z[:20] *= -1.0
+    x[20:25] = np.nan
+    p, st = gm.computeGroundPartialsBatch(x, y, z)
+    ep, est = rm.ground_partials(x, y, z, threads=0)
+    assert np.array_equal(st & _capi.ST_REFERENCE_MASK, est)
+    ok = np.isfinite(ep).all(axis=1)
+    assert np.array_equal(np.isfinite(p).all(axis=1), ok)
+    assert ok.sum() > n * 0.9
+    # partials are pixel differences (each within PX_TOL of the reference's) divided by the step
+    scale = np.abs(ep[ok]).max()
+    assert np.abs(p[ok] - ep[ok]).max() <= 1e-9 * max(1.0, scale)
+    one = gm.computeGroundPartials((x[100], y[100], z[100]))
+    assert one == [float(v) for v in p[100]]
+    import torch
+    dp, dst = gm.computeGroundPartialsBatch(*(torch.as_tensor(a, device="cuda") for a in (x, y, z)))
+    torch.cuda.synchronize()
+    assert np.array_equal(dp.cpu().numpy(), p, equal_nan=True)
+    assert np.array_equal(dst.cpu().numpy().view(np.uint32), st)
+
+
+@pytest.mark.parametrize("kind", ["linescan", "pushframe", "frame", "sar"])
+def test_set_ellipsoid(ref, kind):
+    from usgscsm_b200 import synth
+    gm, rm = _pair(ref, kind)
+    a, b = gm.getEllipsoid()
+    gm.setEllipsoid(a + 1500.0, b - 2500.0)
+    rm.set_ellipsoid(a + 1500.0, b - 2500.0)
+    assert gm.getEllipsoid() == (a + 1500.0, b - 2500.0)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(14)
+    n = 4000
+    line, samp = pixels(rng, n, nl, ns)
+    x, y, z = check_i2g(gm, rm, line, samp, synth.synthetic_dem(line, samp))
+    check_g2i(gm, rm, x, y, z)

@@ -47,6 +47,8 @@ SIGNATURES = {
     "usgscsm_b200_model_num_parameters": (C.c_int, [_h]),
     "usgscsm_b200_model_get_parameter": (C.c_int, [_h, C.c_int, C.POINTER(C.c_double)]),
     "usgscsm_b200_model_set_parameter": (C.c_int, [_h, C.c_int, C.c_double]),
+    "usgscsm_b200_model_set_ellipsoid": (C.c_int, [_h, C.c_double, C.c_double]),
+    "usgscsm_b200_model_get_ellipsoid": (C.c_int, [_h, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "usgscsm_b200_model_ls_derived": (C.c_int, [_h, C.POINTER(C.c_double)]),
     "usgscsm_b200_model_ls_set_projective": (C.c_int, [_h, C.c_int, C.POINTER(C.c_double)]),
     "usgscsm_b200_ground_to_image": (
@@ -62,6 +64,12 @@ SIGNATURES = {
         C.c_int, [_h, C.c_int64, _dp, C.c_double, _dp, _dp, _dp]),
     "usgscsm_b200_image_to_ground_aos": (
         C.c_int, [_h, C.c_int64, _dp, _dp, C.c_int, C.c_double, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_remote_imaging_locus": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_remote_imaging_locus_dev": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_partials": (C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_partials_dev": (C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_ground_to_image_multi": (
         C.c_int, [C.POINTER(_h), C.c_int, C.c_int64, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_image_to_ground_multi": (

@@ -55,6 +55,7 @@ Model::~Model() {
     for (double *p : s.out) cudaFree(p);
     cudaFree(s.status);
     cudaFree(s.aos);
+    cudaFree(s.gen);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
   }
@@ -97,6 +98,17 @@ void Model::ensureAos(int s, long points) {
   p.aos = nullptr;
   UB_CUDA(cudaMalloc(&p.aos, points * 3 * sizeof(double)));
   p.aosCapacity = points;
+}
+
+void Model::ensureGen(int s, long doubles) {
+  PipelineSlot &p = slots[s];
+  if (!p.stream) UB_CUDA(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
+  if (!p.done) UB_CUDA(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
+  if (p.genDoubles >= doubles) return;
+  cudaFree(p.gen);
+  p.gen = nullptr;
+  UB_CUDA(cudaMalloc(&p.gen, doubles * sizeof(double)));
+  p.genDoubles = doubles;
 }
 
 // ---- error plumbing ---------------------------------------------------------------------
@@ -563,6 +575,164 @@ int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n, const dou
       UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
     return USGSCSM_B200_OK;
   });
+}
+
+// ---- imageToRemoteImagingLocus / computeGroundPartials ---------------------------------------
+static cudaError_t launchRemoteLocus(Model &m, long n, const double *line, const double *samp,
+                                     double prec, const LocusOut &o, cudaStream_t stream) {
+  switch (m.kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+      return launchLsRemoteLocus(m.ls, m.smCount, n, line, samp, o, stream);
+    case USGSCSM_B200_MODEL_PUSH_FRAME:
+      return launchPfRemoteLocus(m.ls, m.smCount, n, line, samp, o, stream);
+    case USGSCSM_B200_MODEL_FRAME:
+      return launchFrRemoteLocus(m.fr, m.smCount, n, line, samp, o, stream);
+    case USGSCSM_B200_MODEL_SAR:
+      return launchSarRemoteLocus(m.sar, m.smCount, n, line, samp, prec, o, stream);
+    default:
+      return cudaErrorNotSupported;
+  }
+}
+
+static cudaError_t launchGroundPartials(Model &m, long n, const double *x, const double *y,
+                                        const double *z, double *partials, uint32_t *status,
+                                        cudaStream_t stream) {
+  switch (m.kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+      return launchGroundPartialsLs(m.ls, m.smCount, n, x, y, z, partials, status, stream);
+    case USGSCSM_B200_MODEL_PUSH_FRAME:
+      return launchGroundPartialsPf(m.ls, m.smCount, n, x, y, z, partials, status, stream);
+    case USGSCSM_B200_MODEL_FRAME:
+      return launchGroundPartialsFr(m.fr, m.smCount, n, x, y, z, partials, status, stream);
+    case USGSCSM_B200_MODEL_SAR:
+      return launchGroundPartialsSar(m.sar, m.smCount, n, x, y, z, partials, status, stream);
+    default:
+      return cudaErrorNotSupported;
+  }
+}
+
+int usgscsm_b200_image_to_remote_imaging_locus_dev(usgscsm_b200_model *m, int64_t n,
+                                                   const double *line, const double *samp,
+                                                   double prec, double *px, double *py, double *pz,
+                                                   double *dx, double *dy, double *dz,
+                                                   double *achieved, uint32_t *status, void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp || !px || !py || !pz || !dx || !dy || !dz)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    LocusOut o{px, py, pz, dx, dy, dz, achieved, status};
+    UB_CUDA(launchRemoteLocus(*m, (long)n, line, samp, prec, o, static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_ground_partials_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+                                     const double *y, const double *z, double *partials,
+                                     uint32_t *status, void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!x || !y || !z || !partials) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    UB_CUDA(launchGroundPartials(*m, (long)n, x, y, z, partials, status,
+                                 static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_remote_imaging_locus(usgscsm_b200_model *m, int64_t n, const double *line,
+                                               const double *samp, double prec, double *px,
+                                               double *py, double *pz, double *dx, double *dy,
+                                               double *dz, double *achieved, uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp || !px || !py || !pz || !dx || !dy || !dz)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const int nslots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    double *host[7] = {px, py, pz, dx, dy, dz, achieved};
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % nslots);
+      m->ensureGen(si, chunk * 10);  // 2 in + 7 out + status
+      PipelineSlot &s = m->slots[si];
+      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      double *dl = s.gen, *ds = s.gen + chunk, *dout = s.gen + 2 * chunk;
+      uint32_t *dst = reinterpret_cast<uint32_t *>(s.gen + 9 * chunk);
+      UB_CUDA(cudaMemcpyAsync(dl, line + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(ds, samp + off, b, cudaMemcpyHostToDevice, s.stream));
+      LocusOut o{dout, dout + chunk, dout + 2 * chunk, dout + 3 * chunk, dout + 4 * chunk,
+                 dout + 5 * chunk, achieved ? dout + 6 * chunk : nullptr, status ? dst : nullptr};
+      UB_CUDA(launchRemoteLocus(*m, cnt, dl, ds, prec, o, s.stream));
+      for (int k = 0; k < 7; k++)
+        if (host[k])
+          UB_CUDA(cudaMemcpyAsync(host[k] + off, dout + k * chunk, b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_ground_partials(usgscsm_b200_model *m, int64_t n, const double *x, const double *y,
+                                 const double *z, double *partials, uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!x || !y || !z || !partials) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const int nslots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % nslots);
+      m->ensureGen(si, chunk * 10);  // 3 in + 6 out + status
+      PipelineSlot &s = m->slots[si];
+      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      double *dx = s.gen, *dy = s.gen + chunk, *dz = s.gen + 2 * chunk, *dp = s.gen + 3 * chunk;
+      uint32_t *dst = reinterpret_cast<uint32_t *>(s.gen + 9 * chunk);
+      UB_CUDA(cudaMemcpyAsync(dx, x + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(dy, y + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(dz, z + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launchGroundPartials(*m, cnt, dx, dy, dz, dp, status ? dst : nullptr, s.stream));
+      UB_CUDA(cudaMemcpyAsync(partials + 6 * off, dp, 6 * b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+// csm::SettableEllipsoid::setEllipsoid / getEllipsoid (LS:2116-2119, PF:1663-1666,
+// FR:2235-2240, SAR:1884-1887): replaces the two radii, nothing else is re-derived.
+int usgscsm_b200_model_set_ellipsoid(usgscsm_b200_model *m, double semi_major, double semi_minor) {
+  if (!m) return fail(USGSCSM_B200_EINVAL, "null argument");
+  Ellipsoid &e = m->kind == USGSCSM_B200_MODEL_FRAME ? m->fr.ell
+                 : m->kind == USGSCSM_B200_MODEL_SAR ? m->sar.ell : m->ls.ell;
+  setEllipsoidRadii(e, semi_major, semi_minor);
+  return USGSCSM_B200_OK;
+}
+
+int usgscsm_b200_model_get_ellipsoid(const usgscsm_b200_model *m, double *semi_major,
+                                     double *semi_minor) {
+  if (!m || !semi_major || !semi_minor) return fail(USGSCSM_B200_EINVAL, "null argument");
+  const Ellipsoid &e = m->kind == USGSCSM_B200_MODEL_FRAME ? m->fr.ell
+                       : m->kind == USGSCSM_B200_MODEL_SAR ? m->sar.ell : m->ls.ell;
+  *semi_major = e.majorAxis;
+  *semi_minor = e.minorAxis;
+  return USGSCSM_B200_OK;
 }
 
 // ---- several GPUs from one process -----------------------------------------------------------

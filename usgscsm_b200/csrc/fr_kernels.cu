@@ -174,6 +174,76 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// computeGroundPartials FR:955-1003: the step is the ground size of a pixel, from
+// imageToGround (height 0) of the pixel one line and one sample further (one back if that
+// collapses); then forward differences of groundToImage at default precision.
+__global__ void __launch_bounds__(kThreads)
+    frGroundPartialsKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z,
+                           double *__restrict__ partials, uint32_t *__restrict__ status) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double g[3] = {__ldcs(x + i), __ldcs(y + i), __ldcs(z + i)};
+    double l[4], s[4];
+    uint32_t st = 0;
+    frGroundToImagePoint(S, g[0], g[1], g[2], 0.001, l[0], s[0], st);
+    double nx, ny, nz;
+    frImageToGroundPoint(S, l[0] + 1, s[0] + 1, 0.0, nx, ny, nz, st);
+    double dx = nx - g[0], dy = ny - g[1], dz = nz - g[2];
+    double delta = sqrt((dx * dx + dy * dy + dz * dz) / 2.0);
+    if (delta < 1e-10) {
+      frImageToGroundPoint(S, l[0] - 1, s[0] - 1, 0.0, nx, ny, nz, st);
+      dx = nx - g[0];
+      dy = ny - g[1];
+      dz = nz - g[2];
+      delta = sqrt((dx * dx + dy * dy + dz * dz) / 2.0);
+    }
+#pragma unroll 1
+    for (int k = 1; k < 4; k++) {
+      double q[3] = {g[0], g[1], g[2]};
+      q[k - 1] = g[k - 1] + delta;
+      frGroundToImagePoint(S, q[0], q[1], q[2], 0.001, l[k], s[k], st);
+    }
+    double p[6];
+    p[0] = (l[1] - l[0]) / delta;
+    p[3] = (s[1] - s[0]) / delta;
+    p[1] = (l[2] - l[0]) / delta;
+    p[4] = (s[2] - s[0]) / delta;
+    p[2] = (l[3] - l[0]) / delta;
+    p[5] = (s[3] - s[0]) / delta;
+    storePartials(partials, status, i, p, st);
+  }
+}
+
+// imageToRemoteImagingLocus FR:488-543: no de-jittering; point = the RAW parameters 0..2
+// (m_currentParameterValue), direction = unit(m * (ux, uy, f)); achievedPrecision = 0.
+__global__ void __launch_bounds__(kThreads)
+    frRemoteLocusKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ line,
+                        const double *__restrict__ samp, LocusOut o) {
+  const double *m = S.mNorm;
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t st = 0;
+    double focalPlaneX, focalPlaneY;
+    distortedFocalPlaneCoordinates(__ldcs(line + i), __ldcs(samp + i), S.fp, focalPlaneX, focalPlaneY);
+    double ux, uy;
+    removeDistortion(focalPlaneX, focalPlaneY, ux, uy, S.fp, 1.0E-6, st);
+    const double f = S.fp.focalLength;
+    double lookB[3] = {m[0] * ux + m[1] * uy + m[2] * f, m[3] * ux + m[4] * uy + m[5] * f,
+                       m[6] * ux + m[7] * uy + m[8] * f};
+    double mag = sqrt(lookB[0] * lookB[0] + lookB[1] * lookB[1] + lookB[2] * lookB[2]);
+    double dir[3] = {lookB[0] / mag, lookB[1] / mag, lookB[2] / mag};
+    double pos[3] = {S.rawParams[0], S.rawParams[1], S.rawParams[2]};
+    if (st & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+      st = USGSCSM_B200_ST_ERROR_ALGORITHM;
+      pos[0] = pos[1] = pos[2] = dir[0] = dir[1] = dir[2] = nan("");
+    }
+    if (!(finite3(pos[0], pos[1], pos[2]) && finite3(dir[0], dir[1], dir[2])))
+      st |= USGSCSM_B200_ST_NONFINITE;
+    storeLocus(o, i, pos, dir, 0.0, st);
+  }
+}
+
 int frBlocks(long n, int smCount) {
   long blocksNeeded = (n + kThreads - 1) / kThreads;
   long persistent = (long)smCount * 8;  // light kernels: 8 resident blocks of 256 per SM
@@ -207,6 +277,23 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
   else
     frImageToGroundKernel<false><<<frBlocks(n, smCount), kThreads, 0, stream>>>(
         S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchFrRemoteLocus(const FrameState &S, int smCount, long n, const double *line,
+                                const double *samp, const LocusOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  frRemoteLocusKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, line, samp, o);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchGroundPartialsFr(const FrameState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double *partials,
+                                   uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  frGroundPartialsKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, partials, status);
   countLaunch();
   return cudaGetLastError();
 }

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/usgscsm_b200.h"
 #include "sensor_state.h"
 
 namespace ub200 {
@@ -30,6 +31,58 @@ struct GridSpec {
 
 void countLaunch();
 
+// Outputs of imageToRemoteImagingLocus (csm::EcefLocus = point + direction, csm/csm.h:420-445),
+// SoA; achieved / status nullable.
+struct LocusOut {
+  double *px, *py, *pz, *dx, *dy, *dz, *achieved;
+  uint32_t *status;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ void storeLocus(const LocusOut &o, long i, const double p[3],
+                                           const double d[3], double achieved, uint32_t st) {
+  __stcs(o.px + i, p[0]);
+  __stcs(o.py + i, p[1]);
+  __stcs(o.pz + i, p[2]);
+  __stcs(o.dx + i, d[0]);
+  __stcs(o.dy + i, d[1]);
+  __stcs(o.dz + i, d[2]);
+  if (o.achieved) __stcs(o.achieved + i, achieved);
+  if (o.status) __stcs(o.status + i, st);
+}
+// computeGroundPartials: the scalar call has no warning list and lets a thrown csm::Error
+// escape, so only the error bits of its four groundToImage calls are observable; a point
+// that would have thrown gets NaN partials.  partials: 6 doubles per point,
+// [dLine/dX, dLine/dY, dLine/dZ, dSamp/dX, dSamp/dY, dSamp/dZ] (LS:1296-1298).
+__device__ __forceinline__ void storePartials(double *__restrict__ partials,
+                                              uint32_t *__restrict__ status, long i, double p[6],
+                                              uint32_t st) {
+  st &= (USGSCSM_B200_ST_ERROR_ALGORITHM | USGSCSM_B200_ST_ERROR_UNKNOWN |
+         USGSCSM_B200_ST_ERROR_OTHER);
+  bool finite = true;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    if (st) p[k] = nan("");
+    finite = finite && isfinite(p[k]);
+    __stcs(partials + 6 * i + k, p[k]);
+  }
+  if (!finite) st |= USGSCSM_B200_ST_NONFINITE;
+  if (status) __stcs(status + i, st);
+}
+#endif
+
+cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double *partials,
+                                   uint32_t *status, cudaStream_t stream);
+cudaError_t launchGroundPartialsPf(const LsState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double *partials,
+                                   uint32_t *status, cudaStream_t stream);
+cudaError_t launchGroundPartialsFr(const FrameState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double *partials,
+                                   uint32_t *status, cudaStream_t stream);
+cudaError_t launchGroundPartialsSar(const SarState &S, int smCount, long n, const double *x,
+                                    const double *y, const double *z, double *partials,
+                                    uint32_t *status, cudaStream_t stream);
+
 cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const double *x,
                                   const double *y, const double *z, double prec, double *line,
                                   double *samp, double *achieved, uint32_t *status,
@@ -38,6 +91,16 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
                                   const double *samp, const GridSpec *grid, const double *height,
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream);
+
+cudaError_t launchLsRemoteLocus(const LsState &S, int smCount, long n, const double *line,
+                                const double *samp, const LocusOut &o, cudaStream_t stream);
+cudaError_t launchPfRemoteLocus(const LsState &S, int smCount, long n, const double *line,
+                                const double *samp, const LocusOut &o, cudaStream_t stream);
+cudaError_t launchFrRemoteLocus(const FrameState &S, int smCount, long n, const double *line,
+                                const double *samp, const LocusOut &o, cudaStream_t stream);
+cudaError_t launchSarRemoteLocus(const SarState &S, int smCount, long n, const double *line,
+                                 const double *samp, double prec, const LocusOut &o,
+                                 cudaStream_t stream);
 
 // push-frame (pf_kernels.cu)
 cudaError_t launchPfFrameletOrientations(const LsState &S, double *out, cudaStream_t stream);

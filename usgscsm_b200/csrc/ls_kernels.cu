@@ -354,6 +354,98 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// ---- computeGroundPartials ----------------------------------------------------------------
+// LS:1299-1325: groundToImage (default precision 0.001) at the point and at the point moved by
+// m_gsd along X, Y, Z; forward differences.  One kernel, four searches per point.
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads, kDefaultMinBlocks)
+    lsGroundPartialsKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z,
+                           double *__restrict__ partials, uint32_t *__restrict__ status,
+                           unsigned long long *__restrict__ next, int grab) {
+  extern __shared__ __align__(16) double smem[];
+  StagedTables TS{};
+  OrientationTables TG{S.positions.values, S.velocities.values, S.quaternions.values};
+  if (STAGE) TS = stageOrientationTables(S, S.hasAdj != 0, smem);
+  forEachPointDynamic(n, next, grab, [&](long i) {
+    const double g[3] = {__ldcs(x + i), __ldcs(y + i), __ldcs(z + i)};
+    const double delta = S.gsd;
+    double l[4], s[4];
+    uint32_t st = 0;
+#pragma unroll 1
+    for (int k = 0; k < 4; k++) {
+      double q[3] = {g[0], g[1], g[2]};
+      if (k) q[k - 1] = g[k - 1] + delta;
+      double a;
+      uint32_t sk = 0;
+      if (STAGE)
+        lsGroundToImagePoint<false>(S, TS, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+      else
+        lsGroundToImagePoint<false>(S, TG, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+      st |= sk;
+    }
+    double p[6];
+    p[0] = (l[1] - l[0]) / delta;
+    p[3] = (s[1] - s[0]) / delta;
+    p[1] = (l[2] - l[0]) / delta;
+    p[4] = (s[2] - s[0]) / delta;
+    p[2] = (l[3] - l[0]) / delta;
+    p[5] = (s[3] - s[0]) / delta;
+    storePartials(partials, status, i, p, st);
+  });
+}
+
+// ---- imageToRemoteImagingLocus -----------------------------------------------------------
+// LS:1254-1282: losToEcf (LS:2209-2305) at the pixel; point = sensor position, direction =
+// MINUS the body-fixed look vector losToEcf returns (the reference negates it, LS:1267-1270);
+// achievedPrecision = 0.  Callers ray-trace DEMs from this.
+template <class TAB>
+UB_DEV void lsRemoteLocusPoint(const LsState &S, const TAB &T, double line, double sample,
+                               double pos[3], double dir[3], uint32_t &status) {
+  double time = lsImageTime(S, line);
+  double vel[3];
+  adjSensorPosVel<false>(S, T, time, pos, vel);
+  double distortedFocalPlaneX, distortedFocalPlaneY;
+  distortedFocalPlaneCoordinates(0.0, sample, S.fp, distortedFocalPlaneX, distortedFocalPlaneY);
+  double undistortedFocalPlaneX, undistortedFocalPlaneY;
+  removeDistortion(distortedFocalPlaneX, distortedFocalPlaneY, undistortedFocalPlaneX,
+                   undistortedFocalPlaneY, S.fp, 1.0E-6, status);
+  double cameraLook[3];
+  cameraLookVector(undistortedFocalPlaneX, undistortedFocalPlaneY, S.fp.zDirection,
+                   S.fp.focalLength * (1 - param(S, 15) / S.halfSwath), cameraLook);
+  double bodyLook[3];
+  cameraLookToBody(S, T, time, cameraLook, bodyLook);
+  dir[0] = -bodyLook[0];
+  dir[1] = -bodyLook[1];
+  dir[2] = -bodyLook[2];
+  if (status & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+    status = USGSCSM_B200_ST_ERROR_ALGORITHM;
+    pos[0] = pos[1] = pos[2] = dir[0] = dir[1] = dir[2] = nan("");
+  }
+  if (!(finite3(pos[0], pos[1], pos[2]) && finite3(dir[0], dir[1], dir[2])))
+    status |= USGSCSM_B200_ST_NONFINITE;
+}
+
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    lsRemoteLocusKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                        const double *__restrict__ samp, LocusOut o) {
+  extern __shared__ __align__(16) double smem[];
+  StagedTables TS{};
+  OrientationTables TG{S.positions.values, S.velocities.values, S.quaternions.values};
+  if (STAGE) TS = stageOrientationTables(S, S.hasAdj != 0, smem);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double pos[3], dir[3];
+    uint32_t st = 0;
+    if (STAGE)
+      lsRemoteLocusPoint(S, TS, __ldcs(line + i), __ldcs(samp + i), pos, dir, st);
+    else
+      lsRemoteLocusPoint(S, TG, __ldcs(line + i), __ldcs(samp + i), pos, dir, st);
+    storeLocus(o, i, pos, dir, 0.0, st);
+  }
+}
+
 // ---- model set-up helpers -------------------------------------------------------------------
 // The reference derives a few per-model inputs of the hot path at load time with its own
 // per-point routines (updateState LS:649-735, createProjectiveApproximation LS:2745-2803).
@@ -514,6 +606,48 @@ cudaError_t launchEllipsoidElevation(const Ellipsoid &ell, int n, const double *
   ellipsoidElevationKernel<<<(n + 63) / 64, 64, 0, stream>>>(ell, n, xyz, prec, h);
   countLaunch();
   return cudaGetLastError();
+}
+
+cudaError_t launchLsRemoteLocus(const LsState &S, int smCount, long n, const double *line,
+                                const double *samp, const LocusOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kBlocksPerSm);
+  if (stage) {
+    if (smemBytes > 48 * 1024)
+      cudaFuncSetAttribute(lsRemoteLocusKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)smemBytes);
+    lsRemoteLocusKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, line, samp, o);
+  } else {
+    lsRemoteLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, o);
+  }
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double *partials,
+                                   uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kDefaultMinBlocks);
+  WorkCounter wc;
+  cudaError_t e = wc.acquire(stream);
+  if (e != cudaSuccess) return e;
+  if (stage) {
+    if (smemBytes > 48 * 1024)
+      cudaFuncSetAttribute(lsGroundPartialsKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)smemBytes);
+    lsGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+  } else {
+    lsGroundPartialsKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+  }
+  countLaunch();
+  return wc.release();
 }
 
 }  // namespace ub200

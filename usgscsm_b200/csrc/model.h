@@ -45,6 +45,8 @@ struct PipelineSlot {
   double *out[4] = {nullptr, nullptr, nullptr, nullptr};  // up to x,y,z,achieved
   uint32_t *status = nullptr;
   long capacity = 0;  // points
+  double *gen = nullptr;  // generic scratch of the locus / partials entry points
+  long genDoubles = 0;
   double *aos = nullptr;  // AoS flavours: 3 doubles per point, input then output of a chunk
   long aosCapacity = 0;
 };
@@ -88,6 +90,7 @@ struct Model {
   const double *upload(const std::vector<double> &v);
   void ensureSlot(int s, long points);
   void ensureAos(int s, long points);
+  void ensureGen(int s, long doubles);
 };
 
 // model_ls.cu
@@ -109,6 +112,7 @@ void repackSar(Model &m);
 // shared readers (model_ls.cu)
 void readFocalPlane(FocalPlane &fp, const class StateReader &st, bool lineScanTypes);
 void readEllipsoid(Ellipsoid &e, const class StateReader &st);
+void setEllipsoidRadii(Ellipsoid &e, double a, double b);
 void readOrientation(Model &m, const class StateReader &st);
 
 // projective_fit.cpp

@@ -15,6 +15,7 @@ void checkDistortionCoeffs(int type, size_t n);  // model_ls.cu
 void repackFrame(Model &m) {
   FrameState &S = m.fr;
   for (int i = 0; i < 7; i++) S.params[i] = m.params[i] + 0.0;  // getValue(i, m_noAdjustments)
+  for (int i = 0; i < 3; i++) S.rawParams[i] = m.params[i];
   {
     // calcRotationMatrix(m) FR:2242-2265 reads m_currentParameterValue directly
     double x = m.params[3], y = m.params[4], z = m.params[5], w = m.params[6];

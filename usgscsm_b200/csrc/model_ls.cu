@@ -173,6 +173,8 @@ void readFocalPlane(FocalPlane &fp, const StateReader &st, bool lineScanTypes) {
   fillDivisors({&fp.lineSumming, &fp.sampleSumming});
 }
 
+void setEllipsoidRadii(Ellipsoid &e, double a, double b) { fillEllipsoid(e, a, b); }
+
 void readEllipsoid(Ellipsoid &e, const StateReader &st) {
   fillEllipsoid(e, st.getDouble("m_majorAxis"), st.getDouble("m_minorAxis"));
 }

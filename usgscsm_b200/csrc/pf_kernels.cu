@@ -335,6 +335,99 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// computeGroundPartials PF:1091-1116: as the line-scan model's, delta = m_gsd.
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    pfGroundPartialsKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z,
+                           double *__restrict__ partials, uint32_t *__restrict__ status,
+                           unsigned long long *__restrict__ next, int grab) {
+  extern __shared__ double smem[];
+  OrientCache C = stageOrientCache(S, smem, STAGE);
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  forEachPointDynamic(n, next, grab, [&](long i) {
+    const double g[3] = {__ldcs(x + i), __ldcs(y + i), __ldcs(z + i)};
+    const double delta = S.gsd;
+    double l[4], s[4];
+    uint32_t st = 0;
+#pragma unroll 1
+    for (int k = 0; k < 4; k++) {
+      double q[3] = {g[0], g[1], g[2]};
+      if (k) q[k - 1] = g[k - 1] + delta;
+      double a;
+      uint32_t sk = 0;
+      pfGroundToImagePoint(S, T, C, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+      st |= sk;
+    }
+    double p[6];
+    p[0] = (l[1] - l[0]) / delta;
+    p[3] = (s[1] - s[0]) / delta;
+    p[1] = (l[2] - l[0]) / delta;
+    p[4] = (s[2] - s[0]) / delta;
+    p[2] = (l[3] - l[0]) / delta;
+    p[5] = (s[3] - s[0]) / delta;
+    storePartials(partials, status, i, p, st);
+  });
+}
+
+// imageToRemoteImagingLocus PF:1060-1082: losToEcf (PF:1726-1824) at the pixel; point = sensor
+// position of the pixel's framelet, direction = minus the body-fixed look vector.
+UB_DEV void pfRemoteLocusPoint(const LsState &S, const OrientationTables &T, const OrientCache &C,
+                               double line, double sample, double pos[3], double dir[3],
+                               uint32_t &status) {
+  int frameletNumber = pfTimeFramelet(S, line);
+  Orientation o;
+  orientationAt(S, T, C, frameletNumber, o);
+  double frameletLine = fmod(line, (double)S.summedFrameletHeight);
+  if (S.frameletsFlipped) frameletLine = S.summedFrameletHeight - frameletLine;
+  frameletLine += S.halfOverlap;
+  double distortedFocalPlaneX, distortedFocalPlaneY;
+  distortedFocalPlaneCoordinates(frameletLine, sample, S.fp, distortedFocalPlaneX,
+                                 distortedFocalPlaneY);
+  double undistortedFocalPlaneX, undistortedFocalPlaneY;
+  removeDistortion(distortedFocalPlaneX, distortedFocalPlaneY, undistortedFocalPlaneX,
+                   undistortedFocalPlaneY, S.fp, 1.0E-6, status);
+  double cameraLook[3];
+  cameraLookVector(undistortedFocalPlaneX, undistortedFocalPlaneY, S.fp.zDirection,
+                   S.fp.focalLength * (1 - param(S, 15) / S.halfSwath), cameraLook);
+  double corrected[3];
+  if (S.hasAttAdj) {
+    matVec(o.attCorr, cameraLook, corrected);
+  } else {
+    corrected[0] = cameraLook[0];
+    corrected[1] = cameraLook[1];
+    corrected[2] = cameraLook[2];
+  }
+  double bodyLook[3];
+  matVec(o.camToBody, corrected, bodyLook);
+  for (int k = 0; k < 3; k++) {
+    pos[k] = o.pos[k];
+    dir[k] = -bodyLook[k];
+  }
+  if (status & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+    status = USGSCSM_B200_ST_ERROR_ALGORITHM;
+    pos[0] = pos[1] = pos[2] = dir[0] = dir[1] = dir[2] = nan("");
+  }
+  if (!(finite3(pos[0], pos[1], pos[2]) && finite3(dir[0], dir[1], dir[2])))
+    status |= USGSCSM_B200_ST_NONFINITE;
+}
+
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    pfRemoteLocusKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                        const double *__restrict__ samp, LocusOut o) {
+  extern __shared__ double smem[];
+  OrientCache C = stageOrientCache(S, smem, STAGE);
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double pos[3], dir[3];
+    uint32_t st = 0;
+    pfRemoteLocusPoint(S, T, C, __ldcs(line + i), __ldcs(samp + i), pos, dir, st);
+    storeLocus(o, i, pos, dir, 0.0, st);
+  }
+}
+
 // getSensorPosition(double time) PF:1290-1303: getAdjSensorPosVel at `time`.
 __global__ void pfSensorPositionKernel(const __grid_constant__ LsState S, double time,
                                        double *__restrict__ xyz) {
@@ -419,6 +512,40 @@ cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const d
 #undef UB_LAUNCH_PF
   countLaunch();
   return cudaGetLastError();
+}
+
+cudaError_t launchPfRemoteLocus(const LsState &S, int smCount, long n, const double *line,
+                                const double *samp, const LocusOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  if (stage)
+    pfRemoteLocusKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, line, samp, o);
+  else
+    pfRemoteLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, o);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchGroundPartialsPf(const LsState &S, int smCount, long n, const double *x,
+                                   const double *y, const double *z, double *partials,
+                                   uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  WorkCounter wc;
+  cudaError_t e = wc.acquire(stream);
+  if (e != cudaSuccess) return e;
+  if (stage)
+    pfGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+  else
+    pfGroundPartialsKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+  countLaunch();
+  return wc.release();
 }
 
 }  // namespace ub200

@@ -378,6 +378,65 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// computeGroundPartials SAR:1384-1406: delta = m_scaledPixelWidth.
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    sarGroundPartialsKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
+                            const double *__restrict__ y, const double *__restrict__ z,
+                            double *__restrict__ partials, uint32_t *__restrict__ status,
+                            unsigned long long *__restrict__ next, int grab) {
+  extern __shared__ double smem[];
+  SarTables T = stageSarTables(S, smem, STAGE);
+  forEachPointDynamic(n, next, grab, [&](long i) {
+    const double g[3] = {__ldcs(x + i), __ldcs(y + i), __ldcs(z + i)};
+    const double delta = S.scaledPixelWidth;
+    double l[4], s[4];
+    uint32_t st = 0;
+#pragma unroll 1
+    for (int k = 0; k < 4; k++) {
+      double q[3] = {g[0], g[1], g[2]};
+      if (k) q[k - 1] = g[k - 1] + delta;
+      uint32_t sk = 0;
+      sarGroundToImagePoint(S, T, q[0], q[1], q[2], 0.001, l[k], s[k], sk);
+      st |= sk;
+    }
+    double p[6];
+    p[0] = (l[1] - l[0]) / delta;
+    p[3] = (s[1] - s[0]) / delta;
+    p[1] = (l[2] - l[0]) / delta;
+    p[4] = (s[2] - s[0]) / delta;
+    p[2] = (l[3] - l[0]) / delta;
+    p[5] = (s[3] - s[0]) / delta;
+    storePartials(partials, status, i, p, st);
+  });
+}
+
+// imageToRemoteImagingLocus SAR:1009-1030: point = imageToGround at height 0, direction =
+// normalized(ground - getSensorPosition(imagePt)) with normalized() = (1 / norm) * v (U:972-974);
+// achievedPrecision and warnings are those of the imageToGround call.
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    sarRemoteLocusKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ line,
+                         const double *__restrict__ samp, double prec, LocusOut o) {
+  extern __shared__ double smem[];
+  SarTables T = stageSarTables(S, smem, STAGE);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l = __ldcs(line + i), s = __ldcs(samp + i);
+    double time = S.startingEphemerisTime + (l - 0.5) * S.exposureDuration;
+    double sensor[3], vel[3];
+    sarPosVel(S, T, time, sensor, vel);
+    double g[3], a;
+    uint32_t st = 0;
+    sarImageToGroundPoint(S, T, l, s, 0.0, prec, g[0], g[1], g[2], a, st);
+    double v[3] = {g[0] - sensor[0], g[1] - sensor[1], g[2] - sensor[2]};
+    double inv = 1.0 / sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    double dir[3] = {inv * v[0], inv * v[1], inv * v[2]};
+    if (!finite3(dir[0], dir[1], dir[2])) st |= USGSCSM_B200_ST_NONFINITE;
+    storeLocus(o, i, g, dir, a, st);
+  }
+}
+
 LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
   size_t bytes = sarTableBytes(S);
   stage = bytes <= kSarMaxStagedBytes;
@@ -458,6 +517,48 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
 #undef UB_LAUNCH_SAR
   countLaunch();
   return cudaGetLastError();
+}
+
+cudaError_t launchSarRemoteLocus(const SarState &S, int smCount, long n, const double *line,
+                                 const double *samp, double prec, const LocusOut &o,
+                                 cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
+  if (stage) {
+    cudaError_t e = allowSmem(sarRemoteLocusKernel<true>, smemBytes);
+    if (e != cudaSuccess) return e;
+    sarRemoteLocusKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, line, samp, prec, o);
+  } else {
+    sarRemoteLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, prec, o);
+  }
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchGroundPartialsSar(const SarState &S, int smCount, long n, const double *x,
+                                    const double *y, const double *z, double *partials,
+                                    uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
+  if (stage) {
+    cudaError_t e = allowSmem(sarGroundPartialsKernel<true>, smemBytes);
+    if (e != cudaSuccess) return e;
+  }
+  WorkCounter wc;
+  cudaError_t e = wc.acquire(stream);
+  if (e != cudaSuccess) return e;
+  if (stage)
+    sarGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+  else
+    sarGroundPartialsKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+  countLaunch();
+  return wc.release();
 }
 
 }  // namespace ub200

@@ -227,6 +227,62 @@ class RasterGM(object):
             _ptr(ach), _ptr(st), stream))
         return x, y, z, ach, st
 
+    def imageToRemoteImagingLocusBatch(self, line, samp, desiredPrecision=0.001):
+        """csm::RasterGM::imageToRemoteImagingLocus for arrays (host numpy or torch CUDA).
+        Returns (point (n,3)-like tuple px,py,pz, direction dx,dy,dz, achieved, status)."""
+        if _is_torch(line):
+            import torch
+            n = line.numel()
+            out = [torch.empty_like(line) for _ in range(7)]
+            st = torch.empty(n, dtype=torch.int32, device=line.device)
+            stream = torch.cuda.current_stream(line.device).cuda_stream
+            check(lib.usgscsm_b200_image_to_remote_imaging_locus_dev(
+                self._h, n, _ptr(line), _ptr(samp), desiredPrecision, *[_ptr(o) for o in out],
+                _ptr(st), stream))
+            return tuple(out) + (st,)
+        line = _host(line)
+        n = line.size
+        samp = _host(samp, n)
+        out = [np.empty(n) for _ in range(7)]
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_image_to_remote_imaging_locus(
+            self._h, n, _ptr(line), _ptr(samp), desiredPrecision, *[_ptr(o) for o in out], _ptr(st)))
+        return tuple(out) + (st,)
+
+    def computeGroundPartialsBatch(self, x, y, z):
+        """csm::RasterGM::computeGroundPartials for arrays -> ((n, 6) partials, status)."""
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            p = torch.empty((n, 6), dtype=torch.float64, device=x.device)
+            st = torch.empty(n, dtype=torch.int32, device=x.device)
+            stream = torch.cuda.current_stream(x.device).cuda_stream
+            check(lib.usgscsm_b200_ground_partials_dev(self._h, n, _ptr(x), _ptr(y), _ptr(z),
+                                                       _ptr(p), _ptr(st), stream))
+            return p, st
+        x = _host(x)
+        n = x.size
+        y, z = _host(y, n), _host(z, n)
+        p = np.empty((n, 6))
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_ground_partials(self._h, n, _ptr(x), _ptr(y), _ptr(z), _ptr(p), _ptr(st)))
+        return p, st
+
+    def computeGroundPartials(self, groundPt):
+        """csm::RasterGM::computeGroundPartials (one point): a list of six partials."""
+        p, st = self.computeGroundPartialsBatch([groundPt[0]], [groundPt[1]], [groundPt[2]])
+        self._raise_or_warn(int(st[0]), None, "computeGroundPartials")
+        return [float(v) for v in p[0]]
+
+    def setEllipsoid(self, semiMajor, semiMinor):
+        """csm::SettableEllipsoid::setEllipsoid."""
+        check(lib.usgscsm_b200_model_set_ellipsoid(self._h, float(semiMajor), float(semiMinor)))
+
+    def getEllipsoid(self):
+        a, b = C.c_double(), C.c_double()
+        check(lib.usgscsm_b200_model_get_ellipsoid(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     # ---- csm::RasterGM per-point API (a batch of one) ---------------------------------------
     @staticmethod
     def _raise_or_warn(st, warnings, function):
