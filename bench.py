@@ -220,7 +220,11 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device -- the engine has no CPU path")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_node = None
     if world > 1:
+        from usgscsm_b200 import sharding
+        if os.environ.get("USGSCSM_B200_NUMA_BIND", "1") != "0":
+            numa_node = sharding.bind_to_gpu_numa_node(local)
         # stdout carries ONE JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it
         if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
             os.environ["NCCL_DEBUG"] = "WARN"
@@ -355,6 +359,8 @@ def run_b200(args):
                             "hbm_gbs": I2G_BYTES_PER_POINT * n / (i2g_kern_ms * 1e-3) / 1e9},
         "check": {"round_trip_max_px": err, "points_with_flags": flags},
     }
+    if world > 1:
+        result["config"]["numa_bind"] = "rank 0 bound to NUMA node %s" % numa_node
 
     # second column: desiredPrecision 1e-8, what the reference's own CLI test
     # uses (tests/CMakeLists.txt:30) -- more secant iterations per point

@@ -70,13 +70,32 @@ __device__ inline StagedTables stageOrientationTables(const LsState &S, bool nee
   return t;
 }
 
+// What a kernel may know about the model at compile time.  The generic spec reads everything
+// from the packed state; CommonSpec<DIST> is the common case the launcher can verify on the
+// host -- no parameter adjustments, a single line-rate segment, projective seed available,
+// distortion model DIST -- so that every other branch drops out of the instruction stream.
+struct GenericSpec {
+  static constexpr bool kCommon = false;
+  static constexpr int kDist = -1;
+};
+template <int DIST>
+struct CommonSpec {
+  static constexpr bool kCommon = true;
+  static constexpr int kDist = DIST;
+};
+template <class SPEC>
+UB_DEV bool specHasAdj(const LsState &S) { return SPEC::kCommon ? false : S.hasAdj != 0; }
+template <class SPEC>
+UB_DEV bool specHasAttAdj(const LsState &S) { return SPEC::kCommon ? false : S.hasAttAdj != 0; }
+
 // getValue(i, adj) with adj == _no_adjustment (LS:757-772 passes 16 zeros): the host packs
 // m_currentParameterValue[i] + 0.0.
 UB_DEV double param(const LsState &S, int i) { return S.params[i]; }
 
 // LS::getImageTime LS:1543-1568: std::upper_bound over m_intTimeLines, step back one.
+template <class SPEC = GenericSpec>
 UB_DEV double lsImageTime(const LsState &S, double lineFull) {
-  if (S.numIntTimes == 1) {
+  if (SPEC::kCommon || S.numIntTimes == 1) {
     return S.intStart0 + S.intTime0 * (lineFull - S.intLine0 + 0.5);
   }
   // std::upper_bound: first element with lineFull < element
@@ -101,14 +120,14 @@ UB_DEV double lsImageTime(const LsState &S, double lineFull) {
 //   ALWAYS_VEL = false: line-scan semantics (calc_vel == false at every hot-path call site:
 //                position only unless some parameter is non-zero);
 //   ALWAYS_VEL = true:  push-frame semantics (no shortcut).
-template <bool ALWAYS_VEL, class TAB>
+template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
 UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
                             double pos[3], double vel[3]) {
   LagrangeWeights w;
   lagrangeWeights(S.positions, S.lag, time, w);
   double sensPosNom[3];
   tableApply<3>(T, T.positions, w, sensPosNom);
-  if (!ALWAYS_VEL && !S.hasAdj) {
+  if (!ALWAYS_VEL && !specHasAdj<SPEC>(S)) {
     pos[0] = sensPosNom[0];
     pos[1] = sensPosNom[1];
     pos[2] = sensPosNom[2];
@@ -195,18 +214,18 @@ UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9])
 
 // LS::computeDetectorView LS:2603-2675 (PF:2038-2110 is the same with the push-frame
 // position routine): ground point -> undistorted focal-plane coordinates at `time`.
-template <bool ALWAYS_VEL, class TAB>
+template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
 UB_DEV void detectorView(const LsState &S, const TAB &T, double time, double gx,
                          double gy, double gz, double &focalX, double &focalY) {
   double pos[3], vel[3];
-  adjSensorPosVel<ALWAYS_VEL>(S, T, time, pos, vel);
+  adjSensorPosVel<ALWAYS_VEL, TAB, SPEC>(S, T, time, pos, vel);
   double bodyLook[3] = {gx - pos[0], gy - pos[1], gz - pos[2]};
   double bodyToCamera[9];
   cameraToBodyMatrix(S, T, time, bodyToCamera);
   double cameraLook[3];
   matTVec(bodyToCamera, bodyLook, cameraLook);
   double adjustedLook[3];
-  if (S.hasAttAdj) {
+  if (specHasAttAdj<SPEC>(S)) {
     double attCorr[9];
     attitudeCorrection(S, time, attCorr);
     matTVec(attCorr, cameraLook, adjustedLook);

@@ -10,6 +10,7 @@
 // grid is persistent (a multiple of the SM count, grid-stride over points) so that the
 // staging cost is paid once per resident block, not once per 256 points.
 #include <cstdlib>
+#include <type_traits>
 
 #include "kernels.h"
 #include "ls_common.cuh"
@@ -25,9 +26,10 @@ constexpr int kDefaultThreads = 256;  // block size used unless overridden
 
 // ---- groundToImage ---------------------------------------------------------------------
 // LS::computeProjectiveApproximation LS:2688-2736
+template <class SPEC = GenericSpec>
 UB_DEV void projectiveSeed(const LsState &S, double x, double y, double z, double &line,
                            double &samp) {
-  if (S.useApproxInitTrans) {
+  if (SPEC::kCommon || S.useApproxInitTrans) {
     const double *u = S.projCoeffs;
     double line_den = 1 + u[4] * x + u[5] * y + u[6] * z;
     double samp_den = 1 + u[11] * x + u[12] * y + u[13] * z;
@@ -60,12 +62,12 @@ UB_DEV void projectiveSeed(const LsState &S, double x, double y, double z, doubl
 // computed; only applyDistortion is repeated, now with the caller's desiredPrecision
 // instead of the default 1e-6 (hazard 3 in SURVEY.md §9).  The loop below therefore has a
 // single inlined copy of the detector view and runs it 2 + k times.
-template <bool ALWAYS_VEL, class TAB>
+template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
 UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
                                  double gy, double gz, double desiredPrecision, double &outLine,
                                  double &outSamp, double &achieved, uint32_t &status) {
   double approxLine, approxSamp;
-  projectiveSeed(S, gx, gy, gz, approxLine, approxSamp);
+  projectiveSeed<SPEC>(S, gx, gy, gz, approxLine, approxSamp);
 
   const FocalPlane &fp = S.fp;
   int count = 0;
@@ -77,11 +79,11 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
   uint32_t evals = 0;
   for (;;) {
     evals++;
-    double timei = lsImageTime(S, approxLine + t1);
-    detectorView<ALWAYS_VEL>(S, T, timei, gx, gy, gz, focalX, focalY);
+    double timei = lsImageTime<SPEC>(S, approxLine + t1);
+    detectorView<ALWAYS_VEL, TAB, SPEC>(S, T, timei, gx, gy, gz, focalX, focalY);
     double distortedFocalX, distortedFocalY;
     distStatus = 0;
-    applyDistortion(focalX, focalY, distortedFocalX, distortedFocalY, fp, 1.0E-6, distStatus);
+    applyDistortion<SPEC::kDist>(focalX, focalY, distortedFocalX, distortedFocalY, fp, 1.0E-6, distStatus);
     double detectorLine = fp.iTransL[0] + fp.iTransL[1] * distortedFocalX +
                           fp.iTransL[2] * distortedFocalY + fp.detectorLineOrigin -
                           fp.startingDetectorLine;
@@ -114,8 +116,8 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
   // Final projection: same focal-plane point, distortion at the caller's precision.
   double distortedFocalX, distortedFocalY;
   distStatus = 0;
-  applyDistortion(focalX, focalY, distortedFocalX, distortedFocalY, fp, desiredPrecision,
-                  distStatus);
+  applyDistortion<SPEC::kDist>(focalX, focalY, distortedFocalX, distortedFocalY, fp,
+                               desiredPrecision, distStatus);
   status |= distStatus;
   double detectorLine =
       fp.iTransL[0] + fp.iTransL[1] * distortedFocalX + fp.iTransL[2] * distortedFocalY;
@@ -140,7 +142,7 @@ UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamp
   return st;
 }
 
-template <class TAB>
+template <class SPEC, class TAB>
 UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const double *__restrict__ x,
                                 const double *__restrict__ y, const double *__restrict__ z,
                                 double prec, double *__restrict__ line, double *__restrict__ samp,
@@ -150,7 +152,7 @@ UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const do
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s, a;
     uint32_t st = 0;
-    lsGroundToImagePoint<false>(S, T, gx, gy, gz, prec, l, s, a, st);
+    lsGroundToImagePoint<false, TAB, SPEC>(S, T, gx, gy, gz, prec, l, s, a, st);
     st |= imageRangeStatus(l, s, S.nLines, S.nSamples);
     __stcs(line + i, l);
     __stcs(samp + i, s);
@@ -161,7 +163,16 @@ UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const do
 
 // MINB = resident blocks of 256 threads per SM the register allocation is held to
 // (2: 96+ registers, 3: 80, 4: 64).
-template <bool STAGE, int MINB>
+//
+// DIST >= 0 is the specialised kernel for the common case -- no parameter adjustments, one
+// line-rate segment, distortion model DIST: the launcher has checked those facts of S, and
+// making them compile-time facts (CommonSpec) removes every other branch (the eight other distortion
+// models, the adjusted-position frame, the Euler-angle correction, the line-rate search) from
+// the instruction stream.  Only ~1/6 of the generic kernel's instructions are ever executed
+// for such a model, scattered over 85 KB of code, and ncu shows the search kernel waiting on
+// instruction fetch (icc hit rate 88 %, "no instruction" 14 % of stall samples).
+// DIST = -1 is the generic kernel.  Same arithmetic either way.
+template <bool STAGE, int MINB, int DIST>
 __global__ void __launch_bounds__(kThreads, MINB)
     lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
@@ -169,12 +180,13 @@ __global__ void __launch_bounds__(kThreads, MINB)
                           double *__restrict__ achieved, uint32_t *__restrict__ status,
                           unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
+  using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST>, GenericSpec>::type;
   if (STAGE) {
-    StagedTables T = stageOrientationTables(S, S.hasAdj != 0, smem);
-    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
+    StagedTables T = stageOrientationTables(S, specHasAdj<SPEC>(S), smem);
+    lsGroundToImageLoop<SPEC>(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
   } else {
     OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
-    lsGroundToImageLoop(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
+    lsGroundToImageLoop<SPEC>(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
   }
 }
 
@@ -510,8 +522,7 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   if (n <= 0) return cudaSuccess;
   size_t smemBytes;
   bool stage;
-  static const int minb = envInt("USGSCSM_B200_LS_MINB", kDefaultMinBlocks);
-  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, minb);
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kDefaultMinBlocks);
   // work counter of this launch: stream-ordered scratch, so that launches in flight on
   // different streams never share one
   const int grab = grabSize();
@@ -519,23 +530,31 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   cudaError_t e = wc.acquire(stream);
   if (e != cudaSuccess) return e;
   unsigned long long *next = wc.ptr;
-#define UB_LAUNCH_G2I(STAGE, MINB)                                                            \
+#define UB_LAUNCH_G2I(STAGE, DIST)                                                            \
   do {                                                                                        \
     if (smemBytes > 48 * 1024)                                                                \
-      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, MINB>,                                \
+      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST>,             \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
-    lsGroundToImageKernel<STAGE, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(         \
+    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST><<<sh.blocks, sh.threads, smemBytes, \
+                                                            stream>>>(                        \
         S, n, x, y, z, prec, line, samp, achieved, status, next, grab);                       \
   } while (0)
-  if (stage) {
-    if (minb >= 4) UB_LAUNCH_G2I(true, 4);
-    else if (minb == 3) UB_LAUNCH_G2I(true, 3);
-    else UB_LAUNCH_G2I(true, 2);
-  } else {
-    if (minb >= 4) UB_LAUNCH_G2I(false, 4);
-    else if (minb == 3) UB_LAUNCH_G2I(false, 3);
-    else UB_LAUNCH_G2I(false, 2);
-  }
+#define UB_LAUNCH_G2I_DIST(STAGE)                                                             \
+  do {                                                                                        \
+    if (!common) UB_LAUNCH_G2I(STAGE, -1);                                                    \
+    else if (S.fp.distortionType == 4) UB_LAUNCH_G2I(STAGE, 4); /* LROLROCNAC */              \
+    else if (S.fp.distortionType == 0) UB_LAUNCH_G2I(STAGE, 0); /* RADIAL */                  \
+    else if (S.fp.distortionType == 1) UB_LAUNCH_G2I(STAGE, 1); /* TRANSVERSE */              \
+    else UB_LAUNCH_G2I(STAGE, -1);                                                            \
+  } while (0)
+  static const int specialise = envInt("USGSCSM_B200_LS_SPECIALISE", 1);
+  const bool common = specialise == 1 && !S.hasAdj && !S.hasAttAdj && S.numIntTimes == 1 &&
+                      S.useApproxInitTrans;
+  if (stage)
+    UB_LAUNCH_G2I_DIST(true);
+  else
+    UB_LAUNCH_G2I_DIST(false);
+#undef UB_LAUNCH_G2I_DIST
 #undef UB_LAUNCH_G2I
   countLaunch();
   return wc.release();

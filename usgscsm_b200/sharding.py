@@ -87,3 +87,30 @@ class ShardedImage(object):
 
     def gather(self, local):
         return gather_bands(local, self.n_lines, self.n_samples, self.group)
+
+
+def bind_to_gpu_numa_node(device_index):
+    """Pin this process (and so its page-locked staging buffers, first-touch) to the CPUs of
+    the NUMA node the GPU hangs off.  With one process per GPU the host<->device copies of the
+    host-pointer entry points otherwise cross the socket interconnect for half the ranks.
+    Returns the node number, or None when the topology cannot be read (then nothing changes)."""
+    import os
+    try:
+        props = torch.cuda.get_device_properties(device_index)
+        bus = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return node
+    except (OSError, ValueError, AttributeError):
+        return None
