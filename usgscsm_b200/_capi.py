@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libusgscsm_b200.so")
+# USGSCSM_B200_LIB: another build of the same library (A/B experiments)
+LIB_PATH = os.environ.get("USGSCSM_B200_LIB") or os.path.join(_HERE, "libusgscsm_b200.so")
 
 OK = 0
 EINVAL, ESTATE, ENODEVICE, ECUDA, EUNSUPPORTED = -1, -2, -3, -4, -5

@@ -77,11 +77,16 @@ __device__ inline StagedTables stageOrientationTables(const LsState &S, bool nee
 struct GenericSpec {
   static constexpr bool kCommon = false;
   static constexpr int kDist = -1;
+  static constexpr bool kColdOutOfLine = false;  // see lagrangeWeights
+};
+struct SearchSpec : GenericSpec {  // the line-scan search kernel, any model
+  static constexpr bool kColdOutOfLine = true;
 };
 template <int DIST>
 struct CommonSpec {
   static constexpr bool kCommon = true;
   static constexpr int kDist = DIST;
+  static constexpr bool kColdOutOfLine = true;
 };
 template <class SPEC>
 UB_DEV bool specHasAdj(const LsState &S) { return SPEC::kCommon ? false : S.hasAdj != 0; }
@@ -124,7 +129,7 @@ template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
 UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
                             double pos[3], double vel[3]) {
   LagrangeWeights w;
-  lagrangeWeights(S.positions, S.lag, time, w);
+  lagrangeWeights<SPEC::kColdOutOfLine>(S.positions, S.lag, time, w);
   double sensPosNom[3];
   tableApply<3>(T, T.positions, w, sensPosNom);
   if (!ALWAYS_VEL && !specHasAdj<SPEC>(S)) {
@@ -189,11 +194,11 @@ UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
 }
 
 // LS::getQuaternions LS:2140-2153 + calculateRotationMatrixFromQuaternions U:78-95.
-template <class TAB>
+template <class TAB, class SPEC = GenericSpec>
 UB_DEV void cameraToBodyMatrix(const LsState &S, const TAB &T, double time, double m[9]) {
   double q[4];
   LagrangeWeights w;
-  lagrangeWeights(S.quaternions, S.lag, time, w);
+  lagrangeWeights<SPEC::kColdOutOfLine>(S.quaternions, S.lag, time, w);
   tableApply<4>(T, T.quaternions, w, q);
   rotationFromQuaternion(q, m);
 }
@@ -221,7 +226,7 @@ UB_DEV void detectorView(const LsState &S, const TAB &T, double time, double gx,
   adjSensorPosVel<ALWAYS_VEL, TAB, SPEC>(S, T, time, pos, vel);
   double bodyLook[3] = {gx - pos[0], gy - pos[1], gz - pos[2]};
   double bodyToCamera[9];
-  cameraToBodyMatrix(S, T, time, bodyToCamera);
+  cameraToBodyMatrix<TAB, SPEC>(S, T, time, bodyToCamera);
   double cameraLook[3];
   matTVec(bodyToCamera, bodyLook, cameraLook);
   double adjustedLook[3];

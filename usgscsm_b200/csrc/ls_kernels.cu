@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(kThreads, MINB)
                           double *__restrict__ achieved, uint32_t *__restrict__ status,
                           unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
-  using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST>, GenericSpec>::type;
+  using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST>, SearchSpec>::type;
   if (STAGE) {
     StagedTables T = stageOrientationTables(S, specHasAdj<SPEC>(S), smem);
     lsGroundToImageLoop<SPEC>(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
@@ -321,6 +321,8 @@ UB_DEV void lsImageToGroundLoop(const LsState &S, const TAB &T, long n, const do
                                 const double *__restrict__ height, int heightStride, double prec,
                                 double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
                                 double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  // static grid-stride split: no search in this kernel, every point costs the same, and the
+  // dynamic queue measured 2 % slower here
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     double l, s;
@@ -347,8 +349,8 @@ UB_DEV void lsImageToGroundLoop(const LsState &S, const TAB &T, long n, const do
 
 // GRID = true: pixel coordinates generated from the point index (dense grid);
 // GRID = false: explicit (line, samp) arrays.
-template <bool STAGE, bool GRID>
-__global__ void __launch_bounds__(kThreads)
+template <bool STAGE, bool GRID, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
     lsImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
                           const double *__restrict__ samp, GridSpec g,
                           const double *__restrict__ height, int heightStride, double prec,
@@ -391,9 +393,9 @@ __global__ void __launch_bounds__(kThreads, kDefaultMinBlocks)
       double a;
       uint32_t sk = 0;
       if (STAGE)
-        lsGroundToImagePoint<false>(S, TS, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+        lsGroundToImagePoint<false, StagedTables, SearchSpec>(S, TS, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
       else
-        lsGroundToImagePoint<false>(S, TG, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+        lsGroundToImagePoint<false, OrientationTables, SearchSpec>(S, TG, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
       st |= sk;
     }
     double p[6];
@@ -588,15 +590,22 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
   }
   size_t smemBytes;
   bool stage;
-  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kBlocksPerSm);
+  static const int minb = envInt("USGSCSM_B200_LS_I2G_MINB", 4);
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, minb);
   GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
-#define UB_LAUNCH_I2G(STAGE, GRID)                                                           \
+#define UB_LAUNCH_I2G_M(STAGE, GRID, MINB)                                                   \
   do {                                                                                       \
     if (smemBytes > 48 * 1024)                                                               \
-      cudaFuncSetAttribute(lsImageToGroundKernel<STAGE, GRID>,                               \
+      cudaFuncSetAttribute(lsImageToGroundKernel<STAGE, GRID, MINB>,                         \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);     \
-    lsImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(        \
+    lsImageToGroundKernel<STAGE, GRID, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(  \
         S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status);         \
+  } while (0)
+#define UB_LAUNCH_I2G(STAGE, GRID)                                                           \
+  do {                                                                                       \
+    if (minb >= 4) UB_LAUNCH_I2G_M(STAGE, GRID, 4);                                          \
+    else if (minb == 3) UB_LAUNCH_I2G_M(STAGE, GRID, 3);                                     \
+    else UB_LAUNCH_I2G_M(STAGE, GRID, 2);                                                    \
   } while (0)
   if (stage && grid)
     UB_LAUNCH_I2G(true, true);
@@ -607,6 +616,7 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
   else
     UB_LAUNCH_I2G(false, false);
 #undef UB_LAUNCH_I2G
+#undef UB_LAUNCH_I2G_M
   countLaunch();
   return cudaGetLastError();
 }

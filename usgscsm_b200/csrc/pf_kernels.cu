@@ -18,6 +18,14 @@
 #include "ls_common.cuh"
 #include "work_queue.cuh"
 
+// resident blocks of 256 threads per SM the register allocation is held to (measured best)
+#ifndef UB_PF_G2I_MINB
+#define UB_PF_G2I_MINB 4
+#endif
+#ifndef UB_PF_I2G_MINB
+#define UB_PF_I2G_MINB 4
+#endif
+
 namespace ub200 {
 
 namespace {
@@ -235,7 +243,7 @@ UB_DEV uint32_t pfImageRangeStatus(double line, double samp, const LsState &S) {
 }
 
 template <bool STAGE>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, UB_PF_G2I_MINB)
     pfGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
@@ -302,7 +310,7 @@ UB_DEV void pfImageToGroundPoint(const LsState &S, const OrientationTables &T,
 }
 
 template <bool STAGE, bool GRID>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, UB_PF_I2G_MINB)
     pfImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
                           const double *__restrict__ samp, GridSpec g,
                           const double *__restrict__ height, int heightStride, double prec,

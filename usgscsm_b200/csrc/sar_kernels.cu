@@ -13,6 +13,10 @@
 #include "device_math.cuh"
 #include "work_queue.cuh"
 
+#ifndef UB_SAR_G2I_MINB
+#define UB_SAR_G2I_MINB 3
+#endif
+
 namespace ub200 {
 
 namespace {
@@ -321,7 +325,7 @@ UB_DEV void sarImageToGroundPoint(const SarState &S, const SarTables &T, double 
 }
 
 template <bool STAGE>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, UB_SAR_G2I_MINB)
     sarGroundToImageKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z, double prec,
                            double *__restrict__ line, double *__restrict__ samp,
@@ -351,11 +355,11 @@ __global__ void __launch_bounds__(kThreads)
                            const double *__restrict__ samp, GridSpec g,
                            const double *__restrict__ height, int heightStride, double prec,
                            double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
-                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
+                           double *__restrict__ achieved, uint32_t *__restrict__ status,
+                           unsigned long long *__restrict__ next, int grab) {
   extern __shared__ double smem[];
   SarTables T = stageSarTables(S, smem, STAGE);
-  const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  forEachPointDynamic(n, next, grab, [&](long i) {
     double l, s;
     if (GRID) {
       long r = i / g.nSamps;
@@ -375,7 +379,7 @@ __global__ void __launch_bounds__(kThreads)
     __stcs(z + i, pz);
     if (achieved) __stcs(achieved + i, a);
     if (status) __stcs(status + i, st);
-  }
+  });
 }
 
 // computeGroundPartials SAR:1384-1406: delta = m_scaledPixelWidth.
@@ -499,12 +503,19 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
   bool stage;
   LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
   GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+  if (stage && smemBytes > 48 * 1024) {
+    cudaError_t ea = grid ? allowSmem(sarImageToGroundKernel<true, true>, smemBytes)
+                          : allowSmem(sarImageToGroundKernel<true, false>, smemBytes);
+    if (ea != cudaSuccess) return ea;
+  }
+  WorkCounter wc;
+  cudaError_t e0 = wc.acquire(stream);
+  if (e0 != cudaSuccess) return e0;
 #define UB_LAUNCH_SAR(STAGE, GRID)                                                          \
   do {                                                                                      \
-    cudaError_t e = allowSmem(sarImageToGroundKernel<STAGE, GRID>, smemBytes);              \
-    if (e != cudaSuccess) return e;                                                         \
     sarImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(      \
-        S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status);        \
+        S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status, wc.ptr, \
+        grabSize());                                                                        \
   } while (0)
   if (stage && grid)
     UB_LAUNCH_SAR(true, true);
@@ -516,7 +527,7 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
     UB_LAUNCH_SAR(false, false);
 #undef UB_LAUNCH_SAR
   countLaunch();
-  return cudaGetLastError();
+  return wc.release();
 }
 
 cudaError_t launchSarRemoteLocus(const SarState &S, int smCount, long n, const double *line,
