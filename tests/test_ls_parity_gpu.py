@@ -70,6 +70,10 @@ CASES = {
     "radtan": dict(distortion_type=7, dist_coeffs=(1e-3, -2e-4, 1e-4, -1e-4, 1e-5)),
     "kplo": dict(distortion_type=8, dist_coeffs=(1.81e-5,)),
     "platform0": dict(platform_flag=0),
+    # HiRISE-like attitude sampling: 4 x 41 k quaternion doubles = 1.3 MB, not staged into shared
+    # memory (kMaxStagedTableBytes) -- the kernels read the tables through L1/L2
+    "unstaged_tables": dict(dt_quat=0.0001, dt_ephem=0.01),
+    "ellipsoid": dict(major_axis=3396190.0, minor_axis=3376200.0, altitude=280000.0, gm=4.2828e13),
     "segments": dict(n_time_segments=3),
     "summing2": dict(summing=2, n_samples=2532, n_lines=8192, starting_sample=10.0),
     "adjusted": dict(params=(3.0, -2.0, 1.5, 0.02, -0.01, 0.005, 0.5, -0.3, 0.2, 0.05, 0.04, -0.03,
@@ -194,3 +198,38 @@ def test_chunked_pipeline_large(ref):
     assert max(np.abs(rx - x[sub]).max(), np.abs(ry - y[sub]).max(), np.abs(rz - z[sub]).max()) <= M_TOL
     rl, rs, _, _ = rm.ground_to_image(x[sub], y[sub], z[sub])
     assert max(np.abs(rl - l[sub]).max(), np.abs(rs - s[sub]).max()) <= PX_TOL
+
+
+def test_table_ends_reduced_order(ref):
+    """Times near the ends of the ephemeris / attitude tables: lagrangeInterp drops to order
+    6 / 4 / 2 (src/Utilities.cpp:437-452) and beyond the ends extrapolates from the clamped
+    index.  The padding nodes of the synthetic state are cut off so that the first and last
+    image lines sit on the table ends."""
+    import json
+    from usgscsm_b200 import synth
+    d = synth.linescan_state(n_lines=4096, n_samples=1024, seed=17, as_dict=True)
+    for key, vlen, t0, dt in (("m_positions", 3, "m_t0Ephem", "m_dtEphem"),
+                              ("m_velocities", 3, "m_t0Ephem", None),
+                              ("m_quaternions", 4, "m_t0Quat", "m_dtQuat")):
+        cut = 4 if key != "m_quaternions" else 5   # attitude table ends INSIDE the image
+        d[key] = d[key][cut * vlen:len(d[key]) - cut * vlen]
+        if dt is not None:
+            d[t0] = d[t0] + cut * d[dt]
+    d["m_numPositions"] = len(d["m_positions"])
+    d["m_numQuaternions"] = len(d["m_quaternions"])
+    state = d["m_modelName"] + "\n" + json.dumps(d)
+    gm, rm = _models(ref, state)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(6)
+    # dense near both ends, plus a sprinkling everywhere and a little outside the image
+    line = np.concatenate([rng.uniform(-40, 400, 6000), rng.uniform(nl - 400, nl + 40, 6000),
+                           rng.uniform(0, nl, 3000)])
+    samp = rng.uniform(0, ns, line.size)
+    h = synth.synthetic_dem(line, samp)
+    x, y, z = _check_i2g(gm, rm, line, samp, h)
+    _check_g2i(gm, rm, x, y, z)
+    _check_g2i(gm, rm, x, y, z, prec=1e-8)
+    got = gm.imageToRemoteImagingLocusBatch(line, samp)
+    exp = rm.remote_locus(line, samp)
+    for k in range(6):
+        assert np.abs(got[k] - exp[k]).max() <= (1e-4 if k < 3 else 1e-12)
