@@ -197,6 +197,20 @@ USGSCSM_B200_API int usgscsm_b200_image_to_remote_imaging_locus_dev(usgscsm_b200
                                                    double *achieved, uint32_t *status,
                                                    void *stream);
 
+/* imageToProximateImagingLocus: replaces csm::RasterGM::imageToProximateImagingLocus(const
+ * ImageCoord&, const EcefCoord& groundPt, double desiredPrecision, double* achievedPrecision,
+ * WarningList*) (LS:1175-1235, PF:995-1055, FR:424-462, SAR:959-993): the point of the pixel's
+ * imaging locus nearest the given ground point and the locus direction there.  Inputs SoA
+ * (line, samp, x, y, z); outputs as for the remote locus. */
+USGSCSM_B200_API int usgscsm_b200_image_to_proximate_imaging_locus(
+    usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
+    const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
+    double *dy, double *dz, double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_to_proximate_imaging_locus_dev(
+    usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
+    const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
+    double *dy, double *dz, double *achieved, uint32_t *status, void *stream);
+
 /* computeGroundPartials: replaces csm::RasterGM::computeGroundPartials(const EcefCoord&)
  * (LS:1299-1325, PF:1091-1116, FR:955-1003, SAR:1384-1406), four groundToImage searches per
  * point fused in one kernel.  partials: 6 doubles per point, [dLine/dX, dLine/dY, dLine/dZ,

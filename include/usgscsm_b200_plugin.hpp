@@ -203,6 +203,22 @@ class RasterGM {
     if (achievedPrecision) *achievedPrecision = o[6];
     return csm::EcefLocus(o[0], o[1], o[2], o[3], o[4], o[5]);
   }
+  // LS:1175-1235, PF:995-1055, FR:424-462, SAR:959-993
+  csm::EcefLocus imageToProximateImagingLocus(const csm::ImageCoord &imagePt,
+                                              const csm::EcefCoord &groundPt,
+                                              double desiredPrecision = 0.001,
+                                              double *achievedPrecision = NULL,
+                                              csm::WarningList *warnings = NULL) const {
+    double o[7] = {0, 0, 0, 0, 0, 0, 0};
+    uint32_t st = 0;
+    check(usgscsm_b200_image_to_proximate_imaging_locus(
+              m_h, 1, &imagePt.line, &imagePt.samp, &groundPt.x, &groundPt.y, &groundPt.z,
+              desiredPrecision, o, o + 1, o + 2, o + 3, o + 4, o + 5, o + 6, &st),
+          "imageToProximateImagingLocus");
+    raiseOrWarn(st, warnings, "imageToProximateImagingLocus");
+    if (achievedPrecision) *achievedPrecision = o[6];
+    return csm::EcefLocus(o[0], o[1], o[2], o[3], o[4], o[5]);
+  }
   // LS:1299-1325, PF:1091-1116, FR:955-1003, SAR:1384-1406
   std::vector<double> computeGroundPartials(const csm::EcefCoord &groundPt) const {
     std::vector<double> p(6, 0.0);
@@ -228,6 +244,17 @@ class RasterGM {
                                                      px, py, pz, dx, dy, dz, achievedPrecision,
                                                      status),
           "imageToRemoteImagingLocusBatch");
+  }
+  void imageToProximateImagingLocusBatch(size_t n, const double *line, const double *samp,
+                                         const double *x, const double *y, const double *z,
+                                         double desiredPrecision, double *px, double *py,
+                                         double *pz, double *dx, double *dy, double *dz,
+                                         double *achievedPrecision = NULL,
+                                         uint32_t *status = NULL) const {
+    check(usgscsm_b200_image_to_proximate_imaging_locus(m_h, (int64_t)n, line, samp, x, y, z,
+                                                        desiredPrecision, px, py, pz, dx, dy, dz,
+                                                        achievedPrecision, status),
+          "imageToProximateImagingLocusBatch");
   }
   void computeGroundPartialsBatch(size_t n, const double *x, const double *y, const double *z,
                                   double *partials6n, uint32_t *status = NULL) const {

@@ -44,6 +44,7 @@ def lib():
         L.ref_image_to_ground.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, C.c_int,
                                           C.c_double, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_remote_locus.argtypes = [C.c_void_p, C.c_long, _dp, _dp, C.c_double] + [_dp] * 8 + [C.c_int]
+        L.ref_proximate_locus.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 8 + [C.c_int]
         L.ref_ground_partials.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_set_ellipsoid.argtypes = [C.c_void_p, C.c_double, C.c_double]
         L.ref_lagrange.argtypes = [C.c_int, _dp, C.c_double, C.c_double, C.c_double, C.c_int,
@@ -144,6 +145,18 @@ class RefModel(object):
         st = np.empty(n, dtype=np.uint32)
         self._L.ref_remote_locus(self._h, n, line.ctypes.data, samp.ctypes.data, prec,
                                  *[o.ctypes.data for o in out], st.ctypes.data, threads)
+        return tuple(out) + (st,)
+
+    def proximate_locus(self, line, samp, x, y, z, prec=0.001, threads=1):
+        """imageToProximateImagingLocus per (pixel, ground point)."""
+        line = _a(line)
+        n = line.size
+        samp, x, y, z = _a(samp, n), _a(x, n), _a(y, n), _a(z, n)
+        out = [np.empty(n) for _ in range(7)]
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_proximate_locus(self._h, n, line.ctypes.data, samp.ctypes.data, x.ctypes.data,
+                                    y.ctypes.data, z.ctypes.data, prec,
+                                    *[o.ctypes.data for o in out], st.ctypes.data, threads)
         return tuple(out) + (st,)
 
     def ground_partials(self, x, y, z, threads=1):

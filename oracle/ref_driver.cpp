@@ -291,6 +291,49 @@ int ref_remote_locus(void *h, long n, const double *line, const double *samp, do
   return 0;
 }
 
+// imageToProximateImagingLocus over n (pixel, ground point) pairs.
+int ref_proximate_locus(void *h, long n, const double *line, const double *samp, const double *x,
+                        const double *y, const double *z, double prec, double *px, double *py,
+                        double *pz, double *dx, double *dy, double *dz, double *achieved,
+                        uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    const double q = std::nan("");
+    csm::EcefLocus loc(q, q, q, q, q, q);
+    try {
+      csm::WarningList warn;
+      loc = gm->imageToProximateImagingLocus(csm::ImageCoord(line[i], samp[i]),
+                                             csm::EcefCoord(x[i], y[i], z[i]), prec, &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+      ach = q;
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+      ach = q;
+    }
+    if (!(std::isfinite(loc.point.x) && std::isfinite(loc.point.y) && std::isfinite(loc.point.z) &&
+          std::isfinite(loc.direction.x) && std::isfinite(loc.direction.y) &&
+          std::isfinite(loc.direction.z)))
+      st |= ST_NONFINITE;
+    px[i] = loc.point.x;
+    py[i] = loc.point.y;
+    pz[i] = loc.point.z;
+    dx[i] = loc.direction.x;
+    dy[i] = loc.direction.y;
+    dz[i] = loc.direction.z;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
 // computeGroundPartials over n points; partials = 6 doubles per point (LS:1299-1325 etc.).
 int ref_ground_partials(void *h, long n, const double *x, const double *y, const double *z,
                         double *partials, uint32_t *status, int threads) {

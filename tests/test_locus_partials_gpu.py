@@ -66,6 +66,40 @@ def test_remote_imaging_locus(ref, kind):
 
 
 @pytest.mark.parametrize("kind", KINDS)
+def test_proximate_imaging_locus(ref, kind):
+    from usgscsm_b200 import _capi, synth
+    gm, rm = _pair(ref, kind)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(15)
+    n = 12000
+    line, samp = pixels(rng, n, nl, ns)
+    x, y, z, _, _ = gm.imageToGroundBatch(line, samp, synth.synthetic_dem(line, samp))
+    # ground points off the pixel's ray (the usual case for a caller), some far off, some NaN
+    x += rng.normal(0, 30.0, n)
+    y += rng.normal(0, 30.0, n)
+    z += rng.normal(0, 30.0, n)
+    x[:30] *= 1.5
+    z[30:40] = np.nan
+    got = gm.imageToProximateImagingLocusBatch(line, samp, x, y, z, 1e-5)
+    exp = rm.proximate_locus(line, samp, x, y, z, 1e-5, threads=0)
+    assert np.array_equal(got[7] & _capi.ST_REFERENCE_MASK, exp[7])
+    ok = (exp[7] & _capi.ST_NONFINITE) == 0
+    assert ok.sum() > n * 0.9
+    for k in range(3):
+        assert np.abs(got[k][ok] - exp[k][ok]).max() <= M_TOL
+    for k in range(3, 6):
+        assert np.abs(got[k][ok] - exp[k][ok]).max() <= 1e-9
+    fa = np.isfinite(exp[6])
+    assert np.array_equal(np.isfinite(got[6]), fa)
+    assert np.abs(got[6][fa] - exp[6][fa]).max(initial=0.0) <= M_TOL
+    import torch
+    dev = gm.imageToProximateImagingLocusBatch(*(torch.as_tensor(a, device="cuda") for a in (line, samp, x, y, z)), 1e-5)
+    torch.cuda.synchronize()
+    for k in range(7):
+        assert np.array_equal(dev[k].cpu().numpy(), got[k], equal_nan=True)
+
+
+@pytest.mark.parametrize("kind", KINDS)
 def test_ground_partials(ref, kind):
     from usgscsm_b200 import _capi, synth
     gm, rm = _pair(ref, kind)

@@ -69,6 +69,10 @@ SIGNATURES = {
         C.c_int, [_h, C.c_int64, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_image_to_remote_imaging_locus_dev": (
         C.c_int, [_h, C.c_int64, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_proximate_imaging_locus": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double] + [_dp] * 8),
+    "usgscsm_b200_image_to_proximate_imaging_locus_dev": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double] + [_dp] * 9),
     "usgscsm_b200_ground_partials": (C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_ground_partials_dev": (C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_ground_to_image_multi": (

@@ -594,6 +594,23 @@ static cudaError_t launchRemoteLocus(Model &m, long n, const double *line, const
   }
 }
 
+static cudaError_t launchProximateLocus(Model &m, long n, const double *line, const double *samp,
+                                        const double *x, const double *y, const double *z,
+                                        double prec, const LocusOut &o, cudaStream_t stream) {
+  switch (m.kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+      return launchLsProximateLocus(m.ls, m.smCount, n, line, samp, x, y, z, prec, o, stream);
+    case USGSCSM_B200_MODEL_PUSH_FRAME:
+      return launchPfProximateLocus(m.ls, m.smCount, n, line, samp, x, y, z, prec, o, stream);
+    case USGSCSM_B200_MODEL_FRAME:
+      return launchFrProximateLocus(m.fr, m.smCount, n, line, samp, x, y, z, o, stream);
+    case USGSCSM_B200_MODEL_SAR:
+      return launchSarProximateLocus(m.sar, m.smCount, n, line, samp, x, y, z, o, stream);
+    default:
+      return cudaErrorNotSupported;
+  }
+}
+
 static cudaError_t launchGroundPartials(Model &m, long n, const double *x, const double *y,
                                         const double *z, double *partials, uint32_t *status,
                                         cudaStream_t stream) {
@@ -670,6 +687,65 @@ int usgscsm_b200_image_to_remote_imaging_locus(usgscsm_b200_model *m, int64_t n,
       LocusOut o{dout, dout + chunk, dout + 2 * chunk, dout + 3 * chunk, dout + 4 * chunk,
                  dout + 5 * chunk, achieved ? dout + 6 * chunk : nullptr, status ? dst : nullptr};
       UB_CUDA(launchRemoteLocus(*m, cnt, dl, ds, prec, o, s.stream));
+      for (int k = 0; k < 7; k++)
+        if (host[k])
+          UB_CUDA(cudaMemcpyAsync(host[k] + off, dout + k * chunk, b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_proximate_imaging_locus_dev(
+    usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
+    const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
+    double *dy, double *dz, double *achieved, uint32_t *status, void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp || !x || !y || !z || !px || !py || !pz || !dx || !dy || !dz)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    LocusOut o{px, py, pz, dx, dy, dz, achieved, status};
+    UB_CUDA(launchProximateLocus(*m, (long)n, line, samp, x, y, z, prec, o,
+                                 static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_image_to_proximate_imaging_locus(
+    usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
+    const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
+    double *dy, double *dz, double *achieved, uint32_t *status) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp || !x || !y || !z || !px || !py || !pz || !dx || !dy || !dz)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const int nslots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    const double *in[5] = {line, samp, x, y, z};
+    double *host[7] = {px, py, pz, dx, dy, dz, achieved};
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % nslots);
+      m->ensureGen(si, chunk * 13);  // 5 in + 7 out + status
+      PipelineSlot &s = m->slots[si];
+      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));
+      const size_t b = cnt * sizeof(double);
+      double *din = s.gen, *dout = s.gen + 5 * chunk;
+      uint32_t *dst = reinterpret_cast<uint32_t *>(s.gen + 12 * chunk);
+      for (int k = 0; k < 5; k++)
+        UB_CUDA(cudaMemcpyAsync(din + k * chunk, in[k] + off, b, cudaMemcpyHostToDevice, s.stream));
+      LocusOut o{dout, dout + chunk, dout + 2 * chunk, dout + 3 * chunk, dout + 4 * chunk,
+                 dout + 5 * chunk, achieved ? dout + 6 * chunk : nullptr, status ? dst : nullptr};
+      UB_CUDA(launchProximateLocus(*m, cnt, din, din + chunk, din + 2 * chunk, din + 3 * chunk,
+                                   din + 4 * chunk, prec, o, s.stream));
       for (int k = 0; k < 7; k++)
         if (host[k])
           UB_CUDA(cudaMemcpyAsync(host[k] + off, dout + k * chunk, b, cudaMemcpyDeviceToHost, s.stream));

@@ -217,30 +217,63 @@ __global__ void __launch_bounds__(kThreads)
 
 // imageToRemoteImagingLocus FR:488-543: no de-jittering; point = the RAW parameters 0..2
 // (m_currentParameterValue), direction = unit(m * (ux, uy, f)); achievedPrecision = 0.
+UB_DEV void frRemoteLocusPoint(const FrameState &S, double line, double samp, double pos[3],
+                               double dir[3], uint32_t &st) {
+  const double *m = S.mNorm;
+  double focalPlaneX, focalPlaneY;
+  distortedFocalPlaneCoordinates(line, samp, S.fp, focalPlaneX, focalPlaneY);
+  double ux, uy;
+  removeDistortion(focalPlaneX, focalPlaneY, ux, uy, S.fp, 1.0E-6, st);
+  const double f = S.fp.focalLength;
+  double lookB[3] = {m[0] * ux + m[1] * uy + m[2] * f, m[3] * ux + m[4] * uy + m[5] * f,
+                     m[6] * ux + m[7] * uy + m[8] * f};
+  double mag = sqrt(lookB[0] * lookB[0] + lookB[1] * lookB[1] + lookB[2] * lookB[2]);
+  dir[0] = lookB[0] / mag;
+  dir[1] = lookB[1] / mag;
+  dir[2] = lookB[2] / mag;
+  pos[0] = S.rawParams[0];
+  pos[1] = S.rawParams[1];
+  pos[2] = S.rawParams[2];
+}
+
+UB_DEV void frFinishLocus(double pos[3], double dir[3], uint32_t &st) {
+  if (st & USGSCSM_B200_ST_ERROR_ALGORITHM) {
+    st = USGSCSM_B200_ST_ERROR_ALGORITHM;
+    pos[0] = pos[1] = pos[2] = dir[0] = dir[1] = dir[2] = nan("");
+  }
+  if (!(finite3(pos[0], pos[1], pos[2]) && finite3(dir[0], dir[1], dir[2])))
+    st |= USGSCSM_B200_ST_NONFINITE;
+}
+
 __global__ void __launch_bounds__(kThreads)
     frRemoteLocusKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ line,
                         const double *__restrict__ samp, LocusOut o) {
-  const double *m = S.mNorm;
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     uint32_t st = 0;
-    double focalPlaneX, focalPlaneY;
-    distortedFocalPlaneCoordinates(__ldcs(line + i), __ldcs(samp + i), S.fp, focalPlaneX, focalPlaneY);
-    double ux, uy;
-    removeDistortion(focalPlaneX, focalPlaneY, ux, uy, S.fp, 1.0E-6, st);
-    const double f = S.fp.focalLength;
-    double lookB[3] = {m[0] * ux + m[1] * uy + m[2] * f, m[3] * ux + m[4] * uy + m[5] * f,
-                       m[6] * ux + m[7] * uy + m[8] * f};
-    double mag = sqrt(lookB[0] * lookB[0] + lookB[1] * lookB[1] + lookB[2] * lookB[2]);
-    double dir[3] = {lookB[0] / mag, lookB[1] / mag, lookB[2] / mag};
-    double pos[3] = {S.rawParams[0], S.rawParams[1], S.rawParams[2]};
-    if (st & USGSCSM_B200_ST_ERROR_ALGORITHM) {
-      st = USGSCSM_B200_ST_ERROR_ALGORITHM;
-      pos[0] = pos[1] = pos[2] = dir[0] = dir[1] = dir[2] = nan("");
-    }
-    if (!(finite3(pos[0], pos[1], pos[2]) && finite3(dir[0], dir[1], dir[2])))
-      st |= USGSCSM_B200_ST_NONFINITE;
+    double pos[3], dir[3];
+    frRemoteLocusPoint(S, __ldcs(line + i), __ldcs(samp + i), pos, dir, st);
+    frFinishLocus(pos, dir, st);
     storeLocus(o, i, pos, dir, 0.0, st);
+  }
+}
+
+// imageToProximateImagingLocus FR:424-462: the point of the remote locus' line closest to the
+// ground point: point + dot(direction, ground - point) * direction.
+__global__ void __launch_bounds__(kThreads)
+    frProximateLocusKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ line,
+                           const double *__restrict__ samp, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z, LocusOut o) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t st = 0;
+    double pos[3], dir[3];
+    frRemoteLocusPoint(S, __ldcs(line + i), __ldcs(samp + i), pos, dir, st);
+    double toGround[3] = {__ldcs(x + i) - pos[0], __ldcs(y + i) - pos[1], __ldcs(z + i) - pos[2]};
+    double d = dir[0] * toGround[0] + dir[1] * toGround[1] + dir[2] * toGround[2];
+    double pt[3] = {pos[0] + d * dir[0], pos[1] + d * dir[1], pos[2] + d * dir[2]};
+    frFinishLocus(pt, dir, st);
+    storeLocus(o, i, pt, dir, 0.0, st);
   }
 }
 
@@ -294,6 +327,15 @@ cudaError_t launchGroundPartialsFr(const FrameState &S, int smCount, long n, con
                                    uint32_t *status, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   frGroundPartialsKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, partials, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchFrProximateLocus(const FrameState &S, int smCount, long n, const double *line,
+                                   const double *samp, const double *x, const double *y,
+                                   const double *z, const LocusOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  frProximateLocusKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, line, samp, x, y, z, o);
   countLaunch();
   return cudaGetLastError();
 }

@@ -102,6 +102,21 @@ cudaError_t launchSarRemoteLocus(const SarState &S, int smCount, long n, const d
                                  const double *samp, double prec, const LocusOut &o,
                                  cudaStream_t stream);
 
+cudaError_t launchLsProximateLocus(const LsState &S, int smCount, long n, const double *line,
+                                   const double *samp, const double *x, const double *y,
+                                   const double *z, double prec, const LocusOut &o,
+                                   cudaStream_t stream);
+cudaError_t launchPfProximateLocus(const LsState &S, int smCount, long n, const double *line,
+                                   const double *samp, const double *x, const double *y,
+                                   const double *z, double prec, const LocusOut &o,
+                                   cudaStream_t stream);
+cudaError_t launchFrProximateLocus(const FrameState &S, int smCount, long n, const double *line,
+                                   const double *samp, const double *x, const double *y,
+                                   const double *z, const LocusOut &o, cudaStream_t stream);
+cudaError_t launchSarProximateLocus(const SarState &S, int smCount, long n, const double *line,
+                                    const double *samp, const double *x, const double *y,
+                                    const double *z, const LocusOut &o, cudaStream_t stream);
+
 // push-frame (pf_kernels.cu)
 cudaError_t launchPfFrameletOrientations(const LsState &S, double *out, cudaStream_t stream);
 cudaError_t launchPfSensorPosition(const LsState &S, double time, double *xyz,

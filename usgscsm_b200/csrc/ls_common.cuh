@@ -292,5 +292,50 @@ UB_DEV void lsEllipsoidIntersect(const Ellipsoid &ell, double height, const doub
   achieved = fabs(height - h);
 }
 
+// imageToProximateImagingLocus LS:1175-1235 / PF:995-1055: three imageToGround calls (at the
+// ground point's height, one gsd below it, and at the height of the point of the ray closest to
+// the ground point) and two ellipsoid elevations.  `i2g(height, xyz, achieved, status)` is the
+// model's imageToGround for the pixel.  Only the last call receives the caller's warning
+// list; a csm::Error thrown by any of them escapes (outputs NaN).
+template <class I2G>
+UB_DEV void proximateLocusFromImageToGround(const Ellipsoid &ell, double gsd, double x, double y,
+                                            double z, double desiredPrecision, I2G &&i2g,
+                                            double pos[3], double dir[3], double &achieved,
+                                            uint32_t &status) {
+  const uint32_t kErr = USGSCSM_B200_ST_ERROR_ALGORITHM | USGSCSM_B200_ST_ERROR_UNKNOWN |
+                        USGSCSM_B200_ST_ERROR_OTHER;
+  double height = ellipsoidElevation(x, y, z, ell, desiredPrecision);
+  double gp1[3], gp2[3], a;
+  uint32_t st1 = 0, st2 = 0, st3 = 0;
+  i2g(height, gp1, a, st1);
+  double dx1 = x - gp1[0];
+  double dy1 = y - gp1[1];
+  double dz1 = z - gp1[2];
+  i2g(height - gsd, gp2, a, st2);
+  double dx2 = gp2[0] - gp1[0];
+  double dy2 = gp2[1] - gp1[1];
+  double dz2 = gp2[2] - gp1[2];
+  double mag2 = sqrt(dx2 * dx2 + dy2 * dy2 + dz2 * dz2);
+  dx2 /= mag2;
+  dy2 /= mag2;
+  dz2 /= mag2;
+  double scale = dx1 * dx2 + dy1 * dy2 + dz1 * dz2;
+  gp2[0] = gp1[0] + scale * dx2;
+  gp2[1] = gp1[1] + scale * dy2;
+  gp2[2] = gp1[2] + scale * dz2;
+  double hLocus = ellipsoidElevation(gp2[0], gp2[1], gp2[2], ell, desiredPrecision);
+  i2g(hLocus, pos, achieved, st3);
+  dir[0] = dx2;
+  dir[1] = dy2;
+  dir[2] = dz2;
+  status = (st3 & ~USGSCSM_B200_ST_NONFINITE) | ((st1 | st2) & kErr);
+  if (status & kErr) {
+    status &= kErr;
+    pos[0] = pos[1] = pos[2] = dir[0] = dir[1] = dir[2] = achieved = nan("");
+  }
+  if (!(finite3(pos[0], pos[1], pos[2]) && finite3(dir[0], dir[1], dir[2])))
+    status |= USGSCSM_B200_ST_NONFINITE;
+}
+
 }  // namespace ub200
 #endif

@@ -460,6 +460,35 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// ---- imageToProximateImagingLocus ----------------------------------------------------------
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads, 3)
+    lsProximateLocusKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                           const double *__restrict__ samp, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z, double prec,
+                           LocusOut o) {
+  extern __shared__ __align__(16) double smem[];
+  StagedTables TS{};
+  OrientationTables TG{S.positions.values, S.velocities.values, S.quaternions.values};
+  if (STAGE) TS = stageOrientationTables(S, S.hasAdj != 0, smem);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double l = __ldcs(line + i), sm = __ldcs(samp + i);
+    double pos[3], dir[3], a;
+    uint32_t st = 0;
+    proximateLocusFromImageToGround(
+        S.ell, S.gsd, __ldcs(x + i), __ldcs(y + i), __ldcs(z + i), prec,
+        [&](double h, double g[3], double &ach, uint32_t &s) {
+          if (STAGE)
+            lsImageToGroundPoint(S, TS, l, sm, h, prec, g[0], g[1], g[2], ach, s);
+          else
+            lsImageToGroundPoint(S, TG, l, sm, h, prec, g[0], g[1], g[2], ach, s);
+        },
+        pos, dir, a, st);
+    storeLocus(o, i, pos, dir, a, st);
+  }
+}
+
 // ---- model set-up helpers -------------------------------------------------------------------
 // The reference derives a few per-model inputs of the hot path at load time with its own
 // per-point routines (updateState LS:649-735, createProjectiveApproximation LS:2745-2803).
@@ -677,6 +706,28 @@ cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const 
   }
   countLaunch();
   return wc.release();
+}
+
+cudaError_t launchLsProximateLocus(const LsState &S, int smCount, long n, const double *line,
+                                   const double *samp, const double *x, const double *y,
+                                   const double *z, double prec, const LocusOut &o,
+                                   cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, 3);
+  if (stage) {
+    if (smemBytes > 48 * 1024)
+      cudaFuncSetAttribute(lsProximateLocusKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)smemBytes);
+    lsProximateLocusKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, line, samp, x, y,
+                                                                               z, prec, o);
+  } else {
+    lsProximateLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, x, y, z,
+                                                                        prec, o);
+  }
+  countLaunch();
+  return cudaGetLastError();
 }
 
 }  // namespace ub200

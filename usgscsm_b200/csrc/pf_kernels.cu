@@ -436,6 +436,31 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// imageToProximateImagingLocus PF:995-1055 (same construction as the line-scan model's).
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    pfProximateLocusKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
+                           const double *__restrict__ samp, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z, double prec,
+                           LocusOut o) {
+  extern __shared__ double smem[];
+  OrientCache C = stageOrientCache(S, smem, STAGE);
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double l = __ldcs(line + i), sm = __ldcs(samp + i);
+    double pos[3], dir[3], a;
+    uint32_t st = 0;
+    proximateLocusFromImageToGround(
+        S.ell, S.gsd, __ldcs(x + i), __ldcs(y + i), __ldcs(z + i), prec,
+        [&](double h, double g[3], double &ach, uint32_t &s) {
+          pfImageToGroundPoint(S, T, C, l, sm, h, prec, g[0], g[1], g[2], ach, s);
+        },
+        pos, dir, a, st);
+    storeLocus(o, i, pos, dir, a, st);
+  }
+}
+
 // getSensorPosition(double time) PF:1290-1303: getAdjSensorPosVel at `time`.
 __global__ void pfSensorPositionKernel(const __grid_constant__ LsState S, double time,
                                        double *__restrict__ xyz) {
@@ -554,6 +579,24 @@ cudaError_t launchGroundPartialsPf(const LsState &S, int smCount, long n, const 
         S, n, x, y, z, partials, status, wc.ptr, grabSize());
   countLaunch();
   return wc.release();
+}
+
+cudaError_t launchPfProximateLocus(const LsState &S, int smCount, long n, const double *line,
+                                   const double *samp, const double *x, const double *y,
+                                   const double *z, double prec, const LocusOut &o,
+                                   cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  if (stage)
+    pfProximateLocusKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, line, samp, x, y,
+                                                                               z, prec, o);
+  else
+    pfProximateLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, x, y, z,
+                                                                        prec, o);
+  countLaunch();
+  return cudaGetLastError();
 }
 
 }  // namespace ub200

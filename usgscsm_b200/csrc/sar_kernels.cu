@@ -441,6 +441,52 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// imageToProximateImagingLocus SAR:959-993: the point at the pixel's slant range from the
+// spacecraft, in the direction of the ground point's rejection from the velocity; direction =
+// the tangent of the range circle there.  achievedPrecision = 0, no warnings.
+template <bool STAGE>
+__global__ void __launch_bounds__(kThreads)
+    sarProximateLocusKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ line,
+                            const double *__restrict__ samp, const double *__restrict__ x,
+                            const double *__restrict__ y, const double *__restrict__ z, LocusOut o) {
+  extern __shared__ double smem[];
+  SarTables T = stageSarTables(S, smem, STAGE);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double time = S.startingEphemerisTime + (__ldcs(line + i) - 0.5) * S.exposureDuration;
+    double groundRange = (__ldcs(samp + i) - 0.5) * S.scaledPixelWidth;
+    double c[4];
+    sarRangeCoefficients(S, T, time, c);
+    double slantRange = poly3(c, groundRange);
+    double p[3], v[3];
+    sarPosVel(S, T, time, p, v);
+    // lookVec = normalized(rejection(ground - position, velocity)), U:972-1001
+    double w[3] = {__ldcs(x + i) - p[0], __ldcs(y + i) - p[1], __ldcs(z + i) - p[2]};
+    double pr = (w[0] * v[0] + w[1] * v[1] + w[2] * v[2]) / (v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    double rej[3] = {w[0] - pr * v[0], w[1] - pr * v[1], w[2] - pr * v[2]};
+    double inv = 1.0 / sqrt(rej[0] * rej[0] + rej[1] * rej[1] + rej[2] * rej[2]);
+    double look[3] = {inv * rej[0], inv * rej[1], inv * rej[2]};
+    double pt[3] = {p[0] + slantRange * look[0], p[1] + slantRange * look[1],
+                    p[2] + slantRange * look[2]};
+    double t[3];
+    if (S.lookDirection == 0) {  // LEFT: cross(velocity, lookVec)
+      t[0] = v[1] * look[2] - v[2] * look[1];
+      t[1] = v[2] * look[0] - v[0] * look[2];
+      t[2] = v[0] * look[1] - v[1] * look[0];
+    } else {  // cross(lookVec, velocity)
+      t[0] = look[1] * v[2] - look[2] * v[1];
+      t[1] = look[2] * v[0] - look[0] * v[2];
+      t[2] = look[0] * v[1] - look[1] * v[0];
+    }
+    inv = 1.0 / sqrt(t[0] * t[0] + t[1] * t[1] + t[2] * t[2]);
+    double dir[3] = {inv * t[0], inv * t[1], inv * t[2]};
+    uint32_t st = 0;
+    if (!(finite3(pt[0], pt[1], pt[2]) && finite3(dir[0], dir[1], dir[2])))
+      st |= USGSCSM_B200_ST_NONFINITE;
+    storeLocus(o, i, pt, dir, 0.0, st);
+  }
+}
+
 LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
   size_t bytes = sarTableBytes(S);
   stage = bytes <= kSarMaxStagedBytes;
@@ -570,6 +616,24 @@ cudaError_t launchGroundPartialsSar(const SarState &S, int smCount, long n, cons
         S, n, x, y, z, partials, status, wc.ptr, grabSize());
   countLaunch();
   return wc.release();
+}
+
+cudaError_t launchSarProximateLocus(const SarState &S, int smCount, long n, const double *line,
+                                    const double *samp, const double *x, const double *y,
+                                    const double *z, const LocusOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  size_t smemBytes;
+  bool stage;
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
+  if (stage) {
+    cudaError_t e = allowSmem(sarProximateLocusKernel<true>, smemBytes);
+    if (e != cudaSuccess) return e;
+    sarProximateLocusKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, line, samp, x, y, z, o);
+  } else {
+    sarProximateLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, x, y, z, o);
+  }
+  countLaunch();
+  return cudaGetLastError();
 }
 
 }  // namespace ub200

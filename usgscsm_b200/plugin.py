@@ -249,6 +249,29 @@ class RasterGM(object):
             self._h, n, _ptr(line), _ptr(samp), desiredPrecision, *[_ptr(o) for o in out], _ptr(st)))
         return tuple(out) + (st,)
 
+    def imageToProximateImagingLocusBatch(self, line, samp, x, y, z, desiredPrecision=0.001):
+        """csm::RasterGM::imageToProximateImagingLocus for arrays (host numpy or torch CUDA):
+        (px, py, pz, dx, dy, dz, achieved, status)."""
+        if _is_torch(line):
+            import torch
+            n = line.numel()
+            out = [torch.empty_like(line) for _ in range(7)]
+            st = torch.empty(n, dtype=torch.int32, device=line.device)
+            stream = torch.cuda.current_stream(line.device).cuda_stream
+            check(lib.usgscsm_b200_image_to_proximate_imaging_locus_dev(
+                self._h, n, _ptr(line), _ptr(samp), _ptr(x), _ptr(y), _ptr(z), desiredPrecision,
+                *[_ptr(o) for o in out], _ptr(st), stream))
+            return tuple(out) + (st,)
+        line = _host(line)
+        n = line.size
+        samp, x, y, z = _host(samp, n), _host(x, n), _host(y, n), _host(z, n)
+        out = [np.empty(n) for _ in range(7)]
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_image_to_proximate_imaging_locus(
+            self._h, n, _ptr(line), _ptr(samp), _ptr(x), _ptr(y), _ptr(z), desiredPrecision,
+            *[_ptr(o) for o in out], _ptr(st)))
+        return tuple(out) + (st,)
+
     def computeGroundPartialsBatch(self, x, y, z):
         """csm::RasterGM::computeGroundPartials for arrays -> ((n, 6) partials, status)."""
         if _is_torch(x):
