@@ -89,9 +89,11 @@ USGSCSM_B200_API int usgscsm_b200_device_count(void);
 /* ---- model construction ---------------------------------------------------------------
  * Replaces UsgsAstroPlugin::constructModelFromState (src/UsgsAstroPlugin.cpp:535-555) +
  * <Model>::populateModel (LS: src/UsgsAstroLsSensorModel.cpp:141-293): `state` is a model
- * state string as written by getModelState() -- "<MODEL_NAME>\n{json}", bare JSON, or the
+ * state string as written by getModelState() -- "<MODEL_NAME>\n{json}", bare JSON, the
  * body of a GXP .sup file (non-printable bytes are treated as newlines and the text is cut
- * to the outermost braces, src/Utilities.cpp:2489-2500).  The packed device state is
+ * to the outermost braces, src/Utilities.cpp:2489-2500) -- or the msgpack binary form of the
+ * state (nlohmann::json::to_msgpack; recognised by its first byte like isMsgpack,
+ * src/Utilities.cpp:2511-2530; bin/usgscsm_cam_test.cc:157-170).  The packed device state is
  * uploaded to CUDA device `device`.  Derived quantities the reference computes at load time
  * with its own per-point calls (updateState LS:649-735, createProjectiveApproximation
  * LS:2745-2803) are computed here by running the batch kernels on those points. */

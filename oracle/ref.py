@@ -175,5 +175,19 @@ class RefModel(object):
             raise RuntimeError("model is not a csm::SettableEllipsoid")
 
 
+def state_to_msgpack(state):
+    """nlohmann::json::to_msgpack of a model state string (the reference's binary state)."""
+    L = lib()
+    L.ref_state_to_msgpack.restype = C.c_size_t
+    L.ref_state_to_msgpack.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    raw = state.encode("utf-8") if isinstance(state, str) else state
+    n = L.ref_state_to_msgpack(raw, len(raw), None, 0)
+    if n == 0:
+        raise RuntimeError(L.ref_last_error().decode())
+    buf = C.create_string_buffer(n)
+    L.ref_state_to_msgpack(raw, len(raw), buf, n)
+    return buf.raw
+
+
 def max_threads():
     return lib().ref_max_threads()

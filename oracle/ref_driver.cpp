@@ -365,6 +365,20 @@ int ref_ground_partials(void *h, long n, const double *x, const double *y, const
   return 0;
 }
 
+// nlohmann::json::to_msgpack of a model state (what bin/usgscsm_cam_test.cc
+// --output-binary-model-state writes).  Returns the length; copies up to cap bytes.
+size_t ref_state_to_msgpack(const char *state, size_t len, unsigned char *out, size_t cap) {
+  try {
+    nlohmann::json j = stateAsJson(std::string(state, len));
+    std::vector<uint8_t> v = nlohmann::json::to_msgpack(j);
+    if (out && cap >= v.size()) std::memcpy(out, v.data(), v.size());
+    return v.size();
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return 0;
+  }
+}
+
 // csm::SettableEllipsoid::setEllipsoid (LS:2116-2119 etc.).
 int ref_set_ellipsoid(void *h, double a, double b) {
   RefModel *rm = static_cast<RefModel *>(h);

@@ -213,8 +213,7 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     return fail(USGSCSM_B200_ENODEVICE, "no usable CUDA device with that index");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(device));
-    std::string text = stateJsonText(state, len);
-    json::Value root = json::parse(text);
+    json::Value root = parseState(state, len);
     StateReader st(root);
     std::unique_ptr<usgscsm_b200_model> m(new usgscsm_b200_model);
     m->device = device;
@@ -258,8 +257,7 @@ int usgscsm_b200_model_name_from_state(const char *state, size_t len, char *name
   if (!state || !name || cap == 0) return fail(USGSCSM_B200_EINVAL, "null argument");
   name[0] = 0;
   return guarded([&]() -> int {
-    std::string text = stateJsonText(state, len);
-    json::Value root = json::parse(text);
+    json::Value root = parseState(state, len);
     StateReader st(root);
     std::string n = st.getString("m_modelName");
     if (n != "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL" && n != "USGS_ASTRO_PUSH_FRAME_SENSOR_MODEL" &&

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "json_min.h"
+#include "msgpack_min.h"
 
 namespace ub200 {
 
@@ -32,6 +33,13 @@ inline std::string stateJsonText(const char *state, size_t len) {
   if (first == std::string::npos) first = 0;
   if (last == std::string::npos) throw std::runtime_error("model state holds no JSON object");
   return s.substr(first, last + 1 - first);
+}
+
+// A model state in either encoding -> value tree: msgpack when the first byte is a map marker
+// (isMsgpack, src/Utilities.cpp:2511-2530), JSON text (possibly wrapped in a .sup) otherwise.
+inline json::Value parseState(const char *state, size_t len) {
+  if (msgpack::looksLikeMap(state, len)) return msgpack::parse(state, len);
+  return json::parse(stateJsonText(state, len));
 }
 
 class StateReader {

@@ -376,17 +376,15 @@ class UsgsAstroPlugin(object):
     def getModelNameFromModelState(self, modelState):
         """UsgsAstroPlugin.cpp:176-218: JSON key m_modelName (after stateAsJson)."""
         raw = self._state_bytes(modelState)
-        text = bytes(c if 32 <= c < 127 else 10 for c in raw).decode("ascii")
-        a, b = text.find("{"), text.rfind("}")
-        try:
-            name = json.loads(text[max(a, 0):b + 1])["m_modelName"]
-        except Exception:
-            raise Error(Error.INVALID_SENSOR_MODEL_STATE, "No 'm_modelName' key in the model state object.",
-                        "UsgsAstroPlugin::getModelNameFromModelState")
-        if name not in _MODEL_NAMES:
+        buf = C.create_string_buffer(128)
+        code = lib.usgscsm_b200_model_name_from_state(raw, len(raw), buf, 128)
+        if code == _capi.EUNSUPPORTED:
             raise Error(Error.SENSOR_MODEL_NOT_SUPPORTED, "Sensor model not supported.",
                         "UsgsAstroPlugin::getModelNameFromModelState")
-        return name
+        if code != _capi.OK:
+            raise Error(Error.INVALID_SENSOR_MODEL_STATE, "No 'm_modelName' key in the model state object.",
+                        "UsgsAstroPlugin::getModelNameFromModelState")
+        return buf.value.decode("ascii")
 
     def canModelBeConstructedFromState(self, modelName, modelState, warnings=None):
         try:
@@ -405,7 +403,7 @@ class UsgsAstroPlugin(object):
                         lib.usgscsm_b200_last_error().decode("utf-8", "replace"),
                         "UsgsAstroPlugin::constructModelFromState")
         check(code)
-        return RasterGM(h, modelState if isinstance(modelState, str) else raw.decode("latin-1"))
+        return RasterGM(h, modelState)
 
 
 # ---- building blocks (include/usgscsm/Distortion.h, Utilities.h of the reference) ------------
