@@ -226,6 +226,24 @@ USGSCSM_B200_API int usgscsm_b200_ground_partials_dev(usgscsm_b200_model *m, int
                                      const double *y, const double *z, double *partials,
                                      uint32_t *status, void *stream);
 
+/* computeSensorPartials: replaces csm::RasterGM::computeSensorPartials(int index, const
+ * EcefCoord&, double desiredPrecision, double* achievedPrecision, WarningList*) (LS:1336-1348)
+ * and, when img_line / img_samp are given, the overload that takes the image point
+ * (LS:1373-1396): the partial derivatives of line and sample with respect to adjustable
+ * parameter `index`, by a forward difference of two groundToImage searches, the second with
+ * the parameter moved by m_gsd.  Line-scan model only (USGSCSM_B200_EUNSUPPORTED otherwise).
+ * computeAllSensorPartials (csm/RasterGM.cpp:52-100) is this call once per parameter index. */
+USGSCSM_B200_API int usgscsm_b200_sensor_partials(usgscsm_b200_model *m, int index, int64_t n,
+                                 const double *x, const double *y, const double *z,
+                                 const double *img_line, const double *img_samp, double prec,
+                                 double *dline, double *dsamp, double *achieved,
+                                 uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int index, int64_t n,
+                                     const double *x, const double *y, const double *z,
+                                     const double *img_line, const double *img_samp,
+                                     double prec, double *dline, double *dsamp,
+                                     double *achieved, uint32_t *status, void *stream);
+
 /* Several GPUs from one process (row-band / chunk sharding, no exchange step): models[g] are
  * the SAME model state loaded on n_models different devices; contiguous chunk g of the host
  * arrays (sizes differ by at most one point) is processed on models[g], all concurrently.

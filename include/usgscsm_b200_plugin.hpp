@@ -228,6 +228,30 @@ class RasterGM {
     raiseOrWarn(st, NULL, "computeGroundPartials");
     return p;
   }
+  // LS:1336-1396 (line-scan model; csm::RasterGM::SensorPartials = pair<line, sample> partial)
+  std::pair<double, double> computeSensorPartials(int index, const csm::EcefCoord &groundPt,
+                                                  double desiredPrecision = 0.001,
+                                                  double *achievedPrecision = NULL,
+                                                  csm::WarningList *warnings = NULL) const {
+    double dl = 0, ds = 0, a = 0;
+    uint32_t st = 0;
+    check(usgscsm_b200_sensor_partials(m_h, index, 1, &groundPt.x, &groundPt.y, &groundPt.z, NULL,
+                                       NULL, desiredPrecision, &dl, &ds, &a, &st),
+          "computeSensorPartials");
+    raiseOrWarn(st, warnings, "computeSensorPartials");
+    if (achievedPrecision) *achievedPrecision = a;
+    return std::make_pair(dl, ds);
+  }
+  void computeSensorPartialsBatch(int index, size_t n, const double *x, const double *y,
+                                  const double *z, double desiredPrecision, double *linePartial,
+                                  double *sampPartial, double *achievedPrecision = NULL,
+                                  uint32_t *status = NULL, const double *imgLine = NULL,
+                                  const double *imgSamp = NULL) const {
+    check(usgscsm_b200_sensor_partials(m_h, index, (int64_t)n, x, y, z, imgLine, imgSamp,
+                                       desiredPrecision, linePartial, sampPartial,
+                                       achievedPrecision, status),
+          "computeSensorPartialsBatch");
+  }
   // csm::SettableEllipsoid (LS:2116-2119)
   void setEllipsoid(double semiMajorRadius, double semiMinorRadius) {
     check(usgscsm_b200_model_set_ellipsoid(m_h, semiMajorRadius, semiMinorRadius), "setEllipsoid");

@@ -45,6 +45,7 @@ def lib():
                                           C.c_double, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_remote_locus.argtypes = [C.c_void_p, C.c_long, _dp, _dp, C.c_double] + [_dp] * 8 + [C.c_int]
         L.ref_proximate_locus.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 8 + [C.c_int]
+        L.ref_sensor_partials.argtypes = [C.c_void_p, C.c_int, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 4 + [C.c_int]
         L.ref_ground_partials.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_set_ellipsoid.argtypes = [C.c_void_p, C.c_double, C.c_double]
         L.ref_lagrange.argtypes = [C.c_int, _dp, C.c_double, C.c_double, C.c_double, C.c_int,
@@ -158,6 +159,22 @@ class RefModel(object):
                                     y.ctypes.data, z.ctypes.data, prec,
                                     *[o.ctypes.data for o in out], st.ctypes.data, threads)
         return tuple(out) + (st,)
+
+    def sensor_partials(self, index, x, y, z, prec=0.001, image_pts=None, threads=1):
+        """computeSensorPartials per point -> (dline, dsamp, achieved, status)."""
+        x = _a(x)
+        n = x.size
+        y, z = _a(y, n), _a(z, n)
+        il = isamp = None
+        if image_pts is not None:
+            il, isamp = _a(image_pts[0], n), _a(image_pts[1], n)
+        dl, ds, ach = np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_sensor_partials(self._h, int(index), n, x.ctypes.data, y.ctypes.data, z.ctypes.data,
+                                    None if il is None else il.ctypes.data,
+                                    None if isamp is None else isamp.ctypes.data, prec,
+                                    dl.ctypes.data, ds.ctypes.data, ach.ctypes.data, st.ctypes.data, threads)
+        return dl, ds, ach, st
 
     def ground_partials(self, x, y, z, threads=1):
         """computeGroundPartials per point -> ((n, 6) partials, status)."""

@@ -334,6 +334,45 @@ int ref_proximate_locus(void *h, long n, const double *line, const double *samp,
   return 0;
 }
 
+// computeSensorPartials(index, ...) over n points; img_line / img_samp nullable (then the
+// 5-argument overload computes the image point itself).
+int ref_sensor_partials(void *h, int index, long n, const double *x, const double *y,
+                        const double *z, const double *img_line, const double *img_samp,
+                        double prec, double *dline, double *dsamp, double *achieved,
+                        uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    csm::RasterGM::SensorPartials p(std::nan(""), std::nan(""));
+    try {
+      csm::WarningList warn;
+      if (img_line && img_samp)
+        p = gm->computeSensorPartials(index, csm::ImageCoord(img_line[i], img_samp[i]),
+                                      csm::EcefCoord(x[i], y[i], z[i]), prec, &ach, &warn);
+      else
+        p = gm->computeSensorPartials(index, csm::EcefCoord(x[i], y[i], z[i]), prec, &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+      ach = std::nan("");
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+      ach = std::nan("");
+    }
+    if (!(std::isfinite(p.first) && std::isfinite(p.second))) st |= ST_NONFINITE;
+    dline[i] = p.first;
+    dsamp[i] = p.second;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
 // computeGroundPartials over n points; partials = 6 doubles per point (LS:1299-1325 etc.).
 int ref_ground_partials(void *h, long n, const double *x, const double *y, const double *z,
                         double *partials, uint32_t *status, int threads) {

@@ -145,3 +145,47 @@ def test_set_ellipsoid(ref, kind):
     line, samp = pixels(rng, n, nl, ns)
     x, y, z = check_i2g(gm, rm, line, samp, synth.synthetic_dem(line, samp))
     check_g2i(gm, rm, x, y, z)
+
+
+@pytest.mark.parametrize("kind", ["linescan", "linescan_adjusted"])
+@pytest.mark.parametrize("index", [0, 2, 4, 7, 11, 14, 15])
+def test_sensor_partials_linescan(ref, kind, index):
+    """computeSensorPartials LS:1336-1396: both overloads, every kind of adjustable parameter
+    (position offsets, velocity, attitude bias / rate / acceleration, focal length)."""
+    from usgscsm_b200 import _capi, synth
+    gm, rm = _pair(ref, kind)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(16 + index)
+    n = 6000
+    line, samp = pixels(rng, n, nl, ns)
+    x, y, z, _, _ = gm.imageToGroundBatch(line, samp, synth.synthetic_dem(line, samp))
+    x[:10] = np.nan
+    dl, ds, ach, st = gm.computeSensorPartialsBatch(index, x, y, z, 1e-6)
+    el, es, ea, est = rm.sensor_partials(index, x, y, z, 1e-6, threads=0)
+    assert np.array_equal(st & _capi.ST_REFERENCE_MASK, est)
+    ok = np.isfinite(el)
+    assert np.array_equal(np.isfinite(dl), ok) and ok.sum() == n - 10
+    scale = max(1.0, np.abs(el[ok]).max(), np.abs(es[ok]).max())
+    assert np.abs(dl[ok] - el[ok]).max() <= 1e-9 * scale
+    assert np.abs(ds[ok] - es[ok]).max() <= 1e-9 * scale
+    assert np.abs(ach[ok] - ea[ok]).max() <= PX_TOL
+    # the overload that is handed the image point
+    dl2, ds2, _, st2 = gm.computeSensorPartialsBatch(index, x, y, z, 1e-6, imagePts=(line, samp))
+    el2, es2, _, est2 = rm.sensor_partials(index, x, y, z, 1e-6, image_pts=(line, samp), threads=0)
+    assert np.array_equal(st2 & _capi.ST_REFERENCE_MASK, est2)
+    assert np.abs(dl2[ok] - el2[ok]).max() <= 1e-9 * scale
+    assert np.abs(ds2[ok] - es2[ok]).max() <= 1e-9 * scale
+    import torch
+    d = gm.computeSensorPartialsBatch(index, *(torch.as_tensor(a, device="cuda") for a in (x, y, z)), 1e-6)
+    torch.cuda.synchronize()
+    assert np.array_equal(d[0].cpu().numpy(), dl, equal_nan=True)
+    assert np.array_equal(d[1].cpu().numpy(), ds, equal_nan=True)
+
+
+def test_sensor_partials_other_models_unsupported():
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import _capi, synth
+    gm = ub.UsgsAstroPlugin().constructModelFromState(synth.frame_state())
+    with pytest.raises(_capi.EngineError) as e:
+        gm.computeSensorPartialsBatch(0, np.zeros(3), np.zeros(3), np.zeros(3))
+    assert e.value.code == _capi.EUNSUPPORTED

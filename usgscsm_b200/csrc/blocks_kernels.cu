@@ -64,6 +64,38 @@ __global__ void aosJoinKernel(long n, const double *__restrict__ c0, const doubl
   }
 }
 
+// computeSensorPartials LS:1373-1396: (img1 - image_pt) / DELTA from the two searches.  The
+// warning list of the scalar call only sees the adjusted search; a csm::Error thrown by
+// either search escapes (NaN partials, error bit only).
+__global__ void sensorPartialsCombineKernel(long n, const double *__restrict__ l0,
+                                            const double *__restrict__ s0,
+                                            const uint32_t *__restrict__ st0,
+                                            const double *__restrict__ l1,
+                                            const double *__restrict__ s1, double delta,
+                                            double *__restrict__ dline, double *__restrict__ dsamp,
+                                            double *__restrict__ achieved,
+                                            uint32_t *__restrict__ status) {
+  const uint32_t kErr = USGSCSM_B200_ST_ERROR_ALGORITHM | USGSCSM_B200_ST_ERROR_UNKNOWN |
+                        USGSCSM_B200_ST_ERROR_OTHER;
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t a = st0 ? st0[i] : 0u, b = status[i];
+    double pl = (l1[i] - l0[i]) / delta;
+    double ps = (s1[i] - s0[i]) / delta;
+    uint32_t st = (b & (USGSCSM_B200_ST_NO_INTERSECTION | USGSCSM_B200_ST_PRECISION_NOT_MET)) |
+                  ((a | b) & kErr);
+    if (st & kErr) {
+      st &= kErr;
+      pl = ps = nan("");
+      if (achieved) achieved[i] = nan("");
+    }
+    if (!(isfinite(pl) && isfinite(ps))) st |= USGSCSM_B200_ST_NONFINITE;
+    dline[i] = pl;
+    dsamp[i] = ps;
+    status[i] = st;
+  }
+}
+
 // r[i] = refinedReciprocal(b[i]); a divisor the fast path can never accept (zero, subnormal,
 // huge, non-finite) gets NaN, which sends every division by it to the slow path.
 __global__ void reciprocalKernel(int n, const double *__restrict__ b, double *__restrict__ r) {
@@ -169,6 +201,18 @@ cudaError_t launchAosJoin(int ncomp, long n, const double *c0, const double *c1,
     aosJoinKernel<3><<<blocks, 256, 0, stream>>>(n, c0, c1, c2, aos);
   else
     aosJoinKernel<2><<<blocks, 256, 0, stream>>>(n, c0, c1, c2, aos);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchSensorPartialsCombine(long n, const double *l0, const double *s0,
+                                        const uint32_t *st0, const double *l1, const double *s1,
+                                        double delta, double *dline, double *dsamp,
+                                        double *achieved, uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  sensorPartialsCombineKernel<<<blocks, 256, 0, stream>>>(n, l0, s0, st0, l1, s1, delta, dline,
+                                                          dsamp, achieved, status);
   countLaunch();
   return cudaGetLastError();
 }

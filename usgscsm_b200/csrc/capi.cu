@@ -789,6 +789,104 @@ int usgscsm_b200_ground_partials(usgscsm_b200_model *m, int64_t n, const double 
   });
 }
 
+// computeSensorPartials(index, ground_pt, prec, ach, warn) LS:1336-1396 over n points: the
+// search with the model as it is (skipped when the caller supplies the image points, the
+// 6-argument overload), the search with parameter `index` moved by m_gsd, forward difference.
+static int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
+                             const double *y, const double *z, const double *img_line,
+                             const double *img_samp, double prec, double *dline, double *dsamp,
+                             double *achieved, uint32_t *status, cudaStream_t stream) {
+  const double delta = m->ls.gsd;
+  const LsState adj = adjustedLineScanner(*m, index, delta);
+  const bool haveImage = img_line && img_samp;
+  // scratch: l0, s0 (unless supplied), l1, s1, st0, st1 (unless the caller wants status)
+  double *scratch = nullptr;
+  uint32_t *stScratch = nullptr;
+  UB_CUDA(cudaMallocAsync(&scratch, (size_t)n * 4 * sizeof(double), stream));
+  UB_CUDA(cudaMallocAsync(&stScratch, (size_t)n * 2 * sizeof(uint32_t), stream));
+  double *l0 = scratch, *s0 = scratch + n, *l1 = scratch + 2 * n, *s1 = scratch + 3 * n;
+  uint32_t *st0 = stScratch, *st1 = status ? status : stScratch + n;
+  cudaError_t e = cudaSuccess;
+  if (!haveImage)
+    e = launchLsGroundToImage(m->ls, m->smCount, n, x, y, z, prec, l0, s0, nullptr, st0, stream);
+  if (e == cudaSuccess)
+    e = launchLsGroundToImage(adj, m->smCount, n, x, y, z, prec, l1, s1, achieved, st1, stream);
+  if (e == cudaSuccess)
+    e = launchSensorPartialsCombine(n, haveImage ? img_line : l0, haveImage ? img_samp : s0,
+                                    haveImage ? nullptr : st0, l1, s1, delta, dline, dsamp,
+                                    achieved, st1, stream);
+  cudaFreeAsync(scratch, stream);
+  cudaFreeAsync(stScratch, stream);
+  UB_CUDA(e);
+  return USGSCSM_B200_OK;
+}
+
+static int sensorPartialsCheck(usgscsm_b200_model *m, int index, int64_t n, const void *x,
+                               const void *y, const void *z, const void *dline,
+                               const void *dsamp) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (m->kind != USGSCSM_B200_MODEL_LINE_SCANNER)
+    return fail(USGSCSM_B200_EUNSUPPORTED, "sensor partials are built for the line-scan model only");
+  if (index < 0 || index >= 16) return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
+  if (n > 0 && (!x || !y || !z || !dline || !dsamp)) return fail(USGSCSM_B200_EINVAL, "null array");
+  return USGSCSM_B200_OK;
+}
+
+int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int index, int64_t n, const double *x,
+                                     const double *y, const double *z, const double *img_line,
+                                     const double *img_samp, double prec, double *dline,
+                                     double *dsamp, double *achieved, uint32_t *status,
+                                     void *stream) {
+  int c = sensorPartialsCheck(m, index, n, x, y, z, dline, dsamp);
+  if (c != USGSCSM_B200_OK || n == 0) return c;
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    return sensorPartialsDev(m, index, (long)n, x, y, z, img_line, img_samp, prec, dline, dsamp,
+                             achieved, status, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int usgscsm_b200_sensor_partials(usgscsm_b200_model *m, int index, int64_t n, const double *x,
+                                 const double *y, const double *z, const double *img_line,
+                                 const double *img_samp, double prec, double *dline, double *dsamp,
+                                 double *achieved, uint32_t *status) {
+  int c = sensorPartialsCheck(m, index, n, x, y, z, dline, dsamp);
+  if (c != USGSCSM_B200_OK || n == 0) return c;
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const bool haveImage = img_line && img_samp;
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    m->ensureGen(0, chunk * 9);  // x y z (l s) | dl ds ach | status
+    PipelineSlot &s = m->slots[0];
+    double *g = s.gen;
+    uint32_t *dst = reinterpret_cast<uint32_t *>(g + 8 * chunk);
+    for (long off = 0; off < n; off += chunk) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const size_t b = cnt * sizeof(double);
+      UB_CUDA(cudaMemcpyAsync(g, x + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(g + chunk, y + off, b, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(cudaMemcpyAsync(g + 2 * chunk, z + off, b, cudaMemcpyHostToDevice, s.stream));
+      if (haveImage) {
+        UB_CUDA(cudaMemcpyAsync(g + 3 * chunk, img_line + off, b, cudaMemcpyHostToDevice, s.stream));
+        UB_CUDA(cudaMemcpyAsync(g + 4 * chunk, img_samp + off, b, cudaMemcpyHostToDevice, s.stream));
+      }
+      int rc = sensorPartialsDev(m, index, cnt, g, g + chunk, g + 2 * chunk,
+                                 haveImage ? g + 3 * chunk : nullptr,
+                                 haveImage ? g + 4 * chunk : nullptr, prec, g + 5 * chunk,
+                                 g + 6 * chunk, achieved ? g + 7 * chunk : nullptr, dst, s.stream);
+      if (rc != USGSCSM_B200_OK) return rc;
+      UB_CUDA(cudaMemcpyAsync(dline + off, g + 5 * chunk, b, cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaMemcpyAsync(dsamp + off, g + 6 * chunk, b, cudaMemcpyDeviceToHost, s.stream));
+      if (achieved)
+        UB_CUDA(cudaMemcpyAsync(achieved + off, g + 7 * chunk, b, cudaMemcpyDeviceToHost, s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    return USGSCSM_B200_OK;
+  });
+}
+
 // csm::SettableEllipsoid::setEllipsoid / getEllipsoid (LS:2116-2119, PF:1663-1666,
 // FR:2235-2240, SAR:1884-1887): replaces the two radii, nothing else is re-derived.
 int usgscsm_b200_model_set_ellipsoid(usgscsm_b200_model *m, double semi_major, double semi_minor) {

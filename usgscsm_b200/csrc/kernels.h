@@ -160,6 +160,10 @@ cudaError_t launchAosSplit(int ncomp, long n, const double *aos, double *c0, dou
                            double *c2, cudaStream_t stream);
 cudaError_t launchAosJoin(int ncomp, long n, const double *c0, const double *c1, const double *c2,
                           double *aos, cudaStream_t stream);
+cudaError_t launchSensorPartialsCombine(long n, const double *l0, const double *s0,
+                                        const uint32_t *st0, const double *l1, const double *s1,
+                                        double delta, double *dline, double *dsamp,
+                                        double *achieved, uint32_t *status, cudaStream_t stream);
 cudaError_t launchReciprocals(int n, const double *b, double *r, cudaStream_t stream);
 cudaError_t launchDivisionSelfTest(unsigned long long seed, int blocks, long perThread,
                                    unsigned long long *mismatches, cudaStream_t stream);

@@ -96,6 +96,7 @@ struct Model {
 // model_ls.cu
 void loadLineScanner(Model &m, const class StateReader &st);
 void repackLineScanner(Model &m);  // after a parameter / projective-seed change
+LsState adjustedLineScanner(const Model &m, int index, double delta);
 // model_pf.cu
 void loadPushFrame(Model &m, const class StateReader &st);
 void repackPushFrame(Model &m);  // after a parameter change: params + framelet orientations

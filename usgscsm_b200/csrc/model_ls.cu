@@ -232,6 +232,20 @@ void repackLineScanner(Model &m) {
   }
 }
 
+// The packed state groundToImage(ground_pt, adj, ...) sees when adj[index] = delta and every
+// other adjustment is 0: getValue(i, adj) = m_currentParameterValue[i] + adj[i] (LS:2129-2132).
+LsState adjustedLineScanner(const Model &m, int index, double delta) {
+  LsState S = m.ls;
+  S.hasAdj = 0;
+  S.hasAttAdj = 0;
+  for (int i = 0; i < 16; i++) {
+    S.params[i] = m.params[i] + (i == index ? delta : 0.0);
+    if (S.params[i] != 0) S.hasAdj = 1;
+    if (i >= 6 && i <= 14 && S.params[i] != 0) S.hasAttAdj = 1;
+  }
+  return S;
+}
+
 void loadLineScanner(Model &m, const StateReader &st) {
   LsState &S = m.ls;
   S = LsState{};

@@ -291,6 +291,33 @@ class RasterGM(object):
         check(lib.usgscsm_b200_ground_partials(self._h, n, _ptr(x), _ptr(y), _ptr(z), _ptr(p), _ptr(st)))
         return p, st
 
+    def computeSensorPartialsBatch(self, index, x, y, z, desiredPrecision=0.001, imagePts=None):
+        """csm::RasterGM::computeSensorPartials for arrays (line-scan model): returns
+        (dLine/dParam, dSamp/dParam, achieved, status).  `imagePts` = (line, samp) arrays selects
+        the overload that takes the image point."""
+        il, isamp = (None, None) if imagePts is None else imagePts
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            dl, ds, ach = (torch.empty_like(x) for _ in range(3))
+            st = torch.empty(n, dtype=torch.int32, device=x.device)
+            stream = torch.cuda.current_stream(x.device).cuda_stream
+            check(lib.usgscsm_b200_sensor_partials_dev(
+                self._h, int(index), n, _ptr(x), _ptr(y), _ptr(z), _ptr(il), _ptr(isamp),
+                desiredPrecision, _ptr(dl), _ptr(ds), _ptr(ach), _ptr(st), stream))
+            return dl, ds, ach, st
+        x = _host(x)
+        n = x.size
+        y, z = _host(y, n), _host(z, n)
+        if il is not None:
+            il, isamp = _host(il, n), _host(isamp, n)
+        dl, ds, ach = np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_sensor_partials(
+            self._h, int(index), n, _ptr(x), _ptr(y), _ptr(z), _ptr(il), _ptr(isamp),
+            desiredPrecision, _ptr(dl), _ptr(ds), _ptr(ach), _ptr(st)))
+        return dl, ds, ach, st
+
     def computeGroundPartials(self, groundPt):
         """csm::RasterGM::computeGroundPartials (one point): a list of six partials."""
         p, st = self.computeGroundPartialsBatch([groundPt[0]], [groundPt[1]], [groundPt[2]])
