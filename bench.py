@@ -98,9 +98,11 @@ class ClockSampler(object):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def workload_state(n_gpus, lines_per_gpu):
+def workload_state(image, lines):
+    """Image `image` of the job: a C2-shaped line-scan state (5064 x `lines`), its own orbit
+    phase and attitude wobble (seed 20261104 + image)."""
     from usgscsm_b200 import synth
-    return synth.linescan_state(n_lines=lines_per_gpu * n_gpus, n_samples=N_SAMPLES, seed=20261104)
+    return synth.linescan_state(n_lines=lines, n_samples=N_SAMPLES, seed=20261104 + image)
 
 
 def peak_hbm():
@@ -172,8 +174,9 @@ def run_reference(args):
     if not ref.available():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libusgscsm_ref.so not built"}))
         return
-    state = workload_state(args.gpus, args.lines)
-    n_lines_total = args.lines * args.gpus
+    # every image of the job has the C2 shape and costs the same per point: image 0 is sampled
+    state = workload_state(0, args.lines)
+    n_lines_total = args.lines
     # each step is one pass over a sample sized for ~4 s of host work
     _, cores, kind, desc, again = cpu_reference_rate(state, n_lines_total, 4.0)
     for _ in range(args.warmup):
@@ -198,11 +201,14 @@ def run_reference(args):
 
 
 def workload_config(args):
-    return {"workload": "C2 orbital line-scan (lroLrocNac distortion) %dx%d dense grid per GPU, "
+    return {"workload": "C2 orbital line-scan (lroLrocNac distortion) %dx%d dense grid, "
                         "imageToGround at synthetic-DEM heights then groundToImage; value = "
-                        "groundToImage" % (N_SAMPLES, args.lines),
+                        "groundToImage; at N GPUs the job is N such images (C5 style)"
+                        % (N_SAMPLES, args.lines),
             "points_per_gpu": N_SAMPLES * args.lines, "desired_precision": PREC,
-            "sharding": "row bands, one per GPU" if args.gpus > 1 else "single GPU",
+            "sharding": ("%d images, each split into %d row bands, rank r takes band r of every "
+                         "image; no data-path collective" % (args.gpus, args.gpus))
+            if args.gpus > 1 else "single GPU",
             "l2": "inputs (6.3 GB per GPU) larger than L2; no flush needed"}
 
 
@@ -242,20 +248,31 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # The job: `world` images of the C2 shape; every image is cut into `world` row bands and
+    # this rank takes band `rank` of each (world == 1: the whole single image).  Per-GPU work
+    # is the same at every N (weak scaling) and every image keeps the C2 table sizes.
+    from usgscsm_b200 import sharding
     lines = args.lines
-    n = lines * N_SAMPLES
-    state = workload_state(world, lines)
-    model = ub.UsgsAstroPlugin(device=local).constructModelFromState(state)
-    line0 = rank * lines + 0.5  # this rank's row band
+    first, band = sharding.band_for_rank(lines, rank, world)
+    seg = band * N_SAMPLES                  # points of one band
+    n = world * seg                         # points this rank processes per step
+    n_job = world * lines * N_SAMPLES       # points of the whole job per step
+    states = [workload_state(i, lines) for i in range(world)]
+    plugin = ub.UsgsAstroPlugin(device=local)
+    models = [plugin.constructModelFromState(s) for s in states]
+    model, state = models[0], states[0]
+    line0 = first + 0.5
 
-    # synthetic DEM heights for the band, built band by band on the device
+    # synthetic DEM heights of the band (the same band of every image)
     h = torch.empty(n, dtype=torch.float64, device=dev)
     cols = torch.arange(N_SAMPLES, device=dev, dtype=torch.float64) + 0.5
     cterm = torch.cos(2 * np.pi * cols / 1024.0)
-    for r0 in range(0, lines, 4096):
-        r1 = min(lines, r0 + 4096)
+    for r0 in range(0, band, 4096):
+        r1 = min(band, r0 + 4096)
         rows = torch.arange(r0, r1, device=dev, dtype=torch.float64) + line0
         h[r0 * N_SAMPLES:r1 * N_SAMPLES] = (500.0 * torch.sin(2 * np.pi * rows / 4096.0)[:, None] * cterm[None, :]).reshape(-1)
+    for i in range(1, world):
+        h[i * seg:(i + 1) * seg] = h[:seg]
 
     x, y, z = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
     st_g = torch.empty(n, dtype=torch.int32, device=dev)
@@ -264,15 +281,20 @@ def run_b200(args):
     stream = torch.cuda.current_stream(dev).cuda_stream
     h_lib = model._h
 
-    def i2g():
-        _capi.check(_capi.lib.usgscsm_b200_image_to_ground_grid_dev(
-            h_lib, line0, 0.5, 1.0, 1.0, lines, N_SAMPLES, h.data_ptr(), 1, PREC, x.data_ptr(),
-            y.data_ptr(), z.data_ptr(), None, st_g.data_ptr(), stream))
+    def off(t, i, itemsize=8):
+        return t.data_ptr() + i * seg * itemsize
 
-    def g2i():
-        _capi.check(_capi.lib.usgscsm_b200_ground_to_image_dev(
-            h_lib, n, x.data_ptr(), y.data_ptr(), z.data_ptr(), PREC, out_line.data_ptr(),
-            out_samp.data_ptr(), None, st_i.data_ptr(), stream))
+    def i2g():
+        for i, m in enumerate(models):
+            _capi.check(_capi.lib.usgscsm_b200_image_to_ground_grid_dev(
+                m._h, line0, 0.5, 1.0, 1.0, band, N_SAMPLES, off(h, i), 1, PREC, off(x, i),
+                off(y, i), off(z, i), None, off(st_g, i, 4), stream))
+
+    def g2i(prec=PREC):
+        for i, m in enumerate(models):
+            _capi.check(_capi.lib.usgscsm_b200_ground_to_image_dev(
+                m._h, seg, off(x, i), off(y, i), off(z, i), prec, off(out_line, i),
+                off(out_samp, i), None, off(st_i, i, 4), stream))
 
     def timed(fn, steps):
         """K launches bracketed by barrier + synchronize; per-launch CUDA events on the
@@ -305,11 +327,12 @@ def run_b200(args):
     total_ms, kern_ms = timed(g2i, args.steps)
     launches = _capi.lib.usgscsm_b200_kernel_launches() - launches0
     clocks = sampler.stop() if rank == 0 else None
-    value = world * n * args.steps / (total_ms * 1e-3) / 1e6
+    value = n_job * args.steps / (total_ms * 1e-3) / 1e6
 
     # correctness of what was just timed: the round trip must close and no flag may be set
-    err = max(float((out_line.view(lines, N_SAMPLES) - (torch.arange(lines, device=dev, dtype=torch.float64) + line0)[:, None]).abs().max()),
-              float((out_samp.view(lines, N_SAMPLES) - cols[None, :]).abs().max()))
+    band_rows = (torch.arange(band, device=dev, dtype=torch.float64) + line0)[None, :, None]
+    err = max(float((out_line.view(world, band, N_SAMPLES) - band_rows).abs().max()),
+              float((out_samp.view(world, band, N_SAMPLES) - cols[None, None, :]).abs().max()))
     ev_mask = _capi.ST_EVALS_MASK
     flags = int(((st_i & ~ev_mask) != 0).sum().item()) + int(((st_g & ~ev_mask) != 0).sum().item())
     # evaluations of the detector view per point, counted by the kernel itself (status bits 16-23)
@@ -319,7 +342,7 @@ def run_b200(args):
     for _ in range(args.warmup):
         i2g()
     i2g_total_ms, i2g_kern_ms = timed(i2g, args.steps)
-    i2g_value = world * n * args.steps / (i2g_total_ms * 1e-3) / 1e6
+    i2g_value = n_job * args.steps / (i2g_total_ms * 1e-3) / 1e6
 
     peak, peak_src = peak_hbm()
     traffic, traffic_src = ncu_traffic(n)
@@ -365,32 +388,32 @@ def run_b200(args):
     # second column: desiredPrecision 1e-8, what the reference's own CLI test
     # uses (tests/CMakeLists.txt:30) -- more secant iterations per point
     def g2i_tight():
-        _capi.check(_capi.lib.usgscsm_b200_ground_to_image_dev(
-            h_lib, n, x.data_ptr(), y.data_ptr(), z.data_ptr(), 1e-8, out_line.data_ptr(),
-            out_samp.data_ptr(), None, st_i.data_ptr(), stream))
+        g2i(1e-8)
     g2i_tight()
     tight_total_ms, tight_kern_ms = timed(g2i_tight, args.steps)
     result["ground_to_image_prec_1e-8"] = {
-        "value": world * n * args.steps / (tight_total_ms * 1e-3) / 1e6, "unit": "Mpoints/s",
+        "value": n_job * args.steps / (tight_total_ms * 1e-3) / 1e6, "unit": "Mpoints/s",
         "kernel_ms": tight_kern_ms,
         "evaluations_per_point": float(((st_i >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean().item())}
 
     # imageToGround from explicit (line, samp) arrays (not the dense-grid tables): 52 B/pt
-    ex_line = (torch.arange(lines, device=dev, dtype=torch.float64) + line0).repeat_interleave(N_SAMPLES)
-    ex_samp = cols.repeat(lines)
-    def i2g_explicit():
-        _capi.check(_capi.lib.usgscsm_b200_image_to_ground_dev(
-            h_lib, n, ex_line.data_ptr(), ex_samp.data_ptr(), h.data_ptr(), 1, PREC,
-            out_line.data_ptr(), out_samp.data_ptr(), ex_line.data_ptr(), None, st_i.data_ptr(), stream))
-    i2g_explicit()
-    ex_total_ms, ex_kern_ms = timed(i2g_explicit, max(1, args.steps // 2))
-    result["image_to_ground_explicit"] = {
-        "value": world * n * max(1, args.steps // 2) / (ex_total_ms * 1e-3) / 1e6,
-        "unit": "Mpoints/s", "kernel_ms": ex_kern_ms}
-    del ex_line, ex_samp
+    if world == 1:
+        ex_line = (torch.arange(lines, device=dev, dtype=torch.float64) + line0).repeat_interleave(N_SAMPLES)
+        ex_samp = cols.repeat(lines)
+
+        def i2g_explicit():
+            _capi.check(_capi.lib.usgscsm_b200_image_to_ground_dev(
+                h_lib, n, ex_line.data_ptr(), ex_samp.data_ptr(), h.data_ptr(), 1, PREC,
+                out_line.data_ptr(), out_samp.data_ptr(), ex_line.data_ptr(), None, st_i.data_ptr(), stream))
+        i2g_explicit()
+        ex_total_ms, ex_kern_ms = timed(i2g_explicit, max(1, args.steps // 2))
+        result["image_to_ground_explicit"] = {
+            "value": n * max(1, args.steps // 2) / (ex_total_ms * 1e-3) / 1e6,
+            "unit": "Mpoints/s", "kernel_ms": ex_kern_ms}
+        del ex_line, ex_samp
 
     if not args.no_e2e:
-        result["e2e"] = e2e(args, model, x, y, z, n, world, barrier, max_over_ranks)
+        result["e2e"] = e2e(args, models, x, y, z, seg, n_job, barrier, max_over_ranks)
     if rank == 0 and world == 1 and not args.no_cpu:
         from oracle import ref
         if ref.available():
@@ -484,20 +507,23 @@ def other_models(dev):
     return out
 
 
-def e2e(args, model, x, y, z, n, world, barrier, max_over_ranks):
+def e2e(args, models, x, y, z, seg, n_job, barrier, max_over_ranks):
     """Same metric through the host-pointer C-ABI call: pinned host arrays in, pinned host
-    arrays out, host<->device copies inside the timed region."""
+    arrays out, host<->device copies inside the timed region (one call per image band)."""
     import torch
     from usgscsm_b200 import _capi
+    n = seg * len(models)
     hx, hy, hz = (t.cpu().pin_memory() for t in (x, y, z))
     hl = torch.empty(n, dtype=torch.float64).pin_memory()
     hs = torch.empty(n, dtype=torch.float64).pin_memory()
     hst = torch.empty(n, dtype=torch.int32).pin_memory()
 
     def call():
-        _capi.check(_capi.lib.usgscsm_b200_ground_to_image(
-            model._h, n, hx.data_ptr(), hy.data_ptr(), hz.data_ptr(), PREC, hl.data_ptr(),
-            hs.data_ptr(), None, hst.data_ptr()))
+        for i, m in enumerate(models):
+            o = i * seg
+            _capi.check(_capi.lib.usgscsm_b200_ground_to_image(
+                m._h, seg, hx.data_ptr() + 8 * o, hy.data_ptr() + 8 * o, hz.data_ptr() + 8 * o, PREC,
+                hl.data_ptr() + 8 * o, hs.data_ptr() + 8 * o, None, hst.data_ptr() + 4 * o))
 
     for _ in range(max(1, min(args.warmup, 2))):
         call()
@@ -508,7 +534,7 @@ def e2e(args, model, x, y, z, n, world, barrier, max_over_ranks):
     torch.cuda.synchronize()
     dt = max_over_ranks(time.perf_counter() - t)
     barrier()
-    return {"value": world * n * args.steps / dt / 1e6, "unit": "Mpoints/s",
+    return {"value": n_job * args.steps / dt / 1e6, "unit": "Mpoints/s",
             "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 20 * n,
             "ms_per_step": 1e3 * dt / args.steps,
             "api": "usgscsm_b200_ground_to_image (host pointers, pinned)"}
