@@ -412,6 +412,10 @@ def run_b200(args):
             "unit": "Mpoints/s", "kernel_ms": ex_kern_ms}
         del ex_line, ex_samp
 
+    # the callers' fan-out around the path, line-scan model, first 64 Mi points
+    if world == 1 and not args.no_others:
+        result["callers"] = callers_side(model, x, y, z, min(n, 1 << 26), dev, band)
+
     if not args.no_e2e:
         result["e2e"] = e2e(args, models, x, y, z, seg, n_job, barrier, max_over_ranks)
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -442,6 +446,49 @@ def ncu_traffic(n):
         return per_point * n / 1e9, "profiles/ncu_g2i.json (%s)" % p.get("capture", "ncu --set full")
     except (OSError, KeyError, ValueError):
         return None, None
+
+
+def callers_side(model, x, y, z, m, dev, band):
+    """Side measurements of the batched caller-level entry points on the C2 line-scan model:
+    computeGroundPartials (4 searches per point in one kernel), computeSensorPartials (2
+    searches + difference), imageToRemoteImagingLocus, imageToProximateImagingLocus (3
+    imageToGround + 2 elevations).  Device resident, median of 3 after 1 warm-up."""
+    import torch
+    from usgscsm_b200 import _capi
+    lib, h = _capi.lib, model._h
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    f64 = lambda k: [torch.empty(m, dtype=torch.float64, device=dev) for _ in range(k)]
+    st = torch.empty(m, dtype=torch.int32, device=dev)
+    part = torch.empty(6 * m, dtype=torch.float64, device=dev)
+    o = f64(7)
+    rows = torch.arange(band, device=dev, dtype=torch.float64) + 0.5
+    line = rows.repeat_interleave(N_SAMPLES)[:m].contiguous()
+    samp = (torch.arange(N_SAMPLES, device=dev, dtype=torch.float64) + 0.5).repeat(band)[:m].contiguous()
+    p = lambda t: t.data_ptr()
+    calls = {
+        "ground_partials": lambda: lib.usgscsm_b200_ground_partials_dev(
+            h, m, p(x), p(y), p(z), p(part), p(st), stream),
+        "sensor_partials_index0": lambda: lib.usgscsm_b200_sensor_partials_dev(
+            h, 0, m, p(x), p(y), p(z), None, None, PREC, p(o[0]), p(o[1]), p(o[2]), p(st), stream),
+        "remote_imaging_locus": lambda: lib.usgscsm_b200_image_to_remote_imaging_locus_dev(
+            h, m, p(line), p(samp), PREC, *[p(t) for t in o], p(st), stream),
+        "proximate_imaging_locus": lambda: lib.usgscsm_b200_image_to_proximate_imaging_locus_dev(
+            h, m, p(line), p(samp), p(x), p(y), p(z), PREC, *[p(t) for t in o], p(st), stream),
+    }
+    out = {"points": m, "unit": "Mpoints/s"}
+    for name, fn in calls.items():
+        _capi.check(fn())
+        torch.cuda.synchronize()
+        ms = []
+        for _ in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            _capi.check(fn())
+            b.record()
+            torch.cuda.synchronize()
+            ms.append(a.elapsed_time(b))
+        out[name] = m / sorted(ms)[1] / 1e3
+    return out
 
 
 def other_models(dev):

@@ -105,6 +105,12 @@ USGSCSM_B200_API int usgscsm_b200_model_from_state(const char *state, size_t len
  * four model names above. */
 USGSCSM_B200_API int usgscsm_b200_model_name_from_state(const char *state, size_t len, char *name,
                                        size_t cap);
+/* A model state (any accepted encoding) -> its msgpack binary form, byte for byte what the
+ * reference writes with nlohmann::json::to_msgpack (bin/usgscsm_cam_test.cc
+ * --output-binary-model-state).  *needed receives the size; bytes are written when out holds
+ * at least that many (call with out = NULL to size the buffer).  Host only. */
+USGSCSM_B200_API int usgscsm_b200_state_to_msgpack(const char *state, size_t len, unsigned char *out,
+                                  size_t cap, size_t *needed);
 /* csm::Model destructor. */
 USGSCSM_B200_API void usgscsm_b200_model_free(usgscsm_b200_model *m);
 /* USGSCSM_B200_MODEL_* */
@@ -229,9 +235,10 @@ USGSCSM_B200_API int usgscsm_b200_ground_partials_dev(usgscsm_b200_model *m, int
 /* computeSensorPartials: replaces csm::RasterGM::computeSensorPartials(int index, const
  * EcefCoord&, double desiredPrecision, double* achievedPrecision, WarningList*) (LS:1336-1348)
  * and, when img_line / img_samp are given, the overload that takes the image point
- * (LS:1373-1396): the partial derivatives of line and sample with respect to adjustable
+ * (LS:1373-1396; PF:1121-1162, FR:814-873, SAR:1308-1371): the partial derivatives of line and sample with respect to adjustable
  * parameter `index`, by a forward difference of two groundToImage searches, the second with
- * the parameter moved by m_gsd.  Line-scan model only (USGSCSM_B200_EUNSUPPORTED otherwise).
+ * the parameter moved by the model's own step: m_gsd (LS:1386, PF:1153), 1.0 or 0.01 for the
+ * quaternion parameters (FR:853-859), m_scaledPixelWidth (SAR:1360).
  * computeAllSensorPartials (csm/RasterGM.cpp:52-100) is this call once per parameter index. */
 USGSCSM_B200_API int usgscsm_b200_sensor_partials(usgscsm_b200_model *m, int index, int64_t n,
                                  const double *x, const double *y, const double *z,

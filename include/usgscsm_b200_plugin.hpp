@@ -228,7 +228,7 @@ class RasterGM {
     raiseOrWarn(st, NULL, "computeGroundPartials");
     return p;
   }
-  // LS:1336-1396 (line-scan model; csm::RasterGM::SensorPartials = pair<line, sample> partial)
+  // LS:1336-1396, PF:1121-1162, FR:814-873, SAR:1308-1371 (SensorPartials = pair<line, sample>)
   std::pair<double, double> computeSensorPartials(int index, const csm::EcefCoord &groundPt,
                                                   double desiredPrecision = 0.001,
                                                   double *achievedPrecision = NULL,

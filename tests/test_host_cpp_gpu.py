@@ -101,3 +101,23 @@ def test_aos_entry_points_equal_soa(kind):
     x, y, z, _, _ = gm.imageToGroundBatch(ls[:1000, 0].copy(), ls[:1000, 1].copy(), 25.0)
     assert np.array_equal(xyz[:1000, 0], x) and np.array_equal(xyz[:1000, 2], z)
     assert _capi.lib.usgscsm_b200_ground_to_image_aos(gm._h, 0, None, 0.001, None, None, None) == 0
+
+
+def test_cam_test_binary_state_round_trip(ref, tmp_path):
+    """--output-binary-model-state writes the reference's msgpack bytes; the tool then loads
+    that file and reports the same errors as from the JSON state."""
+    from oracle import ref as oracle_ref
+    state = _states()["linescan"]
+    f = tmp_path / "state.json"
+    f.write_text(state)
+    packed = tmp_path / "state.bin"
+    args = ["--sample-rate", "32", "--desired-precision", "1e-8"]
+    r1 = subprocess.run([TOOL, "--model", str(f), "--output-binary-model-state", str(packed)] + args,
+                        capture_output=True, text=True, timeout=300)
+    assert r1.returncode == 0, r1.stdout + r1.stderr
+    assert packed.read_bytes() == oracle_ref.state_to_msgpack(state)
+    r2 = subprocess.run([TOOL, "--model", str(packed)] + args, capture_output=True, text=True, timeout=300)
+    assert r2.returncode == 0, r2.stdout + r2.stderr
+    assert "Detected msgpack binary model state" in r2.stdout
+    pick = lambda out: [l for l in out.splitlines() if l.startswith(("Min:", "Median:", "Max:", "Count:"))]
+    assert pick(r1.stdout) == pick(r2.stdout) and len(pick(r1.stdout)) == 4

@@ -182,10 +182,38 @@ def test_sensor_partials_linescan(ref, kind, index):
     assert np.array_equal(d[1].cpu().numpy(), ds, equal_nan=True)
 
 
-def test_sensor_partials_other_models_unsupported():
+@pytest.mark.parametrize("kind,index", [("pushframe", 0), ("pushframe", 5), ("pushframe", 8), ("pushframe", 15),
+                                        ("frame", 0), ("frame", 2), ("frame", 3), ("frame", 6),
+                                        ("frame_transverse", 4), ("sar", 0), ("sar", 2), ("sar", 4)])
+def test_sensor_partials_other_models(ref, kind, index):
+    """PF:1121-1162 (step m_gsd, per-framelet orientation table rebuilt for the adjusted model),
+    FR:814-873 (step 1.0 / 0.01), SAR:1308-1371 (step m_scaledPixelWidth)."""
+    from usgscsm_b200 import _capi, synth
+    gm, rm = _pair(ref, kind)
+    nl, ns = rm.image_size()
+    rng = np.random.default_rng(40 + index)
+    n = 1500 if kind == "sar" else 5000
+    line, samp = pixels(rng, n, nl, ns)
+    x, y, z, _, _ = gm.imageToGroundBatch(line, samp, synth.synthetic_dem(line, samp))
+    x[:5] = np.nan
+    for image_pts in (None, (line, samp)):
+        dl, ds, ach, st = gm.computeSensorPartialsBatch(index, x, y, z, 1e-6, imagePts=image_pts)
+        el, es, ea, est = rm.sensor_partials(index, x, y, z, 1e-6, image_pts=image_pts, threads=0)
+        assert np.array_equal(st & _capi.ST_REFERENCE_MASK, est)
+        ok = np.isfinite(el) & np.isfinite(es)
+        assert np.array_equal(np.isfinite(dl) & np.isfinite(ds), ok) and ok.sum() >= n * 0.9
+        scale = max(1.0, np.abs(el[ok]).max(), np.abs(es[ok]).max())
+        assert np.abs(dl[ok] - el[ok]).max() <= 1e-9 * scale
+        assert np.abs(ds[ok] - es[ok]).max() <= 1e-9 * scale
+        fa = np.isfinite(ea)
+        assert np.array_equal(np.isfinite(ach), fa)
+        assert np.abs(ach[fa] - ea[fa]).max(initial=0.0) <= PX_TOL
+
+
+def test_sensor_partials_bad_index():
     import usgscsm_b200 as ub
     from usgscsm_b200 import _capi, synth
     gm = ub.UsgsAstroPlugin().constructModelFromState(synth.frame_state())
     with pytest.raises(_capi.EngineError) as e:
-        gm.computeSensorPartialsBatch(0, np.zeros(3), np.zeros(3), np.zeros(3))
-    assert e.value.code == _capi.EUNSUPPORTED
+        gm.computeSensorPartialsBatch(7, np.zeros(3), np.zeros(3), np.zeros(3))
+    assert e.value.code == _capi.EINVAL

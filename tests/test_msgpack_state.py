@@ -45,6 +45,34 @@ def test_model_name_from_msgpack_state(ref, kind):
     assert _name(packed_py) == (0, expect)
 
 
+@pytest.mark.parametrize("kind", ["linescan", "pushframe", "frame", "sar"])
+def test_writer_is_byte_identical_to_the_reference(ref, kind):
+    """usgscsm_b200_state_to_msgpack against nlohmann::json::to_msgpack on the same state, and
+    a round trip through the engine's own reader."""
+    from oracle import ref as oracle_ref
+    from usgscsm_b200 import plugin
+    state = _states()[kind]
+    ours = plugin.stateToMsgpack(state)
+    assert ours == oracle_ref.state_to_msgpack(state)
+    assert plugin.stateToMsgpack(ours) == ours            # msgpack in -> same msgpack out
+    assert _name(ours) == (0, _json_part(state)["m_modelName"])
+
+
+def test_writer_number_forms():
+    import msgpack
+    from usgscsm_b200 import plugin
+    doc = {"m_modelName": "USGS_ASTRO_FRAME_SENSOR_MODEL",
+           "ints": [0, 127, 128, 255, 256, 65535, 65536, 4294967295, 4294967296, -1, -32, -33,
+                    -128, -129, -32768, -32769, -2147483648, -2147483649],
+           "floats": [0.5, 0.1, 1e300, -2.5, 3.0e38, 1e39], "mixed": [1, 2.5, "x", None, True, [1, 2]],
+           "s": "a" * 40, "long": "b" * 300, "empty": [], "obj": {"k": [1.0, 2]}}
+    ours = plugin.stateToMsgpack(json.dumps(doc))
+    assert msgpack.unpackb(ours) == doc
+    # integer-valued float literals stay floats, integers stay integers
+    back = msgpack.unpackb(ours)
+    assert isinstance(back["obj"]["k"][0], float) and isinstance(back["obj"]["k"][1], int)
+
+
 def test_malformed_msgpack_is_rejected():
     from usgscsm_b200 import _capi
     import msgpack

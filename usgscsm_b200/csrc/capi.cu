@@ -271,6 +271,20 @@ int usgscsm_b200_model_name_from_state(const char *state, size_t len, char *name
   });
 }
 
+// nlohmann::json::to_msgpack(stateAsJson(state)): bin/usgscsm_cam_test.cc
+// --output-binary-model-state.  Host only.
+int usgscsm_b200_state_to_msgpack(const char *state, size_t len, unsigned char *out, size_t cap,
+                                  size_t *needed) {
+  if (!state || !needed) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return guarded([&]() -> int {
+    std::string bytes = msgpack::dump(parseState(state, len));
+    *needed = bytes.size();
+    if (out && cap >= bytes.size()) std::memcpy(out, bytes.data(), bytes.size());
+    else if (out) return fail(USGSCSM_B200_EINVAL, "output buffer too small");
+    return USGSCSM_B200_OK;
+  });
+}
+
 void usgscsm_b200_model_free(usgscsm_b200_model *m) { delete m; }
 
 int usgscsm_b200_model_kind(const usgscsm_b200_model *m) { return m ? m->kind : 0; }
@@ -796,11 +810,17 @@ static int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const dou
                              const double *y, const double *z, const double *img_line,
                              const double *img_samp, double prec, double *dline, double *dsamp,
                              double *achieved, uint32_t *status, cudaStream_t stream) {
-  const double delta = m->ls.gsd;
-  const LsState adj = adjustedLineScanner(*m, index, delta);
+  // DELTA of the scalar call: m_gsd (LS:1386, PF:1153), 1.0 or 0.01 for the quaternion
+  // parameters (FR:853-859), m_scaledPixelWidth (SAR:1360)
+  double delta;
+  switch (m->kind) {
+    case USGSCSM_B200_MODEL_FRAME: delta = (index > 2 && index < 7) ? 0.01 : 1.0; break;
+    case USGSCSM_B200_MODEL_SAR: delta = m->sar.scaledPixelWidth; break;
+    default: delta = m->ls.gsd; break;
+  }
   const bool haveImage = img_line && img_samp;
   // scratch: l0, s0 (unless supplied), l1, s1, st0, st1 (unless the caller wants status)
-  double *scratch = nullptr;
+  double *scratch = nullptr, *pfTable = nullptr;
   uint32_t *stScratch = nullptr;
   UB_CUDA(cudaMallocAsync(&scratch, (size_t)n * 4 * sizeof(double), stream));
   UB_CUDA(cudaMallocAsync(&stScratch, (size_t)n * 2 * sizeof(uint32_t), stream));
@@ -808,15 +828,40 @@ static int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const dou
   uint32_t *st0 = stScratch, *st1 = status ? status : stScratch + n;
   cudaError_t e = cudaSuccess;
   if (!haveImage)
-    e = launchLsGroundToImage(m->ls, m->smCount, n, x, y, z, prec, l0, s0, nullptr, st0, stream);
-  if (e == cudaSuccess)
-    e = launchLsGroundToImage(adj, m->smCount, n, x, y, z, prec, l1, s1, achieved, st1, stream);
+    e = launchGroundToImage(*m, n, x, y, z, prec, l0, s0, nullptr, st0, stream);
+  if (e == cudaSuccess) {
+    switch (m->kind) {
+      case USGSCSM_B200_MODEL_LINE_SCANNER:
+        e = launchLsGroundToImage(adjustedLineScanner(*m, index, delta), m->smCount, n, x, y, z,
+                                  prec, l1, s1, achieved, st1, stream);
+        break;
+      case USGSCSM_B200_MODEL_PUSH_FRAME: {
+        LsState adj = adjustedPushFrame(*m, index, delta);
+        if (m->ls.frameletOrient) {  // per-framelet orientations of the adjusted model
+          e = cudaMallocAsync(&pfTable, (size_t)(adj.numFramelets + 2) * kFrameletOrientDoubles * sizeof(double), stream);
+          if (e == cudaSuccess) e = launchPfFrameletOrientations(adj, pfTable, stream);
+          adj.frameletOrient = pfTable;
+        }
+        if (e == cudaSuccess)
+          e = launchPfGroundToImage(adj, m->smCount, n, x, y, z, prec, l1, s1, achieved, st1, stream);
+      } break;
+      case USGSCSM_B200_MODEL_FRAME:
+        e = launchFrGroundToImage(adjustedFrame(*m, index, delta), m->smCount, n, x, y, z, prec, l1,
+                                  s1, achieved, st1, stream);
+        break;
+      default:
+        e = launchSarGroundToImage(adjustedSar(*m, index, delta), m->smCount, n, x, y, z, prec, l1,
+                                   s1, achieved, st1, stream);
+        break;
+    }
+  }
   if (e == cudaSuccess)
     e = launchSensorPartialsCombine(n, haveImage ? img_line : l0, haveImage ? img_samp : s0,
                                     haveImage ? nullptr : st0, l1, s1, delta, dline, dsamp,
                                     achieved, st1, stream);
   cudaFreeAsync(scratch, stream);
   cudaFreeAsync(stScratch, stream);
+  if (pfTable) cudaFreeAsync(pfTable, stream);
   UB_CUDA(e);
   return USGSCSM_B200_OK;
 }
@@ -825,9 +870,8 @@ static int sensorPartialsCheck(usgscsm_b200_model *m, int index, int64_t n, cons
                                const void *y, const void *z, const void *dline,
                                const void *dsamp) {
   if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (m->kind != USGSCSM_B200_MODEL_LINE_SCANNER)
-    return fail(USGSCSM_B200_EUNSUPPORTED, "sensor partials are built for the line-scan model only");
-  if (index < 0 || index >= 16) return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
+  if (index < 0 || index >= (int)m->params.size())
+    return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
   if (n > 0 && (!x || !y || !z || !dline || !dsamp)) return fail(USGSCSM_B200_EINVAL, "null array");
   return USGSCSM_B200_OK;
 }

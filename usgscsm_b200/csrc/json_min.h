@@ -31,6 +31,7 @@ struct Value {
   bool numericArray = false;
   bool firstIsInt = false;
   std::vector<double> nums;
+  std::vector<unsigned char> numIsInt;  // per element of nums: the literal was an integer
   std::vector<Value> items;
   std::map<std::string, Value> members;
 
@@ -214,16 +215,18 @@ class Parser {
       if (v.numericArray && e.isNumber()) {
         if (v.nums.empty()) v.firstIsInt = (e.type == Type::Int);
         v.nums.push_back(e.num);
+        v.numIsInt.push_back(e.type == Type::Int);
       } else {
         if (v.numericArray) {  // demote: re-box what we have
           v.numericArray = false;
-          for (double d : v.nums) {
+          for (size_t k = 0; k < v.nums.size(); k++) {
             Value n;
-            n.type = Type::Float;
-            n.num = d;
+            n.type = v.numIsInt[k] ? Type::Int : Type::Float;
+            n.num = v.nums[k];
             v.items.push_back(n);
           }
           v.nums.clear();
+          v.numIsInt.clear();
         }
         v.items.push_back(std::move(e));
       }

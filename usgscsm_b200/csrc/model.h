@@ -99,7 +99,8 @@ void repackLineScanner(Model &m);  // after a parameter / projective-seed change
 LsState adjustedLineScanner(const Model &m, int index, double delta);
 // model_pf.cu
 void loadPushFrame(Model &m, const class StateReader &st);
-void repackPushFrame(Model &m);  // after a parameter change: params + framelet orientations
+void repackPushFrame(Model &m);
+LsState adjustedPushFrame(const Model &m, int index, double delta);  // after a parameter change: params + framelet orientations
 // divisors.cu: reciprocals of constant divisors, evaluated on the device
 void fillDivisors(const std::vector<Divisor *> &divisors);
 void appendLagrangeDivisors(LagrangeDivisors &L, std::vector<Divisor *> &out);
@@ -107,9 +108,11 @@ void fillTableSteps(const std::vector<UniformTable *> &tables);
 // model_fr.cu
 void loadFrame(Model &m, const class StateReader &st);
 void repackFrame(Model &m);
+FrameState adjustedFrame(const Model &m, int index, double delta);
 // model_sar.cu
 void loadSar(Model &m, const class StateReader &st);
 void repackSar(Model &m);
+SarState adjustedSar(const Model &m, int index, double delta);
 // shared readers (model_ls.cu)
 void readFocalPlane(FocalPlane &fp, const class StateReader &st, bool lineScanTypes);
 void readEllipsoid(Ellipsoid &e, const class StateReader &st);

@@ -51,6 +51,25 @@ void repackFrame(Model &m) {
   }
 }
 
+// groundToImage(groundPt, adj, ...) with adj[index] = delta (FR:844-873): getValue(i, adj) and
+// the un-normalised matrix of the adjusted quaternion (calcRotationMatrix(m, adj) FR:2267-2286).
+FrameState adjustedFrame(const Model &m, int index, double delta) {
+  FrameState S = m.fr;
+  for (int i = 0; i < 7; i++) S.params[i] = m.params[i] + (i == index ? delta : 0.0);
+  double x = S.params[3], y = S.params[4], z = S.params[5], w = S.params[6];
+  double *r = S.mRaw;
+  r[0] = w * w + x * x - y * y - z * z;
+  r[1] = 2 * (x * y - w * z);
+  r[2] = 2 * (w * y + x * z);
+  r[3] = 2 * (x * y + w * z);
+  r[4] = w * w - x * x + y * y - z * z;
+  r[5] = 2 * (y * z - w * x);
+  r[6] = 2 * (x * z - w * y);
+  r[7] = 2 * (w * x + y * z);
+  r[8] = w * w - x * x - y * y + z * z;
+  return S;
+}
+
 void loadFrame(Model &m, const StateReader &st) {
   FrameState &S = m.fr;
   S = FrameState{};

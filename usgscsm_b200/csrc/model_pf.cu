@@ -91,6 +91,23 @@ void repackPushFrame(Model &m) {
   buildFrameletOrientations(m);
 }
 
+// The packed state groundToImage(ground_pt, adj, ...) sees with adj[index] = delta
+// (PF:1141-1162).  The per-framelet orientation table depends on the parameters: the copy
+// returned here has none (frameletOrient = nullptr, the kernels then evaluate in-thread);
+// the caller may build one for it with launchPfFrameletOrientations.
+LsState adjustedPushFrame(const Model &m, int index, double delta) {
+  LsState S = m.ls;
+  S.hasAdj = 0;
+  S.hasAttAdj = 0;
+  for (int i = 0; i < 16; i++) {
+    S.params[i] = m.params[i] + (i == index ? delta : 0.0);
+    if (S.params[i] != 0) S.hasAdj = 1;
+    if (i >= 6 && i <= 14 && S.params[i] != 0) S.hasAttAdj = 1;
+  }
+  S.frameletOrient = nullptr;
+  return S;
+}
+
 void loadPushFrame(Model &m, const StateReader &st) {
   LsState &S = m.ls;
   S = LsState{};

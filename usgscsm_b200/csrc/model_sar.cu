@@ -13,6 +13,13 @@ void repackSar(Model &m) {
   for (int i = 0; i < 6; i++) m.sar.params[i] = m.params[i] + 0.0;  // getValue(i, m_noAdjustments)
 }
 
+// groundToImage(groundPt, adj, ...) with adj[index] = delta (SAR:1347-1371).
+SarState adjustedSar(const Model &m, int index, double delta) {
+  SarState S = m.sar;
+  for (int i = 0; i < 6; i++) S.params[i] = m.params[i] + (i == index ? delta : 0.0);
+  return S;
+}
+
 void loadSar(Model &m, const StateReader &st) {
   SarState &S = m.sar;
   S = SarState{};

@@ -79,11 +79,14 @@ class Reader {
       if (v.numericArray && e.isNumber()) {
         if (v.nums.empty()) v.firstIsInt = (e.type == json::Type::Int);
         v.nums.push_back(e.num);
+        v.numIsInt.push_back(e.type == json::Type::Int);
       } else {
         if (v.numericArray) {  // demote, as json_min.h does
           v.numericArray = false;
-          for (double d : v.nums) v.items.push_back(real(d));
+          for (size_t k = 0; k < v.nums.size(); k++)
+            v.items.push_back(v.numIsInt[k] ? integer(v.nums[k]) : real(v.nums[k]));
           v.nums.clear();
+          v.numIsInt.clear();
         }
         v.items.push_back(std::move(e));
       }
@@ -152,6 +155,100 @@ class Reader {
 };
 
 inline json::Value parse(const char *data, size_t len) { return Reader(data, data + len).readDocument(); }
+
+// Writer: every value in the smallest msgpack form that holds it (the rule nlohmann::json's
+// to_msgpack follows, so the bytes are the ones the reference writes): integers by range,
+// a double as float32 when that is exact, strings / arrays / maps by length; map keys in
+// sorted order (nlohmann's default object type is a std::map too).
+class Writer {
+ public:
+  std::string out;
+
+  void write(const json::Value &v) {
+    switch (v.type) {
+      case json::Type::Null: put(0xC0); break;
+      case json::Type::Bool: put(v.b ? 0xC3 : 0xC2); break;
+      case json::Type::Int: integer(v.num); break;
+      case json::Type::Float: real(v.num); break;
+      case json::Type::String: str(v.str); break;
+      case json::Type::Array: {
+        const size_t n = v.arraySize();
+        if (n <= 15) put(0x90 | (unsigned)n);
+        else if (n <= 0xFFFF) { put(0xDC); be(n, 2); }
+        else { put(0xDD); be(n, 4); }
+        if (v.numericArray) {
+          for (size_t k = 0; k < n; k++) {
+            if (v.numIsInt[k]) integer(v.nums[k]);
+            else real(v.nums[k]);
+          }
+        } else {
+          for (const json::Value &e : v.items) write(e);
+        }
+      } break;
+      case json::Type::Object: {
+        const size_t n = v.members.size();
+        if (n <= 15) put(0x80 | (unsigned)n);
+        else if (n <= 0xFFFF) { put(0xDE); be(n, 2); }
+        else { put(0xDF); be(n, 4); }
+        for (const auto &kv : v.members) {
+          str(kv.first);
+          write(kv.second);
+        }
+      } break;
+    }
+  }
+
+ private:
+  void put(unsigned b) { out += (char)(unsigned char)b; }
+  void be(uint64_t v, int bytes) {
+    for (int i = bytes - 1; i >= 0; i--) put((unsigned)((v >> (8 * i)) & 0xFF));
+  }
+  void integer(double d) {
+    if (d >= 0) {
+      uint64_t u = (uint64_t)d;
+      if (u < 128) put((unsigned)u);
+      else if (u <= 0xFF) { put(0xCC); be(u, 1); }
+      else if (u <= 0xFFFF) { put(0xCD); be(u, 2); }
+      else if (u <= 0xFFFFFFFFull) { put(0xCE); be(u, 4); }
+      else { put(0xCF); be(u, 8); }
+    } else {
+      int64_t i = (int64_t)d;
+      if (i >= -32) put((unsigned)(uint8_t)(int8_t)i);
+      else if (i >= -128) { put(0xD0); be((uint64_t)(uint8_t)(int8_t)i, 1); }
+      else if (i >= -32768) { put(0xD1); be((uint64_t)(uint16_t)(int16_t)i, 2); }
+      else if (i >= -2147483648LL) { put(0xD2); be((uint64_t)(uint32_t)(int32_t)i, 4); }
+      else { put(0xD3); be((uint64_t)i, 8); }
+    }
+  }
+  void real(double d) {
+    if (d >= -3.4028234663852886e38 && d <= 3.4028234663852886e38 && (double)(float)d == d) {
+      float f = (float)d;
+      uint32_t u;
+      std::memcpy(&u, &f, 4);
+      put(0xCA);
+      be(u, 4);
+    } else {
+      uint64_t u;
+      std::memcpy(&u, &d, 8);
+      put(0xCB);
+      be(u, 8);
+    }
+  }
+  void str(const std::string &s) {
+    const size_t n = s.size();
+    if (n <= 31) put(0xA0 | (unsigned)n);
+    else if (n <= 0xFF) { put(0xD9); be(n, 1); }
+    else if (n <= 0xFFFF) { put(0xDA); be(n, 2); }
+    else { put(0xDB); be(n, 4); }
+    out += s;
+  }
+};
+
+inline std::string dump(const json::Value &v) {
+  Writer w;
+  w.write(v);
+  return w.out;
+}
 
 }  // namespace msgpack
 }  // namespace ub200

@@ -27,7 +27,7 @@
 namespace ub = usgscsm_b200;
 
 struct Options {
-  std::string model, output_model_state, points_file;
+  std::string model, output_model_state, output_binary_state, points_file;
   int sample_rate, device;
   double subpixel_offset, height_above_datum, desired_precision;
   Options()
@@ -80,6 +80,7 @@ static bool parseOptions(int argc, char **argv, Options &opt) {
   }
   if (parsed["desired-precision"].empty()) parsed["desired-precision"] = "0.001";
   opt.output_model_state = parsed["output-model-state"];
+  opt.output_binary_state = parsed["output-binary-model-state"];
   opt.points_file = parsed["points-file"];
   opt.sample_rate = (int)rate;
   opt.device = atoi(parsed["device"].c_str());
@@ -124,6 +125,9 @@ int main(int argc, char **argv) {
   std::unique_ptr<ub::RasterGM> model;
   try {
     std::string name = plugin.getModelNameFromModelState(model_state);
+    const unsigned char b0 = model_state.empty() ? 0 : (unsigned char)model_state[0];
+    if ((b0 >= 0x80 && b0 <= 0x8F) || b0 == 0xDE || b0 == 0xDF)  // isMsgpack, U:2511-2530
+      std::cout << "Detected msgpack binary model state: " << opt.model << "\n";
     std::cout << "Detected model state with model: " << name << "\n";
     model.reset(plugin.constructModelFromState(model_state));
     std::cout << "Loaded a CSM model of type " << name << " from model state file " << opt.model
@@ -139,6 +143,21 @@ int main(int argc, char **argv) {
     std::cout << "Writing model state: " << opt.output_model_state << std::endl;
     std::ofstream ofs(opt.output_model_state.c_str());
     ofs << model->getModelState() << "\n";
+  }
+
+  if (!opt.output_binary_state.empty()) {  // bin/usgscsm_cam_test.cc --output-binary-model-state
+    std::string state = model->getModelState();
+    size_t need = 0;
+    if (usgscsm_b200_state_to_msgpack(state.data(), state.size(), NULL, 0, &need) != 0) {
+      std::cerr << usgscsm_b200_last_error() << "\n";
+      return 1;
+    }
+    std::vector<unsigned char> bytes(need);
+    usgscsm_b200_state_to_msgpack(state.data(), state.size(), bytes.data(), need, &need);
+    std::cout << "Writing binary model state: " << opt.output_binary_state << " (" << need
+              << " bytes)" << std::endl;
+    std::ofstream ofs(opt.output_binary_state.c_str(), std::ios::binary);
+    ofs.write(reinterpret_cast<const char *>(bytes.data()), (std::streamsize)need);
   }
 
   if (opt.sample_rate > 0) {

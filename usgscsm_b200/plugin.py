@@ -292,7 +292,7 @@ class RasterGM(object):
         return p, st
 
     def computeSensorPartialsBatch(self, index, x, y, z, desiredPrecision=0.001, imagePts=None):
-        """csm::RasterGM::computeSensorPartials for arrays (line-scan model): returns
+        """csm::RasterGM::computeSensorPartials for arrays: returns
         (dLine/dParam, dSamp/dParam, achieved, status).  `imagePts` = (line, samp) arrays selects
         the overload that takes the image point."""
         il, isamp = (None, None) if imagePts is None else imagePts
@@ -431,6 +431,17 @@ class UsgsAstroPlugin(object):
                         "UsgsAstroPlugin::constructModelFromState")
         check(code)
         return RasterGM(h, modelState)
+
+
+def stateToMsgpack(modelState):
+    """The msgpack binary form of a model state, as the reference writes it
+    (nlohmann::json::to_msgpack; bin/usgscsm_cam_test.cc --output-binary-model-state)."""
+    raw = modelState if isinstance(modelState, bytes) else modelState.encode("utf-8")
+    need = C.c_size_t()
+    check(lib.usgscsm_b200_state_to_msgpack(raw, len(raw), None, 0, C.byref(need)))
+    buf = C.create_string_buffer(need.value)
+    check(lib.usgscsm_b200_state_to_msgpack(raw, len(raw), buf, need.value, C.byref(need)))
+    return buf.raw
 
 
 # ---- building blocks (include/usgscsm/Distortion.h, Utilities.h of the reference) ------------
