@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../include/usgscsm_b200.h"
+#include "capi_common.h"
 #include "model.h"
 #include "state_reader.h"
 #include "work_queue.cuh"
@@ -51,11 +52,7 @@ Model::~Model() {
   cudaSetDevice(device);
   for (DeviceBuffer &b : owned) cudaFree(b.ptr);
   for (PipelineSlot &s : slots) {
-    for (double *p : s.in) cudaFree(p);
-    for (double *p : s.out) cudaFree(p);
-    cudaFree(s.status);
-    cudaFree(s.aos);
-    cudaFree(s.gen);
+    cudaFree(s.scratch);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
   }
@@ -70,73 +67,22 @@ const double *Model::upload(const std::vector<double> &v) {
   return static_cast<const double *>(b.ptr);
 }
 
-void Model::ensureSlot(int s, long points) {
+void Model::ensureScratch(int s, long doubles) {
   PipelineSlot &p = slots[s];
   if (!p.stream) UB_CUDA(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
   if (!p.done) UB_CUDA(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
-  if (p.capacity >= points) return;
-  for (double *&q : p.in) {
-    cudaFree(q);
-    q = nullptr;
-    UB_CUDA(cudaMalloc(&q, points * sizeof(double)));
-  }
-  for (double *&q : p.out) {
-    cudaFree(q);
-    q = nullptr;
-    UB_CUDA(cudaMalloc(&q, points * sizeof(double)));
-  }
-  cudaFree(p.status);
-  p.status = nullptr;
-  UB_CUDA(cudaMalloc(&p.status, points * sizeof(uint32_t)));
-  p.capacity = points;
+  if (p.scratchDoubles >= doubles) return;
+  cudaFree(p.scratch);
+  p.scratch = nullptr;
+  p.scratchDoubles = 0;
+  UB_CUDA(cudaMalloc(&p.scratch, doubles * sizeof(double)));
+  p.scratchDoubles = doubles;
 }
 
-void Model::ensureAos(int s, long points) {
-  PipelineSlot &p = slots[s];
-  if (p.aosCapacity >= points) return;
-  cudaFree(p.aos);
-  p.aos = nullptr;
-  UB_CUDA(cudaMalloc(&p.aos, points * 3 * sizeof(double)));
-  p.aosCapacity = points;
-}
+// ---- error plumbing (capi_common.h) --------------------------------------------------------
+std::string &lastError() { return g_lastError; }
 
-void Model::ensureGen(int s, long doubles) {
-  PipelineSlot &p = slots[s];
-  if (!p.stream) UB_CUDA(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
-  if (!p.done) UB_CUDA(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
-  if (p.genDoubles >= doubles) return;
-  cudaFree(p.gen);
-  p.gen = nullptr;
-  UB_CUDA(cudaMalloc(&p.gen, doubles * sizeof(double)));
-  p.genDoubles = doubles;
-}
-
-// ---- error plumbing ---------------------------------------------------------------------
-template <class F>
-static int guarded(F &&f) {
-  try {
-    return f();
-  } catch (const CudaError &e) {
-    g_lastError = e.what();
-    return USGSCSM_B200_ECUDA;
-  } catch (const StateError &e) {
-    g_lastError = e.what();
-    return USGSCSM_B200_ESTATE;
-  } catch (const std::invalid_argument &e) {
-    g_lastError = e.what();
-    return USGSCSM_B200_EINVAL;
-  } catch (const std::exception &e) {
-    g_lastError = e.what();
-    return USGSCSM_B200_ESTATE;
-  }
-}
-
-static int fail(int code, const char *msg) {
-  g_lastError = msg;
-  return code;
-}
-
-static int deviceCount() {
+int deviceCount() {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) {
     cudaGetLastError();
@@ -146,7 +92,7 @@ static int deviceCount() {
 }
 
 // Dispatch of the two per-point operations on the model kind (device pointers).
-static cudaError_t launchGroundToImage(Model &m, long n, const double *x, const double *y,
+cudaError_t launchGroundToImage(Model &m, long n, const double *x, const double *y,
                                        const double *z, double prec, double *line, double *samp,
                                        double *achieved, uint32_t *status, cudaStream_t stream) {
   switch (m.kind) {
@@ -167,7 +113,7 @@ static cudaError_t launchGroundToImage(Model &m, long n, const double *x, const 
   }
 }
 
-static cudaError_t launchImageToGround(Model &m, long n, const double *line, const double *samp,
+cudaError_t launchImageToGround(Model &m, long n, const double *line, const double *samp,
                                        const GridSpec *grid, const double *height,
                                        int heightStride, double prec, double *x, double *y,
                                        double *z, double *achieved, uint32_t *status,
@@ -414,183 +360,12 @@ int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, d
   });
 }
 
-// ---- host-pointer flavours ------------------------------------------------------------------
-// Chunked three-slot pipeline: while chunk c runs its kernel, chunk c+1 is copied in and
-// chunk c-1 is copied out, each slot on its own stream.  Copies are truly asynchronous when
-// the caller's arrays are page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory);
-// with pageable arrays the runtime stages them and the calls still complete correctly.
-int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double *x,
-                                 const double *y, const double *z, double prec, double *line,
-                                 double *samp, double *achieved, uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!x || !y || !z || !line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int kPipelineSlots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % kPipelineSlots);
-      m->ensureSlot(si, chunk);
-      PipelineSlot &s = m->slots[si];
-      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      UB_CUDA(cudaMemcpyAsync(s.in[0], x + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(s.in[1], y + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(s.in[2], z + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(launchGroundToImage(*m, cnt, s.in[0], s.in[1], s.in[2], prec, s.out[0], s.out[1],
-                                  achieved ? s.out[2] : nullptr, status ? s.status : nullptr,
-                                  s.stream));
-      UB_CUDA(cudaMemcpyAsync(line + off, s.out[0], b, cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaMemcpyAsync(samp + off, s.out[1], b, cudaMemcpyDeviceToHost, s.stream));
-      if (achieved)
-        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < kPipelineSlots && si < c; si++)
-      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
-
-int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double *line,
-                                 const double *samp, const double *height, int height_stride,
-                                 double prec, double *x, double *y, double *z, double *achieved,
-                                 uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!line || !samp || !height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int kPipelineSlots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % kPipelineSlots);
-      m->ensureSlot(si, chunk);
-      PipelineSlot &s = m->slots[si];
-      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      UB_CUDA(cudaMemcpyAsync(s.in[0], line + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(s.in[1], samp + off, b, cudaMemcpyHostToDevice, s.stream));
-      if (height_stride)
-        UB_CUDA(cudaMemcpyAsync(s.in[2], height + off, b, cudaMemcpyHostToDevice, s.stream));
-      else
-        UB_CUDA(cudaMemcpyAsync(s.in[2], height, sizeof(double), cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(launchImageToGround(*m, cnt, s.in[0], s.in[1], nullptr, s.in[2],
-                                  height_stride ? 1 : 0, prec, s.out[0], s.out[1], s.out[2],
-                                  achieved ? s.out[3] : nullptr, status ? s.status : nullptr,
-                                  s.stream));
-      UB_CUDA(cudaMemcpyAsync(x + off, s.out[0], b, cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaMemcpyAsync(y + off, s.out[1], b, cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaMemcpyAsync(z + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
-      if (achieved)
-        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[3], b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < kPipelineSlots && si < c; si++)
-      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
-
-// ---- AoS flavours (arrays of csm::EcefCoord / csm::ImageCoord, csm/csm.h:212-308) -----------
-// Same three-slot pipeline; a chunk is copied as it lies, split into SoA on the device, run
-// through the same kernels, joined and copied back.
-int usgscsm_b200_ground_to_image_aos(usgscsm_b200_model *m, int64_t n, const double *xyz,
-                                     double prec, double *line_samp, double *achieved,
-                                     uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!xyz || !line_samp) return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int kPipelineSlots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % kPipelineSlots);
-      m->ensureSlot(si, chunk);
-      m->ensureAos(si, chunk);
-      PipelineSlot &s = m->slots[si];
-      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      UB_CUDA(cudaMemcpyAsync(s.aos, xyz + 3 * off, 3 * b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(launchAosSplit(3, cnt, s.aos, s.in[0], s.in[1], s.in[2], s.stream));
-      UB_CUDA(launchGroundToImage(*m, cnt, s.in[0], s.in[1], s.in[2], prec, s.out[0], s.out[1],
-                                  achieved ? s.out[2] : nullptr, status ? s.status : nullptr,
-                                  s.stream));
-      UB_CUDA(launchAosJoin(2, cnt, s.out[0], s.out[1], nullptr, s.aos, s.stream));
-      UB_CUDA(cudaMemcpyAsync(line_samp + 2 * off, s.aos, 2 * b, cudaMemcpyDeviceToHost, s.stream));
-      if (achieved)
-        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[2], b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < kPipelineSlots && si < c; si++)
-      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
-
-int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n, const double *line_samp,
-                                     const double *height, int height_stride, double prec,
-                                     double *xyz, double *achieved, uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!line_samp || !height || !xyz) return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int kPipelineSlots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % kPipelineSlots);
-      m->ensureSlot(si, chunk);
-      m->ensureAos(si, chunk);
-      PipelineSlot &s = m->slots[si];
-      if (c >= kPipelineSlots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      UB_CUDA(cudaMemcpyAsync(s.aos, line_samp + 2 * off, 2 * b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(launchAosSplit(2, cnt, s.aos, s.in[0], s.in[1], nullptr, s.stream));
-      if (height_stride)
-        UB_CUDA(cudaMemcpyAsync(s.in[2], height + off, b, cudaMemcpyHostToDevice, s.stream));
-      else
-        UB_CUDA(cudaMemcpyAsync(s.in[2], height, sizeof(double), cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(launchImageToGround(*m, cnt, s.in[0], s.in[1], nullptr, s.in[2],
-                                  height_stride ? 1 : 0, prec, s.out[0], s.out[1], s.out[2],
-                                  achieved ? s.out[3] : nullptr, status ? s.status : nullptr,
-                                  s.stream));
-      UB_CUDA(launchAosJoin(3, cnt, s.out[0], s.out[1], s.out[2], s.aos, s.stream));
-      UB_CUDA(cudaMemcpyAsync(xyz + 3 * off, s.aos, 3 * b, cudaMemcpyDeviceToHost, s.stream));
-      if (achieved)
-        UB_CUDA(cudaMemcpyAsync(achieved + off, s.out[3], b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, s.status, cnt * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < kPipelineSlots && si < c; si++)
-      UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
+}  // extern "C"
 
 // ---- imageToRemoteImagingLocus / computeGroundPartials ---------------------------------------
-static cudaError_t launchRemoteLocus(Model &m, long n, const double *line, const double *samp,
+namespace ub200 {
+
+cudaError_t launchRemoteLocus(Model &m, long n, const double *line, const double *samp,
                                      double prec, const LocusOut &o, cudaStream_t stream) {
   switch (m.kind) {
     case USGSCSM_B200_MODEL_LINE_SCANNER:
@@ -606,7 +381,7 @@ static cudaError_t launchRemoteLocus(Model &m, long n, const double *line, const
   }
 }
 
-static cudaError_t launchProximateLocus(Model &m, long n, const double *line, const double *samp,
+cudaError_t launchProximateLocus(Model &m, long n, const double *line, const double *samp,
                                         const double *x, const double *y, const double *z,
                                         double prec, const LocusOut &o, cudaStream_t stream) {
   switch (m.kind) {
@@ -623,7 +398,7 @@ static cudaError_t launchProximateLocus(Model &m, long n, const double *line, co
   }
 }
 
-static cudaError_t launchGroundPartials(Model &m, long n, const double *x, const double *y,
+cudaError_t launchGroundPartials(Model &m, long n, const double *x, const double *y,
                                         const double *z, double *partials, uint32_t *status,
                                         cudaStream_t stream) {
   switch (m.kind) {
@@ -639,6 +414,10 @@ static cudaError_t launchGroundPartials(Model &m, long n, const double *x, const
       return cudaErrorNotSupported;
   }
 }
+
+}  // namespace ub200
+
+extern "C" {
 
 int usgscsm_b200_image_to_remote_imaging_locus_dev(usgscsm_b200_model *m, int64_t n,
                                                    const double *line, const double *samp,
@@ -671,46 +450,6 @@ int usgscsm_b200_ground_partials_dev(usgscsm_b200_model *m, int64_t n, const dou
   });
 }
 
-int usgscsm_b200_image_to_remote_imaging_locus(usgscsm_b200_model *m, int64_t n, const double *line,
-                                               const double *samp, double prec, double *px,
-                                               double *py, double *pz, double *dx, double *dy,
-                                               double *dz, double *achieved, uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!line || !samp || !px || !py || !pz || !dx || !dy || !dz)
-    return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int nslots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    double *host[7] = {px, py, pz, dx, dy, dz, achieved};
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % nslots);
-      m->ensureGen(si, chunk * 10);  // 2 in + 7 out + status
-      PipelineSlot &s = m->slots[si];
-      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      double *dl = s.gen, *ds = s.gen + chunk, *dout = s.gen + 2 * chunk;
-      uint32_t *dst = reinterpret_cast<uint32_t *>(s.gen + 9 * chunk);
-      UB_CUDA(cudaMemcpyAsync(dl, line + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(ds, samp + off, b, cudaMemcpyHostToDevice, s.stream));
-      LocusOut o{dout, dout + chunk, dout + 2 * chunk, dout + 3 * chunk, dout + 4 * chunk,
-                 dout + 5 * chunk, achieved ? dout + 6 * chunk : nullptr, status ? dst : nullptr};
-      UB_CUDA(launchRemoteLocus(*m, cnt, dl, ds, prec, o, s.stream));
-      for (int k = 0; k < 7; k++)
-        if (host[k])
-          UB_CUDA(cudaMemcpyAsync(host[k] + off, dout + k * chunk, b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
-
 int usgscsm_b200_image_to_proximate_imaging_locus_dev(
     usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
     const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
@@ -728,85 +467,14 @@ int usgscsm_b200_image_to_proximate_imaging_locus_dev(
   });
 }
 
-int usgscsm_b200_image_to_proximate_imaging_locus(
-    usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
-    const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
-    double *dy, double *dz, double *achieved, uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!line || !samp || !x || !y || !z || !px || !py || !pz || !dx || !dy || !dz)
-    return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int nslots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    const double *in[5] = {line, samp, x, y, z};
-    double *host[7] = {px, py, pz, dx, dy, dz, achieved};
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % nslots);
-      m->ensureGen(si, chunk * 13);  // 5 in + 7 out + status
-      PipelineSlot &s = m->slots[si];
-      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      double *din = s.gen, *dout = s.gen + 5 * chunk;
-      uint32_t *dst = reinterpret_cast<uint32_t *>(s.gen + 12 * chunk);
-      for (int k = 0; k < 5; k++)
-        UB_CUDA(cudaMemcpyAsync(din + k * chunk, in[k] + off, b, cudaMemcpyHostToDevice, s.stream));
-      LocusOut o{dout, dout + chunk, dout + 2 * chunk, dout + 3 * chunk, dout + 4 * chunk,
-                 dout + 5 * chunk, achieved ? dout + 6 * chunk : nullptr, status ? dst : nullptr};
-      UB_CUDA(launchProximateLocus(*m, cnt, din, din + chunk, din + 2 * chunk, din + 3 * chunk,
-                                   din + 4 * chunk, prec, o, s.stream));
-      for (int k = 0; k < 7; k++)
-        if (host[k])
-          UB_CUDA(cudaMemcpyAsync(host[k] + off, dout + k * chunk, b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
+}  // extern "C"
 
-int usgscsm_b200_ground_partials(usgscsm_b200_model *m, int64_t n, const double *x, const double *y,
-                                 const double *z, double *partials, uint32_t *status) {
-  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  if (n == 0) return USGSCSM_B200_OK;
-  if (!x || !y || !z || !partials) return fail(USGSCSM_B200_EINVAL, "null array");
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const int nslots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % nslots);
-      m->ensureGen(si, chunk * 10);  // 3 in + 6 out + status
-      PipelineSlot &s = m->slots[si];
-      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));
-      const size_t b = cnt * sizeof(double);
-      double *dx = s.gen, *dy = s.gen + chunk, *dz = s.gen + 2 * chunk, *dp = s.gen + 3 * chunk;
-      uint32_t *dst = reinterpret_cast<uint32_t *>(s.gen + 9 * chunk);
-      UB_CUDA(cudaMemcpyAsync(dx, x + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(dy, y + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(dz, z + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(launchGroundPartials(*m, cnt, dx, dy, dz, dp, status ? dst : nullptr, s.stream));
-      UB_CUDA(cudaMemcpyAsync(partials + 6 * off, dp, 6 * b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
+namespace ub200 {
 
 // computeSensorPartials(index, ground_pt, prec, ach, warn) LS:1336-1396 over n points: the
 // search with the model as it is (skipped when the caller supplies the image points, the
 // 6-argument overload), the search with parameter `index` moved by m_gsd, forward difference.
-static int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
+int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
                              const double *y, const double *z, const double *img_line,
                              const double *img_samp, double prec, double *dline, double *dsamp,
                              double *achieved, uint32_t *status, cudaStream_t stream) {
@@ -866,7 +534,7 @@ static int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const dou
   return USGSCSM_B200_OK;
 }
 
-static int sensorPartialsCheck(usgscsm_b200_model *m, int index, int64_t n, const void *x,
+int sensorPartialsCheck(usgscsm_b200_model *m, int index, int64_t n, const void *x,
                                const void *y, const void *z, const void *dline,
                                const void *dsamp) {
   if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
@@ -875,6 +543,10 @@ static int sensorPartialsCheck(usgscsm_b200_model *m, int index, int64_t n, cons
   if (n > 0 && (!x || !y || !z || !dline || !dsamp)) return fail(USGSCSM_B200_EINVAL, "null array");
   return USGSCSM_B200_OK;
 }
+
+}  // namespace ub200
+
+extern "C" {
 
 int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int index, int64_t n, const double *x,
                                      const double *y, const double *z, const double *img_line,
@@ -887,47 +559,6 @@ int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int index, int64_t n
     UB_CUDA(cudaSetDevice(m->device));
     return sensorPartialsDev(m, index, (long)n, x, y, z, img_line, img_samp, prec, dline, dsamp,
                              achieved, status, static_cast<cudaStream_t>(stream));
-  });
-}
-
-int usgscsm_b200_sensor_partials(usgscsm_b200_model *m, int index, int64_t n, const double *x,
-                                 const double *y, const double *z, const double *img_line,
-                                 const double *img_samp, double prec, double *dline, double *dsamp,
-                                 double *achieved, uint32_t *status) {
-  int c = sensorPartialsCheck(m, index, n, x, y, z, dline, dsamp);
-  if (c != USGSCSM_B200_OK || n == 0) return c;
-  return guarded([&]() -> int {
-    UB_CUDA(cudaSetDevice(m->device));
-    const bool haveImage = img_line && img_samp;
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    m->ensureGen(0, chunk * 9);  // x y z (l s) | dl ds ach | status
-    PipelineSlot &s = m->slots[0];
-    double *g = s.gen;
-    uint32_t *dst = reinterpret_cast<uint32_t *>(g + 8 * chunk);
-    for (long off = 0; off < n; off += chunk) {
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const size_t b = cnt * sizeof(double);
-      UB_CUDA(cudaMemcpyAsync(g, x + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(g + chunk, y + off, b, cudaMemcpyHostToDevice, s.stream));
-      UB_CUDA(cudaMemcpyAsync(g + 2 * chunk, z + off, b, cudaMemcpyHostToDevice, s.stream));
-      if (haveImage) {
-        UB_CUDA(cudaMemcpyAsync(g + 3 * chunk, img_line + off, b, cudaMemcpyHostToDevice, s.stream));
-        UB_CUDA(cudaMemcpyAsync(g + 4 * chunk, img_samp + off, b, cudaMemcpyHostToDevice, s.stream));
-      }
-      int rc = sensorPartialsDev(m, index, cnt, g, g + chunk, g + 2 * chunk,
-                                 haveImage ? g + 3 * chunk : nullptr,
-                                 haveImage ? g + 4 * chunk : nullptr, prec, g + 5 * chunk,
-                                 g + 6 * chunk, achieved ? g + 7 * chunk : nullptr, dst, s.stream);
-      if (rc != USGSCSM_B200_OK) return rc;
-      UB_CUDA(cudaMemcpyAsync(dline + off, g + 5 * chunk, b, cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaMemcpyAsync(dsamp + off, g + 6 * chunk, b, cudaMemcpyDeviceToHost, s.stream));
-      if (achieved)
-        UB_CUDA(cudaMemcpyAsync(achieved + off, g + 7 * chunk, b, cudaMemcpyDeviceToHost, s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, dst, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
-      UB_CUDA(cudaStreamSynchronize(s.stream));
-    }
-    return USGSCSM_B200_OK;
   });
 }
 
@@ -949,77 +580,6 @@ int usgscsm_b200_model_get_ellipsoid(const usgscsm_b200_model *m, double *semi_m
   *semi_major = e.majorAxis;
   *semi_minor = e.minorAxis;
   return USGSCSM_B200_OK;
-}
-
-// ---- several GPUs from one process -----------------------------------------------------------
-// Points are independent and the packed state is tiny, so a batch shards with no exchange
-// step: contiguous chunk g of the arrays goes to models[g] (the same state
-// loaded on different devices; sizes differ by at most one point), one host thread per model,
-// each running the chunked host-pointer pipeline on its own device.
-}  // extern "C"
-
-static void splitChunk(int64_t n, int parts, int g, int64_t &off, int64_t &cnt) {
-  const int64_t base = n / parts, extra = n % parts;
-  off = base * g + (g < extra ? g : extra);
-  cnt = base + (g < extra ? 1 : 0);
-}
-
-template <class F>
-static int runOnModels(usgscsm_b200_model *const *models, int n_models, int64_t n, F &&call) {
-  if (!models || n_models < 1 || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
-  for (int g = 0; g < n_models; g++) {
-    if (!models[g]) return fail(USGSCSM_B200_EINVAL, "null model");
-    for (int k = 0; k < g; k++)
-      if (models[k] == models[g]) return fail(USGSCSM_B200_EINVAL, "a model is listed twice");
-  }
-  std::vector<int> codes((size_t)n_models, USGSCSM_B200_OK);
-  std::vector<std::string> messages((size_t)n_models);
-  std::vector<std::thread> workers;
-  for (int g = 0; g < n_models; g++) {
-    workers.emplace_back([&, g]() {
-      int64_t off, cnt;
-      splitChunk(n, n_models, g, off, cnt);
-      codes[g] = call(models[g], off, cnt);
-      if (codes[g] != USGSCSM_B200_OK) messages[g] = g_lastError;  // the worker's own copy
-    });
-  }
-  for (std::thread &t : workers) t.join();
-  for (int g = 0; g < n_models; g++)
-    if (codes[g] != USGSCSM_B200_OK) {
-      g_lastError = "model " + std::to_string(g) + ": " + messages[g];
-      return codes[g];
-    }
-  return USGSCSM_B200_OK;
-}
-
-extern "C" {
-
-int usgscsm_b200_ground_to_image_multi(usgscsm_b200_model *const *models, int n_models, int64_t n,
-                                       const double *x, const double *y, const double *z,
-                                       double prec, double *line, double *samp, double *achieved,
-                                       uint32_t *status) {
-  if (n > 0 && (!x || !y || !z || !line || !samp)) return fail(USGSCSM_B200_EINVAL, "null array");
-  return runOnModels(models, n_models, n, [&](usgscsm_b200_model *m, int64_t off, int64_t cnt) {
-    return usgscsm_b200_ground_to_image(m, cnt, x + off, y + off, z + off, prec, line + off,
-                                        samp + off, achieved ? achieved + off : nullptr,
-                                        status ? status + off : nullptr);
-  });
-}
-
-int usgscsm_b200_image_to_ground_multi(usgscsm_b200_model *const *models, int n_models, int64_t n,
-                                       const double *line, const double *samp,
-                                       const double *height, int height_stride, double prec,
-                                       double *x, double *y, double *z, double *achieved,
-                                       uint32_t *status) {
-  if (n > 0 && (!line || !samp || !height || !x || !y || !z))
-    return fail(USGSCSM_B200_EINVAL, "null array");
-  return runOnModels(models, n_models, n, [&](usgscsm_b200_model *m, int64_t off, int64_t cnt) {
-    return usgscsm_b200_image_to_ground(m, cnt, line + off, samp + off,
-                                        height_stride ? height + off : height, height_stride,
-                                        prec, x + off, y + off, z + off,
-                                        achieved ? achieved + off : nullptr,
-                                        status ? status + off : nullptr);
-  });
 }
 
 }  // extern "C"

@@ -1,0 +1,326 @@
+// capi_host.cu -- the HOST-pointer entry points of include/usgscsm_b200.h.
+//
+// Every one of them is the same machine: the arrays are cut into chunks, and each chunk goes
+// through one of a few pipeline slots -- H2D copies, the kernel(s), D2H copies, all on the
+// slot's own stream -- so that while chunk c computes, chunk c+1 is copied in and chunk c-1 is
+// copied out.  Copies are truly asynchronous when the caller's arrays are page-locked
+// (cudaHostAlloc / cudaHostRegister / torch pin_memory); with pageable arrays the runtime
+// stages them and the calls still complete correctly.  The entry points differ only in which
+// arrays they move and which launcher they call; that is what they state below.
+#include <thread>
+#include <vector>
+
+#include "capi_common.h"
+
+namespace ub200 {
+namespace {
+
+struct HostIn {
+  const double *p;  // host array
+  int perPoint;     // doubles per point (3 for an array of csm::EcefCoord)
+  bool broadcast;   // one value for all points (height_stride = 0): a single double is copied
+};
+struct HostOut {
+  double *p;  // host array; nullptr = the caller does not want it (device pointer is null too)
+  int perPoint;
+};
+
+// Device views of one chunk inside a slot's scratch, handed to the launch callback.
+struct Chunk {
+  long count;
+  std::vector<double *> in, out, work;
+  uint32_t *status;  // null when the caller passed no status array
+  cudaStream_t stream;
+};
+
+// launch(chunk) enqueues the kernels of one chunk on chunk.stream and returns a cudaError_t.
+// workPerPoint: extra device doubles per point the launch needs (AoS split / join).
+template <class Launch>
+int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &ins,
+                 const std::vector<HostOut> &outs, uint32_t *status, int workPerPoint,
+                 Launch &&launch) {
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    const int nslots = pipelineSlots();
+    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    long perPoint = workPerPoint + 1;  // + status (half a double, rounded up)
+    for (const HostIn &a : ins) perPoint += a.perPoint;
+    for (const HostOut &a : outs) perPoint += a.perPoint;
+    long c = 0;
+    for (long off = 0; off < n; off += chunk, c++) {
+      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
+      const int si = (int)(c % nslots);
+      m->ensureScratch(si, chunk * perPoint);
+      PipelineSlot &s = m->slots[si];
+      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));  // the slot's previous chunk
+      Chunk k;
+      k.count = cnt;
+      k.stream = s.stream;
+      double *next = s.scratch;
+      for (const HostIn &a : ins) {
+        k.in.push_back(next);
+        if (a.broadcast)
+          UB_CUDA(cudaMemcpyAsync(next, a.p, sizeof(double), cudaMemcpyHostToDevice, s.stream));
+        else
+          UB_CUDA(cudaMemcpyAsync(next, a.p + off * a.perPoint, cnt * a.perPoint * sizeof(double),
+                                  cudaMemcpyHostToDevice, s.stream));
+        next += chunk * a.perPoint;
+      }
+      for (const HostOut &a : outs) {
+        k.out.push_back(a.p ? next : nullptr);
+        next += chunk * a.perPoint;
+      }
+      for (int w = 0; w < workPerPoint; w++, next += chunk) k.work.push_back(next);
+      k.status = status ? reinterpret_cast<uint32_t *>(next) : nullptr;
+      UB_CUDA(launch(k));
+      for (size_t j = 0; j < outs.size(); j++)
+        if (outs[j].p)
+          UB_CUDA(cudaMemcpyAsync(outs[j].p + off * outs[j].perPoint, k.out[j],
+                                  cnt * outs[j].perPoint * sizeof(double), cudaMemcpyDeviceToHost,
+                                  s.stream));
+      if (status)
+        UB_CUDA(cudaMemcpyAsync(status + off, k.status, cnt * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+      UB_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    return USGSCSM_B200_OK;
+  });
+}
+
+bool badCall(usgscsm_b200_model *m, int64_t n, int &rc) {
+  if (!m || n < 0) {
+    rc = fail(USGSCSM_B200_EINVAL, "bad argument");
+    return true;
+  }
+  if (n == 0) {
+    rc = USGSCSM_B200_OK;
+    return true;
+  }
+  return false;
+}
+
+}  // namespace
+}  // namespace ub200
+
+using namespace ub200;
+
+extern "C" {
+
+int usgscsm_b200_ground_to_image(usgscsm_b200_model *m, int64_t n, const double *x,
+                                 const double *y, const double *z, double prec, double *line,
+                                 double *samp, double *achieved, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!x || !y || !z || !line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{x, 1, false}, {y, 1, false}, {z, 1, false}},
+                      {{line, 1}, {samp, 1}, {achieved, 1}}, status, 0, [&](const Chunk &k) {
+                        return launchGroundToImage(*m, k.count, k.in[0], k.in[1], k.in[2], prec,
+                                                   k.out[0], k.out[1], k.out[2], k.status, k.stream);
+                      });
+}
+
+int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double *line,
+                                 const double *samp, const double *height, int height_stride,
+                                 double prec, double *x, double *y, double *z, double *achieved,
+                                 uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!line || !samp || !height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
+  const int hs = height_stride ? 1 : 0;
+  return runPipelined(m, n, {{line, 1, false}, {samp, 1, false}, {height, 1, hs == 0}},
+                      {{x, 1}, {y, 1}, {z, 1}, {achieved, 1}}, status, 0, [&](const Chunk &k) {
+                        return launchImageToGround(*m, k.count, k.in[0], k.in[1], nullptr, k.in[2],
+                                                   hs, prec, k.out[0], k.out[1], k.out[2],
+                                                   k.out[3], k.status, k.stream);
+                      });
+}
+
+// AoS flavours (arrays of csm::EcefCoord / csm::ImageCoord, csm/csm.h:212-308): a chunk is
+// copied as it lies, split into SoA on the device, run through the same kernels, joined and
+// copied back.
+int usgscsm_b200_ground_to_image_aos(usgscsm_b200_model *m, int64_t n, const double *xyz,
+                                     double prec, double *line_samp, double *achieved,
+                                     uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!xyz || !line_samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{xyz, 3, false}}, {{line_samp, 2}, {achieved, 1}}, status, 5,
+                      [&](const Chunk &k) {
+                        double *const *w = k.work.data();  // x y z | line samp
+                        cudaError_t e = launchAosSplit(3, k.count, k.in[0], w[0], w[1], w[2], k.stream);
+                        if (e == cudaSuccess)
+                          e = launchGroundToImage(*m, k.count, w[0], w[1], w[2], prec, w[3], w[4],
+                                                  k.out[1], k.status, k.stream);
+                        if (e == cudaSuccess)
+                          e = launchAosJoin(2, k.count, w[3], w[4], nullptr, k.out[0], k.stream);
+                        return e;
+                      });
+}
+
+int usgscsm_b200_image_to_ground_aos(usgscsm_b200_model *m, int64_t n, const double *line_samp,
+                                     const double *height, int height_stride, double prec,
+                                     double *xyz, double *achieved, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!line_samp || !height || !xyz) return fail(USGSCSM_B200_EINVAL, "null array");
+  const int hs = height_stride ? 1 : 0;
+  return runPipelined(m, n, {{line_samp, 2, false}, {height, 1, hs == 0}}, {{xyz, 3}, {achieved, 1}},
+                      status, 5, [&](const Chunk &k) {
+                        double *const *w = k.work.data();  // line samp | x y z
+                        cudaError_t e = launchAosSplit(2, k.count, k.in[0], w[0], w[1], nullptr, k.stream);
+                        if (e == cudaSuccess)
+                          e = launchImageToGround(*m, k.count, w[0], w[1], nullptr, k.in[1], hs, prec,
+                                                  w[2], w[3], w[4], k.out[1], k.status, k.stream);
+                        if (e == cudaSuccess)
+                          e = launchAosJoin(3, k.count, w[2], w[3], w[4], k.out[0], k.stream);
+                        return e;
+                      });
+}
+
+int usgscsm_b200_image_to_remote_imaging_locus(usgscsm_b200_model *m, int64_t n, const double *line,
+                                               const double *samp, double prec, double *px,
+                                               double *py, double *pz, double *dx, double *dy,
+                                               double *dz, double *achieved, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!line || !samp || !px || !py || !pz || !dx || !dy || !dz)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{line, 1, false}, {samp, 1, false}},
+                      {{px, 1}, {py, 1}, {pz, 1}, {dx, 1}, {dy, 1}, {dz, 1}, {achieved, 1}}, status,
+                      0, [&](const Chunk &k) {
+                        LocusOut o{k.out[0], k.out[1], k.out[2], k.out[3],
+                                   k.out[4], k.out[5], k.out[6], k.status};
+                        return launchRemoteLocus(*m, k.count, k.in[0], k.in[1], prec, o, k.stream);
+                      });
+}
+
+int usgscsm_b200_image_to_proximate_imaging_locus(
+    usgscsm_b200_model *m, int64_t n, const double *line, const double *samp, const double *x,
+    const double *y, const double *z, double prec, double *px, double *py, double *pz, double *dx,
+    double *dy, double *dz, double *achieved, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!line || !samp || !x || !y || !z || !px || !py || !pz || !dx || !dy || !dz)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(
+      m, n, {{line, 1, false}, {samp, 1, false}, {x, 1, false}, {y, 1, false}, {z, 1, false}},
+      {{px, 1}, {py, 1}, {pz, 1}, {dx, 1}, {dy, 1}, {dz, 1}, {achieved, 1}}, status, 0,
+      [&](const Chunk &k) {
+        LocusOut o{k.out[0], k.out[1], k.out[2], k.out[3], k.out[4], k.out[5], k.out[6], k.status};
+        return launchProximateLocus(*m, k.count, k.in[0], k.in[1], k.in[2], k.in[3], k.in[4], prec, o,
+                                    k.stream);
+      });
+}
+
+int usgscsm_b200_ground_partials(usgscsm_b200_model *m, int64_t n, const double *x, const double *y,
+                                 const double *z, double *partials, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!x || !y || !z || !partials) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{x, 1, false}, {y, 1, false}, {z, 1, false}}, {{partials, 6}}, status, 0,
+                      [&](const Chunk &k) {
+                        return launchGroundPartials(*m, k.count, k.in[0], k.in[1], k.in[2], k.out[0],
+                                                    k.status, k.stream);
+                      });
+}
+
+int usgscsm_b200_sensor_partials(usgscsm_b200_model *m, int index, int64_t n, const double *x,
+                                 const double *y, const double *z, const double *img_line,
+                                 const double *img_samp, double prec, double *dline, double *dsamp,
+                                 double *achieved, uint32_t *status) {
+  int c = sensorPartialsCheck(m, index, n, x, y, z, dline, dsamp);
+  if (c != USGSCSM_B200_OK || n == 0) return c;
+  const bool haveImage = img_line && img_samp;
+  std::vector<HostIn> ins = {{x, 1, false}, {y, 1, false}, {z, 1, false}};
+  if (haveImage) {
+    ins.push_back({img_line, 1, false});
+    ins.push_back({img_samp, 1, false});
+  }
+  // the combine step needs a device status array even when the caller wants none
+  return runPipelined(m, n, ins, {{dline, 1}, {dsamp, 1}, {achieved, 1}}, status, 1,
+                      [&](const Chunk &k) {
+                        uint32_t *st = k.status ? k.status : reinterpret_cast<uint32_t *>(k.work[0]);
+                        sensorPartialsDev(m, index, k.count, k.in[0], k.in[1], k.in[2],
+                                          haveImage ? k.in[3] : nullptr, haveImage ? k.in[4] : nullptr,
+                                          prec, k.out[0], k.out[1], k.out[2], st, k.stream);
+                        return cudaSuccess;  // sensorPartialsDev throws CudaError on failure
+                      });
+}
+
+}  // extern "C"
+
+// ---- several GPUs from one process -----------------------------------------------------------
+// Points are independent and the packed state is tiny, so a batch shards with no exchange
+// step: contiguous chunk g of the arrays goes to models[g] (the same state
+// loaded on different devices; sizes differ by at most one point), one host thread per model,
+// each running the pipeline above on its own device.
+namespace {
+
+void splitChunk(int64_t n, int parts, int g, int64_t &off, int64_t &cnt) {
+  const int64_t base = n / parts, extra = n % parts;
+  off = base * g + (g < extra ? g : extra);
+  cnt = base + (g < extra ? 1 : 0);
+}
+
+template <class F>
+int runOnModels(usgscsm_b200_model *const *models, int n_models, int64_t n, F &&call) {
+  if (!models || n_models < 1 || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  for (int g = 0; g < n_models; g++) {
+    if (!models[g]) return fail(USGSCSM_B200_EINVAL, "null model");
+    for (int k = 0; k < g; k++)
+      if (models[k] == models[g]) return fail(USGSCSM_B200_EINVAL, "a model is listed twice");
+  }
+  std::vector<int> codes((size_t)n_models, USGSCSM_B200_OK);
+  std::vector<std::string> messages((size_t)n_models);
+  std::vector<std::thread> workers;
+  for (int g = 0; g < n_models; g++) {
+    workers.emplace_back([&, g]() {
+      int64_t off, cnt;
+      splitChunk(n, n_models, g, off, cnt);
+      codes[g] = call(models[g], off, cnt);
+      if (codes[g] != USGSCSM_B200_OK) messages[g] = lastError();  // the worker thread's own copy
+    });
+  }
+  for (std::thread &t : workers) t.join();
+  for (int g = 0; g < n_models; g++)
+    if (codes[g] != USGSCSM_B200_OK) {
+      lastError() = "model " + std::to_string(g) + ": " + messages[g];
+      return codes[g];
+    }
+  return USGSCSM_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int usgscsm_b200_ground_to_image_multi(usgscsm_b200_model *const *models, int n_models, int64_t n,
+                                       const double *x, const double *y, const double *z,
+                                       double prec, double *line, double *samp, double *achieved,
+                                       uint32_t *status) {
+  if (n > 0 && (!x || !y || !z || !line || !samp)) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runOnModels(models, n_models, n, [&](usgscsm_b200_model *m, int64_t off, int64_t cnt) {
+    return usgscsm_b200_ground_to_image(m, cnt, x + off, y + off, z + off, prec, line + off,
+                                        samp + off, achieved ? achieved + off : nullptr,
+                                        status ? status + off : nullptr);
+  });
+}
+
+int usgscsm_b200_image_to_ground_multi(usgscsm_b200_model *const *models, int n_models, int64_t n,
+                                       const double *line, const double *samp,
+                                       const double *height, int height_stride, double prec,
+                                       double *x, double *y, double *z, double *achieved,
+                                       uint32_t *status) {
+  if (n > 0 && (!line || !samp || !height || !x || !y || !z))
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return runOnModels(models, n_models, n, [&](usgscsm_b200_model *m, int64_t off, int64_t cnt) {
+    return usgscsm_b200_image_to_ground(m, cnt, line + off, samp + off,
+                                        height_stride ? height + off : height, height_stride,
+                                        prec, x + off, y + off, z + off,
+                                        achieved ? achieved + off : nullptr,
+                                        status ? status + off : nullptr);
+  });
+}
+
+}  // extern "C"

@@ -37,18 +37,13 @@ struct DeviceBuffer {
   size_t bytes = 0;
 };
 
-// One slot of the chunked host-pointer pipeline: device scratch for one chunk + a stream.
+// One slot of the chunked host-pointer pipeline (capi_host.cu): device scratch for one chunk's
+// inputs, outputs and status words, a stream, and the event that marks the chunk done.
 struct PipelineSlot {
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;
-  double *in[3] = {nullptr, nullptr, nullptr};   // x,y,z  or line,samp,height
-  double *out[4] = {nullptr, nullptr, nullptr, nullptr};  // up to x,y,z,achieved
-  uint32_t *status = nullptr;
-  long capacity = 0;  // points
-  double *gen = nullptr;  // generic scratch of the locus / partials entry points
-  long genDoubles = 0;
-  double *aos = nullptr;  // AoS flavours: 3 doubles per point, input then output of a chunk
-  long aosCapacity = 0;
+  double *scratch = nullptr;
+  long scratchDoubles = 0;
 };
 
 constexpr int kMaxPipelineSlots = 8;
@@ -88,9 +83,7 @@ struct Model {
 
   ~Model();
   const double *upload(const std::vector<double> &v);
-  void ensureSlot(int s, long points);
-  void ensureAos(int s, long points);
-  void ensureGen(int s, long doubles);
+  void ensureScratch(int s, long doubles);
 };
 
 // model_ls.cu
