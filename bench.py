@@ -418,6 +418,8 @@ def run_b200(args):
 
     if not args.no_e2e:
         result["e2e"] = e2e(args, models, x, y, z, seg, n_job, barrier, max_over_ranks)
+        if world == 1:
+            result["e2e_image_to_ground_grid"] = e2e_grid(args, model, h, lines, line0)
     if rank == 0 and world == 1 and not args.no_cpu:
         from oracle import ref
         if ref.available():
@@ -585,6 +587,33 @@ def e2e(args, models, x, y, z, seg, n_job, barrier, max_over_ranks):
             "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 20 * n,
             "ms_per_step": 1e3 * dt / args.steps,
             "api": "usgscsm_b200_ground_to_image (host pointers, pinned)"}
+
+
+def e2e_grid(args, model, h, lines, line0):
+    """Orthorectification end to end: per-pixel heights up from pinned host memory, ground
+    points and status down, pixel coordinates generated in the kernel (28 B/pt down, 8 up)."""
+    import torch
+    from usgscsm_b200 import _capi
+    n = lines * N_SAMPLES
+    hh = h[:n].cpu().pin_memory()
+    hx, hy, hz = (torch.empty(n, dtype=torch.float64).pin_memory() for _ in range(3))
+    hst = torch.empty(n, dtype=torch.int32).pin_memory()
+
+    def call():
+        _capi.check(_capi.lib.usgscsm_b200_image_to_ground_grid(
+            model._h, line0, 0.5, 1.0, 1.0, lines, N_SAMPLES, hh.data_ptr(), 1, PREC,
+            hx.data_ptr(), hy.data_ptr(), hz.data_ptr(), None, hst.data_ptr()))
+
+    call()
+    steps = max(1, args.steps // 2)
+    t = time.perf_counter()
+    for _ in range(steps):
+        call()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t
+    return {"value": n * steps / dt / 1e6, "unit": "Mpoints/s", "h2d_bytes_per_step": 8 * n,
+            "d2h_bytes_per_step": 28 * n, "ms_per_step": 1e3 * dt / steps,
+            "api": "usgscsm_b200_image_to_ground_grid (host pointers, pinned)"}
 
 
 if __name__ == "__main__":

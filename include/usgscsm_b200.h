@@ -276,6 +276,14 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m
                                           double *z, double *achieved, uint32_t *status,
                                           void *stream);
 
+/* The same with HOST arrays: heights up (one double when height_stride = 0), ground points
+ * down, chunked by whole rows through the copy pipeline. */
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid(usgscsm_b200_model *m, double line0, double samp0,
+                                      double dline, double dsamp, int64_t n_lines,
+                                      int64_t n_samps, const double *height, int height_stride,
+                                      double prec, double *x, double *y, double *z,
+                                      double *achieved, uint32_t *status);
+
 /* ---- building blocks of the per-point math, batched -------------------------------------
  * The reference exposes these as free functions and tests them directly
  * (tests/DistortionTests.cpp, tests/UtilitiesTests.cpp); exporting the device versions lets

@@ -369,6 +369,17 @@ class RasterGM {
           "imageToGroundGridDevice");
   }
 
+  // The same with host arrays (heights up, ground points down, copies inside the call).
+  void imageToGroundGrid(double line0, double samp0, double dline, double dsamp, size_t nLines,
+                         size_t nSamps, const double *height, bool perPointHeight,
+                         double desiredPrecision, double *x, double *y, double *z,
+                         double *achievedPrecision = NULL, uint32_t *status = NULL) const {
+    check(usgscsm_b200_image_to_ground_grid(m_h, line0, samp0, dline, dsamp, (int64_t)nLines,
+                                            (int64_t)nSamps, height, perPointHeight ? 1 : 0,
+                                            desiredPrecision, x, y, z, achievedPrecision, status),
+          "imageToGroundGrid");
+  }
+
   // Status word of one point -> what the scalar reference call does: throw csm::Error for
   // the error bits (Distortion.cpp:357-365, SAR:569-575), append csm::Warning otherwise.
   static void raiseOrWarn(uint32_t st, csm::WarningList *warnings, const char *function) {

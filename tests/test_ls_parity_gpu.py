@@ -233,3 +233,30 @@ def test_table_ends_reduced_order(ref):
     exp = rm.remote_locus(line, samp)
     for k in range(6):
         assert np.abs(got[k] - exp[k]).max() <= (1e-4 if k < 3 else 1e-12)
+
+
+@pytest.mark.parametrize("kind", ["linescan", "pushframe", "frame", "sar"])
+def test_host_grid_equals_explicit(kind):
+    """usgscsm_b200_image_to_ground_grid (host arrays, chunked by whole rows, several chunks)
+    against the explicit-pixel host call, per-point and single heights."""
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import synth
+    state = {"linescan": lambda: synth.linescan_state(n_lines=3000, n_samples=1999, seed=8),
+             "pushframe": lambda: synth.pushframe_state(n_framelets=180, framelet_height=16, n_samples=2001),
+             "frame": lambda: synth.frame_state(n_lines=2500, n_samples=2047),
+             "sar": lambda: synth.sar_state(n_lines=2600, n_samples=2000)}[kind]()
+    gm = ub.UsgsAstroPlugin().constructModelFromState(state)
+    sz = gm.getImageSize()
+    nl, ns = int(sz.line) - 3, int(sz.samp) - 5           # 5.9 M points: two pipeline chunks
+    rng = np.random.default_rng(3)
+    h = rng.uniform(-300, 300, nl * ns)
+    line = np.repeat(1.25 + np.arange(nl), ns)
+    samp = np.tile(2.5 + np.arange(ns), nl)
+    got = gm.imageToGroundGrid(1.25, 2.5, 1.0, 1.0, nl, ns, h, 1e-5, achieved=True)
+    exp = gm.imageToGroundBatch(line, samp, h, 1e-5)
+    for u, v in zip(got, exp):
+        assert np.array_equal(u, v, equal_nan=True)
+    got = gm.imageToGroundGrid(1.25, 2.5, 1.0, 1.0, nl, ns, np.array([40.0]), 1e-5)
+    exp = gm.imageToGroundBatch(line, samp, 40.0, 1e-5)
+    for k in (0, 1, 2, 4):
+        assert np.array_equal(got[k], exp[k], equal_nan=True)

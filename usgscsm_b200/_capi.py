@@ -89,6 +89,9 @@ SIGNATURES = {
     "usgscsm_b200_image_to_ground_grid_dev": (
         C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
                   C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_grid": (
+        C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
+                  C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_apply_distortion": (
         C.c_int, [C.c_int, C.c_int, _dp, C.c_int, C.c_double, C.c_double, C.c_int64, _dp, _dp, _dp,
                   _dp, _dp]),

@@ -27,6 +27,7 @@ struct HostOut {
 
 // Device views of one chunk inside a slot's scratch, handed to the launch callback.
 struct Chunk {
+  long offset;  // index of the chunk's first point in the caller's arrays
   long count;
   std::vector<double *> in, out, work;
   uint32_t *status;  // null when the caller passed no status array
@@ -35,14 +36,16 @@ struct Chunk {
 
 // launch(chunk) enqueues the kernels of one chunk on chunk.stream and returns a cudaError_t.
 // workPerPoint: extra device doubles per point the launch needs (AoS split / join).
+// granule: chunks hold a whole number of granules (image rows for the dense-grid call).
 template <class Launch>
 int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &ins,
                  const std::vector<HostOut> &outs, uint32_t *status, int workPerPoint,
-                 Launch &&launch) {
+                 Launch &&launch, long granule = 1) {
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
     const int nslots = pipelineSlots();
-    const long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
+    if (granule > 1) chunk = chunk < granule ? granule : chunk / granule * granule;
     long perPoint = workPerPoint + 1;  // + status (half a double, rounded up)
     for (const HostIn &a : ins) perPoint += a.perPoint;
     for (const HostOut &a : outs) perPoint += a.perPoint;
@@ -54,6 +57,7 @@ int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &in
       PipelineSlot &s = m->slots[si];
       if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));  // the slot's previous chunk
       Chunk k;
+      k.offset = off;
       k.count = cnt;
       k.stream = s.stream;
       double *next = s.scratch;
@@ -134,6 +138,28 @@ int usgscsm_b200_image_to_ground(usgscsm_b200_model *m, int64_t n, const double 
                                                    hs, prec, k.out[0], k.out[1], k.out[2],
                                                    k.out[3], k.status, k.stream);
                       });
+}
+
+// Dense grid, host arrays: only the heights go up (8 B/pt, or nothing for a single height) and
+// the ground points come down; the pixel coordinates are generated in the kernel.  Chunks are
+// whole image rows.
+int usgscsm_b200_image_to_ground_grid(usgscsm_b200_model *m, double line0, double samp0,
+                                      double dline, double dsamp, int64_t n_lines,
+                                      int64_t n_samps, const double *height, int height_stride,
+                                      double prec, double *x, double *y, double *z,
+                                      double *achieved, uint32_t *status) {
+  if (!m || n_lines < 0 || n_samps < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n_lines == 0 || n_samps == 0) return USGSCSM_B200_OK;
+  if (!height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
+  const int hs = height_stride ? 1 : 0;
+  return runPipelined(
+      m, n_lines * n_samps, {{height, 1, hs == 0}}, {{x, 1}, {y, 1}, {z, 1}, {achieved, 1}}, status, 0,
+      [&](const Chunk &k) {
+        GridSpec g{line0 + (double)(k.offset / n_samps) * dline, samp0, dline, dsamp, (long)n_samps};
+        return launchImageToGround(*m, k.count, nullptr, nullptr, &g, k.in[0], hs, prec, k.out[0],
+                                   k.out[1], k.out[2], k.out[3], k.status, k.stream);
+      },
+      (long)n_samps);
 }
 
 // AoS flavours (arrays of csm::EcefCoord / csm::ImageCoord, csm/csm.h:212-308): a chunk is

@@ -209,8 +209,20 @@ class RasterGM(object):
         """Dense-grid imageToGround (bin/usgscsm_cam_test.cc:294-309) with pixel coordinates
         generated in the kernel.  `height`: torch CUDA tensor with 1 or n_lines*n_samps
         entries.  Returns torch CUDA tensors (x, y, z, achieved, status)."""
-        import torch
         n = int(n_lines) * int(n_samps)
+        if not _is_torch(height):   # host arrays in, host arrays out (copies inside the call)
+            hh = _host(height)
+            if hh.size not in (1, n):
+                raise ValueError("height must hold 1 or n_lines * n_samps entries")
+            x, y, z = np.empty(n), np.empty(n), np.empty(n)
+            ach = np.empty(n) if achieved else None
+            st = np.empty(n, dtype=np.uint32) if status else None
+            check(lib.usgscsm_b200_image_to_ground_grid(
+                self._h, float(line0), float(samp0), float(dline), float(dsamp), int(n_lines),
+                int(n_samps), _ptr(hh), 0 if hh.size == 1 and n != 1 else 1, desiredPrecision,
+                _ptr(x), _ptr(y), _ptr(z), _ptr(ach), _ptr(st)))
+            return x, y, z, ach, st
+        import torch
         dev = height.device
         stride = 0 if height.numel() == 1 else 1
         if out is None:
