@@ -453,7 +453,7 @@ def ncu_traffic(n):
 def callers_side(model, x, y, z, m, dev, band):
     """Side measurements of the batched caller-level entry points on the C2 line-scan model:
     computeGroundPartials (4 searches per point in one kernel), computeSensorPartials (2
-    searches + difference), imageToRemoteImagingLocus, imageToProximateImagingLocus (3
+    searches + difference), computeAllSensorPartials (17 searches, on a quarter of the points), imageToRemoteImagingLocus, imageToProximateImagingLocus (3
     imageToGround + 2 elevations).  Device resident, median of 3 after 1 warm-up."""
     import torch
     from usgscsm_b200 import _capi
@@ -477,6 +477,11 @@ def callers_side(model, x, y, z, m, dev, band):
         "proximate_imaging_locus": lambda: lib.usgscsm_b200_image_to_proximate_imaging_locus_dev(
             h, m, p(line), p(samp), p(x), p(y), p(z), PREC, *[p(t) for t in o], p(st), stream),
     }
+    npar = lib.usgscsm_b200_model_num_parameters(h)
+    m4 = m // 4     # 17 searches and 256 B of partials per point
+    allp = torch.empty(m4 * npar * 2, dtype=torch.float64, device=dev)
+    calls["all_sensor_partials_%d_params" % npar] = lambda: lib.usgscsm_b200_all_sensor_partials_dev(
+        h, npar, None, m4, p(x), p(y), p(z), None, None, PREC, p(allp), p(o[0]), p(st), stream)
     out = {"points": m, "unit": "Mpoints/s"}
     for name, fn in calls.items():
         _capi.check(fn())
@@ -489,7 +494,7 @@ def callers_side(model, x, y, z, m, dev, band):
             b.record()
             torch.cuda.synchronize()
             ms.append(a.elapsed_time(b))
-        out[name] = m / sorted(ms)[1] / 1e3
+        out[name] = (m4 if name.startswith("all_") else m) / sorted(ms)[1] / 1e3
     return out
 
 

@@ -251,6 +251,28 @@ USGSCSM_B200_API int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int
                                      double prec, double *dline, double *dsamp,
                                      double *achieved, uint32_t *status, void *stream);
 
+/* computeAllSensorPartials(ground_pt | image_pt + ground_pt, pSet, prec, *ach, *warn)
+ * (csm/RasterGM.cpp:52-140 through LS:1413-1455, PF:1170-1201, FR:894-940; SAR takes the
+ * RasterGM default): the image point once (skipped when img_line / img_samp are given), then
+ * one adjusted search per requested parameter.  indices = NULL: all parameters, in order
+ * (n_indices must then be usgscsm_b200_model_num_parameters; csm::param::VALID for these
+ * models); otherwise what getParameterSetIndices(pSet) would return.  partials: per point,
+ * per requested parameter, (dline, dsamp) -- n * n_indices * 2 doubles, the batch form of
+ * std::vector<csm::RasterGM::SensorPartials>.  achieved (nullable): the largest achieved
+ * precision over the parameters, starting from 0.  status (nullable): warning and error bits
+ * of all the searches; with an error bit (the scalar call would have thrown) the point's
+ * whole list is NaN. */
+USGSCSM_B200_API int usgscsm_b200_all_sensor_partials(usgscsm_b200_model *m, int n_indices, const int *indices,
+                                     int64_t n, const double *x, const double *y, const double *z,
+                                     const double *img_line, const double *img_samp,
+                                     double desired_precision, double *partials,
+                                     double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_all_sensor_partials_dev(usgscsm_b200_model *m, int n_indices, const int *indices,
+                                         int64_t n, const double *x, const double *y, const double *z,
+                                         const double *img_line, const double *img_samp,
+                                         double desired_precision, double *partials,
+                                         double *achieved, uint32_t *status, void *stream);
+
 /* Several GPUs from one process (row-band / chunk sharding, no exchange step): models[g] are
  * the SAME model state loaded on n_models different devices; contiguous chunk g of the host
  * arrays (sizes differ by at most one point) is processed on models[g], all concurrently.

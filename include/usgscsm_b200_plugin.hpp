@@ -252,6 +252,36 @@ class RasterGM {
                                        achievedPrecision, status),
           "computeSensorPartialsBatch");
   }
+  // csm/RasterGM.cpp:52-140 via LS:1413-1455, PF:1170-1201, FR:894-940 (pSet = VALID: every
+  // parameter of these models)
+  std::vector<std::pair<double, double> > computeAllSensorPartials(
+      const csm::EcefCoord &groundPt, double desiredPrecision = 0.001,
+      double *achievedPrecision = NULL, csm::WarningList *warnings = NULL) const {
+    const int np = getNumParameters();
+    std::vector<double> p((size_t)np * 2);
+    double a = 0;
+    uint32_t st = 0;
+    check(usgscsm_b200_all_sensor_partials(m_h, np, NULL, 1, &groundPt.x, &groundPt.y, &groundPt.z,
+                                           NULL, NULL, desiredPrecision, p.data(), &a, &st),
+          "computeAllSensorPartials");
+    raiseOrWarn(st, warnings, "computeAllSensorPartials");
+    if (achievedPrecision) *achievedPrecision = a;
+    std::vector<std::pair<double, double> > out((size_t)np);
+    for (int k = 0; k < np; k++) out[(size_t)k] = std::make_pair(p[2 * k], p[2 * k + 1]);
+    return out;
+  }
+  // partials: n * numIndices * 2 doubles, (dline, dsamp) per point per parameter;
+  // indices = NULL: all parameters (numIndices = getNumParameters()).
+  void computeAllSensorPartialsBatch(size_t n, const double *x, const double *y, const double *z,
+                                     double desiredPrecision, double *partials,
+                                     double *achievedPrecision = NULL, uint32_t *status = NULL,
+                                     const double *imgLine = NULL, const double *imgSamp = NULL,
+                                     int numIndices = -1, const int *indices = NULL) const {
+    check(usgscsm_b200_all_sensor_partials(m_h, numIndices < 0 ? getNumParameters() : numIndices,
+                                           indices, (int64_t)n, x, y, z, imgLine, imgSamp,
+                                           desiredPrecision, partials, achievedPrecision, status),
+          "computeAllSensorPartialsBatch");
+  }
   // csm::SettableEllipsoid (LS:2116-2119)
   void setEllipsoid(double semiMajorRadius, double semiMinorRadius) {
     check(usgscsm_b200_model_set_ellipsoid(m_h, semiMajorRadius, semiMinorRadius), "setEllipsoid");

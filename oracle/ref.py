@@ -46,6 +46,7 @@ def lib():
         L.ref_remote_locus.argtypes = [C.c_void_p, C.c_long, _dp, _dp, C.c_double] + [_dp] * 8 + [C.c_int]
         L.ref_proximate_locus.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 8 + [C.c_int]
         L.ref_sensor_partials.argtypes = [C.c_void_p, C.c_int, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 4 + [C.c_int]
+        L.ref_all_sensor_partials.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 3 + [C.c_int]
         L.ref_ground_partials.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_set_ellipsoid.argtypes = [C.c_void_p, C.c_double, C.c_double]
         L.ref_lagrange.argtypes = [C.c_int, _dp, C.c_double, C.c_double, C.c_double, C.c_int,
@@ -175,6 +176,25 @@ class RefModel(object):
                                     None if isamp is None else isamp.ctypes.data, prec,
                                     dl.ctypes.data, ds.ctypes.data, ach.ctypes.data, st.ctypes.data, threads)
         return dl, ds, ach, st
+
+    def all_sensor_partials(self, num_params, x, y, z, prec=0.001, image_pts=None, threads=1):
+        """computeAllSensorPartials (csm::param::VALID) per point ->
+        ((n, num_params, 2) partials, achieved, status)."""
+        x = _a(x)
+        n = x.size
+        y, z = _a(y, n), _a(z, n)
+        il = isamp = None
+        if image_pts is not None:
+            il, isamp = _a(image_pts[0], n), _a(image_pts[1], n)
+        p, ach = np.empty((n, num_params, 2)), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        got = self._L.ref_all_sensor_partials(
+            self._h, n, x.ctypes.data, y.ctypes.data, z.ctypes.data,
+            None if il is None else il.ctypes.data, None if isamp is None else isamp.ctypes.data,
+            prec, p.ctypes.data, ach.ctypes.data, st.ctypes.data, threads)
+        if got != num_params:
+            raise RuntimeError("the reference model has %d parameters, not %d" % (got, num_params))
+        return p, ach, st
 
     def ground_partials(self, x, y, z, threads=1):
         """computeGroundPartials per point -> ((n, 6) partials, status)."""

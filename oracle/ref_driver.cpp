@@ -373,6 +373,53 @@ int ref_sensor_partials(void *h, int index, long n, const double *x, const doubl
   return 0;
 }
 
+// computeAllSensorPartials (pSet = VALID) over n points; partials = numParams * 2 doubles per
+// point; img_line / img_samp nullable (then the ground-point overload).
+int ref_all_sensor_partials(void *h, long n, const double *x, const double *y, const double *z,
+                            const double *img_line, const double *img_samp, double prec,
+                            double *partials, double *achieved, uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int np = gm->getNumParameters();
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    std::vector<csm::RasterGM::SensorPartials> p;
+    try {
+      csm::WarningList warn;
+      if (img_line && img_samp)
+        p = gm->computeAllSensorPartials(csm::ImageCoord(img_line[i], img_samp[i]),
+                                         csm::EcefCoord(x[i], y[i], z[i]), csm::param::VALID, prec,
+                                         &ach, &warn);
+      else
+        p = gm->computeAllSensorPartials(csm::EcefCoord(x[i], y[i], z[i]), csm::param::VALID, prec,
+                                         &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+      ach = std::nan("");
+      p.clear();
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+      ach = std::nan("");
+      p.clear();
+    }
+    for (int k = 0; k < np; k++) {
+      const bool have = k < (int)p.size();
+      const double a = have ? p[k].first : std::nan(""), b = have ? p[k].second : std::nan("");
+      if (!(std::isfinite(a) && std::isfinite(b))) st |= ST_NONFINITE;
+      partials[(i * np + k) * 2] = a;
+      partials[(i * np + k) * 2 + 1] = b;
+    }
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return np;
+}
+
 // computeGroundPartials over n points; partials = 6 doubles per point (LS:1299-1325 etc.).
 int ref_ground_partials(void *h, long n, const double *x, const double *y, const double *z,
                         double *partials, uint32_t *status, int threads) {

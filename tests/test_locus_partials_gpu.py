@@ -217,3 +217,65 @@ def test_sensor_partials_bad_index():
     with pytest.raises(_capi.EngineError) as e:
         gm.computeSensorPartialsBatch(7, np.zeros(3), np.zeros(3), np.zeros(3))
     assert e.value.code == _capi.EINVAL
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_all_sensor_partials(ref, kind):
+    """computeAllSensorPartials (csm/RasterGM.cpp:52-140 via LS:1413-1455, PF:1170-1201,
+    FR:894-940; SAR: the RasterGM default): both overloads against the reference, bit-equal to
+    the per-parameter call, index subsets, device flavour."""
+    import torch
+    from usgscsm_b200 import _capi, synth
+    gm, rm = _pair(ref, kind)
+    nl, ns = rm.image_size()
+    npar = gm.getNumParameters()
+    rng = np.random.default_rng(77)
+    n = 600 if kind == "sar" else 3000
+    line, samp = pixels(rng, n, nl, ns)
+    x, y, z, _, _ = gm.imageToGroundBatch(line, samp, synth.synthetic_dem(line, samp))
+    x[:7] = np.nan
+    for image_pts in (None, (line, samp)):
+        p, ach, st = gm.computeAllSensorPartialsBatch(x, y, z, 1e-6, imagePts=image_pts)
+        ep, ea, est = rm.all_sensor_partials(npar, x, y, z, 1e-6, image_pts=image_pts, threads=0)
+        assert p.shape == (n, npar, 2)
+        assert np.array_equal(st & _capi.ST_REFERENCE_MASK, est)
+        ok = np.isfinite(ep).all(axis=(1, 2))
+        assert np.array_equal(np.isfinite(p).all(axis=(1, 2)), ok) and ok.sum() >= n * 0.9
+        assert np.isnan(p[~ok]).all()          # the scalar call threw: no partial survives
+        scale = np.maximum(1.0, np.abs(ep[ok]).max(axis=(0, 2)))[None, :, None]
+        assert (np.abs(p[ok] - ep[ok]) <= 1e-9 * scale).all()
+        fa = np.isfinite(ea)
+        assert np.array_equal(np.isfinite(ach), fa)
+        assert np.abs(ach[fa] - ea[fa]).max(initial=0.0) <= PX_TOL
+        # slot k is what the single-parameter call gives
+        for k in (0, npar // 2, npar - 1):
+            dl, ds, _, _ = gm.computeSensorPartialsBatch(k, x, y, z, 1e-6, imagePts=image_pts)
+            assert np.array_equal(p[ok, k, 0], dl[ok]) and np.array_equal(p[ok, k, 1], ds[ok])
+    # a parameter subset (what getParameterSetIndices(pSet) would select), device arrays
+    idx = [npar - 1, 1]
+    sub, _, _ = gm.computeAllSensorPartialsBatch(x, y, z, 1e-6, indices=idx)
+    assert np.array_equal(sub[ok], p_sub(gm, x, y, z, idx)[ok])
+    d = gm.computeAllSensorPartialsBatch(*(torch.as_tensor(a, device="cuda") for a in (x, y, z)), 1e-6)
+    torch.cuda.synchronize()
+    full, ach0, st0 = gm.computeAllSensorPartialsBatch(x, y, z, 1e-6)
+    assert np.array_equal(d[0].cpu().numpy(), full, equal_nan=True)
+    assert np.array_equal(d[1].cpu().numpy(), ach0, equal_nan=True)
+    assert np.array_equal(d[2].cpu().numpy().view(np.uint32), st0)
+
+
+def p_sub(gm, x, y, z, idx):
+    out = np.empty((x.size, len(idx), 2))
+    for j, k in enumerate(idx):
+        out[:, j, 0], out[:, j, 1], _, _ = gm.computeSensorPartialsBatch(k, x, y, z, 1e-6)
+    return out
+
+
+def test_all_sensor_partials_bad_arguments():
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import _capi, synth
+    gm = ub.UsgsAstroPlugin().constructModelFromState(synth.frame_state())
+    with pytest.raises(_capi.EngineError) as e:
+        gm.computeAllSensorPartialsBatch(np.zeros(3), np.zeros(3), np.zeros(3), indices=[0, 7])
+    assert e.value.code == _capi.EINVAL
+    p, ach, st = gm.computeAllSensorPartialsBatch(np.zeros(0), np.zeros(0), np.zeros(0))
+    assert p.shape == (0, 7, 2)

@@ -81,6 +81,12 @@ SIGNATURES = {
         C.c_int, [_h, C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_sensor_partials_dev": (
         C.c_int, [_h, C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_all_sensor_partials": (
+        C.c_int, [_h, C.c_int, C.POINTER(C.c_int), C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double,
+                  _dp, _dp, _dp]),
+    "usgscsm_b200_all_sensor_partials_dev": (
+        C.c_int, [_h, C.c_int, C.POINTER(C.c_int), C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double,
+                  _dp, _dp, _dp, _dp]),
     "usgscsm_b200_ground_to_image_multi": (
         C.c_int, [C.POINTER(_h), C.c_int, C.c_int64, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_image_to_ground_multi": (

@@ -96,6 +96,47 @@ __global__ void sensorPartialsCombineKernel(long n, const double *__restrict__ l
   }
 }
 
+// One parameter of computeAllSensorPartials (csm/RasterGM.cpp:101-140): the forward difference
+// into slot k of the point's (dline, dsamp) list, achieved = max over the parameters starting
+// from 0.0 ("prec > *achievedPrecision", so a NaN never wins), warnings accumulate.  On the
+// last parameter a point with an error bit (the scalar call would have thrown) has its whole
+// list set to NaN.
+__global__ void sensorPartialsStepKernel(long n, const double *__restrict__ l0,
+                                         const double *__restrict__ s0,
+                                         const uint32_t *__restrict__ st0,
+                                         const double *__restrict__ l1,
+                                         const double *__restrict__ s1,
+                                         const double *__restrict__ achP,
+                                         const uint32_t *__restrict__ stP, double delta,
+                                         double *__restrict__ partials, int numParams, int k,
+                                         double *__restrict__ achieved,
+                                         uint32_t *__restrict__ status) {
+  const uint32_t kErr = USGSCSM_B200_ST_ERROR_ALGORITHM | USGSCSM_B200_ST_ERROR_UNKNOWN |
+                        USGSCSM_B200_ST_ERROR_OTHER;
+  const uint32_t kKeep = kErr | USGSCSM_B200_ST_NO_INTERSECTION | USGSCSM_B200_ST_PRECISION_NOT_MET;
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t acc = k == 0 ? (st0 ? st0[i] & kKeep : 0u) : status[i];
+    double am = (k == 0 || !achieved) ? 0.0 : achieved[i];
+    acc |= stP[i] & kKeep;
+    const double a = achP[i];
+    if (a > am) am = a;
+    const double pl = (l1[i] - l0[i]) / delta;
+    const double ps = (s1[i] - s0[i]) / delta;
+    double *out = partials + (size_t)i * numParams * 2;
+    out[2 * k] = pl;
+    out[2 * k + 1] = ps;
+    if (!(isfinite(pl) && isfinite(ps))) acc |= USGSCSM_B200_ST_NONFINITE;
+    if (k == numParams - 1 && (acc & kErr)) {
+      acc = (acc & kErr) | USGSCSM_B200_ST_NONFINITE;
+      for (int q = 0; q < 2 * numParams; q++) out[q] = nan("");
+      am = nan("");
+    }
+    status[i] = acc;
+    if (achieved) achieved[i] = am;
+  }
+}
+
 // r[i] = refinedReciprocal(b[i]); a divisor the fast path can never accept (zero, subnormal,
 // huge, non-finite) gets NaN, which sends every division by it to the slow path.
 __global__ void reciprocalKernel(int n, const double *__restrict__ b, double *__restrict__ r) {
@@ -213,6 +254,19 @@ cudaError_t launchSensorPartialsCombine(long n, const double *l0, const double *
   int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
   sensorPartialsCombineKernel<<<blocks, 256, 0, stream>>>(n, l0, s0, st0, l1, s1, delta, dline,
                                                           dsamp, achieved, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchSensorPartialsStep(long n, const double *l0, const double *s0,
+                                     const uint32_t *st0, const double *l1, const double *s1,
+                                     const double *achP, const uint32_t *stP, double delta,
+                                     double *partials, int numParams, int k, double *achieved,
+                                     uint32_t *status, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  sensorPartialsStepKernel<<<blocks, 256, 0, stream>>>(n, l0, s0, st0, l1, s1, achP, stP, delta,
+                                                       partials, numParams, k, achieved, status);
   countLaunch();
   return cudaGetLastError();
 }

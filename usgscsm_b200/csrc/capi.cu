@@ -474,18 +474,52 @@ namespace ub200 {
 // computeSensorPartials(index, ground_pt, prec, ach, warn) LS:1336-1396 over n points: the
 // search with the model as it is (skipped when the caller supplies the image points, the
 // 6-argument overload), the search with parameter `index` moved by m_gsd, forward difference.
+// DELTA of the scalar call: m_gsd (LS:1386, PF:1153), 1.0 or 0.01 for the quaternion
+// parameters (FR:853-859), m_scaledPixelWidth (SAR:1360)
+static double sensorPartialDelta(const usgscsm_b200_model *m, int index) {
+  switch (m->kind) {
+    case USGSCSM_B200_MODEL_FRAME: return (index > 2 && index < 7) ? 0.01 : 1.0;
+    case USGSCSM_B200_MODEL_SAR: return m->sar.scaledPixelWidth;
+    default: return m->ls.gsd;
+  }
+}
+
+// groundToImage with parameter `index` moved by delta.  *pfTable: scratch the caller frees on
+// the stream afterwards (per-framelet orientations of the adjusted push-frame model).
+static cudaError_t launchAdjustedGroundToImage(usgscsm_b200_model *m, int index, double delta,
+                                               long n, const double *x, const double *y,
+                                               const double *z, double prec, double *l1,
+                                               double *s1, double *achieved, uint32_t *st1,
+                                               cudaStream_t stream, double **pfTable) {
+  switch (m->kind) {
+    case USGSCSM_B200_MODEL_LINE_SCANNER:
+      return launchLsGroundToImage(adjustedLineScanner(*m, index, delta), m->smCount, n, x, y, z,
+                                   prec, l1, s1, achieved, st1, stream);
+    case USGSCSM_B200_MODEL_PUSH_FRAME: {
+      LsState adj = adjustedPushFrame(*m, index, delta);
+      if (m->ls.frameletOrient) {  // per-framelet orientations of the adjusted model
+        cudaError_t e = cudaMallocAsync(
+            pfTable, (size_t)(adj.numFramelets + 2) * kFrameletOrientDoubles * sizeof(double), stream);
+        if (e == cudaSuccess) e = launchPfFrameletOrientations(adj, *pfTable, stream);
+        if (e != cudaSuccess) return e;
+        adj.frameletOrient = *pfTable;
+      }
+      return launchPfGroundToImage(adj, m->smCount, n, x, y, z, prec, l1, s1, achieved, st1, stream);
+    }
+    case USGSCSM_B200_MODEL_FRAME:
+      return launchFrGroundToImage(adjustedFrame(*m, index, delta), m->smCount, n, x, y, z, prec,
+                                   l1, s1, achieved, st1, stream);
+    default:
+      return launchSarGroundToImage(adjustedSar(*m, index, delta), m->smCount, n, x, y, z, prec, l1,
+                                    s1, achieved, st1, stream);
+  }
+}
+
 int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
                              const double *y, const double *z, const double *img_line,
                              const double *img_samp, double prec, double *dline, double *dsamp,
                              double *achieved, uint32_t *status, cudaStream_t stream) {
-  // DELTA of the scalar call: m_gsd (LS:1386, PF:1153), 1.0 or 0.01 for the quaternion
-  // parameters (FR:853-859), m_scaledPixelWidth (SAR:1360)
-  double delta;
-  switch (m->kind) {
-    case USGSCSM_B200_MODEL_FRAME: delta = (index > 2 && index < 7) ? 0.01 : 1.0; break;
-    case USGSCSM_B200_MODEL_SAR: delta = m->sar.scaledPixelWidth; break;
-    default: delta = m->ls.gsd; break;
-  }
+  const double delta = sensorPartialDelta(m, index);
   const bool haveImage = img_line && img_samp;
   // scratch: l0, s0 (unless supplied), l1, s1, st0, st1 (unless the caller wants status)
   double *scratch = nullptr, *pfTable = nullptr;
@@ -497,32 +531,9 @@ int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
   cudaError_t e = cudaSuccess;
   if (!haveImage)
     e = launchGroundToImage(*m, n, x, y, z, prec, l0, s0, nullptr, st0, stream);
-  if (e == cudaSuccess) {
-    switch (m->kind) {
-      case USGSCSM_B200_MODEL_LINE_SCANNER:
-        e = launchLsGroundToImage(adjustedLineScanner(*m, index, delta), m->smCount, n, x, y, z,
-                                  prec, l1, s1, achieved, st1, stream);
-        break;
-      case USGSCSM_B200_MODEL_PUSH_FRAME: {
-        LsState adj = adjustedPushFrame(*m, index, delta);
-        if (m->ls.frameletOrient) {  // per-framelet orientations of the adjusted model
-          e = cudaMallocAsync(&pfTable, (size_t)(adj.numFramelets + 2) * kFrameletOrientDoubles * sizeof(double), stream);
-          if (e == cudaSuccess) e = launchPfFrameletOrientations(adj, pfTable, stream);
-          adj.frameletOrient = pfTable;
-        }
-        if (e == cudaSuccess)
-          e = launchPfGroundToImage(adj, m->smCount, n, x, y, z, prec, l1, s1, achieved, st1, stream);
-      } break;
-      case USGSCSM_B200_MODEL_FRAME:
-        e = launchFrGroundToImage(adjustedFrame(*m, index, delta), m->smCount, n, x, y, z, prec, l1,
-                                  s1, achieved, st1, stream);
-        break;
-      default:
-        e = launchSarGroundToImage(adjustedSar(*m, index, delta), m->smCount, n, x, y, z, prec, l1,
-                                   s1, achieved, st1, stream);
-        break;
-    }
-  }
+  if (e == cudaSuccess)
+    e = launchAdjustedGroundToImage(m, index, delta, n, x, y, z, prec, l1, s1, achieved, st1,
+                                    stream, &pfTable);
   if (e == cudaSuccess)
     e = launchSensorPartialsCombine(n, haveImage ? img_line : l0, haveImage ? img_samp : s0,
                                     haveImage ? nullptr : st0, l1, s1, delta, dline, dsamp,
@@ -531,6 +542,60 @@ int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
   cudaFreeAsync(stScratch, stream);
   if (pfTable) cudaFreeAsync(pfTable, stream);
   UB_CUDA(e);
+  return USGSCSM_B200_OK;
+}
+
+// computeAllSensorPartials (csm/RasterGM.cpp:52-140 through LS:1413-1455, PF:1170-1201,
+// FR:894-940): the image point once (unless supplied), then one adjusted search per requested
+// parameter, all against that image point; achieved precision = the largest over the
+// parameters starting from 0, warnings of every search accumulate.  partials: per point,
+// per requested parameter, (dline, dsamp).
+int allSensorPartialsDev(usgscsm_b200_model *m, int n_indices, const int *indices, long n,
+                         const double *x, const double *y, const double *z,
+                         const double *img_line, const double *img_samp, double prec,
+                         double *partials, double *achieved, uint32_t *status,
+                         cudaStream_t stream) {
+  const bool haveImage = img_line && img_samp;
+  double *scratch = nullptr;
+  uint32_t *stScratch = nullptr;
+  std::vector<double *> pfTables;
+  UB_CUDA(cudaMallocAsync(&scratch, (size_t)n * 5 * sizeof(double), stream));
+  UB_CUDA(cudaMallocAsync(&stScratch, (size_t)n * 3 * sizeof(uint32_t), stream));
+  double *l0 = scratch, *s0 = scratch + n, *l1 = scratch + 2 * n, *s1 = scratch + 3 * n,
+         *achP = scratch + 4 * n;
+  uint32_t *st0 = stScratch, *stP = stScratch + n, *acc = status ? status : stScratch + 2 * n;
+  cudaError_t e = cudaSuccess;
+  if (!haveImage)
+    e = launchGroundToImage(*m, n, x, y, z, prec, l0, s0, nullptr, st0, stream);
+  for (int k = 0; k < n_indices && e == cudaSuccess; k++) {
+    const int index = indices ? indices[k] : k;
+    const double delta = sensorPartialDelta(m, index);
+    double *pfTable = nullptr;
+    e = launchAdjustedGroundToImage(m, index, delta, n, x, y, z, prec, l1, s1, achP, stP, stream,
+                                    &pfTable);
+    if (pfTable) pfTables.push_back(pfTable);
+    if (e == cudaSuccess)
+      e = launchSensorPartialsStep(n, haveImage ? img_line : l0, haveImage ? img_samp : s0,
+                                   haveImage ? nullptr : st0, l1, s1, achP, stP, delta, partials,
+                                   n_indices, k, achieved, acc, stream);
+  }
+  cudaFreeAsync(scratch, stream);
+  cudaFreeAsync(stScratch, stream);
+  for (double *t : pfTables) cudaFreeAsync(t, stream);
+  UB_CUDA(e);
+  return USGSCSM_B200_OK;
+}
+
+int allSensorPartialsCheck(usgscsm_b200_model *m, int n_indices, const int *indices, int64_t n,
+                           const void *x, const void *y, const void *z, const void *partials) {
+  if (!m || n < 0 || n_indices < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (!indices && n_indices != (int)m->params.size())
+    return fail(USGSCSM_B200_EINVAL, "without an index list n_indices must be the parameter count");
+  for (int k = 0; indices && k < n_indices; k++)
+    if (indices[k] < 0 || indices[k] >= (int)m->params.size())
+      return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
+  if (n > 0 && n_indices > 0 && (!x || !y || !z || !partials))
+    return fail(USGSCSM_B200_EINVAL, "null array");
   return USGSCSM_B200_OK;
 }
 
@@ -559,6 +624,20 @@ int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int index, int64_t n
     UB_CUDA(cudaSetDevice(m->device));
     return sensorPartialsDev(m, index, (long)n, x, y, z, img_line, img_samp, prec, dline, dsamp,
                              achieved, status, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int usgscsm_b200_all_sensor_partials_dev(usgscsm_b200_model *m, int n_indices, const int *indices,
+                                         int64_t n, const double *x, const double *y,
+                                         const double *z, const double *img_line,
+                                         const double *img_samp, double prec, double *partials,
+                                         double *achieved, uint32_t *status, void *stream) {
+  int c = allSensorPartialsCheck(m, n_indices, indices, n, x, y, z, partials);
+  if (c != USGSCSM_B200_OK || n == 0 || n_indices == 0) return c;
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    return allSensorPartialsDev(m, n_indices, indices, (long)n, x, y, z, img_line, img_samp, prec,
+                                partials, achieved, status, static_cast<cudaStream_t>(stream));
   });
 }
 

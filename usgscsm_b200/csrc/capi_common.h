@@ -66,5 +66,13 @@ int sensorPartialsDev(usgscsm_b200_model *m, int index, long n, const double *x,
 int sensorPartialsCheck(usgscsm_b200_model *m, int index, int64_t n, const void *x, const void *y,
                         const void *z, const void *dline, const void *dsamp);
 
+int allSensorPartialsDev(usgscsm_b200_model *m, int n_indices, const int *indices, long n,
+                         const double *x, const double *y, const double *z,
+                         const double *img_line, const double *img_samp, double prec,
+                         double *partials, double *achieved, uint32_t *status,
+                         cudaStream_t stream);
+int allSensorPartialsCheck(usgscsm_b200_model *m, int n_indices, const int *indices, int64_t n,
+                           const void *x, const void *y, const void *z, const void *partials);
+
 }  // namespace ub200
 #endif

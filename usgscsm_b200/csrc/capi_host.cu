@@ -274,6 +274,28 @@ int usgscsm_b200_sensor_partials(usgscsm_b200_model *m, int index, int64_t n, co
                       });
 }
 
+int usgscsm_b200_all_sensor_partials(usgscsm_b200_model *m, int n_indices, const int *indices,
+                                     int64_t n, const double *x, const double *y, const double *z,
+                                     const double *img_line, const double *img_samp, double prec,
+                                     double *partials, double *achieved, uint32_t *status) {
+  int c = allSensorPartialsCheck(m, n_indices, indices, n, x, y, z, partials);
+  if (c != USGSCSM_B200_OK || n == 0 || n_indices == 0) return c;
+  const bool haveImage = img_line && img_samp;
+  std::vector<HostIn> ins = {{x, 1, false}, {y, 1, false}, {z, 1, false}};
+  if (haveImage) {
+    ins.push_back({img_line, 1, false});
+    ins.push_back({img_samp, 1, false});
+  }
+  return runPipelined(m, n, ins, {{partials, 2 * n_indices}, {achieved, 1}}, status, 0,
+                      [&](const Chunk &k) {
+                        allSensorPartialsDev(m, n_indices, indices, k.count, k.in[0], k.in[1],
+                                             k.in[2], haveImage ? k.in[3] : nullptr,
+                                             haveImage ? k.in[4] : nullptr, prec, k.out[0],
+                                             k.out[1], k.status, k.stream);
+                        return cudaSuccess;  // throws CudaError on failure
+                      });
+}
+
 }  // extern "C"
 
 // ---- several GPUs from one process -----------------------------------------------------------

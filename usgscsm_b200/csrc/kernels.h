@@ -164,6 +164,11 @@ cudaError_t launchSensorPartialsCombine(long n, const double *l0, const double *
                                         const uint32_t *st0, const double *l1, const double *s1,
                                         double delta, double *dline, double *dsamp,
                                         double *achieved, uint32_t *status, cudaStream_t stream);
+cudaError_t launchSensorPartialsStep(long n, const double *l0, const double *s0,
+                                     const uint32_t *st0, const double *l1, const double *s1,
+                                     const double *achP, const uint32_t *stP, double delta,
+                                     double *partials, int numParams, int k, double *achieved,
+                                     uint32_t *status, cudaStream_t stream);
 cudaError_t launchReciprocals(int n, const double *b, double *r, cudaStream_t stream);
 cudaError_t launchDivisionSelfTest(unsigned long long seed, int blocks, long perThread,
                                    unsigned long long *mismatches, cudaStream_t stream);

@@ -330,6 +330,41 @@ class RasterGM(object):
             desiredPrecision, _ptr(dl), _ptr(ds), _ptr(ach), _ptr(st)))
         return dl, ds, ach, st
 
+    def computeAllSensorPartialsBatch(self, x, y, z, desiredPrecision=0.001, imagePts=None,
+                                      indices=None):
+        """csm::RasterGM::computeAllSensorPartials for arrays: returns ((n, P, 2) partials --
+        (dLine, dSamp) per requested parameter --, achieved, status).  `indices` = the parameter
+        indices of a csm::param::Set (default: all parameters); `imagePts` = (line, samp)
+        arrays selects the overload that takes the image point."""
+        il, isamp = (None, None) if imagePts is None else imagePts
+        if indices is None:
+            npar, idx = self.getNumParameters(), None
+        else:
+            npar = len(indices)
+            idx = (C.c_int * max(npar, 1))(*[int(i) for i in indices])
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            p = torch.empty((n, npar, 2), dtype=torch.float64, device=x.device)
+            ach = torch.empty_like(x)
+            st = torch.empty(n, dtype=torch.int32, device=x.device)
+            stream = torch.cuda.current_stream(x.device).cuda_stream
+            check(lib.usgscsm_b200_all_sensor_partials_dev(
+                self._h, npar, idx, n, _ptr(x), _ptr(y), _ptr(z), _ptr(il), _ptr(isamp),
+                desiredPrecision, _ptr(p), _ptr(ach), _ptr(st), stream))
+            return p, ach, st
+        x = _host(x)
+        n = x.size
+        y, z = _host(y, n), _host(z, n)
+        if il is not None:
+            il, isamp = _host(il, n), _host(isamp, n)
+        p, ach = np.empty((n, npar, 2)), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_all_sensor_partials(
+            self._h, npar, idx, n, _ptr(x), _ptr(y), _ptr(z), _ptr(il), _ptr(isamp),
+            desiredPrecision, _ptr(p), _ptr(ach), _ptr(st)))
+        return p, ach, st
+
     def computeGroundPartials(self, groundPt):
         """csm::RasterGM::computeGroundPartials (one point): a list of six partials."""
         p, st = self.computeGroundPartialsBatch([groundPt[0]], [groundPt[1]], [groundPt[2]])
