@@ -273,6 +273,48 @@ USGSCSM_B200_API int usgscsm_b200_all_sensor_partials_dev(usgscsm_b200_model *m,
                                          double desired_precision, double *partials,
                                          double *achieved, uint32_t *status, void *stream);
 
+/* ---- error propagation -------------------------------------------------------------------
+ * groundToImage(const csm::EcefCoordCovar&, prec, *ach, *warn) -> csm::ImageCoordCovar and
+ * imageToGround(const csm::ImageCoordCovar&, height, heightVariance, prec, *ach, *warn) ->
+ * csm::EcefCoordCovar of the line-scan, push-frame and SAR models (LS:910-964 / 1075-1157,
+ * PF:784-840 / 909-990, SAR:709-758 / 864-940).  ground_cov: 9 doubles per point (row-major
+ * 3x3, csm::EcefCoordCovar::covariance), image_cov: 4 doubles per point (2x2,
+ * csm::ImageCoordCovar::covariance).  The sensor term uses the model's parameter covariance
+ * (m_covariance of the state, usgscsm_b200_model_set_parameter_covariance) and all sensor
+ * partials at the default precision 0.001, as determineSensorCovarianceInImageSpace does
+ * (LS:1025-1054).  status carries the warnings of the plain projection; an error bit means one
+ * of the scalar calls inside would have thrown, and every output of the point is NaN.  The
+ * frame model's overloads are stubs in the reference (FR:234-278, 374-395):
+ * USGSCSM_B200_EUNSUPPORTED. */
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_covar(usgscsm_b200_model *m, int64_t n, const double *x,
+                                       const double *y, const double *z, const double *ground_cov,
+                                       double desired_precision, double *line, double *samp,
+                                       double *image_cov, double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_covar_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+                                           const double *y, const double *z,
+                                           const double *ground_cov, double desired_precision,
+                                           double *line, double *samp, double *image_cov,
+                                           double *achieved, uint32_t *status, void *stream);
+/* height_stride / variance_stride: 0 = one value for all points, otherwise one per point. */
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_covar(usgscsm_b200_model *m, int64_t n, const double *line,
+                                       const double *samp, const double *image_cov,
+                                       const double *height, int height_stride,
+                                       const double *height_variance, int variance_stride,
+                                       double desired_precision, double *x, double *y, double *z,
+                                       double *ground_cov, double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_covar_dev(usgscsm_b200_model *m, int64_t n, const double *line,
+                                           const double *samp, const double *image_cov,
+                                           const double *height, int height_stride,
+                                           const double *height_variance, int variance_stride,
+                                           double desired_precision, double *x, double *y,
+                                           double *z, double *ground_cov, double *achieved,
+                                           uint32_t *status, void *stream);
+/* getParameterCovariance / setParameterCovariance (LS:1468-1497, PF:1207-1230, SAR:1604-1623) */
+USGSCSM_B200_API int usgscsm_b200_model_get_parameter_covariance(const usgscsm_b200_model *m, int index1,
+                                                int index2, double *value);
+USGSCSM_B200_API int usgscsm_b200_model_set_parameter_covariance(usgscsm_b200_model *m, int index1, int index2,
+                                                double value);
+
 /* Several GPUs from one process (row-band / chunk sharding, no exchange step): models[g] are
  * the SAME model state loaded on n_models different devices; contiguous chunk g of the host
  * arrays (sizes differ by at most one point) is processed on models[g], all concurrently.

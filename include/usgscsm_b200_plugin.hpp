@@ -22,6 +22,7 @@
 #include <cstdint>
 #include <exception>
 #include <list>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -49,6 +50,21 @@ struct EcefCoord {  // csm/csm.h:292-308
   double x, y, z;
   EcefCoord() : x(0.0), y(0.0), z(0.0) {}
   EcefCoord(double aX, double aY, double aZ) : x(aX), y(aY), z(aZ) {}
+};
+
+struct ImageCoordCovar : public ImageCoord {  // csm/csm.h:228-256
+  double covariance[4];                        // 2x2, row-major
+  ImageCoordCovar() : ImageCoord() { std::fill(covariance, covariance + 4, 0.0); }
+  ImageCoordCovar(double aLine, double aSamp) : ImageCoord(aLine, aSamp) {
+    std::fill(covariance, covariance + 4, 0.0);
+  }
+};
+struct EcefCoordCovar : public EcefCoord {  // csm/csm.h:310-358
+  double covariance[9];                      // 3x3, row-major
+  EcefCoordCovar() : EcefCoord() { std::fill(covariance, covariance + 9, 0.0); }
+  EcefCoordCovar(double aX, double aY, double aZ) : EcefCoord(aX, aY, aZ) {
+    std::fill(covariance, covariance + 9, 0.0);
+  }
 };
 
 struct EcefLocus {  // csm/csm.h:420-445
@@ -281,6 +297,69 @@ class RasterGM {
                                            indices, (int64_t)n, x, y, z, imgLine, imgSamp,
                                            desiredPrecision, partials, achievedPrecision, status),
           "computeAllSensorPartialsBatch");
+  }
+  // ---- error propagation (LS:910-964 / 1075-1157, PF:784-840 / 909-990, SAR:709-758 / 864-940)
+  double getParameterCovariance(int index1, int index2) const {
+    double v = 0.0;
+    check(usgscsm_b200_model_get_parameter_covariance(m_h, index1, index2, &v),
+          "getParameterCovariance");
+    return v;
+  }
+  void setParameterCovariance(int index1, int index2, double covariance) {
+    check(usgscsm_b200_model_set_parameter_covariance(m_h, index1, index2, covariance),
+          "setParameterCovariance");
+  }
+  csm::ImageCoordCovar groundToImage(const csm::EcefCoordCovar &groundPt,
+                                     double desiredPrecision = 0.001,
+                                     double *achievedPrecision = NULL,
+                                     csm::WarningList *warnings = NULL) const {
+    csm::ImageCoordCovar r;
+    double a = 0;
+    uint32_t st = 0;
+    check(usgscsm_b200_ground_to_image_covar(m_h, 1, &groundPt.x, &groundPt.y, &groundPt.z,
+                                             groundPt.covariance, desiredPrecision, &r.line,
+                                             &r.samp, r.covariance, &a, &st),
+          "groundToImage");
+    raiseOrWarn(st, warnings, "groundToImage");
+    if (achievedPrecision) *achievedPrecision = a;
+    return r;
+  }
+  csm::EcefCoordCovar imageToGround(const csm::ImageCoordCovar &imagePt, double height,
+                                    double heightVariance, double desiredPrecision = 0.001,
+                                    double *achievedPrecision = NULL,
+                                    csm::WarningList *warnings = NULL) const {
+    csm::EcefCoordCovar r;
+    double a = 0;
+    uint32_t st = 0;
+    check(usgscsm_b200_image_to_ground_covar(m_h, 1, &imagePt.line, &imagePt.samp,
+                                             imagePt.covariance, &height, 0, &heightVariance, 0,
+                                             desiredPrecision, &r.x, &r.y, &r.z, r.covariance, &a,
+                                             &st),
+          "imageToGround");
+    raiseOrWarn(st, warnings, "imageToGround");
+    if (achievedPrecision) *achievedPrecision = a;
+    return r;
+  }
+  // whole arrays: groundCov 9 doubles per point, imageCov 4 doubles per point
+  void groundToImageCovarBatch(size_t n, const double *x, const double *y, const double *z,
+                               const double *groundCov, double desiredPrecision, double *line,
+                               double *samp, double *imageCov, double *achievedPrecision = NULL,
+                               uint32_t *status = NULL) const {
+    check(usgscsm_b200_ground_to_image_covar(m_h, (int64_t)n, x, y, z, groundCov, desiredPrecision,
+                                             line, samp, imageCov, achievedPrecision, status),
+          "groundToImageCovarBatch");
+  }
+  void imageToGroundCovarBatch(size_t n, const double *line, const double *samp,
+                               const double *imageCov, const double *height, bool perPointHeight,
+                               const double *heightVariance, bool perPointVariance,
+                               double desiredPrecision, double *x, double *y, double *z,
+                               double *groundCov, double *achievedPrecision = NULL,
+                               uint32_t *status = NULL) const {
+    check(usgscsm_b200_image_to_ground_covar(m_h, (int64_t)n, line, samp, imageCov, height,
+                                             perPointHeight ? 1 : 0, heightVariance,
+                                             perPointVariance ? 1 : 0, desiredPrecision, x, y, z,
+                                             groundCov, achievedPrecision, status),
+          "imageToGroundCovarBatch");
   }
   // csm::SettableEllipsoid (LS:2116-2119)
   void setEllipsoid(double semiMajorRadius, double semiMinorRadius) {

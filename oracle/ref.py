@@ -47,6 +47,10 @@ def lib():
         L.ref_proximate_locus.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 8 + [C.c_int]
         L.ref_sensor_partials.argtypes = [C.c_void_p, C.c_int, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 4 + [C.c_int]
         L.ref_all_sensor_partials.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 3 + [C.c_int]
+        L.ref_set_parameter_covariance.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+        L.ref_ground_to_image_covar.argtypes = [C.c_void_p, C.c_long] + [_dp] * 4 + [C.c_double] + [_dp] * 5 + [C.c_int]
+        L.ref_image_to_ground_covar.argtypes = ([C.c_void_p, C.c_long] + [_dp] * 4 + [C.c_int, _dp, C.c_int, C.c_double]
+                                                + [_dp] * 6 + [C.c_int])
         L.ref_ground_partials.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_set_ellipsoid.argtypes = [C.c_void_p, C.c_double, C.c_double]
         L.ref_lagrange.argtypes = [C.c_int, _dp, C.c_double, C.c_double, C.c_double, C.c_int,
@@ -195,6 +199,37 @@ class RefModel(object):
         if got != num_params:
             raise RuntimeError("the reference model has %d parameters, not %d" % (got, num_params))
         return p, ach, st
+
+    def set_parameter_covariance(self, i, j, v):
+        self._L.ref_set_parameter_covariance(self._h, int(i), int(j), float(v))
+
+    def ground_to_image_covar(self, x, y, z, ground_cov, prec=0.001, threads=1):
+        """groundToImage(EcefCoordCovar) per point -> (line, samp, (n, 4) cov, achieved, status)."""
+        x = _a(x)
+        n = x.size
+        y, z = _a(y, n), _a(z, n)
+        gc = np.ascontiguousarray(np.asarray(ground_cov, dtype=np.float64).reshape(n, 9))
+        line, samp, ach, ic = np.empty(n), np.empty(n), np.empty(n), np.empty((n, 4))
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_ground_to_image_covar(self._h, n, x.ctypes.data, y.ctypes.data, z.ctypes.data,
+                                          gc.ctypes.data, prec, line.ctypes.data, samp.ctypes.data,
+                                          ic.ctypes.data, ach.ctypes.data, st.ctypes.data, threads)
+        return line, samp, ic, ach, st
+
+    def image_to_ground_covar(self, line, samp, image_cov, height, height_var, prec=0.001, threads=1):
+        """imageToGround(ImageCoordCovar, h, hVar) per point -> (x, y, z, (n, 9) cov, achieved, status)."""
+        line = _a(line)
+        n = line.size
+        samp = _a(samp, n)
+        ic = np.ascontiguousarray(np.asarray(image_cov, dtype=np.float64).reshape(n, 4))
+        h, hv = _a(height, n), _a(height_var, n)
+        x, y, z, ach, gc = np.empty(n), np.empty(n), np.empty(n), np.empty(n), np.empty((n, 9))
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_image_to_ground_covar(self._h, n, line.ctypes.data, samp.ctypes.data, ic.ctypes.data,
+                                          h.ctypes.data, 1, hv.ctypes.data, 1, prec, x.ctypes.data,
+                                          y.ctypes.data, z.ctypes.data, gc.ctypes.data, ach.ctypes.data,
+                                          st.ctypes.data, threads)
+        return x, y, z, gc, ach, st
 
     def ground_partials(self, x, y, z, threads=1):
         """computeGroundPartials per point -> ((n, 6) partials, status)."""

@@ -420,6 +420,103 @@ int ref_all_sensor_partials(void *h, long n, const double *x, const double *y, c
   return np;
 }
 
+// setParameterCovariance
+int ref_set_parameter_covariance(void *h, int i, int j, double v) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  rm->gm->setParameterCovariance(i, j, v);
+  return 0;
+}
+
+// groundToImage(EcefCoordCovar): ground_cov 9 per point -> line, samp, image_cov 4 per point
+int ref_ground_to_image_covar(void *h, long n, const double *x, const double *y, const double *z,
+                              const double *ground_cov, double prec, double *line, double *samp,
+                              double *image_cov, double *achieved, uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const std::pair<csm::ImageCoord, csm::ImageCoord> range = gm->getValidImageRange();
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    csm::ImageCoordCovar r(std::nan(""), std::nan(""));
+    for (int k = 0; k < 4; k++) r.covariance[k] = std::nan("");
+    try {
+      csm::WarningList warn;
+      csm::EcefCoordCovar g(x[i], y[i], z[i]);
+      for (int k = 0; k < 9; k++) g.covariance[k] = ground_cov[i * 9 + k];
+      r = gm->groundToImage(g, prec, &ach, &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+      ach = std::nan("");
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+      ach = std::nan("");
+    }
+    bool finite = true;
+    for (int k = 0; k < 4; k++) {
+      image_cov[i * 4 + k] = r.covariance[k];
+      finite = finite && std::isfinite(r.covariance[k]);
+    }
+    if (!finite || !(std::isfinite(r.line) && std::isfinite(r.samp))) st |= ST_NONFINITE;
+    if (!(r.line >= range.first.line && r.line <= range.second.line &&
+          r.samp >= range.first.samp && r.samp <= range.second.samp))
+      st |= ST_OUT_OF_IMAGE;  // derived, as in ref_ground_to_image
+    line[i] = r.line;
+    samp[i] = r.samp;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
+// imageToGround(ImageCoordCovar, height, heightVariance)
+int ref_image_to_ground_covar(void *h, long n, const double *line, const double *samp,
+                              const double *image_cov, const double *height, int height_stride,
+                              const double *height_var, int var_stride, double prec, double *x,
+                              double *y, double *z, double *ground_cov, double *achieved,
+                              uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double ach = std::nan("");
+    csm::EcefCoordCovar r(std::nan(""), std::nan(""), std::nan(""));
+    for (int k = 0; k < 9; k++) r.covariance[k] = std::nan("");
+    try {
+      csm::WarningList warn;
+      csm::ImageCoordCovar p(line[i], samp[i]);
+      for (int k = 0; k < 4; k++) p.covariance[k] = image_cov[i * 4 + k];
+      r = gm->imageToGround(p, height[i * height_stride], height_var[i * var_stride], prec, &ach,
+                            &warn);
+      st |= bitsFromWarnings(warn);
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+      ach = std::nan("");
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+      ach = std::nan("");
+    }
+    bool finite = true;
+    for (int k = 0; k < 9; k++) {
+      ground_cov[i * 9 + k] = r.covariance[k];
+      finite = finite && std::isfinite(r.covariance[k]);
+    }
+    if (!finite || !(std::isfinite(r.x) && std::isfinite(r.y) && std::isfinite(r.z))) st |= ST_NONFINITE;
+    x[i] = r.x;
+    y[i] = r.y;
+    z[i] = r.z;
+    if (achieved) achieved[i] = ach;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
 // computeGroundPartials over n points; partials = 6 doubles per point (LS:1299-1325 etc.).
 int ref_ground_partials(void *h, long n, const double *x, const double *y, const double *z,
                         double *partials, uint32_t *status, int threads) {

@@ -2,6 +2,7 @@
 and, for the line-scan groundToImage kernel, into profiles/ncu_g2i.json (the DRAM traffic
 bench.py reports as roofline.traffic).  Usage:
     python profiles/summarize_ncu.py gpurun_out/r1_g2i_full.ncu-rep POINTS "capture note" [--json]
+(POINTS = 0 for a report holding launches of different sizes: no per-point line.)
 Runs on the CPU box: `ncu -i` only reads the report."""
 import csv
 import io
@@ -54,7 +55,8 @@ def main():
         scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
         rd = float(v["dram__bytes_read.sum"]) * scale[u["dram__bytes_read.sum"]]
         wr = float(v["dram__bytes_write.sum"]) * scale[u["dram__bytes_write.sum"]]
-        print("DRAM bytes per point: %.2f read + %.2f written = %.2f" % (rd / points, wr / points, (rd + wr) / points))
+        if points > 0:
+            print("DRAM bytes per point: %.2f read + %.2f written = %.2f" % (rd / points, wr / points, (rd + wr) / points))
         if "--json" in sys.argv:
             with open("profiles/ncu_g2i.json", "w") as f:
                 json.dump({"kernel": v["Kernel Name"], "points": points, "dram_bytes_read": rd,

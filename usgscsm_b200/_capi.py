@@ -87,6 +87,19 @@ SIGNATURES = {
     "usgscsm_b200_all_sensor_partials_dev": (
         C.c_int, [_h, C.c_int, C.POINTER(C.c_int), C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double,
                   _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_covar": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_covar_dev": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_covar": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, C.c_int, _dp, C.c_int, C.c_double, _dp, _dp,
+                  _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_covar_dev": (
+        C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, C.c_int, _dp, C.c_int, C.c_double, _dp, _dp,
+                  _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_model_get_parameter_covariance": (
+        C.c_int, [_h, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "usgscsm_b200_model_set_parameter_covariance": (C.c_int, [_h, C.c_int, C.c_int, C.c_double]),
     "usgscsm_b200_ground_to_image_multi": (
         C.c_int, [C.POINTER(_h), C.c_int, C.c_int64, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_image_to_ground_multi": (

@@ -74,5 +74,17 @@ int allSensorPartialsDev(usgscsm_b200_model *m, int n_indices, const int *indice
 int allSensorPartialsCheck(usgscsm_b200_model *m, int n_indices, const int *indices, int64_t n,
                            const void *x, const void *y, const void *z, const void *partials);
 
+// covar.cu
+int covarCheck(const usgscsm_b200_model *m, int64_t n);
+int groundToImageCovarDev(usgscsm_b200_model *m, long n, const double *x, const double *y,
+                          const double *z, const double *groundCov, double prec, double *line,
+                          double *samp, double *imageCov, double *achieved, uint32_t *status,
+                          cudaStream_t stream);
+int imageToGroundCovarDev(usgscsm_b200_model *m, long n, const double *line, const double *samp,
+                          const double *imageCov, const double *height, int heightStride,
+                          const double *heightVar, int hvStride, double prec, double *x, double *y,
+                          double *z, double *groundCov, double *achieved, uint32_t *status,
+                          cudaStream_t stream);
+
 }  // namespace ub200
 #endif

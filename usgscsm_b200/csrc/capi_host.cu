@@ -296,6 +296,48 @@ int usgscsm_b200_all_sensor_partials(usgscsm_b200_model *m, int n_indices, const
                       });
 }
 
+// Error propagation (covar.cu): the covariances travel as arrays of 9 / 4 doubles per point.
+int usgscsm_b200_ground_to_image_covar(usgscsm_b200_model *m, int64_t n, const double *x,
+                                       const double *y, const double *z, const double *ground_cov,
+                                       double prec, double *line, double *samp, double *image_cov,
+                                       double *achieved, uint32_t *status) {
+  int c = covarCheck(m, n);
+  if (c != USGSCSM_B200_OK || n == 0) return c;
+  if (!x || !y || !z || !ground_cov || !line || !samp || !image_cov)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{x, 1, false}, {y, 1, false}, {z, 1, false}, {ground_cov, 9, false}},
+                      {{line, 1}, {samp, 1}, {image_cov, 4}, {achieved, 1}}, status, 1,
+                      [&](const Chunk &k) {
+                        uint32_t *st = k.status ? k.status : reinterpret_cast<uint32_t *>(k.work[0]);
+                        groundToImageCovarDev(m, k.count, k.in[0], k.in[1], k.in[2], k.in[3], prec,
+                                              k.out[0], k.out[1], k.out[2], k.out[3], st, k.stream);
+                        return cudaSuccess;  // throws CudaError on failure
+                      });
+}
+
+int usgscsm_b200_image_to_ground_covar(usgscsm_b200_model *m, int64_t n, const double *line,
+                                       const double *samp, const double *image_cov,
+                                       const double *height, int height_stride,
+                                       const double *height_variance, int variance_stride,
+                                       double prec, double *x, double *y, double *z,
+                                       double *ground_cov, double *achieved, uint32_t *status) {
+  int c = covarCheck(m, n);
+  if (c != USGSCSM_B200_OK || n == 0) return c;
+  if (!line || !samp || !image_cov || !height || !height_variance || !x || !y || !z || !ground_cov)
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  const int hs = height_stride ? 1 : 0, vs = variance_stride ? 1 : 0;
+  return runPipelined(
+      m, n,
+      {{line, 1, false}, {samp, 1, false}, {image_cov, 4, false}, {height, 1, hs == 0},
+       {height_variance, 1, vs == 0}},
+      {{x, 1}, {y, 1}, {z, 1}, {ground_cov, 9}, {achieved, 1}}, status, 1, [&](const Chunk &k) {
+        uint32_t *st = k.status ? k.status : reinterpret_cast<uint32_t *>(k.work[0]);
+        imageToGroundCovarDev(m, k.count, k.in[0], k.in[1], k.in[2], k.in[3], hs, k.in[4], vs, prec,
+                              k.out[0], k.out[1], k.out[2], k.out[3], k.out[4], st, k.stream);
+        return cudaSuccess;
+      });
+}
+
 }  // extern "C"
 
 // ---- several GPUs from one process -----------------------------------------------------------

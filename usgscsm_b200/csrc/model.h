@@ -75,6 +75,7 @@ struct Model {
   std::vector<double> scaleCoeffs, scaleTimes;
 
   std::vector<double> params;  // m_currentParameterValue (raw, without the +0.0)
+  std::vector<double> covariance;  // m_covariance, numParams x numParams (error propagation only)
 
   // ---- device side ---------------------------------------------------------------------
   std::vector<DeviceBuffer> owned;

@@ -365,6 +365,83 @@ class RasterGM(object):
             desiredPrecision, _ptr(p), _ptr(ach), _ptr(st)))
         return p, ach, st
 
+    # ---- error propagation (csm::EcefCoordCovar / csm::ImageCoordCovar overloads) -------------
+    def getParameterCovariance(self, index1, index2):
+        v = C.c_double()
+        check(lib.usgscsm_b200_model_get_parameter_covariance(self._h, int(index1), int(index2),
+                                                              C.byref(v)))
+        return v.value
+
+    def setParameterCovariance(self, index1, index2, covariance):
+        check(lib.usgscsm_b200_model_set_parameter_covariance(self._h, int(index1), int(index2),
+                                                              float(covariance)))
+
+    def groundToImageCovarBatch(self, x, y, z, groundCov, desiredPrecision=0.001):
+        """groundToImage(csm::EcefCoordCovar) for arrays: groundCov (n, 9) row-major 3x3 ->
+        (line, samp, imageCov (n, 4), achieved, status)."""
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            line, samp, ach = (torch.empty_like(x) for _ in range(3))
+            icov = torch.empty((n, 4), dtype=torch.float64, device=x.device)
+            st = torch.empty(n, dtype=torch.int32, device=x.device)
+            check(lib.usgscsm_b200_ground_to_image_covar_dev(
+                self._h, n, _ptr(x), _ptr(y), _ptr(z), _ptr(groundCov.contiguous()),
+                desiredPrecision, _ptr(line), _ptr(samp), _ptr(icov), _ptr(ach), _ptr(st),
+                torch.cuda.current_stream(x.device).cuda_stream))
+            return line, samp, icov, ach, st
+        x = _host(x)
+        n = x.size
+        y, z = _host(y, n), _host(z, n)
+        gcov = np.ascontiguousarray(np.broadcast_to(np.asarray(groundCov, dtype=np.float64).reshape(-1, 9), (n, 9)))
+        line, samp, ach, icov = np.empty(n), np.empty(n), np.empty(n), np.empty((n, 4))
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_ground_to_image_covar(
+            self._h, n, _ptr(x), _ptr(y), _ptr(z), _ptr(gcov), desiredPrecision, _ptr(line),
+            _ptr(samp), _ptr(icov), _ptr(ach), _ptr(st)))
+        return line, samp, icov, ach, st
+
+    def imageToGroundCovarBatch(self, line, samp, imageCov, height, heightVariance,
+                                desiredPrecision=0.001):
+        """imageToGround(csm::ImageCoordCovar, height, heightVariance) for arrays: imageCov
+        (n, 4); height / heightVariance scalars or per-point arrays ->
+        (x, y, z, groundCov (n, 9), achieved, status)."""
+        if _is_torch(line):
+            import torch
+            n = line.numel()
+            dev = line.device
+
+            def per_point(v):
+                if _is_torch(v):
+                    return v.contiguous(), (1 if v.numel() > 1 or n == 1 else 0)
+                return torch.full((1,), float(v), dtype=torch.float64, device=dev), 0
+            h, hs = per_point(height)
+            hv, vs = per_point(heightVariance)
+            x, y, z, ach = (torch.empty_like(line) for _ in range(4))
+            gcov = torch.empty((n, 9), dtype=torch.float64, device=dev)
+            st = torch.empty(n, dtype=torch.int32, device=dev)
+            check(lib.usgscsm_b200_image_to_ground_covar_dev(
+                self._h, n, _ptr(line), _ptr(samp), _ptr(imageCov.contiguous()), _ptr(h), hs,
+                _ptr(hv), vs, desiredPrecision, _ptr(x), _ptr(y), _ptr(z), _ptr(gcov), _ptr(ach),
+                _ptr(st), torch.cuda.current_stream(dev).cuda_stream))
+            return x, y, z, gcov, ach, st
+        line = _host(line)
+        n = line.size
+        samp = _host(samp, n)
+        icov = np.ascontiguousarray(np.broadcast_to(np.asarray(imageCov, dtype=np.float64).reshape(-1, 4), (n, 4)))
+        h = np.ascontiguousarray(np.atleast_1d(np.asarray(height, dtype=np.float64)))
+        hv = np.ascontiguousarray(np.atleast_1d(np.asarray(heightVariance, dtype=np.float64)))
+        for a in (h, hv):
+            if a.size not in (1, n):
+                raise ValueError("height / heightVariance must hold 1 or n entries")
+        x, y, z, ach, gcov = np.empty(n), np.empty(n), np.empty(n), np.empty(n), np.empty((n, 9))
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_image_to_ground_covar(
+            self._h, n, _ptr(line), _ptr(samp), _ptr(icov), _ptr(h), 1 if h.size == n else 0,
+            _ptr(hv), 1 if hv.size == n else 0, desiredPrecision, _ptr(x), _ptr(y), _ptr(z),
+            _ptr(gcov), _ptr(ach), _ptr(st)))
+        return x, y, z, gcov, ach, st
+
     def computeGroundPartials(self, groundPt):
         """csm::RasterGM::computeGroundPartials (one point): a list of six partials."""
         p, st = self.computeGroundPartialsBatch([groundPt[0]], [groundPt[1]], [groundPt[2]])
