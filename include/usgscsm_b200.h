@@ -273,6 +273,21 @@ USGSCSM_B200_API int usgscsm_b200_all_sensor_partials_dev(usgscsm_b200_model *m,
                                          double desired_precision, double *partials,
                                          double *achieved, uint32_t *status, void *stream);
 
+/* getImageTime(ImageCoord), getSensorPosition(ImageCoord) and getSensorVelocity(ImageCoord)
+ * for arrays (LS:1543-1653, PF:1258-1320, FR:665-765, SAR:1113-1238): the model-relative
+ * image time and the sensor's ECEF position / velocity at it, with the model's current
+ * parameter values.  Every output array may be NULL.  status: USGSCSM_B200_ST_ERROR_OTHER where
+ * the scalar call throws csm::Error::BOUNDS (frame model, velocity of a point outside the
+ * image, FR:754-760). */
+USGSCSM_B200_API int usgscsm_b200_image_sensor_state(usgscsm_b200_model *m, int64_t n, const double *line,
+                                    const double *samp, double *time, double *px, double *py,
+                                    double *pz, double *vx, double *vy, double *vz,
+                                    uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_sensor_state_dev(usgscsm_b200_model *m, int64_t n, const double *line,
+                                        const double *samp, double *time, double *px, double *py,
+                                        double *pz, double *vx, double *vy, double *vz,
+                                        uint32_t *status, void *stream);
+
 /* ---- error propagation -------------------------------------------------------------------
  * groundToImage(const csm::EcefCoordCovar&, prec, *ach, *warn) -> csm::ImageCoordCovar and
  * imageToGround(const csm::ImageCoordCovar&, height, heightVariance, prec, *ach, *warn) ->

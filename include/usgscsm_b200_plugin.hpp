@@ -298,6 +298,34 @@ class RasterGM {
                                            desiredPrecision, partials, achievedPrecision, status),
           "computeAllSensorPartialsBatch");
   }
+  // ---- image time and sensor ephemeris of an image point (LS:1543-1653, PF:1258-1320,
+  // FR:665-765, SAR:1113-1238)
+  void imageSensorStateBatch(size_t n, const double *line, const double *samp, double *time,
+                             double *px, double *py, double *pz, double *vx, double *vy,
+                             double *vz, uint32_t *status = NULL) const {
+    check(usgscsm_b200_image_sensor_state(m_h, (int64_t)n, line, samp, time, px, py, pz, vx, vy,
+                                          vz, status),
+          "imageSensorStateBatch");
+  }
+  double getImageTime(const csm::ImageCoord &imagePt) const {
+    double t = 0;
+    imageSensorStateBatch(1, &imagePt.line, &imagePt.samp, &t, NULL, NULL, NULL, NULL, NULL, NULL);
+    return t;
+  }
+  csm::EcefCoord getSensorPosition(const csm::ImageCoord &imagePt) const {
+    csm::EcefCoord p;
+    imageSensorStateBatch(1, &imagePt.line, &imagePt.samp, NULL, &p.x, &p.y, &p.z, NULL, NULL, NULL);
+    return p;
+  }
+  csm::EcefVector getSensorVelocity(const csm::ImageCoord &imagePt) const {
+    csm::EcefVector v;
+    uint32_t st = 0;
+    imageSensorStateBatch(1, &imagePt.line, &imagePt.samp, NULL, NULL, NULL, NULL, &v.x, &v.y, &v.z,
+                          &st);
+    raiseOrWarn(st & ~(uint32_t)USGSCSM_B200_ST_NONFINITE, NULL, "getSensorVelocity");
+    return v;
+  }
+
   // ---- error propagation (LS:910-964 / 1075-1157, PF:784-840 / 909-990, SAR:709-758 / 864-940)
   double getParameterCovariance(int index1, int index2) const {
     double v = 0.0;

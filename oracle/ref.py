@@ -47,6 +47,7 @@ def lib():
         L.ref_proximate_locus.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 8 + [C.c_int]
         L.ref_sensor_partials.argtypes = [C.c_void_p, C.c_int, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 4 + [C.c_int]
         L.ref_all_sensor_partials.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 3 + [C.c_int]
+        L.ref_image_sensor_state.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_set_parameter_covariance.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
         L.ref_ground_to_image_covar.argtypes = [C.c_void_p, C.c_long] + [_dp] * 4 + [C.c_double] + [_dp] * 5 + [C.c_int]
         L.ref_image_to_ground_covar.argtypes = ([C.c_void_p, C.c_long] + [_dp] * 4 + [C.c_int, _dp, C.c_int, C.c_double]
@@ -199,6 +200,17 @@ class RefModel(object):
         if got != num_params:
             raise RuntimeError("the reference model has %d parameters, not %d" % (got, num_params))
         return p, ach, st
+
+    def image_sensor_state(self, line, samp, threads=1):
+        """getImageTime / getSensorPosition / getSensorVelocity per point -> ((n, 7), status)."""
+        line = _a(line)
+        n = line.size
+        samp = _a(samp, n)
+        out = np.empty((n, 7))
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_image_sensor_state(self._h, n, line.ctypes.data, samp.ctypes.data,
+                                       out.ctypes.data, st.ctypes.data, threads)
+        return out, st
 
     def set_parameter_covariance(self, i, j, v):
         self._L.ref_set_parameter_covariance(self._h, int(i), int(j), float(v))

@@ -420,6 +420,42 @@ int ref_all_sensor_partials(void *h, long n, const double *x, const double *y, c
   return np;
 }
 
+// getImageTime / getSensorPosition / getSensorVelocity per image point; out = 7 doubles per
+// point (time, position, velocity).
+int ref_image_sensor_state(void *h, long n, const double *line, const double *samp, double *out,
+                           uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double *o = out + i * 7;
+    for (int k = 0; k < 7; k++) o[k] = std::nan("");
+    const csm::ImageCoord ip(line[i], samp[i]);
+    try {
+      o[0] = gm->getImageTime(ip);
+      const csm::EcefCoord p = gm->getSensorPosition(ip);
+      o[1] = p.x;
+      o[2] = p.y;
+      o[3] = p.z;
+      const csm::EcefVector v = gm->getSensorVelocity(ip);
+      o[4] = v.x;
+      o[5] = v.y;
+      o[6] = v.z;
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+    }
+    for (int k = 0; k < 7; k++)
+      if (!std::isfinite(o[k])) st |= ST_NONFINITE;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
 // setParameterCovariance
 int ref_set_parameter_covariance(void *h, int i, int j, double v) {
   RefModel *rm = static_cast<RefModel *>(h);

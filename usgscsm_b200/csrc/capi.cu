@@ -628,6 +628,29 @@ int usgscsm_b200_sensor_partials_dev(usgscsm_b200_model *m, int index, int64_t n
   });
 }
 
+// getImageTime / getSensorPosition / getSensorVelocity of an image point, for arrays
+// (LS:1543-1653, PF:1258-1320, FR:665-765, SAR:1113-1238).
+int usgscsm_b200_image_sensor_state_dev(usgscsm_b200_model *m, int64_t n, const double *line,
+                                        const double *samp, double *time, double *px, double *py,
+                                        double *pz, double *vx, double *vy, double *vz,
+                                        uint32_t *status, void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    SensorStateOut o{time, px, py, pz, vx, vy, vz, status};
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (m->kind) {
+      case USGSCSM_B200_MODEL_LINE_SCANNER: UB_CUDA(launchLsSensorState(m->ls, (long)n, line, o, s)); break;
+      case USGSCSM_B200_MODEL_PUSH_FRAME: UB_CUDA(launchPfSensorState(m->ls, (long)n, line, o, s)); break;
+      case USGSCSM_B200_MODEL_FRAME: UB_CUDA(launchFrSensorState(m->fr, (long)n, line, samp, o, s)); break;
+      default: UB_CUDA(launchSarSensorState(m->sar, (long)n, line, o, s)); break;
+    }
+    return USGSCSM_B200_OK;
+  });
+}
+
 int usgscsm_b200_all_sensor_partials_dev(usgscsm_b200_model *m, int n_indices, const int *indices,
                                          int64_t n, const double *x, const double *y,
                                          const double *z, const double *img_line,

@@ -296,6 +296,23 @@ int usgscsm_b200_all_sensor_partials(usgscsm_b200_model *m, int n_indices, const
                       });
 }
 
+int usgscsm_b200_image_sensor_state(usgscsm_b200_model *m, int64_t n, const double *line,
+                                    const double *samp, double *time, double *px, double *py,
+                                    double *pz, double *vx, double *vy, double *vz,
+                                    uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{line, 1, false}, {samp, 1, false}},
+                      {{time, 1}, {px, 1}, {py, 1}, {pz, 1}, {vx, 1}, {vy, 1}, {vz, 1}}, status, 0,
+                      [&](const Chunk &k) {
+                        int r = usgscsm_b200_image_sensor_state_dev(
+                            m, k.count, k.in[0], k.in[1], k.out[0], k.out[1], k.out[2], k.out[3],
+                            k.out[4], k.out[5], k.out[6], k.status, k.stream);
+                        return r == USGSCSM_B200_OK ? cudaSuccess : cudaErrorUnknown;
+                      });
+}
+
 // Error propagation (covar.cu): the covariances travel as arrays of 9 / 4 doubles per point.
 int usgscsm_b200_ground_to_image_covar(usgscsm_b200_model *m, int64_t n, const double *x,
                                        const double *y, const double *z, const double *ground_cov,

@@ -284,7 +284,36 @@ int frBlocks(long n, int smCount) {
   return (int)(b < 1 ? 1 : b);
 }
 
+// getImageTime FR:665-673 (0.0: the whole image is acquired at once), getSensorPosition
+// (ImageCoord) FR:689-700 (m_currentParameterValue[0..2]), getSensorVelocity(ImageCoord)
+// FR:749-765 (m_spacecraftVelocity; csm::Error::BOUNDS outside the image).
+__global__ void frSensorStateKernel(const __grid_constant__ FrameState S, long n,
+                                    const double *__restrict__ line,
+                                    const double *__restrict__ samp, SensorStateOut o) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double l = line[i], sm = samp[i];
+    double pos[3] = {S.rawParams[0], S.rawParams[1], S.rawParams[2]};
+    double vel[3] = {S.spacecraftVelocity[0], S.spacecraftVelocity[1], S.spacecraftVelocity[2]};
+    uint32_t st = 0;
+    if ((o.vx || o.vy || o.vz) && (sm < 0.0 || sm > S.nSamples || l < 0.0 || l > S.nLines)) {
+      st = USGSCSM_B200_ST_ERROR_OTHER;
+      vel[0] = vel[1] = vel[2] = nan("");
+    }
+    storeSensorState(o, i, 0.0, pos, vel, st);
+  }
+}
+
 }  // namespace
+
+cudaError_t launchFrSensorState(const FrameState &S, long n, const double *line,
+                                const double *samp, const SensorStateOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long blocks = (n + 255) / 256;
+  frSensorStateKernel<<<(int)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, stream>>>(S, n, line, samp, o);
+  countLaunch();
+  return cudaGetLastError();
+}
 
 cudaError_t launchFrGroundToImage(const FrameState &S, int smCount, long n, const double *x,
                                   const double *y, const double *z, double prec, double *line,

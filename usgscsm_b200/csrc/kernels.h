@@ -70,6 +70,37 @@ __device__ __forceinline__ void storePartials(double *__restrict__ partials,
 }
 #endif
 
+// getImageTime / getSensorPosition / getSensorVelocity per image point; any array may be null.
+struct SensorStateOut {
+  double *time, *px, *py, *pz, *vx, *vy, *vz;
+  uint32_t *status;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ void storeSensorState(const SensorStateOut &o, long i, double time,
+                                                 const double pos[3], const double vel[3],
+                                                 uint32_t st) {
+  if (!(isfinite(time) && isfinite(pos[0]) && isfinite(pos[1]) && isfinite(pos[2]) &&
+        isfinite(vel[0]) && isfinite(vel[1]) && isfinite(vel[2])))
+    st |= USGSCSM_B200_ST_NONFINITE;
+  if (o.time) o.time[i] = time;
+  if (o.px) o.px[i] = pos[0];
+  if (o.py) o.py[i] = pos[1];
+  if (o.pz) o.pz[i] = pos[2];
+  if (o.vx) o.vx[i] = vel[0];
+  if (o.vy) o.vy[i] = vel[1];
+  if (o.vz) o.vz[i] = vel[2];
+  if (o.status) o.status[i] = st;
+}
+#endif
+cudaError_t launchLsSensorState(const LsState &S, long n, const double *line,
+                                const SensorStateOut &o, cudaStream_t stream);
+cudaError_t launchPfSensorState(const LsState &S, long n, const double *line,
+                                const SensorStateOut &o, cudaStream_t stream);
+cudaError_t launchFrSensorState(const FrameState &S, long n, const double *line,
+                                const double *samp, const SensorStateOut &o, cudaStream_t stream);
+cudaError_t launchSarSensorState(const SarState &S, long n, const double *line,
+                                 const SensorStateOut &o, cudaStream_t stream);
+
 cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const double *x,
                                    const double *y, const double *z, double *partials,
                                    uint32_t *status, cudaStream_t stream);

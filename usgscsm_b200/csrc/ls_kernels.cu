@@ -507,6 +507,22 @@ __global__ void lsSensorPositionKernel(const __grid_constant__ LsState S, int n,
   xyz[3 * i + 2] = pos[2];
 }
 
+// getImageTime LS:1543-1568, getSensorPosition(ImageCoord) LS:1580-1611 (calc_vel = false: the
+// nominal position when no parameter is set), getSensorVelocity(ImageCoord) LS:1623-1653
+// (calc_vel = true), per image point.
+__global__ void lsSensorStateKernel(const __grid_constant__ LsState S, long n,
+                                    const double *__restrict__ line, SensorStateOut o) {
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double time = lsImageTime(S, line[i]);
+    double pos[3], vel[3], posV[3], unused[3];
+    adjSensorPosVel<false>(S, T, time, pos, unused);
+    adjSensorPosVel<true>(S, T, time, posV, vel);
+    storeSensorState(o, i, time, pos, vel, 0u);
+  }
+}
+
 // computeEllipsoidElevation U:819-868 for n points (xyz interleaved).
 __global__ void ellipsoidElevationKernel(Ellipsoid ell, int n, const double *__restrict__ xyz,
                                          double prec, double *__restrict__ h) {
@@ -680,6 +696,15 @@ cudaError_t launchLsRemoteLocus(const LsState &S, int smCount, long n, const dou
   } else {
     lsRemoteLocusKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(S, n, line, samp, o);
   }
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchLsSensorState(const LsState &S, long n, const double *line,
+                                const SensorStateOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long blocks = (n + 255) / 256;
+  lsSensorStateKernel<<<(int)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, stream>>>(S, n, line, o);
   countLaunch();
   return cudaGetLastError();
 }

@@ -110,6 +110,11 @@ void loadFrame(Model &m, const StateReader &st) {
   fp.sampleSumming.b = fp.detectorSampleSumming;
   fillDivisors({&fp.lineSumming, &fp.sampleSumming});
 
+  {
+    std::vector<double> v = st.getVecDouble("m_spacecraftVelocity", {0.0, 0.0, 0.0});
+    if (v.size() != 3) throw StateError("m_spacecraftVelocity needs 3 entries");
+    for (int i = 0; i < 3; i++) m.fr.spacecraftVelocity[i] = v[i];
+  }
   m.lineJitter = st.getVecDouble("m_lineJitter", {});
   m.sampleJitter = st.getVecDouble("m_sampleJitter", {});
   m.lineTimes = st.getVecDouble("m_lineTimes", {});

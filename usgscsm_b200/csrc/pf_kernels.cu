@@ -472,6 +472,20 @@ __global__ void pfSensorPositionKernel(const __grid_constant__ LsState S, double
   xyz[2] = pos[2];
 }
 
+// getImageTime PF:1258-1276, getSensorPosition(ImageCoord) PF:1281-1299,
+// getSensorVelocity(ImageCoord) PF:1303-1320, per image point.
+__global__ void pfSensorStateKernel(const __grid_constant__ LsState S, long n,
+                                    const double *__restrict__ line, SensorStateOut o) {
+  OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double time = pfFrameletTime(S, pfTimeFramelet(S, line[i]));
+    double pos[3], vel[3];
+    adjSensorPosVel<true>(S, T, time, pos, vel);
+    storeSensorState(o, i, time, pos, vel, 0u);
+  }
+}
+
 LaunchShape pfShape(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
   size_t bytes = S.frameletOrient ? orientCacheBytes(S) : 0;
   stage = bytes > 0 && bytes <= kMaxStagedTableBytes;
@@ -497,6 +511,15 @@ cudaError_t launchPfFrameletOrientations(const LsState &S, double *out, cudaStre
 cudaError_t launchPfSensorPosition(const LsState &S, double time, double *xyz,
                                    cudaStream_t stream) {
   pfSensorPositionKernel<<<1, 1, 0, stream>>>(S, time, xyz);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchPfSensorState(const LsState &S, long n, const double *line,
+                                const SensorStateOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long blocks = (n + 255) / 256;
+  pfSensorStateKernel<<<(int)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, stream>>>(S, n, line, o);
   countLaunch();
   return cudaGetLastError();
 }

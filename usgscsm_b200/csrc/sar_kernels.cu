@@ -512,7 +512,30 @@ cudaError_t allowSmem(K kernel, size_t bytes) {
   return cudaSuccess;
 }
 
+// getImageTime SAR:1113-1119, getSensorPosition(ImageCoord) SAR:1179-1184,
+// getSensorVelocity(ImageCoord) SAR:1232-1238, per image point.
+__global__ void sarSensorStateKernel(const __grid_constant__ SarState S, long n,
+                                     const double *__restrict__ line, SensorStateOut o) {
+  SarTables T = stageSarTables(S, nullptr, false);
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double time = S.startingEphemerisTime + (line[i] - 0.5) * S.exposureDuration;
+    double pos[3], vel[3];
+    sarPosVel(S, T, time, pos, vel);
+    storeSensorState(o, i, time, pos, vel, 0u);
+  }
+}
+
 }  // namespace
+
+cudaError_t launchSarSensorState(const SarState &S, long n, const double *line,
+                                 const SensorStateOut &o, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long blocks = (n + 255) / 256;
+  sarSensorStateKernel<<<(int)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, stream>>>(S, n, line, o);
+  countLaunch();
+  return cudaGetLastError();
+}
 
 cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const double *x,
                                    const double *y, const double *z, double prec, double *line,

@@ -148,6 +148,7 @@ struct FrameState {
   Ellipsoid ell;
   double params[7];  // x, y, z, qx, qy, qz, qw (m_currentParameterValue + 0.0)
   double rawParams[3];  // m_currentParameterValue[0..2] as stored (imageToRemoteImagingLocus FR:540)
+  double spacecraftVelocity[3];  // m_spacecraftVelocity (getSensorVelocity FR:749-795)
   // Camera-to-body matrices, evaluated once on the host with the reference's expressions
   // (IEEE arithmetic without contraction on both sides, hence the same bits):
   double mNorm[9];  // calcRotationMatrix(m) FR:2242-2265: quaternion normalised (imageToGround)

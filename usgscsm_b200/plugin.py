@@ -365,6 +365,39 @@ class RasterGM(object):
             desiredPrecision, _ptr(p), _ptr(ach), _ptr(st)))
         return p, ach, st
 
+    def imageSensorStateBatch(self, line, samp):
+        """getImageTime / getSensorPosition / getSensorVelocity of image points, for arrays:
+        returns (time, (px, py, pz), (vx, vy, vz), status)."""
+        if _is_torch(line):
+            import torch
+            n = line.numel()
+            o = [torch.empty_like(line) for _ in range(7)]
+            st = torch.empty(n, dtype=torch.int32, device=line.device)
+            check(lib.usgscsm_b200_image_sensor_state_dev(
+                self._h, n, _ptr(line), _ptr(samp), *[_ptr(t) for t in o], _ptr(st),
+                torch.cuda.current_stream(line.device).cuda_stream))
+        else:
+            line = _host(line)
+            n = line.size
+            samp = _host(samp, n)
+            o = [np.empty(n) for _ in range(7)]
+            st = np.empty(n, dtype=np.uint32)
+            check(lib.usgscsm_b200_image_sensor_state(
+                self._h, n, _ptr(line), _ptr(samp), *[_ptr(t) for t in o], _ptr(st)))
+        return o[0], tuple(o[1:4]), tuple(o[4:7]), st
+
+    def getImageTime(self, imagePt):
+        return float(self.imageSensorStateBatch([imagePt[0]], [imagePt[1]])[0][0])
+
+    def getSensorPosition(self, imagePt):
+        _, p, _, _ = self.imageSensorStateBatch([imagePt[0]], [imagePt[1]])
+        return tuple(float(c[0]) for c in p)
+
+    def getSensorVelocity(self, imagePt):
+        _, _, v, st = self.imageSensorStateBatch([imagePt[0]], [imagePt[1]])
+        self._raise_or_warn(int(st[0]) & ~_capi.ST_NONFINITE, None, "getSensorVelocity")
+        return tuple(float(c[0]) for c in v)
+
     # ---- error propagation (csm::EcefCoordCovar / csm::ImageCoordCovar overloads) -------------
     def getParameterCovariance(self, index1, index2):
         v = C.c_double()
