@@ -277,9 +277,19 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
-int frBlocks(long n, int smCount) {
+// One wave: as many blocks as are resident at once for THIS kernel (its register count decides:
+// 3 x 256 threads per SM at 80 registers, 4 at 64), so the grid-stride loop splits the points
+// evenly and no block waits for a second wave.
+template <class K>
+int frBlocks(K kernel, long n, int smCount) {
+  static const int perSm = [&] {
+    int b = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kernel, kThreads, 0) != cudaSuccess || b < 1)
+      b = 4;
+    return b;
+  }();
   long blocksNeeded = (n + kThreads - 1) / kThreads;
-  long persistent = (long)smCount * 8;  // light kernels: 8 resident blocks of 256 per SM
+  long persistent = (long)smCount * perSm;
   long b = blocksNeeded < persistent ? blocksNeeded : persistent;
   return (int)(b < 1 ? 1 : b);
 }
@@ -320,7 +330,7 @@ cudaError_t launchFrGroundToImage(const FrameState &S, int smCount, long n, cons
                                   double *samp, double *achieved, uint32_t *status,
                                   cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  frGroundToImageKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, prec, line,
+  frGroundToImageKernel<<<frBlocks(frGroundToImageKernel, n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, prec, line,
                                                                       samp, achieved, status);
   countLaunch();
   return cudaGetLastError();
@@ -334,10 +344,10 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
   if (n <= 0) return cudaSuccess;
   GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
   if (grid)
-    frImageToGroundKernel<true><<<frBlocks(n, smCount), kThreads, 0, stream>>>(
+    frImageToGroundKernel<true><<<frBlocks(frImageToGroundKernel<true>, n, smCount), kThreads, 0, stream>>>(
         S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
   else
-    frImageToGroundKernel<false><<<frBlocks(n, smCount), kThreads, 0, stream>>>(
+    frImageToGroundKernel<false><<<frBlocks(frImageToGroundKernel<false>, n, smCount), kThreads, 0, stream>>>(
         S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
   countLaunch();
   return cudaGetLastError();
@@ -346,7 +356,7 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
 cudaError_t launchFrRemoteLocus(const FrameState &S, int smCount, long n, const double *line,
                                 const double *samp, const LocusOut &o, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  frRemoteLocusKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, line, samp, o);
+  frRemoteLocusKernel<<<frBlocks(frRemoteLocusKernel, n, smCount), kThreads, 0, stream>>>(S, n, line, samp, o);
   countLaunch();
   return cudaGetLastError();
 }
@@ -355,7 +365,7 @@ cudaError_t launchGroundPartialsFr(const FrameState &S, int smCount, long n, con
                                    const double *y, const double *z, double *partials,
                                    uint32_t *status, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  frGroundPartialsKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, partials, status);
+  frGroundPartialsKernel<<<frBlocks(frGroundPartialsKernel, n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, partials, status);
   countLaunch();
   return cudaGetLastError();
 }
@@ -364,7 +374,7 @@ cudaError_t launchFrProximateLocus(const FrameState &S, int smCount, long n, con
                                    const double *samp, const double *x, const double *y,
                                    const double *z, const LocusOut &o, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  frProximateLocusKernel<<<frBlocks(n, smCount), kThreads, 0, stream>>>(S, n, line, samp, x, y, z, o);
+  frProximateLocusKernel<<<frBlocks(frProximateLocusKernel, n, smCount), kThreads, 0, stream>>>(S, n, line, samp, x, y, z, o);
   countLaunch();
   return cudaGetLastError();
 }
