@@ -288,6 +288,17 @@ USGSCSM_B200_API int usgscsm_b200_image_sensor_state_dev(usgscsm_b200_model *m, 
                                         double *pz, double *vx, double *vy, double *vz,
                                         uint32_t *status, void *stream);
 
+/* getIlluminationDirection(const csm::EcefCoord&) for arrays (LS:1878-1899, PF:1477-1498,
+ * SAR:1095-1102, FR:643-652): the unit vector from the sun to the ground point at the time the
+ * point was imaged (frame model: ground - sun, not normalised, as the reference returns it).
+ * status (nullable): an error bit where the groundToImage inside would have thrown. */
+USGSCSM_B200_API int usgscsm_b200_illumination_direction(usgscsm_b200_model *m, int64_t n, const double *x,
+                                        const double *y, const double *z, double *dx, double *dy,
+                                        double *dz, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_illumination_direction_dev(usgscsm_b200_model *m, int64_t n, const double *x,
+                                            const double *y, const double *z, double *dx,
+                                            double *dy, double *dz, uint32_t *status, void *stream);
+
 /* ---- error propagation -------------------------------------------------------------------
  * groundToImage(const csm::EcefCoordCovar&, prec, *ach, *warn) -> csm::ImageCoordCovar and
  * imageToGround(const csm::ImageCoordCovar&, height, heightVariance, prec, *ach, *warn) ->

@@ -326,6 +326,23 @@ class RasterGM {
     return v;
   }
 
+  // LS:1878-1899, PF:1477-1498, SAR:1095-1102, FR:643-652
+  csm::EcefVector getIlluminationDirection(const csm::EcefCoord &groundPt) const {
+    csm::EcefVector v;
+    uint32_t st = 0;
+    check(usgscsm_b200_illumination_direction(m_h, 1, &groundPt.x, &groundPt.y, &groundPt.z, &v.x,
+                                              &v.y, &v.z, &st),
+          "getIlluminationDirection");
+    raiseOrWarn(st & ~(uint32_t)USGSCSM_B200_ST_NONFINITE, NULL, "getIlluminationDirection");
+    return v;
+  }
+  void getIlluminationDirectionBatch(size_t n, const double *x, const double *y, const double *z,
+                                     double *dx, double *dy, double *dz,
+                                     uint32_t *status = NULL) const {
+    check(usgscsm_b200_illumination_direction(m_h, (int64_t)n, x, y, z, dx, dy, dz, status),
+          "getIlluminationDirectionBatch");
+  }
+
   // ---- error propagation (LS:910-964 / 1075-1157, PF:784-840 / 909-990, SAR:709-758 / 864-940)
   double getParameterCovariance(int index1, int index2) const {
     double v = 0.0;

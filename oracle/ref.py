@@ -48,6 +48,7 @@ def lib():
         L.ref_sensor_partials.argtypes = [C.c_void_p, C.c_int, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 4 + [C.c_int]
         L.ref_all_sensor_partials.argtypes = [C.c_void_p, C.c_long] + [_dp] * 5 + [C.c_double] + [_dp] * 3 + [C.c_int]
         L.ref_image_sensor_state.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, C.c_int]
+        L.ref_illumination_direction.argtypes = [C.c_void_p, C.c_long, _dp, _dp, _dp, _dp, _dp, C.c_int]
         L.ref_set_parameter_covariance.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
         L.ref_ground_to_image_covar.argtypes = [C.c_void_p, C.c_long] + [_dp] * 4 + [C.c_double] + [_dp] * 5 + [C.c_int]
         L.ref_image_to_ground_covar.argtypes = ([C.c_void_p, C.c_long] + [_dp] * 4 + [C.c_int, _dp, C.c_int, C.c_double]
@@ -210,6 +211,17 @@ class RefModel(object):
         st = np.empty(n, dtype=np.uint32)
         self._L.ref_image_sensor_state(self._h, n, line.ctypes.data, samp.ctypes.data,
                                        out.ctypes.data, st.ctypes.data, threads)
+        return out, st
+
+    def illumination_direction(self, x, y, z, threads=1):
+        """getIlluminationDirection per point -> ((n, 3), status)."""
+        x = _a(x)
+        n = x.size
+        y, z = _a(y, n), _a(z, n)
+        out = np.empty((n, 3))
+        st = np.empty(n, dtype=np.uint32)
+        self._L.ref_illumination_direction(self._h, n, x.ctypes.data, y.ctypes.data, z.ctypes.data,
+                                           out.ctypes.data, st.ctypes.data, threads)
         return out, st
 
     def set_parameter_covariance(self, i, j, v):

@@ -456,6 +456,34 @@ int ref_image_sensor_state(void *h, long n, const double *line, const double *sa
   return 0;
 }
 
+// getIlluminationDirection per ground point; out = 3 doubles per point.
+int ref_illumination_direction(void *h, long n, const double *x, const double *y, const double *z,
+                               double *out, uint32_t *status, int threads) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  const csm::RasterGM *gm = rm->gm;
+  const int nt = pickThreads(threads);
+  (void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+  for (long i = 0; i < n; i++) {
+    uint32_t st = 0;
+    double *o = out + i * 3;
+    o[0] = o[1] = o[2] = std::nan("");
+    try {
+      const csm::EcefVector v = gm->getIlluminationDirection(csm::EcefCoord(x[i], y[i], z[i]));
+      o[0] = v.x;
+      o[1] = v.y;
+      o[2] = v.z;
+    } catch (const csm::Error &e) {
+      st |= bitsFromError(e);
+    } catch (const std::exception &) {
+      st |= ST_ERROR_OTHER;
+    }
+    if (!(std::isfinite(o[0]) && std::isfinite(o[1]) && std::isfinite(o[2]))) st |= ST_NONFINITE;
+    if (status) status[i] = st;
+  }
+  return 0;
+}
+
 // setParameterCovariance
 int ref_set_parameter_covariance(void *h, int i, int j, double v) {
   RefModel *rm = static_cast<RefModel *>(h);

@@ -89,6 +89,8 @@ SIGNATURES = {
                   _dp, _dp, _dp, _dp]),
     "usgscsm_b200_image_sensor_state": (C.c_int, [_h, C.c_int64] + [_dp] * 10),
     "usgscsm_b200_image_sensor_state_dev": (C.c_int, [_h, C.c_int64] + [_dp] * 11),
+    "usgscsm_b200_illumination_direction": (C.c_int, [_h, C.c_int64] + [_dp] * 7),
+    "usgscsm_b200_illumination_direction_dev": (C.c_int, [_h, C.c_int64] + [_dp] * 8),
     "usgscsm_b200_ground_to_image_covar": (
         C.c_int, [_h, C.c_int64, _dp, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_ground_to_image_covar_dev": (

@@ -193,6 +193,7 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
       return USGSCSM_B200_EUNSUPPORTED;
     }
     m->covariance = st.getVecDouble("m_covariance", std::vector<double>());
+    loadSun(*m, st);
     UB_CUDA(cudaDeviceSynchronize());
     *out = m.release();
     return USGSCSM_B200_OK;

@@ -74,6 +74,10 @@ int allSensorPartialsDev(usgscsm_b200_model *m, int n_indices, const int *indice
 int allSensorPartialsCheck(usgscsm_b200_model *m, int n_indices, const int *indices, int64_t n,
                            const void *x, const void *y, const void *z, const void *partials);
 
+// illumination.cu
+int illuminationDev(usgscsm_b200_model *m, long n, const double *x, const double *y,
+                    const double *z, double *dx, double *dy, double *dz, uint32_t *status,
+                    cudaStream_t stream);
 // covar.cu
 int covarCheck(const usgscsm_b200_model *m, int64_t n);
 int groundToImageCovarDev(usgscsm_b200_model *m, long n, const double *x, const double *y,

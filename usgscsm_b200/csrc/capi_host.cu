@@ -313,6 +313,20 @@ int usgscsm_b200_image_sensor_state(usgscsm_b200_model *m, int64_t n, const doub
                       });
 }
 
+int usgscsm_b200_illumination_direction(usgscsm_b200_model *m, int64_t n, const double *x,
+                                        const double *y, const double *z, double *dx, double *dy,
+                                        double *dz, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!x || !y || !z || !dx || !dy || !dz) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{x, 1, false}, {y, 1, false}, {z, 1, false}},
+                      {{dx, 1}, {dy, 1}, {dz, 1}}, status, 0, [&](const Chunk &k) {
+                        illuminationDev(m, k.count, k.in[0], k.in[1], k.in[2], k.out[0], k.out[1],
+                                        k.out[2], k.status, k.stream);
+                        return cudaSuccess;  // throws on failure
+                      });
+}
+
 // Error propagation (covar.cu): the covariances travel as arrays of 9 / 4 doubles per point.
 int usgscsm_b200_ground_to_image_covar(usgscsm_b200_model *m, int64_t n, const double *x,
                                        const double *y, const double *z, const double *ground_cov,

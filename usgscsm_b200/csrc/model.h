@@ -76,6 +76,11 @@ struct Model {
 
   std::vector<double> params;  // m_currentParameterValue (raw, without the +0.0)
   std::vector<double> covariance;  // m_covariance, numParams x numParams (error propagation only)
+  // getIlluminationDirection only (illumination.cu)
+  std::vector<double> sunPosition, sunVelocity;
+  UniformTable sunTable{};
+  LagrangeDivisors sunLag{};
+  bool hasSunTable = false;
 
   // ---- device side ---------------------------------------------------------------------
   std::vector<DeviceBuffer> owned;
@@ -112,6 +117,9 @@ void readFocalPlane(FocalPlane &fp, const class StateReader &st, bool lineScanTy
 void readEllipsoid(Ellipsoid &e, const class StateReader &st);
 void setEllipsoidRadii(Ellipsoid &e, double a, double b);
 void readOrientation(Model &m, const class StateReader &st);
+
+// illumination.cu
+void loadSun(Model &m, const class StateReader &st);
 
 // projective_fit.cpp
 // Least-squares fit of the 14-coefficient 3D->2D projective map (the reference's

@@ -398,6 +398,31 @@ class RasterGM(object):
         self._raise_or_warn(int(st[0]) & ~_capi.ST_NONFINITE, None, "getSensorVelocity")
         return tuple(float(c[0]) for c in v)
 
+    def getIlluminationDirectionBatch(self, x, y, z):
+        """csm::RasterGM::getIlluminationDirection for arrays: returns (dx, dy, dz, status)."""
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            d = [torch.empty_like(x) for _ in range(3)]
+            st = torch.empty(n, dtype=torch.int32, device=x.device)
+            check(lib.usgscsm_b200_illumination_direction_dev(
+                self._h, n, _ptr(x), _ptr(y), _ptr(z), *[_ptr(t) for t in d], _ptr(st),
+                torch.cuda.current_stream(x.device).cuda_stream))
+        else:
+            x = _host(x)
+            n = x.size
+            y, z = _host(y, n), _host(z, n)
+            d = [np.empty(n) for _ in range(3)]
+            st = np.empty(n, dtype=np.uint32)
+            check(lib.usgscsm_b200_illumination_direction(
+                self._h, n, _ptr(x), _ptr(y), _ptr(z), *[_ptr(t) for t in d], _ptr(st)))
+        return d[0], d[1], d[2], st
+
+    def getIlluminationDirection(self, groundPt):
+        dx, dy, dz, st = self.getIlluminationDirectionBatch([groundPt[0]], [groundPt[1]], [groundPt[2]])
+        self._raise_or_warn(int(st[0]) & ~_capi.ST_NONFINITE, None, "getIlluminationDirection")
+        return float(dx[0]), float(dy[0]), float(dz[0])
+
     # ---- error propagation (csm::EcefCoordCovar / csm::ImageCoordCovar overloads) -------------
     def getParameterCovariance(self, index1, index2):
         v = C.c_double()
