@@ -453,7 +453,9 @@ def ncu_traffic(n):
 def callers_side(model, x, y, z, m, dev, band):
     """Side measurements of the batched caller-level entry points on the C2 line-scan model:
     computeGroundPartials (4 searches per point in one kernel), computeSensorPartials (2
-    searches + difference), computeAllSensorPartials (17 searches, on a quarter of the points), imageToRemoteImagingLocus, imageToProximateImagingLocus (3
+    searches + difference), computeAllSensorPartials (17 searches) and groundToImage with
+    covariance (22 searches) on a quarter of the points ("all_" keys), getImageTime +
+    getSensorPosition + getSensorVelocity, getIlluminationDirection, imageToRemoteImagingLocus, imageToProximateImagingLocus (3
     imageToGround + 2 elevations).  Device resident, median of 3 after 1 warm-up."""
     import torch
     from usgscsm_b200 import _capi
@@ -482,7 +484,15 @@ def callers_side(model, x, y, z, m, dev, band):
     allp = torch.empty(m4 * npar * 2, dtype=torch.float64, device=dev)
     calls["all_sensor_partials_%d_params" % npar] = lambda: lib.usgscsm_b200_all_sensor_partials_dev(
         h, npar, None, m4, p(x), p(y), p(z), None, None, PREC, p(allp), p(o[0]), p(st), stream)
-    out = {"points": m, "unit": "Mpoints/s"}
+    gcov = torch.eye(3, dtype=torch.float64, device=dev).reshape(1, 9).repeat(m4, 1).contiguous()
+    icov = torch.empty(m4 * 4, dtype=torch.float64, device=dev)
+    calls["all_ground_to_image_covar"] = lambda: lib.usgscsm_b200_ground_to_image_covar_dev(
+        h, m4, p(x), p(y), p(z), p(gcov), PREC, p(o[0]), p(o[1]), p(icov), p(o[2]), p(st), stream)
+    calls["image_sensor_state"] = lambda: lib.usgscsm_b200_image_sensor_state_dev(
+        h, m, p(line), p(samp), *[p(t) for t in o], p(st), stream)
+    calls["illumination_direction"] = lambda: lib.usgscsm_b200_illumination_direction_dev(
+        h, m, p(x), p(y), p(z), p(o[0]), p(o[1]), p(o[2]), p(st), stream)
+    out = {"points": m, "unit": "Mpoints/s", "points_all_": m4}
     for name, fn in calls.items():
         _capi.check(fn())
         torch.cuda.synchronize()

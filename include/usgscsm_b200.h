@@ -105,6 +105,14 @@ USGSCSM_B200_API int usgscsm_b200_model_from_state(const char *state, size_t len
  * four model names above. */
 USGSCSM_B200_API int usgscsm_b200_model_name_from_state(const char *state, size_t len, char *name,
                                        size_t cap);
+/* getModelState (LS:345-483, PF:346-455, FR:1241-1300, SAR:395-455): "<model name>\n<JSON>" of
+ * the state the model was built from, with what the caller may have changed written back:
+ * m_currentParameterValue, m_covariance, m_majorAxis / m_minorAxis.  Doubles are written with
+ * 17 significant digits, so a model built from this text computes the same bits.  Call with
+ * out = NULL to learn the size (*needed, without a terminator). */
+USGSCSM_B200_API int usgscsm_b200_model_get_state(const usgscsm_b200_model *m, char *out, size_t capacity,
+                                 size_t *needed);
+
 /* A model state (any accepted encoding) -> its msgpack binary form, byte for byte what the
  * reference writes with nlohmann::json::to_msgpack (bin/usgscsm_cam_test.cc
  * --output-binary-model-state).  *needed receives the size; bytes are written when out holds

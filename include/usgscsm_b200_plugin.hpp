@@ -152,7 +152,13 @@ class RasterGM {
       default: return "USGS_ASTRO_SAR_SENSOR_MODEL";
     }
   }
-  std::string getModelState() const { return m_state; }
+  std::string getModelState() const {  // current parameters / covariance / ellipsoid written back
+    size_t need = 0;
+    check(usgscsm_b200_model_get_state(m_h, NULL, 0, &need), "getModelState");
+    std::string s(need, '\0');
+    if (need) check(usgscsm_b200_model_get_state(m_h, &s[0], need, &need), "getModelState");
+    return s;
+  }
   csm::ImageVector getImageSize() const {  // LS:1845-1852
     int l = 0, s = 0;
     check(usgscsm_b200_model_image_size(m_h, &l, &s), "getImageSize");

@@ -87,6 +87,7 @@ SIGNATURES = {
     "usgscsm_b200_all_sensor_partials_dev": (
         C.c_int, [_h, C.c_int, C.POINTER(C.c_int), C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double,
                   _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_model_get_state": (C.c_int, [_h, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "usgscsm_b200_image_sensor_state": (C.c_int, [_h, C.c_int64] + [_dp] * 10),
     "usgscsm_b200_image_sensor_state_dev": (C.c_int, [_h, C.c_int64] + [_dp] * 11),
     "usgscsm_b200_illumination_direction": (C.c_int, [_h, C.c_int64] + [_dp] * 7),

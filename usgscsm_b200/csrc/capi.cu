@@ -194,6 +194,7 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     }
     m->covariance = st.getVecDouble("m_covariance", std::vector<double>());
     loadSun(*m, st);
+    m->stateTree = root;
     UB_CUDA(cudaDeviceSynchronize());
     *out = m.release();
     return USGSCSM_B200_OK;
@@ -271,6 +272,55 @@ int usgscsm_b200_model_get_parameter(const usgscsm_b200_model *m, int index, dou
     return fail(USGSCSM_B200_EINVAL, "parameter index out of range");
   *value = m->params[index];
   return USGSCSM_B200_OK;
+}
+
+// getModelState (LS:345-483, PF:346-455, FR:1241-1300, SAR:395-455): the state the model was
+// built from with the members a caller can change written back -- parameter values, parameter
+// covariance, ellipsoid radii -- as "<model name>\n<JSON>".
+int usgscsm_b200_model_get_state(const usgscsm_b200_model *m, char *out, size_t capacity,
+                                 size_t *needed) {
+  if (!m || !needed) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return guarded([&]() -> int {
+    json::Value tree = m->stateTree;
+    // unchanged entries keep their literal kind (integer / real), so an untouched model
+    // re-serialises to the document it was built from
+    auto putArray = [&](const char *key, const std::vector<double> &nums) {
+      json::Value &dst = tree.members[key];
+      if (dst.type == json::Type::Array && dst.numericArray && dst.nums.size() == nums.size()) {
+        for (size_t k = 0; k < nums.size(); k++)
+          if (std::memcmp(&dst.nums[k], &nums[k], sizeof(double)) != 0) {
+            dst.nums[k] = nums[k];
+            dst.numIsInt[k] = 0;
+          }
+      } else {
+        dst = json::numberArray(nums);
+      }
+    };
+    auto putNumber = [&](const char *key, double v) {
+      json::Value &dst = tree.members[key];
+      if (!(dst.isNumber() && std::memcmp(&dst.num, &v, sizeof(double)) == 0)) dst = json::number(v);
+    };
+    putArray("m_currentParameterValue", m->params);
+    if (!m->covariance.empty()) putArray("m_covariance", m->covariance);
+    const Ellipsoid &e = m->kind == USGSCSM_B200_MODEL_FRAME ? m->fr.ell
+                         : m->kind == USGSCSM_B200_MODEL_SAR ? m->sar.ell : m->ls.ell;
+    putNumber("m_majorAxis", e.majorAxis);
+    putNumber("m_minorAxis", e.minorAxis);
+    if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER || m->kind == USGSCSM_B200_MODEL_PUSH_FRAME) {
+      // what updateState derived at load (LS:649-735), so that a reload does not derive it
+      // again from the adjusted model
+      putNumber("m_gsd", m->ls.gsd);
+      putNumber("m_flyingHeight", m->ls.flyingHeight);
+      putNumber("m_halfSwath", m->ls.halfSwath);
+      putNumber("m_halfTime", m->ls.halfTime);
+      putArray("m_referencePointXyz", std::vector<double>(m->referencePoint, m->referencePoint + 3));
+    }
+    const std::string text = m->modelName + "\n" + json::dump(tree);
+    *needed = text.size();
+    if (out && capacity >= text.size()) std::memcpy(out, text.data(), text.size());
+    else if (out) return fail(USGSCSM_B200_EINVAL, "buffer too small");
+    return USGSCSM_B200_OK;
+  });
 }
 
 int usgscsm_b200_model_set_parameter(usgscsm_b200_model *m, int index, double value) {

@@ -9,6 +9,7 @@
 #define USGSCSM_B200_JSON_MIN_H_
 
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -281,6 +282,102 @@ class Parser {
 inline Value parse(const std::string &text) {
   Parser p(text.data(), text.data() + text.size());
   return p.parseDocument();
+}
+
+// Compact JSON text of a value tree: keys in sorted order, doubles with 17 significant digits
+// (they parse back to the same bits), non-finite numbers as null like nlohmann::json::dump.
+inline void dumpNumber(std::string &out, double v, bool isInt) {
+  char buf[40];
+  if (!(v == v) || v - v != 0.0) {
+    out += "null";
+    return;
+  }
+  if (isInt && v > -9.2e18 && v < 9.2e18) {
+    std::snprintf(buf, sizeof buf, "%.0f", v);
+    out += buf;
+    return;
+  }
+  std::snprintf(buf, sizeof buf, "%.17g", v);
+  out += buf;
+  if (!std::strpbrk(buf, ".eEn")) out += ".0";
+}
+
+inline void dumpString(std::string &out, const std::string &s) {
+  out += '"';
+  for (unsigned char c : s) {
+    switch (c) {
+      case '"': out += "\\\""; break;
+      case '\\': out += "\\\\"; break;
+      case '\n': out += "\\n"; break;
+      case '\r': out += "\\r"; break;
+      case '\t': out += "\\t"; break;
+      default:
+        if (c < 0x20) {
+          char buf[8];
+          std::snprintf(buf, sizeof buf, "\\u%04x", c);
+          out += buf;
+        } else {
+          out += (char)c;
+        }
+    }
+  }
+  out += '"';
+}
+
+inline void dumpValue(std::string &out, const Value &v) {
+  switch (v.type) {
+    case Type::Null: out += "null"; break;
+    case Type::Bool: out += v.b ? "true" : "false"; break;
+    case Type::Int: dumpNumber(out, v.num, true); break;
+    case Type::Float: dumpNumber(out, v.num, false); break;
+    case Type::String: dumpString(out, v.str); break;
+    case Type::Array: {
+      out += '[';
+      const size_t n = v.arraySize();
+      for (size_t k = 0; k < n; k++) {
+        if (k) out += ',';
+        if (v.numericArray)
+          dumpNumber(out, v.nums[k], k < v.numIsInt.size() && v.numIsInt[k]);
+        else
+          dumpValue(out, v.items[k]);
+      }
+      out += ']';
+    } break;
+    case Type::Object: {
+      out += '{';
+      bool first = true;
+      for (const auto &kv : v.members) {
+        if (!first) out += ',';
+        first = false;
+        dumpString(out, kv.first);
+        out += ':';
+        dumpValue(out, kv.second);
+      }
+      out += '}';
+    } break;
+  }
+}
+
+inline std::string dump(const Value &v) {
+  std::string out;
+  dumpValue(out, v);
+  return out;
+}
+
+inline Value numberArray(const std::vector<double> &nums) {
+  Value v;
+  v.type = Type::Array;
+  v.numericArray = true;
+  v.nums = nums;
+  v.numIsInt.assign(nums.size(), 0);
+  return v;
+}
+
+inline Value number(double d) {
+  Value v;
+  v.type = Type::Float;
+  v.num = d;
+  return v;
 }
 
 }  // namespace json

@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 
+#include "json_min.h"
 #include "kernels.h"
 #include "sensor_state.h"
 
@@ -75,6 +76,7 @@ struct Model {
   std::vector<double> scaleCoeffs, scaleTimes;
 
   std::vector<double> params;  // m_currentParameterValue (raw, without the +0.0)
+  json::Value stateTree;       // the state as loaded; getModelState re-serialises it
   std::vector<double> covariance;  // m_covariance, numParams x numParams (error propagation only)
   // getIlluminationDirection only (illumination.cu)
   std::vector<double> sunPosition, sunVelocity;

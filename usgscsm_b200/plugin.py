@@ -100,7 +100,13 @@ class RasterGM(object):
         return [k for k, v in _MODEL_NAMES.items() if v == kind][0]
 
     def getModelState(self):
-        return self._state
+        """csm::Model::getModelState: the state with the current parameter values, parameter
+        covariance and ellipsoid written back."""
+        need = C.c_size_t()
+        check(lib.usgscsm_b200_model_get_state(self._h, None, 0, C.byref(need)))
+        buf = C.create_string_buffer(need.value)
+        check(lib.usgscsm_b200_model_get_state(self._h, buf, need.value, C.byref(need)))
+        return buf.raw[:need.value].decode("utf-8")
 
     def getImageSize(self):
         l, s = C.c_int(), C.c_int()
