@@ -78,20 +78,26 @@ struct GenericSpec {
   static constexpr bool kCommon = false;
   static constexpr int kDist = -1;
   static constexpr bool kColdOutOfLine = false;  // see lagrangeWeights
+  static constexpr int kAdj = -1;                // read hasAdj / hasAttAdj from the state
 };
 struct SearchSpec : GenericSpec {  // the line-scan search kernel, any model
   static constexpr bool kColdOutOfLine = true;
 };
-template <int DIST>
+// ADJ: 0 = no parameter is set, 1 = some are but none of the attitude ones (6..14),
+// 2 = attitude parameters too -- the state of a model after bundle adjustment.
+template <int DIST, int ADJ = 0>
 struct CommonSpec {
   static constexpr bool kCommon = true;
   static constexpr int kDist = DIST;
   static constexpr bool kColdOutOfLine = true;
+  static constexpr int kAdj = ADJ;
 };
 template <class SPEC>
-UB_DEV bool specHasAdj(const LsState &S) { return SPEC::kCommon ? false : S.hasAdj != 0; }
+UB_DEV bool specHasAdj(const LsState &S) { return SPEC::kAdj < 0 ? S.hasAdj != 0 : SPEC::kAdj > 0; }
 template <class SPEC>
-UB_DEV bool specHasAttAdj(const LsState &S) { return SPEC::kCommon ? false : S.hasAttAdj != 0; }
+UB_DEV bool specHasAttAdj(const LsState &S) {
+  return SPEC::kAdj < 0 ? S.hasAttAdj != 0 : SPEC::kAdj > 1;
+}
 
 // getValue(i, adj) with adj == _no_adjustment (LS:757-772 passes 16 zeros): the host packs
 // m_currentParameterValue[i] + 0.0.

@@ -172,7 +172,7 @@ UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const do
 // for such a model, scattered over 85 KB of code, and ncu shows the search kernel waiting on
 // instruction fetch (icc hit rate 88 %, "no instruction" 14 % of stall samples).
 // DIST = -1 is the generic kernel.  Same arithmetic either way.
-template <bool STAGE, int MINB, int DIST>
+template <bool STAGE, int MINB, int DIST, int ADJ = 0>
 __global__ void __launch_bounds__(kThreads, MINB)
     lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(kThreads, MINB)
                           double *__restrict__ achieved, uint32_t *__restrict__ status,
                           unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
-  using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST>, SearchSpec>::type;
+  using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST, ADJ>, SearchSpec>::type;
   if (STAGE) {
     StagedTables T = stageOrientationTables(S, specHasAdj<SPEC>(S), smem);
     lsGroundToImageLoop<SPEC>(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
@@ -577,30 +577,40 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   cudaError_t e = wc.acquire(stream);
   if (e != cudaSuccess) return e;
   unsigned long long *next = wc.ptr;
-#define UB_LAUNCH_G2I(STAGE, DIST)                                                            \
+#define UB_LAUNCH_G2I(STAGE, DIST, ADJ)                                                       \
   do {                                                                                        \
     if (smemBytes > 48 * 1024)                                                                \
-      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST>,             \
+      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ>,        \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
-    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST><<<sh.blocks, sh.threads, smemBytes, \
-                                                            stream>>>(                        \
-        S, n, x, y, z, prec, line, samp, achieved, status, next, grab);                       \
+    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ>                                \
+        <<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, x, y, z, prec, line, samp,       \
+                                                       achieved, status, next, grab);         \
+  } while (0)
+#define UB_LAUNCH_G2I_ADJ(STAGE, DIST)                                                        \
+  do {                                                                                        \
+    if (adj == 0) UB_LAUNCH_G2I(STAGE, DIST, 0);                                              \
+    else if (adj == 1) UB_LAUNCH_G2I(STAGE, DIST, 1);                                         \
+    else UB_LAUNCH_G2I(STAGE, DIST, 2);                                                       \
   } while (0)
 #define UB_LAUNCH_G2I_DIST(STAGE)                                                             \
   do {                                                                                        \
-    if (!common) UB_LAUNCH_G2I(STAGE, -1);                                                    \
-    else if (S.fp.distortionType == 4) UB_LAUNCH_G2I(STAGE, 4); /* LROLROCNAC */              \
-    else if (S.fp.distortionType == 0) UB_LAUNCH_G2I(STAGE, 0); /* RADIAL */                  \
-    else if (S.fp.distortionType == 1) UB_LAUNCH_G2I(STAGE, 1); /* TRANSVERSE */              \
-    else UB_LAUNCH_G2I(STAGE, -1);                                                            \
+    if (!common) UB_LAUNCH_G2I(STAGE, -1, 0);                                                 \
+    else if (S.fp.distortionType == 4) UB_LAUNCH_G2I_ADJ(STAGE, 4); /* LROLROCNAC */          \
+    else if (S.fp.distortionType == 0) UB_LAUNCH_G2I_ADJ(STAGE, 0); /* RADIAL */              \
+    else if (S.fp.distortionType == 1) UB_LAUNCH_G2I_ADJ(STAGE, 1); /* TRANSVERSE */          \
+    else UB_LAUNCH_G2I(STAGE, -1, 0);                                                         \
   } while (0)
+  // USGSCSM_B200_LS_SPECIALISE: 1 = specialise (default), 2 = only models without parameter
+  // adjustments, 3 = never
   static const int specialise = envInt("USGSCSM_B200_LS_SPECIALISE", 1);
-  const bool common = specialise == 1 && !S.hasAdj && !S.hasAttAdj && S.numIntTimes == 1 &&
+  const int adj = S.hasAttAdj ? 2 : (S.hasAdj ? 1 : 0);
+  const bool common = (specialise == 1 || (specialise == 2 && adj == 0)) && S.numIntTimes == 1 &&
                       S.useApproxInitTrans;
   if (stage)
     UB_LAUNCH_G2I_DIST(true);
   else
     UB_LAUNCH_G2I_DIST(false);
+#undef UB_LAUNCH_G2I_ADJ
 #undef UB_LAUNCH_G2I_DIST
 #undef UB_LAUNCH_G2I
   countLaunch();
