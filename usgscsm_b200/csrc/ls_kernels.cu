@@ -371,13 +371,16 @@ __global__ void __launch_bounds__(kThreads, MINB)
 // ---- computeGroundPartials ----------------------------------------------------------------
 // LS:1299-1325: groundToImage (default precision 0.001) at the point and at the point moved by
 // m_gsd along X, Y, Z; forward differences.  One kernel, four searches per point.
-template <bool STAGE>
+// DIST >= 0: the specialised search (one line-rate segment, projective seed, distortion DIST;
+// parameter adjustments read from the state), as in lsGroundToImageKernel.
+template <bool STAGE, int DIST>
 __global__ void __launch_bounds__(kThreads, kDefaultMinBlocks)
     lsGroundPartialsKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z,
                            double *__restrict__ partials, uint32_t *__restrict__ status,
                            unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
+  using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST, -1>, SearchSpec>::type;
   StagedTables TS{};
   OrientationTables TG{S.positions.values, S.velocities.values, S.quaternions.values};
   if (STAGE) TS = stageOrientationTables(S, S.hasAdj != 0, smem);
@@ -393,9 +396,9 @@ __global__ void __launch_bounds__(kThreads, kDefaultMinBlocks)
       double a;
       uint32_t sk = 0;
       if (STAGE)
-        lsGroundToImagePoint<false, StagedTables, SearchSpec>(S, TS, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+        lsGroundToImagePoint<false, StagedTables, SPEC>(S, TS, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
       else
-        lsGroundToImagePoint<false, OrientationTables, SearchSpec>(S, TG, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
+        lsGroundToImagePoint<false, OrientationTables, SPEC>(S, TG, q[0], q[1], q[2], 0.001, l[k], s[k], a, sk);
       st |= sk;
     }
     double p[6];
@@ -729,16 +732,30 @@ cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const 
   WorkCounter wc;
   cudaError_t e = wc.acquire(stream);
   if (e != cudaSuccess) return e;
-  if (stage) {
-    if (smemBytes > 48 * 1024)
-      cudaFuncSetAttribute(lsGroundPartialsKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)smemBytes);
-    lsGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());
-  } else {
-    lsGroundPartialsKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());
-  }
+#define UB_LAUNCH_GP(STAGE, DIST)                                                              \
+  do {                                                                                        \
+    if (smemBytes > 48 * 1024)                                                                \
+      cudaFuncSetAttribute(lsGroundPartialsKernel<STAGE, DIST>,                               \
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
+    lsGroundPartialsKernel<STAGE, DIST><<<sh.blocks, sh.threads, smemBytes, stream>>>(        \
+        S, n, x, y, z, partials, status, wc.ptr, grabSize());                                 \
+  } while (0)
+#define UB_LAUNCH_GP_DIST(STAGE)                                                              \
+  do {                                                                                        \
+    if (!common) UB_LAUNCH_GP(STAGE, -1);                                                     \
+    else if (S.fp.distortionType == 4) UB_LAUNCH_GP(STAGE, 4);                                \
+    else if (S.fp.distortionType == 0) UB_LAUNCH_GP(STAGE, 0);                                \
+    else if (S.fp.distortionType == 1) UB_LAUNCH_GP(STAGE, 1);                                \
+    else UB_LAUNCH_GP(STAGE, -1);                                                             \
+  } while (0)
+  static const int specialise = envInt("USGSCSM_B200_LS_SPECIALISE", 1);
+  const bool common = specialise == 1 && S.numIntTimes == 1 && S.useApproxInitTrans;
+  if (stage)
+    UB_LAUNCH_GP_DIST(true);
+  else
+    UB_LAUNCH_GP_DIST(false);
+#undef UB_LAUNCH_GP_DIST
+#undef UB_LAUNCH_GP
   countLaunch();
   return wc.release();
 }
