@@ -382,6 +382,9 @@ def run_b200(args):
                             "hbm_gbs": I2G_BYTES_PER_POINT * n / (i2g_kern_ms * 1e-3) / 1e9},
         "check": {"round_trip_max_px": err, "points_with_flags": flags},
     }
+    ncu = ncu_fp64()
+    if ncu:
+        result["roofline"]["fp64"]["ncu"] = ncu
     if world > 1:
         result["config"]["numa_bind"] = "rank 0 bound to NUMA node %s" % numa_node
 
@@ -434,6 +437,21 @@ def run_b200(args):
         print(json.dumps(result))
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_fp64():
+    """FP64 pipe utilisation of lsGroundToImageKernel from the committed ncu --set full capture
+    (profiles/ncu_g2i.json): share of cycles the pipe is busy and FP64 thread-instructions
+    issued per cycle against the 64 lanes x 148 SMs the chip can issue."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_g2i.json")
+    try:
+        with open(path) as f:
+            p = json.load(f)
+        return {"pipe_active_pct": p["fp64_pipe_active_pct"],
+                "issue_frac": p["fp64_thread_inst_per_cycle"] / p["fp64_issue_peak_per_cycle"],
+                "kernel_ms_under_ncu": p["duration_ms"], "source": "profiles/ncu_g2i.json"}
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def ncu_traffic(n):
