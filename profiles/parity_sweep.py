@@ -1,0 +1,78 @@
+"""Full-size parity sweep (not a pytest: it takes a minute of host CPU): every pixel of the C2
+line-scan image and large samples of the other models go image -> ground -> image through the
+engine on cuda:0 AND through the reference (oracle/_ref, all host threads); results are compared
+bit for bit and the counts are printed.  Run on the GPU box:
+    python profiles/parity_sweep.py > gpurun_out/r1_parity_sweep.txt
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import usgscsm_b200 as ub  # noqa: E402
+from oracle import ref  # noqa: E402
+from usgscsm_b200 import _capi, synth  # noqa: E402
+
+THREADS = len(os.sched_getaffinity(0))
+PREC = 1e-3
+
+
+def sweep(name, state, max_points, adjust=None):
+    gm = ub.UsgsAstroPlugin().constructModelFromState(state)
+    rm = ref.RefModel(state)
+    if adjust:
+        for i, v in adjust.items():
+            gm.setParameterValue(i, v)
+            rm.set_parameter(i, v)
+    if gm.getModelName() == "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL":
+        rm.ls_set_projective(True, gm.lsDerived()[5:19])
+    sz = gm.getImageSize()
+    nl, ns = int(sz.line), int(sz.samp)
+    step = max(1, int(np.ceil(nl * ns / max_points)))
+    rows = np.arange(0, nl, step, dtype=np.float64) + 0.5
+    line = np.repeat(rows, ns)
+    samp = np.tile(np.arange(ns, dtype=np.float64) + 0.5, rows.size)
+    h = synth.synthetic_dem(line, samp)
+    n = line.size
+    t = time.perf_counter()
+    gx, gy, gz, ga, gst = gm.imageToGroundBatch(line, samp, h, PREC)
+    gl, gs, ga2, gst2 = gm.groundToImageBatch(gx, gy, gz, PREC)
+    t_gpu = time.perf_counter() - t
+    t = time.perf_counter()
+    ex, ey, ez, ea, est = rm.image_to_ground(line, samp, h, PREC, threads=THREADS)
+    el, es, ea2, est2 = rm.ground_to_image(gx, gy, gz, PREC, threads=THREADS)
+    t_cpu = time.perf_counter() - t
+
+    def same(a, b):
+        return int(np.sum((a.view(np.uint64) != b.view(np.uint64)) & ~(np.isnan(a) & np.isnan(b))))
+    bad_i2g = same(gx, ex) + same(gy, ey) + same(gz, ez)
+    bad_g2i = same(gl, el) + same(gs, es)
+    bad_st = int(np.sum((gst & _capi.ST_REFERENCE_MASK) != est)) + int(np.sum((gst2 & _capi.ST_REFERENCE_MASK) != est2))
+    worst_m = float(np.nanmax(np.abs(np.stack([gx - ex, gy - ey, gz - ez])))) if n else 0.0
+    worst_px = float(np.nanmax(np.abs(np.stack([gl - el, gs - es])))) if n else 0.0
+    flagged = int(np.sum((est & ~np.uint32(_capi.ST_OUT_OF_IMAGE)) != 0)) + int(np.sum((est2 & ~np.uint32(_capi.ST_OUT_OF_IMAGE)) != 0))
+    print("%-34s %11d points  i2g coords differing in any bit: %d (max %.3g m)  g2i: %d (max %.3g px)  "
+          "status words differing: %d  points the reference flags: %d  [engine %.2f s host arrays, reference %.1f s on %d threads]"
+          % (name, n, bad_i2g, worst_m, bad_g2i, worst_px, bad_st, flagged, t_gpu, t_cpu, THREADS), flush=True)
+    return bad_i2g + bad_g2i + bad_st
+
+
+if __name__ == "__main__":
+    total = 0
+    # every 3rd line of the C2 grid: 88 M points keep the host arrays of both sides under 20 GB
+    total += sweep("linescan C2 5064x52224 (every 3rd line)", synth.linescan_state(), 100_000_000)
+    total += sweep("linescan C2, 6 parameters adjusted", synth.linescan_state(), 40_000_000,
+                   adjust={0: 2.5, 1: -1.5, 4: -0.02, 7: 1e-4, 11: 2e-6, 15: 0.03})
+    total += sweep("linescan radial 4096x4096", synth.linescan_state(n_lines=4096, n_samples=4096, seed=3,
+                                                                    distortion_type=synth.RADIAL, dist_coeffs=(1e-5, 2e-9, 0.0)), 1 << 40)
+    total += sweep("pushframe C3 4096x4096", synth.pushframe_state(n_framelets=256, framelet_height=16, n_samples=4096), 1 << 40)
+    total += sweep("frame radial C3 4096x4096", synth.frame_state(n_lines=4096, n_samples=4096), 1 << 40)
+    total += sweep("frame transverse 4096x4096", synth.frame_state(
+        n_lines=4096, n_samples=4096, distortion_type=synth.TRANSVERSE,
+        dist_coeffs=(0.0, 1.0, 0.0, 1e-6, 2e-6, -1e-6, 1e-8, 0.0, 2e-8, 0.0,
+                     0.0, 0.0, 1.0, -1e-6, 1e-6, 2e-6, 0.0, 1e-8, 0.0, -2e-8)), 1 << 40)
+    total += sweep("sar C4 64576x2367 (every 16th line)", synth.sar_state(), 10_000_000)
+    print("TOTAL differing values: %d" % total)
+    sys.exit(1 if total else 0)
