@@ -119,6 +119,12 @@ USGSCSM_B200_API int usgscsm_b200_model_get_state(const usgscsm_b200_model *m, c
  * at least that many (call with out = NULL to size the buffer).  Host only. */
 USGSCSM_B200_API int usgscsm_b200_state_to_msgpack(const char *state, size_t len, unsigned char *out,
                                   size_t cap, size_t *needed);
+/* The other direction: a state in any accepted encoding (msgpack, JSON text, .sup) ->
+ * "<model name>\n<JSON>", the text getModelState writes (json::from_msgpack + dump in the
+ * reference, bin/usgscsm_cam_test.cc:157-170).  Doubles with 17 significant digits: the text
+ * parses back to the same bits.  No device needed. */
+USGSCSM_B200_API int usgscsm_b200_state_to_json(const char *state, size_t len, char *out, size_t capacity,
+                               size_t *needed);
 /* csm::Model destructor. */
 USGSCSM_B200_API void usgscsm_b200_model_free(usgscsm_b200_model *m);
 /* USGSCSM_B200_MODEL_* */

@@ -108,3 +108,32 @@ def test_model_from_msgpack_equals_model_from_json(ref, kind):
     gb = b.groundToImageBatch(*rb[:3])
     for u, v in zip(ga, gb):
         assert np.array_equal(u, v, equal_nan=True)
+
+
+@pytest.mark.parametrize("kind", ["linescan", "pushframe", "frame", "sar"])
+def test_json_writer_round_trips_every_bit(kind):
+    """usgscsm_b200_state_to_json (the text getModelState writes): JSON -> JSON keeps the
+    document, msgpack -> JSON -> msgpack keeps the bytes, number kinds survive."""
+    from usgscsm_b200 import plugin
+    state = _states()[kind]
+    text = plugin.stateToJson(state)
+    head, body = text.split("\n", 1)
+    assert head == _json_part(state)["m_modelName"]
+    assert json.loads(body) == _json_part(state)
+    packed = plugin.stateToMsgpack(state)
+    assert plugin.stateToJson(packed) == text                    # either encoding in, same text out
+    assert plugin.stateToMsgpack(text) == packed                 # and back to the same bytes
+
+
+def test_json_writer_number_forms_and_escapes():
+    from usgscsm_b200 import plugin
+    doc = {"m_modelName": "USGS_ASTRO_FRAME_SENSOR_MODEL",
+           "ints": [0, -1, 65536, 4294967296, -2147483649], "floats": [0.1, 1e300, -2.5, 5e-324, 1.0, -0.0],
+           "mixed": [1, 2.5, "x", None, True, [1, 2.0]], "s": 'quote " backslash \\ newline \n tab \t',
+           "empty": [], "obj": {"k": [1.0, 2]}}
+    text = plugin.stateToJson(json.dumps(doc))
+    back = json.loads(text.split("\n", 1)[1])
+    assert back == doc
+    assert isinstance(back["floats"][4], float) and isinstance(back["ints"][0], int)
+    assert isinstance(back["obj"]["k"][0], float) and isinstance(back["obj"]["k"][1], int)
+    assert str(back["floats"][5]) == "-0.0"

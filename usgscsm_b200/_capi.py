@@ -43,6 +43,8 @@ SIGNATURES = {
     "usgscsm_b200_model_name_from_state": (C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]),
     "usgscsm_b200_state_to_msgpack": (
         C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "usgscsm_b200_state_to_json": (
+        C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "usgscsm_b200_model_free": (None, [_h]),
     "usgscsm_b200_model_kind": (C.c_int, [_h]),
     "usgscsm_b200_model_device": (C.c_int, [_h]),

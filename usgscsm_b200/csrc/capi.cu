@@ -234,6 +234,23 @@ int usgscsm_b200_state_to_msgpack(const char *state, size_t len, unsigned char *
   });
 }
 
+// The other direction: any accepted encoding (msgpack, JSON text, .sup) -> "<model name>\n<JSON>",
+// the text form getModelState writes (what json::from_msgpack + dump give in the reference,
+// bin/usgscsm_cam_test.cc:157-170).  No device needed.
+int usgscsm_b200_state_to_json(const char *state, size_t len, char *out, size_t cap,
+                               size_t *needed) {
+  if (!state || !needed) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return guarded([&]() -> int {
+    json::Value root = parseState(state, len);
+    StateReader st(root);
+    const std::string text = st.getString("m_modelName") + "\n" + json::dump(root);
+    *needed = text.size();
+    if (out && cap >= text.size()) std::memcpy(out, text.data(), text.size());
+    else if (out) return fail(USGSCSM_B200_EINVAL, "output buffer too small");
+    return USGSCSM_B200_OK;
+  });
+}
+
 void usgscsm_b200_model_free(usgscsm_b200_model *m) { delete m; }
 
 int usgscsm_b200_model_kind(const usgscsm_b200_model *m) { return m ? m->kind : 0; }

@@ -632,6 +632,17 @@ def stateToMsgpack(modelState):
     return buf.raw
 
 
+def stateToJson(modelState):
+    """A model state in any accepted encoding (msgpack bytes, JSON text, .sup) as
+    "<model name>\\n<JSON>" text, doubles written so that they parse back to the same bits."""
+    raw = modelState if isinstance(modelState, bytes) else modelState.encode("utf-8")
+    need = C.c_size_t()
+    check(lib.usgscsm_b200_state_to_json(raw, len(raw), None, 0, C.byref(need)))
+    buf = C.create_string_buffer(need.value)
+    check(lib.usgscsm_b200_state_to_json(raw, len(raw), buf, need.value, C.byref(need)))
+    return buf.raw[:need.value].decode("utf-8")
+
+
 # ---- building blocks (include/usgscsm/Distortion.h, Utilities.h of the reference) ------------
 def applyDistortion(ux, uy, opticalDistCoeffs, focalLength, distortionType,
                     desiredPrecision=1.0e-6, device=0):
