@@ -7,6 +7,8 @@
 // (cudaHostAlloc / cudaHostRegister / torch pin_memory); with pageable arrays the runtime
 // stages them and the calls still complete correctly.  The entry points differ only in which
 // arrays they move and which launcher they call; that is what they state below.
+#include <cstdlib>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -34,6 +36,41 @@ struct Chunk {
   cudaStream_t stream;
 };
 
+// USGSCSM_B200_PIPELINE_THREADS=0 keeps the pageable-array path on the calling thread.
+bool pipelineThreads() {
+  static const bool on = [] {
+    const char *v = getenv("USGSCSM_B200_PIPELINE_THREADS");
+    return !(v && v[0] == '0');
+  }();
+  return on;
+}
+
+// True when the first per-point input or the first output lives in ordinary (pageable) host
+// memory, i.e. not in cudaHostAlloc / cudaHostRegister memory.
+bool anyPageable(const std::vector<HostIn> &ins, const std::vector<HostOut> &outs) {
+  auto pageable = [](const void *p) {
+    if (!p) return false;
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+      cudaGetLastError();
+      return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+  };
+  bool in = false, out = false;
+  for (const HostIn &a : ins)
+    if (!a.broadcast) {
+      in = pageable(a.p);
+      break;
+    }
+  for (const HostOut &a : outs)
+    if (a.p) {
+      out = pageable(a.p);
+      break;
+    }
+  return in || out;
+}
+
 // launch(chunk) enqueues the kernels of one chunk on chunk.stream and returns a cudaError_t.
 // workPerPoint: extra device doubles per point the launch needs (AoS split / join).
 // granule: chunks hold a whole number of granules (image rows for the dense-grid call).
@@ -49,13 +86,12 @@ int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &in
     long perPoint = workPerPoint + 1;  // + status (half a double, rounded up)
     for (const HostIn &a : ins) perPoint += a.perPoint;
     for (const HostOut &a : outs) perPoint += a.perPoint;
-    long c = 0;
-    for (long off = 0; off < n; off += chunk, c++) {
+    const long nChunks = (n + chunk - 1) / chunk;
+    // One chunk through slot si: copies in, kernels, copies out, all on the slot's stream.
+    auto runChunk = [&](long c, int si) {
+      const long off = c * chunk;
       const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      const int si = (int)(c % nslots);
-      m->ensureScratch(si, chunk * perPoint);
       PipelineSlot &s = m->slots[si];
-      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));  // the slot's previous chunk
       Chunk k;
       k.offset = off;
       k.count = cnt;
@@ -85,9 +121,47 @@ int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &in
       if (status)
         UB_CUDA(cudaMemcpyAsync(status + off, k.status, cnt * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, s.stream));
+    };
+    const int used = (int)(nChunks < nslots ? nChunks : nslots);
+    for (int si = 0; si < used; si++) m->ensureScratch(si, chunk * perPoint);
+
+    // Pageable arrays: the runtime stages every copy through its own pinned buffer and the
+    // call returns only when that is done, so one host thread would run copy-in, kernel and
+    // copy-out of successive chunks back to back.  One host thread per slot lets chunks overlap
+    // (the staging of different streams proceeds concurrently).
+    if (used > 1 && pipelineThreads() && anyPageable(ins, outs)) {
+      std::vector<int> codes((size_t)used, USGSCSM_B200_OK);
+      std::vector<std::string> messages((size_t)used);
+      std::vector<std::thread> workers;
+      for (int t = 0; t < used; t++)
+        workers.emplace_back([&, t] {
+          codes[(size_t)t] = guarded([&]() -> int {
+            UB_CUDA(cudaSetDevice(m->device));
+            for (long c = t; c < nChunks; c += used) {
+              runChunk(c, t);
+              UB_CUDA(cudaStreamSynchronize(m->slots[t].stream));
+            }
+            return USGSCSM_B200_OK;
+          });
+          if (codes[(size_t)t] != USGSCSM_B200_OK) messages[(size_t)t] = lastError();
+        });
+      for (std::thread &w : workers) w.join();
+      for (int t = 0; t < used; t++)
+        if (codes[(size_t)t] != USGSCSM_B200_OK) {
+          lastError() = messages[(size_t)t];
+          return codes[(size_t)t];
+        }
+      return USGSCSM_B200_OK;
+    }
+
+    for (long c = 0; c < nChunks; c++) {
+      const int si = (int)(c % nslots);
+      PipelineSlot &s = m->slots[si];
+      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));  // the slot's previous chunk
+      runChunk(c, si);
       UB_CUDA(cudaEventRecord(s.done, s.stream));
     }
-    for (int si = 0; si < nslots && si < c; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
+    for (int si = 0; si < used; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
     return USGSCSM_B200_OK;
   });
 }
