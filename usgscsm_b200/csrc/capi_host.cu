@@ -36,8 +36,13 @@ struct Chunk {
   cudaStream_t stream;
 };
 
+// Set on the per-device worker threads of the _multi entry points: they already run one host
+// thread per device, each keeps its chunk pipeline on that thread.
+thread_local bool tlsSingleThreadPipeline = false;
+
 // USGSCSM_B200_PIPELINE_THREADS=0 keeps the pageable-array path on the calling thread.
 bool pipelineThreads() {
+  if (tlsSingleThreadPipeline) return false;
   static const bool on = [] {
     const char *v = getenv("USGSCSM_B200_PIPELINE_THREADS");
     return !(v && v[0] == '0');
@@ -473,6 +478,7 @@ int runOnModels(usgscsm_b200_model *const *models, int n_models, int64_t n, F &&
     workers.emplace_back([&, g]() {
       int64_t off, cnt;
       splitChunk(n, n_models, g, off, cnt);
+      tlsSingleThreadPipeline = true;
       codes[g] = call(models[g], off, cnt);
       if (codes[g] != USGSCSM_B200_OK) messages[g] = lastError();  // the worker thread's own copy
     });
