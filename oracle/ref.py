@@ -32,6 +32,11 @@ def lib():
         L.ref_max_threads.restype = C.c_int
         L.ref_model_from_state.restype = C.c_void_p
         L.ref_model_from_state.argtypes = [C.c_char_p, C.c_size_t]
+        L.ref_model_from_isd.restype = C.c_void_p
+        L.ref_model_from_isd.argtypes = [C.c_char_p, C.c_char_p]
+        L.ref_state_from_isd.restype = C.c_size_t
+        L.ref_state_from_isd.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+        L.ref_ls_refit_projective.argtypes = [C.c_void_p]
         L.ref_model_free.argtypes = [C.c_void_p]
         L.ref_model_state.restype = C.c_size_t
         L.ref_model_state.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
@@ -80,13 +85,32 @@ def _a(x, n=None):
 class RefModel(object):
     """A reference csm::RasterGM built by the reference plugin from a model-state string."""
 
-    def __init__(self, state):
-        raw = state if isinstance(state, bytes) else state.encode("utf-8")
+    def __init__(self, state, _handle=None):
         self._L = lib()
+        if _handle is not None:
+            self._h = _handle
+            return
+        raw = state if isinstance(state, bytes) else state.encode("utf-8")
         self._h = self._L.ref_model_from_state(raw, len(raw))
         if not self._h:
             raise RuntimeError("reference could not build the model: " +
                                self._L.ref_last_error().decode("utf-8", "replace"))
+
+    @classmethod
+    def from_isd(cls, image_path, model_name=None):
+        """UsgsAstroPlugin::constructModelFromISD(csm::Isd(image_path), model_name): the plugin
+        reads the sidecar <basename>.json next to the (possibly absent) image file."""
+        L = lib()
+        h = L.ref_model_from_isd(os.fsencode(image_path),
+                                 None if model_name is None else model_name.encode())
+        if not h:
+            raise RuntimeError("reference could not build the model from the ISD: " +
+                               L.ref_last_error().decode("utf-8", "replace"))
+        return cls(None, _handle=h)
+
+    def ls_refit_projective(self):
+        if self._L.ref_ls_refit_projective(self._h) != 0:
+            raise RuntimeError("not a line-scan model")
 
     def __del__(self):
         if getattr(self, "_h", None):
@@ -283,6 +307,19 @@ def state_to_msgpack(state):
     buf = C.create_string_buffer(n)
     L.ref_state_to_msgpack(raw, len(raw), buf, n)
     return buf.raw
+
+
+def state_from_isd(isd_text):
+    """<Model>::constructStateFromIsd of an ISD JSON text -> the state as a JSON string (before
+    populateModel derives anything)."""
+    L = lib()
+    raw = isd_text.encode("utf-8") if isinstance(isd_text, str) else isd_text
+    n = L.ref_state_from_isd(raw, len(raw), None, 0)
+    if n == 0:
+        raise RuntimeError(L.ref_last_error().decode("utf-8", "replace"))
+    buf = C.create_string_buffer(n)
+    L.ref_state_from_isd(raw, len(raw), buf, n)
+    return buf.raw.decode("utf-8")
 
 
 def max_threads():

@@ -119,7 +119,84 @@ void *ref_model_from_state(const char *state, size_t len) {
   }
 }
 
+// Build a model through the reference plugin from an ISD, exactly as the reference's test
+// fixtures do (/root/reference/tests/Fixtures.h:219-224): csm::Isd with the IMAGE file name,
+// the plugin reads the sidecar "<basename>.json" (src/UsgsAstroPlugin.cpp:324-353, 488-519).
+// model_name NULL / "" = the ISD's own "name_model" (UsgsAstroPlugin::getStateFromISD).
+void *ref_model_from_isd(const char *image_path, const char *model_name) {
+  try {
+    UsgsAstroPlugin plugin;
+    csm::Isd isd(image_path);
+    std::string name = model_name ? model_name : "";
+    if (name.empty()) {
+      nlohmann::json j = nlohmann::json::parse(plugin.loadImageSupportData(isd));
+      name = j.at("name_model").get<std::string>();
+    }
+    csm::Model *m = plugin.constructModelFromISD(isd, name, nullptr);
+    auto *rm = new RefModel;
+    rm->model.reset(m);
+    rm->gm = dynamic_cast<csm::RasterGM *>(m);
+    if (!rm->gm) {
+      delete rm;
+      g_lastError = "model is not a csm::RasterGM";
+      return nullptr;
+    }
+    return rm;
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return nullptr;
+  }
+}
+
+// <Model>::constructStateFromIsd of an ISD text (what the plugin hands to populateModel, BEFORE
+// the model derives gsd / reference point ...), serialised as JSON.  Returns the length; copies
+// up to cap bytes.  0 = failure (ref_last_error).
+size_t ref_state_from_isd(const char *isd_text, size_t len, char *out, size_t cap) {
+  try {
+    const std::string text(isd_text, len);
+    nlohmann::json j = nlohmann::json::parse(text);
+    const std::string name = j.at("name_model").get<std::string>();
+    VariantMap vm;
+    if (name == UsgsAstroFrameSensorModel::_SENSOR_MODEL_NAME) {
+      UsgsAstroFrameSensorModel m;
+      vm = m.constructStateFromIsd(text, nullptr);
+    } else if (name == UsgsAstroLsSensorModel::_SENSOR_MODEL_NAME) {
+      UsgsAstroLsSensorModel m;
+      vm = m.constructStateFromIsd(text, nullptr);
+    } else if (name == UsgsAstroPushFrameSensorModel::_SENSOR_MODEL_NAME) {
+      UsgsAstroPushFrameSensorModel m;
+      vm = m.constructStateFromIsd(text, nullptr);
+    } else if (name == UsgsAstroSarSensorModel::_SENSOR_MODEL_NAME) {
+      UsgsAstroSarSensorModel m;
+      vm = m.constructStateFromIsd(text, nullptr);
+    } else {
+      g_lastError = "unsupported model name " + name;
+      return 0;
+    }
+    const std::string s = jsonFromVariantMap(vm).dump();
+    if (out && cap >= s.size()) std::memcpy(out, s.data(), s.size());
+    return s.size();
+  } catch (const std::exception &e) {
+    g_lastError = e.what();
+    return 0;
+  }
+}
+
 void ref_model_free(void *h) { delete static_cast<RefModel *>(h); }
+
+// Re-run the reference's own createProjectiveApproximation (LS:2745-2803), e.g. after
+// ref_ls_set_projective replaced the seed.
+int ref_ls_refit_projective(void *h) {
+  RefModel *rm = static_cast<RefModel *>(h);
+  auto *ls = dynamic_cast<UsgsAstroLsSensorModel *>(rm->model.get());
+  if (!ls) return -1;
+  try {
+    ls->createProjectiveApproximation();
+  } catch (...) {
+    ls->m_useApproxInitTrans = false;
+  }
+  return 0;
+}
 
 // getModelState() of the live model; returns the length, copies up to cap bytes.
 size_t ref_model_state(void *h, char *out, size_t cap) {
