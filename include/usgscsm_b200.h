@@ -99,6 +99,27 @@ USGSCSM_B200_API int usgscsm_b200_device_count(void);
  * LS:2745-2803) are computed here by running the batch kernels on those points. */
 USGSCSM_B200_API int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
                                   usgscsm_b200_model **out);
+/* ---- ISD -> model state ---------------------------------------------
+ * Replaces <Model>::constructStateFromIsd (LS: src/UsgsAstroLsSensorModel.cpp:2818-3152, PF:
+ * src/UsgsAstroPushFrameSensorModel.cpp:2114-2463, FR: src/UsgsAstroFrameSensorModel.cpp:1660-1903,
+ * SAR: src/UsgsAstroSarSensorModel.cpp:52-230) and the ALE calls inside them: `isd` is the JSON
+ * text of an ALE-format ISD (what UsgsAstroPlugin::loadImageSupportData reads from the image's
+ * sidecar file, src/UsgsAstroPlugin.cpp:324-353); image_id (nullable) is stored as
+ * m_imageIdentifier, as loadImageSupportData does with the image's base name; model_name
+ * (nullable / "") defaults to the ISD's own "name_model" (UsgsAstroPlugin::getStateFromISD,
+ * src/UsgsAstroPlugin.cpp:459-463).  Writes "<model name>\n<JSON>", the state BEFORE the model
+ * derives its reference point / gsd (those are derived when the state is loaded, as in the
+ * reference).  Host only: no device needed.  Call with out = NULL to learn the size.
+ * USGSCSM_B200_ESTATE: the ISD cannot be converted (csm::Error SENSOR_MODEL_NOT_CONSTRUCTIBLE /
+ * ISD_NOT_SUPPORTED in the reference); the message names the missing key. */
+USGSCSM_B200_API int usgscsm_b200_state_from_isd(const char *isd, size_t len, const char *model_name,
+                                const char *image_id, char *out, size_t capacity,
+                                size_t *needed);
+/* UsgsAstroPlugin::constructModelFromISD (src/UsgsAstroPlugin.cpp:488-519) for the four
+ * un-projected models: usgscsm_b200_state_from_isd, then usgscsm_b200_model_from_state. */
+USGSCSM_B200_API int usgscsm_b200_model_from_isd(const char *isd, size_t len, const char *model_name,
+                                const char *image_id, int device, usgscsm_b200_model **out);
+
 /* UsgsAstroPlugin::getModelNameFromModelState (src/UsgsAstroPlugin.cpp:176-218): the value of
  * the "m_modelName" key, written NUL-terminated into name[cap].  Host only (no device needed).
  * USGSCSM_B200_ESTATE: no such key / unparsable; USGSCSM_B200_EUNSUPPORTED: not one of the

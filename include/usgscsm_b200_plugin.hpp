@@ -20,6 +20,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <cstdio>
 #include <exception>
 #include <list>
 #include <algorithm>
@@ -570,8 +571,8 @@ class RasterGM {
   std::string m_state;
 };
 
-// src/UsgsAstroPlugin.cpp: the factory.  Models are built from model-state strings
-// (constructModelFromISD needs ALE and is outside the hot path).
+// src/UsgsAstroPlugin.cpp: the factory.  Models are built from model-state strings or from
+// ISDs (converted on the host by usgscsm_b200_state_from_isd).
 class UsgsAstroPlugin {
  public:
   explicit UsgsAstroPlugin(int device = 0) : m_device(device) {}
@@ -623,6 +624,73 @@ class UsgsAstroPlugin {
       throw csm::Error(csm::Error::SENSOR_MODEL_NOT_CONSTRUCTIBLE, usgscsm_b200_last_error(),
                        "UsgsAstroPlugin::constructModelFromState");
     return new RasterGM(h, modelState);
+  }
+
+  // ---- ISD side (include/usgscsm/UsgsAstroPlugin.h:42-72) ------------------------------------
+  // loadImageSupportData :324-353: the csm::Isd names the IMAGE; the ISD is the sidecar
+  // "<base name>.json", and the image's base name becomes the image identifier.
+  static std::string loadImageSupportData(const std::string &imageFilename, std::string *identifier) {
+    std::string base = imageFilename.substr(0, imageFilename.find_last_of("."));
+    if (identifier) *identifier = base.substr(base.find_last_of("/") + 1);
+    const std::string isdFilename = base + ".json";
+    FILE *f = std::fopen(isdFilename.c_str(), "rb");
+    if (!f)
+      throw csm::Error(csm::Error::FILE_READ,
+                       "Could not read metadata file associated with image [" + isdFilename + "]",
+                       "UsgsAstroPlugin::loadImageSupportData");
+    std::string text;
+    char buf[1 << 16];
+    size_t got;
+    while ((got = std::fread(buf, 1, sizeof buf, f)) > 0) text.append(buf, got);
+    std::fclose(f);
+    return text;
+  }
+  // <Model>::constructStateFromIsd of the ISD text (host only; modelName "" = the ISD's own)
+  std::string constructStateFromIsd(const std::string &isdText, const std::string &modelName,
+                                    const std::string &imageIdentifier) const {
+    size_t need = 0;
+    const char *name = modelName.empty() ? NULL : modelName.c_str();
+    int code = usgscsm_b200_state_from_isd(isdText.data(), isdText.size(), name,
+                                           imageIdentifier.c_str(), NULL, 0, &need);
+    if (code != USGSCSM_B200_OK)
+      throw csm::Error(csm::Error::SENSOR_MODEL_NOT_CONSTRUCTIBLE, usgscsm_b200_last_error(),
+                       "constructStateFromIsd");
+    std::string state(need, '\0');
+    usgscsm_b200_state_from_isd(isdText.data(), isdText.size(), name, imageIdentifier.c_str(),
+                                &state[0], need, &need);
+    return state;
+  }
+  // :488-519 (the four un-projected models).  imageFilename is csm::Isd::filename().
+  RasterGM *constructModelFromISD(const std::string &imageFilename, const std::string &modelName,
+                                  csm::WarningList *warnings = NULL) const {
+    std::string ident;
+    const std::string isd = loadImageSupportData(imageFilename, &ident);
+    return constructModelFromState(constructStateFromIsd(isd, modelName, ident), warnings);
+  }
+  bool canModelBeConstructedFromISD(const std::string &imageFilename, const std::string &modelName,
+                                    csm::WarningList *warnings = NULL) const {  // :272-307
+    try {
+      RasterGM *m = constructModelFromISD(imageFilename, modelName, warnings);
+      delete m;
+      return true;
+    } catch (const std::exception &e) {
+      if (warnings)
+        warnings->push_back(csm::Warning(
+            csm::Warning::UNKNOWN_WARNING,
+            "Could not create model [" + modelName + "] with error [" + e.what() + "]",
+            "UsgsAstroPlugin::canModelBeConstructedFromISD()"));
+      return false;
+    }
+  }
+  std::string convertISDToModelState(const std::string &imageFilename, const std::string &modelName,
+                                     csm::WarningList *warnings = NULL) const {  // :465-472
+    RasterGM *m = constructModelFromISD(imageFilename, modelName, warnings);
+    std::string state = m->getModelState();
+    delete m;
+    return state;
+  }
+  std::string getStateFromISD(const std::string &imageFilename) const {  // :459-463
+    return convertISDToModelState(imageFilename, "");
   }
 
  private:

@@ -40,6 +40,11 @@ SIGNATURES = {
     "usgscsm_b200_last_error": (C.c_char_p, []),
     "usgscsm_b200_device_count": (C.c_int, []),
     "usgscsm_b200_model_from_state": (C.c_int, [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_h)]),
+    "usgscsm_b200_state_from_isd": (
+        C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t,
+                  C.POINTER(C.c_size_t)]),
+    "usgscsm_b200_model_from_isd": (
+        C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(_h)]),
     "usgscsm_b200_model_name_from_state": (C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]),
     "usgscsm_b200_state_to_msgpack": (
         C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),

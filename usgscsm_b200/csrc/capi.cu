@@ -140,6 +140,10 @@ cudaError_t launchImageToGround(Model &m, long n, const double *line, const doub
 
 namespace ub200 {
 void checkDistortionCoeffs(int type, size_t n);  // model_ls.cu
+namespace isd {  // isd_to_state.cpp
+std::string stateFromIsd(const char *isdText, size_t len, const std::string &modelName,
+                         const std::string &imageIdentifier);
+}
 }
 using namespace ub200;
 
@@ -199,6 +203,34 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
     *out = m.release();
     return USGSCSM_B200_OK;
   });
+}
+
+// constructStateFromIsd of the four models (isd_to_state.cpp).  Host only.
+int usgscsm_b200_state_from_isd(const char *isd, size_t len, const char *model_name,
+                                const char *image_id, char *out, size_t capacity,
+                                size_t *needed) {
+  if (!isd || !needed) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return guarded([&]() -> int {
+    const std::string text =
+        isd::stateFromIsd(isd, len, model_name ? model_name : "", image_id ? image_id : "");
+    *needed = text.size();
+    if (out && capacity >= text.size()) std::memcpy(out, text.data(), text.size());
+    else if (out) return fail(USGSCSM_B200_EINVAL, "output buffer too small");
+    return USGSCSM_B200_OK;
+  });
+}
+
+int usgscsm_b200_model_from_isd(const char *isd, size_t len, const char *model_name,
+                                const char *image_id, int device, usgscsm_b200_model **out) {
+  if (!isd || !out) return fail(USGSCSM_B200_EINVAL, "null argument");
+  *out = nullptr;
+  std::string text;
+  int rc = guarded([&]() -> int {
+    text = isd::stateFromIsd(isd, len, model_name ? model_name : "", image_id ? image_id : "");
+    return USGSCSM_B200_OK;
+  });
+  if (rc != USGSCSM_B200_OK) return rc;
+  return usgscsm_b200_model_from_state(text.data(), text.size(), device, out);
 }
 
 // getModelNameFromModelState (src/UsgsAstroPlugin.cpp:176-218).  Host only: no device needed.

@@ -124,6 +124,20 @@ int main(int argc, char **argv) {
   ub::UsgsAstroPlugin plugin(opt.device);
   std::unique_ptr<ub::RasterGM> model;
   try {
+    // isUsgsCsmIsd (src/Utilities.cpp:2977-3003): a JSON object with "body_rotation",
+    // "instrument_position" and a "USGS_ASTRO_..." model name is an ISD
+    const size_t first = model_state.find_first_not_of(" \t\n\r");
+    const size_t nm = model_state.find("\"USGS_ASTRO_");
+    if (first != std::string::npos && model_state[first] == '{' && nm != std::string::npos &&
+        model_state.find("\"body_rotation\"") != std::string::npos &&
+        model_state.find("\"instrument_position\"") != std::string::npos) {
+      const std::string isd_model_name =
+          model_state.substr(nm + 1, model_state.find("\"", nm + 1) - nm - 1);
+      std::cout << "Detected JSON ISD with model: " << isd_model_name << "\n";
+      model.reset(plugin.constructModelFromISD(opt.model, isd_model_name));
+      std::cout << "Loaded a CSM model of type " << isd_model_name << " from ISD file " << opt.model
+                << ".\n";
+    } else {
     std::string name = plugin.getModelNameFromModelState(model_state);
     const unsigned char b0 = model_state.empty() ? 0 : (unsigned char)model_state[0];
     if ((b0 >= 0x80 && b0 <= 0x8F) || b0 == 0xDE || b0 == 0xDF)  // isMsgpack, U:2511-2530
@@ -132,10 +146,10 @@ int main(int argc, char **argv) {
     model.reset(plugin.constructModelFromState(model_state));
     std::cout << "Loaded a CSM model of type " << name << " from model state file " << opt.model
               << ".\n";
+    }
   } catch (const ub::csm::Error &e) {
     std::cerr << "Failed to load a CSM model from: " << opt.model << " (" << e.getMessage()
-              << ").\nOnly model-state input (.json state, .sup) is supported; ISD input needs "
-                 "ALE.\n";
+              << ").\n";
     return 1;
   }
 

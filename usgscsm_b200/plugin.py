@@ -13,6 +13,7 @@ Every call, scalar or batched, runs on the GPU; there is no CPU path.
 """
 import collections
 import ctypes as C
+import os
 import json
 
 import numpy as np
@@ -619,6 +620,82 @@ class UsgsAstroPlugin(object):
                         "UsgsAstroPlugin::constructModelFromState")
         check(code)
         return RasterGM(h, modelState)
+
+
+    # ---- ISD side (include/usgscsm/UsgsAstroPlugin.h:42-72) ---------------------------------------
+    @staticmethod
+    def loadImageSupportData(imageSupportData):
+        """src/UsgsAstroPlugin.cpp:324-353: `imageSupportData` is a csm::Isd, i.e. the IMAGE file
+        name (a str / os.PathLike, or an object with .filename()); the ISD is the sidecar
+        "<base name>.json" next to it.  Returns (ISD text, image identifier)."""
+        name = imageSupportData.filename() if hasattr(imageSupportData, "filename") else os.fspath(imageSupportData)
+        base = name[:name.rfind(".")] if "." in name else name
+        ident = base[base.rfind(os.sep) + 1:]
+        try:
+            with open(base + ".json", "rb") as f:
+                return f.read(), ident
+        except OSError as e:
+            raise Error(Error.FILE_READ, "Could not read metadata file associated with image [%s.json] "
+                        "with error [%s]" % (base, e), "UsgsAstroPlugin::loadImageSupportData")
+
+    def _state_from_isd(self, imageSupportData, modelName, function):
+        text, ident = self.loadImageSupportData(imageSupportData)
+        need = C.c_size_t()
+        name = None if not modelName else modelName.encode("ascii")
+        code = lib.usgscsm_b200_state_from_isd(text, len(text), name, ident.encode("utf-8"), None, 0,
+                                               C.byref(need))
+        if code == _capi.ESTATE:
+            raise Error(Error.SENSOR_MODEL_NOT_CONSTRUCTIBLE,
+                        lib.usgscsm_b200_last_error().decode("utf-8", "replace"), function)
+        check(code)
+        buf = C.create_string_buffer(need.value)
+        check(lib.usgscsm_b200_state_from_isd(text, len(text), name, ident.encode("utf-8"), buf,
+                                              need.value, C.byref(need)))
+        return buf.raw[:need.value].decode("utf-8")
+
+    def constructModelFromISD(self, imageSupportData, modelName, warnings=None, device=None):
+        """src/UsgsAstroPlugin.cpp:488-519 for the four un-projected models: ISD -> state
+        (constructStateFromIsd, on the host) -> model on the device."""
+        state = self._state_from_isd(imageSupportData, modelName, "UsgsAstroPlugin::constructModelFromISD")
+        return self.constructModelFromState(state, warnings, device)
+
+    def canModelBeConstructedFromISD(self, imageSupportData, modelName, warnings=None):
+        """src/UsgsAstroPlugin.cpp:272-307: true when the model can be built; otherwise a warning
+        with the reason is appended."""
+        try:
+            self.constructModelFromISD(imageSupportData, modelName, warnings)
+            return True
+        except (Error, RuntimeError) as e:
+            if warnings is not None:
+                warnings.append(Warning(Warning.UNKNOWN_WARNING,
+                                        "Could not create model [%s] with error [%s]" % (modelName, e),
+                                        "UsgsAstroPlugin::canModelBeConstructedFromISD()"))
+            return False
+
+    def convertISDToModelState(self, imageSupportData, modelName, warnings=None):
+        """src/UsgsAstroPlugin.cpp:465-472: the state of the model built from the ISD (with what
+        the model derived at load written back)."""
+        return self.constructModelFromISD(imageSupportData, modelName, warnings).getModelState()
+
+    def canISDBeConvertedToModelState(self, imageSupportData, modelName, warnings=None):
+        try:
+            self.convertISDToModelState(imageSupportData, modelName, warnings)
+            return True
+        except (Error, RuntimeError) as e:
+            if warnings is not None:
+                warnings.append(Warning(Warning.UNKNOWN_WARNING,
+                                        "Could not create model [%s] state with error [%s]" % (modelName, e),
+                                        "UsgsAstroPlugin::canISDBeConvertedToModelState()"))
+            return False
+
+    def getStateFromISD(self, imageSupportData):
+        """src/UsgsAstroPlugin.cpp:459-463: convertISDToModelState with the ISD's own name_model."""
+        return self.convertISDToModelState(imageSupportData, None)
+
+    def constructStateFromIsd(self, imageSupportData, modelName=None):
+        """<Model>::constructStateFromIsd: the state BEFORE the model derives anything.  Host only
+        (no CUDA device needed)."""
+        return self._state_from_isd(imageSupportData, modelName, "constructStateFromIsd")
 
 
 def stateToMsgpack(modelState):
