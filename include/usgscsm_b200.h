@@ -442,6 +442,15 @@ USGSCSM_B200_API int usgscsm_b200_lagrange_interp(int device, int num_time, cons
 USGSCSM_B200_API int usgscsm_b200_selftest_division(int device, int64_t pairs, uint64_t seed,
                                    uint64_t *mismatches);
 
+/* Measures the FP64 pipe the kernels are bound by (the roofline denominator of bench.py): a
+ * dependent-free stream of one instruction kind on every SM for at least min_ms of kernel time.
+ * op 0 = DFMA, 1 = DADD, 2 = DMUL, 3 = DADD / DMUL alternating (the mix the engine's bit-exact
+ * arithmetic -- no FMA contraction, like the reference's x86-64 build -- can issue).  Writes FP64
+ * thread-instructions per second (DFMA: x 2 for flops) and, nullable, the device's nominal SM
+ * clock in MHz. */
+USGSCSM_B200_API int usgscsm_b200_measure_fp64(int device, int op, double min_ms,
+                              double *instructions_per_second, double *sm_clock_mhz);
+
 /* Number of kernels this library has launched on the calling process so far (all models,
  * all streams).  bench.py reports the difference over its timed region as gpu_launches. */
 USGSCSM_B200_API int64_t usgscsm_b200_kernel_launches(void);

@@ -118,3 +118,37 @@ def test_frame_model_is_refused():
     with pytest.raises(_capi.EngineError) as e:
         gm.groundToImageCovarBatch(np.zeros(2), np.zeros(2), np.zeros(2), np.zeros((2, 9)))
     assert e.value.code == _capi.EUNSUPPORTED
+
+
+@pytest.mark.parametrize("kind", ["linescan", "pushframe"])
+def test_default_covariance_from_update_state(ref, kind):
+    """a state with m_gsd == 1.0 && m_flyingHeight == 1000.0 (every ISD-fresh state,
+    every synth state) makes updateState REPLACE m_covariance by a gsd-derived diagonal
+    (LS:697-735, PF:660-690).  No setParameterCovariance here: the error-propagation outputs,
+    getParameterCovariance and getModelState's m_covariance must match the reference's."""
+    import json
+    from usgscsm_b200 import synth
+    state = _cases()[kind]
+    gm, rm = models(ref, state)
+    if kind == "linescan":
+        rm.ls_set_projective(True, gm.lsDerived()[5:19])
+    want = np.array(json.loads(rm.state().split("\n", 1)[1])["m_covariance"])
+    got = np.array(json.loads(gm.getModelState().split("\n", 1)[1])["m_covariance"])
+    assert want.shape == got.shape == (256,)
+    assert np.count_nonzero(want) == 16 and want[0] != 1.0        # not the state's identity
+    np.testing.assert_allclose(got, want, rtol=1e-12, atol=0.0)
+    assert gm.getParameterCovariance(3, 3) == pytest.approx(want[3 * 16 + 3], rel=1e-12)
+    rng = np.random.default_rng(8)
+    nl, ns = rm.image_size()
+    line, samp = pixels(rng, 800, nl, ns)
+    x, y, z, _, _ = gm.imageToGroundBatch(line, samp, synth.synthetic_dem(line, samp))
+    gcov = _spd(rng, 800, 3, 2.0)
+    l, s, ic, a, st = gm.groundToImageCovarBatch(x, y, z, gcov)
+    rl, rs, ric, ra, rst = rm.ground_to_image_covar(x, y, z, gcov)
+    ok = np.isfinite(rl)
+    assert ok.all() and np.abs(l - rl).max() <= PX_TOL and np.abs(s - rs).max() <= PX_TOL
+    assert _close(ic.reshape(-1, 4), ric, ok)
+    # the sensor term is not negligible: it must show in the image covariance
+    gm.setParameterCovariance(0, 0, 0.0)
+    l2, s2, ic2, _, _ = gm.groundToImageCovarBatch(x, y, z, gcov)
+    assert np.abs(ic2.reshape(-1, 4) - ic.reshape(-1, 4)).max() > 1e-6

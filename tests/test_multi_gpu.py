@@ -105,3 +105,43 @@ def test_concurrent_host_threads_on_different_models():
         for got in results[k]:
             for u, v in zip(got, expect[k]):
                 assert np.array_equal(u, v, equal_nan=True)
+
+
+def test_concurrent_host_threads_on_the_same_model():
+    """The reference's const per-point calls are re-entrant on ONE model object (SURVEY.md §5,
+    include/usgscsm/UsgsAstroLsSensorModel.h:910-914).  Host-pointer calls on one handle share
+    the handle's pipeline slots; they are serialised by a per-model mutex, so threads
+    hammering the same handle with DIFFERENT inputs -- batches and single points -- must each
+    get their own answers."""
+    from usgscsm_b200 import synth
+    gm = _models(synth.linescan_state(n_lines=4096, n_samples=1024, seed=5), 1)[0]
+    rng = np.random.default_rng(9)
+    nthreads = 6
+    work, expect = [], []
+    for k in range(nthreads):
+        n = 5_000_000 if k == 0 else (1 if k == 1 else 300_000 + 1000 * k)   # several chunks / one point / one chunk
+        line, samp = rng.uniform(0, 4096, n), rng.uniform(0, 1024, n)
+        h = rng.uniform(-300, 300, n)
+        x, y, z, a, st = gm.imageToGroundBatch(line, samp, h)
+        work.append((line, samp, h))
+        expect.append((x, y, z, st) + tuple(gm.groundToImageBatch(x, y, z)[:2]))
+    results = [None] * nthreads
+
+    def run(k):
+        out = []
+        for _ in range(4 if k else 2):
+            line, samp, h = work[k]
+            x, y, z, a, st = gm.imageToGroundBatch(line, samp, h)
+            l, s, _, _ = gm.groundToImageBatch(x, y, z)
+            out.append((x, y, z, st, l, s))
+        results[k] = out
+
+    threads = [threading.Thread(target=run, args=(k,)) for k in range(nthreads)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for k in range(nthreads):
+        for got in results[k]:
+            for u, v in zip(got, expect[k]):
+                assert np.array_equal(u, v, equal_nan=True)

@@ -180,6 +180,8 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
       UB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
     }
     m->modelName = st.getString("m_modelName");
+    // before the loaders: updateState replaces it for states that ask to be derived (LS:283-285)
+    m->covariance = st.getVecDouble("m_covariance", std::vector<double>());
     if (m->modelName == "USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL") {
       m->kind = USGSCSM_B200_MODEL_LINE_SCANNER;
       loadLineScanner(*m, st);
@@ -196,7 +198,6 @@ int usgscsm_b200_model_from_state(const char *state, size_t len, int device,
       g_lastError = "unsupported model name: " + m->modelName;
       return USGSCSM_B200_EUNSUPPORTED;
     }
-    m->covariance = st.getVecDouble("m_covariance", std::vector<double>());
     loadSun(*m, st);
     m->stateTree = root;
     UB_CUDA(cudaDeviceSynchronize());

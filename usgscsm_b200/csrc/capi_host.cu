@@ -8,6 +8,7 @@
 // stages them and the calls still complete correctly.  The entry points differ only in which
 // arrays they move and which launcher they call; that is what they state below.
 #include <cstdlib>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -84,6 +85,10 @@ int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &in
                  const std::vector<HostOut> &outs, uint32_t *status, int workPerPoint,
                  Launch &&launch, long granule = 1) {
   return guarded([&]() -> int {
+    // the slots (scratch, streams, events) belong to the model: one host-pointer call at a time
+    // per handle; a second thread calling on the same handle waits here (the reference's const
+    // per-point calls are re-entrant, include/usgscsm/UsgsAstroLsSensorModel.h:910-914)
+    std::lock_guard<std::mutex> oneCallPerModel(m->hostCallMutex);
     UB_CUDA(cudaSetDevice(m->device));
     const int nslots = pipelineSlots();
     long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();

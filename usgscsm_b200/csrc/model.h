@@ -8,6 +8,7 @@
 
 #include <cuda_runtime.h>
 
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -88,6 +89,10 @@ struct Model {
   std::vector<DeviceBuffer> owned;
   double *frameletOrient = nullptr;  // push-frame: device table behind ls.frameletOrient
   PipelineSlot slots[kMaxPipelineSlots];
+  // Host-pointer entry points share the slots' scratch and streams: one call at a time per model
+  // (capi_host.cu runPipelined).  Concurrent host threads on ONE handle are therefore safe and
+  // serialised; threads on different handles run concurrently.
+  std::mutex hostCallMutex;
 
   ~Model();
   const double *upload(const std::vector<double> &v);
@@ -97,6 +102,7 @@ struct Model {
 // model_ls.cu
 void loadLineScanner(Model &m, const class StateReader &st);
 void repackLineScanner(Model &m);  // after a parameter / projective-seed change
+void fillDefaultCovariance(std::vector<double> &cov, double gsd);  // updateState LS:703-734
 LsState adjustedLineScanner(const Model &m, int index, double delta);
 // model_pf.cu
 void loadPushFrame(Model &m, const class StateReader &st);

@@ -30,6 +30,10 @@ void fillFocalPlaneInverse(FocalPlane &fp) {
   fp.p22 = fp.iTransL[1] / determinant;
 }
 
+}  // namespace
+void fillDefaultCovariance(std::vector<double> &cov, double gsd);
+namespace {
+
 void fillEllipsoid(Ellipsoid &e, double a, double b) {
   e.majorAxis = a;
   e.minorAxis = b;
@@ -52,7 +56,7 @@ void imageToGroundFew(Model &m, int n, const double *line, const double *samp, d
   UB_CUDA(cudaMemcpy(z, dz, n * sizeof(double), cudaMemcpyDeviceToHost));
 }
 
-// updateState LS:649-735 (the members the hot path reads; the covariance is not one).
+// updateState LS:649-735.
 void updateStateLs(Model &m) {
   LsState &S = m.ls;
   const double lineCtr = S.nLines / 2.0;
@@ -80,7 +84,28 @@ void updateStateLs(Model &m) {
   double fullImageTime = m.intTimeStartTimes.back() - m.intTimeStartTimes.front() +
                          m.intTimes.back() * (S.nLines - m.intTimeLines.back());
   S.halfTime = fullImageTime / 2.0;
+  fillDefaultCovariance(m.covariance, S.gsd);
 }
+
+}  // namespace
+
+// Parameter covariance updateState hard-codes ("~1 pixel accuracy", LS:703-734, PF:660-690):
+// a diagonal from the freshly derived gsd.  Read by the error-propagation entry points and
+// written back by getModelState.
+void fillDefaultCovariance(std::vector<double> &cov, double gsd) {
+  const int n = 16;
+  const double positionVariance = gsd * gsd;
+  const double velocityVariance = positionVariance / 2.0;      // parameter time spans [0, 2]
+  const double accelerationVariance = positionVariance / 4.0;
+  cov.assign((size_t)n * n, 0.0);
+  for (int i = 0; i < n; i++) {
+    const bool rate = (i >= 3 && i <= 5) || (i >= 9 && i <= 11);
+    const bool accel = i >= 12 && i <= 14;
+    cov[(size_t)i * n + i] = accel ? accelerationVariance : (rate ? velocityVariance : positionVariance);
+  }
+}
+
+namespace {
 
 // createProjectiveApproximation LS:2745-2803
 void createProjectiveApproximationLs(Model &m) {

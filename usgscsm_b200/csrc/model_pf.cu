@@ -35,7 +35,7 @@ void buildFrameletOrientations(Model &m) {
   S.frameletOrient = m.frameletOrient;
 }
 
-// updateState PF:605-676 (the members the hot path reads).
+// updateState PF:605-690.
 void updateStatePf(Model &m) {
   LsState &S = m.ls;
   S.frameletOrient = nullptr;
@@ -75,6 +75,7 @@ void updateStatePf(Model &m) {
   double fullImageTime = S.startingEphemerisTime + (S.numFramelets - 1) * S.interframeDelay +
                          S.exposureDuration;
   S.halfTime = fullImageTime / 2.0;
+  fillDefaultCovariance(m.covariance, S.gsd);  // PF:660-690, same diagonal as the line-scan model
 }
 
 }  // namespace
