@@ -323,6 +323,16 @@ USGSCSM_B200_API int usgscsm_b200_image_sensor_state_dev(usgscsm_b200_model *m, 
                                         double *pz, double *vx, double *vy, double *vz,
                                         uint32_t *status, void *stream);
 
+/* getSensorPosition(double time) / getSensorVelocity(double time) for arrays of image times
+ * (LS:1599-1653, PF:1281-1320, SAR:1160-1260; frame FR:707-795: the only valid time is 0.0,
+ * any other gets USGSCSM_B200_ST_ERROR_OTHER = csm::Error::BOUNDS and NaN outputs). */
+USGSCSM_B200_API int usgscsm_b200_sensor_state_at_time(usgscsm_b200_model *m, int64_t n, const double *time,
+                                      double *px, double *py, double *pz, double *vx, double *vy,
+                                      double *vz, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_sensor_state_at_time_dev(usgscsm_b200_model *m, int64_t n, const double *time,
+                                          double *px, double *py, double *pz, double *vx,
+                                          double *vy, double *vz, uint32_t *status, void *stream);
+
 /* getIlluminationDirection(const csm::EcefCoord&) for arrays (LS:1878-1899, PF:1477-1498,
  * SAR:1095-1102, FR:643-652): the unit vector from the sun to the ground point at the time the
  * point was imaged (frame model: ground - sun, not normalised, as the reference returns it).

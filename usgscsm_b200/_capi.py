@@ -61,6 +61,8 @@ SIGNATURES = {
     "usgscsm_b200_model_get_ellipsoid": (C.c_int, [_h, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "usgscsm_b200_model_ls_derived": (C.c_int, [_h, C.POINTER(C.c_double)]),
     "usgscsm_b200_model_ls_set_projective": (C.c_int, [_h, C.c_int, C.POINTER(C.c_double)]),
+    "usgscsm_b200_sensor_state_at_time": (C.c_int, [_h, C.c_int64] + [_dp] * 8),
+    "usgscsm_b200_sensor_state_at_time_dev": (C.c_int, [_h, C.c_int64] + [_dp] * 9),
     "usgscsm_b200_measure_fp64": (
         C.c_int, [C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "usgscsm_b200_ground_to_image": (

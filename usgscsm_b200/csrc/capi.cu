@@ -740,13 +740,35 @@ int usgscsm_b200_image_sensor_state_dev(usgscsm_b200_model *m, int64_t n, const 
   if (!line || !samp) return fail(USGSCSM_B200_EINVAL, "null array");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
-    SensorStateOut o{time, px, py, pz, vx, vy, vz, status};
+    SensorStateOut o{time, px, py, pz, vx, vy, vz, status, 0};
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     switch (m->kind) {
       case USGSCSM_B200_MODEL_LINE_SCANNER: UB_CUDA(launchLsSensorState(m->ls, (long)n, line, o, s)); break;
       case USGSCSM_B200_MODEL_PUSH_FRAME: UB_CUDA(launchPfSensorState(m->ls, (long)n, line, o, s)); break;
       case USGSCSM_B200_MODEL_FRAME: UB_CUDA(launchFrSensorState(m->fr, (long)n, line, samp, o, s)); break;
       default: UB_CUDA(launchSarSensorState(m->sar, (long)n, line, o, s)); break;
+    }
+    return USGSCSM_B200_OK;
+  });
+}
+
+// getSensorPosition(double time) / getSensorVelocity(double time) for arrays of image times
+// (LS:1599-1653, PF:1281-1320, FR:707-795, SAR:1160-1260).
+int usgscsm_b200_sensor_state_at_time_dev(usgscsm_b200_model *m, int64_t n, const double *time,
+                                          double *px, double *py, double *pz, double *vx,
+                                          double *vy, double *vz, uint32_t *status, void *stream) {
+  if (!m || n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (!time) return fail(USGSCSM_B200_EINVAL, "null array");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    SensorStateOut o{nullptr, px, py, pz, vx, vy, vz, status, 1};
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (m->kind) {
+      case USGSCSM_B200_MODEL_LINE_SCANNER: UB_CUDA(launchLsSensorState(m->ls, (long)n, time, o, s)); break;
+      case USGSCSM_B200_MODEL_PUSH_FRAME: UB_CUDA(launchPfSensorState(m->ls, (long)n, time, o, s)); break;
+      case USGSCSM_B200_MODEL_FRAME: UB_CUDA(launchFrSensorState(m->fr, (long)n, time, time, o, s)); break;
+      default: UB_CUDA(launchSarSensorState(m->sar, (long)n, time, o, s)); break;
     }
     return USGSCSM_B200_OK;
   });

@@ -397,6 +397,22 @@ int usgscsm_b200_image_sensor_state(usgscsm_b200_model *m, int64_t n, const doub
                       });
 }
 
+int usgscsm_b200_sensor_state_at_time(usgscsm_b200_model *m, int64_t n, const double *time,
+                                      double *px, double *py, double *pz, double *vx, double *vy,
+                                      double *vz, uint32_t *status) {
+  int rc;
+  if (badCall(m, n, rc)) return rc;
+  if (!time) return fail(USGSCSM_B200_EINVAL, "null array");
+  return runPipelined(m, n, {{time, 1, false}},
+                      {{px, 1}, {py, 1}, {pz, 1}, {vx, 1}, {vy, 1}, {vz, 1}}, status, 0,
+                      [&](const Chunk &k) {
+                        int r = usgscsm_b200_sensor_state_at_time_dev(
+                            m, k.count, k.in[0], k.out[0], k.out[1], k.out[2], k.out[3], k.out[4],
+                            k.out[5], k.status, k.stream);
+                        return r == USGSCSM_B200_OK ? cudaSuccess : cudaErrorUnknown;
+                      });
+}
+
 int usgscsm_b200_illumination_direction(usgscsm_b200_model *m, int64_t n, const double *x,
                                         const double *y, const double *z, double *dx, double *dy,
                                         double *dz, uint32_t *status) {

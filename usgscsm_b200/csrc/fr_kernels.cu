@@ -302,10 +302,20 @@ __global__ void frSensorStateKernel(const __grid_constant__ FrameState S, long n
                                     const double *__restrict__ samp, SensorStateOut o) {
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double l = line[i], sm = samp[i];
     double pos[3] = {S.rawParams[0], S.rawParams[1], S.rawParams[2]};
     double vel[3] = {S.spacecraftVelocity[0], S.spacecraftVelocity[1], S.spacecraftVelocity[2]};
     uint32_t st = 0;
+    if (o.atTime) {
+      // getSensorPosition(double) / getSensorVelocity(double) FR:707-745, 769-795: the only valid
+      // image time is 0.0, anything else throws csm::Error::BOUNDS
+      if (line[i] != 0.0) {
+        st = USGSCSM_B200_ST_ERROR_OTHER;
+        pos[0] = pos[1] = pos[2] = vel[0] = vel[1] = vel[2] = nan("");
+      }
+      storeSensorState(o, i, line[i], pos, vel, st);
+      continue;
+    }
+    const double l = line[i], sm = samp[i];
     if ((o.vx || o.vy || o.vz) && (sm < 0.0 || sm > S.nSamples || l < 0.0 || l > S.nLines)) {
       st = USGSCSM_B200_ST_ERROR_OTHER;
       vel[0] = vel[1] = vel[2] = nan("");

@@ -74,6 +74,7 @@ __device__ __forceinline__ void storePartials(double *__restrict__ partials,
 struct SensorStateOut {
   double *time, *px, *py, *pz, *vx, *vy, *vz;
   uint32_t *status;
+  int atTime;  // the input array holds image TIMES (getSensorPosition(double time)), not lines
 };
 #ifdef __CUDACC__
 __device__ __forceinline__ void storeSensorState(const SensorStateOut &o, long i, double time,

@@ -518,7 +518,7 @@ __global__ void lsSensorStateKernel(const __grid_constant__ LsState S, long n,
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double time = lsImageTime(S, line[i]);
+    const double time = o.atTime ? line[i] : lsImageTime(S, line[i]);
     double pos[3], vel[3], posV[3], unused[3];
     adjSensorPosVel<false>(S, T, time, pos, unused);
     adjSensorPosVel<true>(S, T, time, posV, vel);

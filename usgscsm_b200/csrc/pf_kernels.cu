@@ -479,7 +479,7 @@ __global__ void pfSensorStateKernel(const __grid_constant__ LsState S, long n,
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double time = pfFrameletTime(S, pfTimeFramelet(S, line[i]));
+    const double time = o.atTime ? line[i] : pfFrameletTime(S, pfTimeFramelet(S, line[i]));
     double pos[3], vel[3];
     adjSensorPosVel<true>(S, T, time, pos, vel);
     storeSensorState(o, i, time, pos, vel, 0u);

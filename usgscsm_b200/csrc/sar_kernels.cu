@@ -519,7 +519,8 @@ __global__ void sarSensorStateKernel(const __grid_constant__ SarState S, long n,
   SarTables T = stageSarTables(S, nullptr, false);
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double time = S.startingEphemerisTime + (line[i] - 0.5) * S.exposureDuration;
+    const double time =
+        o.atTime ? line[i] : S.startingEphemerisTime + (line[i] - 0.5) * S.exposureDuration;
     double pos[3], vel[3];
     sarPosVel(S, T, time, pos, vel);
     storeSensorState(o, i, time, pos, vel, 0u);
