@@ -63,7 +63,7 @@ def test_findplugin_state_sup(ref):
     pts = _points(rng, 40000, 20000, 400)
     out, state, log = _run("state", os.path.join(G.DATA, "gxp_model_file.sup"), pts)
     assert "plugin UsgsAstroPluginCSM by UsgsAstrogeology, 4 models" in log
-    assert "model USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL family Raster pedigree USGS_LINE_SCANNER" in log
+    assert "model USGS_ASTRO_LINE_SCANNER_SENSOR_MODEL family GeometricRaster pedigree USGS_LINE_SCANNER" in log
     assert "image 40000 x 20000 params 16 [IT Pos. Bias   ] sensor EO/PUSHBROOM" in log
     _compare(ref, out, state, pts)
 

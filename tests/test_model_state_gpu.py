@@ -35,6 +35,12 @@ def test_state_round_trip_after_adjustment(ref, kind):
     assert head == state.split("\n", 1)[0]
     derived = ("m_gsd", "m_flyingHeight", "m_halfSwath", "m_halfTime", "m_referencePointXyz")
     got, exp = json.loads(body), json.loads(state.split("\n", 1)[1])
+    if kind in ("linescan", "pushframe"):
+        # a state with the default gsd / flying height also gets its parameter covariance from
+        # updateState (LS:697-714): compare that with what the REFERENCE model reports
+        derived += ("m_covariance",)
+        ref_cov = json.loads(ref.RefModel(state).state().split("\n", 1)[1])["m_covariance"]
+        assert np.allclose(got["m_covariance"], ref_cov, rtol=1e-12, atol=0)
     assert {k: v for k, v in got.items() if k not in derived} == {k: v for k, v in exp.items() if k not in derived}
     if kind == "frame":   # absolute position parameters: move relative to the current value
         changes = {0: gm.getParameterValue(0) + 12.0, 2: gm.getParameterValue(2) + 7.0}

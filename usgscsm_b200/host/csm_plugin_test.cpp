@@ -85,11 +85,19 @@ int main(int argc, char **argv) {
     std::cerr << "not a csm::RasterGM\n";
     return 1;
   }
+  // the line-scan / push-frame / SAR models project their reference point to date the image
+  // (SAR:1732-1741); a state whose reference point does not project makes that call throw
+  std::string date;
+  try {
+    date = gm->getReferenceDateAndTime();
+  } catch (const csm::Error &e) {
+    date = "<csm::Error: " + e.getMessage() + ">";
+  }
   std::cout << "model " << gm->getModelName() << " family " << gm->getFamily() << " pedigree "
             << gm->getPedigree() << " image " << gm->getImageSize().line << " x "
             << gm->getImageSize().samp << " params " << gm->getNumParameters() << " ["
             << gm->getParameterName(0) << "] sensor " << gm->getSensorType() << "/" << gm->getSensorMode()
-            << " id " << gm->getImageIdentifier() << " date " << gm->getReferenceDateAndTime() << "\n";
+            << " id " << gm->getImageIdentifier() << " date " << date << "\n";
   const long n = std::atol(argv[5]);
   std::vector<double> pts((size_t)n * 3), out((size_t)n * 10);
   FILE *f = std::fopen(argv[4], "rb");
