@@ -66,6 +66,9 @@ extern "C" {
 #define USGSCSM_B200_ST_NONFINITE (1u << 7)         /* an output coordinate is NaN/Inf           */
 #define USGSCSM_B200_ST_OUT_OF_IMAGE (1u << 8)      /* g2i result outside getValidImageRange()   */
 #define USGSCSM_B200_ST_ERROR_OTHER (1u << 9)
+/* DEM entry points only (no counterpart in the reference: its callers own the DEM) */
+#define USGSCSM_B200_ST_DEM_NODATA (1u << 10)  /* the DEM sample (or a bilinear neighbour) is nodata */
+#define USGSCSM_B200_ST_DEM_OUTSIDE (1u << 11) /* the ray left the DEM raster                        */
 /* Bits 16-23 (diagnostic): how many times the root search of groundToImage evaluated its
  * function for this point (line-scan: detector views of the secant search; push-frame: frame
  * distances; SAR: Doppler evaluations of Brent's method).  bench.py derives the algorithmic
@@ -418,6 +421,132 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid(usgscsm_b200_model *m, do
                                       int64_t n_samps, const double *height, int height_stride,
                                       double prec, double *x, double *y, double *z,
                                       double *achieved, uint32_t *status);
+
+/* ---- georeferenced grids: the callers either side of the path ------------
+ * What an orthorectifier does around groundToImage / imageToGround, and what
+ * UsgsAstroProjectedSensorModel wraps around a camera (src/UsgsAstroProjectedSensorModel.cpp:
+ * 289-365): raster pixel -> map coordinates by the GDAL geotransform (pixelToMeter / meterToPixel,
+ * src/Utilities.cpp:2720-2745; gt[2] and gt[4] are ignored as there) -> geographic coordinates by
+ * the inverse map projection -> body-fixed cartesian coordinates.  The reference delegates the
+ * last two steps to PROJ (proj_trans of "+proj=<...>" to "+proj=geocent +a +b",
+ * UsgsAstroProjectedSensorModel.cpp:128-147); the engine evaluates three projections itself with
+ * PROJ's arithmetic (PROJ/src/conversions/cart.cpp, projections/eqc.cpp, projections/gn_sinu.cpp,
+ * mlfn.cpp, fwd.cpp, inv.cpp as vendored with the reference). */
+#define USGSCSM_B200_PROJ_LONGLAT 0 /* +proj=longlat: map x = longitude, y = latitude, degrees */
+#define USGSCSM_B200_PROJ_EQC 1     /* +proj=eqc  (+lat_ts +lat_0 +lon_0 +x_0 +y_0)            */
+#define USGSCSM_B200_PROJ_SINU 2    /* +proj=sinu (+lon_0 +x_0 +y_0), sphere or ellipsoid      */
+
+typedef struct usgscsm_b200_geogrid {
+  double geotransform[6]; /* GDAL order (m_geoTransform): x = gt[0] + samp * gt[1], y = gt[3] + line * gt[5] */
+  int projection;         /* USGSCSM_B200_PROJ_*                                                 */
+  int reserved;
+  double lat_ts_deg, lat_0_deg, lon_0_deg; /* eqc: +lat_ts +lat_0; eqc / sinu: +lon_0             */
+  double x_0, y_0;                         /* false easting / northing, metres                  */
+  double proj_semi_major, proj_semi_minor; /* ellipsoid of the projected CRS (+R, or +a +b)     */
+  double semi_major, semi_minor; /* ellipsoid of the cartesian step; 0 = the projection's.  The
+                                    projected sensor model passes the camera's radii
+                                    (UsgsAstroProjectedSensorModel.cpp:131-139)                  */
+} usgscsm_b200_geogrid;
+
+/* Fills *out from a PROJ string (m_projString) and a geotransform.  Supported: +proj=longlat
+ * (latlong, lonlat, latlon) | eqc | sinu with +lat_ts +lat_0 +lon_0 +x_0 +y_0 +R | +a +b | +a +rf |
+ * +a +f, +units=m, +no_defs, +type=crs.  Anything else: USGSCSM_B200_EUNSUPPORTED.  cart_a / cart_b:
+ * radii of the cartesian step (0 = the projection's ellipsoid).  Host only. */
+USGSCSM_B200_API int usgscsm_b200_geogrid_from_proj_string(const char *proj_string,
+                                                          const double geotransform[6], double cart_a,
+                                                          double cart_b, usgscsm_b200_geogrid *out);
+
+/* UsgsAstroProjectedSensorModel::imageToGround(ImageCoord, height, ...)
+ * (src/UsgsAstroProjectedSensorModel.cpp:329-365) for arrays: raster (line, samp) -> body-fixed
+ * (x, y, z).  height: nullable (0 for every point, what the reference effectively uses), n entries
+ * when height_stride = 1, one when 0.  status (nullable): USGSCSM_B200_ST_NONFINITE outside the
+ * projection's domain.  `device`: the CUDA device to run on (host flavour) / the arrays live on. */
+USGSCSM_B200_API int usgscsm_b200_geogrid_image_to_ground(const usgscsm_b200_geogrid *grid, int device,
+                                                         int64_t n, const double *line, const double *samp,
+                                                         const double *height, int height_stride,
+                                                         double *x, double *y, double *z, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_geogrid_image_to_ground_dev(const usgscsm_b200_geogrid *grid, int device,
+                                                             int64_t n, const double *line, const double *samp,
+                                                             const double *height, int height_stride,
+                                                             double *x, double *y, double *z, uint32_t *status,
+                                                             void *stream);
+/* UsgsAstroProjectedSensorModel::groundToImage(EcefCoord, ...)
+ * (src/UsgsAstroProjectedSensorModel.cpp:289-321): body-fixed (x, y, z) -> raster (line, samp);
+ * height (nullable) receives the height above the ellipsoid PROJ's geodetic conversion yields. */
+USGSCSM_B200_API int usgscsm_b200_geogrid_ground_to_image(const usgscsm_b200_geogrid *grid, int device,
+                                                         int64_t n, const double *x, const double *y,
+                                                         const double *z, double *line, double *samp,
+                                                         double *height, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_geogrid_ground_to_image_dev(const usgscsm_b200_geogrid *grid, int device,
+                                                             int64_t n, const double *x, const double *y,
+                                                             const double *z, double *line, double *samp,
+                                                             double *height, uint32_t *status, void *stream);
+
+/* A DEM raster: heights above the ellipsoid on a georeferenced grid. */
+#define USGSCSM_B200_DEM_F64 0
+#define USGSCSM_B200_DEM_F32 1
+#define USGSCSM_B200_DEM_I16 2
+typedef struct usgscsm_b200_dem {
+  const void *samples;  /* n_rows x n_cols, row-major; HOST memory for the plain entry points,
+                           DEVICE memory for the _dev ones                                         */
+  int sample_type;      /* USGSCSM_B200_DEM_*                                                      */
+  int has_nodata;
+  double nodata;        /* raw sample value that marks a hole                                      */
+  double scale, offset; /* height = raw * scale + offset (GDAL band scale / offset; 1, 0 = metres) */
+  int64_t n_rows, n_cols;
+  usgscsm_b200_geogrid grid;
+} usgscsm_b200_dem;
+
+/* The ground points of a DEM window -- rows row0 .. row0 + n_rows - 1, columns col0 .. col0 +
+ * n_cols - 1, pixel centres (row + 0.5, col + 0.5), point k = r * n_cols + c -- as the chain
+ * above gives them with height = the sample.  For longlat and eqc grids the trigonometry is
+ * evaluated once per row and per column ON THE HOST with the C library (the functions PROJ
+ * calls), so the result equals PROJ's cart conversion of the pixel bit for bit; sinu is
+ * evaluated per pixel with CUDA's sin / cos (<= 2 ulp).  Nodata samples: NaN and
+ * USGSCSM_B200_ST_DEM_NODATA. */
+USGSCSM_B200_API int usgscsm_b200_dem_ground_points(const usgscsm_b200_dem *dem, int device, int64_t row0,
+                                                   int64_t col0, int64_t n_rows, int64_t n_cols, double *x,
+                                                   double *y, double *z, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_dem_ground_points_dev(const usgscsm_b200_dem *dem, int device, int64_t row0,
+                                                       int64_t col0, int64_t n_rows, int64_t n_cols,
+                                                       double *x, double *y, double *z, uint32_t *status,
+                                                       void *stream);
+
+/* Orthorectification's inner loop in one call: groundToImage of every ground point of a DEM
+ * window (as above), the ground points generated in the kernel -- 2 / 4 / 8 bytes per point go
+ * up the host link instead of 24.  Line-scan models run one fused kernel; the other models a
+ * ground-point kernel and their groundToImage kernel.  Outputs as usgscsm_b200_ground_to_image;
+ * a nodata sample gives NaN and USGSCSM_B200_ST_DEM_NODATA | USGSCSM_B200_ST_NONFINITE. */
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_dem_grid(usgscsm_b200_model *m, const usgscsm_b200_dem *dem,
+                                                          int64_t row0, int64_t col0, int64_t n_rows,
+                                                          int64_t n_cols, double prec, double *line,
+                                                          double *samp, double *achieved, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_dem_grid_dev(usgscsm_b200_model *m,
+                                                              const usgscsm_b200_dem *dem, int64_t row0,
+                                                              int64_t col0, int64_t n_rows, int64_t n_cols,
+                                                              double prec, double *line, double *samp,
+                                                              double *achieved, uint32_t *status,
+                                                              void *stream);
+
+/* DEM-iterated ground intersection: imageToGround of each pixel at the height of the DEM where
+ * the ray meets it, by the fixed point callers of the reference run around imageToGround(height):
+ *   h = h0;  repeat { P = imageToGround(pixel, h);  (lon, lat) = geodetic(P);
+ *                     hn = DEM bilinear at (lon, lat);  if |hn - h| <= tolerance stop;  h = hn }
+ * at most max_iterations times (1..64).  The DEM is sampled bilinearly between pixel centres.
+ * Outputs: the ground point, the height it was computed at (nullable), status: the bits of the
+ * last imageToGround, USGSCSM_B200_ST_DEM_OUTSIDE / _DEM_NODATA where the ray leaves the raster
+ * or meets a hole (the point of the last height is returned), USGSCSM_B200_ST_ITERATION_CAP
+ * when the height did not settle.  The plain flavour uploads the whole DEM once per call. */
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_dem(usgscsm_b200_model *m, const usgscsm_b200_dem *dem,
+                                                     int64_t n, const double *line, const double *samp,
+                                                     double h0, double tolerance, int max_iterations,
+                                                     double prec, double *x, double *y, double *z,
+                                                     double *height, uint32_t *status);
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_dem_dev(usgscsm_b200_model *m, const usgscsm_b200_dem *dem,
+                                                         int64_t n, const double *line, const double *samp,
+                                                         double h0, double tolerance, int max_iterations,
+                                                         double prec, double *x, double *y, double *z,
+                                                         double *height, uint32_t *status, void *stream);
 
 /* ---- building blocks of the per-point math, batched -------------------------------------
  * The reference exposes these as free functions and tests them directly

@@ -5,5 +5,5 @@ reached through the C-ABI of include/usgscsm_b200.h.  This package is the thin h
 of the reference's plugin interface; it has no CPU implementation of the math.
 """
 from . import _capi, synth  # noqa: F401  (_capi raises ImportError when the .so is missing)
-from .plugin import (EcefCoord, Error, ImageCoord, RasterGM, UsgsAstroPlugin,  # noqa: F401
-                     Warning, applyDistortion, lagrangeInterp, removeDistortion)
+from .plugin import (Dem, EcefCoord, Error, GeoGrid, ImageCoord, RasterGM,  # noqa: F401
+                     UsgsAstroPlugin, Warning, applyDistortion, lagrangeInterp, removeDistortion)

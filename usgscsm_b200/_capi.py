@@ -26,6 +26,8 @@ ST_ERROR_UNKNOWN = 1 << 6
 ST_NONFINITE = 1 << 7
 ST_OUT_OF_IMAGE = 1 << 8
 ST_ERROR_OTHER = 1 << 9
+ST_DEM_NODATA = 1 << 10
+ST_DEM_OUTSIDE = 1 << 11
 ST_EVALS_SHIFT = 16
 ST_EVALS_MASK = 0xff << 16
 ST_REFERENCE_MASK = (ST_NO_INTERSECTION | ST_PRECISION_NOT_MET | ST_ERROR_ALGORITHM |
@@ -33,6 +35,29 @@ ST_REFERENCE_MASK = (ST_NO_INTERSECTION | ST_PRECISION_NOT_MET | ST_ERROR_ALGORI
 
 _dp = C.c_void_p  # double* / uint32_t* / stream, passed as raw addresses
 _h = C.c_void_p   # usgscsm_b200_model*
+
+PROJ_LONGLAT, PROJ_EQC, PROJ_SINU = 0, 1, 2
+DEM_F64, DEM_F32, DEM_I16 = 0, 1, 2
+
+
+class GeoGrid(C.Structure):
+    """usgscsm_b200_geogrid"""
+    _fields_ = [("geotransform", C.c_double * 6), ("projection", C.c_int), ("reserved", C.c_int),
+                ("lat_ts_deg", C.c_double), ("lat_0_deg", C.c_double), ("lon_0_deg", C.c_double),
+                ("x_0", C.c_double), ("y_0", C.c_double),
+                ("proj_semi_major", C.c_double), ("proj_semi_minor", C.c_double),
+                ("semi_major", C.c_double), ("semi_minor", C.c_double)]
+
+
+class Dem(C.Structure):
+    """usgscsm_b200_dem"""
+    _fields_ = [("samples", C.c_void_p), ("sample_type", C.c_int), ("has_nodata", C.c_int),
+                ("nodata", C.c_double), ("scale", C.c_double), ("offset", C.c_double),
+                ("n_rows", C.c_int64), ("n_cols", C.c_int64), ("grid", GeoGrid)]
+
+
+_gp = C.POINTER(GeoGrid)
+_demp = C.POINTER(Dem)
 
 # name -> (restype, argtypes); the order follows include/usgscsm_b200.h
 SIGNATURES = {
@@ -127,6 +152,31 @@ SIGNATURES = {
     "usgscsm_b200_image_to_ground_grid": (
         C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
                   C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_geogrid_from_proj_string": (
+        C.c_int, [C.c_char_p, C.POINTER(C.c_double), C.c_double, C.c_double, _gp]),
+    "usgscsm_b200_geogrid_image_to_ground": (
+        C.c_int, [_gp, C.c_int, C.c_int64, _dp, _dp, _dp, C.c_int, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_geogrid_image_to_ground_dev": (
+        C.c_int, [_gp, C.c_int, C.c_int64, _dp, _dp, _dp, C.c_int, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_geogrid_ground_to_image": (
+        C.c_int, [_gp, C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_geogrid_ground_to_image_dev": (
+        C.c_int, [_gp, C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_dem_ground_points": (
+        C.c_int, [_demp, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_dem_ground_points_dev": (
+        C.c_int, [_demp, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_dem_grid": (
+        C.c_int, [_h, _demp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_double, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_dem_grid_dev": (
+        C.c_int, [_h, _demp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_double, _dp, _dp, _dp, _dp,
+                  _dp]),
+    "usgscsm_b200_image_to_ground_dem": (
+        C.c_int, [_h, _demp, C.c_int64, _dp, _dp, C.c_double, C.c_double, C.c_int, C.c_double,
+                  _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_dem_dev": (
+        C.c_int, [_h, _demp, C.c_int64, _dp, _dp, C.c_double, C.c_double, C.c_int, C.c_double,
+                  _dp, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_apply_distortion": (
         C.c_int, [C.c_int, C.c_int, _dp, C.c_int, C.c_double, C.c_double, C.c_int64, _dp, _dp, _dp,
                   _dp, _dp]),

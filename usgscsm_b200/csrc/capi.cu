@@ -51,8 +51,10 @@ int grabSize() {
 Model::~Model() {
   cudaSetDevice(device);
   for (DeviceBuffer &b : owned) cudaFree(b.ptr);
+  for (GeoTables &t : geoTables) cudaFree(t.dev);
   for (PipelineSlot &s : slots) {
     cudaFree(s.scratch);
+    if (s.stage) cudaFreeHost(s.stage);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
   }
@@ -77,6 +79,16 @@ void Model::ensureScratch(int s, long doubles) {
   p.scratchDoubles = 0;
   UB_CUDA(cudaMalloc(&p.scratch, doubles * sizeof(double)));
   p.scratchDoubles = doubles;
+}
+
+void Model::ensureStage(int s, long bytes) {
+  PipelineSlot &p = slots[s];
+  if (p.stageBytes >= bytes) return;
+  if (p.stage) cudaFreeHost(p.stage);
+  p.stage = nullptr;
+  p.stageBytes = 0;
+  UB_CUDA(cudaHostAlloc(&p.stage, (size_t)bytes, cudaHostAllocDefault));
+  p.stageBytes = bytes;
 }
 
 // ---- error plumbing (capi_common.h) --------------------------------------------------------
@@ -454,7 +466,7 @@ int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, d
   if (!height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
   return guarded([&]() -> int {
     UB_CUDA(cudaSetDevice(m->device));
-    GridSpec g{line0, samp0, dline, dsamp, (long)n_samps};
+    GridSpec g{line0, samp0, dline, dsamp, (long)n_samps, 0};
     UB_CUDA(launchImageToGround(*m, (long)(n_lines * n_samps), nullptr, nullptr, &g, height,
                                 height_stride ? 1 : 0, prec, x, y, z, achieved, status,
                                 static_cast<cudaStream_t>(stream)));

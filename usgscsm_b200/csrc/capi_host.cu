@@ -8,40 +8,17 @@
 // stages them and the calls still complete correctly.  The entry points differ only in which
 // arrays they move and which launcher they call; that is what they state below.
 #include <cstdlib>
-#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
 
 #include "capi_common.h"
+#include "pipeline.cuh"
 
 namespace ub200 {
-namespace {
 
-struct HostIn {
-  const double *p;  // host array
-  int perPoint;     // doubles per point (3 for an array of csm::EcefCoord)
-  bool broadcast;   // one value for all points (height_stride = 0): a single double is copied
-};
-struct HostOut {
-  double *p;  // host array; nullptr = the caller does not want it (device pointer is null too)
-  int perPoint;
-};
-
-// Device views of one chunk inside a slot's scratch, handed to the launch callback.
-struct Chunk {
-  long offset;  // index of the chunk's first point in the caller's arrays
-  long count;
-  std::vector<double *> in, out, work;
-  uint32_t *status;  // null when the caller passed no status array
-  cudaStream_t stream;
-};
-
-// Set on the per-device worker threads of the _multi entry points: they already run one host
-// thread per device, each keeps its chunk pipeline on that thread.
 thread_local bool tlsSingleThreadPipeline = false;
 
-// USGSCSM_B200_PIPELINE_THREADS=0 keeps the pageable-array path on the calling thread.
 bool pipelineThreads() {
   if (tlsSingleThreadPipeline) return false;
   static const bool on = [] {
@@ -50,145 +27,32 @@ bool pipelineThreads() {
   }();
   return on;
 }
-
-// True when the first per-point input or the first output lives in ordinary (pageable) host
-// memory, i.e. not in cudaHostAlloc / cudaHostRegister memory.
-bool anyPageable(const std::vector<HostIn> &ins, const std::vector<HostOut> &outs) {
-  auto pageable = [](const void *p) {
-    if (!p) return false;
-    cudaPointerAttributes a{};
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-      cudaGetLastError();
-      return true;
-    }
-    return a.type == cudaMemoryTypeUnregistered;
-  };
-  bool in = false, out = false;
-  for (const HostIn &a : ins)
-    if (!a.broadcast) {
-      in = pageable(a.p);
-      break;
-    }
-  for (const HostOut &a : outs)
-    if (a.p) {
-      out = pageable(a.p);
-      break;
-    }
-  return in || out;
+static long envLongHost(const char *name, long def, long lo, long hi) {
+  const char *v = getenv(name);
+  long x = v && *v ? atol(v) : def;
+  return x < lo ? lo : (x > hi ? hi : x);
+}
+int stagedSlots() {
+  static const int n = (int)envLongHost("USGSCSM_B200_STAGE_THREADS", 8, 1, kMaxPipelineSlots);
+  return n;
+}
+long stagedChunk() {
+  static const long n = envLongHost("USGSCSM_B200_STAGE_CHUNK", 1L << 20, 1024, 1L << 26);
+  return n;
 }
 
-// launch(chunk) enqueues the kernels of one chunk on chunk.stream and returns a cudaError_t.
-// workPerPoint: extra device doubles per point the launch needs (AoS split / join).
-// granule: chunks hold a whole number of granules (image rows for the dense-grid call).
-template <class Launch>
-int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &ins,
-                 const std::vector<HostOut> &outs, uint32_t *status, int workPerPoint,
-                 Launch &&launch, long granule = 1) {
-  return guarded([&]() -> int {
-    // the slots (scratch, streams, events) belong to the model: one host-pointer call at a time
-    // per handle; a second thread calling on the same handle waits here (the reference's const
-    // per-point calls are re-entrant, include/usgscsm/UsgsAstroLsSensorModel.h:910-914)
-    std::lock_guard<std::mutex> oneCallPerModel(m->hostCallMutex);
-    UB_CUDA(cudaSetDevice(m->device));
-    const int nslots = pipelineSlots();
-    long chunk = n < pipelineChunk() ? (long)n : pipelineChunk();
-    if (granule > 1) chunk = chunk < granule ? granule : chunk / granule * granule;
-    long perPoint = workPerPoint + 1;  // + status (half a double, rounded up)
-    for (const HostIn &a : ins) perPoint += a.perPoint;
-    for (const HostOut &a : outs) perPoint += a.perPoint;
-    const long nChunks = (n + chunk - 1) / chunk;
-    // One chunk through slot si: copies in, kernels, copies out, all on the slot's stream.
-    auto runChunk = [&](long c, int si) {
-      const long off = c * chunk;
-      const long cnt = (n - off) < chunk ? (long)(n - off) : chunk;
-      PipelineSlot &s = m->slots[si];
-      Chunk k;
-      k.offset = off;
-      k.count = cnt;
-      k.stream = s.stream;
-      double *next = s.scratch;
-      for (const HostIn &a : ins) {
-        k.in.push_back(next);
-        if (a.broadcast)
-          UB_CUDA(cudaMemcpyAsync(next, a.p, sizeof(double), cudaMemcpyHostToDevice, s.stream));
-        else
-          UB_CUDA(cudaMemcpyAsync(next, a.p + off * a.perPoint, cnt * a.perPoint * sizeof(double),
-                                  cudaMemcpyHostToDevice, s.stream));
-        next += chunk * a.perPoint;
-      }
-      for (const HostOut &a : outs) {
-        k.out.push_back(a.p ? next : nullptr);
-        next += chunk * a.perPoint;
-      }
-      for (int w = 0; w < workPerPoint; w++, next += chunk) k.work.push_back(next);
-      k.status = status ? reinterpret_cast<uint32_t *>(next) : nullptr;
-      UB_CUDA(launch(k));
-      for (size_t j = 0; j < outs.size(); j++)
-        if (outs[j].p)
-          UB_CUDA(cudaMemcpyAsync(outs[j].p + off * outs[j].perPoint, k.out[j],
-                                  cnt * outs[j].perPoint * sizeof(double), cudaMemcpyDeviceToHost,
-                                  s.stream));
-      if (status)
-        UB_CUDA(cudaMemcpyAsync(status + off, k.status, cnt * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-    };
-    const int used = (int)(nChunks < nslots ? nChunks : nslots);
-    for (int si = 0; si < used; si++) m->ensureScratch(si, chunk * perPoint);
-
-    // Pageable arrays: the runtime stages every copy through its own pinned buffer and the
-    // call returns only when that is done, so one host thread would run copy-in, kernel and
-    // copy-out of successive chunks back to back.  One host thread per slot lets chunks overlap
-    // (the staging of different streams proceeds concurrently).
-    if (used > 1 && pipelineThreads() && anyPageable(ins, outs)) {
-      std::vector<int> codes((size_t)used, USGSCSM_B200_OK);
-      std::vector<std::string> messages((size_t)used);
-      std::vector<std::thread> workers;
-      for (int t = 0; t < used; t++)
-        workers.emplace_back([&, t] {
-          codes[(size_t)t] = guarded([&]() -> int {
-            UB_CUDA(cudaSetDevice(m->device));
-            for (long c = t; c < nChunks; c += used) {
-              runChunk(c, t);
-              UB_CUDA(cudaStreamSynchronize(m->slots[t].stream));
-            }
-            return USGSCSM_B200_OK;
-          });
-          if (codes[(size_t)t] != USGSCSM_B200_OK) messages[(size_t)t] = lastError();
-        });
-      for (std::thread &w : workers) w.join();
-      for (int t = 0; t < used; t++)
-        if (codes[(size_t)t] != USGSCSM_B200_OK) {
-          lastError() = messages[(size_t)t];
-          return codes[(size_t)t];
-        }
-      return USGSCSM_B200_OK;
-    }
-
-    for (long c = 0; c < nChunks; c++) {
-      const int si = (int)(c % nslots);
-      PipelineSlot &s = m->slots[si];
-      if (c >= nslots) UB_CUDA(cudaEventSynchronize(s.done));  // the slot's previous chunk
-      runChunk(c, si);
-      UB_CUDA(cudaEventRecord(s.done, s.stream));
-    }
-    for (int si = 0; si < used; si++) UB_CUDA(cudaStreamSynchronize(m->slots[si].stream));
-    return USGSCSM_B200_OK;
-  });
-}
-
-bool badCall(usgscsm_b200_model *m, int64_t n, int &rc) {
-  if (!m || n < 0) {
-    rc = fail(USGSCSM_B200_EINVAL, "bad argument");
+// True when p lives in ordinary (pageable) host memory, i.e. not in cudaHostAlloc /
+// cudaHostRegister memory.
+bool hostPointerPageable(const void *p) {
+  if (!p) return false;
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
     return true;
   }
-  if (n == 0) {
-    rc = USGSCSM_B200_OK;
-    return true;
-  }
-  return false;
+  return a.type == cudaMemoryTypeUnregistered;
 }
 
-}  // namespace
 }  // namespace ub200
 
 using namespace ub200;
@@ -239,7 +103,7 @@ int usgscsm_b200_image_to_ground_grid(usgscsm_b200_model *m, double line0, doubl
   return runPipelined(
       m, n_lines * n_samps, {{height, 1, hs == 0}}, {{x, 1}, {y, 1}, {z, 1}, {achieved, 1}}, status, 0,
       [&](const Chunk &k) {
-        GridSpec g{line0 + (double)(k.offset / n_samps) * dline, samp0, dline, dsamp, (long)n_samps};
+        GridSpec g{line0, samp0, dline, dsamp, (long)n_samps, (long)(k.offset / n_samps)};
         return launchImageToGround(*m, k.count, nullptr, nullptr, &g, k.in[0], hs, prec, k.out[0],
                                    k.out[1], k.out[2], k.out[3], k.status, k.stream);
       },

@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kThreads)
     if (GRID) {
       long r = i / g.nSamps;
       long c = i - r * g.nSamps;
-      l = g.line0 + (double)r * g.dline;
+      l = g.line0 + (double)(g.row0 + r) * g.dline;
       s = g.samp0 + (double)c * g.dsamp;
     } else {
       l = __ldcs(line + i);
@@ -352,7 +352,7 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
                                   double *achieved, uint32_t *status, cudaStream_t stream) {
   (void)prec;  // the frame model's imageToGround is closed form: desiredPrecision is unused
   if (n <= 0) return cudaSuccess;
-  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
   if (grid)
     frImageToGroundKernel<true><<<frBlocks(frImageToGroundKernel<true>, n, smCount), kThreads, 0, stream>>>(
         S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);

@@ -23,10 +23,13 @@ struct LaunchShape {
   int threads;
 };
 
-// Dense pixel grid: point k = r * nSamps + c  ->  (line0 + r * dline, samp0 + c * dsamp).
+// Dense pixel grid: point k = r * nSamps + c  ->  (line0 + (row0 + r) * dline, samp0 + c * dsamp).
+// row0: first grid row of this launch (a chunk of a larger grid), so that the line of a row is
+// the same double whichever chunk it falls in.
 struct GridSpec {
   double line0, samp0, dline, dsamp;
   long nSamps;
+  long row0;
 };
 
 void countLaunch();

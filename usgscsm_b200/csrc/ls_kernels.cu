@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <type_traits>
 
+#include "geo_device.cuh"
 #include "kernels.h"
 #include "ls_common.cuh"
 #include "work_queue.cuh"
@@ -142,18 +143,41 @@ UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamp
   return st;
 }
 
-template <class SPEC, class TAB>
-UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const double *__restrict__ x,
-                                const double *__restrict__ y, const double *__restrict__ z,
+// Where the ground points of a launch come from: three SoA arrays, or the samples of a DEM
+// window (the ground point of a sample is generated in the kernel: 2-8 bytes per point read
+// instead of 24; usgscsm_b200_ground_to_image_dem_grid).
+struct ArrayGround {
+  const double *__restrict__ x, *__restrict__ y, *__restrict__ z;
+  UB_DEV bool load(long i, double &gx, double &gy, double &gz) const {
+    gx = __ldcs(x + i);
+    gy = __ldcs(y + i);
+    gz = __ldcs(z + i);
+    return true;
+  }
+};
+struct DemGround {
+  DemWindow w;
+  UB_DEV bool load(long i, double &gx, double &gy, double &gz) const {
+    return demGroundPoint(w, i, gx, gy, gz);
+  }
+};
+
+template <class SPEC, class TAB, class SRC>
+UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const SRC &src,
                                 double prec, double *__restrict__ line, double *__restrict__ samp,
                                 double *__restrict__ achieved, uint32_t *__restrict__ status,
                                 unsigned long long *__restrict__ next, int grab) {
   forEachPointDynamic(n, next, grab, [&](long i) {
-    double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
+    double gx, gy, gz;
     double l, s, a;
     uint32_t st = 0;
-    lsGroundToImagePoint<false, TAB, SPEC>(S, T, gx, gy, gz, prec, l, s, a, st);
-    st |= imageRangeStatus(l, s, S.nLines, S.nSamples);
+    if (src.load(i, gx, gy, gz)) {
+      lsGroundToImagePoint<false, TAB, SPEC>(S, T, gx, gy, gz, prec, l, s, a, st);
+      st |= imageRangeStatus(l, s, S.nLines, S.nSamples);
+    } else {  // a nodata sample: nothing to project
+      l = s = a = nan("");
+      st = USGSCSM_B200_ST_DEM_NODATA | USGSCSM_B200_ST_NONFINITE;
+    }
     __stcs(line + i, l);
     __stcs(samp + i, s);
     if (achieved) __stcs(achieved + i, a);
@@ -172,10 +196,10 @@ UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const do
 // for such a model, scattered over 85 KB of code, and ncu shows the search kernel waiting on
 // instruction fetch (icc hit rate 88 %, "no instruction" 14 % of stall samples).
 // DIST = -1 is the generic kernel.  Same arithmetic either way.
-template <bool STAGE, int MINB, int DIST, int ADJ = 0>
+template <bool STAGE, int MINB, int DIST, int ADJ, class SRC>
 __global__ void __launch_bounds__(kThreads, MINB)
-    lsGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
-                          const double *__restrict__ y, const double *__restrict__ z, double prec,
+    lsGroundToImageKernel(const __grid_constant__ LsState S, long n,
+                          const __grid_constant__ SRC src, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
                           double *__restrict__ achieved, uint32_t *__restrict__ status,
                           unsigned long long *__restrict__ next, int grab) {
@@ -183,10 +207,10 @@ __global__ void __launch_bounds__(kThreads, MINB)
   using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST, ADJ>, SearchSpec>::type;
   if (STAGE) {
     StagedTables T = stageOrientationTables(S, specHasAdj<SPEC>(S), smem);
-    lsGroundToImageLoop<SPEC>(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
+    lsGroundToImageLoop<SPEC>(S, T, n, src, prec, line, samp, achieved, status, next, grab);
   } else {
     OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
-    lsGroundToImageLoop<SPEC>(S, T, n, x, y, z, prec, line, samp, achieved, status, next, grab);
+    lsGroundToImageLoop<SPEC>(S, T, n, src, prec, line, samp, achieved, status, next, grab);
   }
 }
 
@@ -239,7 +263,7 @@ __global__ void lsGridTablesKernel(const __grid_constant__ LsState S, GridSpec g
   long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   if (k < nRows) {
-    double line = g.line0 + (double)k * g.dline;
+    double line = g.line0 + (double)(g.row0 + k) * g.dline;
     double time = lsImageTime(S, line);
     double pos[3], vel[3], m[9], a[9];
     adjSensorPosVel<false>(S, T, time, pos, vel);
@@ -329,7 +353,7 @@ UB_DEV void lsImageToGroundLoop(const LsState &S, const TAB &T, long n, const do
     if (GRID) {
       long r = i / g.nSamps;
       long c = i - r * g.nSamps;
-      l = g.line0 + (double)r * g.dline;
+      l = g.line0 + (double)(g.row0 + r) * g.dline;
       s = g.samp0 + (double)c * g.dsamp;
     } else {
       l = __ldcs(line + i);
@@ -565,10 +589,11 @@ static LaunchShape shapeFor(const LsState &S, long n, int smCount, size_t &smemB
   return sh;
 }
 
-cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const double *x,
-                                  const double *y, const double *z, double prec, double *line,
-                                  double *samp, double *achieved, uint32_t *status,
-                                  cudaStream_t stream) {
+template <class SRC>
+static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long n, const SRC &src,
+                                             double prec, double *line, double *samp,
+                                             double *achieved, uint32_t *status,
+                                             cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   size_t smemBytes;
   bool stage;
@@ -583,10 +608,10 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
 #define UB_LAUNCH_G2I(STAGE, DIST, ADJ)                                                       \
   do {                                                                                        \
     if (smemBytes > 48 * 1024)                                                                \
-      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ>,        \
+      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ, SRC>,   \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
-    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ>                                \
-        <<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, x, y, z, prec, line, samp,       \
+    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ, SRC>                           \
+        <<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, src, prec, line, samp,           \
                                                        achieved, status, next, grab);         \
   } while (0)
 #define UB_LAUNCH_G2I_ADJ(STAGE, DIST)                                                        \
@@ -620,6 +645,22 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
   return wc.release();
 }
 
+cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const double *x,
+                                  const double *y, const double *z, double prec, double *line,
+                                  double *samp, double *achieved, uint32_t *status,
+                                  cudaStream_t stream) {
+  return launchLsGroundToImageFrom(S, smCount, n, ArrayGround{x, y, z}, prec, line, samp, achieved,
+                                   status, stream);
+}
+
+// groundToImage of the ground points of a DEM window, generated in the kernel.
+cudaError_t launchLsGroundToImageDem(const LsState &S, int smCount, long n, const DemWindow &w,
+                                     double prec, double *line, double *samp, double *achieved,
+                                     uint32_t *status, cudaStream_t stream) {
+  return launchLsGroundToImageFrom(S, smCount, n, DemGround{w}, prec, line, samp, achieved, status,
+                                   stream);
+}
+
 cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const double *line,
                                   const double *samp, const GridSpec *grid, const double *height,
                                   int heightStride, double prec, double *x, double *y, double *z,
@@ -650,7 +691,7 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
   bool stage;
   static const int minb = envInt("USGSCSM_B200_LS_I2G_MINB", 4);
   LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, minb);
-  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
 #define UB_LAUNCH_I2G_M(STAGE, GRID, MINB)                                                   \
   do {                                                                                       \
     if (smemBytes > 48 * 1024)                                                               \

@@ -46,6 +46,9 @@ struct PipelineSlot {
   cudaEvent_t done = nullptr;
   double *scratch = nullptr;
   long scratchDoubles = 0;
+  // page-locked host buffer of the same layout, for callers whose arrays are pageable
+  void *stage = nullptr;
+  long stageBytes = 0;
 };
 
 constexpr int kMaxPipelineSlots = 8;
@@ -93,10 +96,21 @@ struct Model {
   // (capi_host.cu runPipelined).  Concurrent host threads on ONE handle are therefore safe and
   // serialised; threads on different handles run concurrently.
   std::mutex hostCallMutex;
+  // Row / column trigonometry tables of the DEM windows last used with this model (capi_geo.cu):
+  // a repeated call on the same window (an orthorectifier re-projecting tile after tile, the
+  // bench loop) re-uses the device copy instead of rebuilding it on the host.
+  struct GeoTables {
+    std::string key;
+    double *dev = nullptr;
+    size_t rowDoubles = 0;
+  };
+  std::vector<GeoTables> geoTables;
+  std::mutex geoTablesMutex;
 
   ~Model();
   const double *upload(const std::vector<double> &v);
   void ensureScratch(int s, long doubles);
+  void ensureStage(int s, long bytes);
 };
 
 // model_ls.cu

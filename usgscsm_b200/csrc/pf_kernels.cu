@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(kThreads, UB_PF_I2G_MINB)
     if (GRID) {
       long r = i / g.nSamps;
       long c = i - r * g.nSamps;
-      l = g.line0 + (double)r * g.dline;
+      l = g.line0 + (double)(g.row0 + r) * g.dline;
       s = g.samp0 + (double)c * g.dsamp;
     } else {
       l = __ldcs(line + i);
@@ -553,7 +553,7 @@ cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const d
   size_t smemBytes;
   bool stage;
   LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
-  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
 #define UB_LAUNCH_PF(STAGE, GRID)                                                         \
   pfImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(       \
       S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status)

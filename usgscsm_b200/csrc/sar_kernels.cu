@@ -364,7 +364,7 @@ __global__ void __launch_bounds__(kThreads)
     if (GRID) {
       long r = i / g.nSamps;
       long c = i - r * g.nSamps;
-      l = g.line0 + (double)r * g.dline;
+      l = g.line0 + (double)(g.row0 + r) * g.dline;
       s = g.samp0 + (double)c * g.dsamp;
     } else {
       l = __ldcs(line + i);
@@ -572,7 +572,7 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
   size_t smemBytes;
   bool stage;
   LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
-  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1};
+  GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
   if (stage && smemBytes > 48 * 1024) {
     cudaError_t ea = grid ? allowSmem(sarImageToGroundKernel<true, true>, smemBytes)
                           : allowSmem(sarImageToGroundKernel<true, false>, smemBytes);

@@ -79,8 +79,31 @@ def _ptr(a):
     if a is None:
         return None
     if _is_torch(a):
+        # raw addresses cross the C-ABI: a strided or CPU tensor would be read as garbage
+        if not (a.is_cuda and a.is_contiguous()):
+            raise ValueError("torch arguments must be contiguous CUDA tensors")
         return a.data_ptr()
     return a.ctypes.data
+
+
+def _dev_inputs(model, n, *tensors, **kw):
+    """Checks of the device-pointer flavours' inputs: CUDA, float64, contiguous, `per` x n
+    elements, on the model's device.  The C-ABI sees raw addresses and cannot check any of it."""
+    import torch
+    per = kw.get("per", 1)
+    for t in tensors:
+        if t is None:
+            continue
+        if not _is_torch(t) or not t.is_cuda:
+            raise ValueError("expected a CUDA tensor")
+        if t.dtype != torch.float64:
+            raise ValueError("expected a float64 tensor, got %s" % t.dtype)
+        if not t.is_contiguous():
+            raise ValueError("expected a contiguous tensor")
+        if t.numel() != per * n:
+            raise ValueError("tensor length %d, expected %d" % (t.numel(), per * n))
+        if t.device.index != model.device:
+            raise ValueError("tensor on cuda:%s, the model lives on cuda:%d" % (t.device.index, model.device))
 
 
 class RasterGM(object):
@@ -153,6 +176,7 @@ class RasterGM(object):
         if _is_torch(x):
             import torch
             n = x.numel()
+            _dev_inputs(self, n, x, y, z)
             if out is not None:
                 line, samp, ach, st = out
             else:
@@ -183,9 +207,11 @@ class RasterGM(object):
         if _is_torch(line):
             import torch
             n = line.numel()
+            _dev_inputs(self, n, line, samp)
             if not _is_torch(height):
                 height = torch.full((1,), float(height), dtype=torch.float64, device=line.device)
             stride = 0 if height.numel() == 1 else 1
+            _dev_inputs(self, n if stride else 1, height)
             x, y, z = torch.empty_like(line), torch.empty_like(line), torch.empty_like(line)
             ach = torch.empty_like(line) if achieved else None
             st = torch.empty(n, dtype=torch.int32, device=line.device) if status else None
@@ -232,6 +258,7 @@ class RasterGM(object):
         import torch
         dev = height.device
         stride = 0 if height.numel() == 1 else 1
+        _dev_inputs(self, n if stride else 1, height)
         if out is None:
             x, y, z = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
             ach = torch.empty(n, dtype=torch.float64, device=dev) if achieved else None
@@ -252,6 +279,7 @@ class RasterGM(object):
         if _is_torch(line):
             import torch
             n = line.numel()
+            _dev_inputs(self, n, line, samp)
             out = [torch.empty_like(line) for _ in range(7)]
             st = torch.empty(n, dtype=torch.int32, device=line.device)
             stream = torch.cuda.current_stream(line.device).cuda_stream
@@ -274,6 +302,7 @@ class RasterGM(object):
         if _is_torch(line):
             import torch
             n = line.numel()
+            _dev_inputs(self, n, line, samp, x, y, z)
             out = [torch.empty_like(line) for _ in range(7)]
             st = torch.empty(n, dtype=torch.int32, device=line.device)
             stream = torch.cuda.current_stream(line.device).cuda_stream
@@ -296,6 +325,7 @@ class RasterGM(object):
         if _is_torch(x):
             import torch
             n = x.numel()
+            _dev_inputs(self, n, x, y, z)
             p = torch.empty((n, 6), dtype=torch.float64, device=x.device)
             st = torch.empty(n, dtype=torch.int32, device=x.device)
             stream = torch.cuda.current_stream(x.device).cuda_stream
@@ -318,6 +348,7 @@ class RasterGM(object):
         if _is_torch(x):
             import torch
             n = x.numel()
+            _dev_inputs(self, n, x, y, z)
             dl, ds, ach = (torch.empty_like(x) for _ in range(3))
             st = torch.empty(n, dtype=torch.int32, device=x.device)
             stream = torch.cuda.current_stream(x.device).cuda_stream
@@ -352,6 +383,7 @@ class RasterGM(object):
         if _is_torch(x):
             import torch
             n = x.numel()
+            _dev_inputs(self, n, x, y, z)
             p = torch.empty((n, npar, 2), dtype=torch.float64, device=x.device)
             ach = torch.empty_like(x)
             st = torch.empty(n, dtype=torch.int32, device=x.device)
@@ -378,6 +410,7 @@ class RasterGM(object):
         if _is_torch(line):
             import torch
             n = line.numel()
+            _dev_inputs(self, n, line, samp)
             o = [torch.empty_like(line) for _ in range(7)]
             st = torch.empty(n, dtype=torch.int32, device=line.device)
             check(lib.usgscsm_b200_image_sensor_state_dev(
@@ -410,6 +443,7 @@ class RasterGM(object):
         if _is_torch(x):
             import torch
             n = x.numel()
+            _dev_inputs(self, n, x, y, z)
             d = [torch.empty_like(x) for _ in range(3)]
             st = torch.empty(n, dtype=torch.int32, device=x.device)
             check(lib.usgscsm_b200_illumination_direction_dev(
@@ -447,6 +481,7 @@ class RasterGM(object):
         if _is_torch(x):
             import torch
             n = x.numel()
+            _dev_inputs(self, n, x, y, z)
             line, samp, ach = (torch.empty_like(x) for _ in range(3))
             icov = torch.empty((n, 4), dtype=torch.float64, device=x.device)
             st = torch.empty(n, dtype=torch.int32, device=x.device)
@@ -474,6 +509,7 @@ class RasterGM(object):
         if _is_torch(line):
             import torch
             n = line.numel()
+            _dev_inputs(self, n, line, samp)
             dev = line.device
 
             def per_point(v):
@@ -697,6 +733,189 @@ class UsgsAstroPlugin(object):
         (no CUDA device needed)."""
         return self._state_from_isd(imageSupportData, modelName, "constructStateFromIsd")
 
+
+
+# ---- georeferenced grids and DEMs (include/usgscsm_b200.h, "the callers either side of the path") ----
+class GeoGrid(object):
+    """Georeferencing of a raster: GDAL geotransform + map projection (longlat, eqc, sinu) +
+    ellipsoid, i.e. m_geoTransform / m_projString of UsgsAstroProjectedSensorModel
+    (src/UsgsAstroProjectedSensorModel.cpp:123-147)."""
+
+    def __init__(self, c_grid):
+        self.c = c_grid
+
+    @staticmethod
+    def fromProjString(projString, geoTransform, semiMajor=0.0, semiMinor=0.0):
+        g = _capi.GeoGrid()
+        gt = (C.c_double * 6)(*[float(v) for v in geoTransform])
+        check(lib.usgscsm_b200_geogrid_from_proj_string(projString.encode("utf-8"), gt,
+                                                        float(semiMajor), float(semiMinor), C.byref(g)))
+        return GeoGrid(g)
+
+    def imageToGround(self, line, samp, height=None, device=0):
+        """UsgsAstroProjectedSensorModel::imageToGround for arrays: raster (line, samp) [+ height]
+        -> body-fixed (x, y, z, status)."""
+        if _is_torch(line):
+            import torch
+            n = line.numel()
+            x, y, z = (torch.empty_like(line) for _ in range(3))
+            st = torch.empty(n, dtype=torch.int32, device=line.device)
+            hs = 0 if height is None or height.numel() == 1 else 1
+            check(lib.usgscsm_b200_geogrid_image_to_ground_dev(
+                C.byref(self.c), line.device.index, n, _ptr(line), _ptr(samp), _ptr(height), hs,
+                _ptr(x), _ptr(y), _ptr(z), _ptr(st), torch.cuda.current_stream(line.device).cuda_stream))
+            return x, y, z, st
+        line = _host(line)
+        n = line.size
+        samp = _host(samp, n)
+        h = None if height is None else _host(height)
+        x, y, z = np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_geogrid_image_to_ground(
+            C.byref(self.c), device, n, _ptr(line), _ptr(samp), _ptr(h),
+            0 if h is None or h.size == 1 else 1, _ptr(x), _ptr(y), _ptr(z), _ptr(st)))
+        return x, y, z, st
+
+    def groundToImage(self, x, y, z, device=0):
+        """UsgsAstroProjectedSensorModel::groundToImage for arrays: body-fixed -> raster
+        (line, samp, height above the ellipsoid, status)."""
+        if _is_torch(x):
+            import torch
+            n = x.numel()
+            line, samp, h = (torch.empty_like(x) for _ in range(3))
+            st = torch.empty(n, dtype=torch.int32, device=x.device)
+            check(lib.usgscsm_b200_geogrid_ground_to_image_dev(
+                C.byref(self.c), x.device.index, n, _ptr(x), _ptr(y), _ptr(z), _ptr(line), _ptr(samp),
+                _ptr(h), _ptr(st), torch.cuda.current_stream(x.device).cuda_stream))
+            return line, samp, h, st
+        x = _host(x)
+        n = x.size
+        y, z = _host(y, n), _host(z, n)
+        line, samp, h = np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_geogrid_ground_to_image(
+            C.byref(self.c), device, n, _ptr(x), _ptr(y), _ptr(z), _ptr(line), _ptr(samp), _ptr(h),
+            _ptr(st)))
+        return line, samp, h, st
+
+
+class Dem(object):
+    """A DEM raster: a 2-D array of float64 / float32 / int16 samples (numpy = host entry points,
+    torch CUDA tensor = device entry points) on a GeoGrid; height = raw * scale + offset."""
+
+    def __init__(self, samples, grid, nodata=None, scale=1.0, offset=0.0):
+        self.torch = _is_torch(samples)
+        if self.torch:
+            import torch
+            types = {torch.float64: _capi.DEM_F64, torch.float32: _capi.DEM_F32, torch.int16: _capi.DEM_I16}
+            if not (samples.is_cuda and samples.is_contiguous() and samples.dim() == 2 and samples.dtype in types):
+                raise ValueError("DEM samples: contiguous 2-D CUDA tensor of float64 / float32 / int16")
+            kind, rows, cols = types[samples.dtype], samples.shape[0], samples.shape[1]
+        else:
+            samples = np.ascontiguousarray(samples)
+            types = {np.dtype("float64"): _capi.DEM_F64, np.dtype("float32"): _capi.DEM_F32,
+                     np.dtype("int16"): _capi.DEM_I16}
+            if samples.ndim != 2 or samples.dtype not in types:
+                raise ValueError("DEM samples: 2-D array of float64 / float32 / int16")
+            kind, rows, cols = types[samples.dtype], samples.shape[0], samples.shape[1]
+        self.samples, self.grid = samples, grid
+        self.c = _capi.Dem(_ptr(samples), kind, 0 if nodata is None else 1,
+                           0.0 if nodata is None else float(nodata), float(scale), float(offset),
+                           rows, cols, grid.c)
+
+    @property
+    def shape(self):
+        return int(self.c.n_rows), int(self.c.n_cols)
+
+    def _window(self, row0, col0, n_rows, n_cols):
+        n_rows = self.c.n_rows - row0 if n_rows is None else n_rows
+        n_cols = self.c.n_cols - col0 if n_cols is None else n_cols
+        return int(row0), int(col0), int(n_rows), int(n_cols)
+
+    def groundPoints(self, row0=0, col0=0, n_rows=None, n_cols=None, device=0):
+        """Body-fixed ground points of the window's pixel centres, height = the sample."""
+        row0, col0, n_rows, n_cols = self._window(row0, col0, n_rows, n_cols)
+        n = n_rows * n_cols
+        if self.torch:
+            import torch
+            dev = self.samples.device
+            x, y, z = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
+            st = torch.empty(n, dtype=torch.int32, device=dev)
+            check(lib.usgscsm_b200_dem_ground_points_dev(
+                C.byref(self.c), dev.index, row0, col0, n_rows, n_cols, _ptr(x), _ptr(y), _ptr(z),
+                _ptr(st), torch.cuda.current_stream(dev).cuda_stream))
+            return x, y, z, st
+        x, y, z = np.empty(n), np.empty(n), np.empty(n)
+        st = np.empty(n, dtype=np.uint32)
+        check(lib.usgscsm_b200_dem_ground_points(C.byref(self.c), device, row0, col0, n_rows, n_cols,
+                                                 _ptr(x), _ptr(y), _ptr(z), _ptr(st)))
+        return x, y, z, st
+
+
+def _ground_to_image_dem_grid(self, dem, row0=0, col0=0, n_rows=None, n_cols=None,
+                              desiredPrecision=0.001, achieved=False, status=True, out=None, stream=None):
+    """groundToImage of every ground point of a DEM window, the points generated in the kernel
+    (orthorectification's inner loop).  Returns (line, samp, achieved, status), row-major over the
+    window."""
+    row0, col0, n_rows, n_cols = dem._window(row0, col0, n_rows, n_cols)
+    n = n_rows * n_cols
+    if dem.torch:
+        import torch
+        dev = dem.samples.device
+        if dev.index != self.device:
+            raise ValueError("DEM on cuda:%s, the model lives on cuda:%d" % (dev.index, self.device))
+        if out is None:
+            line, samp = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(2))
+            ach = torch.empty(n, dtype=torch.float64, device=dev) if achieved else None
+            st = torch.empty(n, dtype=torch.int32, device=dev) if status else None
+        else:
+            line, samp, ach, st = out
+        if stream is None:
+            stream = torch.cuda.current_stream(dev).cuda_stream
+        check(lib.usgscsm_b200_ground_to_image_dem_grid_dev(
+            self._h, C.byref(dem.c), row0, col0, n_rows, n_cols, desiredPrecision, _ptr(line), _ptr(samp),
+            _ptr(ach), _ptr(st), stream))
+        return line, samp, ach, st
+    if out is None:
+        line, samp = np.empty(n), np.empty(n)
+        ach = np.empty(n) if achieved else None
+        st = np.empty(n, dtype=np.uint32) if status else None
+    else:
+        line, samp, ach, st = out
+    check(lib.usgscsm_b200_ground_to_image_dem_grid(
+        self._h, C.byref(dem.c), row0, col0, n_rows, n_cols, desiredPrecision, _ptr(line), _ptr(samp),
+        _ptr(ach), _ptr(st)))
+    return line, samp, ach, st
+
+
+def _image_to_ground_dem(self, dem, line, samp, h0=0.0, tolerance=0.01, maxIterations=8,
+                         desiredPrecision=0.001):
+    """DEM-iterated ground intersection: imageToGround at the height of the DEM where the ray
+    meets it.  Returns (x, y, z, height, status)."""
+    if dem.torch:
+        import torch
+        n = line.numel()
+        _dev_inputs(self, n, line, samp)
+        x, y, z, h = (torch.empty_like(line) for _ in range(4))
+        st = torch.empty(n, dtype=torch.int32, device=line.device)
+        check(lib.usgscsm_b200_image_to_ground_dem_dev(
+            self._h, C.byref(dem.c), n, _ptr(line), _ptr(samp), float(h0), float(tolerance),
+            int(maxIterations), desiredPrecision, _ptr(x), _ptr(y), _ptr(z), _ptr(h), _ptr(st),
+            torch.cuda.current_stream(line.device).cuda_stream))
+        return x, y, z, h, st
+    line = _host(line)
+    n = line.size
+    samp = _host(samp, n)
+    x, y, z, h = np.empty(n), np.empty(n), np.empty(n), np.empty(n)
+    st = np.empty(n, dtype=np.uint32)
+    check(lib.usgscsm_b200_image_to_ground_dem(
+        self._h, C.byref(dem.c), n, _ptr(line), _ptr(samp), float(h0), float(tolerance),
+        int(maxIterations), desiredPrecision, _ptr(x), _ptr(y), _ptr(z), _ptr(h), _ptr(st)))
+    return x, y, z, h, st
+
+
+RasterGM.groundToImageDemGrid = _ground_to_image_dem_grid
+RasterGM.imageToGroundDem = _image_to_ground_dem
 
 def stateToMsgpack(modelState):
     """The msgpack binary form of a model state, as the reference writes it
