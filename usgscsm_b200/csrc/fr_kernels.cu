@@ -100,7 +100,9 @@ UB_DEV void frImageToGroundPoint(const FrameState &S, double line, double sample
   // losEllipsoidIntersect FR:2288-2345: always the (-bt - sqrt) root
   double ap = S.ell.majorAxis + height;
   double bp = S.ell.minorAxis + height;
-  double k = ap * ap / (bp * bp);
+  // sphere: ap and bp are the same double, and x / x == 1 for any finite non-zero x
+  double ap2 = ap * ap;
+  double k = (S.ell.majorAxis == S.ell.minorAxis && ap2 > 0.0 && ap2 < CUDART_INF) ? 1.0 : ap2 / (bp * bp);
   double at = xl * xl + yl * yl + k * zl * zl;
   double bt = 2.0 * (xl * xc + yl * yc + k * zl * zc);
   double ct = xc * xc + yc * yc + k * zc * zc - ap * ap;

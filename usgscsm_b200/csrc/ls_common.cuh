@@ -277,7 +277,9 @@ UB_DEV void lsEllipsoidIntersect(const Ellipsoid &ell, double height, const doub
                                  double &y, double &z, double &achieved, uint32_t &status) {
   double ap = ell.majorAxis + height;
   double bp = ell.minorAxis + height;
-  double k = ap * ap / (bp * bp);
+  // sphere: ap and bp are the same double, and x / x == 1 for any finite non-zero x
+  double ap2 = ap * ap;
+  double k = (ell.majorAxis == ell.minorAxis && ap2 > 0.0 && ap2 < CUDART_INF) ? 1.0 : ap2 / (bp * bp);
   double at = l[0] * l[0] + l[1] * l[1] + k * l[2] * l[2];
   double bt = 2.0 * (l[0] * c[0] + l[1] * c[1] + k * l[2] * c[2]);
   double ct = c[0] * c[0] + c[1] * c[1] + k * c[2] * c[2] - ap * ap;

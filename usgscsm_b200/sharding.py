@@ -93,15 +93,20 @@ def bind_to_gpu_numa_node(device_index):
     """Pin this process (and so its page-locked staging buffers, first-touch) to the CPUs of
     the NUMA node the GPU hangs off.  With one process per GPU the host<->device copies of the
     host-pointer entry points otherwise cross the socket interconnect for half the ranks.
-    Returns the node number, or None when the topology cannot be read (then nothing changes)."""
+    Returns {"node": n or None, "cpus": count bound to, "why": text}: when the topology gives
+    nothing to bind to (a single-node VM reports numa_node = -1) the reason is stated, not hidden."""
     import os
+    info = {"node": None, "cpus": None, "why": None}
     try:
         props = torch.cuda.get_device_properties(device_index)
         bus = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
-        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+        path = "/sys/bus/pci/devices/%s/numa_node" % bus
+        with open(path) as f:
             node = int(f.read().strip())
         if node < 0:
-            return None
+            nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node")]
+            info["why"] = "%s reports %d (%d NUMA node(s) on this host): nothing to bind to" % (path, node, len(nodes))
+            return info
         with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
             cpus = set()
             for part in f.read().strip().split(","):
@@ -109,8 +114,11 @@ def bind_to_gpu_numa_node(device_index):
                 cpus.update(range(int(lo), int(hi or lo) + 1))
         allowed = cpus & os.sched_getaffinity(0)
         if not allowed:
-            return None
+            info["why"] = "no CPU of node %d is in this process's affinity mask" % node
+            return info
         os.sched_setaffinity(0, allowed)
-        return node
-    except (OSError, ValueError, AttributeError):
-        return None
+        info.update(node=node, cpus=len(allowed), why="bound")
+        return info
+    except (OSError, ValueError, AttributeError) as e:
+        info["why"] = "topology unreadable: %s" % e
+        return info

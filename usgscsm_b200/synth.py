@@ -57,8 +57,10 @@ def linescan_state(n_lines=52224, n_samples=5064, focal_length=699.62, pixel_pit
                    distortion_type=LROLROCNAC, dist_coeffs=(1.81e-5,), seed=20261104,
                    wobble=1e-5, wobble_hz=3.0, dt_ephem=1.0, dt_quat=0.05, line_time=None,
                    params=None, platform_flag=1, n_time_segments=1, gm=4.9028e12,
-                   summing=1, starting_sample=0.0, derived=None, as_dict=False):
+                   summing=1, starting_sample=0.0, derived=None, as_dict=False, polar=False):
     """A line-scan model state on a circular, tilted polar orbit with nadir pointing.
+    `polar`: an exactly polar orbit instead (the orbit plane contains the body's axis; the
+    ground track runs along a meridian, so a north-up DEM raster lines up with the image).
 
     `line_time` defaults to the value giving square ground pixels.  `n_time_segments` > 1
     splits the image into segments with slightly different line rates (exercises the
@@ -92,6 +94,9 @@ def linescan_state(n_lines=52224, n_samples=5064, focal_length=699.62, pixel_pit
 
     tilt = _rot(2, 0.3 + 0.1 * rng.random()) @ _rot(0, 0.2 + 0.1 * rng.random())
     phase0 = 0.4 + rng.random()
+    if polar:
+        tilt = _rot(2, 0.3 + 0.1 * rng.random())
+        phase0 = 0.2 + 0.6 * rng.random()   # latitude of the image centre, radians
 
     def frame(tt):
         th = phase0 + omega * tt
