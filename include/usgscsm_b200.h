@@ -403,6 +403,31 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_multi(usgscsm_b200_model *cons
                                        double *x, double *y, double *z, double *achieved,
                                        uint32_t *status);
 
+/* Many small images in one call ("small images can instead be distributed
+ * whole"; config C5 packs several per launch): models[k] (all of one device) processes the next
+ * counts[k] points of the concatenated device arrays.  A 4096 x 4096 frame or push-frame image is
+ * a 0.2 - 0.7 ms kernel that spends a good part of its life ramping up and draining; here the
+ * images' kernels are spread over a few internal streams forked from / joined to `stream`, so one
+ * image's tail overlaps the next image's body.  Nothing is synchronised with the host. */
+USGSCSM_B200_API int usgscsm_b200_ground_to_image_images_dev(usgscsm_b200_model *const *models, int n_models,
+                                                            const int64_t *counts, const double *x,
+                                                            const double *y, const double *z, double prec,
+                                                            double *line, double *samp, double *achieved,
+                                                            uint32_t *status, void *stream);
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_images_dev(usgscsm_b200_model *const *models, int n_models,
+                                                            const int64_t *counts, const double *line,
+                                                            const double *samp, const double *height,
+                                                            int height_stride, double prec, double *x,
+                                                            double *y, double *z, double *achieved,
+                                                            uint32_t *status, void *stream);
+/* The same over dense pixel grids: image k is the grid (line0 + r * dline, samp0 + c * dsamp),
+ * r < n_lines[k], c < n_samps[k]; its n_lines[k] * n_samps[k] points follow image k - 1's. */
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid_images_dev(
+    usgscsm_b200_model *const *models, int n_models, double line0, double samp0, double dline,
+    double dsamp, const int64_t *n_lines, const int64_t *n_samps, const double *height,
+    int height_stride, double prec, double *x, double *y, double *z, double *achieved,
+    uint32_t *status, void *stream);
+
 /* Dense-grid imageToGround: the double loop of bin/usgscsm_cam_test.cc:294-309 (and of an
  * orthorectifier) with the pixel coordinates generated in the kernel.  Point k =
  * r * n_samps + c is pixel (line0 + r * dline, samp0 + c * dsamp), r < n_lines,

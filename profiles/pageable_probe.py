@@ -1,5 +1,9 @@
-"""End-to-end rate of the host-pointer entry points with PAGEABLE numpy arrays, with and without
-the one-thread-per-slot pipeline (USGSCSM_B200_PIPELINE_THREADS), against pinned arrays."""
+"""End-to-end rate of the host-pointer groundToImage with PAGEABLE numpy arrays (what a numpy
+caller passes), round 2: the engine stages them through its own page-locked ring, one copier
+thread per slot (csrc/pipeline.cuh).  Sweeps USGSCSM_B200_STAGE_THREADS x USGSCSM_B200_STAGE_CHUNK
+and compares with the CUDA runtime's own staging (USGSCSM_B200_PIPELINE_THREADS=0) and with plain
+host memcpy bandwidth of the box.  Outputs preallocated and touched (no page faults in the timed
+region); a second line times the call with fresh numpy.empty outputs."""
 import os
 import subprocess
 import sys
@@ -9,36 +13,47 @@ import numpy as np
 
 if len(sys.argv) > 1:
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    import torch
     import usgscsm_b200 as ub
-    from usgscsm_b200 import synth
+    from usgscsm_b200 import synth, _capi
     gm = ub.UsgsAstroPlugin().constructModelFromState(synth.linescan_state())
-    nl, ns = 8192, 5064
+    nl, ns = 12288, 5064
     line = np.repeat(np.arange(nl) + 0.5, ns)
     samp = np.tile(np.arange(ns) + 0.5, nl)
     h = synth.synthetic_dem(line, samp)
     n = line.size
     x, y, z, _, _ = gm.imageToGroundBatch(line, samp, h, 1e-3)
-    from usgscsm_b200 import _capi
     ol, os_ = np.zeros(n), np.zeros(n)
     st = np.zeros(n, dtype=np.uint32)
 
-    def call():
+    def call(ol, os_, st):
         _capi.check(_capi.lib.usgscsm_b200_ground_to_image(
             gm._h, n, x.ctypes.data, y.ctypes.data, z.ctypes.data, 1e-3, ol.ctypes.data,
             os_.ctypes.data, None, st.ctypes.data))
-    call()
+    call(ol, os_, st)
     t = time.perf_counter()
     for _ in range(3):
-        call()
+        call(ol, os_, st)
     dt = (time.perf_counter() - t) / 3
-    print("pageable numpy arrays, USGSCSM_B200_PIPELINE_THREADS=%s: groundToImage %d points, %.1f ms, %.0f Mpoints/s"
-          % (os.environ.get("USGSCSM_B200_PIPELINE_THREADS", "1"), n, dt * 1e3, n / dt / 1e6), flush=True)
-    print("round trip max |dline| %.3g px" % float(np.abs(ol - line).max()))
+    t = time.perf_counter()
+    call(np.empty(n), np.empty(n), np.empty(n, dtype=np.uint32))
+    dt2 = time.perf_counter() - t
+    print("  threads %s chunk %s runtime-staging-off %s: %d points, %.1f ms, %.0f Mpoints/s (%.1f GB/s of "
+          "caller arrays); fresh output arrays: %.0f Mpoints/s; round trip %.3g px"
+          % (os.environ.get("USGSCSM_B200_STAGE_THREADS", "8"), os.environ.get("USGSCSM_B200_STAGE_CHUNK", str(1 << 20)),
+             os.environ.get("USGSCSM_B200_PIPELINE_THREADS", "1"), n, dt * 1e3, n / dt / 1e6, 44 * n / dt / 1e9,
+             n / dt2 / 1e6, float(np.abs(ol - line).max())), flush=True)
 else:
-    for v, slots, chunk in (("1", "3", str(1 << 22)), ("0", "3", str(1 << 22)), ("1", "6", str(1 << 20)),
-                            ("1", "8", str(1 << 21))):
-        env = dict(os.environ, USGSCSM_B200_PIPELINE_THREADS=v, USGSCSM_B200_PIPELINE_SLOTS=slots,
-                   USGSCSM_B200_PIPELINE_CHUNK=chunk)
-        print("slots %s, chunk %s points:" % (slots, chunk), flush=True)
-        subprocess.run([sys.executable, __file__, "child"], env=env, check=True)
+    a = np.ones(1 << 27)
+    b = np.empty_like(a)
+    b[:] = a
+    t = time.perf_counter()
+    b[:] = a
+    print("host memcpy, one thread: %.1f GB/s (read + write counted once)" % (a.nbytes / (time.perf_counter() - t) / 1e9))
+    del a, b
+    print("CUDA runtime staging (round 1 path):", flush=True)
+    subprocess.run([sys.executable, __file__, "child"], env=dict(os.environ, USGSCSM_B200_PIPELINE_THREADS="0"), check=True)
+    print("own pinned ring:", flush=True)
+    for threads in ("4", "8", "12", "16"):
+        for chunk in (str(1 << 18), str(1 << 20)):
+            env = dict(os.environ, USGSCSM_B200_STAGE_THREADS=threads, USGSCSM_B200_STAGE_CHUNK=chunk)
+            subprocess.run([sys.executable, __file__, "child"], env=env, check=True)

@@ -145,3 +145,41 @@ def test_concurrent_host_threads_on_the_same_model():
         for got in results[k]:
             for u, v in zip(got, expect[k]):
                 assert np.array_equal(u, v, equal_nan=True)
+
+
+@pytest.mark.parametrize("kind", ["frame", "pushframe", "linescan", "sar"])
+def test_many_images_per_call(kind):
+    """usgscsm_b200_*_images_dev: several images of one kind in one call (kernels forked over
+    internal streams) give exactly what one call per image gives."""
+    import torch
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import synth
+    make = {"frame": lambda k: synth.frame_state(n_lines=300 + 20 * k, n_samples=256, seed=k),
+            "pushframe": lambda k: synth.pushframe_state(n_framelets=16 + k, framelet_height=16, n_samples=256, seed=k),
+            "linescan": lambda k: synth.linescan_state(n_lines=400 + 30 * k, n_samples=256, seed=40 + k),
+            "sar": lambda k: synth.sar_state(n_lines=2000 + 100 * k, n_samples=300)}[kind]
+    plugin = ub.UsgsAstroPlugin()
+    models = [plugin.constructModelFromState(make(k)) for k in range(6)]
+    dev = torch.device("cuda:0")
+    sizes = [(int(m.getImageSize().line), int(m.getImageSize().samp)) for m in models]
+    counts = [a * b for a, b in sizes]
+    n = sum(counts)
+    h = torch.linspace(-200.0, 300.0, n, dtype=torch.float64, device=dev)
+    x, y, z, a, st = ub.imageToGroundGridImages(models, 0.5, 0.5, 1.0, 1.0, [s[0] for s in sizes],
+                                                [s[1] for s in sizes], h, achieved=True)
+    line, samp, a2, st2 = ub.groundToImageImages(models, counts, x, y, z, achieved=True)
+    rows = torch.cat([(torch.arange(nl, device=dev, dtype=torch.float64) + 0.5).repeat_interleave(ns) for nl, ns in sizes])
+    cols = torch.cat([(torch.arange(ns, device=dev, dtype=torch.float64) + 0.5).repeat(nl) for nl, ns in sizes])
+    xe, ye, ze, ae, ste = ub.imageToGroundImages(models, counts, rows, cols, h, achieved=True)
+    o = 0
+    for m, (nl, ns), c in zip(models, sizes, counts):
+        gx, gy, gz, ga, gst = m.imageToGroundGrid(0.5, 0.5, 1.0, 1.0, nl, ns, h[o:o + c], achieved=True)
+        for u, v in ((x, gx), (y, gy), (z, gz), (a, ga), (xe, gx), (ze, gz)):
+            assert torch.equal(u[o:o + c], v) or torch.allclose(u[o:o + c], v, rtol=0, atol=0, equal_nan=True)
+        assert torch.equal(st[o:o + c], gst)
+        gl, gs, gach, gst2 = m.groundToImageBatch(gx, gy, gz)
+        assert torch.allclose(line[o:o + c], gl, rtol=0, atol=0, equal_nan=True)
+        assert torch.allclose(samp[o:o + c], gs, rtol=0, atol=0, equal_nan=True)
+        assert torch.equal(st2[o:o + c], gst2)
+        o += c
+    torch.cuda.synchronize()

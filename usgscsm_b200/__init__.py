@@ -6,4 +6,5 @@ of the reference's plugin interface; it has no CPU implementation of the math.
 """
 from . import _capi, synth  # noqa: F401  (_capi raises ImportError when the .so is missing)
 from .plugin import (Dem, EcefCoord, Error, GeoGrid, ImageCoord, RasterGM,  # noqa: F401
-                     UsgsAstroPlugin, Warning, applyDistortion, lagrangeInterp, removeDistortion)
+                     UsgsAstroPlugin, Warning, applyDistortion, groundToImageImages, imageToGroundGridImages,
+                     imageToGroundImages, lagrangeInterp, removeDistortion)

@@ -146,6 +146,16 @@ SIGNATURES = {
     "usgscsm_b200_image_to_ground_multi": (
         C.c_int, [C.POINTER(_h), C.c_int, C.c_int64, _dp, _dp, _dp, C.c_int, C.c_double, _dp, _dp,
                   _dp, _dp, _dp]),
+    "usgscsm_b200_ground_to_image_images_dev": (
+        C.c_int, [C.POINTER(_h), C.c_int, C.POINTER(C.c_int64), _dp, _dp, _dp, C.c_double, _dp, _dp, _dp,
+                  _dp, _dp]),
+    "usgscsm_b200_image_to_ground_images_dev": (
+        C.c_int, [C.POINTER(_h), C.c_int, C.POINTER(C.c_int64), _dp, _dp, _dp, C.c_int, C.c_double, _dp,
+                  _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_grid_images_dev": (
+        C.c_int, [C.POINTER(_h), C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
+                  C.POINTER(C.c_int64), C.POINTER(C.c_int64), _dp, C.c_int, C.c_double, _dp, _dp, _dp, _dp,
+                  _dp, _dp]),
     "usgscsm_b200_image_to_ground_grid_dev": (
         C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
                   C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -472,6 +473,131 @@ int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, d
                                 static_cast<cudaStream_t>(stream)));
     return USGSCSM_B200_OK;
   });
+}
+
+}  // extern "C"
+
+// ---- many small images per call ------------------------------------------------------------------
+namespace ub200 {
+namespace {
+
+// A few side streams per device, forked from and joined to the caller's stream: the kernels of
+// consecutive images then overlap (one's tail with the next one's body).
+constexpr int kSideStreams = 4;
+struct SideStreams {
+  cudaStream_t s[kSideStreams] = {};
+  cudaEvent_t done[kSideStreams] = {};
+  cudaEvent_t fork = nullptr;
+  std::mutex mu;  // one fork / join at a time per device
+};
+
+SideStreams &sideStreams(int device) {
+  static std::mutex mu;
+  static std::vector<std::unique_ptr<SideStreams>> perDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if ((int)perDevice.size() <= device) perDevice.resize((size_t)device + 1);
+  if (!perDevice[(size_t)device]) {
+    std::unique_ptr<SideStreams> p(new SideStreams);
+    UB_CUDA(cudaEventCreateWithFlags(&p->fork, cudaEventDisableTiming));
+    for (int k = 0; k < kSideStreams; k++) {
+      UB_CUDA(cudaStreamCreateWithFlags(&p->s[k], cudaStreamNonBlocking));
+      UB_CUDA(cudaEventCreateWithFlags(&p->done[k], cudaEventDisableTiming));
+    }
+    perDevice[(size_t)device] = std::move(p);
+  }
+  return *perDevice[(size_t)device];
+}
+
+// launchOne(k, offset, side stream) enqueues image k.
+template <class F>
+int forEachImage(usgscsm_b200_model *const *models, int n_models, const int64_t *counts,
+                 cudaStream_t stream, F &&launchOne) {
+  if (!models || n_models < 0 || (n_models > 0 && !counts)) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  for (int k = 0; k < n_models; k++) {
+    if (!models[k] || counts[k] < 0) return fail(USGSCSM_B200_EINVAL, "null model / negative count");
+    if (models[k]->device != models[0]->device)
+      return fail(USGSCSM_B200_EINVAL, "the images of one call must live on one device");
+  }
+  if (n_models == 0) return USGSCSM_B200_OK;
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(models[0]->device));
+    SideStreams &ss = sideStreams(models[0]->device);
+    std::lock_guard<std::mutex> lock(ss.mu);
+    const int used = n_models < kSideStreams ? n_models : kSideStreams;
+    UB_CUDA(cudaEventRecord(ss.fork, stream));
+    for (int j = 0; j < used; j++) UB_CUDA(cudaStreamWaitEvent(ss.s[j], ss.fork, 0));
+    int64_t offset = 0;
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < n_models && e == cudaSuccess; k++) {
+      if (counts[k] > 0) e = launchOne(k, offset, ss.s[k % used]);
+      offset += counts[k];
+    }
+    for (int j = 0; j < used; j++) {
+      UB_CUDA(cudaEventRecord(ss.done[j], ss.s[j]));
+      UB_CUDA(cudaStreamWaitEvent(stream, ss.done[j], 0));
+    }
+    UB_CUDA(e);
+    return USGSCSM_B200_OK;
+  });
+}
+
+}  // namespace
+}  // namespace ub200
+
+extern "C" {
+
+int usgscsm_b200_ground_to_image_images_dev(usgscsm_b200_model *const *models, int n_models,
+                                            const int64_t *counts, const double *x, const double *y,
+                                            const double *z, double prec, double *line, double *samp,
+                                            double *achieved, uint32_t *status, void *stream) {
+  if (n_models > 0 && (!x || !y || !z || !line || !samp)) return fail(USGSCSM_B200_EINVAL, "null array");
+  return forEachImage(models, n_models, counts, static_cast<cudaStream_t>(stream),
+                      [&](int k, int64_t o, cudaStream_t s) {
+                        return launchGroundToImage(*models[k], (long)counts[k], x + o, y + o, z + o, prec,
+                                                   line + o, samp + o, achieved ? achieved + o : nullptr,
+                                                   status ? status + o : nullptr, s);
+                      });
+}
+
+int usgscsm_b200_image_to_ground_images_dev(usgscsm_b200_model *const *models, int n_models,
+                                            const int64_t *counts, const double *line,
+                                            const double *samp, const double *height,
+                                            int height_stride, double prec, double *x, double *y,
+                                            double *z, double *achieved, uint32_t *status, void *stream) {
+  if (n_models > 0 && (!line || !samp || !height || !x || !y || !z))
+    return fail(USGSCSM_B200_EINVAL, "null array");
+  const int hs = height_stride ? 1 : 0;
+  return forEachImage(models, n_models, counts, static_cast<cudaStream_t>(stream),
+                      [&](int k, int64_t o, cudaStream_t s) {
+                        return launchImageToGround(*models[k], (long)counts[k], line + o, samp + o, nullptr,
+                                                   hs ? height + o : height, hs, prec, x + o, y + o, z + o,
+                                                   achieved ? achieved + o : nullptr,
+                                                   status ? status + o : nullptr, s);
+                      });
+}
+
+int usgscsm_b200_image_to_ground_grid_images_dev(usgscsm_b200_model *const *models, int n_models,
+                                                 double line0, double samp0, double dline, double dsamp,
+                                                 const int64_t *n_lines, const int64_t *n_samps,
+                                                 const double *height, int height_stride, double prec,
+                                                 double *x, double *y, double *z, double *achieved,
+                                                 uint32_t *status, void *stream) {
+  if (n_models < 0 || (n_models > 0 && (!n_lines || !n_samps || !height || !x || !y || !z)))
+    return fail(USGSCSM_B200_EINVAL, "bad argument");
+  std::vector<int64_t> counts((size_t)(n_models > 0 ? n_models : 0));
+  for (int k = 0; k < n_models; k++) {
+    if (n_lines[k] < 0 || n_samps[k] < 0) return fail(USGSCSM_B200_EINVAL, "negative grid size");
+    counts[(size_t)k] = n_lines[k] * n_samps[k];
+  }
+  const int hs = height_stride ? 1 : 0;
+  return forEachImage(models, n_models, counts.data(), static_cast<cudaStream_t>(stream),
+                      [&](int k, int64_t o, cudaStream_t s) {
+                        GridSpec g{line0, samp0, dline, dsamp, (long)n_samps[k], 0};
+                        return launchImageToGround(*models[k], (long)counts[(size_t)k], nullptr, nullptr, &g,
+                                                   hs ? height + o : height, hs, prec, x + o, y + o, z + o,
+                                                   achieved ? achieved + o : nullptr,
+                                                   status ? status + o : nullptr, s);
+                      });
 }
 
 }  // extern "C"

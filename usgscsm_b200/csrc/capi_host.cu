@@ -33,11 +33,11 @@ static long envLongHost(const char *name, long def, long lo, long hi) {
   return x < lo ? lo : (x > hi ? hi : x);
 }
 int stagedSlots() {
-  static const int n = (int)envLongHost("USGSCSM_B200_STAGE_THREADS", 8, 1, kMaxPipelineSlots);
+  static const int n = (int)envLongHost("USGSCSM_B200_STAGE_THREADS", 12, 1, kMaxPipelineSlots);
   return n;
 }
 long stagedChunk() {
-  static const long n = envLongHost("USGSCSM_B200_STAGE_CHUNK", 1L << 20, 1024, 1L << 26);
+  static const long n = envLongHost("USGSCSM_B200_STAGE_CHUNK", 1L << 18, 1024, 1L << 26);
   return n;
 }
 

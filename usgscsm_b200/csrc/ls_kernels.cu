@@ -291,7 +291,8 @@ __global__ void lsGridTablesKernel(const __grid_constant__ LsState S, GridSpec g
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 3)
+template <int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
     lsImageToGroundGridKernel(const __grid_constant__ LsState S, long n, long nSamps,
                               const double *__restrict__ rowTab, const double *__restrict__ colTab,
                               const double *__restrict__ height, int heightStride, double prec,
@@ -561,9 +562,6 @@ __global__ void ellipsoidElevationKernel(Ellipsoid ell, int n, const double *__r
 }  // namespace
 
 // ---- launchers ---------------------------------------------------------------------------
-// Launch shape: persistent grid of smCount x blocksPerSm blocks.  The two tuning knobs can
-// be overridden from the environment for experiments (USGSCSM_B200_LS_THREADS,
-// USGSCSM_B200_LS_BLOCKS_PER_SM); the defaults are the measured best on B200.
 static int envInt(const char *name, int def) {
   const char *v = getenv(name);
   if (!v || !*v) return def;
@@ -571,6 +569,9 @@ static int envInt(const char *name, int def) {
   return x > 0 ? x : def;
 }
 
+// Launch shape: persistent grid of smCount x blocksPerSm blocks.  The two tuning knobs can
+// be overridden from the environment for experiments (USGSCSM_B200_LS_THREADS,
+// USGSCSM_B200_LS_BLOCKS_PER_SM); the defaults are the measured best on B200.
 static LaunchShape shapeFor(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage,
                             int blocksPerSm) {
   static const int threads = envInt("USGSCSM_B200_LS_THREADS", kDefaultThreads);
@@ -677,11 +678,21 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
     long items = nRows + nCols;
     lsGridTablesKernel<<<(unsigned)((items + 127) / 128), 128, 0, stream>>>(S, *grid, nRows, nCols, rowTab, colTab);
     countLaunch();
+    // register budget of the per-pixel kernel: resident blocks of 256 threads per SM
+    // (USGSCSM_B200_LS_GRID_MINB; the default is the measured best on B200)
+    static const int gridMinb = envInt("USGSCSM_B200_LS_GRID_MINB", 4);
+    const int mb = gridMinb < 3 ? 3 : (gridMinb > 6 ? 6 : gridMinb);
     long blocksNeeded = (n + kThreads - 1) / kThreads;
-    long persistent = (long)smCount * 3;
+    long persistent = (long)smCount * mb;
     int blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
-    lsImageToGroundGridKernel<<<blocks, kThreads, 0, stream>>>(S, n, nCols, rowTab, colTab, height, heightStride,
-                                                              prec, x, y, z, achieved, status);
+#define UB_LAUNCH_GRID(MB)                                                                       \
+  lsImageToGroundGridKernel<MB><<<blocks, kThreads, 0, stream>>>(S, n, nCols, rowTab, colTab, height, \
+                                                                 heightStride, prec, x, y, z, achieved, status)
+    if (mb == 3) UB_LAUNCH_GRID(3);
+    else if (mb == 4) UB_LAUNCH_GRID(4);
+    else if (mb == 5) UB_LAUNCH_GRID(5);
+    else UB_LAUNCH_GRID(6);
+#undef UB_LAUNCH_GRID
     countLaunch();
     e = cudaGetLastError();
     cudaError_t e2 = cudaFreeAsync(scratch, stream);

@@ -51,7 +51,7 @@ struct PipelineSlot {
   long stageBytes = 0;
 };
 
-constexpr int kMaxPipelineSlots = 8;
+constexpr int kMaxPipelineSlots = 16;
 constexpr int kDefaultPipelineSlots = 3;
 constexpr long kDefaultPipelineChunk = 1L << 22;  // 4 Mi points per chunk (~200 MB of I/O)
 // USGSCSM_B200_PIPELINE_SLOTS / USGSCSM_B200_PIPELINE_CHUNK override the defaults (capi.cu)

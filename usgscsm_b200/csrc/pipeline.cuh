@@ -53,8 +53,8 @@ struct Chunk {
 extern thread_local bool tlsSingleThreadPipeline;
 
 bool pipelineThreads();  // USGSCSM_B200_PIPELINE_THREADS=0: pageable arrays are left to the CUDA runtime's staging
-int stagedSlots();       // USGSCSM_B200_STAGE_THREADS (default 8): copier threads = staging slots
-long stagedChunk();      // USGSCSM_B200_STAGE_CHUNK (default 1 Mi points)
+int stagedSlots();       // USGSCSM_B200_STAGE_THREADS (default 12): copier threads = staging slots
+long stagedChunk();      // USGSCSM_B200_STAGE_CHUNK (default 256 Ki points)
 bool hostPointerPageable(const void *p);
 
 inline long roundUp16(long bytes) { return (bytes + 15) & ~15L; }

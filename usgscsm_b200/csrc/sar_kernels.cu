@@ -9,6 +9,8 @@
 //
 // The ephemeris tables (positions, velocities: ~1200 nodes each for an orbital SAR image)
 // and the range-coefficient table are staged once per persistent block into shared memory.
+#include <cstdlib>
+
 #include "kernels.h"
 #include "device_math.cuh"
 #include "work_queue.cuh"
@@ -24,26 +26,51 @@ namespace {
 constexpr int kThreads = 256;
 constexpr size_t kSarMaxStagedBytes = 100 * 1024;  // 2 resident blocks per SM
 
-struct SarTables {
+// Where a kernel reads the tables from: the device arrays of the packed state (rows of 3 doubles),
+// or the block's copy in shared memory, rows padded to 4 doubles on 16-byte boundaries so that a
+// node is two 128-bit loads (unordered points make every lane read its own nodes: fewer, wider
+// shared-memory transactions).
+template <bool PAD>
+struct SarTablesT {
+  static constexpr bool kPadded = PAD;
   const double *positions;
   const double *velocities;
   const double *scale;
 };
+using SarTables = SarTablesT<false>;
 
-__host__ __device__ inline size_t sarTableBytes(const SarState &S) {
-  return ((size_t)S.positions.numNodes * 3 + (size_t)S.velocities.numNodes * 3 +
+template <class TAB>
+UB_DEV void sarApply3(const TAB &, const double *table, const LagrangeWeights &w, double out[3]) {
+  if (TAB::kPadded)
+    lagrangeApplyPadded<3>(table, w, out);
+  else
+    lagrangeApply<3>(table, w, out);
+}
+__host__ __device__ inline size_t sarTableBytes(const SarState &S, bool pad = false) {
+  const size_t row = pad ? 4 : 3;
+  return ((size_t)S.positions.numNodes * row + (size_t)S.velocities.numNodes * row +
           (size_t)S.scale.numNodes * 4) *
          sizeof(double);
 }
 
-__device__ inline SarTables stageSarTables(const SarState &S, double *smem, bool stage) {
-  SarTables t{S.positions.values, S.velocities.values, S.scale.values};
-  if (!stage) return t;
-  const int np = S.positions.numNodes * 3, nv = S.velocities.numNodes * 3,
+// STAGE: copy the tables into `smem`; PAD: rows of 4 doubles there.
+template <bool STAGE, bool PAD = false>
+__device__ inline SarTablesT<STAGE && PAD> stageSarTables(const SarState &S, double *smem) {
+  SarTablesT<STAGE && PAD> t{S.positions.values, S.velocities.values, S.scale.values};
+  if (!STAGE) return t;
+  constexpr int ROW = PAD ? 4 : 3;
+  const int np = S.positions.numNodes * ROW, nv = S.velocities.numNodes * ROW,
             ns = S.scale.numNodes * 4;
   double *sp = smem, *sv = sp + np, *ss = sv + nv;
-  for (int i = threadIdx.x; i < np; i += blockDim.x) sp[i] = __ldg(S.positions.values + i);
-  for (int i = threadIdx.x; i < nv; i += blockDim.x) sv[i] = __ldg(S.velocities.values + i);
+  if (PAD) {
+    for (int i = threadIdx.x; i < np; i += blockDim.x)
+      sp[i] = (i & 3) < 3 ? __ldg(S.positions.values + 3 * (i >> 2) + (i & 3)) : 0.0;
+    for (int i = threadIdx.x; i < nv; i += blockDim.x)
+      sv[i] = (i & 3) < 3 ? __ldg(S.velocities.values + 3 * (i >> 2) + (i & 3)) : 0.0;
+  } else {
+    for (int i = threadIdx.x; i < np; i += blockDim.x) sp[i] = __ldg(S.positions.values + i);
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) sv[i] = __ldg(S.velocities.values + i);
+  }
   for (int i = threadIdx.x; i < ns; i += blockDim.x) ss[i] = __ldg(S.scale.values + i);
   __syncthreads();
   t.positions = sp;
@@ -55,7 +82,8 @@ __device__ inline SarTables stageSarTables(const SarState &S, double *smem, bool
 // getAdjustedSensorPosition SAR:1196-1218 and getAdjustedSensorVelocity SAR:1266-1288 with
 // adj = m_noAdjustments.  Both tables share t0 / dt; when they also have the same node
 // count the Lagrange weights are identical and evaluated once.
-UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double pos[3],
+template <class TAB>
+UB_DEV void sarPosVel(const SarState &S, const TAB &T, double time, double pos[3],
                       double vel[3]) {
   LagrangeWeights w;
   bool haveW = false;
@@ -63,7 +91,7 @@ UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double
     lagrangeWeights(S.positions, S.lag, time, w);
     haveW = true;
     double p[3];
-    lagrangeApply<3>(T.positions, w, p);
+    sarApply3(T, T.positions, w, p);
     pos[0] = p[0] + S.params[0];
     pos[1] = p[1] + S.params[1];
     pos[2] = p[2] + S.params[2];
@@ -76,7 +104,7 @@ UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double
     if (!haveW || S.velocities.numNodes != S.positions.numNodes)
       lagrangeWeights(S.velocities, S.lag, time, w);
     double v[3];
-    lagrangeApply<3>(T.velocities, w, v);
+    sarApply3(T, T.velocities, w, v);
     vel[0] = v[0] + S.params[3];
     vel[1] = v[1] + S.params[4];
     vel[2] = v[2] + S.params[5];
@@ -88,7 +116,8 @@ UB_DEV void sarPosVel(const SarState &S, const SarTables &T, double time, double
 }
 
 // The Doppler-shift function of dopplerShift SAR:603-617; also returns the slant range.
-UB_DEV double sarDoppler(const SarState &S, const SarTables &T, double time, double gx, double gy,
+template <class TAB>
+UB_DEV double sarDoppler(const SarState &S, const TAB &T, double time, double gx, double gy,
                          double gz, double &slantRange) {
   double pos[3], vel[3];
   sarPosVel(S, T, time, pos, vel);
@@ -98,7 +127,8 @@ UB_DEV double sarDoppler(const SarState &S, const SarTables &T, double time, dou
 }
 
 // getRangeCoefficients SAR:1936-1972
-UB_DEV void sarRangeCoefficients(const SarState &S, const SarTables &T, double time, double c[4]) {
+template <class TAB>
+UB_DEV void sarRangeCoefficients(const SarState &S, const TAB &T, double time, double c[4]) {
   if (S.scale.numNodes > 1) {
     LagrangeWeights w;
     lagrangeWeights(S.scale, S.lag, time, w);
@@ -170,87 +200,108 @@ UB_DEV double brentNextPoint(Brent &b, double epsilon) {
   return nextPoint;
 }
 
-// One point of SAR::groundToImage SAR:541-593.
-UB_DEV void sarGroundToImagePoint(const SarState &S, const SarTables &T, double gx, double gy,
-                                  double gz, double desiredPrecision, double &outLine,
-                                  double &outSamp, uint32_t &status) {
-  const double timeTolerance = S.exposureDuration * desiredPrecision / 2.0;
-  const double timePadding = S.exposureDuration * S.nLines * 0.25;
-  const double lowerBound = S.startingEphemerisTime - timePadding;
-  const double upperBound = S.endingEphemerisTime + timePadding;
-
-  // brentRoot with a single inlined copy of the function: stage 0 evaluates the lower
-  // bound, stage 1 the upper bound, stage 2 the iterates.
+// ---- SAR::groundToImage SAR:541-593 as a resumable search ----------------------------------------
+// The zero-Doppler search (brentRoot U:545-622 over dopplerShift SAR:595-632) takes 10 to 32
+// function evaluations depending on the point, so points that share a warp finish at different
+// times.  The search is therefore written as a state that advances by ONE evaluation per call:
+// the kernel below keeps every lane busy by handing a finished lane the next point at once.
+struct SarSearch {
+  double gx, gy, gz;
   Brent b;
-  b.counterPoint = lowerBound;
-  b.currentPoint = upperBound;
-  b.counterFunc = 0.0;
-  b.currentFunc = 0.0;
-  b.previousPoint = b.previousFunc = b.evenOlderPoint = 0.0;
-  b.bisected = true;
-  int stage = 0, iteration = 0;
-  double t = lowerBound, slant = 0.0;
-  bool failed = false;
-  uint32_t evals = 0;
-  for (;;) {
-    evals++;
-    double f = sarDoppler(S, T, t, gx, gy, gz, slant);
-    if (stage == 0) {
-      b.counterFunc = f;
-      t = upperBound;
-      stage = 1;
-      continue;
-    }
-    if (stage == 1) {
-      b.currentFunc = f;
-      if (b.counterFunc * b.currentFunc > 0.0) {  // throws std::invalid_argument
-        failed = true;
-        break;
-      }
-      if (fabs(b.counterFunc) < fabs(b.currentFunc)) {
-        double tp = b.counterPoint;
-        b.counterPoint = b.currentPoint;
-        b.currentPoint = tp;
-        double tf = b.counterFunc;
-        b.counterFunc = b.currentFunc;
-        b.currentFunc = tf;
-      }
-      b.previousPoint = b.counterPoint;
-      b.previousFunc = b.counterFunc;
-      b.evenOlderPoint = b.previousPoint;
-      b.bisected = true;
-      stage = 2;
-      t = brentNextPoint(b, timeTolerance);
-      continue;
-    }
-    // stage 2: f = nextFunc at nextPoint = t
-    if (f == 0) break;
-    if (b.counterFunc * f < 0) {
-      b.currentPoint = t;
-      b.currentFunc = f;
-    } else {
-      b.counterPoint = t;
-      b.counterFunc = f;
-    }
-    if (!(++iteration < 30)) {
-      status |= USGSCSM_B200_ST_ITERATION_CAP;
-      break;
-    }
-    if (!(fabs(b.counterPoint - b.currentPoint) > timeTolerance)) break;
-    t = brentNextPoint(b, timeTolerance);
-  }
+  double t;      // abscissa the next evaluation uses; after the end: the last one evaluated
+  double slant;  // slant range of the last evaluation
+  int stage;     // 0: lower bound, 1: upper bound, 2: iterates
+  int iteration;
+  uint32_t evals;
+  uint32_t status;
+  bool failed;
+};
 
-  status |= evals << USGSCSM_B200_ST_EVALS_SHIFT;
+UB_DEV void sarSearchBegin(const SarState &S, double gx, double gy, double gz, SarSearch &q) {
+  const double timePadding = S.exposureDuration * S.nLines * 0.25;
+  q.gx = gx;
+  q.gy = gy;
+  q.gz = gz;
+  q.b.counterPoint = S.startingEphemerisTime - timePadding;
+  q.b.currentPoint = S.endingEphemerisTime + timePadding;
+  q.b.counterFunc = 0.0;
+  q.b.currentFunc = 0.0;
+  q.b.previousPoint = q.b.previousFunc = q.b.evenOlderPoint = 0.0;
+  q.b.bisected = true;
+  q.stage = 0;
+  q.iteration = 0;
+  q.t = q.b.counterPoint;
+  q.slant = 0.0;
+  q.evals = 0;
+  q.status = 0;
+  q.failed = false;
+}
+
+// One evaluation of the Doppler function and the bookkeeping that follows it in brentRoot.
+// True when the search has ended (q.t, q.slant, q.failed, q.status are final).
+template <class TAB>
+UB_DEV bool sarSearchStep(const SarState &S, const TAB &T, double timeTolerance, SarSearch &q) {
+  Brent &b = q.b;
+  q.evals++;
+  const double f = sarDoppler(S, T, q.t, q.gx, q.gy, q.gz, q.slant);
+  if (q.stage == 0) {
+    b.counterFunc = f;
+    q.t = b.currentPoint;
+    q.stage = 1;
+    return false;
+  }
+  if (q.stage == 1) {
+    b.currentFunc = f;
+    if (b.counterFunc * b.currentFunc > 0.0) {  // throws std::invalid_argument
+      q.failed = true;
+      return true;
+    }
+    if (fabs(b.counterFunc) < fabs(b.currentFunc)) {
+      double tp = b.counterPoint;
+      b.counterPoint = b.currentPoint;
+      b.currentPoint = tp;
+      double tf = b.counterFunc;
+      b.counterFunc = b.currentFunc;
+      b.currentFunc = tf;
+    }
+    b.previousPoint = b.counterPoint;
+    b.previousFunc = b.counterFunc;
+    b.evenOlderPoint = b.previousPoint;
+    b.bisected = true;
+    q.stage = 2;
+    q.t = brentNextPoint(b, timeTolerance);
+    return false;
+  }
+  // stage 2: f = nextFunc at nextPoint = q.t
+  if (f == 0) return true;
+  if (b.counterFunc * f < 0) {
+    b.currentPoint = q.t;
+    b.currentFunc = f;
+  } else {
+    b.counterPoint = q.t;
+    b.counterFunc = f;
+  }
+  if (!(++q.iteration < 30)) {
+    q.status |= USGSCSM_B200_ST_ITERATION_CAP;
+    return true;
+  }
+  if (!(fabs(b.counterPoint - b.currentPoint) > timeTolerance)) return true;
+  q.t = brentNextPoint(b, timeTolerance);
+  return false;
+}
+
+// After the search: time = the last abscissa evaluated; slantRange(groundPt, time) SAR:634-656 is
+// the norm that evaluation computed; ground range by polynomialRoot U:771-791 (maxIterations 30).
+template <class TAB>
+UB_DEV void sarSearchFinish(const SarState &S, const TAB &T, double time, double slant, bool failed,
+                            double desiredPrecision, double &outLine, double &outSamp,
+                            uint32_t &status) {
   if (!failed) {
-    // time = t (the last abscissa evaluated); slantRange(groundPt, time) SAR:634-656 is the
-    // norm already computed by that evaluation.
-    double time = t;
     double c[4];
     sarRangeCoefficients(S, T, time, c);
     double guess = 0.5 * S.nSamples * S.scaledPixelWidth;
     const double groundTolerance = S.scaledPixelWidth * desiredPrecision / 2.0;
     c[0] -= slant;
-    // polynomialRoot U:771-791, maxIterations = 30
     double root = guess;
     double polyValue = poly3(c, root);
     bool converged = false;
@@ -275,8 +326,23 @@ UB_DEV void sarGroundToImagePoint(const SarState &S, const SarTables &T, double 
   outSamp = nan("");
 }
 
+// One point, start to end (the callers that run several searches per point).
+template <class TAB>
+UB_DEV void sarGroundToImagePoint(const SarState &S, const TAB &T, double gx, double gy,
+                                  double gz, double desiredPrecision, double &outLine,
+                                  double &outSamp, uint32_t &status) {
+  const double timeTolerance = S.exposureDuration * desiredPrecision / 2.0;
+  SarSearch q;
+  sarSearchBegin(S, gx, gy, gz, q);
+  while (!sarSearchStep(S, T, timeTolerance, q)) {
+  }
+  status |= q.status | (q.evals << USGSCSM_B200_ST_EVALS_SHIFT);
+  sarSearchFinish(S, T, q.t, q.slant, q.failed, desiredPrecision, outLine, outSamp, status);
+}
+
 // One point of SAR::imageToGround SAR:775-861.
-UB_DEV void sarImageToGroundPoint(const SarState &S, const SarTables &T, double line, double samp,
+template <class TAB>
+UB_DEV void sarImageToGroundPoint(const SarState &S, const TAB &T, double line, double samp,
                                   double height, double desiredPrecision, double &x, double &y,
                                   double &z, double &achieved, uint32_t &status) {
   double time = S.startingEphemerisTime + (line - 0.5) * S.exposureDuration;
@@ -324,15 +390,141 @@ UB_DEV void sarImageToGroundPoint(const SarState &S, const SarTables &T, double 
   if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
 }
 
-template <bool STAGE>
-__global__ void __launch_bounds__(kThreads, UB_SAR_G2I_MINB)
+// groundToImage for a batch.  Every lane runs its own point's search one evaluation per loop
+// pass; a lane whose search has ended parks the result (time, slant range) in the warp's queue
+// in shared memory and takes the next point from the work queue straight away, so the warp
+// never idles behind its slowest point (mean 26 evaluations per point, 32 for the slowest: a
+// warp that waits runs every search to 32).  When the queue holds a warp's worth of results
+// all 32 lanes finish them together (range polynomial, stores).
+constexpr int kSarQueue = 64;  // entries per warp: < 32 left after a flush + at most 32 pushed
+struct SarWarpQueue {
+  double time[kSarQueue];
+  double slant[kSarQueue];
+  long index[kSarQueue];
+  uint32_t status[kSarQueue];  // status bits and the evaluation count; bit 31: no bracket
+};
+
+template <bool STAGE, bool PAD, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
+    sarGroundToImageRefillKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
+                           const double *__restrict__ y, const double *__restrict__ z, double prec,
+                           double *__restrict__ line, double *__restrict__ samp,
+                           double *__restrict__ achieved, uint32_t *__restrict__ status,
+                           unsigned long long *__restrict__ next, int grab) {
+  extern __shared__ __align__(16) double smem[];
+  SarWarpQueue *queues = reinterpret_cast<SarWarpQueue *>(smem);
+  SarWarpQueue &wq = queues[threadIdx.x >> 5];
+  const SarTablesT<STAGE && PAD> T =
+      stageSarTables<STAGE, PAD>(S, smem + (kThreads / 32) * sizeof(SarWarpQueue) / sizeof(double));
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned below = (1u << lane) - 1u;
+  const double timeTolerance = S.exposureDuration * prec / 2.0;
+
+  long chunkNext = 0, chunkEnd = 0;  // this warp's current grab of the work queue (warp-uniform)
+  bool drained = false;              // the work queue is empty
+  int queued = 0;                    // results waiting in wq (warp-uniform)
+  bool busy = false;                 // this lane has a search in flight
+  long point = 0;
+  SarSearch q;
+
+  for (;;) {
+    // idle lanes take the next points
+    unsigned idle = __ballot_sync(0xffffffffu, !busy);
+    while (idle && !drained) {
+      if (chunkNext >= chunkEnd) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(next, (unsigned long long)grab);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if ((long)base >= n) {
+          drained = true;
+          break;
+        }
+        chunkNext = (long)base;
+        chunkEnd = chunkNext + grab < n ? chunkNext + grab : n;
+      }
+      const long avail = chunkEnd - chunkNext;
+      const int rank = __popc(idle & below);
+      if (!busy && rank < avail) {
+        point = chunkNext + rank;
+        sarSearchBegin(S, __ldcs(x + point), __ldcs(y + point), __ldcs(z + point), q);
+        busy = true;
+      }
+      const int wanted = __popc(idle);
+      chunkNext += wanted < avail ? wanted : avail;
+      idle = __ballot_sync(0xffffffffu, !busy);
+    }
+    const unsigned active = __ballot_sync(0xffffffffu, busy);
+    if (active) {
+      bool ended = false;
+      if (busy) ended = sarSearchStep(S, T, timeTolerance, q);
+      const unsigned done = __ballot_sync(0xffffffffu, ended);
+      if (ended) {
+        const int slot = queued + __popc(done & below);
+        wq.time[slot] = q.t;
+        wq.slant[slot] = q.slant;
+        wq.index[slot] = point;
+        wq.status[slot] = q.status | (q.evals << USGSCSM_B200_ST_EVALS_SHIFT) | (q.failed ? 0x80000000u : 0u);
+        busy = false;
+      }
+      queued += __popc(done);
+      __syncwarp();
+    }
+    // finish a warp's worth of results together; at the very end, what is left
+    if (queued >= 32 || (!active && queued > 0)) {
+      const int take = queued < 32 ? queued : 32;
+      if ((int)lane < take) {
+        const long i = wq.index[lane];
+        uint32_t st = wq.status[lane];
+        const bool failed = (st & 0x80000000u) != 0;
+        st &= 0x7fffffffu;
+        double l, s;
+        sarSearchFinish(S, T, wq.time[lane], wq.slant[lane], failed, prec, l, s, st);
+        if (!(isfinite(l) && isfinite(s))) st |= USGSCSM_B200_ST_NONFINITE;
+        // getValidImageRange SAR:1066-1072: (0,0) .. (nLines, nSamples)
+        if (!(l >= 0.0 && l <= 0.0 + S.nLines && s >= 0.0 && s <= 0.0 + S.nSamples))
+          st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+        __stcs(line + i, l);
+        __stcs(samp + i, s);
+        if (achieved) __stcs(achieved + i, nan(""));  // SAR groundToImage never writes achievedPrecision
+        if (status) __stcs(status + i, st);
+      }
+      __syncwarp();
+      const int left = queued - take;
+      double mt = 0.0, ms = 0.0;
+      long mi = 0;
+      uint32_t mst = 0;
+      if ((int)lane < left) {
+        mt = wq.time[32 + lane];
+        ms = wq.slant[32 + lane];
+        mi = wq.index[32 + lane];
+        mst = wq.status[32 + lane];
+      }
+      __syncwarp();
+      if ((int)lane < left) {
+        wq.time[lane] = mt;
+        wq.slant[lane] = ms;
+        wq.index[lane] = mi;
+        wq.status[lane] = mst;
+      }
+      __syncwarp();
+      queued = left;
+    }
+    if (!active && drained && queued == 0) break;
+  }
+}
+
+// The plain form: a warp takes 32 points and runs their searches in lockstep.  Best when
+// neighbouring points need the same number of evaluations (dense grids: 30.4 of 32 lanes active
+// on average) -- and with the fewest registers.
+template <bool STAGE, bool PAD, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
     sarGroundToImageKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z, double prec,
                            double *__restrict__ line, double *__restrict__ samp,
                            double *__restrict__ achieved, uint32_t *__restrict__ status,
                            unsigned long long *__restrict__ next, int grab) {
-  extern __shared__ double smem[];
-  SarTables T = stageSarTables(S, smem, STAGE);
+  extern __shared__ __align__(16) double smem[];
+  const SarTablesT<STAGE && PAD> T = stageSarTables<STAGE, PAD>(S, smem);
   forEachPointDynamic(n, next, grab, [&](long i) {
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s;
@@ -357,8 +549,8 @@ __global__ void __launch_bounds__(kThreads)
                            double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
                            double *__restrict__ achieved, uint32_t *__restrict__ status,
                            unsigned long long *__restrict__ next, int grab) {
-  extern __shared__ double smem[];
-  SarTables T = stageSarTables(S, smem, STAGE);
+  extern __shared__ __align__(16) double smem[];
+  const SarTables T = stageSarTables<STAGE>(S, smem);
   forEachPointDynamic(n, next, grab, [&](long i) {
     double l, s;
     if (GRID) {
@@ -389,8 +581,8 @@ __global__ void __launch_bounds__(kThreads)
                             const double *__restrict__ y, const double *__restrict__ z,
                             double *__restrict__ partials, uint32_t *__restrict__ status,
                             unsigned long long *__restrict__ next, int grab) {
-  extern __shared__ double smem[];
-  SarTables T = stageSarTables(S, smem, STAGE);
+  extern __shared__ __align__(16) double smem[];
+  const SarTables T = stageSarTables<STAGE>(S, smem);
   forEachPointDynamic(n, next, grab, [&](long i) {
     const double g[3] = {__ldcs(x + i), __ldcs(y + i), __ldcs(z + i)};
     const double delta = S.scaledPixelWidth;
@@ -422,8 +614,8 @@ template <bool STAGE>
 __global__ void __launch_bounds__(kThreads)
     sarRemoteLocusKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ line,
                          const double *__restrict__ samp, double prec, LocusOut o) {
-  extern __shared__ double smem[];
-  SarTables T = stageSarTables(S, smem, STAGE);
+  extern __shared__ __align__(16) double smem[];
+  const SarTables T = stageSarTables<STAGE>(S, smem);
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     double l = __ldcs(line + i), s = __ldcs(samp + i);
@@ -449,8 +641,8 @@ __global__ void __launch_bounds__(kThreads)
     sarProximateLocusKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ line,
                             const double *__restrict__ samp, const double *__restrict__ x,
                             const double *__restrict__ y, const double *__restrict__ z, LocusOut o) {
-  extern __shared__ double smem[];
-  SarTables T = stageSarTables(S, smem, STAGE);
+  extern __shared__ __align__(16) double smem[];
+  const SarTables T = stageSarTables<STAGE>(S, smem);
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     double time = S.startingEphemerisTime + (__ldcs(line + i) - 0.5) * S.exposureDuration;
@@ -487,12 +679,13 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
-LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
-  size_t bytes = sarTableBytes(S);
+LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, bool &stage,
+                     size_t extraSmem = 0, int maxPerSm = kBlocksPerSm, bool pad = false) {
+  size_t bytes = sarTableBytes(S, pad);
   stage = bytes <= kSarMaxStagedBytes;
-  smemBytes = stage ? bytes : 0;
-  int perSm = kBlocksPerSm;
-  if (stage && smemBytes > 0) {
+  smemBytes = (stage ? bytes : 0) + extraSmem;
+  int perSm = maxPerSm;
+  if (smemBytes > 0) {
     size_t fit = (size_t)(220 * 1024) / (smemBytes + 1024);
     if (fit < (size_t)perSm) perSm = (int)(fit < 1 ? 1 : fit);
   }
@@ -503,6 +696,11 @@ LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, 
   sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
   if (sh.blocks < 1) sh.blocks = 1;
   return sh;
+}
+
+int sarEnv(const char *name, int def) {
+  const char *v = getenv(name);
+  return v && *v ? atoi(v) : def;
 }
 
 template <class K>
@@ -516,7 +714,7 @@ cudaError_t allowSmem(K kernel, size_t bytes) {
 // getSensorVelocity(ImageCoord) SAR:1232-1238, per image point.
 __global__ void sarSensorStateKernel(const __grid_constant__ SarState S, long n,
                                      const double *__restrict__ line, SensorStateOut o) {
-  SarTables T = stageSarTables(S, nullptr, false);
+  const SarTables T = stageSarTables<false>(S, nullptr);
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const double time =
@@ -545,21 +743,43 @@ cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const
   if (n <= 0) return cudaSuccess;
   size_t smemBytes;
   bool stage;
-  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage);
-  if (stage) {
-    cudaError_t e = allowSmem(sarGroundToImageKernel<true>, smemBytes);
-    if (e != cudaSuccess) return e;
-  }
+  // USGSCSM_B200_SAR_REFILL: lanes take a new point as soon as their search ends (1) or warps run
+  // 32 searches in lockstep (0, default: see DESIGN.md); USGSCSM_B200_SAR_PAD: staged tables in rows
+  // of 4 doubles; USGSCSM_B200_SAR_MINB: register budget as resident blocks per SM (2 or 3)
+  static const int refill = sarEnv("USGSCSM_B200_SAR_REFILL", 0);
+  static const int pad = sarEnv("USGSCSM_B200_SAR_PAD", 0);
+  static const int minb = sarEnv("USGSCSM_B200_SAR_MINB", 3);
+  const size_t queueBytes = refill ? (kThreads / 32) * sizeof(SarWarpQueue) : 0;
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage, queueBytes, minb >= 3 ? 3 : 2, pad != 0);
   WorkCounter wc;
-  cudaError_t e = wc.acquire(stream);
+  cudaError_t e = cudaSuccess;
+#define UB_SAR_G2I(KERNEL, STAGE, PAD, MINB)                                                      \
+  do {                                                                                            \
+    e = allowSmem(KERNEL<STAGE, PAD, MINB>, smemBytes);                                           \
+    if (e == cudaSuccess) e = wc.acquire(stream);                                                 \
+    if (e == cudaSuccess)                                                                         \
+      KERNEL<STAGE, PAD, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(                     \
+          S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());                 \
+  } while (0)
+#define UB_SAR_G2I_M(KERNEL, STAGE, PAD)            \
+  do {                                              \
+    if (minb >= 3) UB_SAR_G2I(KERNEL, STAGE, PAD, 3); \
+    else UB_SAR_G2I(KERNEL, STAGE, PAD, 2);         \
+  } while (0)
+#define UB_SAR_G2I_K(KERNEL)                                   \
+  do {                                                         \
+    if (stage && pad) UB_SAR_G2I_M(KERNEL, true, true);        \
+    else if (stage) UB_SAR_G2I_M(KERNEL, true, false);         \
+    else UB_SAR_G2I_M(KERNEL, false, false);                   \
+  } while (0)
+  if (refill)
+    UB_SAR_G2I_K(sarGroundToImageRefillKernel);
+  else
+    UB_SAR_G2I_K(sarGroundToImageKernel);
+#undef UB_SAR_G2I_K
+#undef UB_SAR_G2I_M
+#undef UB_SAR_G2I
   if (e != cudaSuccess) return e;
-  if (stage) {
-    sarGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
-  } else {
-    sarGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
-  }
   countLaunch();
   return wc.release();
 }

@@ -917,6 +917,83 @@ def _image_to_ground_dem(self, dem, line, samp, h0=0.0, tolerance=0.01, maxItera
 RasterGM.groundToImageDemGrid = _ground_to_image_dem_grid
 RasterGM.imageToGroundDem = _image_to_ground_dem
 
+
+# ---- many small images per call ----------------------------------------------------------------------
+def _handles(models):
+    return (C.c_void_p * len(models))(*[m._h for m in models])
+
+
+def groundToImageImages(models, counts, x, y, z, desiredPrecision=0.001, achieved=False, status=True,
+                        out=None, stream=None):
+    """groundToImage of several images in one call: models[k] takes the next counts[k] points of
+    the concatenated torch CUDA tensors; the images' kernels overlap on internal streams.
+    Returns (line, samp, achieved, status)."""
+    import torch
+    n = int(sum(counts))
+    _dev_inputs(models[0], n, x, y, z)
+    if out is None:
+        line, samp = torch.empty_like(x), torch.empty_like(x)
+        ach = torch.empty_like(x) if achieved else None
+        st = torch.empty(n, dtype=torch.int32, device=x.device) if status else None
+    else:
+        line, samp, ach, st = out
+    if stream is None:
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+    cnt = (C.c_int64 * len(models))(*[int(c) for c in counts])
+    check(lib.usgscsm_b200_ground_to_image_images_dev(
+        _handles(models), len(models), cnt, _ptr(x), _ptr(y), _ptr(z), desiredPrecision, _ptr(line),
+        _ptr(samp), _ptr(ach), _ptr(st), stream))
+    return line, samp, ach, st
+
+
+def imageToGroundImages(models, counts, line, samp, height, desiredPrecision=0.001, achieved=False,
+                        status=True, stream=None):
+    """imageToGround of several images in one call (explicit pixel arrays, concatenated).
+    Returns (x, y, z, achieved, status)."""
+    import torch
+    n = int(sum(counts))
+    _dev_inputs(models[0], n, line, samp)
+    if not _is_torch(height):
+        height = torch.full((1,), float(height), dtype=torch.float64, device=line.device)
+    stride = 0 if height.numel() == 1 else 1
+    _dev_inputs(models[0], n if stride else 1, height)
+    x, y, z = (torch.empty_like(line) for _ in range(3))
+    ach = torch.empty_like(line) if achieved else None
+    st = torch.empty(n, dtype=torch.int32, device=line.device) if status else None
+    if stream is None:
+        stream = torch.cuda.current_stream(line.device).cuda_stream
+    cnt = (C.c_int64 * len(models))(*[int(c) for c in counts])
+    check(lib.usgscsm_b200_image_to_ground_images_dev(
+        _handles(models), len(models), cnt, _ptr(line), _ptr(samp), _ptr(height), stride,
+        desiredPrecision, _ptr(x), _ptr(y), _ptr(z), _ptr(ach), _ptr(st), stream))
+    return x, y, z, ach, st
+
+
+def imageToGroundGridImages(models, line0, samp0, dline, dsamp, n_lines, n_samps, height,
+                            desiredPrecision=0.001, achieved=False, status=True, out=None, stream=None):
+    """Dense-grid imageToGround of several images in one call: image k is the n_lines[k] x
+    n_samps[k] grid; `height`: torch CUDA tensor with 1 entry or one per point of all grids.
+    Returns (x, y, z, achieved, status), the images' points one after the other."""
+    import torch
+    n = int(sum(int(a) * int(b) for a, b in zip(n_lines, n_samps)))
+    stride = 0 if height.numel() == 1 else 1
+    _dev_inputs(models[0], n if stride else 1, height)
+    dev = height.device
+    if out is None:
+        x, y, z = (torch.empty(n, dtype=torch.float64, device=dev) for _ in range(3))
+        ach = torch.empty(n, dtype=torch.float64, device=dev) if achieved else None
+        st = torch.empty(n, dtype=torch.int32, device=dev) if status else None
+    else:
+        x, y, z, ach, st = out
+    if stream is None:
+        stream = torch.cuda.current_stream(dev).cuda_stream
+    nl = (C.c_int64 * len(models))(*[int(v) for v in n_lines])
+    ns = (C.c_int64 * len(models))(*[int(v) for v in n_samps])
+    check(lib.usgscsm_b200_image_to_ground_grid_images_dev(
+        _handles(models), len(models), float(line0), float(samp0), float(dline), float(dsamp), nl, ns,
+        _ptr(height), stride, desiredPrecision, _ptr(x), _ptr(y), _ptr(z), _ptr(ach), _ptr(st), stream))
+    return x, y, z, ach, st
+
 def stateToMsgpack(modelState):
     """The msgpack binary form of a model state, as the reference writes it
     (nlohmann::json::to_msgpack; bin/usgscsm_cam_test.cc --output-binary-model-state)."""
