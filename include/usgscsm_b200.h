@@ -598,6 +598,48 @@ USGSCSM_B200_API int usgscsm_b200_lagrange_interp(int device, int num_time, cons
                                  double start_time, double del_time, int vector_length, int order,
                                  int64_t n, const double *times, double *out);
 
+/* The remaining free functions the reference tests directly (tests/UtilitiesTests.cpp:55-284,
+ * 443-475), batched over n inputs with HOST pointers, so that its known-answer vectors can be
+ * replayed on the device functions the kernels are built from.
+ *
+ * computeDistortedFocalPlaneCoordinates (src/Utilities.cpp:129-151): pixel -> focal plane (mm).
+ * affine12 = iTransS[0..2], iTransL[0..2], sampleOrigin, lineOrigin, sampleSumming, lineSumming,
+ * startingSample, startingLine. */
+USGSCSM_B200_API int usgscsm_b200_focal_plane_coordinates(int device, const double affine12[12], int64_t n,
+                                                         const double *line, const double *sample,
+                                                         double *focal_x, double *focal_y);
+/* computePixel (src/Utilities.cpp:317-331): focal plane (mm) -> pixel. */
+USGSCSM_B200_API int usgscsm_b200_compute_pixel(int device, const double affine12[12], int64_t n,
+                                               const double *focal_x, const double *focal_y, double *line,
+                                               double *sample);
+/* createCameraLookVector (src/Utilities.cpp:360-373): look = 3 doubles per input (x, y, z). */
+USGSCSM_B200_API int usgscsm_b200_camera_look_vector(int device, double z_direction, double focal_length,
+                                                    int64_t n, const double *focal_x, const double *focal_y,
+                                                    double *look);
+/* removeJitter / addJitter (src/Utilities.cpp:182-282): rolling-shutter jitter polynomial of the
+ * frame model; remove != 0 selects removeJitter.  addJitter's tolerance / max_iterations as in the
+ * reference's signature (defaults 1e-6, 20). */
+USGSCSM_B200_API int usgscsm_b200_jitter(int device, int remove, int num_coeffs, const double *line_jitter,
+                                        const double *sample_jitter, int num_line_times,
+                                        const double *line_times, double tolerance, int max_iterations,
+                                        int64_t n, const double *line, const double *sample,
+                                        double *out_line, double *out_sample);
+/* evaluatePolynomial / evaluatePolynomialDerivative (src/Utilities.cpp:696-727) of
+ * c[0] + c[1] x + c[2] x^2 + c[3] x^3; either output may be NULL. */
+USGSCSM_B200_API int usgscsm_b200_polynomial(int device, const double coeffs4[4], int64_t n, const double *x,
+                                            double *value, double *derivative);
+/* polynomialRoot (src/Utilities.cpp:771-791, maxIterations 30) of the same cubic from guess[i];
+ * status: USGSCSM_B200_ST_ERROR_UNKNOWN where the reference throws. */
+USGSCSM_B200_API int usgscsm_b200_polynomial_root(int device, const double coeffs4[4], double threshold,
+                                                 int64_t n, const double *guess, double *root,
+                                                 uint32_t *status);
+/* brentRoot (src/Utilities.cpp:545-622) of the same cubic between lower[i] and upper[i]; status:
+ * USGSCSM_B200_ST_ERROR_UNKNOWN where the reference throws (no sign change),
+ * USGSCSM_B200_ST_ITERATION_CAP after 30 iterations; bits 16-23: function evaluations. */
+USGSCSM_B200_API int usgscsm_b200_brent_root(int device, const double coeffs4[4], double epsilon, int64_t n,
+                                            const double *lower, const double *upper, double *root,
+                                            uint32_t *status);
+
 /* Self-test of the engine's division: the kernels replace a / b by divideBy(a, b, r) with a
  * hoisted reciprocal (usgscsm_b200/csrc/device_math.cuh), which must equal the IEEE quotient
  * bit for bit.  Compares the two on `pairs` pseudo-random operand pairs (all exponents,

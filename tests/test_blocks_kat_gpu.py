@@ -116,3 +116,79 @@ def test_division_with_hoisted_reciprocal_is_ieee_division():
     for seed in (1, 20261104):
         _capi.check(_capi.lib.usgscsm_b200_selftest_division(0, 1_000_000_000, seed, C.byref(bad)))
         assert bad.value == 0
+
+
+# ---- tests/UtilitiesTests.cpp:55-284, 443-475 on the device functions ------------------------------
+def test_kat_focal_plane_affine():
+    """computeDistortedFocalPlaneCoordinates (UtilitiesTests.cpp:55-101) and computePixel (:238-282):
+    EXPECT_DOUBLE_EQ = 4 ulp."""
+    from usgscsm_b200 import plugin as P
+    S, L = [0.0, 0.0, 10.0], [0.0, 10.0, 0.0]
+    for args, expect, tol in (
+            ((0.5, 4.0, 8.0, 0.5, 1.0, 1.0, 0.0, 0.0, S, L), (0.0, -0.4), 0),                 # :55
+            ((2.0, 4.0, 8.0, 8.0, 2.0, 2.0, 0.0, 0.0, S, L), (-0.4, 0.0), 0),                 # :66 Summing
+            ((11.0, -9.0, 0.0, 0.0, 1.0, 1.0, 0.0, 0.0, [-10.0, 0.0, 0.1], [10.0, -0.1, 0.0]), (-10.0, 10.0), 1e-12),  # :77
+            ((2.0, 4.0, 8.0, 8.0, 1.0, 1.0, 2.0, 1.0, S, L), (-0.5, -0.2), 0)):               # :88 Start
+        x, y = P.computeDistortedFocalPlaneCoordinates([args[0]], [args[1]], *args[2:])
+        assert _close([x[0], y[0]], expect, tol), args
+    for args, expect in (
+            ((0.0, -0.4, 8.0, 0.5, 1.0, 1.0, 0.0, 0.0, S, L), (0.5, 4.0)),                    # :238
+            ((-0.4, 0.0, 8.0, 8.0, 2.0, 2.0, 0.0, 0.0, S, L), (2.0, 4.0)),                    # :248
+            ((-0.5, -0.2, 8.0, 8.0, 1.0, 1.0, 2.0, 1.0, S, L), (2.0, 4.0)),                   # :258
+            ((-0.5, -0.2, 8.0, 8.0, 2.0, 4.0, 2.0, 1.0, S, L), (0.5, 2.0))):                  # :268
+        line, samp = P.computePixel([args[0]], [args[1]], *args[2:])
+        assert _close([line[0], samp[0]], expect, 0), args
+
+
+def test_kat_camera_look_vector():
+    """createCameraLookVector (UtilitiesTests.cpp:278-284)."""
+    from usgscsm_b200 import plugin as P
+    look = P.createCameraLookVector([0.0], [-0.4], 1, 50)[0]
+    assert _close(look, [0.0, 0.007999744, -0.999968001], 1e-8)
+
+
+def test_kat_jitter():
+    """removeJitter / addJitter (UtilitiesTests.cpp:103-236)."""
+    import usgscsm_b200 as ub
+    from usgscsm_b200 import plugin as P
+    lj, sj, lt = [2.0, 3.0, 4.0], [-10.0, -20.0, -30.0], [0.0, 1.0, 2.0, 3.0, 4.0]
+    rm = lambda l, s: tuple(v[0] for v in P.removeJitter([l], [s], lj, sj, lt))
+    assert _close(rm(1, 0), (1, 0), 0)                                            # t = 0: nothing
+    assert _close(rm(2, 5.0), (2 - (2.0 + 3.0 + 4.0), 5.0 + (10.0 + 20.0 + 30.0)), 0)   # t = 1
+    assert _close(rm(3, 5.0), (3 - (8 * 2.0 + 4 * 3.0 + 2 * 4.0), 5.0 + (8 * 10.0 + 4 * 20.0 + 2 * 30.0)), 0)
+    a, b = rm(1, 0), rm(-100, 0)                                                   # bounded to the image
+    assert _close((-100 - b[0], 0 - b[1]), (1 - a[0], 0 - a[1]), 0)
+    a, b = rm(5.0, 0), rm(100, 0)
+    assert _close((100 - b[0], 0 - b[1]), (5.0 - a[0], 0 - a[1]), 0)
+    a = rm(1.0, 5.0)                                                               # rounding of the line
+    for frac in (0.75, 1.35):
+        b = rm(frac, 5.0)
+        assert _close((frac - b[0], 5.0 - b[1]), (1.0 - a[0], 5.0 - a[1]), 0)
+    for bad in ((lj[:2], sj, lt), (lj, sj + [-40.0], lt), (lj, sj, [])):           # removeJitterErrors
+        with pytest.raises(ub.Error):
+            P.removeJitter([4], [15], *bad)
+    lj2, sj2 = [0.01, 0.02, 0.03], [-0.01, -0.02, -0.03]                           # addJitter :203-236
+    dl, ds = P.removeJitter([4], [15.0], lj2, sj2, lt)
+    jl, js = P.addJitter(dl, ds, 1e-7, 30, lj2, sj2, lt)
+    assert abs(jl[0] - 4) <= 1e-7 and abs(js[0] - 15.0) <= 1e-7
+
+
+def test_kat_polynomial_and_roots():
+    """polynomialEval, polynomialRoot, brentRoot (UtilitiesTests.cpp:443-475)."""
+    from usgscsm_b200 import plugin as P, _capi
+    c = [-12.0, 4.0, -3.0, 1.0]
+    x = [-1.0, 0.0, 2.0, 3.5]
+    assert _close(P.evaluatePolynomial(c, x), [-20.0, -12.0, -8.0, 8.125], 0)
+    assert _close(P.evaluatePolynomialDerivative(c, x), [13.0, 4.0, 4.0, 19.75], 0)
+    with pytest.raises(ValueError):
+        P.evaluatePolynomial([], [0.0])
+    root, st = P.polynomialRoot(c, [0.0])
+    assert abs(root[0] - 3.0) <= 1e-10 and st[0] == 0
+    root, st = P.polynomialRoot([4.0, 0.0, 1.0], [0.0])        # no real root: the reference throws
+    assert st[0] & _capi.ST_ERROR_UNKNOWN and np.isnan(root[0])
+    # (x - 2)(x + 1)(x + 7) = x^3 + 6 x^2 - 9 x - 14
+    poly = [-14.0, -9.0, 6.0, 1.0]
+    root, st = P.brentRoot([1.0, 0.0, -3.0], [3.0, -3.0, 3.0], poly, 1e-10)
+    assert abs(root[0] - 2.0) <= 1e-10 and abs(root[1] + 1.0) <= 1e-10
+    assert not (st[:2] & _capi.ST_ERROR_UNKNOWN).any()
+    assert st[2] & _capi.ST_ERROR_UNKNOWN and np.isnan(root[2])   # brentRoot(-3, 3): std::invalid_argument

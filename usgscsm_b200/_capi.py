@@ -196,6 +196,16 @@ SIGNATURES = {
     "usgscsm_b200_lagrange_interp": (
         C.c_int, [C.c_int, C.c_int, _dp, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int64, _dp,
                   _dp]),
+    "usgscsm_b200_focal_plane_coordinates": (C.c_int, [C.c_int, _dp, C.c_int64, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_compute_pixel": (C.c_int, [C.c_int, _dp, C.c_int64, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_camera_look_vector": (
+        C.c_int, [C.c_int, C.c_double, C.c_double, C.c_int64, _dp, _dp, _dp]),
+    "usgscsm_b200_jitter": (
+        C.c_int, [C.c_int, C.c_int, C.c_int, _dp, _dp, C.c_int, _dp, C.c_double, C.c_int, C.c_int64,
+                  _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_polynomial": (C.c_int, [C.c_int, _dp, C.c_int64, _dp, _dp, _dp]),
+    "usgscsm_b200_polynomial_root": (C.c_int, [C.c_int, _dp, C.c_double, C.c_int64, _dp, _dp, _dp]),
+    "usgscsm_b200_brent_root": (C.c_int, [C.c_int, _dp, C.c_double, C.c_int64, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_selftest_division": (C.c_int, [C.c_int, C.c_int64, C.c_uint64, C.POINTER(C.c_uint64)]),
     "usgscsm_b200_kernel_launches": (C.c_int64, []),
 }

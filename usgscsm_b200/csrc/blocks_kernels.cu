@@ -40,6 +40,67 @@ __global__ void lagrangeKernel(UniformTable tab, LagrangeDivisors lag, long n, c
   }
 }
 
+// The focal-plane affine both ways, the look vector, the cubic and its roots: the free functions
+// tests/UtilitiesTests.cpp:55-284, 443-475 exercise, over arrays.
+__global__ void focalPlaneKernel(const __grid_constant__ FocalPlane fp, int toPixel, long n,
+                                 const double *__restrict__ a, const double *__restrict__ b,
+                                 double *__restrict__ outA, double *__restrict__ outB) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double u, v;
+    if (toPixel)
+      computePixel(a[i], b[i], fp, u, v);  // (focal x, y) -> (line, sample)
+    else
+      distortedFocalPlaneCoordinates(a[i], b[i], fp, u, v);  // (line, sample) -> (focal x, y)
+    outA[i] = u;
+    outB[i] = v;
+  }
+}
+
+__global__ void lookVectorKernel(double zDirection, double focalLength, long n,
+                                 const double *__restrict__ ux, const double *__restrict__ uy,
+                                 double *__restrict__ look) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l[3];
+    cameraLookVector(ux[i], uy[i], zDirection, focalLength, l);
+    look[3 * i] = l[0];
+    look[3 * i + 1] = l[1];
+    look[3 * i + 2] = l[2];
+  }
+}
+
+struct Cubic {
+  double c[4];
+};
+
+// mode 0: value / derivative at x; 1: polynomialRoot from guess a; 2: brentRoot between a and b
+__global__ void cubicKernel(Cubic P, int mode, double eps, long n, const double *__restrict__ a,
+                            const double *__restrict__ b, double *__restrict__ out0,
+                            double *__restrict__ out1, uint32_t *__restrict__ status) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    if (mode == 0) {
+      if (out0) out0[i] = poly3(P.c, a[i]);
+      if (out1) out1[i] = poly3Derivative(P.c, a[i]);
+    } else if (mode == 1) {
+      double root;
+      const bool ok = polynomialRoot3(P.c, a[i], eps, root);
+      out0[i] = ok ? root : nan("");
+      if (status) status[i] = ok ? 0u : (uint32_t)USGSCSM_B200_ST_ERROR_UNKNOWN;
+    } else {
+      BrentSearch q;
+      brentBegin(a[i], b[i], q);
+      while (!brentStep([&](double t) { return poly3(P.c, t); }, eps, q)) {
+      }
+      out0[i] = q.failed ? nan("") : q.t;
+      if (status)
+        status[i] = q.status | (q.evals << USGSCSM_B200_ST_EVALS_SHIFT) |
+                    (q.failed ? (uint32_t)USGSCSM_B200_ST_ERROR_UNKNOWN : 0u);
+    }
+  }
+}
+
 // AoS <-> SoA for the csm value types (csm::EcefCoord = 3 doubles, csm::ImageCoord = 2,
 // csm/csm.h:212-308): arrays of structs are copied to the device as they are and split /
 // joined there, so the per-point kernels always see coalesced SoA arrays.
@@ -267,6 +328,35 @@ cudaError_t launchSensorPartialsStep(long n, const double *l0, const double *s0,
   int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
   sensorPartialsStepKernel<<<blocks, 256, 0, stream>>>(n, l0, s0, st0, l1, s1, achP, stP, delta,
                                                        partials, numParams, k, achieved, status);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+static int katBlocks(long n) { return (int)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184); }
+
+cudaError_t launchFocalPlane(const FocalPlane &fp, int toPixel, long n, const double *a, const double *b,
+                             double *outA, double *outB, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  focalPlaneKernel<<<katBlocks(n), 256, 0, stream>>>(fp, toPixel, n, a, b, outA, outB);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchLookVector(double zDirection, double focalLength, long n, const double *ux,
+                             const double *uy, double *look, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  lookVectorKernel<<<katBlocks(n), 256, 0, stream>>>(zDirection, focalLength, n, ux, uy, look);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchCubic(const double coeffs[4], int mode, double eps, long n, const double *a,
+                        const double *b, double *out0, double *out1, uint32_t *status,
+                        cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  Cubic P;
+  for (int k = 0; k < 4; k++) P.c[k] = coeffs[k];
+  cubicKernel<<<katBlocks(n), 256, 0, stream>>>(P, mode, eps, n, a, b, out0, out1, status);
   countLaunch();
   return cudaGetLastError();
 }

@@ -796,6 +796,16 @@ int allSensorPartialsDev(usgscsm_b200_model *m, int n_indices, const int *indice
                          double *partials, double *achieved, uint32_t *status,
                          cudaStream_t stream) {
   const bool haveImage = img_line && img_samp;
+  if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER) {
+    // one kernel: the searches share the seed and the interpolations of their first two evaluations
+    cudaError_t fe = cudaSuccess;
+    if (launchLsAllSensorPartials(m->ls, m->smCount, n_indices, indices, n, x, y, z,
+                                  haveImage ? img_line : nullptr, haveImage ? img_samp : nullptr, prec,
+                                  partials, achieved, status, stream, fe)) {
+      UB_CUDA(fe);
+      return USGSCSM_B200_OK;
+    }
+  }
   double *scratch = nullptr;
   uint32_t *stScratch = nullptr;
   std::vector<double *> pfTables;
@@ -1044,6 +1054,154 @@ int usgscsm_b200_lagrange_interp(int device, int num_time, const double *values,
     UB_CUDA(launchLagrange(tab, lag, vector_length, (long)n, dt, dout, nullptr));
     UB_CUDA(cudaMemcpy(out, dout, n * vector_length * sizeof(double), cudaMemcpyDeviceToHost));
     return USGSCSM_B200_OK;
+  });
+}
+
+// ---- the reference's remaining free functions, for known-answer replay ------------------------
+}  // extern "C"
+namespace ub200 {
+void fillFocalPlaneInverse(FocalPlane &fp);  // model_ls.cu
+}
+namespace {
+FocalPlane affineFocalPlane(const double a[12]) {
+  FocalPlane fp{};
+  for (int i = 0; i < 3; i++) {
+    fp.iTransS[i] = a[i];
+    fp.iTransL[i] = a[3 + i];
+  }
+  fp.detectorSampleOrigin = a[6];
+  fp.detectorLineOrigin = a[7];
+  fp.detectorSampleSumming = a[8];
+  fp.detectorLineSumming = a[9];
+  fp.startingDetectorSample = a[10];
+  fp.startingDetectorLine = a[11];
+  fillFocalPlaneInverse(fp);
+  fp.lineSumming.b = fp.detectorLineSumming;
+  fp.sampleSumming.b = fp.detectorSampleSumming;
+  fillDivisors({&fp.lineSumming, &fp.sampleSumming});
+  return fp;
+}
+
+// n-element host arrays in, n * outWidth-element host arrays out, through one small kernel
+template <class Launch>
+int katCall(int device, int64_t n, Launch &&launch) {
+  if (n < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (n == 0) return USGSCSM_B200_OK;
+  if (device < 0 || device >= deviceCount())
+    return fail(USGSCSM_B200_ENODEVICE, "no usable CUDA device with that index");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(device));
+    DevArrays d;
+    launch(d);
+    return USGSCSM_B200_OK;
+  });
+}
+template <class T>
+void download(T *host, const T *dev, size_t count) {
+  if (host) UB_CUDA(cudaMemcpy(host, dev, count * sizeof(T), cudaMemcpyDeviceToHost));
+}
+}  // namespace
+extern "C" {
+
+int usgscsm_b200_focal_plane_coordinates(int device, const double affine12[12], int64_t n,
+                                         const double *line, const double *sample, double *focal_x,
+                                         double *focal_y) {
+  if (!affine12 || (n > 0 && (!line || !sample || !focal_x || !focal_y)))
+    return fail(USGSCSM_B200_EINVAL, "null argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    const FocalPlane fp = affineFocalPlane(affine12);
+    const double *a = d.upload(line, (size_t)n), *b = d.upload(sample, (size_t)n);
+    double *oa = d.alloc<double>((size_t)n), *ob = d.alloc<double>((size_t)n);
+    UB_CUDA(launchFocalPlane(fp, 0, (long)n, a, b, oa, ob, nullptr));
+    download(focal_x, oa, (size_t)n);
+    download(focal_y, ob, (size_t)n);
+  });
+}
+
+int usgscsm_b200_compute_pixel(int device, const double affine12[12], int64_t n, const double *focal_x,
+                               const double *focal_y, double *line, double *sample) {
+  if (!affine12 || (n > 0 && (!line || !sample || !focal_x || !focal_y)))
+    return fail(USGSCSM_B200_EINVAL, "null argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    const FocalPlane fp = affineFocalPlane(affine12);
+    const double *a = d.upload(focal_x, (size_t)n), *b = d.upload(focal_y, (size_t)n);
+    double *oa = d.alloc<double>((size_t)n), *ob = d.alloc<double>((size_t)n);
+    UB_CUDA(launchFocalPlane(fp, 1, (long)n, a, b, oa, ob, nullptr));
+    download(line, oa, (size_t)n);
+    download(sample, ob, (size_t)n);
+  });
+}
+
+int usgscsm_b200_camera_look_vector(int device, double z_direction, double focal_length, int64_t n,
+                                    const double *focal_x, const double *focal_y, double *look) {
+  if (n > 0 && (!focal_x || !focal_y || !look)) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    const double *a = d.upload(focal_x, (size_t)n), *b = d.upload(focal_y, (size_t)n);
+    double *o = d.alloc<double>((size_t)n * 3);
+    UB_CUDA(launchLookVector(z_direction, focal_length, (long)n, a, b, o, nullptr));
+    download(look, o, (size_t)n * 3);
+  });
+}
+
+int usgscsm_b200_jitter(int device, int remove, int num_coeffs, const double *line_jitter,
+                        const double *sample_jitter, int num_line_times, const double *line_times,
+                        double tolerance, int max_iterations, int64_t n, const double *line,
+                        const double *sample, double *out_line, double *out_sample) {
+  if (num_coeffs < 0 || num_line_times < 1 || !line_times || (num_coeffs && (!line_jitter || !sample_jitter)) ||
+      (n > 0 && (!line || !sample || !out_line || !out_sample)))
+    return fail(USGSCSM_B200_EINVAL, "bad argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    FrameState S{};
+    S.numJitterCoeffs = num_coeffs;
+    S.numLineTimes = num_line_times;
+    S.lineJitter = d.upload(line_jitter, (size_t)num_coeffs);
+    S.sampleJitter = d.upload(sample_jitter, (size_t)num_coeffs);
+    S.lineTimes = d.upload(line_times, (size_t)num_line_times);
+    const double *a = d.upload(line, (size_t)n), *b = d.upload(sample, (size_t)n);
+    double *oa = d.alloc<double>((size_t)n), *ob = d.alloc<double>((size_t)n);
+    UB_CUDA(launchJitter(S, remove, tolerance, max_iterations, (long)n, a, b, oa, ob, nullptr));
+    download(out_line, oa, (size_t)n);
+    download(out_sample, ob, (size_t)n);
+  });
+}
+
+int usgscsm_b200_polynomial(int device, const double coeffs4[4], int64_t n, const double *x,
+                            double *value, double *derivative) {
+  if (!coeffs4 || (n > 0 && !x)) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    const double *a = d.upload(x, (size_t)n);
+    double *o0 = value ? d.alloc<double>((size_t)n) : nullptr;
+    double *o1 = derivative ? d.alloc<double>((size_t)n) : nullptr;
+    UB_CUDA(launchCubic(coeffs4, 0, 0.0, (long)n, a, nullptr, o0, o1, nullptr, nullptr));
+    download(value, o0, (size_t)n);
+    download(derivative, o1, (size_t)n);
+  });
+}
+
+int usgscsm_b200_polynomial_root(int device, const double coeffs4[4], double threshold, int64_t n,
+                                 const double *guess, double *root, uint32_t *status) {
+  if (!coeffs4 || (n > 0 && (!guess || !root))) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    const double *a = d.upload(guess, (size_t)n);
+    double *o0 = d.alloc<double>((size_t)n);
+    uint32_t *st = status ? d.alloc<uint32_t>((size_t)n) : nullptr;
+    UB_CUDA(launchCubic(coeffs4, 1, threshold, (long)n, a, nullptr, o0, nullptr, st, nullptr));
+    download(root, o0, (size_t)n);
+    download(status, st, (size_t)n);
+  });
+}
+
+int usgscsm_b200_brent_root(int device, const double coeffs4[4], double epsilon, int64_t n,
+                            const double *lower, const double *upper, double *root,
+                            uint32_t *status) {
+  if (!coeffs4 || (n > 0 && (!lower || !upper || !root))) return fail(USGSCSM_B200_EINVAL, "null argument");
+  return katCall(device, n, [&](DevArrays &d) {
+    const double *a = d.upload(lower, (size_t)n), *b = d.upload(upper, (size_t)n);
+    double *o0 = d.alloc<double>((size_t)n);
+    uint32_t *st = status ? d.alloc<uint32_t>((size_t)n) : nullptr;
+    UB_CUDA(launchCubic(coeffs4, 2, epsilon, (long)n, a, b, o0, nullptr, st, nullptr));
+    download(root, o0, (size_t)n);
+    download(status, st, (size_t)n);
   });
 }
 

@@ -53,6 +53,23 @@ UB_DEV void addJitter(const FrameState &S, double line, double sample, double to
   jitteredSample = currentSample;
 }
 
+// removeJitter / addJitter over arrays (known-answer replay, usgscsm_b200_jitter)
+__global__ void jitterKernel(const __grid_constant__ FrameState S, int remove, double tolerance,
+                             int maxIts, long n, const double *__restrict__ line,
+                             const double *__restrict__ sample, double *__restrict__ outLine,
+                             double *__restrict__ outSample) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double l, s;
+    if (remove)
+      removeJitter(S, line[i], sample[i], l, s);
+    else
+      addJitter(S, line[i], sample[i], tolerance, maxIts, l, s);
+    outLine[i] = l;
+    outSample[i] = s;
+  }
+}
+
 UB_DEV void frGroundToImagePoint(const FrameState &S, double x, double y, double z,
                                  double desiredPrecision, double &outLine, double &outSamp,
                                  uint32_t &status) {
@@ -387,6 +404,16 @@ cudaError_t launchFrProximateLocus(const FrameState &S, int smCount, long n, con
                                    const double *z, const LocusOut &o, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   frProximateLocusKernel<<<frBlocks(frProximateLocusKernel, n, smCount), kThreads, 0, stream>>>(S, n, line, samp, x, y, z, o);
+  countLaunch();
+  return cudaGetLastError();
+}
+
+cudaError_t launchJitter(const FrameState &S, int remove, double tolerance, int maxIts, long n,
+                         const double *line, const double *sample, double *outLine,
+                         double *outSample, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  jitterKernel<<<(int)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184), 256, 0, stream>>>(
+      S, remove, tolerance, maxIts, n, line, sample, outLine, outSample);
   countLaunch();
   return cudaGetLastError();
 }

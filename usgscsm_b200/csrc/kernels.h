@@ -127,6 +127,14 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream);
 
+// computeAllSensorPartials of the line-scan model in one kernel (ls_all_partials.cu); false: not
+// applicable, run the per-parameter launches
+bool launchLsAllSensorPartials(const LsState &S, int smCount, int nIndices, const int *indices, long n,
+                               const double *x, const double *y, const double *z,
+                               const double *imgLine, const double *imgSamp, double prec,
+                               double *partials, double *achieved, uint32_t *status,
+                               cudaStream_t stream, cudaError_t &err);
+
 cudaError_t launchLsRemoteLocus(const LsState &S, int smCount, long n, const double *line,
                                 const double *samp, const LocusOut &o, cudaStream_t stream);
 cudaError_t launchPfRemoteLocus(const LsState &S, int smCount, long n, const double *line,
@@ -191,6 +199,16 @@ cudaError_t launchDistortion(bool apply, const FocalPlane &fp, double precision,
                              uint32_t *status, cudaStream_t stream);
 cudaError_t launchLagrange(const UniformTable &tab, const LagrangeDivisors &lag, int vlen, long n,
                            const double *times, double *out, cudaStream_t stream);
+cudaError_t launchFocalPlane(const FocalPlane &fp, int toPixel, long n, const double *a, const double *b,
+                             double *outA, double *outB, cudaStream_t stream);
+cudaError_t launchLookVector(double zDirection, double focalLength, long n, const double *ux,
+                             const double *uy, double *look, cudaStream_t stream);
+cudaError_t launchCubic(const double coeffs[4], int mode, double eps, long n, const double *a,
+                        const double *b, double *out0, double *out1, uint32_t *status,
+                        cudaStream_t stream);
+cudaError_t launchJitter(const FrameState &S, int remove, double tolerance, int maxIts, long n,
+                         const double *line, const double *sample, double *outLine,
+                         double *outSample, cudaStream_t stream);
 cudaError_t launchAosSplit(int ncomp, long n, const double *aos, double *c0, double *c1,
                            double *c2, cudaStream_t stream);
 cudaError_t launchAosJoin(int ncomp, long n, const double *c0, const double *c1, const double *c2,

@@ -127,6 +127,81 @@ UB_DEV double lsImageTime(const LsState &S, double lineFull) {
   return S.intTimeStartTimes[idx] + S.intTimes[idx] * (lineFull - S.intTimeLines[idx] + 0.5);
 }
 
+// The in-track / cross-track / radial frame of LS::getAdjSensorPosVel LS:2530-2565 (PF:1994-2020)
+// from the nominal position and velocity: columns of ecfFromIcr.
+UB_DEV void icrFrame(const double sensPosNom[3], const double sensVelNom[3], double ecfFromIcr[9]) {
+  double radialUnitVec[3];
+  double radMag = sqrt(sensPosNom[0] * sensPosNom[0] + sensPosNom[1] * sensPosNom[1] +
+                       sensPosNom[2] * sensPosNom[2]);
+  double rRadMag = refinedReciprocal(radMag);
+  for (int i = 0; i < 3; i++) radialUnitVec[i] = divideBy(sensPosNom[i], radMag, rRadMag);
+  double crossTrackUnitVec[3];
+  crossTrackUnitVec[0] = sensPosNom[1] * sensVelNom[2] - sensPosNom[2] * sensVelNom[1];
+  crossTrackUnitVec[1] = sensPosNom[2] * sensVelNom[0] - sensPosNom[0] * sensVelNom[2];
+  crossTrackUnitVec[2] = sensPosNom[0] * sensVelNom[1] - sensPosNom[1] * sensVelNom[0];
+  double crossMag = sqrt(crossTrackUnitVec[0] * crossTrackUnitVec[0] +
+                         crossTrackUnitVec[1] * crossTrackUnitVec[1] +
+                         crossTrackUnitVec[2] * crossTrackUnitVec[2]);
+  double rCrossMag = refinedReciprocal(crossMag);
+  for (int i = 0; i < 3; i++)
+    crossTrackUnitVec[i] = divideBy(crossTrackUnitVec[i], crossMag, rCrossMag);
+  double inTrackUnitVec[3];
+  inTrackUnitVec[0] =
+      crossTrackUnitVec[1] * radialUnitVec[2] - crossTrackUnitVec[2] * radialUnitVec[1];
+  inTrackUnitVec[1] =
+      crossTrackUnitVec[2] * radialUnitVec[0] - crossTrackUnitVec[0] * radialUnitVec[2];
+  inTrackUnitVec[2] =
+      crossTrackUnitVec[0] * radialUnitVec[1] - crossTrackUnitVec[1] * radialUnitVec[0];
+  ecfFromIcr[0] = inTrackUnitVec[0];
+  ecfFromIcr[1] = crossTrackUnitVec[0];
+  ecfFromIcr[2] = radialUnitVec[0];
+  ecfFromIcr[3] = inTrackUnitVec[1];
+  ecfFromIcr[4] = crossTrackUnitVec[1];
+  ecfFromIcr[5] = radialUnitVec[1];
+  ecfFromIcr[6] = inTrackUnitVec[2];
+  ecfFromIcr[7] = crossTrackUnitVec[2];
+  ecfFromIcr[8] = radialUnitVec[2];
+}
+
+// Division by the model's derived scales (m_halfTime, m_flyingHeight, m_halfSwath) in the
+// adjustment formulas: as written, or with reciprocals the caller hoisted out of its point loop
+// (divideBy returns the IEEE quotient either way).
+struct ScaleDivision {
+  UB_DEV double byHalfTime(const LsState &S, double a) const { return a / S.halfTime; }
+  UB_DEV double byFlyingHeight(const LsState &S, double a) const { return a / S.flyingHeight; }
+  UB_DEV double byHalfSwath(const LsState &S, double a) const { return a / S.halfSwath; }
+};
+struct HoistedScaleDivision {
+  double rHalfTime, rFlyingHeight, rHalfSwath;
+  UB_DEV explicit HoistedScaleDivision(const LsState &S)
+      : rHalfTime(refinedReciprocal(S.halfTime)), rFlyingHeight(refinedReciprocal(S.flyingHeight)),
+        rHalfSwath(refinedReciprocal(S.halfSwath)) {}
+  UB_DEV double byHalfTime(const LsState &S, double a) const { return divideBy(a, S.halfTime, rHalfTime); }
+  UB_DEV double byFlyingHeight(const LsState &S, double a) const { return divideBy(a, S.flyingHeight, rFlyingHeight); }
+  UB_DEV double byHalfSwath(const LsState &S, double a) const { return divideBy(a, S.halfSwath, rHalfSwath); }
+};
+
+// The bias / rate adjustments of LS:2567-2583 applied in that frame; pa(i) = getValue(i, adj).
+template <class PA, class DIV = ScaleDivision>
+UB_DEV void applyPositionAdjustment(const LsState &S, const double ecfFromIcr[9],
+                                    const double sensPosNom[3], const double sensVelNom[3],
+                                    double time, PA &&pa, double pos[3], double vel[3],
+                                    const DIV &div = DIV()) {
+  double aTime = time - S.positions.t0;
+  double dvi = div.byHalfTime(S, pa(3));
+  double dvc = div.byHalfTime(S, pa(4));
+  double dvr = div.byHalfTime(S, pa(5));
+  vel[0] = sensVelNom[0] + ecfFromIcr[0] * dvi + ecfFromIcr[1] * dvc + ecfFromIcr[2] * dvr;
+  vel[1] = sensVelNom[1] + ecfFromIcr[3] * dvi + ecfFromIcr[4] * dvc + ecfFromIcr[5] * dvr;
+  vel[2] = sensVelNom[2] + ecfFromIcr[6] * dvi + ecfFromIcr[7] * dvc + ecfFromIcr[8] * dvr;
+  double di = pa(0) + dvi * aTime;
+  double dc = pa(1) + dvc * aTime;
+  double dr = pa(2) + dvr * aTime;
+  pos[0] = sensPosNom[0] + ecfFromIcr[0] * di + ecfFromIcr[1] * dc + ecfFromIcr[2] * dr;
+  pos[1] = sensPosNom[1] + ecfFromIcr[3] * di + ecfFromIcr[4] * dc + ecfFromIcr[5] * dr;
+  pos[2] = sensPosNom[2] + ecfFromIcr[6] * di + ecfFromIcr[7] * dc + ecfFromIcr[8] * dr;
+}
+
 // LS::getAdjSensorPosVel LS:2484-2589 / PF:1955-2034.
 //   ALWAYS_VEL = false: line-scan semantics (calc_vel == false at every hot-path call site:
 //                position only unless some parameter is non-zero);
@@ -150,53 +225,10 @@ UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
   // Same grid, same time, same order => the same weights (the reference recomputes them).
   double sensVelNom[3];
   tableApply<3>(T, T.velocities, w, sensVelNom);
-
-  double radialUnitVec[3];
-  double radMag = sqrt(sensPosNom[0] * sensPosNom[0] + sensPosNom[1] * sensPosNom[1] +
-                       sensPosNom[2] * sensPosNom[2]);
-  double rRadMag = refinedReciprocal(radMag);
-  for (int i = 0; i < 3; i++) radialUnitVec[i] = divideBy(sensPosNom[i], radMag, rRadMag);
-  double crossTrackUnitVec[3];
-  crossTrackUnitVec[0] = sensPosNom[1] * sensVelNom[2] - sensPosNom[2] * sensVelNom[1];
-  crossTrackUnitVec[1] = sensPosNom[2] * sensVelNom[0] - sensPosNom[0] * sensVelNom[2];
-  crossTrackUnitVec[2] = sensPosNom[0] * sensVelNom[1] - sensPosNom[1] * sensVelNom[0];
-  double crossMag = sqrt(crossTrackUnitVec[0] * crossTrackUnitVec[0] +
-                         crossTrackUnitVec[1] * crossTrackUnitVec[1] +
-                         crossTrackUnitVec[2] * crossTrackUnitVec[2]);
-  double rCrossMag = refinedReciprocal(crossMag);
-  for (int i = 0; i < 3; i++)
-    crossTrackUnitVec[i] = divideBy(crossTrackUnitVec[i], crossMag, rCrossMag);
-  double inTrackUnitVec[3];
-  inTrackUnitVec[0] =
-      crossTrackUnitVec[1] * radialUnitVec[2] - crossTrackUnitVec[2] * radialUnitVec[1];
-  inTrackUnitVec[1] =
-      crossTrackUnitVec[2] * radialUnitVec[0] - crossTrackUnitVec[0] * radialUnitVec[2];
-  inTrackUnitVec[2] =
-      crossTrackUnitVec[0] * radialUnitVec[1] - crossTrackUnitVec[1] * radialUnitVec[0];
   double ecfFromIcr[9];
-  ecfFromIcr[0] = inTrackUnitVec[0];
-  ecfFromIcr[1] = crossTrackUnitVec[0];
-  ecfFromIcr[2] = radialUnitVec[0];
-  ecfFromIcr[3] = inTrackUnitVec[1];
-  ecfFromIcr[4] = crossTrackUnitVec[1];
-  ecfFromIcr[5] = radialUnitVec[1];
-  ecfFromIcr[6] = inTrackUnitVec[2];
-  ecfFromIcr[7] = crossTrackUnitVec[2];
-  ecfFromIcr[8] = radialUnitVec[2];
-
-  double aTime = time - S.positions.t0;
-  double dvi = param(S, 3) / S.halfTime;
-  double dvc = param(S, 4) / S.halfTime;
-  double dvr = param(S, 5) / S.halfTime;
-  vel[0] = sensVelNom[0] + ecfFromIcr[0] * dvi + ecfFromIcr[1] * dvc + ecfFromIcr[2] * dvr;
-  vel[1] = sensVelNom[1] + ecfFromIcr[3] * dvi + ecfFromIcr[4] * dvc + ecfFromIcr[5] * dvr;
-  vel[2] = sensVelNom[2] + ecfFromIcr[6] * dvi + ecfFromIcr[7] * dvc + ecfFromIcr[8] * dvr;
-  double di = param(S, 0) + dvi * aTime;
-  double dc = param(S, 1) + dvc * aTime;
-  double dr = param(S, 2) + dvr * aTime;
-  pos[0] = sensPosNom[0] + ecfFromIcr[0] * di + ecfFromIcr[1] * dc + ecfFromIcr[2] * dr;
-  pos[1] = sensPosNom[1] + ecfFromIcr[3] * di + ecfFromIcr[4] * dc + ecfFromIcr[5] * dr;
-  pos[2] = sensPosNom[2] + ecfFromIcr[6] * di + ecfFromIcr[7] * dc + ecfFromIcr[8] * dr;
+  icrFrame(sensPosNom, sensVelNom, ecfFromIcr);
+  applyPositionAdjustment(S, ecfFromIcr, sensPosNom, sensVelNom, time,
+                          [&](int i) { return param(S, i); }, pos, vel);
 }
 
 // LS::getQuaternions LS:2140-2153 + calculateRotationMatrixFromQuaternions U:78-95.
@@ -212,15 +244,20 @@ UB_DEV void cameraToBodyMatrix(const LsState &S, const TAB &T, double time, doub
 // LS::calculateAttitudeCorrection LS:2162-2187.  Only called when S.hasAttAdj: with
 // parameters 6..14 all zero the Euler angles are exactly 0 and the matrix is the identity
 // up to the sign of its zeros, so applying it returns its argument unchanged.
-UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9]) {
+template <class PA, class DIV = ScaleDivision>
+UB_DEV void attitudeCorrectionWith(const LsState &S, double time, PA &&pa, double attCorr[9],
+                                   const DIV &div = DIV()) {
   double aTime = time - S.quaternions.t0;
   double euler[3];
-  double nTime = aTime / S.halfTime;
+  double nTime = div.byHalfTime(S, aTime);
   double nTime2 = nTime * nTime;
-  euler[0] = (param(S, 6) + param(S, 9) * nTime + param(S, 12) * nTime2) / S.flyingHeight;
-  euler[1] = (param(S, 7) + param(S, 10) * nTime + param(S, 13) * nTime2) / S.flyingHeight;
-  euler[2] = (param(S, 8) + param(S, 11) * nTime + param(S, 14) * nTime2) / S.halfSwath;
+  euler[0] = div.byFlyingHeight(S, pa(6) + pa(9) * nTime + pa(12) * nTime2);
+  euler[1] = div.byFlyingHeight(S, pa(7) + pa(10) * nTime + pa(13) * nTime2);
+  euler[2] = div.byHalfSwath(S, pa(8) + pa(11) * nTime + pa(14) * nTime2);
   rotationFromEuler(euler, attCorr);
+}
+UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9]) {
+  attitudeCorrectionWith(S, time, [&](int i) { return param(S, i); }, attCorr);
 }
 
 // LS::computeDetectorView LS:2603-2675 (PF:2038-2110 is the same with the push-frame
@@ -298,6 +335,43 @@ UB_DEV void lsEllipsoidIntersect(const Ellipsoid &ell, double height, const doub
   z = c[2] + scale * l[2];
   double h = ellipsoidElevation(x, y, z, ell, desired_precision);
   achieved = fabs(height - h);
+}
+
+// LS::computeProjectiveApproximation LS:2688-2736
+template <class SPEC = GenericSpec>
+UB_DEV void projectiveSeed(const LsState &S, double x, double y, double z, double &line,
+                           double &samp) {
+  if (SPEC::kCommon || S.useApproxInitTrans) {
+    const double *u = S.projCoeffs;
+    double line_den = 1 + u[4] * x + u[5] * y + u[6] * z;
+    double samp_den = 1 + u[11] * x + u[12] * y + u[13] * z;
+    if (line_den == 0.0 || isnan(line_den) || isinf(line_den) || samp_den == 0.0 ||
+        isnan(samp_den) || isinf(samp_den)) {
+      line = S.nLines / 2.0;
+      samp = S.nSamples / 2.0;
+      return;
+    }
+    line = (u[0] + u[1] * x + u[2] * y + u[3] * z) / line_den;
+    samp = (u[7] + u[8] * x + u[9] * y + u[10] * z) / samp_den;
+    double numRows = S.nLines;
+    double numCols = S.nSamples;
+    if (line < 0.0) line = 0.0;
+    if (line > numRows) line = numRows;
+    if (samp < 0.0) samp = 0.0;
+    if (samp > numCols) samp = numCols;
+  } else {
+    line = S.nLines / 2.0;
+    samp = S.nSamples / 2.0;
+  }
+}
+
+UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamples) {
+  uint32_t st = 0;
+  if (!(isfinite(line) && isfinite(samp))) st |= USGSCSM_B200_ST_NONFINITE;
+  // getValidImageRange LS:1862-1869: (0,0) .. (nLines, nSamples), inclusive
+  if (!(line >= 0.0 && line <= (double)nLines && samp >= 0.0 && samp <= (double)nSamples))
+    st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+  return st;
 }
 
 // imageToProximateImagingLocus LS:1175-1235 / PF:995-1055: three imageToGround calls (at the

@@ -26,34 +26,6 @@ constexpr int kDefaultMinBlocks = 4;
 constexpr int kDefaultThreads = 256;  // block size used unless overridden
 
 // ---- groundToImage ---------------------------------------------------------------------
-// LS::computeProjectiveApproximation LS:2688-2736
-template <class SPEC = GenericSpec>
-UB_DEV void projectiveSeed(const LsState &S, double x, double y, double z, double &line,
-                           double &samp) {
-  if (SPEC::kCommon || S.useApproxInitTrans) {
-    const double *u = S.projCoeffs;
-    double line_den = 1 + u[4] * x + u[5] * y + u[6] * z;
-    double samp_den = 1 + u[11] * x + u[12] * y + u[13] * z;
-    if (line_den == 0.0 || isnan(line_den) || isinf(line_den) || samp_den == 0.0 ||
-        isnan(samp_den) || isinf(samp_den)) {
-      line = S.nLines / 2.0;
-      samp = S.nSamples / 2.0;
-      return;
-    }
-    line = (u[0] + u[1] * x + u[2] * y + u[3] * z) / line_den;
-    samp = (u[7] + u[8] * x + u[9] * y + u[10] * z) / samp_den;
-    double numRows = S.nLines;
-    double numCols = S.nSamples;
-    if (line < 0.0) line = 0.0;
-    if (line > numRows) line = numRows;
-    if (samp < 0.0) samp = 0.0;
-    if (samp > numCols) samp = numCols;
-  } else {
-    line = S.nLines / 2.0;
-    samp = S.nSamples / 2.0;
-  }
-}
-
 // One point of LS::groundToImage(groundPt, adj = 0, desiredPrecision, ...) LS:795-890.
 //
 // The reference evaluates calcDetectorLineErr (LS:3209-3231) at t = 0, t = 0.1 and at
@@ -132,15 +104,6 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
   achieved = finalUpdate;
   if ((desiredPrecision > 0.0) && (fabs(finalUpdate) > desiredPrecision))
     status |= USGSCSM_B200_ST_PRECISION_NOT_MET;
-}
-
-UB_DEV uint32_t imageRangeStatus(double line, double samp, int nLines, int nSamples) {
-  uint32_t st = 0;
-  if (!(isfinite(line) && isfinite(samp))) st |= USGSCSM_B200_ST_NONFINITE;
-  // getValidImageRange LS:1862-1869: (0,0) .. (nLines, nSamples), inclusive
-  if (!(line >= 0.0 && line <= (double)nLines && samp >= 0.0 && samp <= (double)nSamples))
-    st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
-  return st;
 }
 
 // Where the ground points of a launch come from: three SoA arrays, or the samples of a DEM
@@ -299,12 +262,17 @@ __global__ void __launch_bounds__(kThreads, MINB)
                               double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
                               double *__restrict__ achieved, uint32_t *__restrict__ status) {
   const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  // the height is the one input that comes from DRAM: the next pass's is requested before this
+  // pass's arithmetic starts (ncu: long-scoreboard stalls 3.1 per issue without it)
+  double hNext = (i < n) ? (heightStride ? __ldcs(height + i) : __ldg(height)) : 0.0;
+  for (; i < n; i += stride) {
     long r = i / nSamps;
     long c = i - r * nSamps;
     const double *re = rowTab + r * kRowDoubles;
     const double *ce = colTab + c * kColDoubles;
-    double h = heightStride ? __ldcs(height + i) : __ldg(height);
+    const double h = hNext;
+    if (heightStride && i + stride < n) hNext = __ldcs(height + i + stride);
     double cameraLook[3] = {__ldg(ce), __ldg(ce + 1), __ldg(ce + 2)};
     uint32_t st = (uint32_t)__ldg(ce + 3);
     double pos[3] = {__ldg(re), __ldg(re + 1), __ldg(re + 2)};

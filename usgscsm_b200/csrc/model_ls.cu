@@ -21,6 +21,8 @@ struct DeviceScratch {
   ~DeviceScratch() { cudaFree(p); }
 };
 
+}  // namespace
+
 void fillFocalPlaneInverse(FocalPlane &fp) {
   // computeDistortedFocalPlaneCoordinates src/Utilities.cpp:143-147
   double determinant = fp.iTransS[2] * fp.iTransL[1] - fp.iTransS[1] * fp.iTransL[2];
@@ -30,7 +32,6 @@ void fillFocalPlaneInverse(FocalPlane &fp) {
   fp.p22 = fp.iTransL[1] / determinant;
 }
 
-}  // namespace
 void fillDefaultCovariance(std::vector<double> &cov, double gsd);
 namespace {
 

@@ -141,65 +141,6 @@ UB_DEV void sarRangeCoefficients(const SarState &S, const TAB &T, double time, d
   }
 }
 
-// evaluatePolynomial / evaluatePolynomialDerivative U:696-727 for 4 coefficients
-UB_DEV double poly3(const double c[4], double x) {
-  double value = c[3];
-  value *= x;
-  value += c[2];
-  value *= x;
-  value += c[1];
-  value *= x;
-  value += c[0];
-  return value;
-}
-UB_DEV double poly3Derivative(const double c[4], double x) {
-  double value = 3 * c[3];
-  value *= x;
-  value += 2 * c[2];
-  value *= x;
-  value += 1 * c[1];
-  return value;
-}
-
-// Brent's method state (brentRoot U:545-622) and the choice of the next abscissa.
-struct Brent {
-  double counterPoint, currentPoint, counterFunc, currentFunc;
-  double previousPoint, previousFunc, evenOlderPoint;
-  bool bisected;
-};
-
-UB_DEV double brentNextPoint(Brent &b, double epsilon) {
-  double nextPoint;
-  if (b.counterFunc != b.previousFunc && b.counterFunc != b.currentFunc &&
-      b.currentFunc != b.previousFunc) {
-    nextPoint = (b.counterPoint * b.currentFunc * b.previousFunc) /
-                ((b.counterFunc - b.currentFunc) * (b.counterFunc - b.previousFunc));
-    nextPoint += (b.currentPoint * b.counterFunc * b.previousFunc) /
-                 ((b.currentFunc - b.counterFunc) * (b.currentFunc - b.previousFunc));
-    nextPoint += (b.previousPoint * b.currentFunc * b.counterFunc) /
-                 ((b.previousFunc - b.counterFunc) * (b.previousFunc - b.currentFunc));
-  } else {
-    nextPoint = b.currentPoint -
-                b.currentFunc * (b.currentPoint - b.counterPoint) / (b.currentFunc - b.counterFunc);
-  }
-  if (((b.currentPoint - nextPoint) * (nextPoint - (3 * b.counterPoint + b.currentPoint) / 4) < 0) ||
-      (b.bisected &&
-       fabs(nextPoint - b.currentPoint) >= fabs(b.currentPoint - b.previousPoint) / 2) ||
-      (!b.bisected &&
-       fabs(nextPoint - b.currentPoint) >= fabs(b.previousPoint - b.evenOlderPoint) / 2) ||
-      (b.bisected && fabs(b.currentPoint - b.previousPoint) < epsilon) ||
-      (!b.bisected && fabs(b.previousPoint - b.evenOlderPoint) < epsilon)) {
-    nextPoint = (b.currentPoint + b.counterPoint) / 2;
-    b.bisected = true;
-  } else {
-    b.bisected = false;
-  }
-  b.evenOlderPoint = b.previousPoint;
-  b.previousPoint = b.currentPoint;
-  b.previousFunc = b.currentFunc;
-  return nextPoint;
-}
-
 // ---- SAR::groundToImage SAR:541-593 as a resumable search ----------------------------------------
 // The zero-Doppler search (brentRoot U:545-622 over dopplerShift SAR:595-632) takes 10 to 32
 // function evaluations depending on the point, so points that share a warp finish at different
@@ -207,14 +148,8 @@ UB_DEV double brentNextPoint(Brent &b, double epsilon) {
 // the kernel below keeps every lane busy by handing a finished lane the next point at once.
 struct SarSearch {
   double gx, gy, gz;
-  Brent b;
-  double t;      // abscissa the next evaluation uses; after the end: the last one evaluated
+  BrentSearch r;
   double slant;  // slant range of the last evaluation
-  int stage;     // 0: lower bound, 1: upper bound, 2: iterates
-  int iteration;
-  uint32_t evals;
-  uint32_t status;
-  bool failed;
 };
 
 UB_DEV void sarSearchBegin(const SarState &S, double gx, double gy, double gz, SarSearch &q) {
@@ -222,72 +157,16 @@ UB_DEV void sarSearchBegin(const SarState &S, double gx, double gy, double gz, S
   q.gx = gx;
   q.gy = gy;
   q.gz = gz;
-  q.b.counterPoint = S.startingEphemerisTime - timePadding;
-  q.b.currentPoint = S.endingEphemerisTime + timePadding;
-  q.b.counterFunc = 0.0;
-  q.b.currentFunc = 0.0;
-  q.b.previousPoint = q.b.previousFunc = q.b.evenOlderPoint = 0.0;
-  q.b.bisected = true;
-  q.stage = 0;
-  q.iteration = 0;
-  q.t = q.b.counterPoint;
   q.slant = 0.0;
-  q.evals = 0;
-  q.status = 0;
-  q.failed = false;
+  brentBegin(S.startingEphemerisTime - timePadding, S.endingEphemerisTime + timePadding, q.r);
 }
 
 // One evaluation of the Doppler function and the bookkeeping that follows it in brentRoot.
-// True when the search has ended (q.t, q.slant, q.failed, q.status are final).
+// True when the search has ended (q.r.t, q.slant, q.r.failed, q.r.status are final).
 template <class TAB>
 UB_DEV bool sarSearchStep(const SarState &S, const TAB &T, double timeTolerance, SarSearch &q) {
-  Brent &b = q.b;
-  q.evals++;
-  const double f = sarDoppler(S, T, q.t, q.gx, q.gy, q.gz, q.slant);
-  if (q.stage == 0) {
-    b.counterFunc = f;
-    q.t = b.currentPoint;
-    q.stage = 1;
-    return false;
-  }
-  if (q.stage == 1) {
-    b.currentFunc = f;
-    if (b.counterFunc * b.currentFunc > 0.0) {  // throws std::invalid_argument
-      q.failed = true;
-      return true;
-    }
-    if (fabs(b.counterFunc) < fabs(b.currentFunc)) {
-      double tp = b.counterPoint;
-      b.counterPoint = b.currentPoint;
-      b.currentPoint = tp;
-      double tf = b.counterFunc;
-      b.counterFunc = b.currentFunc;
-      b.currentFunc = tf;
-    }
-    b.previousPoint = b.counterPoint;
-    b.previousFunc = b.counterFunc;
-    b.evenOlderPoint = b.previousPoint;
-    b.bisected = true;
-    q.stage = 2;
-    q.t = brentNextPoint(b, timeTolerance);
-    return false;
-  }
-  // stage 2: f = nextFunc at nextPoint = q.t
-  if (f == 0) return true;
-  if (b.counterFunc * f < 0) {
-    b.currentPoint = q.t;
-    b.currentFunc = f;
-  } else {
-    b.counterPoint = q.t;
-    b.counterFunc = f;
-  }
-  if (!(++q.iteration < 30)) {
-    q.status |= USGSCSM_B200_ST_ITERATION_CAP;
-    return true;
-  }
-  if (!(fabs(b.counterPoint - b.currentPoint) > timeTolerance)) return true;
-  q.t = brentNextPoint(b, timeTolerance);
-  return false;
+  return brentStep([&](double t) { return sarDoppler(S, T, t, q.gx, q.gy, q.gz, q.slant); },
+                   timeTolerance, q.r);
 }
 
 // After the search: time = the last abscissa evaluated; slantRange(groundPt, time) SAR:634-656 is
@@ -302,19 +181,8 @@ UB_DEV void sarSearchFinish(const SarState &S, const TAB &T, double time, double
     double guess = 0.5 * S.nSamples * S.scaledPixelWidth;
     const double groundTolerance = S.scaledPixelWidth * desiredPrecision / 2.0;
     c[0] -= slant;
-    double root = guess;
-    double polyValue = poly3(c, root);
-    bool converged = false;
-    for (int it = 0; it < 31; it++) {
-      if (fabs(polyValue) < groundTolerance) {
-        converged = true;
-        break;
-      }
-      double polyDeriv = poly3Derivative(c, root);
-      if (fabs(polyDeriv) < 1e-15) break;  // throws
-      root -= polyValue / polyDeriv;
-      polyValue = poly3(c, root);
-    }
+    double root;
+    const bool converged = polynomialRoot3(c, guess, groundTolerance, root);
     if (converged) {
       outLine = divideBy(time - S.startingEphemerisTime, S.exposure) + 0.5;
       outSamp = divideBy(root, S.pixelWidth) + 0.5;
@@ -336,8 +204,8 @@ UB_DEV void sarGroundToImagePoint(const SarState &S, const TAB &T, double gx, do
   sarSearchBegin(S, gx, gy, gz, q);
   while (!sarSearchStep(S, T, timeTolerance, q)) {
   }
-  status |= q.status | (q.evals << USGSCSM_B200_ST_EVALS_SHIFT);
-  sarSearchFinish(S, T, q.t, q.slant, q.failed, desiredPrecision, outLine, outSamp, status);
+  status |= q.r.status | (q.r.evals << USGSCSM_B200_ST_EVALS_SHIFT);
+  sarSearchFinish(S, T, q.r.t, q.slant, q.r.failed, desiredPrecision, outLine, outSamp, status);
 }
 
 // One point of SAR::imageToGround SAR:775-861.
@@ -460,10 +328,11 @@ __global__ void __launch_bounds__(kThreads, MINB)
       const unsigned done = __ballot_sync(0xffffffffu, ended);
       if (ended) {
         const int slot = queued + __popc(done & below);
-        wq.time[slot] = q.t;
+        wq.time[slot] = q.r.t;
         wq.slant[slot] = q.slant;
         wq.index[slot] = point;
-        wq.status[slot] = q.status | (q.evals << USGSCSM_B200_ST_EVALS_SHIFT) | (q.failed ? 0x80000000u : 0u);
+        wq.status[slot] =
+            q.r.status | (q.r.evals << USGSCSM_B200_ST_EVALS_SHIFT) | (q.r.failed ? 0x80000000u : 0u);
         busy = false;
       }
       queued += __popc(done);

@@ -994,6 +994,111 @@ def imageToGroundGridImages(models, line0, samp0, dline, dsamp, n_lines, n_samps
         _ptr(height), stride, desiredPrecision, _ptr(x), _ptr(y), _ptr(z), _ptr(ach), _ptr(st), stream))
     return x, y, z, ach, st
 
+
+# ---- the reference's remaining free functions (known-answer replay on the device functions) ---------
+def _affine12(iTransS, iTransL, sampleOrigin, lineOrigin, sampleSumming, lineSumming, startingSample,
+              startingLine):
+    return np.array(list(iTransS) + list(iTransL) + [sampleOrigin, lineOrigin, sampleSumming, lineSumming,
+                                                     startingSample, startingLine], dtype=np.float64)
+
+
+def computeDistortedFocalPlaneCoordinates(line, sample, sampleOrigin, lineOrigin, sampleSumming, lineSumming,
+                                          startingSample, startingLine, iTransS, iTransL, device=0):
+    """src/Utilities.cpp:129-151, same argument order; arrays in, (x, y) arrays out."""
+    line = _host(line)
+    sample = _host(sample, line.size)
+    a = _affine12(iTransS, iTransL, sampleOrigin, lineOrigin, sampleSumming, lineSumming, startingSample, startingLine)
+    x, y = np.empty(line.size), np.empty(line.size)
+    check(lib.usgscsm_b200_focal_plane_coordinates(device, _ptr(a), line.size, _ptr(line), _ptr(sample), _ptr(x), _ptr(y)))
+    return x, y
+
+
+def computePixel(distortedX, distortedY, sampleOrigin, lineOrigin, sampleSumming, lineSumming, startingSample,
+                 startingLine, iTransS, iTransL, device=0):
+    """src/Utilities.cpp:317-331, same argument order; returns (line, sample) arrays."""
+    fx = _host(distortedX)
+    fy = _host(distortedY, fx.size)
+    a = _affine12(iTransS, iTransL, sampleOrigin, lineOrigin, sampleSumming, lineSumming, startingSample, startingLine)
+    line, sample = np.empty(fx.size), np.empty(fx.size)
+    check(lib.usgscsm_b200_compute_pixel(device, _ptr(a), fx.size, _ptr(fx), _ptr(fy), _ptr(line), _ptr(sample)))
+    return line, sample
+
+
+def createCameraLookVector(undistortedX, undistortedY, zDirection, focalLength, device=0):
+    """src/Utilities.cpp:360-373; returns an (n, 3) array of unit look vectors."""
+    ux = _host(undistortedX)
+    uy = _host(undistortedY, ux.size)
+    look = np.empty((ux.size, 3))
+    check(lib.usgscsm_b200_camera_look_vector(device, float(zDirection), float(focalLength), ux.size, _ptr(ux),
+                                              _ptr(uy), _ptr(look)))
+    return look
+
+
+def _jitter(remove, line, sample, lineJitterCoeffs, sampleJitterCoeffs, lineTimes, tolerance, maxIts, device):
+    lj, sj, lt = _host(lineJitterCoeffs), _host(sampleJitterCoeffs), _host(lineTimes)
+    if lj.size != sj.size or lt.size == 0:   # U:186-197: csm::Error(INDEX_OUT_OF_RANGE)
+        raise Error(Error.INDEX_OUT_OF_RANGE, "Jitter coefficient arrays must be the same length / line times "
+                                              "must not be empty.", "removeJitter")
+    line = _host(line)
+    sample = _host(sample, line.size)
+    ol, os_ = np.empty(line.size), np.empty(line.size)
+    check(lib.usgscsm_b200_jitter(device, remove, lj.size, _ptr(lj), _ptr(sj), lt.size, _ptr(lt), float(tolerance),
+                                  int(maxIts), line.size, _ptr(line), _ptr(sample), _ptr(ol), _ptr(os_)))
+    return ol, os_
+
+
+def removeJitter(line, sample, lineJitterCoeffs, sampleJitterCoeffs, lineTimes, device=0):
+    """src/Utilities.cpp:182-213; returns (dejitteredLine, dejitteredSample)."""
+    return _jitter(1, line, sample, lineJitterCoeffs, sampleJitterCoeffs, lineTimes, 0.0, 0, device)
+
+
+def addJitter(line, sample, tolerance, maxIts, lineJitterCoeffs, sampleJitterCoeffs, lineTimes, device=0):
+    """src/Utilities.cpp:244-282; returns (jitteredLine, jitteredSample)."""
+    return _jitter(0, line, sample, lineJitterCoeffs, sampleJitterCoeffs, lineTimes, tolerance, maxIts, device)
+
+
+def _cubic(coeffs):
+    c = [float(v) for v in coeffs]
+    if not c:
+        raise ValueError("Polynomial coeffs must be non-empty.")   # U:698-700 throws std::invalid_argument
+    if len(c) > 4:
+        raise ValueError("the engine evaluates polynomials of degree <= 3 (the SAR range polynomial)")
+    return np.array(c + [0.0] * (4 - len(c)), dtype=np.float64)
+
+
+def evaluatePolynomial(coeffs, x, device=0):
+    """src/Utilities.cpp:696-710 (degree <= 3)."""
+    c, x = _cubic(coeffs), _host(x)
+    v = np.empty(x.size)
+    check(lib.usgscsm_b200_polynomial(device, _ptr(c), x.size, _ptr(x), _ptr(v), None))
+    return v
+
+
+def evaluatePolynomialDerivative(coeffs, x, device=0):
+    """src/Utilities.cpp:712-727 (degree <= 3)."""
+    c, x = _cubic(coeffs), _host(x)
+    v = np.empty(x.size)
+    check(lib.usgscsm_b200_polynomial(device, _ptr(c), x.size, _ptr(x), None, _ptr(v)))
+    return v
+
+
+def polynomialRoot(coeffs, guess, threshold=1.0e-10, device=0):
+    """src/Utilities.cpp:771-791 (maxIterations 30); returns (root, status): status has
+    ST_ERROR_UNKNOWN where the reference throws std::invalid_argument."""
+    c, g = _cubic(coeffs), _host(guess)
+    r, st = np.empty(g.size), np.empty(g.size, dtype=np.uint32)
+    check(lib.usgscsm_b200_polynomial_root(device, _ptr(c), float(threshold), g.size, _ptr(g), _ptr(r), _ptr(st)))
+    return r, st
+
+
+def brentRoot(lowerBound, upperBound, coeffs, epsilon=1e-10, device=0):
+    """src/Utilities.cpp:545-622 on the polynomial `coeffs` (degree <= 3); returns (root, status)."""
+    c, lo = _cubic(coeffs), _host(lowerBound)
+    hi = _host(upperBound, lo.size)
+    r, st = np.empty(lo.size), np.empty(lo.size, dtype=np.uint32)
+    check(lib.usgscsm_b200_brent_root(device, _ptr(c), float(epsilon), lo.size, _ptr(lo), _ptr(hi), _ptr(r), _ptr(st)))
+    return r, st
+
 def stateToMsgpack(modelState):
     """The msgpack binary form of a model state, as the reference writes it
     (nlohmann::json::to_msgpack; bin/usgscsm_cam_test.cc --output-binary-model-state)."""
