@@ -409,7 +409,7 @@ def run_b200(args):
             host["numa_bind"] = sharding.bind_to_gpu_numa_node(local)
         # stdout carries ONE JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it
         if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+            os.environ.pop("NCCL_DEBUG", None)
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -641,6 +641,18 @@ def run_single(ctx):
     torch.cuda.empty_cache()
     if not args.no_others:
         result["configs"] = other_configs(dev, fp64, ops, not args.no_cpu)
+        # the N > 1 job (C5) on this one GPU, same timing method: the 1-GPU point of its strong scaling
+        import copy
+        a5 = copy.copy(args)
+        a5.lines, a5.no_e2e, a5.steps, a5.warmup = C5_LINES, True, 1, 3
+        c5 = run_c5(dict(ctx, args=a5))
+        torch.cuda.empty_cache()
+        result["configs"]["C5_64_images_on_one_gpu"] = {
+            "value": c5["value"], "unit": "Mpoints/s", "ms_per_step": c5["ms_per_step"],
+            "evaluations_per_point": c5["check"]["evaluations_per_point"],
+            "roofline_frac": c5["roofline"]["frac"], "job": c5["job"],
+            "note": "bench.py --gpus N (N > 1) runs this job; its images need 3.0 to 5.2 evaluations per point "
+                    "(mean above C2's 3.04) because the reference's projective seed is poorer for some orbits"}
     return result
 
 
@@ -1050,12 +1062,15 @@ def run_c5(ctx):
                 models[i]._h, first + 0.5, 0.5, 1.0, 1.0, band, N_SAMPLES, p(h), 1, PREC,
                 p(gx) + 8 * k * nb, p(gy) + 8 * k * nb, p(gz) + 8 * k * nb, None, p(st_g), stream))
 
+    def project_one(k, i):
+        r = k % ring
+        _capi.check(lib.usgscsm_b200_ground_to_image_dev(
+            models[i]._h, nb, p(gx) + 8 * k * nb, p(gy) + 8 * k * nb, p(gz) + 8 * k * nb, PREC,
+            p(ol) + 8 * r * nb, p(os_) + 8 * r * nb, None, p(ost) + 4 * r * nb, stream))
+
     def project(pass_images):
         for k, i in enumerate(pass_images):
-            r = k % ring
-            _capi.check(lib.usgscsm_b200_ground_to_image_dev(
-                models[i]._h, nb, p(gx) + 8 * k * nb, p(gy) + 8 * k * nb, p(gz) + 8 * k * nb, PREC,
-                p(ol) + 8 * r * nb, p(os_) + 8 * r * nb, None, p(ost) + 4 * r * nb, stream))
+            project_one(k, i)
 
     def step(timed):
         """One pass over the 64-image job.  Returns the timed milliseconds (max over ranks): the
@@ -1070,25 +1085,54 @@ def run_c5(ctx):
                 project(pi)
                 b.record()
                 torch.cuda.synchronize()
-                total += max_over_ranks(a.elapsed_time(b))
+                own = a.elapsed_time(b)
+                own_ms[0] += own
+                total += max_over_ranks(own)
             else:
                 project(pi)
                 torch.cuda.synchronize()
             barrier()
         return total
 
+    own_ms = [0.0]
     for _ in range(max(1, args.warmup // 3)):     # a warm-up step is 64 launches per rank
         step(False)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    sampler = ClockSampler(local)   # every rank samples its own GPU; rank 0's goes to "clocks"
+    sampler.start()
     launches0 = lib.usgscsm_b200_kernel_launches()
     total_ms = 0.0
     for _ in range(args.steps):
         total_ms += step(True)
     launches = lib.usgscsm_b200_kernel_launches() - launches0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
     value = n_job * args.steps / (total_ms * 1e-3) / 1e6
+    # every rank's own timed milliseconds and clock, for the record
+    mine = torch.tensor([own_ms[0] / args.steps, float(clocks.get("sm_mhz") or 0.0)], dtype=torch.float64, device=dev)
+    everyone = [torch.empty_like(mine) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(everyone, mine)
+    else:
+        everyone = [mine]
+    per_rank = [{"rank": r, "ms_per_step": float(t[0]), "sm_mhz": float(t[1])} for r, t in enumerate(everyone)]
+
+    # one more, untimed, walk over the job with an event pair and the evaluation count per image:
+    # the images differ (orbit phase, attitude), and so does the quality of their projective seed
+    per_image_ms, per_image_evals = [], []
+    for pi in passes:
+        fill(pi)
+        torch.cuda.synchronize()
+        for k, i in enumerate(pi):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            project_one(k, i)
+            b.record()
+            r = k % ring
+            ev = ((ost[r * nb:(r + 1) * nb] >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean()
+            torch.cuda.synchronize()
+            per_image_ms.append(a.elapsed_time(b))
+            per_image_evals.append(float(ev.item()))
+    per_launch = sorted(per_image_ms)
+    mean_evals_job = sum(per_image_evals) / len(per_image_evals)
 
     # check: the last image's band closes the round trip
     last = (len(passes[-1]) - 1) % ring
@@ -1097,7 +1141,7 @@ def run_c5(ctx):
               float((os_[last * nb:(last + 1) * nb].view(band, N_SAMPLES) - cols[None, :]).abs().max()))
     err = max_over_ranks(err)
     flags = int(sum_over_ranks(float(((ost[last * nb:(last + 1) * nb] & _capi.ST_REFERENCE_MASK) != 0).sum().item())))
-    mean_evals = float(((ost[last * nb:(last + 1) * nb] >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean().item())
+    mean_evals = sum_over_ranks(mean_evals_job) / world
 
     # the gather of one image's outputs (line, samp, status) onto every rank, timed on its own
     def gather_once():
@@ -1138,7 +1182,12 @@ def run_c5(ctx):
                     "outputs_kept_sharded": ring == per_pass,
                     "timed_region": "the groundToImage launches of every pass, CUDA events, max over ranks per "
                                     "pass, summed; the imageToGround that produces a pass's inputs is not timed",
-                    "model_build_seconds_rank0": t_build},
+                    "model_build_seconds_rank0": t_build, "per_rank": per_rank,
+                    "band_launch_ms_rank0": {"min": per_launch[0], "median": per_launch[len(per_launch) // 2],
+                                             "max": per_launch[-1], "launches": len(per_launch),
+                                             "sum": sum(per_launch)},
+                    "evaluations_per_point_by_image_rank0": {"min": min(per_image_evals), "max": max(per_image_evals),
+                                                             "mean": mean_evals_job}},
             "gather": {"ms_per_image": gather_ms, "bytes_per_image": 20 * lines * N_SAMPLES,
                        "gbs_per_rank_received": 20 * lines * N_SAMPLES / (gather_ms * 1e-3) / 1e9,
                        "ms_for_all_images": gather_ms * images,

@@ -1,0 +1,98 @@
+"""Tuning knobs are read once per process, so each variant runs in its own interpreter: every
+combination must compute the same bits."""
+import os
+import subprocess
+import sys
+import textwrap
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(code, **env):
+    e = dict(os.environ, **{k: str(v) for k, v in env.items()})
+    r = subprocess.run([sys.executable, "-c", "import sys; sys.path.insert(0, %r)\n" % ROOT + textwrap.dedent(code)],
+                       env=e, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return r.stdout
+
+
+def test_grid_chunks_compute_the_same_lines():
+    """a dense grid cut into pipeline chunks must give every row the line
+    line0 + (row0 + r) * dline, whatever the chunk size -- non-dyadic dline, 4 Ki-point chunks."""
+    out = _run("""
+        import numpy as np, torch
+        import usgscsm_b200 as ub
+        from usgscsm_b200 import synth
+        gm = ub.UsgsAstroPlugin().constructModelFromState(synth.linescan_state(n_lines=4096, n_samples=512, seed=3))
+        nl, ns = 700, 37
+        h = np.linspace(-300.0, 300.0, nl * ns)
+        x, y, z, a, st = gm.imageToGroundGrid(0.3, 0.7, 0.1, 1.3, nl, ns, h, achieved=True)      # host, chunked
+        dx, dy, dz, da, dst = gm.imageToGroundGrid(0.3, 0.7, 0.1, 1.3, nl, ns, torch.as_tensor(h, device="cuda:0"),
+                                                   achieved=True)                                 # device, one launch
+        line = np.repeat(0.3 + np.arange(nl) * 0.1, ns); samp = np.tile(0.7 + np.arange(ns) * 1.3, nl)
+        ex, ey, ez, ea, est = gm.imageToGroundBatch(line, samp, h)                                # explicit pixels
+        for u, v, w in ((x, dx, ex), (y, dy, ey), (z, dz, ez), (a, da, ea)):
+            assert np.array_equal(u, v.cpu().numpy()) and np.array_equal(u, w)
+        assert np.array_equal(st, dst.cpu().numpy().view(np.uint32)) and np.array_equal(st, est)
+        print("OK")
+        """, USGSCSM_B200_PIPELINE_CHUNK=4096)
+    assert "OK" in out
+
+
+@pytest.mark.parametrize("env", [dict(USGSCSM_B200_SAR_REFILL=1), dict(USGSCSM_B200_SAR_REFILL=1, USGSCSM_B200_SAR_PAD=1),
+                                 dict(USGSCSM_B200_SAR_PAD=1, USGSCSM_B200_SAR_MINB=2)])
+def test_sar_kernel_variants_same_bits(env):
+    """Lane-refill / padded-table variants of SAR groundToImage against the
+    default kernel's output saved by the first run."""
+    code = """
+        import numpy as np, torch, os
+        import usgscsm_b200 as ub
+        from usgscsm_b200 import synth
+        gm = ub.UsgsAstroPlugin().constructModelFromState(synth.sar_state())
+        rng = np.random.default_rng(9)
+        n = 200000
+        line, samp, h = rng.uniform(0, 64576, n), rng.uniform(0, 2367, n), rng.uniform(-900, 900, n)
+        x, y, z, _, _ = gm.imageToGroundBatch(line, samp, h)
+        x[:500] *= 1.3    # no Doppler bracket / far off: the error paths
+        l, s, a, st = gm.groundToImageBatch(x, y, z)
+        np.save(os.environ["OUT"], np.concatenate([l, s, st.astype(np.float64)]))
+        print("OK")
+        """
+    import tempfile
+    import numpy as np
+    with tempfile.TemporaryDirectory() as d:
+        _run(code, OUT=os.path.join(d, "a.npy"))
+        _run(code, OUT=os.path.join(d, "b.npy"), **env)
+        a, b = np.load(os.path.join(d, "a.npy")), np.load(os.path.join(d, "b.npy"))
+        # the evaluation counter (status bits 16-23) is the same too: same search, same order
+        assert np.array_equal(a, b, equal_nan=True)
+
+
+def test_pageable_and_pinned_arrays_same_bits():
+    """numpy (pageable) arrays go through the engine's page-locked ring with copier threads;
+    pinned arrays through the three-slot pipeline: same results, several chunks each."""
+    out = _run("""
+        import numpy as np, torch
+        import usgscsm_b200 as ub
+        from usgscsm_b200 import synth, _capi
+        gm = ub.UsgsAstroPlugin().constructModelFromState(synth.linescan_state(n_lines=4096, n_samples=1024, seed=8))
+        n = 300000
+        rng = np.random.default_rng(2)
+        line, samp, h = rng.uniform(0, 4096, n), rng.uniform(0, 1024, n), rng.uniform(-500, 500, n)
+        x, y, z, a, st = gm.imageToGroundBatch(line, samp, h)                 # pageable in / out
+        pin = lambda v: torch.as_tensor(v).pin_memory()
+        pl, ps, ph = pin(line), pin(samp), pin(h)
+        px, py, pz, pa = (torch.empty(n, dtype=torch.float64).pin_memory() for _ in range(4))
+        pst = torch.empty(n, dtype=torch.int32).pin_memory()
+        _capi.check(_capi.lib.usgscsm_b200_image_to_ground(gm._h, n, pl.data_ptr(), ps.data_ptr(), ph.data_ptr(), 1, 0.001,
+                                                           px.data_ptr(), py.data_ptr(), pz.data_ptr(), pa.data_ptr(), pst.data_ptr()))
+        assert np.array_equal(x, px.numpy()) and np.array_equal(z, pz.numpy()) and np.array_equal(a, pa.numpy())
+        assert np.array_equal(st, pst.numpy().view(np.uint32))
+        l, s, ach, st2 = gm.groundToImageBatch(x, y, z)
+        assert np.abs(l - line).max() < 5e-3 and np.abs(s - samp).max() < 5e-3
+        print("OK")
+        """, USGSCSM_B200_STAGE_CHUNK=20000, USGSCSM_B200_STAGE_THREADS=5, USGSCSM_B200_PIPELINE_CHUNK=50000)
+    assert "OK" in out
