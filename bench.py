@@ -790,6 +790,30 @@ def other_configs(dev, fp64, ops, with_cpu):
                "evaluations_per_point": float(((st2 >> _capi.ST_EVALS_SHIFT) & 0xff).double().mean())}
         if "transverse" in name:
             res["note"] = "flops per point op-counted on the radial variant of the same model"
+        else:
+            # 16 images of this size in ONE call (usgscsm_b200_*_images_dev: kernels forked over side
+            # streams, one image's tail under the next one's body)
+            K = 16
+            maker = (lambda k: synth.pushframe_state(n_framelets=256, framelet_height=16, n_samples=4096, seed=3 + k)) \
+                if "pushframe" in name else (lambda k: synth.frame_state(n_lines=4096, n_samples=4096, seed=5 + k))
+            many = [gm] + [plugin.constructModelFromState(maker(k)) for k in range(1, K)]
+            hk = h.repeat(K)
+            m1 = tuple(torch.empty(n * K, dtype=torch.float64, device=dev) for _ in range(3)) + (
+                None, torch.empty(n * K, dtype=torch.int32, device=dev))
+            m2 = tuple(torch.empty(n * K, dtype=torch.float64, device=dev) for _ in range(2)) + (
+                None, torch.empty(n * K, dtype=torch.int32, device=dev))
+            msi = median_ms(lambda: ub.imageToGroundGridImages(many, 0.5, 0.5, 1.0, 1.0, [nl] * K, [ns] * K, hk, PREC, out=m1))
+            msg = median_ms(lambda: ub.groundToImageImages(many, [n] * K, m1[0], m1[1], m1[2], PREC, out=m2))
+            res["sixteen_images_per_call"] = {
+                "points": n * K,
+                "image_to_ground": {"value": n * K / msi / 1e3, "unit": "Mpoints/s", "ms": msi,
+                                    "hbm_frac": I2G_GRID_BYTES_PER_POINT * n * K / (msi * 1e-3) / 1e9 / hbm_peak,
+                                    "fp64_frac": ops[opkey]["image_to_ground"]["flops_per_point"] * n * K / (msi * 1e-3) / 1e12 / fp64["fma_peak_tflops"]},
+                "ground_to_image": {"value": n * K / msg / 1e3, "unit": "Mpoints/s", "ms": msg,
+                                    "hbm_frac": G2I_BYTES_PER_POINT * n * K / (msg * 1e-3) / 1e9 / hbm_peak,
+                                    "fp64_frac": ops[opkey]["ground_to_image_prec_0.001"]["flops_per_point"] * n * K / (msg * 1e-3) / 1e12 / fp64["fma_peak_tflops"]},
+                "api": "usgscsm_b200_image_to_ground_grid_images_dev / usgscsm_b200_ground_to_image_images_dev"}
+            del many, hk, m1, m2
         k = 400000
         idx = torch.arange(0, n, max(1, n // k), device=dev)[:k]
         cpu = cpu_rates(state, (idx // ns).double().cpu().numpy() + 0.5, (idx % ns).double().cpu().numpy() + 0.5,

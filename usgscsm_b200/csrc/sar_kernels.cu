@@ -572,10 +572,15 @@ int sarEnv(const char *name, int def) {
   return v && *v ? atoi(v) : def;
 }
 
+// Opt the kernel in to more than 48 KB of dynamic shared memory.  Always the SAME ceiling (the
+// largest request any launch of these kernels can make), never the launch's own size: two host
+// threads launching models with different table sizes would otherwise lower the limit under
+// each other between the attribute call and the launch.
+constexpr size_t kSarSmemCeiling = kSarMaxStagedBytes * 4 / 3 + 16 * 1024;  // padded tables + result queues
 template <class K>
 cudaError_t allowSmem(K kernel, size_t bytes) {
   if (bytes > 48 * 1024)
-    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSarSmemCeiling);
   return cudaSuccess;
 }
 
