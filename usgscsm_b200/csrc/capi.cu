@@ -493,7 +493,8 @@ struct SideStreams {
 
 SideStreams &sideStreams(int device) {
   static std::mutex mu;
-  static std::vector<std::unique_ptr<SideStreams>> perDevice;
+  // never destroyed (CUDA objects must not be released from a static destructor)
+  static std::vector<std::unique_ptr<SideStreams>> &perDevice = *new std::vector<std::unique_ptr<SideStreams>>();
   std::lock_guard<std::mutex> lock(mu);
   if ((int)perDevice.size() <= device) perDevice.resize((size_t)device + 1);
   if (!perDevice[(size_t)device]) {

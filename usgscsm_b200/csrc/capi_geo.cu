@@ -150,16 +150,19 @@ const void *sampleAt(const usgscsm_b200_dem &dem, int64_t row, int64_t col) {
 // A model-less pipeline owner for the grid-only host entry points: they reuse runPipelined, which
 // keeps its slots in a Model.
 usgscsm_b200_model *scratchModel(int device) {
+  // never destroyed: their streams and buffers must not be released from a static destructor,
+  // after the CUDA runtime has begun to unload
   static std::mutex mu;
-  static std::vector<std::unique_ptr<usgscsm_b200_model>> perDevice;
+  static std::vector<usgscsm_b200_model *> *perDevice = new std::vector<usgscsm_b200_model *>();
   std::lock_guard<std::mutex> lock(mu);
-  if ((int)perDevice.size() <= device) perDevice.resize((size_t)device + 1);
-  if (!perDevice[(size_t)device]) {
-    perDevice[(size_t)device].reset(new usgscsm_b200_model);
-    perDevice[(size_t)device]->device = device;
-    perDevice[(size_t)device]->smCount = smCountOf(device);
+  if ((int)perDevice->size() <= device) perDevice->resize((size_t)device + 1, nullptr);
+  if (!(*perDevice)[(size_t)device]) {
+    usgscsm_b200_model *m = new usgscsm_b200_model;
+    m->device = device;
+    m->smCount = smCountOf(device);
+    (*perDevice)[(size_t)device] = m;
   }
-  return perDevice[(size_t)device].get();
+  return (*perDevice)[(size_t)device];
 }
 
 }  // namespace
