@@ -96,3 +96,35 @@ def test_pageable_and_pinned_arrays_same_bits():
         print("OK")
         """, USGSCSM_B200_STAGE_CHUNK=20000, USGSCSM_B200_STAGE_THREADS=5, USGSCSM_B200_PIPELINE_CHUNK=50000)
     assert "OK" in out
+
+
+def test_fused_all_sensor_partials_same_bits():
+    """USGSCSM_B200_LS_FUSED_PARTIALS=1: computeAllSensorPartials in one kernel (shared seed and
+    first two evaluations) against the default per-parameter searches, unadjusted and adjusted
+    model, both overloads."""
+    code = """
+        import numpy as np, os
+        import usgscsm_b200 as ub
+        from usgscsm_b200 import synth
+        gm = ub.UsgsAstroPlugin().constructModelFromState(synth.linescan_state(n_lines=4096, n_samples=1024, seed=12))
+        rng = np.random.default_rng(3)
+        n = 20000
+        line, samp, h = rng.uniform(0, 4096, n), rng.uniform(0, 1024, n), rng.uniform(-500, 500, n)
+        x, y, z, _, _ = gm.imageToGroundBatch(line, samp, h)
+        out = []
+        for params in ({}, {1: 1.5, 5: 0.01, 8: -3e-5, 15: 0.01}):
+            for i, v in params.items():
+                gm.setParameterValue(i, v)
+            p, a, st = gm.computeAllSensorPartialsBatch(x, y, z)
+            p2, a2, st2 = gm.computeAllSensorPartialsBatch(x, y, z, imagePts=(line, samp), indices=[0, 7, 15])
+            out += [p.reshape(-1), a, st.astype(np.float64), p2.reshape(-1), a2, st2.astype(np.float64)]
+        np.save(os.environ["OUT"], np.concatenate(out))
+        print("OK")
+        """
+    import tempfile
+    import numpy as np
+    with tempfile.TemporaryDirectory() as d:
+        _run(code, OUT=os.path.join(d, "a.npy"))
+        _run(code, OUT=os.path.join(d, "b.npy"), USGSCSM_B200_LS_FUSED_PARTIALS=1)
+        a, b = np.load(os.path.join(d, "a.npy")), np.load(os.path.join(d, "b.npy"))
+        assert np.array_equal(a, b, equal_nan=True)

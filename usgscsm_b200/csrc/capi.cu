@@ -821,6 +821,14 @@ int allSensorPartialsDev(usgscsm_b200_model *m, int n_indices, const int *indice
   for (int k = 0; k < n_indices && e == cudaSuccess; k++) {
     const int index = indices ? indices[k] : k;
     const double delta = sensorPartialDelta(m, index);
+    if (m->kind == USGSCSM_B200_MODEL_LINE_SCANNER) {
+      // the search writes its forward difference itself (no separate step kernel)
+      e = launchLsSensorPartialStep(adjustedLineScanner(*m, index, delta), m->smCount, n, x, y, z, prec,
+                                    haveImage ? img_line : l0, haveImage ? img_samp : s0,
+                                    haveImage ? nullptr : st0, delta, partials, n_indices, k, achieved,
+                                    acc, stream);
+      continue;
+    }
     double *pfTable = nullptr;
     e = launchAdjustedGroundToImage(m, index, delta, n, x, y, z, prec, l1, s1, achP, stP, stream,
                                     &pfTable);

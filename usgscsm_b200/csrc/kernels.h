@@ -122,6 +122,11 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
                                   const double *y, const double *z, double prec, double *line,
                                   double *samp, double *achieved, uint32_t *status,
                                   cudaStream_t stream);
+cudaError_t launchLsSensorPartialStep(const LsState &S, int smCount, long n, const double *x,
+                                      const double *y, const double *z, double prec, const double *l0,
+                                      const double *s0, const uint32_t *st0, double delta,
+                                      double *partials, int numParams, int k, double *achieved,
+                                      uint32_t *status, cudaStream_t stream);
 cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const double *line,
                                   const double *samp, const GridSpec *grid, const double *height,
                                   int heightStride, double prec, double *x, double *y, double *z,

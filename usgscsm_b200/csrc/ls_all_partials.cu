@@ -271,7 +271,10 @@ bool launchLsAllSensorPartials(const LsState &S, int smCount, int nIndices, cons
                                const double *imgLine, const double *imgSamp, double prec,
                                double *partials, double *achieved, uint32_t *status,
                                cudaStream_t stream, cudaError_t &err) {
-  static const int fused = envInt("USGSCSM_B200_LS_FUSED_PARTIALS", 1);
+  // Off by default: the per-parameter searches (each a launch of the specialised search kernel
+  // that writes its forward difference itself) measure 7.2 G searches/s against this kernel's 5.1
+  // -- it carries 1 KB of per-thread state (profiles/r2_ab_partials.txt, r2_ncu_all_partials.txt).
+  static const int fused = envInt("USGSCSM_B200_LS_FUSED_PARTIALS", 0);
   err = cudaSuccess;
   if (!fused || nIndices < 1 || nIndices > kMaxIndices) return false;
   if (n <= 0) return true;

@@ -83,8 +83,8 @@ struct GenericSpec {
 struct SearchSpec : GenericSpec {  // the line-scan search kernel, any model
   static constexpr bool kColdOutOfLine = true;
 };
-// ADJ: 0 = no parameter is set, 1 = some are but none of the attitude ones (6..14),
-// 2 = attitude parameters too -- the state of a model after bundle adjustment.
+// ADJ: bit 0 = some of the position / velocity parameters (0..5) are set, bit 1 = some of the
+// attitude parameters (6..14) are; 3 = the state of a model after bundle adjustment.
 template <int DIST, int ADJ = 0>
 struct CommonSpec {
   static constexpr bool kCommon = true;
@@ -93,10 +93,10 @@ struct CommonSpec {
   static constexpr int kAdj = ADJ;
 };
 template <class SPEC>
-UB_DEV bool specHasAdj(const LsState &S) { return SPEC::kAdj < 0 ? S.hasAdj != 0 : SPEC::kAdj > 0; }
+UB_DEV bool specHasAdj(const LsState &S) { return SPEC::kAdj < 0 ? S.hasAdj != 0 : (SPEC::kAdj & 1) != 0; }
 template <class SPEC>
 UB_DEV bool specHasAttAdj(const LsState &S) {
-  return SPEC::kAdj < 0 ? S.hasAttAdj != 0 : SPEC::kAdj > 1;
+  return SPEC::kAdj < 0 ? S.hasAttAdj != 0 : (SPEC::kAdj & 2) != 0;
 }
 
 // getValue(i, adj) with adj == _no_adjustment (LS:757-772 passes 16 zeros): the host packs
@@ -167,6 +167,8 @@ UB_DEV void icrFrame(const double sensPosNom[3], const double sensVelNom[3], dou
 // adjustment formulas: as written, or with reciprocals the caller hoisted out of its point loop
 // (divideBy returns the IEEE quotient either way).
 struct ScaleDivision {
+  UB_DEV ScaleDivision() {}
+  UB_DEV explicit ScaleDivision(const LsState &) {}
   UB_DEV double byHalfTime(const LsState &S, double a) const { return a / S.halfTime; }
   UB_DEV double byFlyingHeight(const LsState &S, double a) const { return a / S.flyingHeight; }
   UB_DEV double byHalfSwath(const LsState &S, double a) const { return a / S.halfSwath; }
@@ -206,9 +208,9 @@ UB_DEV void applyPositionAdjustment(const LsState &S, const double ecfFromIcr[9]
 //   ALWAYS_VEL = false: line-scan semantics (calc_vel == false at every hot-path call site:
 //                position only unless some parameter is non-zero);
 //   ALWAYS_VEL = true:  push-frame semantics (no shortcut).
-template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
+template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec, class DIV = ScaleDivision>
 UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
-                            double pos[3], double vel[3]) {
+                            double pos[3], double vel[3], const DIV &div = DIV()) {
   LagrangeWeights w;
   lagrangeWeights<SPEC::kColdOutOfLine>(S.positions, S.lag, time, w);
   double sensPosNom[3];
@@ -228,7 +230,7 @@ UB_DEV void adjSensorPosVel(const LsState &S, const TAB &T, double time,
   double ecfFromIcr[9];
   icrFrame(sensPosNom, sensVelNom, ecfFromIcr);
   applyPositionAdjustment(S, ecfFromIcr, sensPosNom, sensVelNom, time,
-                          [&](int i) { return param(S, i); }, pos, vel);
+                          [&](int i) { return param(S, i); }, pos, vel, div);
 }
 
 // LS::getQuaternions LS:2140-2153 + calculateRotationMatrixFromQuaternions U:78-95.
@@ -256,17 +258,19 @@ UB_DEV void attitudeCorrectionWith(const LsState &S, double time, PA &&pa, doubl
   euler[2] = div.byHalfSwath(S, pa(8) + pa(11) * nTime + pa(14) * nTime2);
   rotationFromEuler(euler, attCorr);
 }
-UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9]) {
-  attitudeCorrectionWith(S, time, [&](int i) { return param(S, i); }, attCorr);
+template <class DIV = ScaleDivision>
+UB_DEV void attitudeCorrection(const LsState &S, double time, double attCorr[9], const DIV &div = DIV()) {
+  attitudeCorrectionWith(S, time, [&](int i) { return param(S, i); }, attCorr, div);
 }
 
 // LS::computeDetectorView LS:2603-2675 (PF:2038-2110 is the same with the push-frame
 // position routine): ground point -> undistorted focal-plane coordinates at `time`.
-template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
+template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec, class DIV = ScaleDivision>
 UB_DEV void detectorView(const LsState &S, const TAB &T, double time, double gx,
-                         double gy, double gz, double &focalX, double &focalY) {
+                         double gy, double gz, double &focalX, double &focalY,
+                         const DIV &div = DIV()) {
   double pos[3], vel[3];
-  adjSensorPosVel<ALWAYS_VEL, TAB, SPEC>(S, T, time, pos, vel);
+  adjSensorPosVel<ALWAYS_VEL, TAB, SPEC, DIV>(S, T, time, pos, vel, div);
   double bodyLook[3] = {gx - pos[0], gy - pos[1], gz - pos[2]};
   double bodyToCamera[9];
   cameraToBodyMatrix<TAB, SPEC>(S, T, time, bodyToCamera);
@@ -275,7 +279,7 @@ UB_DEV void detectorView(const LsState &S, const TAB &T, double time, double gx,
   double adjustedLook[3];
   if (specHasAttAdj<SPEC>(S)) {
     double attCorr[9];
-    attitudeCorrection(S, time, attCorr);
+    attitudeCorrection(S, time, attCorr, div);
     matTVec(attCorr, cameraLook, adjustedLook);
   } else {
     adjustedLook[0] = cameraLook[0];

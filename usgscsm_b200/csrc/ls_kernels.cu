@@ -35,10 +35,11 @@ constexpr int kDefaultThreads = 256;  // block size used unless overridden
 // computed; only applyDistortion is repeated, now with the caller's desiredPrecision
 // instead of the default 1e-6 (hazard 3 in SURVEY.md §9).  The loop below therefore has a
 // single inlined copy of the detector view and runs it 2 + k times.
-template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec>
+template <bool ALWAYS_VEL, class TAB, class SPEC = GenericSpec, class DIV = ScaleDivision>
 UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
                                  double gy, double gz, double desiredPrecision, double &outLine,
-                                 double &outSamp, double &achieved, uint32_t &status) {
+                                 double &outSamp, double &achieved, uint32_t &status,
+                                 const DIV &div = DIV()) {
   double approxLine, approxSamp;
   projectiveSeed<SPEC>(S, gx, gy, gz, approxLine, approxSamp);
 
@@ -47,14 +48,14 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
   double t0 = 0.0, lineErr0 = 0.0;
   double t1 = 0.0, lineErr1;
   double focalX, focalY;
+  double distortedFocalX, distortedFocalY;
   uint32_t distStatus;
   int stage = 0;  // 0: residual at t = 0; 1: residual at t1 (0.1, then secant iterates)
   uint32_t evals = 0;
   for (;;) {
     evals++;
     double timei = lsImageTime<SPEC>(S, approxLine + t1);
-    detectorView<ALWAYS_VEL, TAB, SPEC>(S, T, timei, gx, gy, gz, focalX, focalY);
-    double distortedFocalX, distortedFocalY;
+    detectorView<ALWAYS_VEL, TAB, SPEC, DIV>(S, T, timei, gx, gy, gz, focalX, focalY, div);
     distStatus = 0;
     applyDistortion<SPEC::kDist>(focalX, focalY, distortedFocalX, distortedFocalY, fp, 1.0E-6, distStatus);
     double detectorLine = fp.iTransL[0] + fp.iTransL[1] * distortedFocalX +
@@ -86,11 +87,16 @@ UB_DEV void lsGroundToImagePoint(const LsState &S, const TAB &T, double gx,
 
   status |= evals << USGSCSM_B200_ST_EVALS_SHIFT;
   approxLine += t1;
-  // Final projection: same focal-plane point, distortion at the caller's precision.
-  double distortedFocalX, distortedFocalY;
-  distStatus = 0;
-  applyDistortion<SPEC::kDist>(focalX, focalY, distortedFocalX, distortedFocalY, fp,
-                               desiredPrecision, distStatus);
+  // Final projection: same focal-plane point, distortion at the caller's precision.  Only the
+  // RADIAL and CAHVOR models read that precision (D:490, D:754; the others iterate to hard-coded
+  // tolerances), so for every other model -- and for those two at the default 1e-6 -- this call
+  // would recompute the last residual's distorted point bit for bit: it is reused.
+  const int distType = SPEC::kDist >= 0 ? SPEC::kDist : fp.distortionType;
+  if ((distType == DIST_RADIAL || distType == DIST_CAHVOR) && desiredPrecision != 1.0E-6) {
+    distStatus = 0;
+    applyDistortion<SPEC::kDist>(focalX, focalY, distortedFocalX, distortedFocalY, fp,
+                                 desiredPrecision, distStatus);
+  }
   status |= distStatus;
   double detectorLine =
       fp.iTransL[0] + fp.iTransL[1] * distortedFocalX + fp.iTransL[2] * distortedFocalY;
@@ -125,26 +131,73 @@ struct DemGround {
   }
 };
 
-template <class SPEC, class TAB, class SRC>
+// Where the results of a launch go: the four output arrays of groundToImage, or -- for the
+// per-parameter searches of computeAllSensorPartials (csm/RasterGM.cpp:101-140) -- straight into
+// slot k of the point's list of partial derivatives, with the achieved precision and the
+// warnings accumulated over the parameters (what a separate "step" kernel did before, at 0.3 ms
+// of uncoalesced traffic per parameter).
+struct PlainOut {
+  double *__restrict__ line, *__restrict__ samp, *__restrict__ achieved;
+  uint32_t *__restrict__ status;
+  UB_DEV void store(long i, double l, double s, double a, uint32_t st) const {
+    __stcs(line + i, l);
+    __stcs(samp + i, s);
+    if (achieved) __stcs(achieved + i, a);
+    if (status) __stcs(status + i, st);
+  }
+};
+struct PartialsOut {
+  const double *__restrict__ l0, *__restrict__ s0;  // the image point the differences are taken from
+  const uint32_t *__restrict__ st0;                 // its status (null when the caller supplied the point)
+  double delta;
+  double *__restrict__ partials;  // numParams x (dline, dsamp) per point
+  int numParams, k;
+  double *__restrict__ achieved;  // nullable: running maximum over the parameters
+  uint32_t *__restrict__ status;  // running accumulation of the warning / error bits
+  UB_DEV void store(long i, double l1, double s1, double a, uint32_t stP) const {
+    const uint32_t kErr = USGSCSM_B200_ST_ERROR_ALGORITHM | USGSCSM_B200_ST_ERROR_UNKNOWN |
+                          USGSCSM_B200_ST_ERROR_OTHER;
+    const uint32_t kKeep = kErr | USGSCSM_B200_ST_NO_INTERSECTION | USGSCSM_B200_ST_PRECISION_NOT_MET;
+    uint32_t acc = k == 0 ? (st0 ? st0[i] & kKeep : 0u) : status[i];
+    double am = (k == 0 || !achieved) ? 0.0 : achieved[i];
+    acc |= stP & kKeep;
+    if (a > am) am = a;
+    const double pl = (l1 - l0[i]) / delta;
+    const double ps = (s1 - s0[i]) / delta;
+    double *out = partials + (size_t)i * numParams * 2;
+    out[2 * k] = pl;
+    out[2 * k + 1] = ps;
+    if (!(isfinite(pl) && isfinite(ps))) acc |= USGSCSM_B200_ST_NONFINITE;
+    if (k == numParams - 1 && (acc & kErr)) {
+      acc = (acc & kErr) | USGSCSM_B200_ST_NONFINITE;
+      for (int q = 0; q < 2 * numParams; q++) out[q] = nan("");
+      am = nan("");
+    }
+    status[i] = acc;
+    if (achieved) achieved[i] = am;
+  }
+};
+
+template <class SPEC, class TAB, class SRC, class OUT>
 UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const SRC &src,
-                                double prec, double *__restrict__ line, double *__restrict__ samp,
-                                double *__restrict__ achieved, uint32_t *__restrict__ status,
+                                double prec, const OUT &out,
                                 unsigned long long *__restrict__ next, int grab) {
+  // (reciprocals of m_halfTime / m_flyingHeight / m_halfSwath hoisted out of the loop --
+  // HoistedScaleDivision -- measured 9 % SLOWER here: three more live doubles at 64 registers)
+  using DIV = ScaleDivision;
+  const DIV div(S);
   forEachPointDynamic(n, next, grab, [&](long i) {
     double gx, gy, gz;
     double l, s, a;
     uint32_t st = 0;
     if (src.load(i, gx, gy, gz)) {
-      lsGroundToImagePoint<false, TAB, SPEC>(S, T, gx, gy, gz, prec, l, s, a, st);
+      lsGroundToImagePoint<false, TAB, SPEC, DIV>(S, T, gx, gy, gz, prec, l, s, a, st, div);
       st |= imageRangeStatus(l, s, S.nLines, S.nSamples);
     } else {  // a nodata sample: nothing to project
       l = s = a = nan("");
       st = USGSCSM_B200_ST_DEM_NODATA | USGSCSM_B200_ST_NONFINITE;
     }
-    __stcs(line + i, l);
-    __stcs(samp + i, s);
-    if (achieved) __stcs(achieved + i, a);
-    if (status) __stcs(status + i, st);
+    out.store(i, l, s, a, st);
   });
 }
 
@@ -159,21 +212,20 @@ UB_DEV void lsGroundToImageLoop(const LsState &S, const TAB &T, long n, const SR
 // for such a model, scattered over 85 KB of code, and ncu shows the search kernel waiting on
 // instruction fetch (icc hit rate 88 %, "no instruction" 14 % of stall samples).
 // DIST = -1 is the generic kernel.  Same arithmetic either way.
-template <bool STAGE, int MINB, int DIST, int ADJ, class SRC>
+template <bool STAGE, int MINB, int DIST, int ADJ, class SRC, class OUT>
 __global__ void __launch_bounds__(kThreads, MINB)
     lsGroundToImageKernel(const __grid_constant__ LsState S, long n,
                           const __grid_constant__ SRC src, double prec,
-                          double *__restrict__ line, double *__restrict__ samp,
-                          double *__restrict__ achieved, uint32_t *__restrict__ status,
+                          const __grid_constant__ OUT out,
                           unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
   using SPEC = typename std::conditional<(DIST >= 0), CommonSpec<DIST, ADJ>, SearchSpec>::type;
   if (STAGE) {
     StagedTables T = stageOrientationTables(S, specHasAdj<SPEC>(S), smem);
-    lsGroundToImageLoop<SPEC>(S, T, n, src, prec, line, samp, achieved, status, next, grab);
+    lsGroundToImageLoop<SPEC>(S, T, n, src, prec, out, next, grab);
   } else {
     OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
-    lsGroundToImageLoop<SPEC>(S, T, n, src, prec, line, samp, achieved, status, next, grab);
+    lsGroundToImageLoop<SPEC>(S, T, n, src, prec, out, next, grab);
   }
 }
 
@@ -558,11 +610,9 @@ static LaunchShape shapeFor(const LsState &S, long n, int smCount, size_t &smemB
   return sh;
 }
 
-template <class SRC>
+template <class SRC, class OUT>
 static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long n, const SRC &src,
-                                             double prec, double *line, double *samp,
-                                             double *achieved, uint32_t *status,
-                                             cudaStream_t stream) {
+                                             double prec, const OUT &out, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   size_t smemBytes;
   bool stage;
@@ -577,17 +627,17 @@ static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long
 #define UB_LAUNCH_G2I(STAGE, DIST, ADJ)                                                       \
   do {                                                                                        \
     if (smemBytes > 48 * 1024)                                                                \
-      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ, SRC>,   \
+      cudaFuncSetAttribute(lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ, SRC, OUT>, \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
-    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ, SRC>                           \
-        <<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, src, prec, line, samp,           \
-                                                       achieved, status, next, grab);         \
+    lsGroundToImageKernel<STAGE, kDefaultMinBlocks, DIST, ADJ, SRC, OUT>                      \
+        <<<sh.blocks, sh.threads, smemBytes, stream>>>(S, n, src, prec, out, next, grab);     \
   } while (0)
 #define UB_LAUNCH_G2I_ADJ(STAGE, DIST)                                                        \
   do {                                                                                        \
     if (adj == 0) UB_LAUNCH_G2I(STAGE, DIST, 0);                                              \
     else if (adj == 1) UB_LAUNCH_G2I(STAGE, DIST, 1);                                         \
-    else UB_LAUNCH_G2I(STAGE, DIST, 2);                                                       \
+    else if (adj == 2) UB_LAUNCH_G2I(STAGE, DIST, 2);                                         \
+    else UB_LAUNCH_G2I(STAGE, DIST, 3);                                                       \
   } while (0)
 #define UB_LAUNCH_G2I_DIST(STAGE)                                                             \
   do {                                                                                        \
@@ -600,7 +650,7 @@ static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long
   // USGSCSM_B200_LS_SPECIALISE: 1 = specialise (default), 2 = only models without parameter
   // adjustments, 3 = never
   static const int specialise = envInt("USGSCSM_B200_LS_SPECIALISE", 1);
-  const int adj = S.hasAttAdj ? 2 : (S.hasAdj ? 1 : 0);
+  const int adj = (S.hasAdj ? 1 : 0) | (S.hasAttAdj ? 2 : 0);
   const bool common = (specialise == 1 || (specialise == 2 && adj == 0)) && S.numIntTimes == 1 &&
                       S.useApproxInitTrans;
   if (stage)
@@ -618,16 +668,28 @@ cudaError_t launchLsGroundToImage(const LsState &S, int smCount, long n, const d
                                   const double *y, const double *z, double prec, double *line,
                                   double *samp, double *achieved, uint32_t *status,
                                   cudaStream_t stream) {
-  return launchLsGroundToImageFrom(S, smCount, n, ArrayGround{x, y, z}, prec, line, samp, achieved,
-                                   status, stream);
+  return launchLsGroundToImageFrom(S, smCount, n, ArrayGround{x, y, z}, prec,
+                                   PlainOut{line, samp, achieved, status}, stream);
+}
+
+// One parameter of computeAllSensorPartials: the search with the adjusted state S, its result
+// differenced against (l0, s0) into slot k of the point's list.
+cudaError_t launchLsSensorPartialStep(const LsState &S, int smCount, long n, const double *x,
+                                      const double *y, const double *z, double prec, const double *l0,
+                                      const double *s0, const uint32_t *st0, double delta,
+                                      double *partials, int numParams, int k, double *achieved,
+                                      uint32_t *status, cudaStream_t stream) {
+  return launchLsGroundToImageFrom(S, smCount, n, ArrayGround{x, y, z}, prec,
+                                   PartialsOut{l0, s0, st0, delta, partials, numParams, k, achieved, status},
+                                   stream);
 }
 
 // groundToImage of the ground points of a DEM window, generated in the kernel.
 cudaError_t launchLsGroundToImageDem(const LsState &S, int smCount, long n, const DemWindow &w,
                                      double prec, double *line, double *samp, double *achieved,
                                      uint32_t *status, cudaStream_t stream) {
-  return launchLsGroundToImageFrom(S, smCount, n, DemGround{w}, prec, line, samp, achieved, status,
-                                   stream);
+  return launchLsGroundToImageFrom(S, smCount, n, DemGround{w}, prec,
+                                   PlainOut{line, samp, achieved, status}, stream);
 }
 
 cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const double *line,

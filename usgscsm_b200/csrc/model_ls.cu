@@ -253,7 +253,7 @@ void repackLineScanner(Model &m) {
   for (int i = 0; i < 16; i++) {
     // getValue(i, adj) = m_currentParameterValue[i] + adj[i], adj = 0 (LS:757-772)
     S.params[i] = m.params[i] + 0.0;
-    if (S.params[i] != 0) S.hasAdj = 1;
+    if (i < 6 && S.params[i] != 0) S.hasAdj = 1;
     if (i >= 6 && i <= 14 && S.params[i] != 0) S.hasAttAdj = 1;
   }
 }
@@ -266,7 +266,7 @@ LsState adjustedLineScanner(const Model &m, int index, double delta) {
   S.hasAttAdj = 0;
   for (int i = 0; i < 16; i++) {
     S.params[i] = m.params[i] + (i == index ? delta : 0.0);
-    if (S.params[i] != 0) S.hasAdj = 1;
+    if (i < 6 && S.params[i] != 0) S.hasAdj = 1;
     if (i >= 6 && i <= 14 && S.params[i] != 0) S.hasAttAdj = 1;
   }
   return S;

@@ -100,7 +100,12 @@ struct LsState {
   int nSamples;
   int numIntTimes;        // m_intTimeLines.size()
   int useApproxInitTrans; // LS:2688-2736
-  int hasAdj;             // any m_currentParameterValue[i] != 0 (LS:2505-2509)
+  // Line-scan: any of parameters 0..5 (position / velocity bias and rate) != 0.  The reference
+  // takes its adjusted-position path when ANY parameter is non-zero (LS:2505-2509), but with
+  // parameters 0..5 all zero that path adds products with exact zeros to the nominal position
+  // (LS:2567-2583): same bits, so the frame and the velocity interpolation are only needed for
+  // these six.  Push-frame: any parameter != 0 (its position routine has no shortcut).
+  int hasAdj;
   int hasAttAdj;          // any of parameters 6..14 != 0 (Euler angles not identically 0)
   Ellipsoid ell;
   double gsd;
