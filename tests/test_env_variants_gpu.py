@@ -128,3 +128,43 @@ def test_fused_all_sensor_partials_same_bits():
         _run(code, OUT=os.path.join(d, "b.npy"), USGSCSM_B200_LS_FUSED_PARTIALS=1)
         a, b = np.load(os.path.join(d, "a.npy")), np.load(os.path.join(d, "b.npy"))
         assert np.array_equal(a, b, equal_nan=True)
+
+
+def test_frame_kernel_variants_same_bits():
+    """The frame kernels specialised on the distortion type, two points per 128-bit access
+    (default) against the generic one-point kernel; odd lengths, arrays off the 16-byte
+    boundary, radial / transverse / other distortion, sphere and oblate body, dense grid."""
+    code = """
+        import numpy as np, os, torch
+        import usgscsm_b200 as ub
+        from usgscsm_b200 import synth
+        out = []
+        dev = torch.device("cuda:0")
+        for kw in (dict(), dict(distortion_type=synth.TRANSVERSE, dist_coeffs=(0.0, 1.0, 0.0, 1e-6, 2e-6, -1e-6, 1e-8, 0.0, 2e-8, 0.0,
+                                                                       0.0, 0.0, 1.0, -1e-6, 1e-6, 2e-6, 0.0, 1e-8, 0.0, 2e-8)),
+                   dict(distortion_type=synth.DAWNFC, dist_coeffs=(8.4e-6,)), dict(minor_axis=synth.MOON_RADIUS * 0.99),
+                   dict(summing=2, starting_sample=3.0)):
+            gm = ub.UsgsAstroPlugin().constructModelFromState(synth.frame_state(n_lines=1024, n_samples=766, **kw))
+            nl, ns = 301, 766
+            n = nl * ns
+            h = torch.linspace(-200.0, 300.0, n + 3, dtype=torch.float64, device=dev)
+            g = gm.imageToGroundGrid(0.5, 0.5, 1.0, 1.0, nl, ns, h[:n], achieved=True)
+            out += [t.double().cpu().numpy() for t in g]
+            for off, m in ((0, n), (1, n - 1), (0, n - 1), (1, n - 2)):   # aligned / shifted by 8 bytes, even / odd
+                x, y, z = (t[off:off + m] for t in g[:3])
+                r = gm.groundToImageBatch(x, y, z, achieved=True)
+                out += [t.double().cpu().numpy() for t in r]
+                b = gm.imageToGroundBatch(r[0], r[1], h[off:off + m], achieved=True)
+                out += [t.double().cpu().numpy() for t in b]
+        np.save(os.environ["OUT"], np.concatenate(out))
+        print("OK")
+        """
+    import tempfile
+    import numpy as np
+    with tempfile.TemporaryDirectory() as d:
+        _run(code, OUT=os.path.join(d, "a.npy"))
+        _run(code, OUT=os.path.join(d, "b.npy"), USGSCSM_B200_FR_PAIRS=0)
+        _run(code, OUT=os.path.join(d, "c.npy"), USGSCSM_B200_FR_SPECIALISE=0)
+        a, b, c = (np.load(os.path.join(d, f)) for f in ("a.npy", "b.npy", "c.npy"))
+        assert a.size > 10 ** 6
+        assert np.array_equal(a, b, equal_nan=True) and np.array_equal(a, c, equal_nan=True)

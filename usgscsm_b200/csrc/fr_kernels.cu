@@ -8,6 +8,10 @@
 // matrices are evaluated once on the host (sensor_state.h) and the per-point work is ~100
 // flop against 44-52 B of HBM traffic: this is the one HBM-bound kernel pair of the engine
 // (SURVEY.md §8d).  I/O is SoA, coalesced, streaming.
+#include <cstdint>
+#include <cstdlib>
+#include <initializer_list>
+
 #include "kernels.h"
 #include "device_math.cuh"
 
@@ -70,6 +74,9 @@ __global__ void jitterKernel(const __grid_constant__ FrameState S, int remove, d
   }
 }
 
+// DIST >= 0 / JITTER = false: the launcher knows the model's distortion type and that it has no
+// jitter tables, and only that arithmetic is compiled in (the same operations on the same values).
+template <int DIST = -1, bool JITTER = true>
 UB_DEV void frGroundToImagePoint(const FrameState &S, double x, double y, double z,
                                  double desiredPrecision, double &outLine, double &outSamp,
                                  uint32_t &status) {
@@ -79,13 +86,14 @@ UB_DEV void frGroundToImagePoint(const FrameState &S, double x, double y, double
   double zo = z - S.params[2];
   double f = S.fp.focalLength;
   double denom = m[2] * xo + m[5] * yo + m[8] * zo;
-  double undistortedx = (f * (m[0] * xo + m[3] * yo + m[6] * zo) / denom);
-  double undistortedy = (f * (m[1] * xo + m[4] * yo + m[7] * zo) / denom);
+  const double rdenom = refinedReciprocal(denom);  // one reciprocal for the two quotients
+  double undistortedx = divideBy(f * (m[0] * xo + m[3] * yo + m[6] * zo), denom, rdenom);
+  double undistortedy = divideBy(f * (m[1] * xo + m[4] * yo + m[7] * zo), denom, rdenom);
   double distortedX, distortedY;
-  applyDistortion(undistortedx, undistortedy, distortedX, distortedY, S.fp, 1.0E-6, status);
+  applyDistortion<DIST>(undistortedx, undistortedy, distortedX, distortedY, S.fp, 1.0E-6, status);
   double line, sample;
   computePixel(distortedX, distortedY, S.fp, line, sample);
-  if (S.numLineTimes) {
+  if (JITTER && S.numLineTimes) {
     double jitteredLine, jitteredSample;
     addJitter(S, line, sample, desiredPrecision, 20, jitteredLine, jitteredSample);
     line = jitteredLine;
@@ -95,10 +103,11 @@ UB_DEV void frGroundToImagePoint(const FrameState &S, double x, double y, double
   outSamp = sample;
 }
 
+template <int DIST = -1, bool JITTER = true>
 UB_DEV void frImageToGroundPoint(const FrameState &S, double line, double sample, double height,
                                  double &x, double &y, double &z, uint32_t &status) {
   const double *m = S.mNorm;
-  if (S.numLineTimes) {
+  if (JITTER && S.numLineTimes) {
     double dejitteredLine, dejitteredSample;
     removeJitter(S, line, sample, dejitteredLine, dejitteredSample);
     line = dejitteredLine;
@@ -107,7 +116,7 @@ UB_DEV void frImageToGroundPoint(const FrameState &S, double line, double sample
   double x_camera, y_camera;
   distortedFocalPlaneCoordinates(line, sample, S.fp, x_camera, y_camera);
   double undistortedX, undistortedY;
-  removeDistortion(x_camera, y_camera, undistortedX, undistortedY, S.fp, 1.0E-6, status);
+  removeDistortion<DIST>(x_camera, y_camera, undistortedX, undistortedY, S.fp, 1.0E-6, status);
   const double f = S.fp.focalLength;
   double xl = m[0] * undistortedX + m[1] * undistortedY - m[2] * -f;
   double yl = m[3] * undistortedX + m[4] * undistortedY - m[5] * -f;
@@ -139,58 +148,156 @@ UB_DEV void frImageToGroundPoint(const FrameState &S, double line, double sample
   if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
 }
 
+// VEC points per thread per trip: VEC = 2 moves two neighbouring points with one 128-bit access
+// per array (half the address arithmetic and load / store instructions per point; the arrays
+// must then be 16-byte aligned, the launcher checks).  An odd last point goes through the
+// scalar path of the same kernel.
+template <int VEC>
+struct PointPack;
+template <>
+struct PointPack<1> {
+  typedef double D;
+  typedef uint32_t U;
+  static __device__ __forceinline__ double get(const D &v, int) { return v; }
+  static __device__ __forceinline__ D make(const double *a) { return a[0]; }
+  static __device__ __forceinline__ U makeStatus(const uint32_t *a) { return a[0]; }
+};
+template <>
+struct PointPack<2> {
+  typedef double2 D;
+  typedef uint2 U;
+  static __device__ __forceinline__ double get(const D &v, int k) { return k ? v.y : v.x; }
+  static __device__ __forceinline__ D make(const double *a) { return make_double2(a[0], a[1]); }
+  static __device__ __forceinline__ U makeStatus(const uint32_t *a) { return make_uint2(a[0], a[1]); }
+};
+
+template <int DIST, bool JITTER>
+UB_DEV void frGroundToImageChecked(const FrameState &S, double gx, double gy, double gz, double prec,
+                                   double &l, double &s, uint32_t &st) {
+  st = 0;
+  frGroundToImagePoint<DIST, JITTER>(S, gx, gy, gz, prec, l, s, st);
+  if (!(isfinite(l) && isfinite(s))) st |= USGSCSM_B200_ST_NONFINITE;
+  // getValidImageRange FR:600-608: (startingDetectorLine, startingDetectorSample) .. (nLines, nSamples)
+  if (!(l >= S.fp.startingDetectorLine && l <= (double)S.nLines &&
+        s >= S.fp.startingDetectorSample && s <= (double)S.nSamples))
+    st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
+}
+
+template <int DIST, bool JITTER, int VEC>
 __global__ void __launch_bounds__(kThreads)
     frGroundToImageKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  typedef PointPack<VEC> P;
+  typedef typename P::D D;
+  typedef typename P::U U;
   const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
-    double l, s;
-    uint32_t st = 0;
-    frGroundToImagePoint(S, gx, gy, gz, prec, l, s, st);
-    if (!(isfinite(l) && isfinite(s))) st |= USGSCSM_B200_ST_NONFINITE;
-    // getValidImageRange FR:600-608: (startingDetectorLine, startingDetectorSample) .. (nLines, nSamples)
-    if (!(l >= S.fp.startingDetectorLine && l <= (double)S.nLines &&
-          s >= S.fp.startingDetectorSample && s <= (double)S.nSamples))
-      st |= USGSCSM_B200_ST_OUT_OF_IMAGE;
-    __stcs(line + i, l);
-    __stcs(samp + i, s);
-    if (achieved) __stcs(achieved + i, nan(""));  // the frame model never writes achievedPrecision
-    if (status) __stcs(status + i, st);
+  const long first = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long packs = n / VEC;
+  const double never[2] = {nan(""), nan("")};  // the frame model never writes achievedPrecision
+  for (long p = first; p < packs; p += stride) {
+    const D gx = __ldcs(reinterpret_cast<const D *>(x) + p);
+    const D gy = __ldcs(reinterpret_cast<const D *>(y) + p);
+    const D gz = __ldcs(reinterpret_cast<const D *>(z) + p);
+    double l[VEC], s[VEC];
+    uint32_t st[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; k++)
+      frGroundToImageChecked<DIST, JITTER>(S, P::get(gx, k), P::get(gy, k), P::get(gz, k), prec, l[k],
+                                           s[k], st[k]);
+    __stcs(reinterpret_cast<D *>(line) + p, P::make(l));
+    __stcs(reinterpret_cast<D *>(samp) + p, P::make(s));
+    if (achieved) __stcs(reinterpret_cast<D *>(achieved) + p, P::make(never));
+    if (status) __stcs(reinterpret_cast<U *>(status) + p, P::makeStatus(st));
   }
+  if (VEC > 1 && first == 0)
+    for (long i = packs * VEC; i < n; i++) {
+      double l, s;
+      uint32_t st;
+      frGroundToImageChecked<DIST, JITTER>(S, x[i], y[i], z[i], prec, l, s, st);
+      line[i] = l;
+      samp[i] = s;
+      if (achieved) achieved[i] = never[0];
+      if (status) status[i] = st;
+    }
 }
 
-template <bool GRID>
+template <bool GRID, int DIST, bool JITTER, int VEC>
 __global__ void __launch_bounds__(kThreads)
     frImageToGroundKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ line,
                           const double *__restrict__ samp, GridSpec g,
                           const double *__restrict__ height, int heightStride,
                           double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
+  typedef PointPack<VEC> P;
+  typedef typename P::D D;
+  typedef typename P::U U;
   const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    double l, s;
-    if (GRID) {
-      long r = i / g.nSamps;
-      long c = i - r * g.nSamps;
-      l = g.line0 + (double)(g.row0 + r) * g.dline;
-      s = g.samp0 + (double)c * g.dsamp;
-    } else {
-      l = __ldcs(line + i);
-      s = __ldcs(samp + i);
-    }
-    double h = heightStride ? __ldcs(height + i) : __ldg(height);
-    double px, py, pz;
-    uint32_t st = 0;
-    frImageToGroundPoint(S, l, s, h, px, py, pz, st);
-    __stcs(x + i, px);
-    __stcs(y + i, py);
-    __stcs(z + i, pz);
-    if (achieved) __stcs(achieved + i, nan(""));
-    if (status) __stcs(status + i, st);
+  const long first = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long packs = n / VEC;
+  const double never[2] = {nan(""), nan("")};
+  const double oneHeight = heightStride ? 0.0 : __ldg(height);
+  // dense grid (its rows hold a whole number of packs, the launcher checks): (row, column) of
+  // the thread's pack, advanced by the stride's (rows, columns) instead of a division per point
+  long r = 0, strideRows = 0;
+  int c = 0, strideCols = 0;
+  if (GRID) {
+    const long perRow = g.nSamps / VEC;
+    r = first / perRow;
+    c = (int)(first - r * perRow) * VEC;
+    strideRows = stride / perRow;
+    strideCols = (int)(stride - strideRows * perRow) * VEC;
   }
+  for (long p = first; p < packs; p += stride) {
+    D lv, sv, hv;
+    if (!GRID) {
+      lv = __ldcs(reinterpret_cast<const D *>(line) + p);
+      sv = __ldcs(reinterpret_cast<const D *>(samp) + p);
+    }
+    if (heightStride) hv = __ldcs(reinterpret_cast<const D *>(height) + p);
+    double px[VEC], py[VEC], pz[VEC];
+    uint32_t st[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      double l, sm;
+      if (GRID) {
+        l = g.line0 + (double)(g.row0 + r) * g.dline;
+        sm = g.samp0 + (double)(c + k) * g.dsamp;
+      } else {
+        l = P::get(lv, k);
+        sm = P::get(sv, k);
+      }
+      st[k] = 0;
+      frImageToGroundPoint<DIST, JITTER>(S, l, sm, heightStride ? P::get(hv, k) : oneHeight, px[k],
+                                         py[k], pz[k], st[k]);
+    }
+    if (GRID) {
+      r += strideRows;
+      c += strideCols;
+      if (c >= g.nSamps) {
+        c -= (int)g.nSamps;
+        r++;
+      }
+    }
+    __stcs(reinterpret_cast<D *>(x) + p, P::make(px));
+    __stcs(reinterpret_cast<D *>(y) + p, P::make(py));
+    __stcs(reinterpret_cast<D *>(z) + p, P::make(pz));
+    if (achieved) __stcs(reinterpret_cast<D *>(achieved) + p, P::make(never));
+    if (status) __stcs(reinterpret_cast<U *>(status) + p, P::makeStatus(st));
+  }
+  if (VEC > 1 && !GRID && first == 0)
+    for (long i = packs * VEC; i < n; i++) {
+      double px, py, pz;
+      uint32_t st = 0;
+      frImageToGroundPoint<DIST, JITTER>(S, line[i], samp[i], heightStride ? height[i] : oneHeight, px,
+                                         py, pz, st);
+      x[i] = px;
+      y[i] = py;
+      z[i] = pz;
+      if (achieved) achieved[i] = never[0];
+      if (status) status[i] = st;
+    }
 }
 
 // computeGroundPartials FR:955-1003: the step is the ground size of a pixel, from
@@ -354,13 +461,50 @@ cudaError_t launchFrSensorState(const FrameState &S, long n, const double *line,
   return cudaGetLastError();
 }
 
+// The compile-time variants: the distortion types the frame ISDs carry most (radial, transverse,
+// none = radial with zero coefficients is still "radial") without jitter tables; anything else
+// runs the generic kernel.  USGSCSM_B200_FR_SPECIALISE=0 forces the generic kernel.
+static bool frSpecialise() {
+  static const bool on = [] {
+    const char *v = getenv("USGSCSM_B200_FR_SPECIALISE");
+    return !(v && *v == '0');
+  }();
+  return on;
+}
+#define UB_FR_DISPATCH(LAUNCH, VEC)                                              \
+  do {                                                                           \
+    if (!frSpecialise() || S.numLineTimes) LAUNCH(-1, true, 1);                  \
+    else if (S.fp.distortionType == DIST_RADIAL) LAUNCH(DIST_RADIAL, false, VEC);         \
+    else if (S.fp.distortionType == DIST_TRANSVERSE) LAUNCH(DIST_TRANSVERSE, false, VEC); \
+    else LAUNCH(-1, false, 1);                                                   \
+  } while (0)
+
+// every non-null array on a 16-byte boundary (status: 8): two points per 128-bit access
+static bool frPairable(std::initializer_list<const void *> doubles, const void *status) {
+  static const bool on = [] {
+    const char *v = getenv("USGSCSM_B200_FR_PAIRS");
+    return !(v && *v == '0');
+  }();
+  if (!on || (reinterpret_cast<uintptr_t>(status) & 7)) return false;
+  for (const void *p : doubles)
+    if (reinterpret_cast<uintptr_t>(p) & 15) return false;
+  return true;
+}
+
 cudaError_t launchFrGroundToImage(const FrameState &S, int smCount, long n, const double *x,
                                   const double *y, const double *z, double prec, double *line,
                                   double *samp, double *achieved, uint32_t *status,
                                   cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  frGroundToImageKernel<<<frBlocks(frGroundToImageKernel, n, smCount), kThreads, 0, stream>>>(S, n, x, y, z, prec, line,
-                                                                      samp, achieved, status);
+#define UB_FR_G2I(DIST, JITTER, VEC)                                                                  \
+  frGroundToImageKernel<DIST, JITTER, VEC>                                                            \
+      <<<frBlocks(frGroundToImageKernel<DIST, JITTER, VEC>, (n + VEC - 1) / VEC, smCount), kThreads,  \
+         0, stream>>>(S, n, x, y, z, prec, line, samp, achieved, status)
+  if (frPairable({x, y, z, line, samp, achieved}, status))
+    UB_FR_DISPATCH(UB_FR_G2I, 2);
+  else
+    UB_FR_DISPATCH(UB_FR_G2I, 1);
+#undef UB_FR_G2I
   countLaunch();
   return cudaGetLastError();
 }
@@ -372,12 +516,28 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
   (void)prec;  // the frame model's imageToGround is closed form: desiredPrecision is unused
   if (n <= 0) return cudaSuccess;
   GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
-  if (grid)
-    frImageToGroundKernel<true><<<frBlocks(frImageToGroundKernel<true>, n, smCount), kThreads, 0, stream>>>(
-        S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
-  else
-    frImageToGroundKernel<false><<<frBlocks(frImageToGroundKernel<false>, n, smCount), kThreads, 0, stream>>>(
-        S, n, line, samp, g, height, heightStride, x, y, z, achieved, status);
+#define UB_FR_I2G_OF(GRID, DIST, JITTER, VEC)                                                         \
+  frImageToGroundKernel<GRID, DIST, JITTER, VEC>                                                      \
+      <<<frBlocks(frImageToGroundKernel<GRID, DIST, JITTER, VEC>, (n + VEC - 1) / VEC, smCount),      \
+         kThreads, 0, stream>>>(S, n, line, samp, g, height, heightStride, x, y, z, achieved, status)
+#define UB_FR_I2G_GRID(DIST, JITTER, VEC) UB_FR_I2G_OF(true, DIST, JITTER, VEC)
+#define UB_FR_I2G_ARRAY(DIST, JITTER, VEC) UB_FR_I2G_OF(false, DIST, JITTER, VEC)
+  const bool pairs = frPairable({x, y, z, achieved, heightStride ? height : nullptr,
+                                 grid ? nullptr : line, grid ? nullptr : samp}, status);
+  if (grid) {
+    // rows of an even number of samples, fewer than 2^31 rows and columns
+    if (pairs && g.nSamps % 2 == 0)
+      UB_FR_DISPATCH(UB_FR_I2G_GRID, 2);
+    else
+      UB_FR_DISPATCH(UB_FR_I2G_GRID, 1);
+  } else if (pairs) {
+    UB_FR_DISPATCH(UB_FR_I2G_ARRAY, 2);
+  } else {
+    UB_FR_DISPATCH(UB_FR_I2G_ARRAY, 1);
+  }
+#undef UB_FR_I2G_ARRAY
+#undef UB_FR_I2G_GRID
+#undef UB_FR_I2G_OF
   countLaunch();
   return cudaGetLastError();
 }
