@@ -168,3 +168,47 @@ def test_frame_kernel_variants_same_bits():
         a, b, c = (np.load(os.path.join(d, f)) for f in ("a.npy", "b.npy", "c.npy"))
         assert a.size > 10 ** 6
         assert np.array_equal(a, b, equal_nan=True) and np.array_equal(a, c, equal_nan=True)
+
+
+def test_pushframe_kernel_variants_same_bits():
+    """The push-frame kernels specialised on distortion type / attitude correction (framelet
+    numbers without a division, hoisted line split, orientation outside the table out of line)
+    against the generic kernels (USGSCSM_B200_PF_SPECIALISE=0): lines far outside the image,
+    negative lines, flipped / reversed framelets, summing, oblate body, adjusted parameters."""
+    code = """
+        import numpy as np, os, torch
+        import usgscsm_b200 as ub
+        from usgscsm_b200 import synth
+        T = (0.0, 1.0, 0.0, 1e-6, 2e-6, -1e-6, 1e-8, 0.0, 2e-8, 0.0, 0.0, 0.0, 1.0, -1e-6, 1e-6, 2e-6, 0.0, 1e-8, 0.0, -2e-8)
+        out = []
+        rng = np.random.default_rng(8)
+        for kw in (dict(), dict(flipped=True, reversed_order=True, line_sign=1.0), dict(summing=2.0),
+                   dict(distortion_type=1, dist_coeffs=T), dict(distortion_type=3, dist_coeffs=(8.4e-6,)),
+                   dict(major_axis=3396190.0, minor_axis=3376200.0, gm=4.2828e13, altitude=300000.0),
+                   dict(params=(3.0, -2.0, 1.5, 0.02, -0.01, 0.005, 0.5, -0.3, 0.2, 0.05, 0.04, -0.03, 1e-4, 2e-4, -1e-4, 0.01)),
+                   dict(n_framelets=3, framelet_height=7, n_samples=200)):
+            gm = ub.UsgsAstroPlugin().constructModelFromState(synth.pushframe_state(n_framelets=kw.pop("n_framelets", 64),
+                                                               framelet_height=kw.pop("framelet_height", 16),
+                                                               n_samples=kw.pop("n_samples", 600), seed=4, **kw))
+            sz = gm.getImageSize(); nl, ns = int(sz.line), int(sz.samp)
+            g = gm.imageToGroundGrid(0.5, 0.5, 1.0, 1.0, nl, ns, np.linspace(-300.0, 300.0, nl * ns), achieved=True)
+            out += [np.asarray(t, dtype=np.float64) for t in g]
+            n = 40000
+            line = np.concatenate([rng.uniform(-3 * nl, 4 * nl, n), np.arange(-40.0, 40.0, 0.25), nl + np.arange(-40.0, 40.0, 0.25),
+                                   [1e300, -1e300, 5e15, -5e15, 4503599627370496.0, np.nan, np.inf, -0.0, 0.0]])
+            samp = rng.uniform(-50, ns + 50, line.size)
+            b = gm.imageToGroundBatch(line, samp, rng.uniform(-500, 500, line.size), achieved=True)
+            out += [np.asarray(t, dtype=np.float64) for t in b]
+            r = gm.groundToImageBatch(g[0], g[1], g[2], achieved=True)
+            out += [np.asarray(t, dtype=np.float64) for t in r]
+        np.save(os.environ["OUT"], np.concatenate(out))
+        print("OK")
+        """
+    import tempfile
+    import numpy as np
+    with tempfile.TemporaryDirectory() as d:
+        _run(code, OUT=os.path.join(d, "a.npy"))
+        _run(code, OUT=os.path.join(d, "b.npy"), USGSCSM_B200_PF_SPECIALISE=0)
+        a, b = np.load(os.path.join(d, "a.npy")), np.load(os.path.join(d, "b.npy"))
+        assert a.size > 10 ** 6
+        assert np.array_equal(a, b, equal_nan=True)

@@ -68,31 +68,44 @@ struct OrientCache {
   int stride;             // doubles per entry in `entries`
 };
 
+// ATT: -1 = S.hasAttAdj decides at run time, 0 / 1 = the launcher knows (compile-time variant).
+template <int ATT>
+UB_DEV bool pfHasAttAdj(const LsState &S) { return ATT < 0 ? S.hasAttAdj != 0 : ATT != 0; }
+
+// entry of a framelet the caller knows to be inside the table
+template <int ATT>
+UB_DEV void orientationFromTable(const LsState &S, const OrientCache &C, int frameletNumber,
+                                 Orientation &o) {
+  const double *e = C.entries + (long)(frameletNumber + 1) * C.stride;
+#pragma unroll
+  for (int i = 0; i < 3; i++) o.pos[i] = e[i];
+#pragma unroll
+  for (int i = 0; i < 9; i++) o.camToBody[i] = e[3 + i];
+  if (pfHasAttAdj<ATT>(S)) {
+#pragma unroll
+    for (int i = 0; i < 9; i++) o.attCorr[i] = e[12 + i];
+  }
+}
+
+template <int ATT = -1>
 UB_DEV void orientationAt(const LsState &S, const OrientationTables &T, const OrientCache &C,
                           int frameletNumber, Orientation &o) {
   if (C.entries && frameletNumber >= -1 && frameletNumber <= S.numFramelets) {
-    const double *e = C.entries + (long)(frameletNumber + 1) * C.stride;
-#pragma unroll
-    for (int i = 0; i < 3; i++) o.pos[i] = e[i];
-#pragma unroll
-    for (int i = 0; i < 9; i++) o.camToBody[i] = e[3 + i];
-    if (S.hasAttAdj) {
-#pragma unroll
-      for (int i = 0; i < 9; i++) o.attCorr[i] = e[12 + i];
-    }
+    orientationFromTable<ATT>(S, C, frameletNumber, o);
   } else {
     computeOrientation(S, T, pfFrameletTime(S, frameletNumber), o);
   }
 }
 
 // Second half of computeDetectorView PF:2038-2110 given the exterior orientation.
+template <int ATT = -1>
 UB_DEV void viewFromOrientation(const LsState &S, const Orientation &o, double gx, double gy,
                                 double gz, double &focalX, double &focalY) {
   double bodyLook[3] = {gx - o.pos[0], gy - o.pos[1], gz - o.pos[2]};
   double cameraLook[3];
   matTVec(o.camToBody, bodyLook, cameraLook);
   double adjustedLook[3];
-  if (S.hasAttAdj) {
+  if (pfHasAttAdj<ATT>(S)) {
     matTVec(o.attCorr, cameraLook, adjustedLook);
   } else {  // Euler angles identically 0: the correction is the identity
     adjustedLook[0] = cameraLook[0];
@@ -150,6 +163,14 @@ __global__ void pfFrameletOrientKernel(const __grid_constant__ LsState S, double
 }
 
 // ---- groundToImage -------------------------------------------------------------------------
+// DIST >= 0 / ATT >= 0: compile-time variants of the launcher (distortion type, attitude
+// correction live or not).  The launcher picks them only when the framelet table exists and
+// (2 numFramelets + 1) * summedFrameletHeight < 2^53 (pfFrameletNumbersExact), and then the time
+// framelet of calcFrameDistance needs no division and is always inside the table:
+// (e + 0.5) * h is exact, so its correctly rounded quotient by h is e + 0.5 and truncates to e,
+// and (h * e + 0.5) / h = e + 0.5 / h truncates to e as well -- the final view is the last
+// evaluation's.  e is clamped to [0, numFramelets], the table spans [-1, numFramelets].
+template <int DIST = -1, int ATT = -1>
 UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
                                  const OrientCache &C, double gx, double gy, double gz,
                                  double desiredPrecision, double &outLine, double &outSamp,
@@ -172,11 +193,16 @@ UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
   for (;;) {
     evals++;
     // calcFrameDistance PF:2496-2521 at endFramelet
-    double centerLine = (endFramelet + 0.5) * summedFrameletHeight;
-    viewFramelet = pfTimeFramelet(S, centerLine);
     Orientation o;
-    orientationAt(S, T, C, viewFramelet, o);
-    viewFromOrientation(S, o, gx, gy, gz, focalX, focalY);
+    if (DIST >= 0) {
+      viewFramelet = S.frameletsOrderReversed ? numFramelets - endFramelet - 1 : endFramelet;
+      orientationFromTable<ATT>(S, C, viewFramelet, o);
+    } else {
+      double centerLine = (endFramelet + 0.5) * summedFrameletHeight;
+      viewFramelet = pfTimeFramelet(S, centerLine);
+      orientationAt<ATT>(S, T, C, viewFramelet, o);
+    }
+    viewFromOrientation<ATT>(S, o, gx, gy, gz, focalX, focalY);
     double detectorLine = fp.iTransL[0] + fp.iTransL[1] * focalX + fp.iTransL[2] * focalY +
                           fp.detectorLineOrigin - fp.startingDetectorLine;
     detectorLine = divideBy(detectorLine, fp.lineSumming);
@@ -210,14 +236,16 @@ UB_DEV void pfGroundToImagePoint(const LsState &S, const OrientationTables &T,
   // getImageTime(ImageCoord(0.5 + summedFrameletHeight * endFramelet, 0.0)) + computeDetectorView:
   // the same framelet time as the last distance evaluation, hence the same focal-plane point.
   status |= evals << USGSCSM_B200_ST_EVALS_SHIFT;
-  int finalFramelet = pfTimeFramelet(S, 0.5 + summedFrameletHeight * endFramelet);
-  if (finalFramelet != viewFramelet) {
-    Orientation o;
-    orientationAt(S, T, C, finalFramelet, o);
-    viewFromOrientation(S, o, gx, gy, gz, focalX, focalY);
+  if (DIST < 0) {
+    int finalFramelet = pfTimeFramelet(S, 0.5 + summedFrameletHeight * endFramelet);
+    if (finalFramelet != viewFramelet) {
+      Orientation o;
+      orientationAt<ATT>(S, T, C, finalFramelet, o);
+      viewFromOrientation<ATT>(S, o, gx, gy, gz, focalX, focalY);
+    }
   }
   double distortedFocalX, distortedFocalY;
-  applyDistortion(focalX, focalY, distortedFocalX, distortedFocalY, fp, desiredPrecision, status);
+  applyDistortion<DIST>(focalX, focalY, distortedFocalX, distortedFocalY, fp, desiredPrecision, status);
   double detectorLine =
       fp.iTransL[0] + fp.iTransL[1] * distortedFocalX + fp.iTransL[2] * distortedFocalY;
   double detectorSample =
@@ -242,7 +270,7 @@ UB_DEV uint32_t pfImageRangeStatus(double line, double samp, const LsState &S) {
   return st;
 }
 
-template <bool STAGE>
+template <bool STAGE, int DIST, int ATT>
 __global__ void __launch_bounds__(kThreads, UB_PF_G2I_MINB)
     pfGroundToImageKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
@@ -256,7 +284,7 @@ __global__ void __launch_bounds__(kThreads, UB_PF_G2I_MINB)
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s, a;
     uint32_t st = 0;
-    pfGroundToImagePoint(S, T, C, gx, gy, gz, prec, l, s, a, st);
+    pfGroundToImagePoint<DIST, ATT>(S, T, C, gx, gy, gz, prec, l, s, a, st);
     st |= pfImageRangeStatus(l, s, S);
     __stcs(line + i, l);
     __stcs(samp + i, s);
@@ -266,16 +294,64 @@ __global__ void __launch_bounds__(kThreads, UB_PF_G2I_MINB)
 }
 
 // ---- imageToGround -------------------------------------------------------------------------
+// A framelet outside the table (a line far outside the image): evaluated in the thread, out of
+// line so that the specialised kernels do not carry its registers and instructions.
+static __device__ __noinline__ void computeOrientationCold(const LsState &S, const OrientationTables &T,
+                                                           int frameletNumber, Orientation &o) {
+  computeOrientation(S, T, pfFrameletTime(S, frameletNumber), o);
+}
+
+// line / h and fmod(line, h) for the framelet height h (a positive integer as a double) from ONE
+// quotient with the reciprocal rh = refinedReciprocal(h) hoisted: q = RN(|line| / h) (divideBy
+// returns the division's bits) truncates to n or n + 1, n the integer part of the true quotient;
+// |line| - trunc(q) h is exact in one fma (a multiple of ulp(line) below 2 h), and one
+// correction brings it into [0, h): that is fmod's exact remainder, with line's sign.
+UB_DEV void pfSplitLine(double line, double h, double rh, double &quotient, double &remainder) {
+  const double a = fabs(line);
+  if (!(a < 4503599627370496.0)) {  // 2^52 and up, NaN: the library routines
+    quotient = line / h;
+    remainder = fmod(line, h);
+    return;
+  }
+  const double q = divideBy(a, h, rh);
+  double r = __fma_rn(-trunc(q), h, a);
+  if (r < 0.0) r += h;
+  quotient = copysign(q, line);
+  remainder = copysign(r, line);
+}
+
+// DIST >= 0 / ATT >= 0: the launcher's compile-time variants (see pfGroundToImagePoint); rh is
+// refinedReciprocal(summedFrameletHeight), used by them only.
+template <int DIST = -1, int ATT = -1>
 UB_DEV void pfImageToGroundPoint(const LsState &S, const OrientationTables &T,
                                  const OrientCache &C, double line, double sample, double height,
                                  double desiredPrecision, double &x, double &y, double &z,
-                                 double &achieved, uint32_t &status) {
-  int frameletNumber = pfTimeFramelet(S, line);
+                                 double &achieved, uint32_t &status, double rh = 0.0) {
+  int frameletNumber;
+  double frameletLine;  // line within the framelet, PF:1757-1764
   Orientation o;
-  orientationAt(S, T, C, frameletNumber, o);
-
-  // line within the framelet, PF:1757-1764
-  double frameletLine = fmod(line, (double)S.summedFrameletHeight);
+  if (DIST >= 0) {
+    double quotient;
+    pfSplitLine(line, (double)S.summedFrameletHeight, rh, quotient, frameletLine);
+    frameletNumber = truncToInt(quotient);
+    if (S.frameletsOrderReversed) frameletNumber = S.numFramelets - frameletNumber - 1;
+    if (C.entries && frameletNumber >= -1 && frameletNumber <= S.numFramelets) {
+      orientationFromTable<ATT>(S, C, frameletNumber, o);
+    } else {
+      Orientation cold;  // the callee's copy lives in local memory; `o` stays in registers
+      computeOrientationCold(S, T, frameletNumber, cold);
+#pragma unroll
+      for (int i = 0; i < 3; i++) o.pos[i] = cold.pos[i];
+#pragma unroll
+      for (int i = 0; i < 9; i++) o.camToBody[i] = cold.camToBody[i];
+#pragma unroll
+      for (int i = 0; i < 9; i++) o.attCorr[i] = cold.attCorr[i];
+    }
+  } else {
+    frameletNumber = pfTimeFramelet(S, line);
+    orientationAt<ATT>(S, T, C, frameletNumber, o);
+    frameletLine = fmod(line, (double)S.summedFrameletHeight);
+  }
   if (S.frameletsFlipped) frameletLine = S.summedFrameletHeight - frameletLine;
   frameletLine += S.halfOverlap;
 
@@ -283,13 +359,13 @@ UB_DEV void pfImageToGroundPoint(const LsState &S, const OrientationTables &T,
   distortedFocalPlaneCoordinates(frameletLine, sample, S.fp, distortedFocalPlaneX,
                                  distortedFocalPlaneY);
   double undistortedFocalPlaneX, undistortedFocalPlaneY;
-  removeDistortion(distortedFocalPlaneX, distortedFocalPlaneY, undistortedFocalPlaneX,
-                   undistortedFocalPlaneY, S.fp, 1.0E-6, status);
+  removeDistortion<DIST>(distortedFocalPlaneX, distortedFocalPlaneY, undistortedFocalPlaneX,
+                         undistortedFocalPlaneY, S.fp, 1.0E-6, status);
   double cameraLook[3];
   cameraLookVector(undistortedFocalPlaneX, undistortedFocalPlaneY, S.fp.zDirection,
                    S.fp.focalLength * (1 - param(S, 15) / S.halfSwath), cameraLook);
   double corrected[3];
-  if (S.hasAttAdj) {
+  if (pfHasAttAdj<ATT>(S)) {
     matVec(o.attCorr, cameraLook, corrected);
   } else {
     corrected[0] = cameraLook[0];
@@ -309,7 +385,7 @@ UB_DEV void pfImageToGroundPoint(const LsState &S, const OrientationTables &T,
   if (!finite3(x, y, z)) status |= USGSCSM_B200_ST_NONFINITE;
 }
 
-template <bool STAGE, bool GRID>
+template <bool STAGE, bool GRID, int DIST, int ATT>
 __global__ void __launch_bounds__(kThreads, UB_PF_I2G_MINB)
     pfImageToGroundKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
                           const double *__restrict__ samp, GridSpec g,
@@ -319,14 +395,29 @@ __global__ void __launch_bounds__(kThreads, UB_PF_I2G_MINB)
   extern __shared__ double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
+  const double rh = DIST >= 0 ? refinedReciprocal((double)S.summedFrameletHeight) : 0.0;
   const long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  const long first = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  // dense grid: (row, column) of the thread's point, advanced by the stride's (rows, columns)
+  // instead of a 64-bit division per point
+  long r = 0, c = 0, strideRows = 0, strideCols = 0;
+  if (GRID) {
+    r = first / g.nSamps;
+    c = first - r * g.nSamps;
+    strideRows = stride / g.nSamps;
+    strideCols = stride - strideRows * g.nSamps;
+  }
+  for (long i = first; i < n; i += stride) {
     double l, s;
     if (GRID) {
-      long r = i / g.nSamps;
-      long c = i - r * g.nSamps;
       l = g.line0 + (double)(g.row0 + r) * g.dline;
       s = g.samp0 + (double)c * g.dsamp;
+      r += strideRows;
+      c += strideCols;
+      if (c >= g.nSamps) {
+        c -= g.nSamps;
+        r++;
+      }
     } else {
       l = __ldcs(line + i);
       s = __ldcs(samp + i);
@@ -334,7 +425,7 @@ __global__ void __launch_bounds__(kThreads, UB_PF_I2G_MINB)
     double h = heightStride ? __ldcs(height + i) : __ldg(height);
     double px, py, pz, a;
     uint32_t st = 0;
-    pfImageToGroundPoint(S, T, C, l, s, h, prec, px, py, pz, a, st);
+    pfImageToGroundPoint<DIST, ATT>(S, T, C, l, s, h, prec, px, py, pz, a, st, rh);
     __stcs(x + i, px);
     __stcs(y + i, py);
     __stcs(z + i, pz);
@@ -524,6 +615,21 @@ cudaError_t launchPfSensorState(const LsState &S, long n, const double *line,
   return cudaGetLastError();
 }
 
+// USGSCSM_B200_PF_SPECIALISE=0: the generic kernels only
+static bool pfSpecialise() {
+  static const bool on = [] {
+    const char *v = getenv("USGSCSM_B200_PF_SPECIALISE");
+    return !(v && *v == '0');
+  }();
+  return on;
+}
+
+// see pfGroundToImagePoint
+static bool pfFrameletNumbersExact(const LsState &S) {
+  return S.frameletOrient && S.numFramelets >= 1 && S.summedFrameletHeight >= 1 &&
+         (2.0 * S.numFramelets + 1.0) * S.summedFrameletHeight < 2147483648.0;
+}
+
 cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const double *x,
                                   const double *y, const double *z, double prec, double *line,
                                   double *samp, double *achieved, uint32_t *status,
@@ -535,12 +641,28 @@ cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const d
   WorkCounter wc;
   cudaError_t e = wc.acquire(stream);
   if (e != cudaSuccess) return e;
+#define UB_PF_G2I(STAGE, DIST, ATT)                                                          \
+  pfGroundToImageKernel<STAGE, DIST, ATT><<<sh.blocks, sh.threads, STAGE ? smemBytes : 0, stream>>>( \
+      S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize())
+#define UB_PF_G2I_ATT(STAGE, DIST)                \
+  do {                                            \
+    if (S.hasAttAdj) UB_PF_G2I(STAGE, DIST, 1);   \
+    else UB_PF_G2I(STAGE, DIST, 0);               \
+  } while (0)
+#define UB_PF_G2I_DIST(STAGE)                                                             \
+  do {                                                                                    \
+    if (!pfSpecialise() || !pfFrameletNumbersExact(S)) UB_PF_G2I(STAGE, -1, -1);          \
+    else if (S.fp.distortionType == DIST_RADIAL) UB_PF_G2I_ATT(STAGE, DIST_RADIAL);       \
+    else if (S.fp.distortionType == DIST_TRANSVERSE) UB_PF_G2I_ATT(STAGE, DIST_TRANSVERSE); \
+    else UB_PF_G2I(STAGE, -1, -1);                                                        \
+  } while (0)
   if (stage)
-    pfGroundToImageKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
+    UB_PF_G2I_DIST(true);
   else
-    pfGroundToImageKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());
+    UB_PF_G2I_DIST(false);
+#undef UB_PF_G2I_DIST
+#undef UB_PF_G2I_ATT
+#undef UB_PF_G2I
   countLaunch();
   return wc.release();
 }
@@ -554,18 +676,32 @@ cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const d
   bool stage;
   LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
   GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
-#define UB_LAUNCH_PF(STAGE, GRID)                                                         \
-  pfImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(       \
+#define UB_PF_I2G(STAGE, GRID, DIST, ATT)                                                       \
+  pfImageToGroundKernel<STAGE, GRID, DIST, ATT><<<sh.blocks, sh.threads, smemBytes, stream>>>(  \
       S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status)
+#define UB_PF_I2G_ATT(STAGE, GRID, DIST)                \
+  do {                                                  \
+    if (S.hasAttAdj) UB_PF_I2G(STAGE, GRID, DIST, 1);   \
+    else UB_PF_I2G(STAGE, GRID, DIST, 0);               \
+  } while (0)
+#define UB_PF_I2G_DIST(STAGE, GRID)                                                               \
+  do {                                                                                            \
+    if (!pfSpecialise() || S.summedFrameletHeight < 1) UB_PF_I2G(STAGE, GRID, -1, -1);            \
+    else if (S.fp.distortionType == DIST_RADIAL) UB_PF_I2G_ATT(STAGE, GRID, DIST_RADIAL);         \
+    else if (S.fp.distortionType == DIST_TRANSVERSE) UB_PF_I2G_ATT(STAGE, GRID, DIST_TRANSVERSE); \
+    else UB_PF_I2G(STAGE, GRID, -1, -1);                                                          \
+  } while (0)
   if (stage && grid)
-    UB_LAUNCH_PF(true, true);
+    UB_PF_I2G_DIST(true, true);
   else if (stage)
-    UB_LAUNCH_PF(true, false);
+    UB_PF_I2G_DIST(true, false);
   else if (grid)
-    UB_LAUNCH_PF(false, true);
+    UB_PF_I2G_DIST(false, true);
   else
-    UB_LAUNCH_PF(false, false);
-#undef UB_LAUNCH_PF
+    UB_PF_I2G_DIST(false, false);
+#undef UB_PF_I2G_DIST
+#undef UB_PF_I2G_ATT
+#undef UB_PF_I2G
   countLaunch();
   return cudaGetLastError();
 }
