@@ -20,6 +20,14 @@ namespace ub200 {
 namespace {
 
 constexpr int kThreads = 256;
+// resident blocks of 256 threads per SM the register allocation is held to (measured best:
+// profiles/r2_ab_c3_occupancy.txt)
+#ifndef UB_FR_G2I_MINB
+#define UB_FR_G2I_MINB 4
+#endif
+#ifndef UB_FR_I2G_MINB
+#define UB_FR_I2G_MINB 5
+#endif
 
 // removeJitter U:182-213.  Coefficients are in descending power, no constant term.
 UB_DEV void removeJitter(const FrameState &S, double line, double sample, double &dejitteredLine,
@@ -184,7 +192,7 @@ UB_DEV void frGroundToImageChecked(const FrameState &S, double gx, double gy, do
 }
 
 template <int DIST, bool JITTER, int VEC>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, UB_FR_G2I_MINB)
     frGroundToImageKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ x,
                           const double *__restrict__ y, const double *__restrict__ z, double prec,
                           double *__restrict__ line, double *__restrict__ samp,
@@ -224,7 +232,7 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 template <bool GRID, int DIST, bool JITTER, int VEC>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, UB_FR_I2G_MINB)
     frImageToGroundKernel(const __grid_constant__ FrameState S, long n, const double *__restrict__ line,
                           const double *__restrict__ samp, GridSpec g,
                           const double *__restrict__ height, int heightStride,

@@ -23,7 +23,7 @@
 #define UB_PF_G2I_MINB 4
 #endif
 #ifndef UB_PF_I2G_MINB
-#define UB_PF_I2G_MINB 4
+#define UB_PF_I2G_MINB 3
 #endif
 
 namespace ub200 {
@@ -584,7 +584,7 @@ LaunchShape pfShape(const LsState &S, long n, int smCount, size_t &smemBytes, bo
   LaunchShape sh;
   sh.threads = kThreads;
   long blocksNeeded = (n + kThreads - 1) / kThreads;
-  long persistent = (long)smCount * kBlocksPerSm;
+  long persistent = (long)smCount * (UB_PF_G2I_MINB > kBlocksPerSm ? UB_PF_G2I_MINB : kBlocksPerSm);
   sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
   if (sh.blocks < 1) sh.blocks = 1;
   return sh;
