@@ -431,8 +431,18 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    def gather_floats(v):
+        """[v of rank 0, v of rank 1, ...] on every rank"""
+        if world == 1:
+            return [float(v)]
+        t = torch.zeros(world, dtype=torch.float64, device=dev)
+        t[rank] = v
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(x) for x in t.tolist()]
+
     ctx = dict(args=args, rank=rank, world=world, local=local, dev=dev, barrier=barrier,
-               max_over_ranks=max_over_ranks, sum_over_ranks=sum_over_ranks, host=host)
+               max_over_ranks=max_over_ranks, sum_over_ranks=sum_over_ranks, gather_floats=gather_floats,
+               host=host)
     result = run_single(ctx) if world == 1 else run_c5(ctx)
     if rank == 0:
         print(json.dumps(result))
@@ -907,10 +917,12 @@ def link_fraction(h2d_bytes, d2h_bytes, seconds, link):
             "link": link}
 
 
-def e2e_dem_grid(ctx, models, dems, lines, n_job, link, steps=None):
+def e2e_dem_grid(ctx, models, dems, lines, n_job, link, steps=None, bands=None):
     """The metric end to end the way an orthorectifier calls it: a float32 DEM raster in PINNED host
     memory up (4 B/pt), line / samp / status down to pinned host arrays (20 B/pt), ground points
-    generated in the kernel.  One call per image (band)."""
+    generated in the kernel.  One call per image (band).  bands: this job's row bands, one per rank
+    (default: equal); the result carries each rank's own seconds per step (`own_seconds`) so that the
+    caller can size the bands to the rates the ranks' host links sustain."""
     import numpy as np
     import torch
     import ctypes as C
@@ -918,7 +930,7 @@ def e2e_dem_grid(ctx, models, dems, lines, n_job, link, steps=None):
     args, barrier, max_over_ranks = ctx["args"], ctx["barrier"], ctx["max_over_ranks"]
     world, rank = ctx["world"], ctx["rank"]
     from usgscsm_b200 import sharding
-    first, band = sharding.band_for_rank(lines, rank, world)
+    first, band = bands[rank] if bands else sharding.band_for_rank(lines, rank, world)
     nb = band * N_SAMPLES
     host_h = dems[0].samples.cpu().pin_memory()            # the same heights serve every image
     hl = torch.empty(nb, dtype=torch.float64).pin_memory()
@@ -945,12 +957,13 @@ def e2e_dem_grid(ctx, models, dems, lines, n_job, link, steps=None):
     for _ in range(steps):
         call()
     torch.cuda.synchronize()
-    dt = max_over_ranks(time.perf_counter() - t)
+    own = time.perf_counter() - t
+    dt = max_over_ranks(own)
     barrier()
     pts_rank = nb * len(models)
     res = {"value": n_job * steps / dt / 1e6, "unit": "Mpoints/s",
            "h2d_bytes_per_step": 4 * pts_rank, "d2h_bytes_per_step": 20 * pts_rank,
-           "ms_per_step": 1e3 * dt / steps, "steps": steps,
+           "ms_per_step": 1e3 * dt / steps, "steps": steps, "own_seconds": own / steps, "band_lines": band,
            "api": "usgscsm_b200_ground_to_image_dem_grid (host pointers, pinned; float32 DEM raster in, "
                   "line / samp / status out; ground points generated in the kernel)"}
     res.update(link_fraction(4 * pts_rank * steps, 20 * pts_rank * steps, dt, link))
@@ -1053,6 +1066,7 @@ def run_c5(ctx):
     from usgscsm_b200 import _capi, sharding
     args, dev, local, rank, world = ctx["args"], ctx["dev"], ctx["local"], ctx["rank"], ctx["world"]
     barrier, max_over_ranks, sum_over_ranks = ctx["barrier"], ctx["max_over_ranks"], ctx["sum_over_ranks"]
+    gather_floats = ctx["gather_floats"]
     lines, images = args.lines, args.images
     first, band = sharding.band_for_rank(lines, rank, world)
     nb = band * N_SAMPLES                       # points of this rank's band of one image
@@ -1243,8 +1257,23 @@ def run_c5(ctx):
         dem0 = footprint_dem(models[e2e_images[0]], lines, N_SAMPLES, dev)
         full = [dem0] + [ub.Dem(dem0.samples, footprint_grid(models[i], lines, N_SAMPLES, dev))
                          for i in e2e_images[1:]]
-        e = e2e_dem_grid(ctx, [models[i] for i in e2e_images], full, lines,
-                         len(e2e_images) * lines * N_SAMPLES, link, steps=max(1, min(2, args.steps)))
+        e2e_models = [models[i] for i in e2e_images]
+        n_e2e = len(e2e_images) * lines * N_SAMPLES
+        # Row bands sized to what each rank's host link sustains: the ranks of one box share the
+        # host's PCIe complex unevenly (per-rank rates under load are in link_per_rank), and with
+        # equal bands the job waits for the slowest link.  Two passes with the current bands give
+        # each rank's rate; the timed run uses the bands proportional to them.
+        bands = sharding.row_bands(lines, world)
+        history = []
+        for _ in range(2 if world > 1 else 0):
+            probe = e2e_dem_grid(ctx, e2e_models, full, lines, n_e2e, link, steps=1, bands=bands)
+            rates = gather_floats(bands[rank][1] / probe["own_seconds"])
+            history.append({"band_lines": [b for _, b in bands], "value": probe["value"]})
+            bands = sharding.weighted_row_bands(lines, rates)
+        e = e2e_dem_grid(ctx, e2e_models, full, lines, n_e2e, link, steps=max(1, min(2, args.steps)), bands=bands)
+        e["band_lines_by_rank"] = [b for _, b in bands]
+        e["band_sizing_passes"] = history
+        e["link_per_rank"] = {k: gather_floats(v) for k, v in link.items()}
         e["images_per_step"] = len(e2e_images)
         e["link_all_ranks"] = agg
         e["frac_of_box_link"] = max(sum_over_ranks(e["h2d_gbs"]) / agg["h2d_gbs_alone"],

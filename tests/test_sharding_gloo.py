@@ -26,6 +26,27 @@ def test_row_bands_cover_and_balance():
         row_bands(10, 0)
 
 
+def test_weighted_row_bands_cover_and_follow_the_weights():
+    """Bands sized to per-rank rates (the host-pointer path on a box whose ranks share the PCIe
+    complex unevenly): contiguous, covering, proportional, one line at least where possible."""
+    from usgscsm_b200.sharding import row_bands, weighted_row_bands
+    rng = np.random.default_rng(0)
+    for n in (0, 1, 7, 5064, 52224):
+        for w in (1, 2, 3, 8):
+            for weights in ([1.0] * w, list(rng.uniform(0.2, 3.0, w)), [0.0] * w,
+                            [float("nan")] + [2.0] * (w - 1), [1e-9] + [1.0] * (w - 1)):
+                b = weighted_row_bands(n, weights)
+                assert len(b) == w and b[0][0] == 0
+                assert sum(c for _, c in b) == n and all(c >= 0 for _, c in b)
+                assert all(b[i][0] + b[i][1] == b[i + 1][0] for i in range(w - 1))
+                if n >= w:
+                    assert min(c for _, c in b) >= 1
+    assert weighted_row_bands(5064, [1.0] * 8) == row_bands(5064, 8) or \
+        max(abs(a[1] - b[1]) for a, b in zip(weighted_row_bands(5064, [1.0] * 8), row_bands(5064, 8))) <= 1
+    b = weighted_row_bands(6000, [1.0, 2.0, 3.0])
+    assert [c for _, c in b] == [1000, 2000, 3000]
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))

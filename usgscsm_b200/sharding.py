@@ -29,6 +29,31 @@ def band_for_rank(n_lines, rank, world_size):
     return row_bands(n_lines, world_size)[rank]
 
 
+def weighted_row_bands(n_lines, weights):
+    """Contiguous row bands sized in proportion to `weights` (one per rank, e.g. the rate each
+    rank's host link sustained in a warm-up pass): [(first_line, n_lines_in_band)].  For the
+    host-pointer path the ranks of one box share the host's PCIe complex unevenly, and equal
+    bands leave the job waiting for the rank with the slowest link.  Every band keeps at least
+    one line while there are lines to give; non-positive or non-finite weights count as the mean."""
+    world = len(weights)
+    good = [w for w in weights if w == w and w > 0 and w != float("inf")]
+    mean = sum(good) / len(good) if good else 1.0
+    w = [x if (x == x and x > 0 and x != float("inf")) else mean for x in weights]
+    total = sum(w)
+    edges = [0]
+    acc = 0.0
+    for r in range(world):
+        acc += w[r]
+        edges.append(int(round(n_lines * acc / total)))
+    edges[-1] = n_lines
+    # at least one line per band where possible, edges monotone
+    for r in range(1, world + 1):
+        edges[r] = max(edges[r], min(edges[r - 1] + 1, n_lines))
+    for r in range(world - 1, 0, -1):
+        edges[r] = min(edges[r], max(edges[r + 1] - 1, 0)) if n_lines >= world else edges[r]
+    return [(edges[r], edges[r + 1] - edges[r]) for r in range(world)]
+
+
 def chunk_for_rank(n_points, rank, world_size):
     """(offset, count) of this rank's contiguous chunk of an n_points list."""
     return row_bands(n_points, world_size)[rank]
