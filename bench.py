@@ -1035,7 +1035,9 @@ def e2e_pageable(model, x, y, z, m):
     import numpy as np
     from usgscsm_b200 import _capi
     hx, hy, hz = (t[:m].cpu().numpy().copy() for t in (x, y, z))
-    ol, os_, ost = np.zeros(m), np.zeros(m), np.zeros(m, dtype=np.uint32)   # touched: no page faults when timed
+    # written once before the timed call: numpy.zeros hands out untouched (calloc) pages and
+    # their first-touch faults would be timed with the call
+    ol, os_, ost = np.full(m, -1.0), np.full(m, -1.0), np.full(m, 7, dtype=np.uint32)
 
     def call(n):
         _capi.check(_capi.lib.usgscsm_b200_ground_to_image(
