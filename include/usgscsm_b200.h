@@ -439,6 +439,24 @@ USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m
                                           double *z, double *achieved, uint32_t *status,
                                           void *stream);
 
+/* usgscsm_b200_image_to_ground_grid_dev for callers that may not allocate device memory (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  This entry
+ * point has no counterpart in the reference.
+ * Same arguments, same results (the same two kernels); line-scan models only
+ * (USGSCSM_B200_EUNSUPPORTED otherwise: the other models' grid kernels use no scratch).  The
+ * per-row / per-column tables go to a file-scope device array of 2 Mi doubles = 16 MiB, which
+ * every GPU that loads the library holds until the process exits; a grid fits when
+ * n_lines * 21 + n_samps * 4 <= 2097152 (config C2's 52224 x 5064 does), anything larger is
+ * rejected with USGSCSM_B200_EINVAL.  The call makes no cudaMalloc / cudaFree / stream-ordered
+ * allocation.  All calls share the one array per GPU, and it keeps the last call's tables
+ * (every entry a call reads is rewritten by that call first): calls whose kernels overlap on
+ * one GPU -- different streams or host threads -- race; order them on one stream. */
+#define USGSCSM_B200_STATIC_GRID_SCRATCH_DOUBLES 2097152
+USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid_static_dev(
+    usgscsm_b200_model *m, double line0, double samp0, double dline, double dsamp, int64_t n_lines,
+    int64_t n_samps, const double *height, int height_stride, double prec, double *x, double *y,
+    double *z, double *achieved, uint32_t *status, void *stream);
+
 /* The same with HOST arrays: heights up (one double when height_stride = 0), ground points
  * down, chunked by whole rows through the copy pipeline. */
 USGSCSM_B200_API int usgscsm_b200_image_to_ground_grid(usgscsm_b200_model *m, double line0, double samp0,

@@ -162,6 +162,9 @@ SIGNATURES = {
     "usgscsm_b200_image_to_ground_grid": (
         C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
                   C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp]),
+    "usgscsm_b200_image_to_ground_grid_static_dev": (
+        C.c_int, [_h, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int64, _dp,
+                  C.c_int, C.c_double, _dp, _dp, _dp, _dp, _dp, _dp]),
     "usgscsm_b200_geogrid_from_proj_string": (
         C.c_int, [C.c_char_p, C.POINTER(C.c_double), C.c_double, C.c_double, _gp]),
     "usgscsm_b200_geogrid_image_to_ground": (

@@ -475,6 +475,37 @@ int usgscsm_b200_image_to_ground_grid_dev(usgscsm_b200_model *m, double line0, d
   });
 }
 
+// The dense-grid imageToGround of the line-scan model without any allocation: the row / column
+// tables go to a file-scope device array (ls_kernels.cu) instead of stream-ordered scratch.
+int usgscsm_b200_image_to_ground_grid_static_dev(usgscsm_b200_model *m, double line0, double samp0,
+                                                 double dline, double dsamp, int64_t n_lines,
+                                                 int64_t n_samps, const double *height,
+                                                 int height_stride, double prec, double *x, double *y,
+                                                 double *z, double *achieved, uint32_t *status,
+                                                 void *stream) {
+  if (!m || n_lines < 0 || n_samps < 0) return fail(USGSCSM_B200_EINVAL, "bad argument");
+  if (m->kind != USGSCSM_B200_MODEL_LINE_SCANNER)
+    return fail(USGSCSM_B200_EUNSUPPORTED,
+                "usgscsm_b200_image_to_ground_grid_static_dev: line-scan models only (the other "
+                "models' dense-grid kernels use no scratch: usgscsm_b200_image_to_ground_grid_dev "
+                "allocates nothing for them)");
+  if (n_lines == 0 || n_samps == 0) return USGSCSM_B200_OK;
+  if (!height || !x || !y || !z) return fail(USGSCSM_B200_EINVAL, "null array");
+  if (!staticGridScratchFits((long)n_lines, (long)n_samps))
+    return fail(USGSCSM_B200_EINVAL,
+                "usgscsm_b200_image_to_ground_grid_static_dev: grid too large for the static scratch "
+                "(n_lines * 21 + n_samps * 4 must not exceed 2097152 doubles = 16 MiB); use "
+                "usgscsm_b200_image_to_ground_grid_dev or split the grid into row bands");
+  return guarded([&]() -> int {
+    UB_CUDA(cudaSetDevice(m->device));
+    GridSpec g{line0, samp0, dline, dsamp, (long)n_samps, 0};
+    UB_CUDA(launchLsImageToGroundGridStatic(m->ls, m->smCount, g, (long)n_lines, height,
+                                            height_stride ? 1 : 0, prec, x, y, z, achieved, status,
+                                            static_cast<cudaStream_t>(stream)));
+    return USGSCSM_B200_OK;
+  });
+}
+
 }  // extern "C"
 
 // ---- many small images per call ------------------------------------------------------------------

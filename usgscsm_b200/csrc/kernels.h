@@ -132,6 +132,16 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
                                   int heightStride, double prec, double *x, double *y, double *z,
                                   double *achieved, uint32_t *status, cudaStream_t stream);
 
+// Dense-grid imageToGround with its row / column tables in a file-scope device array instead of
+// stream-ordered scratch: no allocation of any kind (usgscsm_b200_image_to_ground_grid_static_dev).
+// 2 Mi doubles = 16 MiB per GPU; a grid fits when rows * 21 + columns * 4 <= that.
+constexpr long kStaticGridScratchDoubles = 1L << 21;
+bool staticGridScratchFits(long nRows, long nCols);
+cudaError_t launchLsImageToGroundGridStatic(const LsState &S, int smCount, const GridSpec &grid, long nRows,
+                                            const double *height, int heightStride, double prec,
+                                            double *x, double *y, double *z, double *achieved,
+                                            uint32_t *status, cudaStream_t stream);
+
 // computeAllSensorPartials of the line-scan model in one kernel (ls_all_partials.cu); false: not
 // applicable, run the per-parameter launches
 bool launchLsAllSensorPartials(const LsState &S, int smCount, int nIndices, const int *indices, long n,

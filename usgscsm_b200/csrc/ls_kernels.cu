@@ -10,6 +10,7 @@
 // grid is persistent (a multiple of the SM count, grid-stride over points) so that the
 // staging cost is paid once per resident block, not once per 256 points.
 #include <cstdlib>
+#include <mutex>
 #include <type_traits>
 
 #include "geo_device.cuh"
@@ -757,6 +758,70 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
     UB_LAUNCH_I2G(false, false);
 #undef UB_LAUNCH_I2G
 #undef UB_LAUNCH_I2G_M
+  countLaunch();
+  return cudaGetLastError();
+}
+
+// ---- dense-grid imageToGround without any allocation ----------------------------------------
+// The row / column tables of launchLsImageToGround's dense-grid path live in stream-ordered
+// scratch (cudaMallocAsync).  Callers that may not allocate (CUDA graph capture, serving loops)
+// get the same two kernels over a file-scope array instead: every GPU that loads the library
+// holds kStaticGridScratchDoubles * 8 bytes (16 MiB) until the process exits.  Every call shares
+// the array and it keeps the last call's tables; lsGridTablesKernel writes every entry the
+// per-pixel kernel reads (all rows, all columns of THIS call), so nothing has to start at zero.
+// Two calls whose kernels overlap on one GPU (different streams, different host threads) race.
+static __device__ __align__(256) double gStaticGridScratch[kStaticGridScratchDoubles];
+
+// In host code the array's name is a stand-in, not a device address: the address is asked for
+// once per device, with that device current.
+static cudaError_t staticGridScratch(double **ptr) {
+  constexpr int kMaxDevices = 64;
+  static double *perDevice[kMaxDevices] = {};
+  static std::mutex mu;
+  int device = -1;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess) return e;
+  if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!perDevice[device]) {
+    double *p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), gStaticGridScratch);
+    if (e != cudaSuccess) return e;
+    if (!p) return cudaErrorInvalidSymbol;
+    perDevice[device] = p;
+  }
+  *ptr = perDevice[device];
+  return cudaSuccess;
+}
+
+// The caller has checked nRows * kRowDoubles + nCols * kColDoubles <= kStaticGridScratchDoubles
+// (staticGridScratchFits) and made the model's device current.
+bool staticGridScratchFits(long nRows, long nCols) {
+  return nRows >= 0 && nCols >= 0 && nRows <= kStaticGridScratchDoubles && nCols <= kStaticGridScratchDoubles &&
+         nRows * kRowDoubles + nCols * kColDoubles <= (long)kStaticGridScratchDoubles;
+}
+
+cudaError_t launchLsImageToGroundGridStatic(const LsState &S, int smCount, const GridSpec &grid, long nRows,
+                                            const double *height, int heightStride, double prec,
+                                            double *x, double *y, double *z, double *achieved,
+                                            uint32_t *status, cudaStream_t stream) {
+  const long nCols = grid.nSamps, n = nRows * nCols;
+  if (n <= 0) return cudaSuccess;
+  if (!staticGridScratchFits(nRows, nCols)) return cudaErrorInvalidValue;
+  double *scratch = nullptr;
+  cudaError_t e = staticGridScratch(&scratch);
+  if (e != cudaSuccess) return e;
+  double *rowTab = scratch, *colTab = scratch + nRows * kRowDoubles;
+  const long items = nRows + nCols;
+  lsGridTablesKernel<<<(unsigned)((items + 127) / 128), 128, 0, stream>>>(S, grid, nRows, nCols, rowTab, colTab);
+  countLaunch();
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const long blocksNeeded = (n + kThreads - 1) / kThreads;
+  const long persistent = (long)smCount * 4;
+  const int blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
+  lsImageToGroundGridKernel<4><<<blocks, kThreads, 0, stream>>>(S, n, nCols, rowTab, colTab, height, heightStride,
+                                                               prec, x, y, z, achieved, status);
   countLaunch();
   return cudaGetLastError();
 }
