@@ -69,6 +69,9 @@ CASES = {
     "lunarorbiter": dict(distortion_type=6, dist_coeffs=(0.0,)),
     "radtan": dict(distortion_type=7, dist_coeffs=(1e-3, -2e-4, 1e-4, -1e-4, 1e-5)),
     "kplo": dict(distortion_type=8, dist_coeffs=(1.81e-5,)),
+    # LRO NAC coefficients outside |k1| <= 1e-4: the forward iteration keeps its divergence test
+    "lro_strong": dict(distortion_type=4, dist_coeffs=(3.0e-4,)),
+    "lro_negative": dict(distortion_type=4, dist_coeffs=(-2.5e-4,)),
     "platform0": dict(platform_flag=0),
     # HiRISE-like attitude sampling: 4 x 41 k quaternion doubles = 1.3 MB, not staged into shared
     # memory (kMaxStagedTableBytes) -- the kernels read the tables through L1/L2
