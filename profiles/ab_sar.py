@@ -1,4 +1,4 @@
-"""A/B of the SAR groundToImage kernel variants (USGSCSM_B200_SAR_REFILL / _PAD / _MINB) on the
+"""A/B of the SAR groundToImage kernel variants (USGSCSM_B200_SAR_REFILL / _PAD / _MINB / _INTERLEAVE) on the
 C4 workload (unordered random ground points, 0.1 % without a Doppler bracket) and on an ordered
 dense grid.  Each setting in its own process."""
 import itertools
@@ -40,7 +40,12 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
         res.append("%s %.0f Mpt/s (%.1f ms, round trip %.2g px)" % (name, n / ms / 1e3, ms, err))
     print("  ".join(res), flush=True)
 else:
-    for refill, pad, minb in itertools.product("01", "01", "32"):
-        env = dict(os.environ, USGSCSM_B200_SAR_REFILL=refill, USGSCSM_B200_SAR_PAD=pad, USGSCSM_B200_SAR_MINB=minb)
-        print("refill %s pad %s minb %s:" % (refill, pad, minb), end=" ", flush=True)
+    # "quick": only the table layouts of the lockstep kernel
+    quick = len(sys.argv) > 1 and sys.argv[1] == "quick"
+    for refill, pad, minb, inter in itertools.product("0" if quick else "01", "01", "32", "10"):
+        if pad == "1" and inter == "1":
+            continue
+        env = dict(os.environ, USGSCSM_B200_SAR_REFILL=refill, USGSCSM_B200_SAR_PAD=pad, USGSCSM_B200_SAR_MINB=minb,
+                   USGSCSM_B200_SAR_INTERLEAVE=inter)
+        print("refill %s pad %s minb %s interleave %s:" % (refill, pad, minb, inter), end=" ", flush=True)
         subprocess.run([sys.executable, __file__, "child"], env=env)

@@ -30,14 +30,23 @@ constexpr size_t kSarMaxStagedBytes = 100 * 1024;  // 2 resident blocks per SM
 // or the block's copy in shared memory, rows padded to 4 doubles on 16-byte boundaries so that a
 // node is two 128-bit loads (unordered points make every lane read its own nodes: fewer, wider
 // shared-memory transactions).
-template <bool PAD>
+// LAYOUT 0: rows of 3 doubles (the device arrays, or a plain copy in shared memory); 1: the
+// padded copy; 2: positions and velocities INTERLEAVED in shared memory, one row of 6 doubles
+// (px, py, pz, vx, vy, vz) per node on a 16-byte boundary -- the Doppler function needs both
+// vectors at the same 8 nodes, and three 128-bit loads per node instead of six 64-bit ones halve
+// the shared-memory instructions of unordered points (every lane reads its own nodes, so the
+// search is bound by shared-memory wavefronts, not arithmetic).  `positions` then points at the
+// interleaved table and `velocities` is unused.
+constexpr int kSarPlain = 0, kSarPadded = 1, kSarInterleaved = 2;
+template <int LAYOUT>
 struct SarTablesT {
-  static constexpr bool kPadded = PAD;
+  static constexpr bool kPadded = LAYOUT == kSarPadded;
+  static constexpr bool kInterleaved = LAYOUT == kSarInterleaved;
   const double *positions;
   const double *velocities;
   const double *scale;
 };
-using SarTables = SarTablesT<false>;
+using SarTables = SarTablesT<kSarPlain>;
 
 template <class TAB>
 UB_DEV void sarApply3(const TAB &, const double *table, const LagrangeWeights &w, double out[3]) {
@@ -46,23 +55,36 @@ UB_DEV void sarApply3(const TAB &, const double *table, const LagrangeWeights &w
   else
     lagrangeApply<3>(table, w, out);
 }
-__host__ __device__ inline size_t sarTableBytes(const SarState &S, bool pad = false) {
-  const size_t row = pad ? 4 : 3;
+// (the interleaved layout takes the same room as the plain one: 6 doubles per node)
+__host__ __device__ inline size_t sarTableBytes(const SarState &S, int layout = kSarPlain) {
+  const size_t row = layout == kSarPadded ? 4 : 3;
   return ((size_t)S.positions.numNodes * row + (size_t)S.velocities.numNodes * row +
           (size_t)S.scale.numNodes * 4) *
          sizeof(double);
 }
 
-// STAGE: copy the tables into `smem`; PAD: rows of 4 doubles there.
-template <bool STAGE, bool PAD = false>
-__device__ inline SarTablesT<STAGE && PAD> stageSarTables(const SarState &S, double *smem) {
-  SarTablesT<STAGE && PAD> t{S.positions.values, S.velocities.values, S.scale.values};
+// the interleaved layout needs the two tables on the same nodes (they share t0 / dt in the state)
+__host__ __device__ inline bool sarInterleavable(const SarState &S) {
+  return S.positions.numNodes > 1 && S.positions.numNodes == S.velocities.numNodes;
+}
+
+// STAGE: copy the tables into `smem` in layout LAYOUT (the launcher has checked
+// sarInterleavable for layout 2).
+template <bool STAGE, int LAYOUT = kSarPlain>
+__device__ inline SarTablesT<STAGE ? LAYOUT : kSarPlain> stageSarTables(const SarState &S, double *smem) {
+  SarTablesT<STAGE ? LAYOUT : kSarPlain> t{S.positions.values, S.velocities.values, S.scale.values};
   if (!STAGE) return t;
+  constexpr bool PAD = LAYOUT == kSarPadded;
   constexpr int ROW = PAD ? 4 : 3;
   const int np = S.positions.numNodes * ROW, nv = S.velocities.numNodes * ROW,
             ns = S.scale.numNodes * 4;
   double *sp = smem, *sv = sp + np, *ss = sv + nv;
-  if (PAD) {
+  if (LAYOUT == kSarInterleaved) {
+    for (int i = threadIdx.x; i < np + nv; i += blockDim.x) {
+      const int node = i / 6, j = i - node * 6;
+      sp[i] = j < 3 ? __ldg(S.positions.values + 3 * node + j) : __ldg(S.velocities.values + 3 * node + j - 3);
+    }
+  } else if (PAD) {
     for (int i = threadIdx.x; i < np; i += blockDim.x)
       sp[i] = (i & 3) < 3 ? __ldg(S.positions.values + 3 * (i >> 2) + (i & 3)) : 0.0;
     for (int i = threadIdx.x; i < nv; i += blockDim.x)
@@ -86,6 +108,18 @@ template <class TAB>
 UB_DEV void sarPosVel(const SarState &S, const TAB &T, double time, double pos[3],
                       double vel[3]) {
   LagrangeWeights w;
+  if (TAB::kInterleaved) {
+    lagrangeWeights(S.positions, S.lag, time, w);
+    double pv[6];
+    lagrangeApplyInterleaved6(T.positions, w, pv);
+    pos[0] = pv[0] + S.params[0];
+    pos[1] = pv[1] + S.params[1];
+    pos[2] = pv[2] + S.params[2];
+    vel[0] = pv[3] + S.params[3];
+    vel[1] = pv[4] + S.params[4];
+    vel[2] = pv[5] + S.params[5];
+    return;
+  }
   bool haveW = false;
   if (S.positions.numNodes > 1) {
     lagrangeWeights(S.positions, S.lag, time, w);
@@ -272,7 +306,7 @@ struct SarWarpQueue {
   uint32_t status[kSarQueue];  // status bits and the evaluation count; bit 31: no bracket
 };
 
-template <bool STAGE, bool PAD, int MINB>
+template <bool STAGE, int LAYOUT, int MINB>
 __global__ void __launch_bounds__(kThreads, MINB)
     sarGroundToImageRefillKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z, double prec,
@@ -282,8 +316,8 @@ __global__ void __launch_bounds__(kThreads, MINB)
   extern __shared__ __align__(16) double smem[];
   SarWarpQueue *queues = reinterpret_cast<SarWarpQueue *>(smem);
   SarWarpQueue &wq = queues[threadIdx.x >> 5];
-  const SarTablesT<STAGE && PAD> T =
-      stageSarTables<STAGE, PAD>(S, smem + (kThreads / 32) * sizeof(SarWarpQueue) / sizeof(double));
+  const SarTablesT<STAGE ? LAYOUT : kSarPlain> T =
+      stageSarTables<STAGE, LAYOUT>(S, smem + (kThreads / 32) * sizeof(SarWarpQueue) / sizeof(double));
   const unsigned lane = threadIdx.x & 31u;
   const unsigned below = (1u << lane) - 1u;
   const double timeTolerance = S.exposureDuration * prec / 2.0;
@@ -385,7 +419,7 @@ __global__ void __launch_bounds__(kThreads, MINB)
 // The plain form: a warp takes 32 points and runs their searches in lockstep.  Best when
 // neighbouring points need the same number of evaluations (dense grids: 30.4 of 32 lanes active
 // on average) -- and with the fewest registers.
-template <bool STAGE, bool PAD, int MINB>
+template <bool STAGE, int LAYOUT, int MINB>
 __global__ void __launch_bounds__(kThreads, MINB)
     sarGroundToImageKernel(const __grid_constant__ SarState S, long n, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z, double prec,
@@ -393,7 +427,7 @@ __global__ void __launch_bounds__(kThreads, MINB)
                            double *__restrict__ achieved, uint32_t *__restrict__ status,
                            unsigned long long *__restrict__ next, int grab) {
   extern __shared__ __align__(16) double smem[];
-  const SarTablesT<STAGE && PAD> T = stageSarTables<STAGE, PAD>(S, smem);
+  const SarTablesT<STAGE ? LAYOUT : kSarPlain> T = stageSarTables<STAGE, LAYOUT>(S, smem);
   forEachPointDynamic(n, next, grab, [&](long i) {
     double gx = __ldcs(x + i), gy = __ldcs(y + i), gz = __ldcs(z + i);
     double l, s;
@@ -549,8 +583,8 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 LaunchShape sarShape(const SarState &S, long n, int smCount, size_t &smemBytes, bool &stage,
-                     size_t extraSmem = 0, int maxPerSm = kBlocksPerSm, bool pad = false) {
-  size_t bytes = sarTableBytes(S, pad);
+                     size_t extraSmem = 0, int maxPerSm = kBlocksPerSm, int layout = kSarPlain) {
+  size_t bytes = sarTableBytes(S, layout);
   stage = bytes <= kSarMaxStagedBytes;
   smemBytes = (stage ? bytes : 0) + extraSmem;
   int perSm = maxPerSm;
@@ -622,9 +656,12 @@ cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const
   // of 4 doubles; USGSCSM_B200_SAR_MINB: register budget as resident blocks per SM (2 or 3)
   static const int refill = sarEnv("USGSCSM_B200_SAR_REFILL", 0);
   static const int pad = sarEnv("USGSCSM_B200_SAR_PAD", 0);
+  // USGSCSM_B200_SAR_INTERLEAVE=0: positions and velocities as two tables (rows of 3 doubles)
+  static const int interleave = sarEnv("USGSCSM_B200_SAR_INTERLEAVE", 1);
+  const int layout = pad ? kSarPadded : (interleave && sarInterleavable(S) ? kSarInterleaved : kSarPlain);
   static const int minb = sarEnv("USGSCSM_B200_SAR_MINB", 3);
   const size_t queueBytes = refill ? (kThreads / 32) * sizeof(SarWarpQueue) : 0;
-  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage, queueBytes, minb >= 3 ? 3 : 2, pad != 0);
+  LaunchShape sh = sarShape(S, n, smCount, smemBytes, stage, queueBytes, minb >= 3 ? 3 : 2, layout);
   WorkCounter wc;
   cudaError_t e = cudaSuccess;
 #define UB_SAR_G2I(KERNEL, STAGE, PAD, MINB)                                                      \
@@ -640,11 +677,12 @@ cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const
     if (minb >= 3) UB_SAR_G2I(KERNEL, STAGE, PAD, 3); \
     else UB_SAR_G2I(KERNEL, STAGE, PAD, 2);         \
   } while (0)
-#define UB_SAR_G2I_K(KERNEL)                                   \
-  do {                                                         \
-    if (stage && pad) UB_SAR_G2I_M(KERNEL, true, true);        \
-    else if (stage) UB_SAR_G2I_M(KERNEL, true, false);         \
-    else UB_SAR_G2I_M(KERNEL, false, false);                   \
+#define UB_SAR_G2I_K(KERNEL)                                                        \
+  do {                                                                              \
+    if (stage && layout == kSarPadded) UB_SAR_G2I_M(KERNEL, true, kSarPadded);      \
+    else if (stage && layout == kSarInterleaved) UB_SAR_G2I_M(KERNEL, true, kSarInterleaved); \
+    else if (stage) UB_SAR_G2I_M(KERNEL, true, kSarPlain);                          \
+    else UB_SAR_G2I_M(KERNEL, false, kSarPlain);                                    \
   } while (0)
   if (refill)
     UB_SAR_G2I_K(sarGroundToImageRefillKernel);
