@@ -43,7 +43,8 @@ def test_grid_chunks_compute_the_same_lines():
 
 
 @pytest.mark.parametrize("env", [dict(USGSCSM_B200_SAR_REFILL=1), dict(USGSCSM_B200_SAR_REFILL=1, USGSCSM_B200_SAR_PAD=1),
-                                 dict(USGSCSM_B200_SAR_PAD=1, USGSCSM_B200_SAR_MINB=2)])
+                                 dict(USGSCSM_B200_SAR_PAD=1, USGSCSM_B200_SAR_MINB=2),
+                                 dict(USGSCSM_B200_SAR_INTERLEAVE=0), dict(USGSCSM_B200_SAR_INTERLEAVE=0, USGSCSM_B200_SAR_MINB=2)])
 def test_sar_kernel_variants_same_bits(env):
     """Lane-refill / padded-table variants of SAR groundToImage against the
     default kernel's output saved by the first run."""
