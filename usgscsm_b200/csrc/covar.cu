@@ -23,6 +23,7 @@ constexpr long kCovarBatch = 1L << 22;  // points per internal pass (bounds the 
 
 struct ParamCov {
   int numParams;
+  uint32_t nonzero[kMaxParams * kMaxParams / 32];  // bit k: c[k] is not zero (a NaN entry counts as set)
   double c[kMaxParams * kMaxParams];  // getParameterCovariance(i, j) = c[i * numParams + j]
 };
 
@@ -45,6 +46,52 @@ __device__ inline void sensorCovariance(const ParamCov &C, const double *__restr
       s[3] += si * cij * sj;
     }
   }
+}
+
+// The same sums for a parameter count known at compile time: the point's 2 P partials are loaded
+// once (128-bit loads) and stay in registers, the covariance entries are constant-bank operands,
+// and the terms of entries that are exactly zero are skipped when every partial of the point is
+// finite -- such a term is li * 0 * lj = +-0, and adding +-0 leaves a sum that started at +0
+// unchanged, so the result has the same bits (with a non-finite partial the term is NaN and
+// nothing is skipped).  A model straight from an ISD has a diagonal covariance: 16 terms of 256.
+template <int P>
+__device__ inline void sensorCovarianceFixed(const ParamCov &C, const double *__restrict__ spPoint,
+                                             double s[4]) {
+  double sp[2 * P];
+  const double2 *q = reinterpret_cast<const double2 *>(spPoint);
+  bool finite = true;
+#pragma unroll
+  for (int k = 0; k < P; k++) {
+    const double2 v = __ldg(q + k);
+    sp[2 * k] = v.x;
+    sp[2 * k + 1] = v.y;
+    finite = finite && isfinite(v.x) && isfinite(v.y);
+  }
+  s[0] = s[1] = s[2] = s[3] = 0.0;
+#pragma unroll
+  for (int i = 0; i < P; i++) {
+#pragma unroll
+    for (int j = 0; j < P; j++) {
+      const int k = i * P + j;
+      if (finite && !((C.nonzero[k >> 5] >> (k & 31)) & 1u)) continue;
+      const double cij = C.c[k];
+      s[0] += sp[2 * i] * cij * sp[2 * j];
+      s[1] += sp[2 * i + 1] * cij * sp[2 * j];
+      s[2] += sp[2 * i] * cij * sp[2 * j + 1];
+      s[3] += sp[2 * i + 1] * cij * sp[2 * j + 1];
+    }
+  }
+}
+
+__device__ inline void sensorCovarianceOf(const ParamCov &C, const double *__restrict__ spAll, long i,
+                                          double s[4]) {
+  const double *sp = spAll + i * 2 * C.numParams;
+  if (C.numParams == 16)
+    sensorCovarianceFixed<16>(C, sp, s);
+  else if (C.numParams == 6)
+    sensorCovarianceFixed<6>(C, sp, s);
+  else
+    sensorCovariance(C, sp, s);
 }
 
 // LS:930-961
@@ -74,7 +121,7 @@ __global__ void groundToImageCovarKernel(long n, const __grid_constant__ ParamCo
     g[2] = stx * prt[0] + sty * prt[1] + stz * prt[2];
     g[3] = stx * prt[3] + sty * prt[4] + stz * prt[5];
     double s[4];
-    sensorCovariance(C, spAll + i * 2 * C.numParams, s);
+    sensorCovarianceOf(C, spAll, i, s);
     uint32_t st = status[i];
     const uint32_t err = (st | stPartials[i] | stSensor[i]) & kErrBits;
     bool finite = true;
@@ -133,7 +180,7 @@ __global__ void imageToGroundCovarKernel(long n, const __grid_constant__ ParamCo
     const double xph = (gh[i] - gx) / deltaGround, yph = (gh[ld + i] - gy) / deltaGround,
                  zph = (gh[2 * ld + i] - gz) / deltaGround;
     double s[4], ic[4];
-    sensorCovariance(C, spAll + i * 2 * C.numParams, s);
+    sensorCovarianceOf(C, spAll, i, s);
     for (int k = 0; k < 4; k++) ic[k] = imageCovIn[i * 4 + k] + s[k] + 0.0;
     const double hv = heightVar[i * hvStride];
     const double t00 = xpl * ic[0] + xps * ic[2], t01 = xpl * ic[1] + xps * ic[3], t02 = xph * hv;
@@ -174,7 +221,10 @@ ParamCov paramCov(const usgscsm_b200_model *m) {
   if (C.numParams > kMaxParams ||
       m->covariance.size() != (size_t)C.numParams * (size_t)C.numParams)
     throw std::invalid_argument("m_covariance does not hold numParameters x numParameters entries");
-  for (size_t k = 0; k < m->covariance.size(); k++) C.c[k] = m->covariance[k];
+  for (size_t k = 0; k < m->covariance.size(); k++) {
+    C.c[k] = m->covariance[k];
+    if (!(C.c[k] == 0.0)) C.nonzero[k >> 5] |= 1u << (k & 31);  // NaN: set
+  }
   return C;
 }
 
