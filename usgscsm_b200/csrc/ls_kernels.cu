@@ -319,9 +319,15 @@ __global__ void __launch_bounds__(kThreads, MINB)
   // the height is the one input that comes from DRAM: the next pass's is requested before this
   // pass's arithmetic starts (ncu: long-scoreboard stalls 3.1 per issue without it)
   double hNext = (i < n) ? (heightStride ? __ldcs(height + i) : __ldg(height)) : 0.0;
-  for (; i < n; i += stride) {
-    long r = i / nSamps;
-    long c = i - r * nSamps;
+  // (row, column) of the thread's pixel, advanced by the stride's (rows, columns) instead of a
+  // 64-bit division per pixel
+  long r = i / nSamps, c = i - r * nSamps;
+  const long strideRows = stride / nSamps, strideCols = stride - strideRows * nSamps;
+  for (; i < n; i += stride, r += strideRows, c += strideCols) {
+    if (c >= nSamps) {
+      c -= nSamps;
+      r++;
+    }
     const double *re = rowTab + r * kRowDoubles;
     const double *ce = colTab + c * kColDoubles;
     const double h = hNext;
