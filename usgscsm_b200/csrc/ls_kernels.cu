@@ -9,7 +9,9 @@
 // attitude tables are staged once per block into shared memory when they fit, and the
 // grid is persistent (a multiple of the SM count, grid-stride over points) so that the
 // staging cost is paid once per resident block, not once per 256 points.
+#include <cstdint>
 #include <cstdlib>
+#include <initializer_list>
 #include <mutex>
 #include <type_traits>
 
@@ -307,6 +309,8 @@ __global__ void lsGridTablesKernel(const __grid_constant__ LsState S, GridSpec g
   }
 }
 
+// (Two pixels per thread with 128-bit accesses -- what pays in the frame kernels -- measured
+// 74.3 against 73.9 Gpt/s here at its best register budget: not kept.)
 template <int MINB>
 __global__ void __launch_bounds__(kThreads, MINB)
     lsImageToGroundGridKernel(const __grid_constant__ LsState S, long n, long nSamps,
@@ -329,11 +333,12 @@ __global__ void __launch_bounds__(kThreads, MINB)
       r++;
     }
     const double *re = rowTab + r * kRowDoubles;
-    const double *ce = colTab + c * kColDoubles;
+    const double2 *ce = reinterpret_cast<const double2 *>(colTab + c * kColDoubles);  // 16-byte aligned
     const double h = hNext;
     if (heightStride && i + stride < n) hNext = __ldcs(height + i + stride);
-    double cameraLook[3] = {__ldg(ce), __ldg(ce + 1), __ldg(ce + 2)};
-    uint32_t st = (uint32_t)__ldg(ce + 3);
+    const double2 c01 = __ldg(ce), c23 = __ldg(ce + 1);
+    double cameraLook[3] = {c01.x, c01.y, c23.x};
+    uint32_t st = (uint32_t)c23.y;
     double pos[3] = {__ldg(re), __ldg(re + 1), __ldg(re + 2)};
     double m[9];
 #pragma unroll
@@ -711,21 +716,23 @@ cudaError_t launchLsImageToGround(const LsState &S, int smCount, long n, const d
     double *scratch = nullptr;
     cudaError_t e = cudaMallocAsync(&scratch, (nRows * kRowDoubles + nCols * kColDoubles) * sizeof(double), stream);
     if (e != cudaSuccess) return e;
-    double *rowTab = scratch, *colTab = scratch + nRows * kRowDoubles;
+    // column entries first: they are read with 128-bit loads and need the 16-byte boundary
+    double *colTab = scratch, *rowTab = scratch + nCols * kColDoubles;
     long items = nRows + nCols;
     lsGridTablesKernel<<<(unsigned)((items + 127) / 128), 128, 0, stream>>>(S, *grid, nRows, nCols, rowTab, colTab);
     countLaunch();
     // register budget of the per-pixel kernel: resident blocks of 256 threads per SM
     // (USGSCSM_B200_LS_GRID_MINB; the default is the measured best on B200)
     static const int gridMinb = envInt("USGSCSM_B200_LS_GRID_MINB", 4);
-    const int mb = gridMinb < 3 ? 3 : (gridMinb > 6 ? 6 : gridMinb);
+    const int mb = gridMinb < 2 ? 2 : (gridMinb > 6 ? 6 : gridMinb);
     long blocksNeeded = (n + kThreads - 1) / kThreads;
-    long persistent = (long)smCount * mb;
+    const long persistent = (long)smCount * mb;
     int blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
 #define UB_LAUNCH_GRID(MB)                                                                       \
   lsImageToGroundGridKernel<MB><<<blocks, kThreads, 0, stream>>>(S, n, nCols, rowTab, colTab, height, \
                                                                  heightStride, prec, x, y, z, achieved, status)
-    if (mb == 3) UB_LAUNCH_GRID(3);
+    if (mb == 2) UB_LAUNCH_GRID(2);
+    else if (mb == 3) UB_LAUNCH_GRID(3);
     else if (mb == 4) UB_LAUNCH_GRID(4);
     else if (mb == 5) UB_LAUNCH_GRID(5);
     else UB_LAUNCH_GRID(6);
@@ -817,7 +824,7 @@ cudaError_t launchLsImageToGroundGridStatic(const LsState &S, int smCount, const
   double *scratch = nullptr;
   cudaError_t e = staticGridScratch(&scratch);
   if (e != cudaSuccess) return e;
-  double *rowTab = scratch, *colTab = scratch + nRows * kRowDoubles;
+  double *colTab = scratch, *rowTab = scratch + nCols * kColDoubles;  // 128-bit loads of column entries
   const long items = nRows + nCols;
   lsGridTablesKernel<<<(unsigned)((items + 127) / 128), 128, 0, stream>>>(S, grid, nRows, nCols, rowTab, colTab);
   countLaunch();
