@@ -66,6 +66,7 @@ UB_DEV void computeOrientation(const LsState &S, const OrientationTables &T, dou
 struct OrientCache {
   const double *entries;  // entry k + 1 <-> time framelet number k; null = no cache
   int stride;             // doubles per entry in `entries`
+  bool pairs;             // entries of 12 doubles on 16-byte boundaries (the staged copy): 128-bit loads
 };
 
 // ATT: -1 = S.hasAttAdj decides at run time, 0 / 1 = the launcher knows (compile-time variant).
@@ -76,6 +77,15 @@ UB_DEV bool pfHasAttAdj(const LsState &S) { return ATT < 0 ? S.hasAttAdj != 0 : 
 template <int ATT>
 UB_DEV void orientationFromTable(const LsState &S, const OrientCache &C, int frameletNumber,
                                  Orientation &o) {
+  if (ATT == 0 && C.pairs) {
+    const double2 *q = reinterpret_cast<const double2 *>(C.entries + (long)(frameletNumber + 1) * 12);
+    const double2 a = q[0], b = q[1], c = q[2], d = q[3], f = q[4], g = q[5];
+    o.pos[0] = a.x, o.pos[1] = a.y, o.pos[2] = b.x;
+    o.camToBody[0] = b.y, o.camToBody[1] = c.x, o.camToBody[2] = c.y;
+    o.camToBody[3] = d.x, o.camToBody[4] = d.y, o.camToBody[5] = f.x;
+    o.camToBody[6] = f.y, o.camToBody[7] = g.x, o.camToBody[8] = g.y;
+    return;
+  }
   const double *e = C.entries + (long)(frameletNumber + 1) * C.stride;
 #pragma unroll
   for (int i = 0; i < 3; i++) o.pos[i] = e[i];
@@ -121,6 +131,7 @@ UB_DEV void viewFromOrientation(const LsState &S, const Orientation &o, double g
 // the attitude correction is live).  All threads of the block call it.
 __device__ inline OrientCache stageOrientCache(const LsState &S, double *smem, bool stage) {
   OrientCache c;
+  c.pairs = false;
   if (!S.frameletOrient) {
     c.entries = nullptr;
     c.stride = 0;
@@ -140,6 +151,7 @@ __device__ inline OrientCache stageOrientCache(const LsState &S, double *smem, b
   __syncthreads();
   c.entries = smem;
   c.stride = stride;
+  c.pairs = stride == 12;
   return c;
 }
 
@@ -277,7 +289,7 @@ __global__ void __launch_bounds__(kThreads, UB_PF_G2I_MINB)
                           double *__restrict__ line, double *__restrict__ samp,
                           double *__restrict__ achieved, uint32_t *__restrict__ status,
                           unsigned long long *__restrict__ next, int grab) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   forEachPointDynamic(n, next, grab, [&](long i) {
@@ -392,7 +404,7 @@ __global__ void __launch_bounds__(kThreads, UB_PF_I2G_MINB)
                           const double *__restrict__ height, int heightStride, double prec,
                           double *__restrict__ x, double *__restrict__ y, double *__restrict__ z,
                           double *__restrict__ achieved, uint32_t *__restrict__ status) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   const double rh = DIST >= 0 ? refinedReciprocal((double)S.summedFrameletHeight) : 0.0;
@@ -441,7 +453,7 @@ __global__ void __launch_bounds__(kThreads)
                            const double *__restrict__ y, const double *__restrict__ z,
                            double *__restrict__ partials, uint32_t *__restrict__ status,
                            unsigned long long *__restrict__ next, int grab) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   forEachPointDynamic(n, next, grab, [&](long i) {
@@ -515,7 +527,7 @@ template <bool STAGE>
 __global__ void __launch_bounds__(kThreads)
     pfRemoteLocusKernel(const __grid_constant__ LsState S, long n, const double *__restrict__ line,
                         const double *__restrict__ samp, LocusOut o) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   const long stride = (long)gridDim.x * blockDim.x;
@@ -534,7 +546,7 @@ __global__ void __launch_bounds__(kThreads)
                            const double *__restrict__ samp, const double *__restrict__ x,
                            const double *__restrict__ y, const double *__restrict__ z, double prec,
                            LocusOut o) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   OrientCache C = stageOrientCache(S, smem, STAGE);
   OrientationTables T{S.positions.values, S.velocities.values, S.quaternions.values};
   const long stride = (long)gridDim.x * blockDim.x;
