@@ -226,13 +226,13 @@ __global__ void __launch_bounds__(kThreads, UB_FR_I2G_MINB)
   // dense grid (its rows hold a whole number of packs, the launcher checks): (row, column) of
   // the thread's pack, advanced by the stride's (rows, columns) instead of a division per point
   long r = 0, strideRows = 0;
-  int c = 0, strideCols = 0;
+  long c = 0, strideCols = 0;
   if (GRID) {
     const long perRow = g.nSamps / VEC;
     r = first / perRow;
-    c = (int)(first - r * perRow) * VEC;
+    c = (first - r * perRow) * VEC;
     strideRows = stride / perRow;
-    strideCols = (int)(stride - strideRows * perRow) * VEC;
+    strideCols = (stride - strideRows * perRow) * VEC;
   }
   for (long p = first; p < packs; p += stride) {
     D lv, sv, hv;
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(kThreads, UB_FR_I2G_MINB)
       r += strideRows;
       c += strideCols;
       if (c >= g.nSamps) {
-        c -= (int)g.nSamps;
+        c -= g.nSamps;
         r++;
       }
     }
@@ -460,7 +460,7 @@ static bool frSpecialise() {
   do {                                                                           \
     if (!frSpecialise() || S.numLineTimes) LAUNCH(-1, true, 1);                  \
     else if (S.fp.distortionType == DIST_RADIAL) LAUNCH(DIST_RADIAL, false, VEC);         \
-    else if (S.fp.distortionType == DIST_TRANSVERSE) LAUNCH(DIST_TRANSVERSE, false, VEC); \
+    else if (S.fp.distortionType == DIST_TRANSVERSE && transverseCoeffsPlain(S.fp)) LAUNCH(DIST_TRANSVERSE, false, VEC); \
     else LAUNCH(-1, false, 1);                                                   \
   } while (0)
 
@@ -510,7 +510,7 @@ cudaError_t launchFrImageToGround(const FrameState &S, int smCount, long n, cons
   const bool pairs = frPairable({x, y, z, achieved, heightStride ? height : nullptr,
                                  grid ? nullptr : line, grid ? nullptr : samp}, status);
   if (grid) {
-    // rows of an even number of samples, fewer than 2^31 rows and columns
+    // rows of an even number of samples
     if (pairs && g.nSamps % 2 == 0)
       UB_FR_DISPATCH(UB_FR_I2G_GRID, 2);
     else

@@ -309,7 +309,7 @@ bool launchLsAllSensorPartials(const LsState &S, int smCount, int nIndices, cons
     if (!common) UB_LAUNCH_AP(STAGE, -1);                                 \
     else if (S.fp.distortionType == 4) UB_LAUNCH_AP(STAGE, 4);            \
     else if (S.fp.distortionType == 0) UB_LAUNCH_AP(STAGE, 0);            \
-    else if (S.fp.distortionType == 1) UB_LAUNCH_AP(STAGE, 1);            \
+    else if (S.fp.distortionType == 1 && transverseCoeffsPlain(S.fp)) UB_LAUNCH_AP(STAGE, 1);            \
     else UB_LAUNCH_AP(STAGE, -1);                                         \
   } while (0)
   if (stage)

@@ -656,7 +656,7 @@ static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long
     if (!common) UB_LAUNCH_G2I(STAGE, -1, 0);                                                 \
     else if (S.fp.distortionType == 4) UB_LAUNCH_G2I_ADJ(STAGE, 4); /* LROLROCNAC */          \
     else if (S.fp.distortionType == 0) UB_LAUNCH_G2I_ADJ(STAGE, 0); /* RADIAL */              \
-    else if (S.fp.distortionType == 1) UB_LAUNCH_G2I_ADJ(STAGE, 1); /* TRANSVERSE */          \
+    else if (S.fp.distortionType == 1 && transverseCoeffsPlain(S.fp)) UB_LAUNCH_G2I_ADJ(STAGE, 1); /* TRANSVERSE */          \
     else UB_LAUNCH_G2I(STAGE, -1, 0);                                                         \
   } while (0)
   // USGSCSM_B200_LS_SPECIALISE: 1 = specialise (default), 2 = only models without parameter
@@ -905,7 +905,7 @@ cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const 
     if (!common) UB_LAUNCH_GP(STAGE, -1);                                                     \
     else if (S.fp.distortionType == 4) UB_LAUNCH_GP(STAGE, 4);                                \
     else if (S.fp.distortionType == 0) UB_LAUNCH_GP(STAGE, 0);                                \
-    else if (S.fp.distortionType == 1) UB_LAUNCH_GP(STAGE, 1);                                \
+    else if (S.fp.distortionType == 1 && transverseCoeffsPlain(S.fp)) UB_LAUNCH_GP(STAGE, 1);                                \
     else UB_LAUNCH_GP(STAGE, -1);                                                             \
   } while (0)
   static const int specialise = envInt("USGSCSM_B200_LS_SPECIALISE", 1);

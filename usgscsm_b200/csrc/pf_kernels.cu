@@ -665,7 +665,7 @@ cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const d
   do {                                                                                    \
     if (!pfSpecialise() || !pfFrameletNumbersExact(S)) UB_PF_G2I(STAGE, -1, -1);          \
     else if (S.fp.distortionType == DIST_RADIAL) UB_PF_G2I_ATT(STAGE, DIST_RADIAL);       \
-    else if (S.fp.distortionType == DIST_TRANSVERSE) UB_PF_G2I_ATT(STAGE, DIST_TRANSVERSE); \
+    else if (S.fp.distortionType == DIST_TRANSVERSE && transverseCoeffsPlain(S.fp)) UB_PF_G2I_ATT(STAGE, DIST_TRANSVERSE); \
     else UB_PF_G2I(STAGE, -1, -1);                                                        \
   } while (0)
   if (stage)
@@ -700,7 +700,7 @@ cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const d
   do {                                                                                            \
     if (!pfSpecialise() || S.summedFrameletHeight < 1) UB_PF_I2G(STAGE, GRID, -1, -1);            \
     else if (S.fp.distortionType == DIST_RADIAL) UB_PF_I2G_ATT(STAGE, GRID, DIST_RADIAL);         \
-    else if (S.fp.distortionType == DIST_TRANSVERSE) UB_PF_I2G_ATT(STAGE, GRID, DIST_TRANSVERSE); \
+    else if (S.fp.distortionType == DIST_TRANSVERSE && transverseCoeffsPlain(S.fp)) UB_PF_I2G_ATT(STAGE, GRID, DIST_TRANSVERSE); \
     else UB_PF_I2G(STAGE, GRID, -1, -1);                                                          \
   } while (0)
   if (stage && grid)
