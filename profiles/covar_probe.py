@@ -1,4 +1,4 @@
-"""groundToImage with covariance (22 searches per point) on 4 Mi points of the C2 model: wall time
+"""groundToImage with covariance (22 searches per point) on 8 Mi points of the C2 model: wall time
 per call; under `ncu --metrics gpu__time_duration.sum` the launch list shows where it goes."""
 import os
 import sys
@@ -10,8 +10,8 @@ from usgscsm_b200 import _capi, synth
 
 dev = torch.device("cuda:0")
 gm = ub.UsgsAstroPlugin().constructModelFromState(synth.linescan_state())
-n = 1 << 22
-nl, ns = 832, 5042
+n = 1 << 23
+nl, ns = 1664, 5042
 h = torch.zeros(nl * ns, dtype=torch.float64, device=dev)
 x, y, z, _, _ = gm.imageToGroundGrid(20000.5, 10.5, 1.0, 1.0, nl, ns, h, achieved=False)
 x, y, z = x[:n].contiguous(), y[:n].contiguous(), z[:n].contiguous()

@@ -19,7 +19,7 @@ namespace ub200 {
 namespace {
 
 constexpr int kMaxParams = 16;
-constexpr long kCovarBatch = 1L << 22;  // points per internal pass (bounds the scratch)
+constexpr long kCovarBatch = 1L << 23;  // points per internal pass (bounds the scratch: 2.6 GB)
 
 struct ParamCov {
   int numParams;
@@ -275,9 +275,15 @@ int groundToImageCovarDev(usgscsm_b200_model *m, long n, const double *x, const 
     UB_CUDA(launchGroundToImage(*m, cnt, x + off, y + off, z + off, prec, line + off, samp + off,
                                 ach, st, stream));
     UB_CUDA(launchGroundPartials(*m, cnt, x + off, y + off, z + off, prt, stP, stream));
-    // computeAllSensorPartials(gp): default arguments, i.e. precision 0.001 (LS:1034-1035)
-    allSensorPartialsDev(m, P, nullptr, cnt, x + off, y + off, z + off, nullptr, nullptr, 0.001, sp,
-                         nullptr, stS, stream);
+    // computeAllSensorPartials(gp): default arguments, i.e. precision 0.001 (LS:1034-1035): it
+    // starts with groundToImage(gp, 0.001) -- the search just made when the caller's precision is
+    // 0.001 too (the default), whose image point is then handed over instead of searched again
+    // (its status is in `st`, which the combining kernel reads beside stS)
+    const bool sameBase = prec == 0.001;
+    const int rcPartials =
+        allSensorPartialsDev(m, P, nullptr, cnt, x + off, y + off, z + off, sameBase ? line + off : nullptr,
+                             sameBase ? samp + off : nullptr, 0.001, sp, nullptr, stS, stream);
+    if (rcPartials != USGSCSM_B200_OK) return rcPartials;
     groundToImageCovarKernel<<<gridFor(cnt), 256, 0, stream>>>(
         cnt, C, groundCov + off * 9, prt, sp, stP, stS, line + off, samp + off, imageCov + off * 4,
         ach, st);
