@@ -589,14 +589,24 @@ __global__ void pfSensorStateKernel(const __grid_constant__ LsState S, long n,
   }
 }
 
-LaunchShape pfShape(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage) {
+LaunchShape pfShape(const LsState &S, long n, int smCount, size_t &smemBytes, bool &stage,
+                    bool staticSplit = false) {
   size_t bytes = S.frameletOrient ? orientCacheBytes(S) : 0;
   stage = bytes > 0 && bytes <= kMaxStagedTableBytes;
   smemBytes = stage ? bytes : 0;
   LaunchShape sh;
   sh.threads = kThreads;
   long blocksNeeded = (n + kThreads - 1) / kThreads;
-  long persistent = (long)smCount * (UB_PF_G2I_MINB > kBlocksPerSm ? UB_PF_G2I_MINB : kBlocksPerSm);
+  // staticSplit: the kernel splits its points statically over the grid (imageToGround); two
+  // short waves of blocks (USGSCSM_B200_PF_WAVES) balance the tail of a sub-millisecond launch
+  // (one 4096^2 image: +10 %).  The searches take their points from a queue: one wave.
+  static const int envWaves = [] {
+    const char *v = getenv("USGSCSM_B200_PF_WAVES");
+    const int w = v && *v ? atoi(v) : 2;
+    return w < 1 ? 1 : w;
+  }();
+  const int waves = staticSplit ? envWaves : 1;
+  long persistent = (long)smCount * (UB_PF_G2I_MINB > kBlocksPerSm ? UB_PF_G2I_MINB : kBlocksPerSm) * waves;
   sh.blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
   if (sh.blocks < 1) sh.blocks = 1;
   return sh;
@@ -686,7 +696,7 @@ cudaError_t launchPfImageToGround(const LsState &S, int smCount, long n, const d
   if (n <= 0) return cudaSuccess;
   size_t smemBytes;
   bool stage;
-  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
+  LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage, true);
   GridSpec g = grid ? *grid : GridSpec{0, 0, 0, 0, 1, 0};
 #define UB_PF_I2G(STAGE, GRID, DIST, ATT)                                                       \
   pfImageToGroundKernel<STAGE, GRID, DIST, ATT><<<sh.blocks, sh.threads, smemBytes, stream>>>(  \
