@@ -291,7 +291,7 @@ bool launchLsAllSensorPartials(const LsState &S, int smCount, int nIndices, cons
   long persistent = (long)smCount * mb;
   const int blocks = (int)(blocksNeeded < persistent ? blocksNeeded : persistent);
   WorkCounter wc;
-  err = wc.acquire(stream);
+  err = wc.acquire(stream, n);
   if (err != cudaSuccess) return true;
   static const int specialise = envInt("USGSCSM_B200_LS_SPECIALISE", 1);
   const bool common = specialise == 1 && S.numIntTimes == 1 && S.useApproxInitTrans;

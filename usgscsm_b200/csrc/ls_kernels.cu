@@ -633,7 +633,7 @@ static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long
   // different streams never share one
   const int grab = grabSize();
   WorkCounter wc;
-  cudaError_t e = wc.acquire(stream);
+  cudaError_t e = wc.acquire(stream, n);
   if (e != cudaSuccess) return e;
   unsigned long long *next = wc.ptr;
 #define UB_LAUNCH_G2I(STAGE, DIST, ADJ)                                                       \
@@ -890,7 +890,7 @@ cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const 
   bool stage;
   LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kDefaultMinBlocks);
   WorkCounter wc;
-  cudaError_t e = wc.acquire(stream);
+  cudaError_t e = wc.acquire(stream, n);
   if (e != cudaSuccess) return e;
 #define UB_LAUNCH_GP(STAGE, DIST)                                                              \
   do {                                                                                        \

@@ -661,7 +661,7 @@ cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const d
   bool stage;
   LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
   WorkCounter wc;
-  cudaError_t e = wc.acquire(stream);
+  cudaError_t e = wc.acquire(stream, n);
   if (e != cudaSuccess) return e;
 #define UB_PF_G2I(STAGE, DIST, ATT)                                                          \
   pfGroundToImageKernel<STAGE, DIST, ATT><<<sh.blocks, sh.threads, STAGE ? smemBytes : 0, stream>>>( \
@@ -750,7 +750,7 @@ cudaError_t launchGroundPartialsPf(const LsState &S, int smCount, long n, const 
   bool stage;
   LaunchShape sh = pfShape(S, n, smCount, smemBytes, stage);
   WorkCounter wc;
-  cudaError_t e = wc.acquire(stream);
+  cudaError_t e = wc.acquire(stream, n);
   if (e != cudaSuccess) return e;
   if (stage)
     pfGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(

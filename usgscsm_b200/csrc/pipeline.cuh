@@ -58,6 +58,8 @@ long stagedChunk();      // USGSCSM_B200_STAGE_CHUNK (default 256 Ki points)
 bool hostPointerPageable(const void *p);
 
 inline long roundUp16(long bytes) { return (bytes + 15) & ~15L; }
+constexpr long kSmallCall = 4096;  // points at or below which a host-pointer call takes the single-copy path
+constexpr long kZeroCopyCall = 64;  // ... and at or below which the kernels work on the page-locked block directly
 
 // launch(chunk) enqueues the kernels of one chunk on chunk.stream and returns a cudaError_t.
 // workPerPoint: extra device doubles per point the launch needs (AoS split / join).
@@ -72,6 +74,66 @@ int runPipelined(usgscsm_b200_model *m, int64_t n, const std::vector<HostIn> &in
     // per-point calls are re-entrant, include/usgscsm/UsgsAstroLsSensorModel.h:910-914)
     std::lock_guard<std::mutex> oneCallPerModel(m->hostCallMutex);
     UB_CUDA(cudaSetDevice(m->device));
+    // A handful of points (the scalar calls of a CSM application arrive here as batches of one):
+    // latency is all that counts.  Everything goes through the model's page-locked block laid out
+    // like the device scratch -- ONE copy up, the kernels, ONE copy down, on the calling thread.
+    if (n <= kSmallCall && granule <= n) {
+      const long cnt = (long)n;
+      long inBytes = 0;
+      for (const HostIn &a : ins) inBytes += roundUp16(cnt * a.bytesPerPoint);
+      long total = inBytes;
+      for (const HostOut &a : outs) total += roundUp16(cnt * a.perPoint * 8);
+      total += (long)workPerPoint * roundUp16(cnt * 8) + roundUp16(cnt * 4);
+      m->ensureScratch(0, (total + 7) / 8);
+      m->ensureStage(0, total);
+      PipelineSlot &s = m->slots[0];
+      char *stage = static_cast<char *>(s.stage);
+      // A few points: the kernels read and write the page-locked block itself (it is mapped into
+      // the device's address space under unified addressing) -- no copy at all, a launch and a
+      // synchronisation.  Beyond that the block is copied (latency-bound reads over the link cost
+      // more than one DMA transfer).
+      const bool zeroCopy = n <= kZeroCopyCall;
+      char *base = zeroCopy ? stage : reinterpret_cast<char *>(s.scratch);
+      Chunk k;
+      k.offset = 0;
+      k.count = cnt;
+      k.stream = s.stream;
+      long off = 0;
+      for (const HostIn &a : ins) {
+        k.in.push_back(reinterpret_cast<double *>(base + off));
+        if (a.broadcast) {
+          std::memcpy(stage + off, a.p, (size_t)a.bytesPerPoint);
+        } else if (a.rowPoints > 0) {
+          const long rows = cnt / a.rowPoints;
+          const size_t width = (size_t)a.rowPoints * a.bytesPerPoint;
+          for (long r = 0; r < rows; r++)
+            std::memcpy(stage + off + r * width, static_cast<const char *>(a.p) + r * a.rowPitchBytes, width);
+        } else {
+          std::memcpy(stage + off, a.p, (size_t)cnt * a.bytesPerPoint);
+        }
+        off += roundUp16(cnt * a.bytesPerPoint);
+      }
+      for (const HostOut &a : outs) {
+        k.out.push_back(a.p ? reinterpret_cast<double *>(base + off) : nullptr);
+        off += roundUp16(cnt * a.perPoint * 8);
+      }
+      for (int w = 0; w < workPerPoint; w++, off += roundUp16(cnt * 8))
+        k.work.push_back(reinterpret_cast<double *>(base + off));
+      k.status = status ? reinterpret_cast<uint32_t *>(base + off) : nullptr;
+      if (!zeroCopy && inBytes > 0)
+        UB_CUDA(cudaMemcpyAsync(base, stage, (size_t)inBytes, cudaMemcpyHostToDevice, s.stream));
+      UB_CUDA(launch(k));
+      if (!zeroCopy)
+        UB_CUDA(cudaMemcpyAsync(stage + inBytes, base + inBytes, (size_t)(total - inBytes), cudaMemcpyDeviceToHost,
+                                s.stream));
+      UB_CUDA(cudaStreamSynchronize(s.stream));
+      for (size_t j = 0; j < outs.size(); j++)
+        if (outs[j].p)
+          std::memcpy(outs[j].p, stage + (reinterpret_cast<char *>(k.out[j]) - base),
+                      (size_t)cnt * outs[j].perPoint * 8);
+      if (status) std::memcpy(status, stage + (reinterpret_cast<char *>(k.status) - base), cnt * sizeof(uint32_t));
+      return USGSCSM_B200_OK;
+    }
     bool pageableIn = false, pageableOut = false;
     for (const HostIn &a : ins)
       if (!a.broadcast) {

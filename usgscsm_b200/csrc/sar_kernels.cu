@@ -667,7 +667,7 @@ cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const
 #define UB_SAR_G2I(KERNEL, STAGE, PAD, MINB)                                                      \
   do {                                                                                            \
     e = allowSmem(KERNEL<STAGE, PAD, MINB>, smemBytes);                                           \
-    if (e == cudaSuccess) e = wc.acquire(stream);                                                 \
+    if (e == cudaSuccess) e = wc.acquire(stream, refill ? -1 : n);                                                 \
     if (e == cudaSuccess)                                                                         \
       KERNEL<STAGE, PAD, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(                     \
           S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());                 \
@@ -711,7 +711,7 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
     if (ea != cudaSuccess) return ea;
   }
   WorkCounter wc;
-  cudaError_t e0 = wc.acquire(stream);
+  cudaError_t e0 = wc.acquire(stream, n);
   if (e0 != cudaSuccess) return e0;
 #define UB_LAUNCH_SAR(STAGE, GRID)                                                          \
   do {                                                                                      \
@@ -762,7 +762,7 @@ cudaError_t launchGroundPartialsSar(const SarState &S, int smCount, long n, cons
     if (e != cudaSuccess) return e;
   }
   WorkCounter wc;
-  cudaError_t e = wc.acquire(stream);
+  cudaError_t e = wc.acquire(stream, n);
   if (e != cudaSuccess) return e;
   if (stage)
     sarGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
