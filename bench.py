@@ -1263,11 +1263,11 @@ def run_c5(ctx):
         n_e2e = len(e2e_images) * lines * N_SAMPLES
         # Row bands sized to what each rank's host link sustains: the ranks of one box share the
         # host's PCIe complex unevenly (per-rank rates under load are in link_per_rank), and with
-        # equal bands the job waits for the slowest link.  Two passes with the current bands give
+        # equal bands the job waits for the slowest link.  Three passes with the current bands give
         # each rank's rate; the timed run uses the bands proportional to them.
         bands = sharding.row_bands(lines, world)
         history = []
-        for _ in range(2 if world > 1 else 0):
+        for _ in range(3 if world > 1 else 0):
             probe = e2e_dem_grid(ctx, e2e_models, full, lines, n_e2e, link, steps=1, bands=bands)
             rates = gather_floats(bands[rank][1] / probe["own_seconds"])
             history.append({"band_lines": [b for _, b in bands], "value": probe["value"]})
