@@ -631,7 +631,7 @@ static cudaError_t launchLsGroundToImageFrom(const LsState &S, int smCount, long
   LaunchShape sh = shapeFor(S, n, smCount, smemBytes, stage, kDefaultMinBlocks);
   // work counter of this launch: stream-ordered scratch, so that launches in flight on
   // different streams never share one
-  const int grab = grabSize();
+  const int grab = grabFor(n);
   WorkCounter wc;
   cudaError_t e = wc.acquire(stream, n);
   if (e != cudaSuccess) return e;
@@ -898,7 +898,7 @@ cudaError_t launchGroundPartialsLs(const LsState &S, int smCount, long n, const 
       cudaFuncSetAttribute(lsGroundPartialsKernel<STAGE, DIST>,                               \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);      \
     lsGroundPartialsKernel<STAGE, DIST><<<sh.blocks, sh.threads, smemBytes, stream>>>(        \
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());                                 \
+        S, n, x, y, z, partials, status, wc.ptr, grabFor(n));                                 \
   } while (0)
 #define UB_LAUNCH_GP_DIST(STAGE)                                                              \
   do {                                                                                        \

@@ -665,7 +665,7 @@ cudaError_t launchPfGroundToImage(const LsState &S, int smCount, long n, const d
   if (e != cudaSuccess) return e;
 #define UB_PF_G2I(STAGE, DIST, ATT)                                                          \
   pfGroundToImageKernel<STAGE, DIST, ATT><<<sh.blocks, sh.threads, STAGE ? smemBytes : 0, stream>>>( \
-      S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize())
+      S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabFor(n))
 #define UB_PF_G2I_ATT(STAGE, DIST)                \
   do {                                            \
     if (S.hasAttAdj) UB_PF_G2I(STAGE, DIST, 1);   \
@@ -754,10 +754,10 @@ cudaError_t launchGroundPartialsPf(const LsState &S, int smCount, long n, const 
   if (e != cudaSuccess) return e;
   if (stage)
     pfGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+        S, n, x, y, z, partials, status, wc.ptr, grabFor(n));
   else
     pfGroundPartialsKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+        S, n, x, y, z, partials, status, wc.ptr, grabFor(n));
   countLaunch();
   return wc.release();
 }

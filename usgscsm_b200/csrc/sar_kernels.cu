@@ -670,7 +670,7 @@ cudaError_t launchSarGroundToImage(const SarState &S, int smCount, long n, const
     if (e == cudaSuccess) e = wc.acquire(stream, refill ? -1 : n);                                                 \
     if (e == cudaSuccess)                                                                         \
       KERNEL<STAGE, PAD, MINB><<<sh.blocks, sh.threads, smemBytes, stream>>>(                     \
-          S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabSize());                 \
+          S, n, x, y, z, prec, line, samp, achieved, status, wc.ptr, grabFor(n));                 \
   } while (0)
 #define UB_SAR_G2I_M(KERNEL, STAGE, PAD)            \
   do {                                              \
@@ -717,7 +717,7 @@ cudaError_t launchSarImageToGround(const SarState &S, int smCount, long n, const
   do {                                                                                      \
     sarImageToGroundKernel<STAGE, GRID><<<sh.blocks, sh.threads, smemBytes, stream>>>(      \
         S, n, line, samp, g, height, heightStride, prec, x, y, z, achieved, status, wc.ptr, \
-        grabSize());                                                                        \
+        grabFor(n));                                                                        \
   } while (0)
   if (stage && grid)
     UB_LAUNCH_SAR(true, true);
@@ -766,10 +766,10 @@ cudaError_t launchGroundPartialsSar(const SarState &S, int smCount, long n, cons
   if (e != cudaSuccess) return e;
   if (stage)
     sarGroundPartialsKernel<true><<<sh.blocks, sh.threads, smemBytes, stream>>>(
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+        S, n, x, y, z, partials, status, wc.ptr, grabFor(n));
   else
     sarGroundPartialsKernel<false><<<sh.blocks, sh.threads, 0, stream>>>(
-        S, n, x, y, z, partials, status, wc.ptr, grabSize());
+        S, n, x, y, z, partials, status, wc.ptr, grabFor(n));
   countLaunch();
   return wc.release();
 }
