@@ -293,6 +293,38 @@ def measure_link(dev, barrier, nbytes=1 << 30, reps=4):
     res = {"h2d_gbs_alone": run(True, False), "d2h_gbs_alone": run(False, True)}
     both = run(True, True)
     res["h2d_gbs_duplex"] = res["d2h_gbs_duplex"] = both
+    # the DEM-grid call's own traffic mix, copies only: 4 bytes up for every 20 down, both at once
+    up_view, up_dst = h_in[:nbytes // 5], d_in[:nbytes // 5]
+    barrier()
+    t = time.perf_counter()
+    for _ in range(reps):
+        with torch.cuda.stream(s1):
+            up_dst.copy_(up_view, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True)
+    s1.synchronize()
+    s2.synchronize()
+    res["d2h_gbs_mix_4_up_20_down"] = nbytes * reps / (time.perf_counter() - t) / 1e9
+    # The same mix for a fixed WINDOW of time instead of a fixed volume: with several ranks on one
+    # host the fixed-volume figures above flatter the slower links (the faster ranks finish first
+    # and leave them the host to themselves); here every rank copies until the window closes.
+    piece = min(nbytes, 256 << 20)
+    window = 0.75
+    barrier()
+    t = time.perf_counter()
+    moved = 0
+    while True:
+        with torch.cuda.stream(s1):
+            d_in[:piece // 5].copy_(h_in[:piece // 5], non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_out[:piece].copy_(d_out[:piece], non_blocking=True)
+        s2.synchronize()
+        s1.synchronize()
+        moved += piece
+        dt = time.perf_counter() - t
+        if dt >= window:
+            break
+    res["d2h_gbs_mix_sustained"] = moved / dt / 1e9
     del h_in, h_out, d_in, d_out
     return res
 
@@ -912,9 +944,12 @@ def other_configs(dev, fp64, ops, with_cpu):
 def link_fraction(h2d_bytes, d2h_bytes, seconds, link):
     """Share of the measured duplex link rate the call sustained, for the direction that binds."""
     up, down = h2d_bytes / seconds / 1e9, d2h_bytes / seconds / 1e9
-    return {"h2d_gbs": up, "d2h_gbs": down,
-            "frac_of_link": max(up / link["h2d_gbs_alone"], down / link["d2h_gbs_alone"]),
-            "link": link}
+    res = {"h2d_gbs": up, "d2h_gbs": down,
+           "frac_of_link": max(up / link["h2d_gbs_alone"], down / link["d2h_gbs_alone"]),
+           "link": link}
+    if "d2h_gbs_mix_4_up_20_down" in link and h2d_bytes * 5 == d2h_bytes:
+        res["frac_of_link_same_mix"] = down / link["d2h_gbs_mix_4_up_20_down"]   # against copies of the same mix
+    return res
 
 
 def e2e_dem_grid(ctx, models, dems, lines, n_job, link, steps=None, bands=None):
@@ -1263,23 +1298,28 @@ def run_c5(ctx):
         n_e2e = len(e2e_images) * lines * N_SAMPLES
         # Row bands sized to what each rank's host link sustains: the ranks of one box share the
         # host's PCIe complex unevenly (per-rank rates under load are in link_per_rank), and with
-        # equal bands the job waits for the slowest link.  Three passes with the current bands give
+        # equal bands the job waits for the slowest link.  Five passes with the current bands give
         # each rank's rate; the timed run uses the bands proportional to them.
         bands = sharding.row_bands(lines, world)
         history = []
-        for _ in range(3 if world > 1 else 0):
+        for _ in range(5 if world > 1 else 0):
             probe = e2e_dem_grid(ctx, e2e_models, full, lines, n_e2e, link, steps=1, bands=bands)
             rates = gather_floats(bands[rank][1] / probe["own_seconds"])
             history.append({"band_lines": [b for _, b in bands], "value": probe["value"]})
             bands = sharding.weighted_row_bands(lines, rates)
         e = e2e_dem_grid(ctx, e2e_models, full, lines, n_e2e, link, steps=max(1, min(2, args.steps)), bands=bands)
         e["band_lines_by_rank"] = [b for _, b in bands]
+        e["seconds_per_step_by_rank"] = gather_floats(e["own_seconds"])   # how even the sized bands finish
         e["band_sizing_passes"] = history
         e["link_per_rank"] = {k: gather_floats(v) for k, v in link.items()}
         e["images_per_step"] = len(e2e_images)
         e["link_all_ranks"] = agg
         e["frac_of_box_link"] = max(sum_over_ranks(e["h2d_gbs"]) / agg["h2d_gbs_alone"],
                                     sum_over_ranks(e["d2h_gbs"]) / agg["d2h_gbs_alone"])
+        # against what the box sustains when every rank only COPIES the same 4-up / 20-down mix
+        e["frac_of_box_link_same_mix"] = sum_over_ranks(e["d2h_gbs"]) / agg["d2h_gbs_mix_4_up_20_down"]
+        # ... and when every rank keeps copying for the same window of time (the sustained ceiling)
+        e["frac_of_box_link_sustained"] = sum_over_ranks(e["d2h_gbs"]) / agg["d2h_gbs_mix_sustained"]
         if rank == 0:
             result["e2e"] = e
     return result
